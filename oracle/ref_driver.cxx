@@ -1,0 +1,205 @@
+/* oracle/ref_driver.cxx  --  TEST INFRASTRUCTURE ONLY.
+ *
+ * A thin extern "C" bridge that lets the parity tests (ctypes) and bench.py's reference arm call the
+ * UNMODIFIED VELOCIraptor reference functions that the GPU path replaces:
+ *
+ *   vrref_kdfof            -> NBody::KDTree::FOF                 (NBodylib/src/KDTree/KDFOF.cxx:12)
+ *   vrref_search_full_set  -> SearchFullSet                       (src/search.cxx:24)
+ *   vrref_potential        -> Potential(Options&,Int_t,Particle*) (src/unbind.cxx:1607)
+ *   vrref_unbind           -> CheckUnboundGroups                  (src/unbind.cxx:196)
+ *
+ * It is compiled against the reference headers where they lie and linked with the reference's own
+ * objects into oracle/_ref/libvrref*.so (see oracle/Makefile).  Nothing here re-implements the
+ * algorithms; it only marshals flat arrays into NBody::Particle and back.
+ */
+#include "stf.h"
+#include <chrono>
+
+using namespace std;
+using namespace NBody;
+
+extern "C" {
+
+/* Options subset that steers the hot path.  Field meaning = the reference Options member cited. */
+typedef struct {
+    double period;            /* Options::p (0 = open box)                         allvars.h */
+    double ellxscale;         /* Options::ellxscale  (LN for cosmological input)  gadgetio.cxx:1417 */
+    double ellphys;           /* Options::ellphys                                  */
+    double ellhalophysfac;    /* Options::ellhalophysfac (ui.cxx:901-906)          */
+    double ellhalo6dxfac;     /* Options::ellhalo6dxfac                            */
+    double ellhalo6dvfac;     /* Options::ellhalo6dvfac                            */
+    long long halo_min_size;  /* Options::HaloMinSize                              */
+    long long min_size;       /* Options::MinSize                                  */
+    int fofbgtype;            /* Options::fofbgtype: 5 FOF3D, 4 FOF6D, 3 FOF6DADAPTIVE (allvars.h) */
+    int bound_halos;          /* Options::iBoundHalos                              */
+    int omp_fof;              /* Options::iopenmpfof                               */
+    long long omp_fof_size;   /* Options::openmpfofsize (<=0: keep default)        */
+    /* UnbindInfo */
+    double G;                 /* Options::G                                        */
+    double eps;               /* uinfo.eps (already multiplied by LN)              */
+    double Eratio;            /* uinfo.Eratio                                      */
+    double minEfrac;          /* uinfo.minEfrac                                    */
+    int unbindtype;           /* uinfo.unbindtype: 0 USYSANDPART, 1 UPART          */
+    int bgpot;                /* uinfo.bgpot                                       */
+    int cmvelreftype;         /* uinfo.cmvelreftype                                */
+    double fracpotref;        /* uinfo.fracpotref                                  */
+    long long Npotref;        /* uinfo.Npotref                                     */
+    double maxunbindfrac;     /* uinfo.maxunbindfrac                               */
+    double maxunboundfracforiterativeunbind;
+    double maxallowedunboundfrac;
+    double TreeThetaOpen;     /* uinfo.TreeThetaOpen                               */
+    int BucketSize;           /* uinfo.BucketSize                                  */
+    int verbose;
+} vrref_opts;
+
+static void fill_options(Options &opt, const vrref_opts *o)
+{
+    opt.p = o->period;
+    opt.ellxscale = o->ellxscale;
+    opt.ellphys = o->ellphys;
+    opt.ellhalophysfac = o->ellhalophysfac;
+    opt.ellhalo6dxfac = o->ellhalo6dxfac;
+    opt.ellhalo6dvfac = o->ellhalo6dvfac;
+    opt.HaloMinSize = o->halo_min_size;
+    opt.MinSize = o->min_size;
+    opt.fofbgtype = o->fofbgtype;
+    opt.iBoundHalos = o->bound_halos;
+    opt.iopenmpfof = o->omp_fof;
+    if (o->omp_fof_size > 0) opt.openmpfofsize = o->omp_fof_size;
+    opt.iSubSearch = 0;
+    opt.iKeepFOF = 0;
+    opt.iBaryonSearch = 0;
+    opt.partsearchtype = PSTALL;
+    opt.iverbose = o->verbose;
+    opt.G = o->G;
+    opt.uinfo.eps = o->eps;
+    opt.uinfo.Eratio = o->Eratio;
+    opt.uinfo.minEfrac = o->minEfrac;
+    opt.uinfo.unbindtype = o->unbindtype;
+    opt.uinfo.bgpot = o->bgpot;
+    opt.uinfo.cmvelreftype = o->cmvelreftype;
+    opt.uinfo.fracpotref = o->fracpotref;
+    opt.uinfo.Npotref = o->Npotref;
+    opt.uinfo.maxunbindfrac = o->maxunbindfrac;
+    opt.uinfo.maxunboundfracforiterativeunbind = o->maxunboundfracforiterativeunbind;
+    opt.uinfo.maxallowedunboundfrac = o->maxallowedunboundfrac;
+    opt.uinfo.TreeThetaOpen = o->TreeThetaOpen;
+    opt.uinfo.BucketSize = o->BucketSize;
+    opt.uinfo.icalculatepotential = true;
+    opt.uinfo.unbindflag = 1;
+}
+
+static void fill_particles(vector<Particle> &P, long long n, const double *pos, const double *vel,
+                           const double *mass, const long long *pid)
+{
+    P.resize(n);
+    for (long long i = 0; i < n; i++) {
+        P[i].SetPosition(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
+        if (vel) P[i].SetVelocity(vel[3 * i], vel[3 * i + 1], vel[3 * i + 2]);
+        else P[i].SetVelocity(0., 0., 0.);
+        P[i].SetMass(mass ? mass[i] : 1.0);
+        P[i].SetPID(pid ? pid[i] : i);
+        P[i].SetID(i);
+        P[i].SetType(DARKTYPE);
+        P[i].SetDensity(0.);
+        P[i].SetPotential(0.);
+    }
+}
+
+size_t vrref_sizeof_particle(void) { return sizeof(Particle); }
+int vrref_has_openmp(void)
+{
+#ifdef USEOPENMP
+    return 1;
+#else
+    return 0;
+#endif
+}
+int vrref_unbindnum(void) { return UNBINDNUM; }
+
+/* Direct call of KDTree::FOF.  ndim = 3 (TPHYS, optional period) or 6 (TPHS, non periodic).
+ * Returns number of groups; pfof_out[i] for input index i (order=1 -> size ordered). */
+long long vrref_kdfof(long long n, const double *pos, const double *vel, int ndim, double fdist,
+                      const double *period /*NULL or [3]*/, long long minnum, int bucket_size,
+                      long long *pfof_out)
+{
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, NULL, NULL);
+    Double_t per[3];
+    Double_t *pp = NULL;
+    if (period) { for (int k = 0; k < 3; k++) per[k] = period[k]; pp = per; }
+    KDTree *tree;
+    if (ndim == 6) tree = new KDTree(P.data(), n, bucket_size, tree->TPHS, tree->KEPAN, 100);
+    else tree = new KDTree(P.data(), n, bucket_size, tree->TPHYS, tree->KEPAN, 100, 0, 0, 0, pp);
+    Int_t ng = 0;
+    Int_t *pfof = tree->FOF(fdist, ng, minnum, 1);
+    delete tree; /* restores input order */
+    for (long long i = 0; i < n; i++) pfof_out[i] = pfof[i];
+    delete[] pfof;
+    return ng;
+}
+
+/* SearchFullSet on flat arrays.  pos/vel are IN/OUT (the reference unwraps periodic positions and
+ * perturbs coordinates by the 6DFOF scale/unscale).  Returns number of groups.
+ * seconds_out (optional) receives the wall time of the SearchFullSet call itself. */
+long long vrref_search_full_set(long long n, double *pos, double *vel, const double *mass, const long long *pid,
+                                const vrref_opts *o, long long *pfof_out, double *seconds_out)
+{
+    Options opt;
+    fill_options(opt, o);
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, mass, pid);
+    Int_t ng = 0;
+    streambuf *old = NULL;
+    stringstream sink;
+    if (!o->verbose) old = cout.rdbuf(sink.rdbuf());
+    auto t0 = chrono::steady_clock::now();
+    Int_t *pfof = SearchFullSet(opt, n, P, ng);
+    auto t1 = chrono::steady_clock::now();
+    if (old) cout.rdbuf(old);
+    if (seconds_out) *seconds_out = chrono::duration<double>(t1 - t0).count();
+    for (long long i = 0; i < n; i++) {
+        pfof_out[i] = pfof[i];
+        for (int k = 0; k < 3; k++) { pos[3 * i + k] = P[i].GetPosition(k); vel[3 * i + k] = P[i].GetVelocity(k); }
+    }
+    delete[] pfof;
+    return ng;
+}
+
+/* Tree potential of one group (Potential(), unbind.cxx:1607).  phi_out in input order. */
+void vrref_potential(long long n, const double *pos, const double *mass, const vrref_opts *o, double *phi_out)
+{
+    Options opt;
+    fill_options(opt, o);
+    vector<Particle> P;
+    fill_particles(P, n, pos, NULL, mass, NULL);
+    Potential(opt, n, P.data());
+    for (long long i = 0; i < n; i++) phi_out[i] = P[i].GetPotential();
+}
+
+/* CheckUnboundGroups on flat arrays. pfof is IN/OUT, returns new number of groups; *changed = return flag. */
+long long vrref_unbind(long long n, const double *pos, const double *vel, const double *mass, const vrref_opts *o,
+                       long long *pfof, long long ngroup, int *changed, double *seconds_out)
+{
+    Options opt;
+    fill_options(opt, o);
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, mass, NULL);
+    Int_t *pf = new Int_t[n];
+    for (long long i = 0; i < n; i++) pf[i] = pfof[i];
+    Int_t ng = ngroup;
+    streambuf *old = NULL;
+    stringstream sink;
+    if (!o->verbose) old = cout.rdbuf(sink.rdbuf());
+    auto t0 = chrono::steady_clock::now();
+    int flag = CheckUnboundGroups(opt, n, P.data(), ng, pf);
+    auto t1 = chrono::steady_clock::now();
+    if (old) cout.rdbuf(old);
+    if (seconds_out) *seconds_out = chrono::duration<double>(t1 - t0).count();
+    if (changed) *changed = flag;
+    for (long long i = 0; i < n; i++) pfof[i] = pf[i];
+    delete[] pf;
+    return ng;
+}
+
+} /* extern "C" */

@@ -1,0 +1,165 @@
+"""oracle/vroracle.py -- TEST INFRASTRUCTURE ONLY (ctypes loaders for the checkers).
+
+Two checkers live under oracle/:
+  * `ref`    : the UNMODIFIED reference compiled into oracle/_ref/libvrref.so (serial, parity truth) and
+               oracle/_ref/libvrref_omp.so (OpenMP, timed CPU baseline) -- see oracle/Makefile, ref_driver.cxx.
+  * `oracle` : our plain-C restatement oracle/liboracle.so (vr_oracle.c), pinned against `ref`.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
+module.  The product (velociraptor-stf_b200/) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+c_ll = C.c_longlong
+c_dbl = C.c_double
+P_ll = C.POINTER(C.c_longlong)
+P_dbl = C.POINTER(C.c_double)
+
+
+class RefOpts(C.Structure):
+    """Mirror of vrref_opts in oracle/ref_driver.cxx (same order)."""
+    _fields_ = [
+        ("period", c_dbl), ("ellxscale", c_dbl), ("ellphys", c_dbl), ("ellhalophysfac", c_dbl),
+        ("ellhalo6dxfac", c_dbl), ("ellhalo6dvfac", c_dbl),
+        ("halo_min_size", c_ll), ("min_size", c_ll),
+        ("fofbgtype", C.c_int), ("bound_halos", C.c_int), ("omp_fof", C.c_int),
+        ("omp_fof_size", c_ll),
+        ("G", c_dbl), ("eps", c_dbl), ("Eratio", c_dbl), ("minEfrac", c_dbl),
+        ("unbindtype", C.c_int), ("bgpot", C.c_int), ("cmvelreftype", C.c_int),
+        ("fracpotref", c_dbl), ("Npotref", c_ll),
+        ("maxunbindfrac", c_dbl), ("maxunboundfracforiterativeunbind", c_dbl), ("maxallowedunboundfrac", c_dbl),
+        ("TreeThetaOpen", c_dbl), ("BucketSize", C.c_int), ("verbose", C.c_int),
+    ]
+
+
+def default_opts(**kw) -> RefOpts:
+    """Defaults = reference defaults (allvars.h:312-329, 660-847) + the sample cfg's unbinding block."""
+    o = RefOpts()
+    o.period = 0.0
+    o.ellxscale = 1.0
+    o.ellphys = 0.2
+    o.ellhalophysfac = 1.0
+    o.ellhalo6dxfac = 1.0
+    o.ellhalo6dvfac = 1.25
+    o.halo_min_size = 20
+    o.min_size = 20
+    o.fofbgtype = 5
+    o.bound_halos = 0
+    o.omp_fof = 0
+    o.omp_fof_size = 0
+    o.G = 43.0211349
+    o.eps = 0.0
+    o.Eratio = 0.95
+    o.minEfrac = 0.65
+    o.unbindtype = 0
+    o.bgpot = 1
+    o.cmvelreftype = 0
+    o.fracpotref = 1.0
+    o.Npotref = 20
+    o.maxunbindfrac = 0.5
+    o.maxunboundfracforiterativeunbind = 0.95
+    o.maxallowedunboundfrac = 0.025
+    o.TreeThetaOpen = 0.5
+    o.BucketSize = 8
+    o.verbose = 0
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise AttributeError(k)
+        setattr(o, k, v)
+    return o
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i64(a):
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+def _pd(a):
+    return a.ctypes.data_as(P_dbl) if a is not None else None
+
+
+def _pl(a):
+    return a.ctypes.data_as(P_ll) if a is not None else None
+
+
+class Ref:
+    """The reference itself (oracle/_ref/libvrref*.so)."""
+
+    def __init__(self, variant: str = "serial"):
+        name = {"serial": "libvrref.so", "omp": "libvrref_omp.so", "pp": "libvrref_pp.so"}[variant]
+        path = os.path.join(HERE, "_ref", name)
+        if not os.path.exists(path):
+            raise FileNotFoundError(path + " (run `make -C oracle ref` where /root/reference exists)")
+        self.variant = variant
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.vrref_sizeof_particle.restype = C.c_size_t
+        L.vrref_kdfof.restype = c_ll
+        L.vrref_kdfof.argtypes = [c_ll, P_dbl, P_dbl, C.c_int, c_dbl, P_dbl, c_ll, C.c_int, P_ll]
+        L.vrref_search_full_set.restype = c_ll
+        L.vrref_search_full_set.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, P_ll, C.POINTER(RefOpts), P_ll, P_dbl]
+        L.vrref_potential.restype = None
+        L.vrref_potential.argtypes = [c_ll, P_dbl, P_dbl, C.POINTER(RefOpts), P_dbl]
+        L.vrref_unbind.restype = c_ll
+        L.vrref_unbind.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, C.POINTER(RefOpts), P_ll, c_ll,
+                                   C.POINTER(C.c_int), P_dbl]
+        assert L.vrref_sizeof_particle() == 96
+
+    @staticmethod
+    def available(variant: str = "serial") -> bool:
+        name = {"serial": "libvrref.so", "omp": "libvrref_omp.so", "pp": "libvrref_pp.so"}[variant]
+        return os.path.exists(os.path.join(HERE, "_ref", name))
+
+    def unbindnum(self) -> int:
+        return int(self.lib.vrref_unbindnum())
+
+    def kdfof(self, pos, vel=None, ndim=3, fdist=1.0, period=None, minnum=2, bucket=16):
+        pos = _f64(pos)
+        n = pos.shape[0]
+        vel = _f64(vel) if vel is not None else None
+        per = _f64([period] * 3) if period else None
+        out = np.zeros(n, dtype=np.int64)
+        ng = self.lib.vrref_kdfof(n, _pd(pos), _pd(vel), ndim, fdist, _pd(per), minnum, bucket, _pl(out))
+        return out, int(ng)
+
+    def search_full_set(self, pos, vel, mass, pid, opts: RefOpts):
+        pos = _f64(pos).copy()
+        vel = _f64(vel).copy()
+        mass = _f64(mass)
+        pid = _i64(pid)
+        n = pos.shape[0]
+        out = np.zeros(n, dtype=np.int64)
+        sec = c_dbl(0)
+        ng = self.lib.vrref_search_full_set(n, _pd(pos), _pd(vel), _pd(mass), _pl(pid), C.byref(opts), _pl(out),
+                                            C.byref(sec))
+        return {"pfof": out, "ngroups": int(ng), "pos": pos, "vel": vel, "seconds": sec.value}
+
+    def potential(self, pos, mass, opts: RefOpts):
+        pos = _f64(pos)
+        mass = _f64(mass)
+        n = pos.shape[0]
+        phi = np.zeros(n)
+        self.lib.vrref_potential(n, _pd(pos), _pd(mass), C.byref(opts), _pd(phi))
+        return phi
+
+    def unbind(self, pos, vel, mass, pfof, ngroup, opts: RefOpts):
+        pos = _f64(pos)
+        vel = _f64(vel)
+        mass = _f64(mass)
+        pf = _i64(pfof).copy()
+        n = pos.shape[0]
+        ch = C.c_int(0)
+        sec = c_dbl(0)
+        ng = self.lib.vrref_unbind(n, _pd(pos), _pd(vel), _pd(mass), C.byref(opts), _pl(pf), ngroup, C.byref(ch),
+                                   C.byref(sec))
+        return {"pfof": pf, "ngroups": int(ng), "changed": int(ch.value), "seconds": sec.value}
