@@ -1,0 +1,73 @@
+/* oracle/vr_oracle.h -- TEST INFRASTRUCTURE ONLY.
+ *
+ * Plain-C CPU restatement of the VELOCIraptor structure-finding hot path (3DFOF -> 6DFOF -> unbinding).
+ * It exists to CHECK the CUDA path (tests/, __graft_entry__.smoke(), bench.py cpu_baseline); the product
+ * library never links, loads or calls it.  Parity status: PINNED against the reference itself compiled
+ * into oracle/_ref (tests/test_oracle_vs_ref.py) and against vectors generated from it (tests/golden/).
+ *
+ * Every function cites the reference code it follows (paths under /root/reference).
+ */
+#ifndef VR_ORACLE_H
+#define VR_ORACLE_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+    double G;                 /* Options::G */
+    double eps;               /* uinfo.eps (softening, already in code length) */
+    double Eratio;            /* uinfo.Eratio */
+    double minEfrac;          /* uinfo.minEfrac */
+    int unbindtype;           /* 0 USYSANDPART, 1 UPART  (allvars.h:211-213) */
+    int bgpot;                /* uinfo.bgpot (1: keep background potential) */
+    double fracpotref;        /* must be 1.0 (CM frame of the whole group, unbind.cxx:440-459) */
+    double maxunbindfrac;     /* 0.5 */
+    double maxunboundfracforiterativeunbind; /* 0.95 */
+    double maxallowedunboundfrac;            /* 0.025 */
+    double theta;             /* uinfo.TreeThetaOpen 0.5 */
+    int bucket;               /* uinfo.BucketSize 8 */
+    long long min_size;       /* Options::MinSize at the call */
+    long long pp_threshold;   /* UNBINDNUM: groups with n <= this use the direct sum (allvars.h:210); <0: all direct */
+    long long large_threshold;/* ompunbindnum 1000 (ompvar.h:26) */
+    int sortflag_mode;        /* 0: oldnumingroup initialised per group (intended semantics, what the GPU does)
+                                 1: literal serial reference: oldnumingroup carried across groups */
+} vro_unbind_opts;
+
+/* KDTree::FOF with TPHYS (KDFOF.cxx:12-129, KDLeafNode.cxx:518-573, KDSplitNode.cxx:1496-1540):
+ * transitive closure of the strict fp64 predicate d^2 < b*b, periodic images evaluated with the target shifted
+ * by +-period.  Groups smaller than minsize are dropped; ids are 1..G by (size desc, min pid asc).
+ * pid may be NULL (index is used).  Returns G. */
+long long vro_fof3d(long long n, const double *pos, double b, const double *period, long long minsize,
+                    const long long *pid, long long *pfof_out);
+
+/* AdjustStructureForPeriod (search.cxx:856-895): pos modified in place. */
+void vro_adjust_for_period(long long n, double *pos, double period, const long long *pfof, long long ngroups);
+
+/* 6DFOF inside each 3D group (search.cxx:400-698).  mode 3 = FOF6DADAPTIVE (per-group dispersion),
+ * mode 4 = FOF6D (single scale from the largest group, including the reference's quirk Q1).
+ * pos/vel are scaled and unscaled in place exactly like the reference (two multiplies, quirk Q3).
+ * vscale2_out (may be NULL) receives vscale2array[1..ngroups3d] at index g. Returns number of 6D groups. */
+long long vro_fof6d(long long n, double *pos, double *vel, const double *mass, const long long *pfof3d,
+                    long long ngroups3d, double b6, double vfac, int mode, long long minsize,
+                    const long long *pid, long long *pfof_out, double *vscale2_out);
+
+/* Direct-sum potential of one group in the reference's pair order (unbind.cxx:398-416). */
+void vro_potential_pp(long long n, const double *pos, const double *mass, double G, double eps, double *phi_out);
+
+/* kd-tree monopole potential of one group (Potential(), unbind.cxx:1607-1741; tree build KDTree.cxx:438-507).
+ * interactions_out (may be NULL) receives the number of cell+particle interactions (F_tree). */
+void vro_potential_tree(long long n, const double *pos, const double *mass, double G, double eps, double theta,
+                        int bucket, double *phi_out, long long *interactions_out);
+
+/* CheckUnboundGroups + Unbind (unbind.cxx:196-304, 320-729) for fracpotref==1.
+ * pfof in/out (0 = unbound), returns the new number of groups, ids re-ordered (size desc, min pid asc) when
+ * anything changed.  n_marginal_out (may be NULL): number of grouped particles whose |E| <= tol*|phi| at the
+ * moment they were last evaluated.  phi_out (may be NULL, length n): potential used for each grouped particle. */
+long long vro_unbind(long long n, const double *pos, const double *vel, const double *mass, long long *pfof,
+                     long long ngroups, const vro_unbind_opts *opts, const long long *pid, double marginal_tol,
+                     long long *n_marginal_out, double *phi_out, int *changed_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

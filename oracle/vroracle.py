@@ -163,3 +163,104 @@ class Ref:
         ng = self.lib.vrref_unbind(n, _pd(pos), _pd(vel), _pd(mass), C.byref(opts), _pl(pf), ngroup, C.byref(ch),
                                    C.byref(sec))
         return {"pfof": pf, "ngroups": int(ng), "changed": int(ch.value), "seconds": sec.value}
+
+
+class UnbindOpts(C.Structure):
+    """Mirror of vro_unbind_opts (oracle/vr_oracle.h)."""
+    _fields_ = [
+        ("G", c_dbl), ("eps", c_dbl), ("Eratio", c_dbl), ("minEfrac", c_dbl),
+        ("unbindtype", C.c_int), ("bgpot", C.c_int),
+        ("fracpotref", c_dbl), ("maxunbindfrac", c_dbl),
+        ("maxunboundfracforiterativeunbind", c_dbl), ("maxallowedunboundfrac", c_dbl),
+        ("theta", c_dbl), ("bucket", C.c_int),
+        ("min_size", c_ll), ("pp_threshold", c_ll), ("large_threshold", c_ll),
+        ("sortflag_mode", C.c_int),
+    ]
+
+
+def unbind_opts_from(o: RefOpts, pp_threshold: int = 150, sortflag_mode: int = 0) -> UnbindOpts:
+    u = UnbindOpts()
+    u.G = o.G; u.eps = o.eps; u.Eratio = o.Eratio; u.minEfrac = o.minEfrac
+    u.unbindtype = o.unbindtype; u.bgpot = o.bgpot; u.fracpotref = o.fracpotref
+    u.maxunbindfrac = o.maxunbindfrac
+    u.maxunboundfracforiterativeunbind = o.maxunboundfracforiterativeunbind
+    u.maxallowedunboundfrac = o.maxallowedunboundfrac
+    u.theta = o.TreeThetaOpen; u.bucket = o.BucketSize
+    u.min_size = o.min_size; u.pp_threshold = pp_threshold; u.large_threshold = 1000
+    u.sortflag_mode = sortflag_mode
+    return u
+
+
+class Oracle:
+    """Our plain-C restatement (oracle/liboracle.so)."""
+
+    def __init__(self):
+        path = os.path.join(HERE, "liboracle.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError(path + " (run `make -C oracle oracle`)")
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.vro_fof3d.restype = c_ll
+        L.vro_fof3d.argtypes = [c_ll, P_dbl, c_dbl, P_dbl, c_ll, P_ll, P_ll]
+        L.vro_adjust_for_period.restype = None
+        L.vro_adjust_for_period.argtypes = [c_ll, P_dbl, c_dbl, P_ll, c_ll]
+        L.vro_fof6d.restype = c_ll
+        L.vro_fof6d.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, P_ll, c_ll, c_dbl, c_dbl, C.c_int, c_ll, P_ll, P_ll, P_dbl]
+        L.vro_potential_pp.restype = None
+        L.vro_potential_pp.argtypes = [c_ll, P_dbl, P_dbl, c_dbl, c_dbl, P_dbl]
+        L.vro_potential_tree.restype = None
+        L.vro_potential_tree.argtypes = [c_ll, P_dbl, P_dbl, c_dbl, c_dbl, c_dbl, C.c_int, P_dbl, P_ll]
+        L.vro_unbind.restype = c_ll
+        L.vro_unbind.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, P_ll, c_ll, C.POINTER(UnbindOpts), P_ll, c_dbl,
+                                 P_ll, P_dbl, C.POINTER(C.c_int)]
+
+    def fof3d(self, pos, b, period=None, minsize=20, pid=None):
+        pos = _f64(pos)
+        n = pos.shape[0]
+        per = _f64([period] * 3) if period else None
+        pid = _i64(pid) if pid is not None else None
+        out = np.zeros(n, dtype=np.int64)
+        ng = self.lib.vro_fof3d(n, _pd(pos), b, _pd(per), minsize, _pl(pid), _pl(out))
+        return out, int(ng)
+
+    def adjust_for_period(self, pos, period, pfof, ngroups):
+        pos = _f64(pos).copy()
+        pfof = _i64(pfof)
+        self.lib.vro_adjust_for_period(pos.shape[0], _pd(pos), period, _pl(pfof), ngroups)
+        return pos
+
+    def fof6d(self, pos, vel, mass, pfof3d, ngroups3d, b6, vfac=1.25, mode=3, minsize=20, pid=None):
+        pos = _f64(pos).copy(); vel = _f64(vel).copy(); mass = _f64(mass)
+        pf3 = _i64(pfof3d)
+        n = pos.shape[0]
+        pid = _i64(pid) if pid is not None else None
+        out = np.zeros(n, dtype=np.int64)
+        vs2 = np.zeros(ngroups3d + 2)
+        ng = self.lib.vro_fof6d(n, _pd(pos), _pd(vel), _pd(mass), _pl(pf3), ngroups3d, b6, vfac, mode, minsize,
+                                _pl(pid), _pl(out), _pd(vs2))
+        return {"pfof": out, "ngroups": int(ng), "pos": pos, "vel": vel, "vscale2": vs2[:ngroups3d + 1]}
+
+    def potential_pp(self, pos, mass, G, eps=0.0):
+        pos = _f64(pos); mass = _f64(mass)
+        phi = np.zeros(pos.shape[0])
+        self.lib.vro_potential_pp(pos.shape[0], _pd(pos), _pd(mass), G, eps, _pd(phi))
+        return phi
+
+    def potential_tree(self, pos, mass, G, eps=0.0, theta=0.5, bucket=8):
+        pos = _f64(pos); mass = _f64(mass)
+        phi = np.zeros(pos.shape[0])
+        inter = c_ll(0)
+        self.lib.vro_potential_tree(pos.shape[0], _pd(pos), _pd(mass), G, eps, theta, bucket, _pd(phi), C.byref(inter))
+        return phi, int(inter.value)
+
+    def unbind(self, pos, vel, mass, pfof, ngroups, uopts: UnbindOpts, pid=None, marginal_tol=1e-6):
+        pos = _f64(pos); vel = _f64(vel); mass = _f64(mass)
+        pf = _i64(pfof).copy()
+        n = pos.shape[0]
+        pid = _i64(pid) if pid is not None else None
+        nm = c_ll(0)
+        ch = C.c_int(0)
+        phi = np.zeros(n)
+        ng = self.lib.vro_unbind(n, _pd(pos), _pd(vel), _pd(mass), _pl(pf), ngroups, C.byref(uopts), _pl(pid),
+                                 marginal_tol, C.byref(nm), _pd(phi), C.byref(ch))
+        return {"pfof": pf, "ngroups": int(ng), "n_marginal": int(nm.value), "phi": phi, "changed": int(ch.value)}
