@@ -1,0 +1,140 @@
+/* include/vrgpu.h -- C ABI of libvrgpu.so, the B200 (sm_100a) implementation of VELOCIraptor's
+ * structure-finding hot path: 3D friends-of-friends -> 6D phase-space FOF -> potential + unbinding.
+ *
+ * This is the drop-in boundary.  Every entry point replaces one reference interface (paths under the
+ * reference tree, cited per function) and is what the reference-side host adaptor
+ * (velociraptor-stf_b200/host/vrgpu_adaptor.cxx) binds.
+ *
+ * Conventions
+ *   - plain C, no exceptions cross the boundary; return 0 = OK, non-zero = VRGPU_E* code,
+ *     vrgpu_last_error(ctx) gives the text.
+ *   - every pointer is a HOST pointer owned by the caller (pinned or pageable); the library never frees
+ *     or retains caller memory.  Outputs are fully written on success and untouched on failure.
+ *   - Int_t == long long (the reference's default LONGINT build, NBodylib/src/Math/Precision.h:49),
+ *     Double_t == double.  NBody::Particle must be the 96-byte default layout
+ *     (NBodylib/src/NBody/Particle.h:75-109); other layouts are described through vrgpu_view.
+ *   - one caller thread per context (all reference call sites are on the main thread).
+ *   - there is NO CPU fallback: without a CUDA device vrgpu_init fails with VRGPU_ENODEV.
+ */
+#ifndef VRGPU_H
+#define VRGPU_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VRGPU_OK 0
+#define VRGPU_ENODEV 1      /* no usable CUDA device */
+#define VRGPU_ECUDA 2       /* a CUDA runtime call failed */
+#define VRGPU_EINVAL 3      /* bad argument */
+#define VRGPU_EUNSUPPORTED 4/* option combination outside the implemented path */
+#define VRGPU_ENOMEM 5
+
+typedef struct vrgpu_ctx vrgpu_ctx;
+
+/* Strided view straight into the caller's particle array (AoS NBody::Particle or anything else), so the
+ * host does no repacking.  Offsets are in bytes from `base`; pos/vel are 3 consecutive doubles, mass one
+ * double, pid one long long.  off_vel/off_mass/off_pid may be (size_t)-1 when a call does not need them
+ * (mass then defaults to 1.0, pid to the index). */
+typedef struct {
+    const void *base;
+    size_t stride;
+    size_t off_pos, off_vel, off_mass, off_pid;
+    long long n;
+} vrgpu_view;
+#define VRGPU_NOFIELD ((size_t)-1)
+
+/* Unbinding controls == reference UnbindInfo (src/allvars.h:270-330) + the Options members Unbind() reads. */
+typedef struct {
+    double G;                  /* Options::G                                                        */
+    double eps;                /* UnbindInfo::eps (softening, code length)                          */
+    double Eratio;             /* UnbindInfo::Eratio                                                */
+    double minEfrac;           /* UnbindInfo::minEfrac                                              */
+    int unbindtype;            /* UnbindInfo::unbindtype 0 = USYSANDPART, 1 = UPART                 */
+    int bgpot;                 /* UnbindInfo::bgpot; only 1 (keep background potential) implemented */
+    double fracpotref;         /* UnbindInfo::fracpotref; only 1.0 (whole-group CM frame)           */
+    double maxunbindfrac;      /* UnbindInfo::maxunbindfrac (0.5)                                   */
+    double maxunboundfracforiterativeunbind; /* (0.95)                                              */
+    double maxallowedunboundfrac;            /* (0.025)                                             */
+    double theta;              /* UnbindInfo::TreeThetaOpen (0.5)                                   */
+    int bucket;                /* UnbindInfo::BucketSize (8)                                        */
+    long long min_size;        /* Options::MinSize at the call                                      */
+    long long pp_threshold;    /* UNBINDNUM (150): n <= this -> direct sum; < 0 -> direct sum always */
+    long long large_threshold; /* ompunbindnum (1000): selects the reference's two loop variants    */
+    double marginal_tol;       /* |E| <= tol*|phi| counts as marginal (BASELINE.json: 1e-6)         */
+} vrgpu_unbind_opts;
+
+/* Options subset SearchFullSet reads on the DM-only path (src/search.cxx:24-854). */
+typedef struct {
+    double period;             /* Options::p, 0 = open                                              */
+    double param1;             /* param[1] = (ellxscale^2)*(ellphys^2)*(ellhalophysfac^2), the SQUARED physical linking
+                                  length exactly as search.cxx:77 forms it; 3DFOF uses b = sqrt(param1), b2 = b*b
+                                  (search.cxx:203, KDFOF.cxx:14); 6DFOF uses param1*ellhalo6dxfac^2 (search.cxx:410) */
+    long long halo_min_size;   /* Options::HaloMinSize                                              */
+    int fofbgtype;             /* 5 FOF3D, 3 FOF6DADAPTIVE, 4 FOF6D (Options::fofbgtype)            */
+    double ellhalo6dxfac;      /* Options::ellhalo6dxfac (search.cxx:410)                           */
+    double ellhalo6dvfac;      /* Options::ellhalo6dvfac (search.cxx:464,492)                       */
+    int bound_halos;           /* Options::iBoundHalos >= 1 -> CheckUnboundGroups (search.cxx:702)  */
+    vrgpu_unbind_opts unbind;
+} vrgpu_search_opts;
+
+/* Per-stage device timings (milliseconds, CUDA events) of the last call, for bench.py / profiling. */
+typedef struct {
+    double h2d_ms, sort_ms, link_ms, label_ms, fof6d_ms, potential_ms, unbind_ms, d2h_ms, total_ms;
+    long long n_cells, n_groups3d, n_groups_final, n_grouped, n_pairs_potential, n_marginal;
+    long long h2d_bytes, d2h_bytes, kernel_launches;
+} vrgpu_stats;
+
+/* Create / destroy a context on CUDA device `device` (-1 = current device). */
+int vrgpu_init(int device, vrgpu_ctx **out);
+void vrgpu_destroy(vrgpu_ctx *ctx);
+const char *vrgpu_last_error(const vrgpu_ctx *ctx);
+/* Library / build identification: returns "vrgpu <version> sm_100a". */
+const char *vrgpu_version(void);
+void vrgpu_get_stats(const vrgpu_ctx *ctx, vrgpu_stats *out);
+
+/* 3D FOF.  Replaces NBody::KDTree::FOF (NBodylib/src/KDTree/KDFOF.cxx:12-129) as called by
+ * SearchFullSet (src/search.cxx:203): groups = transitive closure of the strict fp64 predicate
+ * d^2 < b*b (KDLeafNode.cxx:556-558), periodic images as KDSplitNode.cxx:1496-1540; groups below
+ * `minsize` dropped; ids 1..G by size descending, ties by minimum pid.  pfof_out[i] is indexed by the
+ * particle's position in the view. */
+int vrgpu_fof3d(vrgpu_ctx *ctx, vrgpu_view view, double b, const double *period /*NULL = open, else [3] equal*/,
+                long long minsize, long long *pfof_out, long long *ngroups_out);
+
+/* AdjustStructureForPeriod (src/search.cxx:856-895): writes the unwrapped positions back through a
+ * writable view (pos field only).  view.base is cast to non-const. */
+int vrgpu_adjust_for_period(vrgpu_ctx *ctx, vrgpu_view view, double period, const long long *pfof, long long ngroups);
+
+/* 6D FOF inside every 3D group.  Replaces src/search.cxx:400-698 (regroup, per-group dispersion,
+ * ScalePhase, 6-D KDTree::FOF(1.0), unscale, ReorderGroupIDs).  mode 3 = FOF6DADAPTIVE, 4 = FOF6D.
+ * b6 = sqrt(param[1]) after search.cxx:410.  The view must be writable: positions/velocities receive the
+ * reference's scale/unscale rounding (two multiplies). */
+int vrgpu_fof6d(vrgpu_ctx *ctx, vrgpu_view view, const long long *pfof3d, long long ngroups3d, double b6,
+                double vfac, int mode, long long minsize, long long *pfof_out, long long *ngroups_out);
+
+/* Potentials of groups given in CSR form (offsets[G+1], index[offsets[G]] = particle index in the view).
+ * Replaces the direct-sum loop of Unbind (src/unbind.cxx:398-416) for n <= pp_threshold and
+ * Potential() (src/unbind.cxx:1607-1741; kd-tree of KDTree.cxx:438-507, bucket, theta) above it.
+ * phi_out[k] corresponds to index[k]. */
+int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets,
+                    const long long *index, double G, double eps, double theta, int bucket,
+                    long long pp_threshold, double *phi_out);
+
+/* CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729).  pfof in/out (0 = unbound), group ids
+ * re-ordered by size when anything changed (ireorder=1).  *changed_out = the reference's return flag. */
+int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long long *ngroups_inout,
+                 const vrgpu_unbind_opts *opts, int *changed_out, long long *n_marginal_out);
+
+/* The whole of SearchFullSet's DM path in one call with the particles resident on the device between the
+ * stages: 3DFOF -> AdjustStructureForPeriod -> [6DFOF] -> [CheckUnboundGroups]  (src/search.cxx:24-854).
+ * The view must be writable when period > 0 or fofbgtype <= 4 (positions/velocities are updated as the
+ * reference updates them). */
+int vrgpu_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, const vrgpu_search_opts *opts,
+                          long long *pfof_out, long long *ngroups_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,54 @@
+// velociraptor-stf_b200/csrc/fof.cuh -- device-resident state shared by the FOF / unbinding stages.
+#pragma once
+#include "common.cuh"
+
+namespace vrgpu {
+
+// Particles as uploaded from the caller's (strided) view, original order.
+struct DeviceParticles {
+    size_t n = 0;
+    DBuf<double> pos;      // packed xyz, 3n
+    DBuf<double> vel;      // packed xyz, 3n (optional)
+    DBuf<double> mass;     // n (optional)
+    DBuf<long long> pid;   // n (optional)
+    bool has_vel = false, has_mass = false, has_pid = false;
+};
+
+// Uniform fine-cell grid used by the 3D linker.  Cell edge c < b/sqrt(3) so that any two particles in the
+// same cell are linked by construction; neighbours are searched within +-2 cells.
+struct Grid {
+    double lo[3];
+    double inv_c[3];
+    double c[3];
+    int nc[3];
+    double period; // 0 = open
+    int bits[3];   // bits per axis in the packed key
+};
+
+struct Fof3dState {
+    size_t n = 0;
+    uint32_t ncells = 0;
+    Grid grid{};
+    DBuf<uint32_t> order;      // sorted slot -> original index
+    DBuf<double> sx, sy, sz;   // positions in sorted (cell) order
+    DBuf<uint32_t> cell_of;    // sorted slot -> cell
+    DBuf<uint32_t> cell_start; // ncells + 1
+    DBuf<uint64_t> cell_key;   // ncells
+    DBuf<uint32_t> root;       // ncells: root cell after linking
+    DBuf<long long> pfof;      // n, by ORIGINAL index
+    long long ngroups = 0;
+    long long ngrouped = 0;
+};
+
+// helpers in api.cu / io.cu
+void upload_view(vrgpu_ctx *ctx, const vrgpu_view &view, bool need_vel, bool need_mass, bool need_pid, DeviceParticles &out);
+void download_i64(vrgpu_ctx *ctx, const long long *dev, long long *host, size_t n);
+
+// stages
+void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double period, long long minsize, Fof3dState &S);
+// AdjustStructureForPeriod on the device copy (P.pos updated in place); returns the number of moved particles and
+// fills compact lists (original index, new xyz) for the host write-back.
+size_t adjust_for_period_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof_dev, long long ngroups, double period,
+                                DBuf<uint32_t> &moved_idx, DBuf<double> &moved_xyz);
+
+} // namespace vrgpu

@@ -1,0 +1,24 @@
+// velociraptor-stf_b200/csrc/stages.cuh -- stage entry points behind the C ABI (6DFOF, potentials, unbinding).
+#pragma once
+#include "fof.cuh"
+
+namespace vrgpu {
+
+// 6DFOF inside each 3D group (src/search.cxx:400-698).  pfof3d_dev / pfof6d_dev are device arrays in ORIGINAL
+// particle order.  When apply_q3 is set, P.pos / P.vel receive the reference's scale-unscale rounding.
+long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof3d_dev, long long ngroups3d, double b6, double vfac,
+                       int mode, long long minsize, long long *pfof6d_dev, bool apply_q3);
+
+// write pos+vel of every particle with pfof_dev[i] > 0 back into the caller's writable view
+void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
+
+// potentials for host-side CSR groups (vrgpu_potential)
+void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                        const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,
+                        double *phi_out_host);
+
+// CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729) on device-resident particles
+void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
+                   int &changed, long long &n_marginal);
+
+} // namespace vrgpu

@@ -1,0 +1,270 @@
+"""ctypes binding of libvrgpu.so (include/vrgpu.h) -- the B200 structure-finding hot path.
+
+This module is host-side plumbing only: it builds `vrgpu_view`s over numpy / torch host buffers and forwards
+to the C ABI.  There is NO CPU fallback: if the CUDA library is missing or no B200 is present, loading or
+`Context()` raises.
+
+`PARTICLE_DTYPE` is the reference's default 96-byte NBody::Particle layout
+(NBodylib/src/NBody/Particle.h:75-109: mass, position[3], velocity[3], pid, id, type, rho, phi).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libvrgpu.so")
+
+PARTICLE_DTYPE = np.dtype({
+    "names": ["mass", "pos", "vel", "pid", "id", "type", "rho", "phi"],
+    "formats": ["<f8", ("<f8", 3), ("<f8", 3), "<i8", "<i8", "<i4", "<f8", "<f8"],
+    "offsets": [0, 8, 32, 56, 64, 72, 80, 88],
+    "itemsize": 96,
+})
+
+NOFIELD = C.c_size_t(-1).value
+
+ERRORS = {1: "VRGPU_ENODEV", 2: "VRGPU_ECUDA", 3: "VRGPU_EINVAL", 4: "VRGPU_EUNSUPPORTED", 5: "VRGPU_ENOMEM"}
+
+
+class VrgpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{ERRORS.get(code, code)}: {msg}")
+        self.code = code
+
+
+class View(C.Structure):
+    _fields_ = [("base", C.c_void_p), ("stride", C.c_size_t), ("off_pos", C.c_size_t), ("off_vel", C.c_size_t),
+                ("off_mass", C.c_size_t), ("off_pid", C.c_size_t), ("n", C.c_longlong)]
+
+
+class UnbindOpts(C.Structure):
+    _fields_ = [("G", C.c_double), ("eps", C.c_double), ("Eratio", C.c_double), ("minEfrac", C.c_double),
+                ("unbindtype", C.c_int), ("bgpot", C.c_int), ("fracpotref", C.c_double),
+                ("maxunbindfrac", C.c_double), ("maxunboundfracforiterativeunbind", C.c_double),
+                ("maxallowedunboundfrac", C.c_double), ("theta", C.c_double), ("bucket", C.c_int),
+                ("min_size", C.c_longlong), ("pp_threshold", C.c_longlong), ("large_threshold", C.c_longlong),
+                ("marginal_tol", C.c_double)]
+
+
+class SearchOpts(C.Structure):
+    _fields_ = [("period", C.c_double), ("param1", C.c_double), ("halo_min_size", C.c_longlong),
+                ("fofbgtype", C.c_int), ("ellhalo6dxfac", C.c_double), ("ellhalo6dvfac", C.c_double),
+                ("bound_halos", C.c_int), ("unbind", UnbindOpts)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(k, C.c_double) for k in ("h2d_ms", "sort_ms", "link_ms", "label_ms", "fof6d_ms", "potential_ms",
+                                          "unbind_ms", "d2h_ms", "total_ms")] + \
+               [(k, C.c_longlong) for k in ("n_cells", "n_groups3d", "n_groups_final", "n_grouped",
+                                            "n_pairs_potential", "n_marginal", "h2d_bytes", "d2h_bytes",
+                                            "kernel_launches")]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+def default_unbind_opts(**kw) -> UnbindOpts:
+    """UnbindInfo defaults (allvars.h:312-329) overlaid with the sample cfg's unbinding block
+    (examples/sample_dmcosmological_run.cfg: Unbinding_type=0, Eratio 0.95, Min_bound_mass_frac 0.65)."""
+    u = UnbindOpts()
+    u.G = 43.0211349
+    u.eps = 0.0
+    u.Eratio = 0.95
+    u.minEfrac = 0.65
+    u.unbindtype = 0
+    u.bgpot = 1
+    u.fracpotref = 1.0
+    u.maxunbindfrac = 0.5
+    u.maxunboundfracforiterativeunbind = 0.95
+    u.maxallowedunboundfrac = 0.025
+    u.theta = 0.5
+    u.bucket = 8
+    u.min_size = 20
+    u.pp_threshold = 150
+    u.large_threshold = 1000
+    u.marginal_tol = 1e-6
+    for k, v in kw.items():
+        if not hasattr(u, k):
+            raise AttributeError(k)
+        setattr(u, k, v)
+    return u
+
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH):
+    """Load libvrgpu.so; raises (never falls back) if the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(path)
+    L.vrgpu_version.restype = C.c_char_p
+    L.vrgpu_init.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    L.vrgpu_destroy.argtypes = [C.c_void_p]
+    L.vrgpu_destroy.restype = None
+    L.vrgpu_last_error.argtypes = [C.c_void_p]
+    L.vrgpu_last_error.restype = C.c_char_p
+    L.vrgpu_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+    L.vrgpu_get_stats.restype = None
+    P_ll = C.POINTER(C.c_longlong)
+    P_d = C.POINTER(C.c_double)
+    L.vrgpu_fof3d.argtypes = [C.c_void_p, View, C.c_double, P_d, C.c_longlong, P_ll, P_ll]
+    L.vrgpu_adjust_for_period.argtypes = [C.c_void_p, View, C.c_double, P_ll, C.c_longlong]
+    L.vrgpu_fof6d.argtypes = [C.c_void_p, View, P_ll, C.c_longlong, C.c_double, C.c_double, C.c_int, C.c_longlong, P_ll, P_ll]
+    L.vrgpu_potential.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_ll, C.c_double, C.c_double, C.c_double, C.c_int,
+                                  C.c_longlong, P_d]
+    L.vrgpu_unbind.argtypes = [C.c_void_p, View, P_ll, P_ll, C.POINTER(UnbindOpts), C.POINTER(C.c_int), P_ll]
+    L.vrgpu_search_full_set.argtypes = [C.c_void_p, View, C.POINTER(SearchOpts), P_ll, P_ll]
+    _lib = L
+    return L
+
+
+EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_version", "vrgpu_get_stats", "vrgpu_fof3d",
+                    "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set"]
+
+
+def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
+    """Build the reference's 96-byte AoS (what SearchFullSet receives as vector<Particle>) from columns.
+    pinned=True allocates the records in page-locked host memory through torch (zero-copy upload path)."""
+    pos = np.asarray(pos, dtype=np.float64)
+    n = pos.shape[0]
+    if pinned:
+        import torch
+        buf = torch.empty(n * PARTICLE_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True)
+        parts = buf.numpy().view(PARTICLE_DTYPE)
+        _KEEP.append(buf)
+    else:
+        parts = np.zeros(n, dtype=PARTICLE_DTYPE)
+    parts["pos"] = pos
+    parts["vel"] = 0.0 if vel is None else np.asarray(vel, dtype=np.float64)
+    parts["mass"] = 1.0 if mass is None else np.asarray(mass, dtype=np.float64)
+    parts["pid"] = np.arange(n, dtype=np.int64) if pid is None else np.asarray(pid, dtype=np.int64)
+    parts["id"] = np.arange(n, dtype=np.int64)
+    parts["type"] = 1
+    parts["rho"] = 0.0
+    parts["phi"] = 0.0
+    return parts
+
+
+_KEEP: list = []
+
+
+def view_of(parts: np.ndarray) -> View:
+    """vrgpu_view over a PARTICLE_DTYPE array (no copy)."""
+    assert parts.dtype == PARTICLE_DTYPE and parts.flags["C_CONTIGUOUS"]
+    v = View()
+    v.base = parts.ctypes.data
+    v.stride = PARTICLE_DTYPE.itemsize
+    v.off_pos, v.off_vel, v.off_mass, v.off_pid = 8, 32, 0, 56
+    v.n = parts.shape[0]
+    return v
+
+
+class Context:
+    """One vrgpu_ctx (one CUDA device, one caller thread)."""
+
+    def __init__(self, device: int = -1):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.vrgpu_init(device, C.byref(h))
+        if rc != 0:
+            raise VrgpuError(rc, "vrgpu_init failed (no B200 / CUDA device available; there is no CPU fallback)")
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vrgpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise VrgpuError(rc, self.lib.vrgpu_last_error(self.h).decode())
+
+    def stats(self) -> dict:
+        s = Stats()
+        self.lib.vrgpu_get_stats(self.h, C.byref(s))
+        return s.asdict()
+
+    # ---- stage calls (names follow the reference functions they replace) ----
+    def fof3d(self, parts, b, period=None, minsize=20, out=None):
+        """KDTree::FOF (KDFOF.cxx:12) as used by SearchFullSet (search.cxx:203)."""
+        n = parts.shape[0]
+        pfof = out if out is not None else np.zeros(n, dtype=np.int64)
+        ng = C.c_longlong(0)
+        per = (C.c_double * 3)(period, period, period) if period else None
+        self._check(self.lib.vrgpu_fof3d(self.h, view_of(parts), b, per, minsize,
+                                         pfof.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
+        return pfof, int(ng.value)
+
+    def adjust_for_period(self, parts, period, pfof, ngroups):
+        """AdjustStructureForPeriod (search.cxx:856); parts['pos'] is updated in place."""
+        pfof = np.ascontiguousarray(pfof, dtype=np.int64)
+        self._check(self.lib.vrgpu_adjust_for_period(self.h, view_of(parts), period,
+                                                     pfof.ctypes.data_as(C.POINTER(C.c_longlong)), ngroups))
+
+    def fof6d(self, parts, pfof3d, ngroups3d, b6, vfac=1.25, mode=3, minsize=20):
+        """6DFOF block of SearchFullSet (search.cxx:400-698); parts pos/vel get the Q3 rounding in place."""
+        n = parts.shape[0]
+        pfof3d = np.ascontiguousarray(pfof3d, dtype=np.int64)
+        pfof = np.zeros(n, dtype=np.int64)
+        ng = C.c_longlong(0)
+        P = C.POINTER(C.c_longlong)
+        self._check(self.lib.vrgpu_fof6d(self.h, view_of(parts), pfof3d.ctypes.data_as(P), ngroups3d, b6, vfac, mode,
+                                         minsize, pfof.ctypes.data_as(P), C.byref(ng)))
+        return pfof, int(ng.value)
+
+    def potential(self, parts, offsets, index, G, eps=0.0, theta=0.5, bucket=8, pp_threshold=150):
+        """Unbind's direct sum (unbind.cxx:398-416) / Potential() (unbind.cxx:1607) for CSR groups."""
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        index = np.ascontiguousarray(index, dtype=np.int64)
+        ng = offsets.shape[0] - 1
+        phi = np.zeros(index.shape[0], dtype=np.float64)
+        P = C.POINTER(C.c_longlong)
+        self._check(self.lib.vrgpu_potential(self.h, view_of(parts), ng, offsets.ctypes.data_as(P), index.ctypes.data_as(P),
+                                             G, eps, theta, bucket, pp_threshold, phi.ctypes.data_as(C.POINTER(C.c_double))))
+        return phi
+
+    def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
+        """CheckUnboundGroups (unbind.cxx:196)."""
+        pf = np.ascontiguousarray(pfof, dtype=np.int64).copy()
+        ng = C.c_longlong(ngroups)
+        ch = C.c_int(0)
+        nm = C.c_longlong(0)
+        self._check(self.lib.vrgpu_unbind(self.h, view_of(parts), pf.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng),
+                                          C.byref(opts), C.byref(ch), C.byref(nm)))
+        return {"pfof": pf, "ngroups": int(ng.value), "changed": int(ch.value), "n_marginal": int(nm.value)}
+
+    def search_full_set(self, parts, opts: SearchOpts, out=None):
+        """SearchFullSet (search.cxx:24-854), DM-only path."""
+        n = parts.shape[0]
+        pfof = out if out is not None else np.zeros(n, dtype=np.int64)
+        ng = C.c_longlong(0)
+        self._check(self.lib.vrgpu_search_full_set(self.h, view_of(parts), C.byref(opts),
+                                                   pfof.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
+        return pfof, int(ng.value)
+
+
+def search_opts(period, param1, halo_min_size=20, fofbgtype=5, ellhalo6dxfac=1.0, ellhalo6dvfac=1.25, bound_halos=0,
+                unbind: UnbindOpts | None = None) -> SearchOpts:
+    o = SearchOpts()
+    o.period = period
+    o.param1 = param1
+    o.halo_min_size = halo_min_size
+    o.fofbgtype = fofbgtype
+    o.ellhalo6dxfac = ellhalo6dxfac
+    o.ellhalo6dvfac = ellhalo6dvfac
+    o.bound_halos = bound_halos
+    o.unbind = unbind if unbind is not None else default_unbind_opts()
+    return o
