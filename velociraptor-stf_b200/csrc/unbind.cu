@@ -1,0 +1,626 @@
+// velociraptor-stf_b200/csrc/unbind.cu -- CheckUnboundGroups / Unbind on the device.
+//
+// Replaces src/unbind.cxx:196-304 (CheckUnboundGroups), :320-729 (Unbind) and their helpers
+// GetBoundFractionAndMaxE (:146-185), CheckGroupForBoundness (:49-60), FillUnboundArrays (:62-98),
+// UpdateCMForUnboundParticles (:111-127), RemoveUnboundParticles (:101-108), RemoveGroup (:129-140)
+// for the configuration every sample cfg uses: Frac_pot_ref = 1 (CM frame of the whole group) and
+// Keep_background_potential = 1 (potentials computed once).
+//
+// Structure (mirrors the reference's two loops):
+//   phase A  groups with n >= large_threshold (ompunbindnum): the reference's "large" loop can only ever make
+//            ONE removal pass (its continue-condition contradicts FillUnboundArrays' cancel rule), so this is a
+//            data-parallel pass: energies -> per-group counters -> global (gid, E) sort -> decide -> apply.
+//   phase B  every group that now has 0 < n <= large_threshold: one CTA per group runs the reference's
+//            small-group state machine entirely in shared memory (energies, bitonic sort by E, tail removal,
+//            CM update, termination rules).
+// Deviation (documented in DESIGN.md): `oldnumingroup`, which the reference reads uninitialised in
+// the small-group loop, is initialised to the group's size when its loop starts.
+#include "groups.cuh"
+#include "stages.cuh"
+
+#include <algorithm>
+#include <cmath>
+
+namespace vrgpu {
+
+constexpr int UB_CAP = 2048; // max members handled by the in-CTA state machine
+constexpr int UB_T = 256;
+
+struct UbParams {
+    double Eratio, minEfrac, maxunbindfrac, maxunboundfrac, maxallowed, marginal_tol;
+    int unbindtype;
+    long long min_size, large_threshold;
+};
+
+struct UbArrays {
+    const double *vx, *vy, *vz, *m, *phi;
+    const uint32_t *gid, *off;
+    double *E;                // per slot
+    uint32_t *ord;            // per slot: arrangement of each group's segment (gPart order)
+    unsigned char *alive;     // per slot
+    unsigned char *marg;      // per slot: |E| <= tol |phi| at the last evaluation
+    double *cmvel;            // 3 per group
+    double *gmass;            // per group
+    uint32_t *ning;           // per group: current member count
+    uint32_t *nunb, *nefrac;  // per group counters (phase A)
+    unsigned long long *maxE; // per group, ordered-uint image of a double (phase A)
+    uint32_t *nrem;           // per group (phase A)
+    int *status;              // per group: 0 untouched, 1 removed some, 2 dissolved
+    unsigned int *changed;    // global flag (iunbindflag != 0)
+};
+
+__device__ __forceinline__ unsigned long long dbl_to_ord(double d)
+{
+    unsigned long long u = (unsigned long long)__double_as_longlong(d);
+    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double ord_to_dbl(unsigned long long u)
+{
+    u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
+    return __longlong_as_double((long long)u);
+}
+
+// energy of one member in the frame cm (GetBoundFractionAndMaxE, unbind.cxx:163-178)
+__device__ __forceinline__ void member_energy(const UbArrays &A, const UbParams &P, uint32_t slot, double cx, double cy, double cz,
+                                              double &E, bool &bound_frac, bool &marginal)
+{
+    double m = A.m[slot];
+    double dx = A.vx[slot] - cx, dy = A.vy[slot] - cy, dz = A.vz[slot] - cz;
+    double v2 = 0.0;
+    v2 = __dadd_rn(v2, __dmul_rn(dx, dx));
+    v2 = __dadd_rn(v2, __dmul_rn(dy, dy));
+    v2 = __dadd_rn(v2, __dmul_rn(dz, dz));
+    double Ti = __dmul_rn(__dmul_rn(0.5, m), v2);
+    double phi = A.phi[slot];
+    E = __dadd_rn(__dmul_rn(P.Eratio, Ti), phi);
+    bound_frac = __dadd_rn(Ti, phi) < 0;
+    marginal = fabs(E) <= P.marginal_tol * fabs(phi);
+}
+
+// CM velocity and mass of every group (unbind.cxx:447-455): one warp per group, fixed reduction shape
+__global__ void __launch_bounds__(256) k_group_cm(UbArrays A, uint32_t ngroups)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t g = 1 + wg; g <= ngroups; g += nw) {
+        uint32_t s0 = A.off[g], s1 = A.off[g + 1];
+        double sm = 0, sx = 0, sy = 0, sz = 0;
+        for (uint32_t s = s0 + lane; s < s1; s += 32) {
+            double m = A.m[s];
+            sm += m; sx += A.vx[s] * m; sy += A.vy[s] * m; sz += A.vz[s] * m;
+        }
+        for (int o = 16; o; o >>= 1) {
+            sm += __shfl_xor_sync(0xffffffffu, sm, o); sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            sy += __shfl_xor_sync(0xffffffffu, sy, o); sz += __shfl_xor_sync(0xffffffffu, sz, o);
+        }
+        if (lane == 0) {
+            double inv = 1.0 / sm;
+            A.gmass[g] = sm;
+            A.cmvel[3 * g] = sx * inv; A.cmvel[3 * g + 1] = sy * inv; A.cmvel[3 * g + 2] = sz * inv;
+            A.ning[g] = s1 - s0;
+            A.status[g] = 0;
+        }
+    }
+}
+
+__global__ void k_init_slots(UbArrays A, uint32_t ntot)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    A.ord[s] = s;
+    A.alive[s] = 1;
+    A.marg[s] = 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// phase A: large groups
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_large_energy(UbArrays A, UbParams P, uint32_t ntot, uint32_t *__restrict__ lflag)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t g = 0;
+    bool large = false;
+    if (s < ntot) {
+        g = A.gid[s];
+        large = (long long)(A.off[g + 1] - A.off[g]) >= P.large_threshold;
+        lflag[s] = large ? 1u : 0u;
+    }
+    double E = 0;
+    bool bf = false, mg = false;
+    if (large) {
+        member_energy(A, P, s, A.cmvel[3 * g], A.cmvel[3 * g + 1], A.cmvel[3 * g + 2], E, bf, mg);
+        A.E[s] = E;
+        A.marg[s] = mg ? 1 : 0;
+    }
+    // warp-aggregated per-group counters (integer sums and a max: order independent)
+    const unsigned key = large ? g : 0u;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const bool uni = __all_sync(0xffffffffu, peers == 0xffffffffu);
+    if (uni) {
+        if (large) { // whole warp inside one large group
+            const unsigned lane = threadIdx.x & 31;
+            unsigned u = __ballot_sync(0xffffffffu, E > 0), f = __ballot_sync(0xffffffffu, bf);
+            unsigned long long mo = dbl_to_ord(E);
+            for (int o = 16; o; o >>= 1) {
+                unsigned long long y = __shfl_xor_sync(0xffffffffu, mo, o);
+                if (y > mo) mo = y;
+            }
+            if (lane == 0) { atomicAdd(&A.nunb[g], __popc(u)); atomicAdd(&A.nefrac[g], __popc(f)); atomicMax(&A.maxE[g], mo); }
+        }
+    } else if (large) {
+        // mixed warp (group boundary or array tail): per-lane atomics
+        atomicAdd(&A.nunb[g], E > 0 ? 1u : 0u);
+        atomicAdd(&A.nefrac[g], bf ? 1u : 0u);
+        atomicMax(&A.maxE[g], dbl_to_ord(E));
+    }
+}
+
+__global__ void k_large_keys(const UbArrays A, const uint32_t *__restrict__ lflag, const uint32_t *__restrict__ lexcl, uint32_t ntot,
+                             uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot || !lflag[s]) return;
+    uint32_t k = lexcl[s];
+    keys[k] = dbl_to_ord(A.E[s]);
+    vals[k] = s;
+}
+__global__ void k_large_gidkeys(const UbArrays A, const uint32_t *__restrict__ vals, uint32_t nl, uint64_t *__restrict__ keys)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < nl) keys[k] = A.gid[vals[k]];
+}
+__global__ void k_large_lstart(const uint32_t *__restrict__ off, const uint32_t *__restrict__ lexcl, uint32_t ngroups, uint32_t ntot,
+                               uint32_t *__restrict__ lstart)
+{
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g > ngroups) return;
+    uint32_t s = off[g];
+    lstart[g] = s < ntot ? lexcl[s] : 0u;
+}
+
+// one thread per group: the decisions of unbind.cxx:556-570 (first evaluation of a large group)
+__global__ void k_large_decide(UbArrays A, UbParams P, uint32_t ngroups)
+{
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    if (g > ngroups) return;
+    uint32_t n = A.off[g + 1] - A.off[g];
+    A.nrem[g] = 0;
+    if ((long long)n < P.large_threshold) return;
+    uint32_t nunb = A.nunb[g];
+    double Efrac = (double)A.nefrac[g] / (double)n;
+    double maxE = ord_to_dbl(A.maxE[g]);
+    if ((double)nunb >= P.maxunboundfrac * (double)n) {
+        A.status[g] = 2;
+        A.nrem[g] = n;
+        atomicOr(A.changed, 1u);
+        return;
+    }
+    long long maxunbindsize = (long long)(P.maxunbindfrac * (double)nunb + 1);
+    bool check;
+    if (P.unbindtype == 0) check = ((Efrac < P.minEfrac) || (maxE > 0)) && ((long long)n >= P.min_size);
+    else check = (maxE > 0) && ((long long)n >= P.min_size);
+    long long nEplus = 0;
+    if (check) {
+        // FillUnboundArrays on an energy-sorted group: the tail walk takes max(nunbound, nEfrac) entries, capped
+        long long nEfrac = 0;
+        if (P.unbindtype == 0 && Efrac < P.minEfrac) nEfrac = (long long)((P.minEfrac - Efrac) * (double)n);
+        long long want = P.unbindtype == 1 ? (long long)nunb : ((long long)nunb > nEfrac ? (long long)nunb : nEfrac);
+        nEplus = want < maxunbindsize ? want : maxunbindsize;
+        if (nEplus > (long long)n) nEplus = n;
+        if ((double)nEplus < P.maxallowed * (double)n) nEplus = 0;
+    }
+    if (nEplus > 0) {
+        A.status[g] = 1;
+        A.nrem[g] = (uint32_t)nEplus;
+        atomicOr(A.changed, 1u);
+    }
+}
+
+// one thread per sorted large-group slot: record the arrangement and retire the removed tail
+__global__ void k_large_apply(UbArrays A, const uint32_t *__restrict__ sorted_slots, const uint32_t *__restrict__ lstart, uint32_t nl)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nl) return;
+    uint32_t s = sorted_slots[k];
+    uint32_t g = A.gid[s];
+    uint32_t p = k - lstart[g];
+    uint32_t n = A.off[g + 1] - A.off[g];
+    A.ord[A.off[g] + p] = s;
+    if (A.status[g] == 2 || p >= n - A.nrem[g]) A.alive[s] = 0;
+}
+
+// one warp per large group that lost particles: UpdateCMForUnboundParticles (unbind.cxx:111-127), RemoveGroup (:129-140)
+__global__ void __launch_bounds__(256) k_large_finish(UbArrays A, UbParams P, uint32_t ngroups)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t g = 1 + wg; g <= ngroups; g += nw) {
+        int st = A.status[g];
+        if (st == 0) continue;
+        uint32_t n = A.off[g + 1] - A.off[g];
+        if ((long long)n < P.large_threshold) continue;
+        uint32_t base = A.off[g];
+        if (st == 2) { if (lane == 0) A.ning[g] = 0; continue; }
+        uint32_t nrem = A.nrem[g], nn = n - nrem;
+        double sm = 0, sx = 0, sy = 0, sz = 0;
+        for (uint32_t p = nn + lane; p < n; p += 32) {
+            uint32_t s = A.ord[base + p];
+            double m = A.m[s];
+            sm += m; sx += A.vx[s] * m; sy += A.vy[s] * m; sz += A.vz[s] * m;
+        }
+        for (int o = 16; o; o >>= 1) {
+            sm += __shfl_xor_sync(0xffffffffu, sm, o); sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            sy += __shfl_xor_sync(0xffffffffu, sy, o); sz += __shfl_xor_sync(0xffffffffu, sz, o);
+        }
+        if ((long long)nn < P.min_size) {
+            for (uint32_t p = lane; p < nn; p += 32) A.alive[A.ord[base + p]] = 0;
+            nn = 0;
+        }
+        if (lane == 0) {
+            double mass = A.gmass[g];
+            double temp = 1.0 / mass;
+            double cx = A.cmvel[3 * g] - sx * temp, cy = A.cmvel[3 * g + 1] - sy * temp, cz = A.cmvel[3 * g + 2] - sz * temp;
+            temp = mass / (mass - sm);
+            A.cmvel[3 * g] = cx * temp; A.cmvel[3 * g + 1] = cy * temp; A.cmvel[3 * g + 2] = cz * temp;
+            A.gmass[g] = mass - sm;
+            A.ning[g] = nn;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// phase B: one CTA per group with 0 < n <= large_threshold -- the small-group loop of unbind.cxx:641-720
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool ub_less(double ea, uint32_t ia, double eb, uint32_t ib)
+{
+    return ea < eb || (ea == eb && ia < ib);
+}
+
+template <typename T> __device__ __forceinline__ T ub_block_sum(T v, T *scratch)
+{
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) scratch[warp] = v;
+    __syncthreads();
+    T r = 0;
+    for (int w = 0; w < UB_T / 32; w++) r += scratch[w];
+    return r;
+}
+__device__ __forceinline__ double ub_block_max(double v, double *scratch)
+{
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();
+    if (lane == 0) scratch[warp] = v;
+    __syncthreads();
+    double r = scratch[0];
+    for (int w = 1; w < UB_T / 32; w++) r = fmax(r, scratch[w]);
+    return r;
+}
+
+__global__ void __launch_bounds__(UB_T) k_unbind_small(UbArrays A, UbParams P, uint32_t ngroups)
+{
+    __shared__ double sE[UB_CAP];
+    __shared__ uint32_t sid[UB_CAP];
+    __shared__ double dscr[UB_T / 32];
+    __shared__ int iscr[UB_T / 32];
+    __shared__ long long s_nEplus;
+    const uint32_t g = blockIdx.x + 1;
+    if (g > ngroups) return;
+    uint32_t n = A.ning[g];
+    if (n == 0 || (long long)n > P.large_threshold || n > UB_CAP) return;
+    const uint32_t base = A.off[g];
+    const int tid = threadIdx.x;
+    for (uint32_t j = tid; j < n; j += UB_T) sid[j] = A.ord[base + j];
+    double cx = A.cmvel[3 * g], cy = A.cmvel[3 * g + 1], cz = A.cmvel[3 * g + 2], mass = A.gmass[g];
+    long long oldn = n; // intended initialisation of `oldnumingroup`
+    bool changed = false, sortflag = true, first = true, check = true;
+    __syncthreads();
+    while (check) {
+        // ---- GetBoundFractionAndMaxE (unbind.cxx:146-185) ----
+        int nunb_l = 0, nef_l = 0;
+        double mx_l = -1e32;
+        for (uint32_t j = tid; j < n; j += UB_T) {
+            double E;
+            bool bf, mg;
+            member_energy(A, P, sid[j], cx, cy, cz, E, bf, mg);
+            sE[j] = E;
+            A.marg[sid[j]] = mg ? 1 : 0;
+            nunb_l += E > 0;
+            nef_l += bf;
+            mx_l = fmax(mx_l, E);
+        }
+        const int nunb = ub_block_sum<int>(nunb_l, iscr);
+        const int nef = ub_block_sum<int>(nef_l, iscr);
+        const double maxE = ub_block_max(mx_l, dscr);
+        const double Efrac = (double)nef / (double)n;
+        bool sorted_now = false;
+        if ((double)nunb < P.maxunboundfrac * (double)n && sortflag) {
+            // std::sort by energy (unbind.cxx:181-184): bitonic network over the next power of two
+            uint32_t np2 = 1;
+            while (np2 < n) np2 <<= 1;
+            for (uint32_t j = n + tid; j < np2; j += UB_T) { sE[j] = 1e308; sid[j] = 0xffffffffu; }
+            __syncthreads();
+            for (uint32_t k = 2; k <= np2; k <<= 1)
+                for (uint32_t jj = k >> 1; jj > 0; jj >>= 1) {
+                    for (uint32_t i = tid; i < np2; i += UB_T) {
+                        uint32_t l = i ^ jj;
+                        if (l > i) {
+                            bool up = (i & k) == 0;
+                            double ei = sE[i], el = sE[l];
+                            uint32_t ii = sid[i], il = sid[l];
+                            bool sw = up ? ub_less(el, il, ei, ii) : ub_less(ei, ii, el, il);
+                            if (sw) { sE[i] = el; sE[l] = ei; sid[i] = il; sid[l] = ii; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            sorted_now = true;
+        }
+        __syncthreads();
+        if (first) {
+            first = false;
+            if ((double)nunb >= P.maxunboundfrac * (double)n) { // unbind.cxx:654-658
+                for (uint32_t j = tid; j < n; j += UB_T) A.alive[sid[j]] = 0;
+                n = 0;
+                changed = true;
+                break;
+            }
+        }
+        // ---- CheckGroupForBoundness + FillUnboundArrays (unbind.cxx:49-98) ----
+        const long long maxunbindsize = (long long)(P.maxunbindfrac * (double)nunb + 1);
+        if (P.unbindtype == 0) check = ((Efrac < P.minEfrac) || (maxE > 0)) && ((long long)n >= P.min_size);
+        else check = (maxE > 0) && ((long long)n >= P.min_size);
+        long long nEplus = 0;
+        if (check) {
+            long long nEfrac = 0;
+            if (P.unbindtype == 0 && Efrac < P.minEfrac) nEfrac = (long long)((P.minEfrac - Efrac) * (double)n);
+            if (sorted_now) {
+                long long want = P.unbindtype == 1 ? (long long)nunb : ((long long)nunb > nEfrac ? (long long)nunb : nEfrac);
+                nEplus = want < maxunbindsize ? want : maxunbindsize;
+                if (nEplus > (long long)n) nEplus = n;
+            } else {
+                // stale arrangement (sortflag == false): literal walk from the tail
+                if (tid == 0) {
+                    long long c = 0;
+                    for (long long j = 0; j < maxunbindsize && j < (long long)n; j++) {
+                        double e = sE[n - 1 - j];
+                        if (e > 0 || (P.unbindtype == 0 && c < nEfrac)) c++;
+                        else break;
+                    }
+                    s_nEplus = c;
+                }
+                __syncthreads();
+                nEplus = s_nEplus;
+                __syncthreads();
+            }
+            if ((double)nEplus < P.maxallowed * (double)n) { nEplus = 0; check = false; }
+        }
+        if (!check) break;
+        // ---- loop body (unbind.cxx:666-709) ----
+        changed = true;
+        {
+            double sm_l = 0, sx_l = 0, sy_l = 0, sz_l = 0;
+            for (uint32_t p = n - (uint32_t)nEplus + tid; p < n; p += UB_T) {
+                uint32_t s = sid[p];
+                double m = A.m[s];
+                sm_l += m; sx_l += A.vx[s] * m; sy_l += A.vy[s] * m; sz_l += A.vz[s] * m;
+                A.alive[s] = 0;
+            }
+            double sm = ub_block_sum<double>(sm_l, dscr), sx = ub_block_sum<double>(sx_l, dscr);
+            double sy = ub_block_sum<double>(sy_l, dscr), sz = ub_block_sum<double>(sz_l, dscr);
+            double temp = 1.0 / mass;
+            cx -= sx * temp; cy -= sy * temp; cz -= sz * temp;
+            temp = mass / (mass - sm);
+            cx *= temp; cy *= temp; cz *= temp;
+            mass -= sm;
+        }
+        n -= (uint32_t)nEplus;
+        if ((double)nEplus < P.maxallowed * (double)n) break; // unbind.cxx:695-697
+        sortflag = false;
+        if ((double)(oldn - (long long)n) > P.maxallowed * (double)oldn) { oldn = n; sortflag = true; }
+        __syncthreads();
+    }
+    // RemoveGroup (unbind.cxx:129-140)
+    if (n > 0 && (long long)n < P.min_size) {
+        for (uint32_t j = tid; j < n; j += UB_T) A.alive[sid[j]] = 0;
+        n = 0;
+        changed = true;
+    }
+    if (tid == 0) {
+        A.ning[g] = n;
+        if (changed) atomicOr(A.changed, 1u);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// relabelling after unbinding (ReorderGroupIDs, buildandsortarrays.cxx:170-181; canonical tie break)
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_iota_u32(uint32_t *a, uint32_t n)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i] = i;
+}
+__global__ void k_new_group_stats(const UbArrays A, const uint32_t *__restrict__ idx, const long long *__restrict__ pid, uint32_t ntot,
+                                  uint32_t *__restrict__ newsize, unsigned long long *__restrict__ minpid, unsigned long long *__restrict__ nmarg)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    bool mg = false;
+    if (s < ntot) {
+        mg = A.marg[s];
+        if (A.alive[s]) {
+            uint32_t g = A.gid[s];
+            uint32_t i = idx[s];
+            atomicAdd(&newsize[g], 1u);
+            atomicMin(&minpid[g], pid ? (unsigned long long)pid[i] : (unsigned long long)i);
+        }
+    }
+    unsigned b = __ballot_sync(0xffffffffu, mg);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(nmarg, (unsigned long long)__popc(b));
+}
+__global__ void k_write_unbound(const UbArrays A, const uint32_t *__restrict__ idx, const uint32_t *__restrict__ gid_of, uint32_t ntot,
+                                long long *__restrict__ pfof)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    pfof[idx[s]] = A.alive[s] ? (long long)gid_of[A.gid[s]] : 0ll;
+}
+__global__ void k_csr_gid(const uint32_t *__restrict__ off, uint32_t ngroups, uint32_t *__restrict__ gid)
+{
+    // one warp per group paints its slots
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t g = 1 + wg; g <= ngroups; g += nw)
+        for (uint32_t s = off[g] + lane; s < off[g + 1]; s += 32) gid[s] = g;
+}
+
+static void compute_potentials(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, double theta, int bucket, long long pp_threshold,
+                               double *phi)
+{
+    StageTimer t(ctx);
+    ctx->stats.n_pairs_potential += (long long)potential_direct(ctx, gs, G, eps, pp_threshold, phi);
+    if (pp_threshold >= 0) potential_tree(ctx, gs, G, eps, theta, bucket, pp_threshold, phi);
+    ctx->stats.potential_ms += t.stop();
+}
+
+void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
+                   int &changed, long long &n_marginal)
+{
+    changed = 0;
+    n_marginal = 0;
+    if (ngroups <= 0 || P.n == 0) return;
+    VR_REQUIRE(o.fracpotref == 1.0, VRGPU_EUNSUPPORTED, "only Frac_pot_ref=1 (whole-group CM frame) is implemented");
+    VR_REQUIRE(o.bgpot == 1, VRGPU_EUNSUPPORTED, "only Keep_background_potential=1 is implemented");
+    VR_REQUIRE(o.large_threshold >= 1 && o.large_threshold <= UB_CAP, VRGPU_EUNSUPPORTED, "large_threshold must be in [1, 2048]");
+    VR_REQUIRE(o.unbindtype == 0 || o.unbindtype == 1, VRGPU_EINVAL, "unbindtype must be 0 or 1");
+    VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "unbinding needs velocities");
+    const int T = 256;
+    GroupSet gs;
+    build_groupset(ctx, pfof_dev, P.n, ngroups, gs);
+    if (gs.ntot == 0) return;
+    gather_groupset(ctx, P, gs, true, true);
+    const uint32_t ntot = (uint32_t)gs.ntot, G = (uint32_t)ngroups;
+    DBuf<double> phi(ctx, ntot);
+    compute_potentials(ctx, gs, o.G, o.eps, o.theta, o.bucket, o.pp_threshold, phi.p);
+
+    StageTimer t(ctx);
+    const size_t G1 = (size_t)G + 1;
+    DBuf<double> E(ctx, ntot), cmvel(ctx, 3 * G1), gmass(ctx, G1);
+    DBuf<uint32_t> ord(ctx, ntot), ning(ctx, G1), nunb(ctx, G1), nefrac(ctx, G1), nrem(ctx, G1);
+    DBuf<unsigned char> alive(ctx, ntot), marg(ctx, ntot);
+    DBuf<unsigned long long> maxE(ctx, G1);
+    DBuf<int> status(ctx, G1);
+    DBuf<unsigned int> chg(ctx, 1);
+    VR_CUDA(cudaMemsetAsync(nunb.p, 0, sizeof(uint32_t) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(nefrac.p, 0, sizeof(uint32_t) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(nrem.p, 0, sizeof(uint32_t) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(ning.p, 0, sizeof(uint32_t) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(maxE.p, 0, sizeof(unsigned long long) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(status.p, 0, sizeof(int) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(chg.p, 0, sizeof(unsigned int), ctx->stream));
+    UbArrays A{};
+    A.vx = gs.vx.p; A.vy = gs.vy.p; A.vz = gs.vz.p; A.m = gs.m.p; A.phi = phi.p;
+    A.gid = gs.gid.p; A.off = gs.off.p;
+    A.E = E.p; A.ord = ord.p; A.alive = alive.p; A.marg = marg.p;
+    A.cmvel = cmvel.p; A.gmass = gmass.p; A.ning = ning.p; A.nunb = nunb.p; A.nefrac = nefrac.p; A.maxE = maxE.p; A.nrem = nrem.p;
+    A.status = status.p; A.changed = chg.p;
+    UbParams Pm{};
+    Pm.Eratio = o.Eratio; Pm.minEfrac = o.minEfrac; Pm.maxunbindfrac = o.maxunbindfrac;
+    Pm.maxunboundfrac = o.maxunboundfracforiterativeunbind; Pm.maxallowed = o.maxallowedunboundfrac;
+    Pm.marginal_tol = o.marginal_tol; Pm.unbindtype = o.unbindtype; Pm.min_size = o.min_size; Pm.large_threshold = o.large_threshold;
+    const unsigned warp_grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 16u));
+
+    VR_LAUNCH(ctx, k_init_slots, grid_for(ntot, T), T, 0, A, ntot);
+    VR_LAUNCH(ctx, k_group_cm, warp_grid, T, 0, A, G);
+
+    // ---- phase A ----
+    {
+        DBuf<uint32_t> lflag(ctx, ntot), lexcl(ctx, ntot), ltotal(ctx, 1);
+        VR_LAUNCH(ctx, k_large_energy, grid_for(ntot, T), T, 0, A, Pm, ntot, lflag.p);
+        exclusive_scan_u32(ctx, lflag.p, lexcl.p, ntot, ltotal.p);
+        uint32_t nl = 0;
+        VR_CUDA(cudaMemcpyAsync(&nl, ltotal.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (nl > 0) {
+            DBuf<uint64_t> keys(ctx, nl), keys_tmp(ctx, nl);
+            DBuf<uint32_t> vals(ctx, nl), vals_tmp(ctx, nl), lstart(ctx, G1 + 1);
+            VR_LAUNCH(ctx, k_large_keys, grid_for(ntot, T), T, 0, A, lflag.p, lexcl.p, ntot, keys.p, vals.p);
+            radix_sort_pairs(ctx, keys.p, vals.p, keys_tmp.p, vals_tmp.p, nl, 64);
+            VR_LAUNCH(ctx, k_large_gidkeys, grid_for(nl, T), T, 0, A, vals.p, nl, keys.p);
+            int gbits = 1;
+            while ((1ull << gbits) <= (unsigned long long)G) gbits++;
+            radix_sort_pairs(ctx, keys.p, vals.p, keys_tmp.p, vals_tmp.p, nl, gbits);
+            VR_LAUNCH(ctx, k_large_decide, grid_for(G, T), T, 0, A, Pm, G);
+            // lstart[g] = position of group g's first member in the compacted gid-sorted list = lexcl[off[g]]
+            // (slots of one group are contiguous and a large group is compacted whole)
+            VR_LAUNCH(ctx, k_large_lstart, grid_for(G1, T), T, 0, gs.off.p, lexcl.p, G, ntot, lstart.p);
+            VR_LAUNCH(ctx, k_large_apply, grid_for(nl, T), T, 0, A, vals.p, lstart.p, nl);
+            VR_LAUNCH(ctx, k_large_finish, warp_grid, T, 0, A, Pm, G);
+        }
+    }
+    // ---- phase B ----
+    VR_LAUNCH(ctx, k_unbind_small, G, UB_T, 0, A, Pm, G);
+
+    // ---- results ----
+    DBuf<uint32_t> newsize(ctx, G1), iota(ctx, G1), gid_of(ctx, G1);
+    DBuf<unsigned long long> minpid(ctx, G1), nmarg(ctx, 1);
+    VR_CUDA(cudaMemsetAsync(newsize.p, 0, sizeof(uint32_t) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(minpid.p, 0xff, sizeof(unsigned long long) * G1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(nmarg.p, 0, sizeof(unsigned long long), ctx->stream));
+    VR_LAUNCH(ctx, k_new_group_stats, grid_for(ntot, T), T, 0, A, gs.idx.p, P.has_pid ? P.pid.p : (const long long *)nullptr, ntot, newsize.p,
+              minpid.p, nmarg.p);
+    unsigned int hchg = 0;
+    unsigned long long hmarg = 0;
+    VR_CUDA(cudaMemcpyAsync(&hchg, chg.p, sizeof(hchg), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(&hmarg, nmarg.p, sizeof(hmarg), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    n_marginal = (long long)hmarg;
+    changed = hchg ? 1 : 0;
+    if (changed) {
+        VR_LAUNCH(ctx, k_iota_u32, grid_for(G1, T), T, 0, iota.p, G + 1);
+        uint32_t ng = order_groups(ctx, iota.p, newsize.p, minpid.p, G + 1, 1u, gid_of.p);
+        VR_LAUNCH(ctx, k_write_unbound, grid_for(ntot, T), T, 0, A, gs.idx.p, gid_of.p, ntot, pfof_dev);
+        ngroups = ng;
+    }
+    ctx->stats.unbind_ms += t.stop();
+}
+
+// vrgpu_potential: groups handed over in CSR form by the host
+void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                        const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,
+                        double *phi_out_host)
+{
+    const long long ntot = offsets_host[ngroups];
+    if (ntot == 0) return;
+    VR_REQUIRE(ntot < 0xfffffff0LL && ngroups < 0x7fffffffLL, VRGPU_EINVAL, "CSR too large");
+    VR_REQUIRE(offsets_host[0] == 0, VRGPU_EINVAL, "offsets[0] must be 0");
+    std::vector<uint32_t> off((size_t)ngroups + 2), idx((size_t)ntot);
+    off[0] = 0;
+    for (long long g = 0; g <= ngroups; g++) {
+        VR_REQUIRE(offsets_host[g] >= 0 && (g == 0 || offsets_host[g] >= offsets_host[g - 1]), VRGPU_EINVAL, "offsets must be non-decreasing");
+        off[(size_t)g + 1] = (uint32_t)offsets_host[g];
+    }
+    for (long long k = 0; k < ntot; k++) {
+        VR_REQUIRE(index_host[k] >= 0 && (size_t)index_host[k] < P.n, VRGPU_EINVAL, "index out of range");
+        idx[(size_t)k] = (uint32_t)index_host[k];
+    }
+    GroupSet gs;
+    gs.ntot = (size_t)ntot;
+    gs.ngroups = ngroups;
+    gs.off.alloc(ctx, off.size());
+    gs.idx.alloc(ctx, idx.size());
+    gs.gid.alloc(ctx, idx.size());
+    VR_CUDA(cudaMemcpyAsync(gs.off.p, off.data(), off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(gs.idx.p, idx.data(), idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    VR_LAUNCH(ctx, k_csr_gid, std::max(1u, std::min<unsigned>(grid_for((size_t)ngroups * 32, 256), (unsigned)ctx->sm_count * 16u)), 256, 0,
+              gs.off.p, (uint32_t)ngroups, gs.gid.p);
+    gather_groupset(ctx, P, gs, false, true);
+    DBuf<double> phi(ctx, (size_t)ntot);
+    compute_potentials(ctx, gs, G, eps, theta, bucket, pp_threshold, phi.p);
+    VR_CUDA(cudaMemcpyAsync(phi_out_host, phi.p, (size_t)ntot * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->stats.d2h_bytes += ntot * 8;
+}
+
+} // namespace vrgpu
