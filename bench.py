@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py -- FOF + unbinding throughput of the B200 structure-finding path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--nside 256]
+
+A "step" is one pass of the hot path (SearchFullSet DM path: 3DFOF -> AdjustStructureForPeriod -> [6DFOF] ->
+CheckUnboundGroups) over one synthetic clustered periodic box.  Default workload = BASELINE.json configs[1]:
+3DFOF + direct-sum potential unbinding on a 256^3 box on one B200.
+
+  value     Mparticles/s with the particles already resident in HBM (vrgpu_search_full_set_resident), timed with
+            CUDA events on the library's stream, max over ranks.
+  e2e       the same metric through the reference-facing call vrgpu_search_full_set on pinned HOST particles
+            (96-byte NBody::Particle AoS): host->device unpack, the path, pfof + unwrapped positions back.
+  roofline  dominant kernel group (by measured device time), algorithmic bytes or flops from DESIGN.md.
+  cpu_baseline  the reference's own OpenMP SearchFullSet (oracle/_ref/libvrref_omp.so) on a bounded sample.
+
+`--impl reference` times only the reference CPU implementation (all host threads) on bounded samples.
+Nothing here reads /root/reference; oracle/ is used only for the cpu_baseline / reference legs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "velociraptor-stf_b200"))
+
+import numpy as np  # noqa: E402
+
+METRIC = "fof_unbind_throughput"
+UNIT = "Mparticles/s"
+
+# algorithmic work per particle / pair (DESIGN.md "Roofline accounting")
+ALG_BYTES = {
+    "fof3d.link_cells": 32.0,     # sorted position read once (24 B) + label written (8 B)
+    "fof3d.radix_sort": 64.0,     # 4 digit passes x (8 B read + 8 B write) of (key32, index32)
+    "fof3d.gather_pos": 48.0,     # 24 B read + 24 B write
+    "fof3d.cell_keys": 28.0,      # 24 B read + 4 B key written
+}
+FLOPS_PER_ORDERED_PAIR = 8.0      # F_pp = 8 n (n-1) per group (16 flops per unordered pair, unbind.cxx:404-409)
+FP64_PEAK_TFLOPS_NOMINAL = 40.0   # B200 vector FP64 (vendor figure; not in MEASURED_PEAKS.json)
+
+
+def workload_name(nside: int, fofbgtype: int, pp: int) -> str:
+    stages = "3DFOF" + ("+6DFOF" if fofbgtype <= 4 else "") + ("+direct-sum unbinding" if pp < 0 else "+tree/direct unbinding")
+    return f"{stages} on a {nside}^3 synthetic clustered periodic DM box (L=100, b=0.2, seed {seed_for(nside)})"
+
+
+def seed_for(nside: int) -> int:
+    return {128: 101, 256: 102, 512: 103, 1024: 104}.get(nside, 100 + nside)
+
+
+def measured_peaks() -> tuple[dict, str]:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi sampling DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm),
+                       power_w_max=float(max(pw)))
+        return out
+
+
+def make_search_opts(vrgpu, nside: int, fofbgtype: int, pp: int):
+    import vrsynth
+    ell = vrsynth.BOX / nside
+    param1 = (ell * ell) * (0.2 * 0.2) * (1.0 * 1.0)          # search.cxx:77
+    ub = vrgpu.default_unbind_opts(pp_threshold=pp)
+    return vrgpu.search_opts(vrsynth.BOX, param1, halo_min_size=20, fofbgtype=fofbgtype, bound_halos=1, unbind=ub)
+
+
+# ------------------------------------------------------------------------------------------------------
+# reference / cpu baseline leg (oracle/_ref, test infrastructure -- never on the product path)
+# ------------------------------------------------------------------------------------------------------
+def reference_step(nside: int, fofbgtype: int, seed: int | None = None) -> dict:
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import vroracle
+    import vrsynth
+    kind = "reference"
+    variant = "omp" if vroracle.Ref.available("omp") else ("serial" if vroracle.Ref.available("serial") else None)
+    d = vrsynth.make_box(nside ** 3, seed if seed is not None else seed_for(nside))
+    cores = os.cpu_count() or 1
+    if variant is not None:
+        if variant == "omp":
+            os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+        ref = vroracle.Ref(variant)
+        o = vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, fofbgtype=fofbgtype, bound_halos=1,
+                                  omp_fof=1 if variant == "omp" else 0)
+        r = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], o)
+        sec, ng = r["seconds"], r["ngroups"]
+        if variant != "omp":
+            cores = 1
+    else:  # compiled reference absent: our scalar C port
+        kind, cores = "port", 1
+        orc = vroracle.Oracle()
+        t0 = time.perf_counter()
+        b = 0.2 * vrsynth.BOX / nside
+        pf, ng = orc.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+        pos = orc.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+        uo = vroracle.unbind_opts_from(vroracle.default_opts(), pp_threshold=150)
+        ng = orc.unbind(pos, d["vel"], d["mass"], pf, ng, uo, d["pid"], 1e-6)["ngroups"]
+        sec = time.perf_counter() - t0
+    return {"seconds": sec, "n": nside ** 3, "ngroups": ng, "kind": kind, "cores": cores,
+            "sample": f"{nside}^3 box from the same generator (seed {seed if seed is not None else seed_for(nside)}), the reference's own SearchFullSet "
+                      f"({'OpenMP' if variant == 'omp' else 'serial'} build, -O2), whole call timed"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # bounded sample: ~1.5e-5 s per particle on a handful of cores -> pick the box so K+W steps stay within minutes
+    total_steps = args.steps + args.warmup
+    ns = args.cpu_nside or (128 if total_steps <= 3 else (96 if total_steps <= 8 else 64))
+    for _ in range(args.warmup):
+        reference_step(ns, args.fofbgtype)
+    secs = []
+    r = None
+    for _ in range(args.steps):
+        r = reference_step(ns, args.fofbgtype)
+        secs.append(r["seconds"])
+    t = float(np.sum(secs))
+    value = args.steps * r["n"] / t / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args.nside, args.fofbgtype, args.pp_threshold), "cpu_sample_nside": ns},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import vrgpu
+    import vrsynth
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import bench_multigpu
+        return bench_multigpu.run(args, rank, world, local)
+
+    nside = args.nside
+    n = nside ** 3
+    d = vrsynth.make_box(n, seed_for(nside))
+    ctx = vrgpu.Context(local)
+    so = make_search_opts(vrgpu, nside, args.fofbgtype, args.pp_threshold)
+    pristine = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"])
+    parts = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"], pinned=True)
+    del d
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=local)
+
+    # ---- resident arm (`value`) ----
+    ctx.particles_upload(parts)
+    ng = 0
+    for _ in range(args.warmup):
+        ng = ctx.search_full_set_resident(so)
+    ctx.kernel_times_reset()
+    sampler = ClockSampler(local)
+    sampler.start()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches = 0
+    stage_ms = {}
+    ev0.record(stream)
+    for _ in range(args.steps):
+        ng = ctx.search_full_set_resident(so)
+        st = ctx.stats()
+        launches += st["kernel_launches"]
+        for k in ("sort_ms", "link_ms", "label_ms", "fof6d_ms", "potential_ms", "unbind_ms"):
+            stage_ms[k] = stage_ms.get(k, 0.0) + st[k]
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    ktimes = ctx.kernel_times()
+    st_last = ctx.stats()
+    ms_step = ms_total / args.steps
+    value = n / (ms_step * 1e-3) / 1e6
+    ctx.particles_release()
+
+    # ---- e2e arm: reference-facing call on pinned host particles ----
+    e2e_ms = []
+    h2d = d2h = 0
+    for it in range(1 + args.steps):          # one warm-up
+        parts[:] = pristine                    # the call rewrites positions in place (AdjustStructureForPeriod): restore, untimed
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        pf, ng_e = ctx.search_full_set(parts, so)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) * 1e3
+        if it > 0:
+            e2e_ms.append(dt)
+            s = ctx.stats()
+            h2d, d2h = s["h2d_bytes"], s["d2h_bytes"]
+    e2e_value = n / (float(np.mean(e2e_ms)) * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel group ----
+    peaks, peaks_kind = measured_peaks()
+    groups = {k: v for k, v in ktimes.items() if k != "copy_pristine"}
+    dom = max(groups, key=lambda k: groups[k]["ms"]) if groups else None
+    roof_all = {}
+    for k, v in groups.items():
+        ms = v["ms"] / args.steps
+        if ms <= 0:
+            continue
+        if k in ALG_BYTES:
+            a = ALG_BYTES[k] * n / (ms * 1e-3) / 1e9
+            roof_all[k] = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"], "ms": ms}
+        elif k == "potential.direct":
+            a = FLOPS_PER_ORDERED_PAIR * st_last["n_pairs_potential"] / (ms * 1e-3) / 1e12
+            roof_all[k] = {"bound": "fp64", "achieved": a, "peak": FP64_PEAK_TFLOPS_NOMINAL, "unit": "TFLOP/s",
+                           "frac": a / FP64_PEAK_TFLOPS_NOMINAL, "ms": ms, "peak_kind": "nominal vector FP64"}
+        else:
+            roof_all[k] = {"ms": ms}
+    roofline = dict(roof_all.get(dom, {}))
+    roofline.update({"kernel": dom, "traffic": None, "peak_kind": roofline.get("peak_kind", peaks_kind)})
+
+    # ---- cpu baseline (bounded sample) ----
+    cpu = None
+    if not args.no_cpu_baseline:
+        r = reference_step(args.cpu_nside or 128, args.fofbgtype)
+        cpu = {"value": r["n"] / r["seconds"] / 1e6, "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
+               "seconds": r["seconds"]}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(nside, args.fofbgtype, args.pp_threshold), "n_particles": n, "ngroups": ng,
+                       "l2": "inputs (1.07 GB of columns at 256^3) larger than the 126 MB L2; no explicit flush",
+                       "parallelism": "1 GPU"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": float(np.mean(e2e_ms)), "ngroups": ng_e},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "roofline_all": roof_all,
+            "stage_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
+            "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    ctx.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--nside", type=int, default=256)
+    ap.add_argument("--fofbgtype", type=int, default=5, help="5 = 3DFOF, 3 = adaptive 6DFOF inside each halo")
+    ap.add_argument("--pp-threshold", type=int, default=-1, help="<0: direct sum for every group (configs[1]); 150 = reference UNBINDNUM")
+    ap.add_argument("--cpu-nside", type=int, default=0, help="box side of the bounded CPU sample (default 128)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -134,6 +134,26 @@ int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long lo
 int vrgpu_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, const vrgpu_search_opts *opts,
                           long long *pfof_out, long long *ngroups_out);
 
+/* ---- device-resident variant ---------------------------------------------------------------------------
+ * The reference is also driven as a library on particles its caller already holds in memory
+ * (InvokeVelociraptor, src/swiftinterface.cxx:271-598, calls SearchFullSet at :419 on the simulation's own
+ * particle array).  The equivalent here: hand the particles over ONCE, keep them in HBM, and run the path on
+ * them any number of times (each run restarts from the pristine copy, because the path rewrites positions
+ * and velocities exactly as the reference does).  Results stay on the device until asked for. */
+int vrgpu_particles_upload(vrgpu_ctx *ctx, vrgpu_view view);
+int vrgpu_particles_release(vrgpu_ctx *ctx);
+int vrgpu_search_full_set_resident(vrgpu_ctx *ctx, const vrgpu_search_opts *opts, long long *ngroups_out);
+/* copy the pfof of the last resident run to the host (n entries, caller's particle order) */
+int vrgpu_resident_pfof(vrgpu_ctx *ctx, long long *pfof_out);
+
+/* ---- measurement hooks ------------------------------------------------------------------------------- */
+/* the CUDA stream (cudaStream_t) every kernel of this context is launched on, for event timing by the caller */
+void *vrgpu_stream(vrgpu_ctx *ctx);
+/* Per-kernel device times accumulated since the last reset: one line per kernel group,
+ * "<name> <milliseconds> <launch-brackets>\n".  Returns a pointer owned by the context. */
+const char *vrgpu_kernel_times(vrgpu_ctx *ctx);
+void vrgpu_kernel_times_reset(vrgpu_ctx *ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -775,7 +775,7 @@ long long vro_unbind(long long n, const double *pos, const double *vel, const do
     free(gphi); free(gm); free(gx);
 
     int iunbindflag = 0;
-    i64 oldnumingroup = 0;
+    i64 oldnumingroup = o->sortflag_mode == 1 ? o->oldn_init : 0;
     /* unbind.cxx:552: large groups first, serial */
     for (i64 g = 1; g <= ngroups; g++)
         if (num[g] >= o->large_threshold)

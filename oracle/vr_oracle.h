@@ -30,7 +30,9 @@ typedef struct {
     long long pp_threshold;   /* UNBINDNUM: groups with n <= this use the direct sum (allvars.h:210); <0: all direct */
     long long large_threshold;/* ompunbindnum 1000 (ompvar.h:26) */
     int sortflag_mode;        /* 0: oldnumingroup initialised per group (intended semantics, what the GPU does)
-                                 1: literal serial reference: oldnumingroup carried across groups */
+                                 1: literal serial reference: oldnumingroup carried across groups,
+                                    starting from oldn_init (the reference reads it UNINITIALISED: stack garbage) */
+    long long oldn_init;      /* mode 1 only: the garbage value assumed for the uninitialised oldnumingroup */
 } vro_unbind_opts;
 
 /* KDTree::FOF with TPHYS (KDFOF.cxx:12-129, KDLeafNode.cxx:518-573, KDSplitNode.cxx:1496-1540):

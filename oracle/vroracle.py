@@ -174,11 +174,11 @@ class UnbindOpts(C.Structure):
         ("maxunboundfracforiterativeunbind", c_dbl), ("maxallowedunboundfrac", c_dbl),
         ("theta", c_dbl), ("bucket", C.c_int),
         ("min_size", c_ll), ("pp_threshold", c_ll), ("large_threshold", c_ll),
-        ("sortflag_mode", C.c_int),
+        ("sortflag_mode", C.c_int), ("oldn_init", c_ll),
     ]
 
 
-def unbind_opts_from(o: RefOpts, pp_threshold: int = 150, sortflag_mode: int = 0) -> UnbindOpts:
+def unbind_opts_from(o: RefOpts, pp_threshold: int = 150, sortflag_mode: int = 0, oldn_init: int = 0) -> UnbindOpts:
     u = UnbindOpts()
     u.G = o.G; u.eps = o.eps; u.Eratio = o.Eratio; u.minEfrac = o.minEfrac
     u.unbindtype = o.unbindtype; u.bgpot = o.bgpot; u.fracpotref = o.fracpotref
@@ -188,6 +188,7 @@ def unbind_opts_from(o: RefOpts, pp_threshold: int = 150, sortflag_mode: int = 0
     u.theta = o.TreeThetaOpen; u.bucket = o.BucketSize
     u.min_size = o.min_size; u.pp_threshold = pp_threshold; u.large_threshold = 1000
     u.sortflag_mode = sortflag_mode
+    u.oldn_init = oldn_init
     return u
 
 

@@ -1,0 +1,49 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference compiled into oracle/_ref (run where
+/root/reference exists: `python tests/golden/make_golden.py`).  The vectors pin the oracle restatement and
+the CUDA path on machines where the reference cannot be rebuilt.
+
+Each file holds the float32-exact inputs and the reference's outputs:
+  pfof3d     SearchFullSet, FoF_Field_search_type=5 (3DFOF), Bound_halos=0, canonical ids
+  pfof6d     SearchFullSet, FoF_Field_search_type=3 (adaptive 6DFOF inside each 3D group), canonical ids
+  pfof_unb   SearchFullSet, type 5 + Bound_halos=1 (CheckUnboundGroups: direct sum n<=150, tree above)
+  phi_tree   Potential() (kd-tree monopole, theta 0.5, bucket 8) of the largest 3D group, member order = index order
+  pos_out    positions after the type-5 run (AdjustStructureForPeriod applied)
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, os.path.join(ROOT, "velociraptor-stf_b200"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import vroracle  # noqa: E402
+import vrsynth  # noqa: E402
+
+CASES = [("box20_s1", 20, 1), ("box24_s2", 24, 2), ("box32_s7", 32, 7)]
+
+
+def main():
+    ref = vroracle.Ref("serial")
+    for name, nside, seed in CASES:
+        d = vrsynth.make_box(nside ** 3, seed)
+        base = dict(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, omp_fof=0)
+        r5 = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], vroracle.default_opts(fofbgtype=5, **base))
+        r3 = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], vroracle.default_opts(fofbgtype=3, **base))
+        ru = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], vroracle.default_opts(fofbgtype=5, bound_halos=1, **base))
+        c5, _ = vrsynth.canonical_groups(r5["pfof"], d["pid"])
+        c3, _ = vrsynth.canonical_groups(r3["pfof"], d["pid"])
+        cu, _ = vrsynth.canonical_groups(ru["pfof"], d["pid"])
+        sel = np.flatnonzero(c5 == 1)
+        phi = ref.potential(r5["pos"][sel], d["mass"][sel], vroracle.default_opts())
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), nside=nside, seed=seed, box=vrsynth.BOX,
+                            pos=d["pos"].astype(np.float32), vel=d["vel"].astype(np.float32),
+                            mass=np.float32(d["mass"][0]), pfof3d=c5.astype(np.int32), pfof6d=c3.astype(np.int32),
+                            pfof_unb=cu.astype(np.int32), phi_tree=phi, pos_out=r5["pos"],
+                            ng3d=int(c5.max()), ng6d=int(c3.max()), ngunb=int(cu.max()))
+        print(name, "groups 3d/6d/unbound:", int(c5.max()), int(c3.max()), int(cu.max()), "largest", len(sel))
+
+
+if __name__ == "__main__":
+    main()

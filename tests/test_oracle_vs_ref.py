@@ -1,0 +1,105 @@
+"""CPU: the oracle restatement against the reference itself (oracle/_ref/libvrref.so, compiled from /root/reference by
+oracle/Makefile).  Skipped where the reference library is absent."""
+import numpy as np
+import pytest
+
+import vrsynth
+
+G = 43.0211349
+
+
+def _opts(vroracle, nside, **kw):
+    return vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, omp_fof=0, **kw)
+
+
+@pytest.mark.parametrize("nside,seed", [(16, 3), (40, 5)])
+def test_fof3d_vs_kdtree_fof(ref, oracle, nside, seed):
+    d = vrsynth.make_box(nside ** 3, seed)
+    b = 0.2 * vrsynth.BOX / nside
+    pr, nr = ref.kdfof(d["pos"], None, 3, b, vrsynth.BOX, 20, 16)
+    cr, _ = vrsynth.canonical_groups(pr, d["pid"])
+    po, no = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    assert nr == no and np.array_equal(cr, po)
+    # open box too
+    pr, nr = ref.kdfof(d["pos"], None, 3, b, None, 5, 16)
+    cr, _ = vrsynth.canonical_groups(pr, d["pid"])
+    po, no = oracle.fof3d(d["pos"], b, None, 5, d["pid"])
+    assert nr == no and np.array_equal(cr, po)
+
+
+def test_fof6d_direct_tree_call(ref, oracle):
+    """KDTree::FOF on a 6-D tree (TPHS) == oracle 6-D link of pre-scaled coordinates."""
+    rng = np.random.default_rng(2)
+    x = rng.random((3000, 3)) * 6
+    v = rng.normal(size=(3000, 3)) * 0.4
+    pr, nr = ref.kdfof(x, v, 6, 1.0, None, 5, 16)
+    cr, _ = vrsynth.canonical_groups(pr)
+    # oracle: one 3D "group" holding everything, b6 = 1, vscale forced to 1 through mode 3 is not possible, so compare
+    # through the public 6DFOF with a single group and unit dispersion scaling
+    pf3 = np.ones(3000, dtype=np.int64)
+    mass = np.ones(3000)
+    r = oracle.fof6d(x, v, mass, pf3, 1, 1.0, 1.0, 3, 5)
+    vs2 = r["vscale2"][1]
+    # rescale velocities so that the reference sees the same metric
+    pr, nr = ref.kdfof(x * (1.0 / 1.0), v * (1.0 / np.sqrt(vs2)), 6, 1.0, None, 5, 16)
+    cr, _ = vrsynth.canonical_groups(pr)
+    assert nr == r["ngroups"] and np.array_equal(cr, r["pfof"])
+
+
+@pytest.mark.parametrize("fofbgtype", [3, 4])
+def test_search_full_set_6dfof(ref, oracle, fofbgtype):
+    import vroracle
+    nside = 32
+    d = vrsynth.make_box(nside ** 3, 11)
+    r = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], _opts(vroracle, nside, fofbgtype=fofbgtype))
+    cr, _ = vrsynth.canonical_groups(r["pfof"], d["pid"])
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    o = oracle.fof6d(pos, d["vel"], d["mass"], pf, ng, b, 1.25, fofbgtype, 20, d["pid"])
+    assert o["ngroups"] == r["ngroups"]
+    assert np.array_equal(o["pfof"], cr)
+    # Q3: scale/unscale rounding reproduced exactly
+    assert np.array_equal(o["pos"], r["pos"]) and np.array_equal(o["vel"], r["vel"])
+
+
+@pytest.mark.parametrize("n", [151, 1000, 4000])
+def test_tree_potential(ref, oracle, n):
+    import vroracle
+    rng = np.random.default_rng(n)
+    r = rng.random(n) ** 1.5
+    dd = rng.normal(size=(n, 3))
+    pos = 50 + r[:, None] * dd / np.linalg.norm(dd, axis=1)[:, None]
+    mass = 0.5 + rng.random(n)
+    for eps in (0.0, 0.02):
+        want = ref.potential(pos, mass, vroracle.default_opts(eps=eps))
+        got, _ = oracle.potential_tree(pos, mass, G, eps, 0.5, 8)
+        assert np.max(np.abs(got / want - 1.0)) < 1e-12
+
+
+@pytest.mark.parametrize("nside,seed,unbindtype", [(32, 7, 0), (40, 3, 1), (24, 2, 0)])
+def test_unbind(ref, oracle, nside, seed, unbindtype):
+    """CheckUnboundGroups.  The reference reads `oldnumingroup` uninitialised in its small-group loop (unbind.cxx:643,700;
+    SURVEY Q10), so groups that need a second removal pass depend on stack garbage.  The oracle is run with the three
+    possible behaviours (garbage 0, garbage huge, intended per-group initialisation); every particle on which the three
+    agree must match the reference exactly, and the reference must be within the envelope of the three elsewhere."""
+    import vroracle
+    d = vrsynth.make_box(nside ** 3, seed)
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    ro = vroracle.default_opts(unbindtype=unbindtype)
+    want = ref.unbind(pos, d["vel"], d["mass"], pf, ng, ro)
+    wb = want["pfof"] > 0
+    variants = []
+    for mode, init in ((1, 0), (1, 1 << 60), (0, 0)):
+        uo = vroracle.unbind_opts_from(ro, 150, sortflag_mode=mode, oldn_init=init)
+        variants.append(oracle.unbind(pos, d["vel"], d["mass"], pf, ng, uo, d["pid"], 1e-6))
+    bound = np.stack([v["pfof"] > 0 for v in variants])
+    agree = np.all(bound == bound[0], axis=0)
+    nmarg = max(v["n_marginal"] for v in variants)
+    assert int(np.count_nonzero(bound[0][agree] != wb[agree])) <= nmarg
+    # where the variants disagree the reference sides with at least one of them
+    assert np.all(np.any(bound[:, ~agree] == wb[~agree], axis=0))
+    assert int(np.count_nonzero(~agree)) < 0.01 * np.count_nonzero(pf > 0) + 50
+    assert all(v["changed"] == want["changed"] for v in variants)

@@ -5,8 +5,17 @@
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
+#include <memory>
 
 using namespace vrgpu;
+
+namespace vrgpu {
+struct ResidentState {
+    DeviceParticles pristine;
+    DBuf<long long> pfof;
+    long long ngroups = 0;
+};
+} // namespace vrgpu
 
 namespace {
 
@@ -39,6 +48,7 @@ struct CallTimer {
     ~CallTimer()
     {
         cudaStreamSynchronize(ctx->stream);
+        resolve_ktimes(ctx);
         ctx->stats.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
 };
@@ -65,6 +75,83 @@ void upload_i64(vrgpu_ctx *ctx, const long long *host, size_t n, DBuf<long long>
     dev.alloc(ctx, n ? n : 1);
     if (n) VR_CUDA(cudaMemcpyAsync(dev.p, host, n * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream));
     ctx->stats.h2d_bytes += (long long)(n * sizeof(long long));
+}
+
+
+void check_search_opts(const vrgpu_search_opts *o)
+{
+    VR_REQUIRE(o->fofbgtype == 5 || o->fofbgtype == 4 || o->fofbgtype == 3, VRGPU_EUNSUPPORTED,
+               "FoF_Field_search_type must be 5 (3DFOF), 4 (6DFOF) or 3 (adaptive 6DFOF)");
+    VR_REQUIRE(o->param1 > 0, VRGPU_EINVAL, "param1 (squared linking length) must be positive");
+}
+
+// Borrow read-only columns (vel / mass / pid) of the pristine resident copy into a working DeviceParticles without
+// copying; the borrowed DBufs are detached again before they could be returned to the pool twice.
+struct BorrowGuard {
+    DeviceParticles &P;
+    bool vel;
+    BorrowGuard(DeviceParticles &p, const DeviceParticles &S, bool borrow_vel) : P(p), vel(borrow_vel && S.has_vel)
+    {
+        if (vel) { P.vel.p = S.vel.p; P.vel.n = S.vel.n; P.vel.ctx = nullptr; P.has_vel = true; }
+        if (S.has_mass) { P.mass.p = S.mass.p; P.mass.n = S.mass.n; P.mass.ctx = nullptr; P.has_mass = true; }
+        if (S.has_pid) { P.pid.p = S.pid.p; P.pid.n = S.pid.n; P.pid.ctx = nullptr; P.has_pid = true; }
+    }
+    ~BorrowGuard()
+    {
+        if (vel) { P.vel.p = nullptr; P.vel.n = 0; }
+        if (P.mass.ctx == nullptr) { P.mass.p = nullptr; P.mass.n = 0; }
+        if (P.pid.ctx == nullptr) { P.pid.p = nullptr; P.pid.n = 0; }
+    }
+};
+
+// The DM path of SearchFullSet (src/search.cxx:24-854) on device-resident particles.  `view` (may be null) is the
+// caller's writable host array that receives the reference's in-place coordinate updates.
+void run_search(vrgpu_ctx *ctx, DeviceParticles &P, const vrgpu_search_opts *o, const vrgpu_view *view, DBuf<long long> &pf, long long &ng)
+{
+    const bool six = o->fofbgtype <= 4;
+    const bool unbind = o->bound_halos >= 1;
+    Fof3dState S;
+    fof3d_device(ctx, P, std::sqrt(o->param1), o->period, o->halo_min_size, S);
+    ng = S.ngroups;
+    pf = std::move(S.pfof);
+    // search.cxx:393-396
+    if (o->period > 0 && ng > 0) {
+        DBuf<uint32_t> midx;
+        DBuf<double> mxyz;
+        size_t cnt;
+        {
+            KScope k(ctx, "adjust_for_period");
+            cnt = adjust_for_period_device(ctx, P, pf.p, ng, o->period, midx, mxyz);
+        }
+        if (view) {
+            StageTimer t(ctx);
+            scatter_positions_to_host(ctx, *view, view->off_pos, midx.p, mxyz.p, cnt);
+            ctx->stats.d2h_ms += t.stop();
+        }
+    }
+    // free the grid before the later stages need memory
+    S = Fof3dState{};
+    if (six && ng > 0) {
+        DBuf<long long> pf6(ctx, P.n);
+        StageTimer t(ctx);
+        // search.cxx:410: param[1] *= ellhalo6dxfac^2 ; b6 = sqrt(param[1])
+        double param1 = o->param1 * (o->ellhalo6dxfac * o->ellhalo6dxfac);
+        long long ng6 = fof6d_device(ctx, P, pf.p, ng, std::sqrt(param1), o->ellhalo6dvfac, o->fofbgtype, o->halo_min_size, pf6.p, true);
+        ctx->stats.fof6d_ms += t.stop();
+        if (view) {
+            StageTimer t2(ctx);
+            writeback_phase(ctx, *view, P, pf.p);
+            ctx->stats.d2h_ms += t2.stop();
+        }
+        pf = std::move(pf6);
+        ng = ng6;
+    }
+    if (unbind && ng > 0) {
+        int changed = 0;
+        long long nmarg = 0;
+        unbind_device(ctx, P, pf.p, ng, o->unbind, changed, nmarg);
+        ctx->stats.n_marginal = nmarg;
+    }
 }
 
 } // namespace
@@ -109,6 +196,12 @@ void vrgpu_destroy(vrgpu_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    delete ctx->resident;
+    ctx->resident = nullptr;
+    mg_destroy(ctx);
+    resolve_ktimes(ctx);
+    for (cudaEvent_t e : ctx->evpool) cudaEventDestroy(e);
+    ctx->evpool.clear();
     ctx->pool.release_all();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     cudaStreamDestroy(ctx->stream);
@@ -250,8 +343,7 @@ int vrgpu_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, const vrgpu_search_op
 {
     return guarded(ctx, [&] {
         VR_REQUIRE(o && pfof_out && ngroups_out, VRGPU_EINVAL, "null pointer");
-        VR_REQUIRE(o->fofbgtype == 5 || o->fofbgtype == 4 || o->fofbgtype == 3, VRGPU_EUNSUPPORTED,
-                   "FoF_Field_search_type must be 5 (3DFOF), 4 (6DFOF) or 3 (adaptive 6DFOF)");
+        check_search_opts(o);
         CallTimer ct(ctx);
         const bool six = o->fofbgtype <= 4;
         const bool unbind = o->bound_halos >= 1;
@@ -261,42 +353,9 @@ int vrgpu_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, const vrgpu_search_op
             upload_view(ctx, view, six || unbind, six || unbind, true, P);
             ctx->stats.h2d_ms += t.stop();
         }
-        Fof3dState S;
-        fof3d_device(ctx, P, std::sqrt(o->param1), o->period, o->halo_min_size, S);
-        long long ng = S.ngroups;
-        DBuf<long long> pf = std::move(S.pfof);
-        // search.cxx:393-396
-        if (o->period > 0 && ng > 0) {
-            DBuf<uint32_t> midx;
-            DBuf<double> mxyz;
-            size_t cnt = adjust_for_period_device(ctx, P, pf.p, ng, o->period, midx, mxyz);
-            StageTimer t(ctx);
-            scatter_positions_to_host(ctx, view, view.off_pos, midx.p, mxyz.p, cnt);
-            ctx->stats.d2h_ms += t.stop();
-        }
-        // free the grid before the later stages need memory
-        S = Fof3dState{};
-        if (six && ng > 0) {
-            DBuf<long long> pf6(ctx, P.n);
-            StageTimer t(ctx);
-            // search.cxx:410: param[1] *= ellhalo6dxfac^2 ; b6 = sqrt(param[1])
-            double param1 = o->param1 * (o->ellhalo6dxfac * o->ellhalo6dxfac);
-            long long ng6 = fof6d_device(ctx, P, pf.p, ng, std::sqrt(param1), o->ellhalo6dvfac, o->fofbgtype, o->halo_min_size, pf6.p, true);
-            ctx->stats.fof6d_ms += t.stop();
-            {
-                StageTimer t2(ctx);
-                writeback_phase(ctx, view, P, pf.p);
-                ctx->stats.d2h_ms += t2.stop();
-            }
-            pf = std::move(pf6);
-            ng = ng6;
-        }
-        if (unbind && ng > 0) {
-            int changed = 0;
-            long long nmarg = 0;
-            unbind_device(ctx, P, pf.p, ng, o->unbind, changed, nmarg);
-            ctx->stats.n_marginal = nmarg;
-        }
+        DBuf<long long> pf;
+        long long ng = 0;
+        run_search(ctx, P, o, &view, pf, ng);
         {
             StageTimer t(ctx);
             download_i64(ctx, pf.p, pfof_out, P.n);
@@ -305,6 +364,93 @@ int vrgpu_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, const vrgpu_search_op
         *ngroups_out = ng;
         ctx->stats.n_groups_final = ng;
     });
+}
+
+int vrgpu_particles_upload(vrgpu_ctx *ctx, vrgpu_view view)
+{
+    return guarded(ctx, [&] {
+        CallTimer ct(ctx);
+        delete ctx->resident;
+        ctx->resident = nullptr;
+        std::unique_ptr<ResidentState> R(new ResidentState);
+        StageTimer t(ctx);
+        upload_view(ctx, view, view.off_vel != VRGPU_NOFIELD, view.off_mass != VRGPU_NOFIELD, view.off_pid != VRGPU_NOFIELD, R->pristine);
+        ctx->stats.h2d_ms += t.stop();
+        ctx->resident = R.release();
+    });
+}
+
+int vrgpu_particles_release(vrgpu_ctx *ctx)
+{
+    return guarded(ctx, [&] {
+        delete ctx->resident;
+        ctx->resident = nullptr;
+        ctx->pool.release_cached();
+    });
+}
+
+int vrgpu_search_full_set_resident(vrgpu_ctx *ctx, const vrgpu_search_opts *o, long long *ngroups_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(o && ngroups_out, VRGPU_EINVAL, "null pointer");
+        VR_REQUIRE(ctx->resident != nullptr, VRGPU_EINVAL, "no resident particles: call vrgpu_particles_upload first");
+        check_search_opts(o);
+        CallTimer ct(ctx);
+        ResidentState &R = *ctx->resident;
+        const DeviceParticles &S = R.pristine;
+        const bool six = o->fofbgtype <= 4;
+        const bool unbind = o->bound_halos >= 1;
+        VR_REQUIRE(!(six || unbind) || S.has_vel, VRGPU_EINVAL, "resident particles were uploaded without velocities");
+        // working copy: the path rewrites positions (AdjustStructureForPeriod) and phase-space coordinates (6DFOF)
+        DeviceParticles P;
+        P.n = S.n;
+        {
+            KScope k(ctx, "copy_pristine");
+            P.pos.alloc(ctx, 3 * S.n + 1);
+            VR_CUDA(cudaMemcpyAsync(P.pos.p, S.pos.p, 3 * S.n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+            if (six && S.has_vel) {
+                P.vel.alloc(ctx, 3 * S.n + 1);
+                VR_CUDA(cudaMemcpyAsync(P.vel.p, S.vel.p, 3 * S.n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+                P.has_vel = true;
+            }
+        }
+        // columns the path only reads are borrowed from the pristine copy
+        BorrowGuard bg(P, S, !(six && S.has_vel) && (six || unbind));
+        run_search(ctx, P, o, nullptr, R.pfof, R.ngroups);
+        *ngroups_out = R.ngroups;
+        ctx->stats.n_groups_final = R.ngroups;
+    });
+}
+
+int vrgpu_resident_pfof(vrgpu_ctx *ctx, long long *pfof_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(pfof_out, VRGPU_EINVAL, "null pointer");
+        VR_REQUIRE(ctx->resident && ctx->resident->pfof.p, VRGPU_EINVAL, "no resident result");
+        download_i64(ctx, ctx->resident->pfof.p, pfof_out, ctx->resident->pristine.n);
+    });
+}
+
+void *vrgpu_stream(vrgpu_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+const char *vrgpu_kernel_times(vrgpu_ctx *ctx)
+{
+    if (!ctx) return "";
+    resolve_ktimes(ctx);
+    ctx->ktimes_text.clear();
+    char line[256];
+    for (auto &kv : ctx->ktimes) {
+        snprintf(line, sizeof line, "%s %.6f %lld\n", kv.first.c_str(), kv.second.ms, kv.second.count);
+        ctx->ktimes_text += line;
+    }
+    return ctx->ktimes_text.c_str();
+}
+
+void vrgpu_kernel_times_reset(vrgpu_ctx *ctx)
+{
+    if (!ctx) return;
+    resolve_ktimes(ctx);
+    ctx->ktimes.clear();
 }
 
 } // extern "C"

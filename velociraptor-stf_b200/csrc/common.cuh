@@ -99,6 +99,13 @@ class Pool {
 
 } // namespace vrgpu
 
+namespace vrgpu {
+struct ResidentState; // api.cu: pristine device copy of the caller's particles + last result
+struct MultiGpu;      // multigpu.cu: NCCL communicator + slab decomposition state
+struct KTimeRec { double ms = 0; long long count = 0; };
+struct KPending { const char *name; cudaEvent_t a, b; };
+} // namespace vrgpu
+
 struct vrgpu_ctx {
     int device = 0;
     int sm_count = 148;
@@ -106,10 +113,17 @@ struct vrgpu_ctx {
     std::string err;
     vrgpu::Pool pool;
     vrgpu_stats stats{};
-    cudaEvent_t ev[16]{};
+    // deferred per-kernel timers (CUDA events on `stream`, resolved when the call ends)
+    std::vector<vrgpu::KPending> kpending;
+    std::vector<cudaEvent_t> evpool;
+    std::map<std::string, vrgpu::KTimeRec> ktimes;
+    std::string ktimes_text;
+    bool ktiming = true;
     // pinned bounce buffers for pageable host memory
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
+    vrgpu::ResidentState *resident = nullptr;
+    vrgpu::MultiGpu *mg = nullptr;
 };
 
 namespace vrgpu {
@@ -156,6 +170,48 @@ inline unsigned grid_for(size_t n, int threads) { return (unsigned)((n + threads
         (ctx)->stats.kernel_launches++;                                                  \
         VR_CUDA(cudaGetLastError());                                                     \
     } while (0)
+
+// Deferred timer: brackets a kernel (or a short kernel sequence) with two events on the context stream without
+// synchronising; resolve_ktimes() adds the elapsed times to ctx->ktimes[name] once the call has drained.
+struct KScope {
+    vrgpu_ctx *ctx;
+    const char *name;
+    cudaEvent_t a = nullptr;
+    static cudaEvent_t get(vrgpu_ctx *c)
+    {
+        if (!c->evpool.empty()) { cudaEvent_t e = c->evpool.back(); c->evpool.pop_back(); return e; }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+    KScope(vrgpu_ctx *c, const char *n) : ctx(c), name(n)
+    {
+        if (!c->ktiming) return;
+        a = get(c);
+        cudaEventRecord(a, c->stream);
+    }
+    ~KScope()
+    {
+        if (!a) return;
+        cudaEvent_t b = get(ctx);
+        cudaEventRecord(b, ctx->stream);
+        ctx->kpending.push_back({name, a, b});
+    }
+};
+inline void resolve_ktimes(vrgpu_ctx *ctx)
+{
+    for (auto &k : ctx->kpending) {
+        float ms = 0;
+        if (cudaEventSynchronize(k.b) == cudaSuccess && cudaEventElapsedTime(&ms, k.a, k.b) == cudaSuccess) {
+            auto &r = ctx->ktimes[k.name];
+            r.ms += ms;
+            r.count++;
+        } else cudaGetLastError();
+        ctx->evpool.push_back(k.a);
+        ctx->evpool.push_back(k.b);
+    }
+    ctx->kpending.clear();
+}
 
 struct StageTimer {
     vrgpu_ctx *ctx;

@@ -555,14 +555,14 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
     VR_CUDA(cudaMemsetAsync(nbad.p, 0, sizeof(unsigned int), ctx->stream));
     {
         StageTimer t(ctx);
-        VR_LAUNCH(ctx, k_cell_keys, grid_for(n, T), T, 0, P.pos.p, n, g, keys.p, S.order.p, nbad.p);
-        radix_sort_pairs(ctx, keys.p, S.order.p, keys_tmp.p, order_tmp.p, n, nbits);
+        { KScope k(ctx, "fof3d.cell_keys"); VR_LAUNCH(ctx, k_cell_keys, grid_for(n, T), T, 0, P.pos.p, n, g, keys.p, S.order.p, nbad.p); }
+        { KScope k(ctx, "fof3d.radix_sort"); radix_sort_pairs(ctx, keys.p, S.order.p, keys_tmp.p, order_tmp.p, n, nbits); }
         S.sx.alloc(ctx, n); S.sy.alloc(ctx, n); S.sz.alloc(ctx, n);
-        VR_LAUNCH(ctx, k_gather_pos, grid_for(n, T), T, 0, P.pos.p, S.order.p, n, S.sx.p, S.sy.p, S.sz.p);
+        { KScope k(ctx, "fof3d.gather_pos"); VR_LAUNCH(ctx, k_gather_pos, grid_for(n, T), T, 0, P.pos.p, S.order.p, n, S.sx.p, S.sy.p, S.sz.p); }
         // cells
         DBuf<uint32_t> flags(ctx, n), excl(ctx, n), total(ctx, 1);
-        VR_LAUNCH(ctx, k_flag_heads, grid_for(n, T), T, 0, keys.p, n, flags.p);
-        exclusive_scan_u32(ctx, flags.p, excl.p, n, total.p);
+        { KScope k(ctx, "fof3d.cell_table"); VR_LAUNCH(ctx, k_flag_heads, grid_for(n, T), T, 0, keys.p, n, flags.p);
+        exclusive_scan_u32(ctx, flags.p, excl.p, n, total.p); }
         uint32_t hn = 0;
         unsigned int hbad = 0;
         VR_CUDA(cudaMemcpyAsync(&hn, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
@@ -573,7 +573,7 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         S.cell_of.alloc(ctx, n);
         S.cell_start.alloc(ctx, (size_t)hn + 1);
         S.cell_key.alloc(ctx, hn);
-        VR_LAUNCH(ctx, k_fill_cells, grid_for(n, T), T, 0, keys.p, flags.p, excl.p, n, S.cell_of.p, S.cell_start.p, S.cell_key.p, hn);
+        { KScope k(ctx, "fof3d.cell_table"); VR_LAUNCH(ctx, k_fill_cells, grid_for(n, T), T, 0, keys.p, flags.p, excl.p, n, S.cell_of.p, S.cell_start.p, S.cell_key.p, hn); }
         ctx->stats.sort_ms += t.stop();
     }
     keys.reset(); keys_tmp.reset(); order_tmp.reset();
@@ -588,8 +588,8 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         while (h < 2 * (size_t)ncells) h <<= 1;
         DBuf<uint64_t> hkeys(ctx, h);
         DBuf<uint32_t> hvals(ctx, h);
-        VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
-        VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), parent.p);
+        { KScope k(ctx, "fof3d.hash_build"); VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
+        VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), parent.p); }
         LinkParams L{};
         L.sx = S.sx.p; L.sy = S.sy.p; L.sz = S.sz.p;
         L.cell_start = S.cell_start.p; L.cell_key = S.cell_key.p; L.ncells = ncells;
@@ -603,10 +603,10 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         unsigned warps_needed = ncells;
         unsigned blocks = std::min<unsigned>((warps_needed + 7) / 8, (unsigned)ctx->sm_count * 32u);
         blocks = std::max(blocks, 1u);
-        VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 0, 13);
-        VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 13, 62);
+        { KScope k(ctx, "fof3d.link_cells"); VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 0, 13);
+        VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 13, 62); }
         S.root.alloc(ctx, ncells);
-        VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p);
+        { KScope k(ctx, "fof3d.flatten"); VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); }
         ctx->stats.link_ms += t.stop();
     }
 
@@ -619,10 +619,12 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         VR_CUDA(cudaMemsetAsync(gminidx.p, 0xff, sizeof(uint32_t) * ncells, ctx->stream));
         VR_CUDA(cudaMemsetAsync(gminpid.p, 0xff, sizeof(unsigned long long) * ncells, ctx->stream));
         VR_CUDA(cudaMemsetAsync(ngrouped.p, 0, sizeof(unsigned long long), ctx->stream));
-        VR_LAUNCH(ctx, k_group_stats, grid_for(ncells, T), T, 0, S.root.p, S.cell_start.p, ncells, S.order.p,
-                  P.has_pid ? P.pid.p : (const long long *)nullptr, gsize.p, gminpid.p, gminidx.p);
+        { KScope k(ctx, "fof3d.group_stats"); VR_LAUNCH(ctx, k_group_stats, grid_for(ncells, T), T, 0, S.root.p, S.cell_start.p, ncells, S.order.p,
+                  P.has_pid ? P.pid.p : (const long long *)nullptr, gsize.p, gminpid.p, gminidx.p); }
         uint32_t ms = minsize < 1 ? 1u : (minsize > 0xffffffffLL ? 0xffffffffu : (uint32_t)minsize);
-        uint32_t ng = order_groups(ctx, S.root.p, gsize.p, gminpid.p, ncells, ms, gid_of_cell.p);
+        uint32_t ng;
+        { KScope k(ctx, "fof3d.order_groups"); ng = order_groups(ctx, S.root.p, gsize.p, gminpid.p, ncells, ms, gid_of_cell.p); }
+        KScope kw(ctx, "fof3d.write_pfof");
         VR_LAUNCH(ctx, k_write_pfof, grid_for(n, T), T, 0, S.order.p, S.cell_of.p, S.root.p, gid_of_cell.p, n, S.pfof.p, ngrouped.p);
         unsigned long long hg = 0;
         VR_CUDA(cudaMemcpyAsync(&hg, ngrouped.p, sizeof(hg), cudaMemcpyDeviceToHost, ctx->stream));

@@ -21,4 +21,7 @@ void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngro
 void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
                    int &changed, long long &n_marginal);
 
+// multi-GPU state teardown (multigpu.cu)
+void mg_destroy(vrgpu_ctx *ctx);
+
 } // namespace vrgpu

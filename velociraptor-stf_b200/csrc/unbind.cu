@@ -479,8 +479,8 @@ static void compute_potentials(vrgpu_ctx *ctx, const GroupSet &gs, double G, dou
                                double *phi)
 {
     StageTimer t(ctx);
-    ctx->stats.n_pairs_potential += (long long)potential_direct(ctx, gs, G, eps, pp_threshold, phi);
-    if (pp_threshold >= 0) potential_tree(ctx, gs, G, eps, theta, bucket, pp_threshold, phi);
+    { KScope k(ctx, "potential.direct"); ctx->stats.n_pairs_potential += (long long)potential_direct(ctx, gs, G, eps, pp_threshold, phi); }
+    if (pp_threshold >= 0) { KScope k(ctx, "potential.tree"); potential_tree(ctx, gs, G, eps, theta, bucket, pp_threshold, phi); }
     ctx->stats.potential_ms += t.stop();
 }
 
@@ -497,9 +497,9 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
     VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "unbinding needs velocities");
     const int T = 256;
     GroupSet gs;
-    build_groupset(ctx, pfof_dev, P.n, ngroups, gs);
+    { KScope k(ctx, "unbind.regroup"); build_groupset(ctx, pfof_dev, P.n, ngroups, gs); }
     if (gs.ntot == 0) return;
-    gather_groupset(ctx, P, gs, true, true);
+    { KScope k(ctx, "unbind.gather"); gather_groupset(ctx, P, gs, true, true); }
     const uint32_t ntot = (uint32_t)gs.ntot, G = (uint32_t)ngroups;
     DBuf<double> phi(ctx, ntot);
     compute_potentials(ctx, gs, o.G, o.eps, o.theta, o.bucket, o.pp_threshold, phi.p);
@@ -531,11 +531,12 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
     Pm.marginal_tol = o.marginal_tol; Pm.unbindtype = o.unbindtype; Pm.min_size = o.min_size; Pm.large_threshold = o.large_threshold;
     const unsigned warp_grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 16u));
 
-    VR_LAUNCH(ctx, k_init_slots, grid_for(ntot, T), T, 0, A, ntot);
-    VR_LAUNCH(ctx, k_group_cm, warp_grid, T, 0, A, G);
+    { KScope k(ctx, "unbind.cm_frame"); VR_LAUNCH(ctx, k_init_slots, grid_for(ntot, T), T, 0, A, ntot);
+    VR_LAUNCH(ctx, k_group_cm, warp_grid, T, 0, A, G); }
 
     // ---- phase A ----
     {
+        KScope ka(ctx, "unbind.large_groups");
         DBuf<uint32_t> lflag(ctx, ntot), lexcl(ctx, ntot), ltotal(ctx, 1);
         VR_LAUNCH(ctx, k_large_energy, grid_for(ntot, T), T, 0, A, Pm, ntot, lflag.p);
         exclusive_scan_u32(ctx, lflag.p, lexcl.p, ntot, ltotal.p);
@@ -560,7 +561,7 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
         }
     }
     // ---- phase B ----
-    VR_LAUNCH(ctx, k_unbind_small, G, UB_T, 0, A, Pm, G);
+    { KScope k(ctx, "unbind.small_groups"); VR_LAUNCH(ctx, k_unbind_small, G, UB_T, 0, A, Pm, G); }
 
     // ---- results ----
     DBuf<uint32_t> newsize(ctx, G1), iota(ctx, G1), gid_of(ctx, G1);

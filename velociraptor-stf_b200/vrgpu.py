@@ -121,12 +121,24 @@ def load_library(path: str = LIB_PATH):
                                   C.c_longlong, P_d]
     L.vrgpu_unbind.argtypes = [C.c_void_p, View, P_ll, P_ll, C.POINTER(UnbindOpts), C.POINTER(C.c_int), P_ll]
     L.vrgpu_search_full_set.argtypes = [C.c_void_p, View, C.POINTER(SearchOpts), P_ll, P_ll]
+    L.vrgpu_particles_upload.argtypes = [C.c_void_p, View]
+    L.vrgpu_particles_release.argtypes = [C.c_void_p]
+    L.vrgpu_search_full_set_resident.argtypes = [C.c_void_p, C.POINTER(SearchOpts), P_ll]
+    L.vrgpu_resident_pfof.argtypes = [C.c_void_p, P_ll]
+    L.vrgpu_stream.argtypes = [C.c_void_p]
+    L.vrgpu_stream.restype = C.c_void_p
+    L.vrgpu_kernel_times.argtypes = [C.c_void_p]
+    L.vrgpu_kernel_times.restype = C.c_char_p
+    L.vrgpu_kernel_times_reset.argtypes = [C.c_void_p]
+    L.vrgpu_kernel_times_reset.restype = None
     _lib = L
     return L
 
 
 EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_version", "vrgpu_get_stats", "vrgpu_fof3d",
-                    "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set"]
+                    "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
+                    "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
+                    "vrgpu_resident_pfof", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset"]
 
 
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
@@ -254,6 +266,37 @@ class Context:
         self._check(self.lib.vrgpu_search_full_set(self.h, view_of(parts), C.byref(opts),
                                                    pfof.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
         return pfof, int(ng.value)
+
+    # ---- device-resident variant (InvokeVelociraptor-style: particles handed over once) ----
+    def particles_upload(self, parts):
+        self._check(self.lib.vrgpu_particles_upload(self.h, view_of(parts)))
+
+    def particles_release(self):
+        self._check(self.lib.vrgpu_particles_release(self.h))
+
+    def search_full_set_resident(self, opts: SearchOpts) -> int:
+        ng = C.c_longlong(0)
+        self._check(self.lib.vrgpu_search_full_set_resident(self.h, C.byref(opts), C.byref(ng)))
+        return int(ng.value)
+
+    def resident_pfof(self, n: int) -> np.ndarray:
+        pfof = np.zeros(n, dtype=np.int64)
+        self._check(self.lib.vrgpu_resident_pfof(self.h, pfof.ctypes.data_as(C.POINTER(C.c_longlong))))
+        return pfof
+
+    # ---- measurement hooks ----
+    def stream(self) -> int:
+        return int(self.lib.vrgpu_stream(self.h) or 0)
+
+    def kernel_times(self) -> dict:
+        out = {}
+        for line in self.lib.vrgpu_kernel_times(self.h).decode().splitlines():
+            name, ms, cnt = line.split()
+            out[name] = {"ms": float(ms), "count": int(cnt)}
+        return out
+
+    def kernel_times_reset(self):
+        self.lib.vrgpu_kernel_times_reset(self.h)
 
 
 def search_opts(period, param1, halo_min_size=20, fofbgtype=5, ellhalo6dxfac=1.0, ellhalo6dvfac=1.25, bound_halos=0,
