@@ -18,13 +18,12 @@
 // reference, so both orientations are evaluated.
 #include "fof.cuh"
 #include "groups.cuh"
+#include "ufhash.cuh"
 
 #include <algorithm>
 #include <cmath>
 
 namespace vrgpu {
-
-constexpr uint64_t HASH_EMPTY = ~0ull;
 
 struct LinkParams {
     const double *sx, *sy, *sz;
@@ -44,16 +43,6 @@ struct LinkParams {
 };
 
 __constant__ signed char c_offsets[62][3];
-
-__host__ __device__ __forceinline__ uint64_t hash64(uint64_t k)
-{
-    k ^= k >> 33;
-    k *= 0xff51afd7ed558ccdULL;
-    k ^= k >> 33;
-    k *= 0xc4ceb9fe1a85ec53ULL;
-    k ^= k >> 33;
-    return k;
-}
 
 // ---------------------------------------------------------------------------------------------------
 // binning
@@ -141,67 +130,6 @@ __global__ void k_fill_cells(const uint64_t *__restrict__ keys, const uint32_t *
         cell_key[c] = keys[k];
     }
     if (k == n - 1) cell_start[ncells] = (uint32_t)n;
-}
-
-__global__ void k_hash_fill(uint64_t *__restrict__ hkeys, size_t h)
-{
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < h) hkeys[i] = HASH_EMPTY;
-}
-
-__global__ void k_hash_insert(const uint64_t *__restrict__ cell_key, uint32_t ncells, uint64_t *__restrict__ hkeys, uint32_t *__restrict__ hvals,
-                              uint32_t hmask, uint32_t *__restrict__ parent)
-{
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncells) return;
-    parent[c] = c;
-    uint64_t key = cell_key[c];
-    uint32_t slot = (uint32_t)hash64(key) & hmask;
-    for (;;) {
-        unsigned long long old = atomicCAS((unsigned long long *)&hkeys[slot], (unsigned long long)HASH_EMPTY, (unsigned long long)key);
-        if (old == HASH_EMPTY) { hvals[slot] = c; return; }
-        slot = (slot + 1) & hmask;
-    }
-}
-
-__device__ __forceinline__ int hash_lookup(const uint64_t *__restrict__ hkeys, const uint32_t *__restrict__ hvals, uint32_t hmask, uint64_t key)
-{
-    uint32_t slot = (uint32_t)hash64(key) & hmask;
-    for (;;) {
-        uint64_t k = __ldg(&hkeys[slot]);
-        if (k == key) return (int)__ldg(&hvals[slot]);
-        if (k == HASH_EMPTY) return -1;
-        slot = (slot + 1) & hmask;
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------
-// lock-free union-find over cells (roots always have the smallest index of their set)
-// ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t uf_find(uint32_t *parent, uint32_t x)
-{
-    volatile uint32_t *vp = parent;
-    uint32_t p = vp[x];
-    while (p != x) {
-        uint32_t gp = vp[p];
-        if (gp != p) parent[x] = gp; // path halving; a stale value is still an ancestor
-        x = p;
-        p = gp;
-    }
-    return x;
-}
-
-__device__ __forceinline__ void uf_union(uint32_t *parent, uint32_t a, uint32_t b)
-{
-    for (;;) {
-        a = uf_find(parent, a);
-        b = uf_find(parent, b);
-        if (a == b) return;
-        if (a < b) { uint32_t t = a; a = b; b = t; }
-        // a > b: hook the larger root under the smaller one
-        uint32_t old = atomicCAS(&parent[a], a, b);
-        if (old == a) return;
-    }
 }
 
 __device__ __forceinline__ bool pair_links(double ax, double ay, double az, double bx, double by, double bz, double b2)

@@ -1,0 +1,653 @@
+// velociraptor-stf_b200/csrc/fof6d.cu -- 6D phase-space FOF inside every 3D group.
+//
+// Replaces the 6DFOF block of SearchFullSet (src/search.cxx:400-698): regroup by 3D group (qsort by PID :434),
+// per-group velocity dispersion (:472-499, or the single-scale variant :443-470 with its quirk Q1), ScalePhase
+// (:565-568), a 6-D KDTree + KDTree::FOF(1.0) per group (:570-571), un-scaling (:573-575), id offsets (:659-669) and
+// ReorderGroupIDs (:681-689).
+//
+// Device design (not the reference's): all 3D groups are processed in ONE set of launches.
+//   1. group-major SoA (groups.cu), members in ascending particle index like the reference's stable qsort;
+//   2. per-group dispersion: one warp per group; the reference's summation ORDER is kept (a sequential chain in member
+//      order, products rounded before the add) so the scale factors -- and with them every scaled coordinate -- are
+//      bit-identical to the reference;
+//   3. coordinates scaled in place (one rounding per coordinate), un-scaled copies written back (Q3);
+//   4. cells of edge 1 in SCALED position space, key = (group, cz, cy, cx); radix sort + hash table;
+//   5. lock-free union-find over PARTICLES: a cheap seeding pass (each particle against the head of its own cell)
+//      builds the big components, a per-cell "uniform root" flag then lets the exhaustive pass skip whole cell pairs
+//      that are already one component; the exhaustive pass (one warp per 32 particles, neighbour tiles staged in
+//      shared memory) tests every remaining pair whose roots differ with the reference predicate
+//         d2 = (dx^2+dy^2+dz^2) + (dvx^2+dvy^2+dvz^2) < 1   (KDLeafNode.cxx:556-558; fp64, left to right, no FMA);
+//   6. component sizes / min pid -> ids by (size desc, min pid asc) over ALL groups (== per-group ids + offsets +
+//      ReorderGroupIDs, canonicalised).
+#include "groups.cuh"
+#include "stages.cuh"
+#include "ufhash.cuh"
+
+#include <algorithm>
+#include <cmath>
+
+namespace vrgpu {
+
+constexpr uint32_t NONE32 = 0xffffffffu;
+constexpr int CBITS = 14;               // bits per scaled-cell coordinate in the key
+constexpr uint64_t CMASK = (1ull << CBITS) - 1;
+
+// ---------------------------------------------------------------------------------------------------
+// per-group velocity scale
+// ---------------------------------------------------------------------------------------------------
+// FOF6DADAPTIVE (search.cxx:480-493): vmean = sum(m v)/sum(m); vscale2 = sum_k pow(v_k - vmean_k, 2) m / sum(m) * vfac^2.
+// One warp per group; all lanes carry the same sequential sums (the chain is the reference's order).
+__global__ void __launch_bounds__(256) k_group_dispersion(const double *__restrict__ vx, const double *__restrict__ vy,
+                                                          const double *__restrict__ vz, const double *__restrict__ m,
+                                                          const uint32_t *__restrict__ off, uint32_t ngroups, double vfac,
+                                                          double *__restrict__ vs2)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    // big groups first: group ids are size-descending, so a plain grid-stride already starts the long chains early
+    for (uint32_t g = 1 + wg; g <= ngroups; g += nw) {
+        const uint32_t s0 = off[g], s1 = off[g + 1];
+        double sx = 0, sy = 0, sz = 0, sm = 0;
+        for (uint32_t base = s0; base < s1; base += 32) {
+            const uint32_t s = base + lane;
+            double px = 0, py = 0, pz = 0, mm = 0;
+            if (s < s1) {
+                mm = m[s];
+                px = __dmul_rn(vx[s], mm); py = __dmul_rn(vy[s], mm); pz = __dmul_rn(vz[s], mm);
+            }
+            const int cnt = (int)min(32u, s1 - base);
+            for (int t = 0; t < cnt; t++) {
+                sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
+                sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
+                sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
+                sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
+            }
+        }
+        const double mx = __ddiv_rn(sx, sm), my = __ddiv_rn(sy, sm), mz = __ddiv_rn(sz, sm);
+        double acc = 0;
+        for (uint32_t base = s0; base < s1; base += 32) {
+            const uint32_t s = base + lane;
+            double tx = 0, ty = 0, tz = 0;
+            if (s < s1) {
+                const double mm = m[s];
+                double d = __dsub_rn(vx[s], mx); tx = __dmul_rn(__dmul_rn(d, d), mm);
+                d = __dsub_rn(vy[s], my); ty = __dmul_rn(__dmul_rn(d, d), mm);
+                d = __dsub_rn(vz[s], mz); tz = __dmul_rn(__dmul_rn(d, d), mm);
+            }
+            const int cnt = (int)min(32u, s1 - base);
+            for (int t = 0; t < cnt; t++) {
+                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
+                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
+                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
+            }
+        }
+        if (lane == 0) vs2[g] = __dmul_rn(__dmul_rn(__ddiv_rn(acc, sm), vfac), vfac);
+    }
+}
+
+// FOF6D single scale (search.cxx:443-470) INCLUDING quirk Q1: the mass normalisation is ONE particle's mass (the
+// particle that follows the largest group in the group-sorted array).  One warp; result broadcast to every chunk.
+__global__ void k_single_dispersion(const double *__restrict__ vx, const double *__restrict__ vy, const double *__restrict__ vz,
+                                    const double *__restrict__ m, uint32_t n1, double mnorm, double vfac, uint32_t nchunks,
+                                    double *__restrict__ vs2)
+{
+    const unsigned lane = threadIdx.x & 31;
+    double sx = 0, sy = 0, sz = 0;
+    for (uint32_t base = 0; base < n1; base += 32) {
+        const uint32_t s = base + lane;
+        double px = 0, py = 0, pz = 0;
+        if (s < n1) { const double mm = m[s]; px = __dmul_rn(vx[s], mm); py = __dmul_rn(vy[s], mm); pz = __dmul_rn(vz[s], mm); }
+        const int cnt = (int)min(32u, n1 - base);
+        for (int t = 0; t < cnt; t++) {
+            sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
+            sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
+            sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
+        }
+    }
+    const double mx = __ddiv_rn(sx, mnorm), my = __ddiv_rn(sy, mnorm), mz = __ddiv_rn(sz, mnorm);
+    double acc = 0;
+    for (uint32_t base = 0; base < n1; base += 32) {
+        const uint32_t s = base + lane;
+        double tx = 0, ty = 0, tz = 0;
+        if (s < n1) {
+            const double mm = m[s];
+            double d = __dsub_rn(vx[s], mx); tx = __dmul_rn(__dmul_rn(d, d), mm);
+            d = __dsub_rn(vy[s], my); ty = __dmul_rn(__dmul_rn(d, d), mm);
+            d = __dsub_rn(vz[s], mz); tz = __dmul_rn(__dmul_rn(d, d), mm);
+        }
+        const int cnt = (int)min(32u, n1 - base);
+        for (int t = 0; t < cnt; t++) {
+            acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
+            acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
+            acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
+        }
+    }
+    if (mnorm > 0) acc = __ddiv_rn(acc, mnorm);
+    acc = __dmul_rn(acc, __dmul_rn(vfac, vfac)); // search.cxx:464
+    for (uint32_t g = 1 + lane; g <= nchunks; g += 32) vs2[g] = acc;
+}
+
+// ScalePhase (search.cxx:565-568) on the group-major columns; optionally the un-scaled values (search.cxx:573-575,
+// SURVEY Q3) go back to the original-order device arrays.
+__global__ void k_scale_phase(double *__restrict__ x, double *__restrict__ y, double *__restrict__ z, double *__restrict__ vx,
+                              double *__restrict__ vy, double *__restrict__ vz, const uint32_t *__restrict__ gid,
+                              const uint32_t *__restrict__ idx, const double *__restrict__ vs2, uint32_t ntot, double xs,
+                              double xsinv, double *__restrict__ pos_out, double *__restrict__ vel_out)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    const double vsc = __ddiv_rn(1.0, sqrt(vs2[gid[s]]));
+    const double vinv = __ddiv_rn(1.0, vsc);
+    const double a = __dmul_rn(x[s], xs), b = __dmul_rn(y[s], xs), c = __dmul_rn(z[s], xs);
+    const double d = __dmul_rn(vx[s], vsc), e = __dmul_rn(vy[s], vsc), f = __dmul_rn(vz[s], vsc);
+    x[s] = a; y[s] = b; z[s] = c; vx[s] = d; vy[s] = e; vz[s] = f;
+    if (pos_out) {
+        const size_t i = idx[s];
+        pos_out[3 * i] = __dmul_rn(a, xsinv); pos_out[3 * i + 1] = __dmul_rn(b, xsinv); pos_out[3 * i + 2] = __dmul_rn(c, xsinv);
+        vel_out[3 * i] = __dmul_rn(d, vinv); vel_out[3 * i + 1] = __dmul_rn(e, vinv); vel_out[3 * i + 2] = __dmul_rn(f, vinv);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// cells in scaled position space
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long dbl_ord(double d)
+{
+    unsigned long long u = (unsigned long long)__double_as_longlong(d);
+    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+static double ord_dbl_host(unsigned long long u)
+{
+    u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
+    double d;
+    std::memcpy(&d, &u, 8);
+    return d;
+}
+
+__global__ void k_minmax3(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z, uint32_t n,
+                          unsigned long long *__restrict__ out /* min[3], max[3] as ordered ints */)
+{
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        double v[3] = {x[i], y[i], z[i]};
+        for (int k = 0; k < 3; k++) { mn[k] = fmin(mn[k], v[k]); mx[k] = fmax(mx[k], v[k]); }
+    }
+    for (int k = 0; k < 3; k++) {
+        for (int o = 16; o; o >>= 1) {
+            mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+        if ((threadIdx.x & 31) == 0) { atomicMin(&out[k], dbl_ord(mn[k])); atomicMax(&out[3 + k], dbl_ord(mx[k])); }
+    }
+}
+
+struct CellOrigin { long long c0[3]; };
+
+__global__ void k_keys6(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                        const uint32_t *__restrict__ gid, uint32_t ntot, CellOrigin o, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    const uint64_t cx = (uint64_t)((long long)floor(x[s]) - o.c0[0]);
+    const uint64_t cy = (uint64_t)((long long)floor(y[s]) - o.c0[1]);
+    const uint64_t cz = (uint64_t)((long long)floor(z[s]) - o.c0[2]);
+    keys[s] = ((uint64_t)gid[s] << (3 * CBITS)) | (cz << (2 * CBITS)) | (cy << CBITS) | cx;
+    vals[s] = s;
+}
+
+__global__ void k_gather6(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                          const double *__restrict__ vx, const double *__restrict__ vy, const double *__restrict__ vz,
+                          const uint32_t *__restrict__ ord, uint32_t ntot, double *__restrict__ q /* 6 columns of ntot */)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ntot) return;
+    const uint32_t s = ord[p];
+    q[p] = x[s]; q[(size_t)ntot + p] = y[s]; q[2 * (size_t)ntot + p] = z[s];
+    q[3 * (size_t)ntot + p] = vx[s]; q[4 * (size_t)ntot + p] = vy[s]; q[5 * (size_t)ntot + p] = vz[s];
+}
+
+__global__ void k_flag_heads6(const uint64_t *__restrict__ keys, uint32_t n, uint32_t *__restrict__ flags)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    flags[k] = (k == 0 || keys[k] != keys[k - 1]) ? 1u : 0u;
+}
+
+__global__ void k_fill_cells6(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ flags, const uint32_t *__restrict__ excl,
+                              uint32_t n, uint32_t *__restrict__ cell_of, uint32_t *__restrict__ cell_start, uint64_t *__restrict__ cell_key,
+                              uint32_t ncells)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t f = flags[k];
+    const uint32_t c = excl[k] - (f ? 0u : 1u);
+    cell_of[k] = c;
+    if (f) { cell_start[c] = k; cell_key[c] = keys[k]; }
+    if (k == n - 1) cell_start[ncells] = n;
+}
+
+__global__ void k_chunk_counts(const uint32_t *__restrict__ cell_start, uint32_t ncells, uint32_t *__restrict__ nchunk)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < ncells) nchunk[c] = (cell_start[c + 1] - cell_start[c] + 31) >> 5;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// linking
+// ---------------------------------------------------------------------------------------------------
+struct Link6 {
+    const double *q;            // 6 columns of ntot (sorted order)
+    uint32_t ntot;
+    const uint32_t *cell_of, *cell_start;
+    const uint64_t *cell_key;
+    uint32_t ncells;
+    const uint64_t *hkeys;
+    const uint32_t *hvals;
+    uint32_t hmask;
+    uint32_t *parent;
+    const uint32_t *uni;        // per cell: common root of all its particles, or NONE32
+    const uint32_t *chunk_start; // exclusive scan of per-cell 32-particle chunk counts
+    uint32_t nchunks;
+};
+
+__device__ __forceinline__ bool links6(double ax, double ay, double az, double avx, double avy, double avz, double bx, double by,
+                                       double bz, double bvx, double bvy, double bvz)
+{
+    double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by), dz = __dsub_rn(az, bz);
+    double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+    dx = __dsub_rn(avx, bvx); dy = __dsub_rn(avy, bvy); dz = __dsub_rn(avz, bvz);
+    double v2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+    return __dadd_rn(d2, v2) < 1.0;
+}
+
+// seeding: every particle against (up to) the first 32 particles of its own cell that precede it; stop at the first link
+__global__ void __launch_bounds__(256) k_seed6(Link6 L)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L.ntot) return;
+    const uint32_t a0 = L.cell_start[L.cell_of[i]];
+    const uint32_t jend = min(i, a0 + 32u);
+    if (jend <= a0) return;
+    const size_t n = L.ntot;
+    const double ax = L.q[i], ay = L.q[n + i], az = L.q[2 * n + i], avx = L.q[3 * n + i], avy = L.q[4 * n + i], avz = L.q[5 * n + i];
+    for (uint32_t j = a0; j < jend; j++) {
+        if (links6(ax, ay, az, avx, avy, avz, L.q[j], L.q[n + j], L.q[2 * n + j], L.q[3 * n + j], L.q[4 * n + j], L.q[5 * n + j])) {
+            uf_union(L.parent, i, j);
+            return;
+        }
+    }
+}
+
+// one warp per cell (grid stride): common root of the cell or NONE32.  parent[] must be flat.
+__global__ void __launch_bounds__(256) k_cell_uniform(const uint32_t *__restrict__ parent, const uint32_t *__restrict__ cell_start,
+                                                      uint32_t ncells, uint32_t *__restrict__ uni)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t c = wg; c < ncells; c += nw) {
+        const uint32_t a0 = cell_start[c], a1 = cell_start[c + 1];
+        const uint32_t r0 = parent[a0];
+        bool same = true;
+        for (uint32_t p = a0 + lane; p < a1 && same; p += 32) same = parent[p] == r0;
+        same = __all_sync(0xffffffffu, same);
+        if (lane == 0) uni[c] = same ? r0 : NONE32;
+    }
+}
+
+constexpr int L6_WARPS = 8;
+
+// exhaustive pass: one warp per 32-particle chunk of a cell; 13 forward neighbour cells + the cell itself.
+__global__ void __launch_bounds__(L6_WARPS * 32) k_link6(Link6 L)
+{
+    __shared__ double tq[L6_WARPS][6][32];
+    __shared__ uint32_t tr[L6_WARPS][32];
+    const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t nw = gridDim.x * L6_WARPS;
+    const size_t n = L.ntot;
+    for (uint32_t item = blockIdx.x * L6_WARPS + w; item < L.nchunks; item += nw) {
+        // cell of this chunk: largest c with chunk_start[c] <= item
+        uint32_t lo = 0, hi = L.ncells - 1;
+        while (lo < hi) {
+            uint32_t mid = (lo + hi + 1) >> 1;
+            if (L.chunk_start[mid] <= item) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t A = lo;
+        const uint32_t a0 = L.cell_start[A], a1 = L.cell_start[A + 1];
+        const uint32_t i = a0 + ((item - L.chunk_start[A]) << 5) + lane;
+        const bool valid = i < a1;
+        double ax = 0, ay = 0, az = 0, avx = 0, avy = 0, avz = 0;
+        uint32_t ri = NONE32;
+        if (valid) {
+            ax = L.q[i]; ay = L.q[n + i]; az = L.q[2 * n + i]; avx = L.q[3 * n + i]; avy = L.q[4 * n + i]; avz = L.q[5 * n + i];
+            ri = uf_find(L.parent, i);
+        }
+        const uint64_t key = L.cell_key[A];
+        const uint32_t uniA = L.uni[A];
+        // neighbour lookup: lane o < 14 owns half-space offset o (0 = the cell itself)
+        int nb = -1;
+        if (lane < 14) {
+            int dx = 0, dy = 0, dz = 0;
+            if (lane > 0) {
+                // forward half space: dz=1 (9), dz=0 & dy=1 (3), dz=0 & dy=0 & dx=1 (1)
+                int o = (int)lane - 1;
+                if (o < 9) { dz = 1; dy = o / 3 - 1; dx = o % 3 - 1; }
+                else if (o < 12) { dz = 0; dy = 1; dx = o - 9 - 1; }
+                else { dz = 0; dy = 0; dx = 1; }
+            }
+            const long long cx = (long long)(key & CMASK) + dx, cy = (long long)((key >> CBITS) & CMASK) + dy,
+                            cz = (long long)((key >> (2 * CBITS)) & CMASK) + dz;
+            if (lane == 0) nb = (int)A;
+            else if (cx >= 0 && cy >= 0 && cz >= 0 && cx <= (long long)CMASK && cy <= (long long)CMASK && cz <= (long long)CMASK) {
+                const uint64_t nkey = (key & ~((1ull << (3 * CBITS)) - 1)) | ((uint64_t)cz << (2 * CBITS)) | ((uint64_t)cy << CBITS) | (uint64_t)cx;
+                nb = hash_lookup(L.hkeys, L.hvals, L.hmask, nkey);
+            }
+        }
+        unsigned found = __ballot_sync(0xffffffffu, nb >= 0);
+        while (found) {
+            const int src = __ffs(found) - 1;
+            found &= found - 1;
+            const uint32_t B = (uint32_t)__shfl_sync(0xffffffffu, nb, src);
+            const uint32_t uniB = L.uni[B];
+            if (uniA != NONE32 && uniA == uniB) continue; // both cells already inside one component
+            const uint32_t b0 = L.cell_start[B], b1 = L.cell_start[B + 1];
+            const bool self = B == A;
+            for (uint32_t tb = b0; tb < b1; tb += 32) {
+                // lanes already in B's (uniform) component have nothing left to find in B
+                if (uniB != NONE32 && __all_sync(0xffffffffu, !valid || ri == uniB)) break;
+                if (self && tb + 31 <= a0 + ((item - L.chunk_start[A]) << 5)) continue; // tile entirely before this chunk (j > i only)
+                const uint32_t j = tb + lane;
+                __syncwarp();
+                if (j < b1) {
+                    tq[w][0][lane] = L.q[j]; tq[w][1][lane] = L.q[n + j]; tq[w][2][lane] = L.q[2 * n + j];
+                    tq[w][3][lane] = L.q[3 * n + j]; tq[w][4][lane] = L.q[4 * n + j]; tq[w][5][lane] = L.q[5 * n + j];
+                    tr[w][lane] = ((volatile uint32_t *)L.parent)[j]; // possibly stale ancestor: only costs a redundant test
+                }
+                __syncwarp();
+                const int cnt = (int)min(32u, b1 - tb);
+                if (valid) {
+                    for (int jj = 0; jj < cnt; jj++) {
+                        const uint32_t jx = tb + jj;
+                        if (self && jx <= i) continue;
+                        if (tr[w][jj] == ri) continue;
+                        if (links6(ax, ay, az, avx, avy, avz, tq[w][0][jj], tq[w][1][jj], tq[w][2][jj], tq[w][3][jj], tq[w][4][jj], tq[w][5][jj])) {
+                            uf_union(L.parent, i, jx);
+                            ri = uf_find(L.parent, i);
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// labels
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_comp_stats(const uint32_t *__restrict__ root, const uint32_t *__restrict__ ord, const uint32_t *__restrict__ idx,
+                             const long long *__restrict__ pid, uint32_t ntot, uint32_t *__restrict__ csize,
+                             unsigned long long *__restrict__ cminpid)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ntot) return;
+    const uint32_t r = root[p];
+    const uint32_t i = idx[ord[p]];
+    atomicAdd(&csize[r], 1u);
+    atomicMin(&cminpid[r], pid ? (unsigned long long)pid[i] : (unsigned long long)i);
+}
+
+__global__ void k_write_pfof6(const uint32_t *__restrict__ root, const uint32_t *__restrict__ ord, const uint32_t *__restrict__ idx,
+                              const uint32_t *__restrict__ gid_of, uint32_t ntot, long long *__restrict__ pfof)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ntot) return;
+    pfof[idx[ord[p]]] = (long long)gid_of[root[p]];
+}
+
+__global__ void k_remap_chunks(const long long *__restrict__ pfof, size_t n, long long iend, long long *__restrict__ out)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    long long g = pfof[i];
+    out[i] = g > iend ? iend : g;
+}
+
+__global__ void k_first_ungrouped(const long long *__restrict__ pfof, size_t n, unsigned int *__restrict__ first)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && pfof[i] == 0) atomicMin(first, (unsigned int)i);
+}
+
+long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof3d_dev, long long ngroups3d, double b6, double vfac,
+                       int mode, long long minsize, long long *pfof6d_dev, bool apply_q3)
+{
+    const int T = 256;
+    VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "6DFOF needs velocities");
+    VR_REQUIRE(b6 > 0 && vfac > 0, VRGPU_EINVAL, "6DFOF linking lengths must be positive");
+    VR_CUDA(cudaMemsetAsync(pfof6d_dev, 0, sizeof(long long) * (P.n ? P.n : 1), ctx->stream));
+    if (P.n == 0 || ngroups3d <= 0) return 0;
+
+    // ---- search chunks: one per 3D group; FOF6D (mode 4) merges every group with n <= ompunbindnum(1000) into ONE
+    //      chunk (search.cxx:529-535) ----
+    GroupSet gs;
+    DBuf<long long> chunk_of;
+    long long nchunks = ngroups3d;
+    long long n_first = 0, inext = -1;
+    {
+        KScope k(ctx, "fof6d.regroup");
+        if (mode == 4) {
+            GroupSet g0;
+            build_groupset(ctx, pfof3d_dev, P.n, ngroups3d, g0);
+            std::vector<uint32_t> off((size_t)ngroups3d + 2);
+            VR_CUDA(cudaMemcpyAsync(off.data(), g0.off.p, off.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            long long iend = ngroups3d;
+            for (long long g = 1; g <= ngroups3d; g++)
+                if (off[g + 1] - off[g] <= 1000u) { iend = g; break; }
+            n_first = off[2] - off[1];
+            if (ngroups3d >= 2) {
+                uint32_t h = 0;
+                VR_CUDA(cudaMemcpyAsync(&h, g0.idx.p + off[2], sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                inext = h;
+            } else {
+                DBuf<unsigned int> first(ctx, 1);
+                VR_CUDA(cudaMemsetAsync(first.p, 0xff, sizeof(unsigned int), ctx->stream));
+                VR_LAUNCH(ctx, k_first_ungrouped, grid_for(P.n, T), T, 0, pfof3d_dev, P.n, first.p);
+                unsigned int h = 0;
+                VR_CUDA(cudaMemcpyAsync(&h, first.p, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                inext = h == 0xffffffffu ? 0 : (long long)h;
+            }
+            nchunks = iend;
+            chunk_of.alloc(ctx, P.n);
+            VR_LAUNCH(ctx, k_remap_chunks, grid_for(P.n, T), T, 0, pfof3d_dev, P.n, iend, chunk_of.p);
+            build_groupset(ctx, chunk_of.p, P.n, nchunks, gs);
+        } else {
+            build_groupset(ctx, pfof3d_dev, P.n, ngroups3d, gs);
+        }
+    }
+    if (gs.ntot == 0) return 0;
+    { KScope k(ctx, "fof6d.gather"); gather_groupset(ctx, P, gs, true, true); }
+    const uint32_t ntot = (uint32_t)gs.ntot;
+    const uint32_t G = (uint32_t)nchunks;
+
+    // ---- velocity scale per chunk ----
+    DBuf<double> vs2(ctx, (size_t)G + 2);
+    {
+        KScope k(ctx, "fof6d.dispersion");
+        if (mode == 4) {
+            double mnorm = 1.0;
+            if (P.has_mass) {
+                VR_CUDA(cudaMemcpyAsync(&mnorm, P.mass.p + (inext >= 0 ? inext : 0), sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            }
+            // group 1 is chunk 1 unless it was itself merged (then its members are no longer contiguous: use the 3D layout)
+            if (nchunks >= 2 || ngroups3d == 1) {
+                VR_LAUNCH(ctx, k_single_dispersion, 1, 32, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
+            } else {
+                GroupSet g0;
+                build_groupset(ctx, pfof3d_dev, P.n, ngroups3d, g0);
+                gather_groupset(ctx, P, g0, true, true);
+                VR_LAUNCH(ctx, k_single_dispersion, 1, 32, 0, g0.vx.p, g0.vy.p, g0.vz.p, g0.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            }
+        } else {
+            const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 8u));
+            VR_LAUNCH(ctx, k_group_dispersion, grid, T, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, G, vfac, vs2.p);
+        }
+    }
+
+    // ---- scale (and write the un-scaled values back, Q3) ----
+    const double xs = 1.0 / b6;
+    const double xsinv = 1.0 / xs;
+    {
+        KScope k(ctx, "fof6d.scale_phase");
+        VR_LAUNCH(ctx, k_scale_phase, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.vx.p, gs.vy.p, gs.vz.p, gs.gid.p, gs.idx.p, vs2.p,
+                  ntot, xs, xsinv, apply_q3 ? P.pos.p : (double *)nullptr, apply_q3 ? P.vel.p : (double *)nullptr);
+    }
+
+    // ---- cells of edge 1 in scaled position space ----
+    DBuf<uint64_t> keys(ctx, ntot), keys_tmp(ctx, ntot);
+    DBuf<uint32_t> ord(ctx, ntot), ord_tmp(ctx, ntot);
+    DBuf<double> q(ctx, 6 * (size_t)ntot);
+    DBuf<uint32_t> cell_of(ctx, ntot), cell_start, nchunk, chunk_start;
+    DBuf<uint64_t> cell_key;
+    uint32_t ncells = 0, nwork = 0;
+    {
+        KScope k(ctx, "fof6d.cells");
+        DBuf<unsigned long long> mm(ctx, 6);
+        unsigned long long init[6] = {~0ull, ~0ull, ~0ull, 0ull, 0ull, 0ull};
+        VR_CUDA(cudaMemcpyAsync(mm.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+        VR_LAUNCH(ctx, k_minmax3, std::min<unsigned>(grid_for(ntot, T), (unsigned)ctx->sm_count * 8u), T, 0, gs.x.p, gs.y.p, gs.z.p, ntot, mm.p);
+        unsigned long long enc[6];
+        VR_CUDA(cudaMemcpyAsync(enc, mm.p, sizeof(enc), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        CellOrigin o{};
+        for (int a = 0; a < 3; a++) {
+            const double lo = ord_dbl_host(enc[a]), hi = ord_dbl_host(enc[3 + a]);
+            VR_REQUIRE(std::isfinite(lo) && std::isfinite(hi), VRGPU_EINVAL, "non-finite scaled positions in 6DFOF (zero velocity dispersion?)");
+            o.c0[a] = (long long)std::floor(lo);
+            VR_REQUIRE((long long)std::floor(hi) - o.c0[a] <= (long long)CMASK, VRGPU_EUNSUPPORTED,
+                       "6DFOF: extent / linking length exceeds 16384 cells per axis");
+        }
+        VR_REQUIRE(bits_for_u64v(G) + 3 * CBITS <= 64, VRGPU_EUNSUPPORTED, "6DFOF: too many 3D groups for the cell key");
+        VR_LAUNCH(ctx, k_keys6, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.gid.p, ntot, o, keys.p, ord.p);
+        radix_sort_pairs(ctx, keys.p, ord.p, keys_tmp.p, ord_tmp.p, ntot, bits_for_u64v(G) + 3 * CBITS);
+        VR_LAUNCH(ctx, k_gather6, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.vx.p, gs.vy.p, gs.vz.p, ord.p, ntot, q.p);
+        DBuf<uint32_t> flags(ctx, ntot), excl(ctx, ntot), total(ctx, 1);
+        VR_LAUNCH(ctx, k_flag_heads6, grid_for(ntot, T), T, 0, keys.p, ntot, flags.p);
+        exclusive_scan_u32(ctx, flags.p, excl.p, ntot, total.p);
+        VR_CUDA(cudaMemcpyAsync(&ncells, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        cell_start.alloc(ctx, (size_t)ncells + 1);
+        cell_key.alloc(ctx, ncells);
+        VR_LAUNCH(ctx, k_fill_cells6, grid_for(ntot, T), T, 0, keys.p, flags.p, excl.p, ntot, cell_of.p, cell_start.p, cell_key.p, ncells);
+        nchunk.alloc(ctx, ncells);
+        chunk_start.alloc(ctx, ncells);
+        VR_LAUNCH(ctx, k_chunk_counts, grid_for(ncells, T), T, 0, cell_start.p, ncells, nchunk.p);
+        exclusive_scan_u32(ctx, nchunk.p, chunk_start.p, ncells, total.p);
+        VR_CUDA(cudaMemcpyAsync(&nwork, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    keys.reset(); keys_tmp.reset(); ord_tmp.reset();
+    // the group-major columns are no longer needed (q holds the sorted copy)
+    gs.x.reset(); gs.y.reset(); gs.z.reset(); gs.vx.reset(); gs.vy.reset(); gs.vz.reset(); gs.m.reset();
+
+    // ---- union-find over particles ----
+    DBuf<uint32_t> parent(ctx, ntot), root(ctx, ntot), uni(ctx, ncells);
+    {
+        size_t h = 1;
+        while (h < 2 * (size_t)ncells) h <<= 1;
+        DBuf<uint64_t> hkeys(ctx, h);
+        DBuf<uint32_t> hvals(ctx, h);
+        Link6 L{};
+        L.q = q.p; L.ntot = ntot; L.cell_of = cell_of.p; L.cell_start = cell_start.p; L.cell_key = cell_key.p; L.ncells = ncells;
+        L.hkeys = hkeys.p; L.hvals = hvals.p; L.hmask = (uint32_t)(h - 1); L.parent = parent.p; L.uni = uni.p;
+        L.chunk_start = chunk_start.p; L.nchunks = nwork;
+        {
+            KScope k(ctx, "fof6d.hash_build");
+            VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
+            VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), (uint32_t *)nullptr);
+            VR_LAUNCH(ctx, k_uf_init, grid_for(ntot, T), T, 0, parent.p, ntot);
+        }
+        {
+            KScope k(ctx, "fof6d.seed");
+            VR_LAUNCH(ctx, k_seed6, grid_for(ntot, T), T, 0, L);
+            VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, parent.p);
+            const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)ncells * 32, T), (unsigned)ctx->sm_count * 16u));
+            VR_LAUNCH(ctx, k_cell_uniform, grid, T, 0, parent.p, cell_start.p, ncells, uni.p);
+        }
+        {
+            KScope k(ctx, "fof6d.link");
+            const unsigned grid = std::max(1u, std::min<unsigned>((nwork + L6_WARPS - 1) / L6_WARPS, (unsigned)ctx->sm_count * 32u));
+            VR_LAUNCH(ctx, k_link6, grid, L6_WARPS * 32, 0, L);
+            VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, root.p);
+        }
+    }
+
+    // ---- labels: (size desc, min pid asc) over all chunks ----
+    uint32_t ng = 0;
+    {
+        KScope k(ctx, "fof6d.labels");
+        DBuf<uint32_t> csize(ctx, ntot), gid_of(ctx, ntot);
+        DBuf<unsigned long long> cminpid(ctx, ntot);
+        VR_CUDA(cudaMemsetAsync(csize.p, 0, sizeof(uint32_t) * ntot, ctx->stream));
+        VR_CUDA(cudaMemsetAsync(cminpid.p, 0xff, sizeof(unsigned long long) * ntot, ctx->stream));
+        VR_LAUNCH(ctx, k_comp_stats, grid_for(ntot, T), T, 0, root.p, ord.p, gs.idx.p, P.has_pid ? P.pid.p : (const long long *)nullptr, ntot,
+                  csize.p, cminpid.p);
+        uint32_t ms = minsize < 1 ? 1u : (minsize > 0xffffffffLL ? 0xffffffffu : (uint32_t)minsize);
+        ng = order_groups(ctx, root.p, csize.p, cminpid.p, ntot, ms, gid_of.p);
+        VR_LAUNCH(ctx, k_write_pfof6, grid_for(ntot, T), T, 0, root.p, ord.p, gs.idx.p, gid_of.p, ntot, pfof6d_dev);
+    }
+    return (long long)ng;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host write-back of the phase-space coordinates the path rewrote (AdjustStructureForPeriod + Q3)
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_flag_pos(const long long *__restrict__ pfof, size_t n, uint32_t *__restrict__ flags)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = pfof[i] > 0 ? 1u : 0u;
+}
+__global__ void k_pack_phase(const double *__restrict__ pos, const double *__restrict__ vel, const uint32_t *__restrict__ flags,
+                             const uint32_t *__restrict__ excl, size_t n, uint32_t *__restrict__ oidx, double *__restrict__ out)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !flags[i]) return;
+    const size_t s = excl[i];
+    oidx[s] = (uint32_t)i;
+    for (int k = 0; k < 3; k++) { out[6 * s + k] = pos[3 * i + k]; out[6 * s + 3 + k] = vel[3 * i + k]; }
+}
+
+void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev)
+{
+    if (P.n == 0) return;
+    VR_REQUIRE(P.has_vel && view.off_vel != VRGPU_NOFIELD, VRGPU_EINVAL, "write-back needs velocities in the view");
+    const int T = 256;
+    DBuf<uint32_t> flags(ctx, P.n), excl(ctx, P.n), total(ctx, 1);
+    VR_LAUNCH(ctx, k_flag_pos, grid_for(P.n, T), T, 0, pfof_dev, P.n, flags.p);
+    exclusive_scan_u32(ctx, flags.p, excl.p, P.n, total.p);
+    uint32_t cnt = 0;
+    VR_CUDA(cudaMemcpyAsync(&cnt, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (cnt == 0) return;
+    DBuf<uint32_t> oidx(ctx, cnt);
+    DBuf<double> out(ctx, 6 * (size_t)cnt);
+    VR_LAUNCH(ctx, k_pack_phase, grid_for(P.n, T), T, 0, P.pos.p, P.vel.p, flags.p, excl.p, P.n, oidx.p, out.p);
+    std::vector<uint32_t> hidx(cnt);
+    std::vector<double> hq(6 * (size_t)cnt);
+    VR_CUDA(cudaMemcpyAsync(hidx.data(), oidx.p, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(hq.data(), out.p, 6 * (size_t)cnt * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->stats.d2h_bytes += (long long)cnt * 52;
+    unsigned char *base = const_cast<unsigned char *>(static_cast<const unsigned char *>(view.base));
+    for (size_t k = 0; k < cnt; k++) {
+        unsigned char *rec = base + (size_t)hidx[k] * view.stride;
+        double *p = reinterpret_cast<double *>(rec + view.off_pos);
+        double *v = reinterpret_cast<double *>(rec + view.off_vel);
+        for (int a = 0; a < 3; a++) { p[a] = hq[6 * k + a]; v[a] = hq[6 * k + 3 + a]; }
+    }
+}
+
+} // namespace vrgpu
