@@ -85,6 +85,7 @@ typedef struct {
     double h2d_ms, sort_ms, link_ms, label_ms, fof6d_ms, potential_ms, unbind_ms, d2h_ms, total_ms;
     long long n_cells, n_groups3d, n_groups_final, n_grouped, n_pairs_potential, n_marginal;
     long long h2d_bytes, d2h_bytes, kernel_launches;
+    long long n_tree_interactions, n_tree_nodes; /* kd-tree potential: cell + leaf-particle interactions, nodes built */
 } vrgpu_stats;
 
 /* Create / destroy a context on CUDA device `device` (-1 = current device). */
@@ -145,6 +146,23 @@ int vrgpu_particles_release(vrgpu_ctx *ctx);
 int vrgpu_search_full_set_resident(vrgpu_ctx *ctx, const vrgpu_search_opts *opts, long long *ngroups_out);
 /* copy the pfof of the last resident run to the host (n entries, caller's particle order) */
 int vrgpu_resident_pfof(vrgpu_ctx *ctx, long long *pfof_out);
+
+/* ---- multi-GPU: one process (one context) per GPU, x-slab domain decomposition ------------------------------
+ * Replaces the MPI build of SearchFullSet (src/search.cxx:242-347; mpiroutines.cxx MPIInitialDomainDecomposition :49,
+ * MPIBuildParticleExportList :867, MPILinkAcross :2387, MPIGroupExchange :2548, MPICompileGroups :2818).
+ * Rank r of `nranks` holds the particles with slab_lo <= x < slab_hi; the slabs are ordered by rank and tile
+ * [0, period).  Rank 0 creates the 128-byte id, the host code broadcasts it (MPI_Bcast in the reference's world,
+ * torch.distributed in bench.py), every rank calls vrgpu_dist_init.  The search returns GLOBAL group ids (identical on
+ * every rank and identical to the single-GPU ids); *ngroups_out is the global group count.  Unlike the single-GPU
+ * call, coordinates are not written back to the caller (pfof only). */
+#define VRGPU_UNIQUE_ID_BYTES 128
+int vrgpu_dist_unique_id(char *id_out /*[128]*/);
+int vrgpu_dist_init(vrgpu_ctx *ctx, int nranks, int rank, const char *id /*[128]*/);
+int vrgpu_dist_search_full_set(vrgpu_ctx *ctx, vrgpu_view local, double slab_lo, double slab_hi, const vrgpu_search_opts *opts,
+                               long long *pfof_out, long long *ngroups_out);
+/* the same on the particles handed over with vrgpu_particles_upload (result: vrgpu_resident_pfof) */
+int vrgpu_dist_search_full_set_resident(vrgpu_ctx *ctx, double slab_lo, double slab_hi, const vrgpu_search_opts *opts,
+                                        long long *ngroups_out);
 
 /* ---- measurement hooks ------------------------------------------------------------------------------- */
 /* the CUDA stream (cudaStream_t) every kernel of this context is launched on, for event timing by the caller */

@@ -1,0 +1,101 @@
+"""GPU parity: kd-tree monopole potentials (vrgpu_potential with n > pp_threshold) against the oracle restatement of
+Potential() (unbind.cxx:1607-1741), which itself is pinned to the reference at 1e-12 (tests/test_oracle_vs_ref.py).
+
+Tolerance: BASELINE.json asks 1e-6 relative "against its tree at identical settings"; asserted here at 1e-10 on inputs whose
+coordinates are distinct (node membership is then unique).  With exactly tied coordinates at a median the reference's
+quickselect picks by swap history; the GPU build picks the lower member index, so a few cells differ by one particle:
+that case is measured separately and bounded by the monopole truncation error."""
+import numpy as np
+import pytest
+
+import vrsynth
+
+pytestmark = pytest.mark.gpu
+G = 43.0211349
+
+
+def _clustered(n, rng, scale=1.0):
+    r = rng.random(n) ** 1.5
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    return 50.0 + scale * r[:, None] * d
+
+
+@pytest.mark.parametrize("eps", [0.0, 0.01])
+def test_tree_potential_matches_oracle(gpu_ctx, oracle, eps):
+    import vrgpu
+    rng = np.random.default_rng(17)
+    sizes = [151, 152, 400, 1000, 5000, 40000, 9, 150]
+    pos = np.concatenate([_clustered(s, rng) for s in sizes])
+    mass = 0.5 + rng.random(len(pos))
+    parts = vrgpu.particles_from_arrays(pos, mass=mass)
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    index = np.arange(len(pos))
+    phi = gpu_ctx.potential(parts, off, index, G, eps=eps, theta=0.5, bucket=8, pp_threshold=150)
+    st = gpu_ctx.stats()
+    ninter = 0
+    for g, s in enumerate(sizes):
+        sel = index[off[g]:off[g + 1]]
+        if s > 150:
+            ref, inter = oracle.potential_tree(pos[sel], mass[sel], G, eps, 0.5, 8)
+            ninter += inter
+        else:
+            ref = oracle.potential_pp(pos[sel], mass[sel], G, eps)
+        assert np.max(np.abs(phi[off[g]:off[g + 1]] / ref - 1.0)) < 1e-10, (g, s)
+    assert st["n_tree_interactions"] == ninter  # same cells opened, same leaves visited
+
+
+@pytest.mark.parametrize("theta,bucket", [(0.7, 8), (0.5, 16), (0.3, 4)])
+def test_tree_settings(gpu_ctx, oracle, theta, bucket):
+    import vrgpu
+    rng = np.random.default_rng(3)
+    n = 6000
+    pos = _clustered(n, rng, 2.0)
+    mass = np.ones(n)
+    parts = vrgpu.particles_from_arrays(pos, mass=mass)
+    phi = gpu_ctx.potential(parts, np.array([0, n]), np.arange(n), G, eps=0.0, theta=theta, bucket=bucket, pp_threshold=150)
+    ref, _ = oracle.potential_tree(pos, mass, G, 0.0, theta, bucket)
+    assert np.max(np.abs(phi / ref - 1.0)) < 1e-10
+
+
+def test_tree_with_tied_coordinates(gpu_ctx, oracle):
+    """float32-quantised positions (what a Gadget snapshot holds): ties at split medians make the reference's node
+    membership depend on its quickselect history.  Most particles still agree to 1e-10; the rest stay inside the
+    monopole truncation error."""
+    import vrgpu
+    rng = np.random.default_rng(8)
+    n = 30000
+    pos = _clustered(n, rng, 0.5).astype(np.float32).astype(np.float64)
+    mass = np.ones(n)
+    parts = vrgpu.particles_from_arrays(pos, mass=mass)
+    eps = 1e-3  # coincident float32 positions exist: keep every term finite
+    phi = gpu_ctx.potential(parts, np.array([0, n]), np.arange(n), G, eps=eps, pp_threshold=150)
+    ref, _ = oracle.potential_tree(pos, mass, G, eps, 0.5, 8)
+    pp = oracle.potential_pp(pos, mass, G, eps)
+    rel = np.abs(phi / ref - 1.0)
+    print("tied-coordinate case: frac(|dphi/phi| > 1e-6) =", float(np.mean(rel > 1e-6)), "max", float(rel.max()))
+    assert np.max(np.abs(phi / pp - 1.0)) < 5e-2
+    assert rel.max() < 1e-2  # same order as the tree's own truncation error; NOT the 1e-10 of the tie-free case
+
+
+def test_unbind_with_tree_potentials(gpu_ctx, oracle):
+    """CheckUnboundGroups with the stock thresholds (direct sum n <= 150, tree above)."""
+    import vrgpu
+    import vroracle
+    nside = 64
+    d = vrsynth.make_box(nside ** 3, 7)
+    # de-quantise so that kd-tree membership is unique (see test_tree_with_tied_coordinates)
+    rng = np.random.default_rng(1)
+    pos0 = np.mod(d["pos"] + rng.random(d["pos"].shape) * 1e-7, vrsynth.BOX)
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(pos0, b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(pos0, vrsynth.BOX, pf, ng)
+    uo = vroracle.unbind_opts_from(vroracle.default_opts(), pp_threshold=150, sortflag_mode=0)
+    want = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, uo, d["pid"], 1e-6)
+    parts = vrgpu.particles_from_arrays(pos, d["vel"], d["mass"], d["pid"])
+    got = gpu_ctx.unbind(parts, pf, ng, vrgpu.default_unbind_opts(pp_threshold=150))
+    assert gpu_ctx.stats()["n_tree_nodes"] > 0
+    ndiff = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
+    assert ndiff <= want["n_marginal"] + got["n_marginal"]
+    if ndiff == 0:
+        assert got["ngroups"] == want["ngroups"] and np.array_equal(got["pfof"], want["pfof"])

@@ -431,6 +431,71 @@ int vrgpu_resident_pfof(vrgpu_ctx *ctx, long long *pfof_out)
     });
 }
 
+int vrgpu_dist_unique_id(char *id_out)
+{
+    if (!id_out) return VRGPU_EINVAL;
+    try {
+        mg_unique_id(id_out);
+        return VRGPU_OK;
+    } catch (const Error &e) {
+        g_init_error = e.what();
+        return e.code;
+    }
+}
+
+int vrgpu_dist_init(vrgpu_ctx *ctx, int nranks, int rank, const char *id)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(id != nullptr || nranks == 1, VRGPU_EINVAL, "null unique id");
+        mg_init(ctx, nranks, rank, id);
+    });
+}
+
+int vrgpu_dist_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, double slab_lo, double slab_hi, const vrgpu_search_opts *o,
+                               long long *pfof_out, long long *ngroups_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(o && pfof_out && ngroups_out, VRGPU_EINVAL, "null pointer");
+        check_search_opts(o);
+        CallTimer ct(ctx);
+        const bool six = o->fofbgtype <= 4;
+        const bool unbind = o->bound_halos >= 1;
+        DeviceParticles P;
+        {
+            StageTimer t(ctx);
+            upload_view(ctx, view, six || unbind, six || unbind, true, P);
+            ctx->stats.h2d_ms += t.stop();
+        }
+        DBuf<long long> pf;
+        long long ng = 0;
+        if (mg_nranks(ctx) == 1) run_search(ctx, P, o, nullptr, pf, ng);
+        else mg_search(ctx, P, slab_lo, slab_hi, o, pf, ng);
+        {
+            StageTimer t(ctx);
+            download_i64(ctx, pf.p, pfof_out, P.n);
+            ctx->stats.d2h_ms += t.stop();
+        }
+        *ngroups_out = ng;
+        ctx->stats.n_groups_final = ng;
+    });
+}
+
+int vrgpu_dist_search_full_set_resident(vrgpu_ctx *ctx, double slab_lo, double slab_hi, const vrgpu_search_opts *o, long long *ngroups_out)
+{
+    if (ctx && mg_nranks(ctx) == 1) return vrgpu_search_full_set_resident(ctx, o, ngroups_out);
+    return guarded(ctx, [&] {
+        VR_REQUIRE(o && ngroups_out, VRGPU_EINVAL, "null pointer");
+        VR_REQUIRE(ctx->resident != nullptr, VRGPU_EINVAL, "no resident particles: call vrgpu_particles_upload first");
+        check_search_opts(o);
+        CallTimer ct(ctx);
+        ResidentState &R = *ctx->resident;
+        // the multi-GPU path never writes into its input columns (it works on the extended / consolidated copies)
+        mg_search(ctx, R.pristine, slab_lo, slab_hi, o, R.pfof, R.ngroups);
+        *ngroups_out = R.ngroups;
+        ctx->stats.n_groups_final = R.ngroups;
+    });
+}
+
 void *vrgpu_stream(vrgpu_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 
 const char *vrgpu_kernel_times(vrgpu_ctx *ctx)

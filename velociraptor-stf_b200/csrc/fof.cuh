@@ -22,6 +22,7 @@ struct Grid {
     double c[3];
     int nc[3];
     double period; // 0 = open
+    int periodic[3]; // per axis: wraps at `period`
     int bits[3];   // bits per axis in the packed key
 };
 
@@ -46,9 +47,12 @@ void download_i64(vrgpu_ctx *ctx, const long long *dev, long long *host, size_t 
 
 // stages
 void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double period, long long minsize, Fof3dState &S);
+// the two halves of fof3d_device: linking (periodic_axes == nullptr: every axis wraps when period > 0) and labelling
+void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double period, const int *periodic_axes, Fof3dState &S);
+void fof3d_label(vrgpu_ctx *ctx, const DeviceParticles &P, long long minsize, Fof3dState &S);
 // AdjustStructureForPeriod on the device copy (P.pos updated in place); returns the number of moved particles and
 // fills compact lists (original index, new xyz) for the host write-back.
 size_t adjust_for_period_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof_dev, long long ngroups, double period,
-                                DBuf<uint32_t> &moved_idx, DBuf<double> &moved_xyz);
+                                DBuf<uint32_t> &moved_idx, DBuf<double> &moved_xyz, bool by_pid = false);
 
 } // namespace vrgpu

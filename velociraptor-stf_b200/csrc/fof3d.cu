@@ -39,7 +39,7 @@ struct LinkParams {
     double lox, loy, loz;
     double period;
     double b2;
-    int periodic;
+    int perx, pery, perz; // per-axis periodicity (a slab of a multi-GPU run is open along x)
 };
 
 __constant__ signed char c_offsets[62][3];
@@ -54,7 +54,9 @@ __global__ void k_cell_keys(const double *__restrict__ pos, size_t n, Grid g, ui
     if (i >= n) return;
     double x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
     bool bad = !(x == x) || !(y == y) || !(z == z);
-    if (g.period > 0) bad = bad || x < 0 || y < 0 || z < 0 || x > g.period || y > g.period || z > g.period;
+    if (g.periodic[0]) bad = bad || x < 0 || x > g.period;
+    if (g.periodic[1]) bad = bad || y < 0 || y > g.period;
+    if (g.periodic[2]) bad = bad || z < 0 || z > g.period;
     if (bad) atomicAdd(nbad, 1u);
     long long ix = (long long)floor((x - g.lo[0]) * g.inv_c[0]);
     long long iy = (long long)floor((y - g.lo[1]) * g.inv_c[1]);
@@ -165,13 +167,12 @@ __global__ void __launch_bounds__(256) k_link_cells(LinkParams P, int off_begin,
                 int nx = ix + dx, ny = iy + dy, nz = iz + dz;
                 int sx = 0, sy = 0, sz = 0;
                 bool ok = true;
-                if (P.periodic) {
-                    if (nx < 0) { nx += P.ncx; sx = 1; } else if (nx >= P.ncx) { nx -= P.ncx; sx = -1; }
-                    if (ny < 0) { ny += P.ncy; sy = 1; } else if (ny >= P.ncy) { ny -= P.ncy; sy = -1; }
-                    if (nz < 0) { nz += P.ncz; sz = 1; } else if (nz >= P.ncz) { nz -= P.ncz; sz = -1; }
-                } else {
-                    ok = nx >= 0 && ny >= 0 && nz >= 0 && nx < P.ncx && ny < P.ncy && nz < P.ncz;
-                }
+                if (nx < 0) { if (P.perx) { nx += P.ncx; sx = 1; } else ok = false; }
+                else if (nx >= P.ncx) { if (P.perx) { nx -= P.ncx; sx = -1; } else ok = false; }
+                if (ny < 0) { if (P.pery) { ny += P.ncy; sy = 1; } else ok = false; }
+                else if (ny >= P.ncy) { if (P.pery) { ny -= P.ncy; sy = -1; } else ok = false; }
+                if (nz < 0) { if (P.perz) { nz += P.ncz; sz = 1; } else ok = false; }
+                else if (nz >= P.ncz) { if (P.perz) { nz -= P.ncz; sz = -1; } else ok = false; }
                 if (ok) {
                     uint64_t nkey = ((uint64_t)nz * (uint64_t)P.ncy + (uint64_t)ny) * (uint64_t)P.ncx + (uint64_t)nx;
                     nb = hash_lookup(P.hkeys, P.hvals, P.hmask, nkey);
@@ -421,12 +422,19 @@ uint32_t order_groups(vrgpu_ctx *ctx, const uint32_t *root, const uint32_t *gsiz
 
 void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double period, long long minsize, Fof3dState &S)
 {
+    fof3d_link(ctx, P, b, period, nullptr, S);
+    fof3d_label(ctx, P, minsize, S);
+}
+
+// cells + union-find: fills S.order / cell_of / cell_start / cell_key / root (root cell of every non-empty cell)
+void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double period, const int *periodic_axes, Fof3dState &S)
+{
     const size_t n = P.n;
     const int T = 256;
     S.n = n;
     S.ngroups = 0;
     S.ngrouped = 0;
-    S.pfof.alloc(ctx, n ? n : 1);
+    S.ncells = 0;
     if (n == 0) return;
     VR_REQUIRE(n < (size_t)0xfffffff0u, VRGPU_EINVAL, "more than 2^32 particles on one device");
     VR_REQUIRE(b > 0, VRGPU_EINVAL, "linking length must be positive");
@@ -435,18 +443,14 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
     // ---- grid ----
     Grid g{};
     g.period = period > 0 ? period : 0.0;
+    bool any_open = false;
+    for (int k = 0; k < 3; k++) {
+        g.periodic[k] = g.period > 0 && (!periodic_axes || periodic_axes[k]);
+        any_open = any_open || !g.periodic[k];
+    }
     const double cmax = b / std::sqrt(3.0) * (1.0 - 1e-8);
-    if (g.period > 0) {
-        for (int k = 0; k < 3; k++) {
-            g.lo[k] = 0.0;
-            double m = std::ceil(g.period / cmax);
-            VR_REQUIRE(m < 2.0e6, VRGPU_EUNSUPPORTED, "linking length too small for the cell key (period/b > ~1e6)");
-            g.nc[k] = (int)m;
-            VR_REQUIRE(g.nc[k] >= 8, VRGPU_EUNSUPPORTED, "periodic box smaller than ~5 linking lengths is not supported");
-            g.c[k] = g.period / g.nc[k];
-            g.inv_c[k] = (double)g.nc[k] / g.period;
-        }
-    } else {
+    double lohi[6] = {0, 0, 0, 0, 0, 0};
+    if (any_open) {
         DBuf<double> mm(ctx, 6);
         unsigned long long init[6] = {~0ull, ~0ull, ~0ull, 0ull, 0ull, 0ull};
         VR_CUDA(cudaMemcpyAsync(mm.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
@@ -454,13 +458,22 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         unsigned long long enc[6];
         VR_CUDA(cudaMemcpyAsync(enc, mm.p, sizeof(enc), cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
-        double lohi[6];
         for (int k = 0; k < 6; k++) {
             unsigned long long u = enc[k];
             u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
             std::memcpy(&lohi[k], &u, 8);
         }
-        for (int k = 0; k < 3; k++) {
+    }
+    for (int k = 0; k < 3; k++) {
+        if (g.periodic[k]) {
+            g.lo[k] = 0.0;
+            double m = std::ceil(g.period / cmax);
+            VR_REQUIRE(m < 2.0e6, VRGPU_EUNSUPPORTED, "linking length too small for the cell key (period/b > ~1e6)");
+            g.nc[k] = (int)m;
+            VR_REQUIRE(g.nc[k] >= 8, VRGPU_EUNSUPPORTED, "periodic box smaller than ~5 linking lengths is not supported");
+            g.c[k] = g.period / g.nc[k];
+            g.inv_c[k] = (double)g.nc[k] / g.period;
+        } else {
             g.lo[k] = lohi[k];
             double ext = lohi[3 + k] - lohi[k];
             VR_REQUIRE(std::isfinite(ext), VRGPU_EINVAL, "non-finite positions");
@@ -525,7 +538,7 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         L.ncx = g.nc[0]; L.ncy = g.nc[1]; L.ncz = g.nc[2];
         L.cx = g.c[0]; L.cy = g.c[1]; L.cz = g.c[2];
         L.lox = g.lo[0]; L.loy = g.lo[1]; L.loz = g.lo[2];
-        L.period = g.period; L.periodic = g.period > 0;
+        L.period = g.period; L.perx = g.periodic[0]; L.pery = g.periodic[1]; L.perz = g.periodic[2];
         L.b2 = b * b; // KDFOF.cxx:14
         // one warp per cell, grid a multiple of the SM count
         unsigned warps_needed = ncells;
@@ -538,7 +551,16 @@ void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double per
         ctx->stats.link_ms += t.stop();
     }
 
-    // ---- groups ----
+}
+
+// group sizes / min pid per root cell, drop < minsize, ids by (size desc, min pid asc), pfof in caller order
+void fof3d_label(vrgpu_ctx *ctx, const DeviceParticles &P, long long minsize, Fof3dState &S)
+{
+    const size_t n = P.n;
+    const int T = 256;
+    S.pfof.alloc(ctx, n ? n : 1);
+    if (n == 0) return;
+    const uint32_t ncells = S.ncells;
     {
         StageTimer t(ctx);
         DBuf<uint32_t> gsize(ctx, ncells), gminidx(ctx, ncells), gid_of_cell(ctx, ncells);
@@ -604,14 +626,38 @@ __global__ void k_adjust_period(double *__restrict__ pos, const long long *__res
     (void)pass;
 }
 
+__global__ void k_group_minpid(const long long *__restrict__ pfof, const long long *__restrict__ pid, size_t n, unsigned long long *__restrict__ minpid)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    long long g = pfof[i];
+    if (g > 0) atomicMin(&minpid[g], (unsigned long long)pid[i]);
+}
+__global__ void k_group_first_by_pid(const long long *__restrict__ pfof, const long long *__restrict__ pid, size_t n,
+                                     const unsigned long long *__restrict__ minpid, uint32_t *__restrict__ first)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    long long g = pfof[i];
+    if (g > 0 && (unsigned long long)pid[i] == minpid[g]) atomicMin(&first[g], (uint32_t)i);
+}
+
 size_t adjust_for_period_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof_dev, long long ngroups, double period,
-                                DBuf<uint32_t> &moved_idx, DBuf<double> &moved_xyz)
+                                DBuf<uint32_t> &moved_idx, DBuf<double> &moved_xyz, bool by_pid)
 {
     if (P.n == 0 || ngroups <= 0 || !(period > 0)) return 0;
     const int T = 256;
     DBuf<uint32_t> first(ctx, (size_t)ngroups + 1);
     VR_CUDA(cudaMemsetAsync(first.p, 0xff, sizeof(uint32_t) * ((size_t)ngroups + 1), ctx->stream));
-    VR_LAUNCH(ctx, k_group_first, grid_for(P.n, T), T, 0, pfof_dev, P.n, first.p);
+    if (by_pid && P.has_pid) {
+        // multi-GPU runs: the array order of a consolidated group is not the caller's, so the reference particle is the
+        // member with the smallest pid (== the first member whenever pids follow the input order)
+        DBuf<unsigned long long> minpid(ctx, (size_t)ngroups + 1);
+        VR_CUDA(cudaMemsetAsync(minpid.p, 0xff, sizeof(unsigned long long) * ((size_t)ngroups + 1), ctx->stream));
+        VR_LAUNCH(ctx, k_group_minpid, grid_for(P.n, T), T, 0, pfof_dev, P.pid.p, P.n, minpid.p);
+        VR_LAUNCH(ctx, k_group_first_by_pid, grid_for(P.n, T), T, 0, pfof_dev, P.pid.p, P.n, minpid.p, first.p);
+    } else
+        VR_LAUNCH(ctx, k_group_first, grid_for(P.n, T), T, 0, pfof_dev, P.n, first.p);
     // worst case every grouped particle moves; allocate for n (lists are compacted by the atomic counter)
     moved_idx.alloc(ctx, P.n);
     moved_xyz.alloc(ctx, 3 * P.n);

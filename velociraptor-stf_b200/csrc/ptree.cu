@@ -1,0 +1,472 @@
+// velociraptor-stf_b200/csrc/ptree.cu -- kd-tree monopole ("Barnes-Hut") potentials for large groups.
+//
+// Replaces Potential() (src/unbind.cxx:1607-1741) with its helpers GetNodeList (:13-21) and MarkCell (:24-44) and the
+// kd-tree it builds (NBody::KDTree::BuildNodes, NBodylib/src/KDTree/KDTree.cxx:438-507: split dimension = largest
+// spread (first wins), median index k = start + (size-1)/2, left child = the k-start+1 smallest along that dimension,
+// leaf when size <= BucketSize).
+//
+// Device design: every group above the direct-sum threshold is built in the SAME launches, level by level.
+//   * ranks: three global radix sorts give every particle its rank along x, y, z (ties -> member order);
+//   * a level = the "frontier" of current nodes, ordered by start.  Per level: segment index per particle (head flags +
+//     scan), per-node min/max per axis (ordered-integer atomics), split dimension, then ONE stable radix sort on the
+//     key (frontier index, rank along the node's split dimension) -- after it the first k-start+1 particles of each
+//     segment are the left child.  Finished leaves carry key (index, 0) and keep their place;
+//   * node monopoles bottom-up (leaf sums sequentially in tree order, parents = sum of children: deterministic),
+//     Bmax by ordered-integer atomicMax along every particle's root-to-leaf path, cR2max = 4/3 Bmax^2 / theta^2;
+//   * walk: one thread per particle (tree order, so a warp walks neighbouring paths), explicit stack, MarkCell's
+//     opening test r2 < cR2max evaluated in the reference's operation order, monopole and leaf terms accumulated in
+//     fp64 in visiting order.
+// Node MEMBERSHIP equals the reference's whenever the coordinates along a split dimension are distinct at the median
+// (the reference's quickselect leaves the choice among exactly equal coordinates to its swap sequence; here the tie
+// goes to the lower member index) -- see DESIGN.md "tree parity".
+#include "groups.cuh"
+#include "ufhash.cuh"
+
+#include <algorithm>
+#include <cmath>
+
+namespace vrgpu {
+
+namespace {
+
+constexpr uint32_t NOCHILD = 0xffffffffu;
+
+__device__ __forceinline__ unsigned long long pt_ord(double d)
+{
+    unsigned long long u = (unsigned long long)__double_as_longlong(d);
+    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double pt_unord(unsigned long long u)
+{
+    u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
+    return __longlong_as_double((long long)u);
+}
+
+// ---- selection of the large groups ------------------------------------------------------------------
+__global__ void k_pt_flag(const uint32_t *__restrict__ gid, const uint32_t *__restrict__ off, uint32_t ntot, long long pp,
+                          uint32_t *__restrict__ flags)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    const uint32_t g = gid[s];
+    flags[s] = (long long)(off[g + 1] - off[g]) > pp ? 1u : 0u;
+}
+__global__ void k_pt_compact(const uint32_t *__restrict__ flags, const uint32_t *__restrict__ excl, uint32_t ntot,
+                             uint32_t *__restrict__ slot_of)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < ntot && flags[s]) slot_of[excl[s]] = s;
+}
+__global__ void k_pt_gflag(const uint32_t *__restrict__ off, uint32_t G, long long pp, uint32_t *__restrict__ gflag)
+{
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g > G) return;
+    gflag[g] = (g >= 1 && (long long)(off[g + 1] - off[g]) > pp) ? 1u : 0u;
+}
+// root node r (= rank of the group among the large ones) covers the group's compacted range
+__global__ void k_pt_roots(const uint32_t *__restrict__ off, const uint32_t *__restrict__ gflag, const uint32_t *__restrict__ gexcl,
+                           const uint32_t *__restrict__ sexcl, uint32_t G, uint32_t ntot, uint32_t *__restrict__ nstart,
+                           uint32_t *__restrict__ nend, uint32_t *__restrict__ nleft, uint32_t *__restrict__ frontier)
+{
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g > G || !gflag[g]) return;
+    const uint32_t r = gexcl[g];
+    const uint32_t s0 = off[g];
+    const uint32_t c0 = sexcl[s0];
+    nstart[r] = c0;
+    nend[r] = c0 + (off[g + 1] - s0);
+    nleft[r] = NOCHILD;
+    frontier[r] = r;
+}
+
+// ---- ranks along each axis --------------------------------------------------------------------------
+__global__ void k_pt_coord_keys(const double *__restrict__ c, const uint32_t *__restrict__ slot_of, uint32_t nL,
+                                uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nL) return;
+    keys[p] = pt_ord(c[slot_of[p]]);
+    vals[p] = p;
+}
+__global__ void k_pt_rank(const uint32_t *__restrict__ vals, uint32_t nL, uint32_t *__restrict__ rank)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < nL) rank[vals[p]] = p;
+}
+__global__ void k_pt_iota(uint32_t *__restrict__ a, uint32_t n)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) a[p] = p;
+}
+
+// ---- one level ----------------------------------------------------------------------------------------
+__global__ void k_pt_heads(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ nstart, uint32_t *__restrict__ heads)
+{
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < nF) heads[nstart[frontier[f]]] = 1u;
+}
+// fidx[pos] = index of the frontier entry that contains pos (exclusive scan of heads, + head - 1)
+__global__ void k_pt_fidx(const uint32_t *__restrict__ heads, const uint32_t *__restrict__ excl, uint32_t nL, uint32_t *__restrict__ fidx)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < nL) fidx[p] = excl[p] + heads[p] - 1u;
+}
+
+struct PtCols { const double *x, *y, *z; };
+
+// min / max per axis of every frontier node that will split (size > bucket)
+__global__ void __launch_bounds__(256) k_pt_minmax(PtCols C, const uint32_t *__restrict__ slot_of, const uint32_t *__restrict__ perm,
+                                                   const uint32_t *__restrict__ fidx, const uint32_t *__restrict__ frontier,
+                                                   const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend, uint32_t nL,
+                                                   uint32_t bucket, unsigned long long *__restrict__ mm /* 6 per frontier entry */)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t f = NOCHILD;
+    double v[3] = {0, 0, 0};
+    if (p < nL) {
+        f = fidx[p];
+        const uint32_t nd = frontier[f];
+        if (nend[nd] - nstart[nd] > bucket) {
+            const uint32_t s = slot_of[perm[p]];
+            v[0] = C.x[s]; v[1] = C.y[s]; v[2] = C.z[s];
+        } else f = NOCHILD;
+    }
+    const uint32_t f0 = __shfl_sync(0xffffffffu, f, 0);
+    if (__all_sync(0xffffffffu, f == f0)) {
+        if (f0 == NOCHILD) return;
+        for (int k = 0; k < 3; k++) {
+            double mn = v[k], mx = v[k];
+            for (int o = 16; o; o >>= 1) {
+                mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            }
+            if ((threadIdx.x & 31) == 0) { atomicMin(&mm[6 * (size_t)f0 + k], pt_ord(mn)); atomicMax(&mm[6 * (size_t)f0 + 3 + k], pt_ord(mx)); }
+        }
+    } else if (f != NOCHILD) {
+        for (int k = 0; k < 3; k++) { atomicMin(&mm[6 * (size_t)f + k], pt_ord(v[k])); atomicMax(&mm[6 * (size_t)f + 3 + k], pt_ord(v[k])); }
+    }
+}
+
+// split flag + split dimension (KDTree.cxx:438-507: largest spread, the first dimension wins a tie)
+__global__ void k_pt_choose(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ nstart,
+                            const uint32_t *__restrict__ nend, uint32_t bucket, const unsigned long long *__restrict__ mm,
+                            uint32_t *__restrict__ splitflag, uint32_t *__restrict__ splitdim)
+{
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nF) return;
+    const uint32_t nd = frontier[f];
+    const bool sp = nend[nd] - nstart[nd] > bucket;
+    splitflag[f] = sp ? 1u : 0u;
+    uint32_t d = 0;
+    if (sp) {
+        double best = __dsub_rn(pt_unord(mm[6 * (size_t)f + 3]), pt_unord(mm[6 * (size_t)f]));
+        for (int k = 1; k < 3; k++) {
+            double s = __dsub_rn(pt_unord(mm[6 * (size_t)f + 3 + k]), pt_unord(mm[6 * (size_t)f + k]));
+            if (s > best) { best = s; d = k; }
+        }
+    }
+    splitdim[f] = d;
+}
+
+__global__ void k_pt_level_keys(const uint32_t *__restrict__ perm, const uint32_t *__restrict__ fidx, const uint32_t *__restrict__ splitflag,
+                                const uint32_t *__restrict__ splitdim, const uint32_t *__restrict__ rank /* 3 x nL */, uint32_t nL,
+                                int rb, uint64_t *__restrict__ keys)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nL) return;
+    const uint32_t f = fidx[p];
+    uint32_t lo = 0;
+    if (splitflag[f]) lo = rank[(size_t)splitdim[f] * nL + perm[p]];
+    keys[p] = ((uint64_t)f << rb) | lo;
+}
+
+// children of the splitting nodes + next frontier (ordered by start)
+__global__ void k_pt_children(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ splitflag,
+                              const uint32_t *__restrict__ sexcl, uint32_t node_base, uint32_t *__restrict__ nstart,
+                              uint32_t *__restrict__ nend, uint32_t *__restrict__ nleft, uint32_t *__restrict__ next_frontier)
+{
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nF) return;
+    const uint32_t nd = frontier[f];
+    const uint32_t k = sexcl[f];
+    if (!splitflag[f]) { next_frontier[f + k] = nd; return; }
+    const uint32_t s = nstart[nd], e = nend[nd];
+    const uint32_t mid = s + (e - s - 1) / 2 + 1; // left = [s, k+1) with k = s + (size-1)/2
+    const uint32_t l = node_base + 2 * k, r = l + 1;
+    nleft[nd] = l;                                // right child = left + 1
+    nstart[l] = s; nend[l] = mid; nleft[l] = NOCHILD;
+    nstart[r] = mid; nend[r] = e; nleft[r] = NOCHILD;
+    next_frontier[f + k] = l;
+    next_frontier[f + k + 1] = r;
+}
+
+} // namespace
+
+namespace {
+
+// ---- monopoles ------------------------------------------------------------------------------------------
+struct PtNodes {
+    uint32_t *start, *end, *left;
+    double *sx, *sy, *sz, *sm;      // sums, then centre of mass in place
+    unsigned long long *bmax;       // ordered-int image of Bmax
+    double *r2max;
+};
+
+// leaves: sequential sums in tree order (unbind.cxx:1672-1675: cm += x*m, product rounded before the add)
+__global__ void k_pt_leaf_sums(PtNodes N, uint32_t nnodes, const double *__restrict__ tx, const double *__restrict__ ty,
+                               const double *__restrict__ tz, const double *__restrict__ tm)
+{
+    uint32_t nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= nnodes || N.left[nd] != NOCHILD) return;
+    double sx = 0, sy = 0, sz = 0, sm = 0;
+    for (uint32_t p = N.start[nd]; p < N.end[nd]; p++) {
+        const double m = tm[p];
+        sx = __dadd_rn(sx, __dmul_rn(tx[p], m)); sy = __dadd_rn(sy, __dmul_rn(ty[p], m)); sz = __dadd_rn(sz, __dmul_rn(tz[p], m));
+        sm = __dadd_rn(sm, m);
+    }
+    N.sx[nd] = sx; N.sy[nd] = sy; N.sz[nd] = sz; N.sm[nd] = sm;
+}
+// internal nodes of one level: sum of the two children
+__global__ void k_pt_inner_sums(PtNodes N, uint32_t n0, uint32_t n1)
+{
+    uint32_t nd = n0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= n1) return;
+    const uint32_t l = N.left[nd];
+    if (l == NOCHILD) return;
+    N.sx[nd] = __dadd_rn(N.sx[l], N.sx[l + 1]); N.sy[nd] = __dadd_rn(N.sy[l], N.sy[l + 1]);
+    N.sz[nd] = __dadd_rn(N.sz[l], N.sz[l + 1]); N.sm[nd] = __dadd_rn(N.sm[l], N.sm[l + 1]);
+}
+__global__ void k_pt_cm(PtNodes N, uint32_t nnodes)
+{
+    uint32_t nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= nnodes) return;
+    const double m = N.sm[nd];
+    N.sx[nd] = __ddiv_rn(N.sx[nd], m); N.sy[nd] = __ddiv_rn(N.sy[nd], m); N.sz[nd] = __ddiv_rn(N.sz[nd], m);
+    N.bmax[nd] = 0ull;
+}
+// Bmax (unbind.cxx:1677-1683): max over the node's particles of |cm - x|; every particle visits its root-to-leaf path
+__global__ void __launch_bounds__(256) k_pt_bmax(PtNodes N, const uint32_t *__restrict__ rootidx, uint32_t nL, const double *__restrict__ tx,
+                                                 const double *__restrict__ ty, const double *__restrict__ tz)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = p < nL;
+    uint32_t nd = valid ? rootidx[p] : NOCHILD;
+    double x = 0, y = 0, z = 0;
+    if (valid) { x = tx[p]; y = ty[p]; z = tz[p]; }
+    while (__any_sync(0xffffffffu, nd != NOCHILD)) {
+        double l = -1.0;
+        if (nd != NOCHILD) {
+            const double dx = __dsub_rn(N.sx[nd], x), dy = __dsub_rn(N.sy[nd], y), dz = __dsub_rn(N.sz[nd], z);
+            l = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+        }
+        const uint32_t n0 = __shfl_sync(0xffffffffu, nd, 0);
+        if (__all_sync(0xffffffffu, nd == n0)) {
+            for (int o = 16; o; o >>= 1) l = fmax(l, __shfl_xor_sync(0xffffffffu, l, o));
+            if ((threadIdx.x & 31) == 0) atomicMax(&N.bmax[n0], pt_ord(l));
+        } else if (nd != NOCHILD) atomicMax(&N.bmax[nd], pt_ord(l));
+        if (nd != NOCHILD) {
+            const uint32_t lc = N.left[nd];
+            nd = lc == NOCHILD ? NOCHILD : (p < N.end[lc] ? lc : lc + 1);
+        }
+    }
+}
+__global__ void k_pt_r2max(PtNodes N, uint32_t nnodes, double theta)
+{
+    uint32_t nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= nnodes) return;
+    const double xdiff = pt_unord(N.bmax[nd]);
+    // cR2max = 4.0/3.0*xdiff*xdiff/(theta*theta)   (unbind.cxx:1684, evaluated left to right)
+    N.r2max[nd] = __ddiv_rn(__dmul_rn(__dmul_rn(4.0 / 3.0, xdiff), xdiff), __dmul_rn(theta, theta));
+}
+
+__device__ __forceinline__ double pt_rsqrt(double r2)
+{
+    float f = (float)r2;
+    if (!(f > 0.0f) || !(f < 3.0e38f)) return 1.0 / sqrt(r2);
+    double y = (double)rsqrtf(f);
+    const double h = 0.5 * r2;
+    y = y * (1.5 - h * y * y);
+    y = y * (1.5 - h * y * y); // second step: ~1e-16, so the sum is dominated by fp64 accumulation error only
+    return y;
+}
+
+// ---- walk (MarkCell, unbind.cxx:24-44 + the sums at :1710-1723) ---------------------------------------------
+constexpr int PT_STACK = 96;
+__global__ void __launch_bounds__(128) k_pt_walk(PtNodes N, const uint32_t *__restrict__ rootidx, uint32_t nL, const double *__restrict__ tx,
+                                                 const double *__restrict__ ty, const double *__restrict__ tz, const double *__restrict__ tm,
+                                                 double G, double eps2, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of,
+                                                 double *__restrict__ phi, unsigned long long *__restrict__ ninter, unsigned int *__restrict__ overflow)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long cnt = 0;
+    if (p < nL) {
+        const double x = tx[p], y = ty[p], z = tz[p], mj = tm[p];
+        uint32_t stack[PT_STACK];
+        int sp = 0;
+        stack[sp++] = rootidx[p];
+        double acc = 0.0;
+        while (sp > 0) {
+            const uint32_t nd = stack[--sp];
+            const double dx = __dsub_rn(N.sx[nd], x), dy = __dsub_rn(N.sy[nd], y), dz = __dsub_rn(N.sz[nd], z);
+            const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+            if (r2 < N.r2max[nd]) {
+                const uint32_t lc = N.left[nd];
+                if (lc != NOCHILD) {
+                    if (sp + 2 > PT_STACK) { atomicAdd(overflow, 1u); break; }
+                    stack[sp++] = lc + 1; // right is visited after left
+                    stack[sp++] = lc;
+                } else {
+                    const uint32_t s = N.start[nd], e = N.end[nd];
+                    for (uint32_t l = s; l < e; l++) {
+                        if (l == p) continue;
+                        const double ax = __dsub_rn(x, tx[l]), ay = __dsub_rn(y, ty[l]), az = __dsub_rn(z, tz[l]);
+                        const double q2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)), eps2);
+                        acc -= (mj * tm[l]) * pt_rsqrt(q2);
+                        cnt++;
+                    }
+                }
+            } else {
+                acc -= mj * (N.sm[nd] * pt_rsqrt(r2 + eps2));
+                cnt++;
+            }
+        }
+        phi[slot_of[perm[p]]] = acc * G;
+    }
+    for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(ninter, cnt);
+}
+
+__global__ void k_pt_gather_tree(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                                 const double *__restrict__ m, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of, uint32_t nL,
+                                 double *__restrict__ tx, double *__restrict__ ty, double *__restrict__ tz, double *__restrict__ tm)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nL) return;
+    const uint32_t s = slot_of[perm[p]];
+    tx[p] = x[s]; ty[p] = y[s]; tz[p] = z[s]; tm[p] = m[s];
+}
+
+} // namespace
+
+namespace {
+__global__ void k_pt_mm_init(unsigned long long *__restrict__ mm, uint32_t nF)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 6 * nF) mm[i] = (i % 6) < 3 ? ~0ull : 0ull;
+}
+} // namespace
+
+void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, double theta, int bucket, long long pp_threshold, double *phi)
+{
+    if (gs.ntot == 0 || gs.ngroups == 0 || pp_threshold < 0) return;
+    VR_REQUIRE(bucket >= 1, VRGPU_EINVAL, "BucketSize must be >= 1");
+    VR_REQUIRE(theta > 0, VRGPU_EINVAL, "TreeThetaOpen must be positive");
+    const int T = 256;
+    const uint32_t ntot = (uint32_t)gs.ntot, NG = (uint32_t)gs.ngroups;
+
+    // ---- large groups -> compact positions ----
+    DBuf<uint32_t> flags(ctx, ntot), sexcl(ctx, ntot), total(ctx, 2), gflag(ctx, (size_t)NG + 1), gexcl(ctx, (size_t)NG + 1);
+    VR_LAUNCH(ctx, k_pt_flag, grid_for(ntot, T), T, 0, gs.gid.p, gs.off.p, ntot, pp_threshold, flags.p);
+    exclusive_scan_u32(ctx, flags.p, sexcl.p, ntot, total.p);
+    VR_LAUNCH(ctx, k_pt_gflag, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, NG, pp_threshold, gflag.p);
+    exclusive_scan_u32(ctx, gflag.p, gexcl.p, (size_t)NG + 1, total.p + 1);
+    uint32_t h2[2];
+    VR_CUDA(cudaMemcpyAsync(h2, total.p, sizeof(h2), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint32_t nL = h2[0], nLG = h2[1];
+    if (nL == 0) return;
+    DBuf<uint32_t> slot_of(ctx, nL);
+    VR_LAUNCH(ctx, k_pt_compact, grid_for(ntot, T), T, 0, flags.p, sexcl.p, ntot, slot_of.p);
+
+    // ---- ranks along the three axes (ties: lower member first) ----
+    DBuf<uint32_t> rank(ctx, 3 * (size_t)nL), perm(ctx, nL), vtmp(ctx, nL);
+    DBuf<uint64_t> keys(ctx, nL), ktmp(ctx, nL);
+    {
+        KScope k(ctx, "ptree.ranks");
+        const double *cols[3] = {gs.x.p, gs.y.p, gs.z.p};
+        for (int d = 0; d < 3; d++) {
+            VR_LAUNCH(ctx, k_pt_coord_keys, grid_for(nL, T), T, 0, cols[d], slot_of.p, nL, keys.p, perm.p);
+            radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nL, 64);
+            VR_LAUNCH(ctx, k_pt_rank, grid_for(nL, T), T, 0, perm.p, nL, rank.p + (size_t)d * nL);
+        }
+    }
+
+    // ---- nodes ----
+    const uint32_t minleaf = std::max(1u, ((uint32_t)bucket + 1u) / 2u);
+    const size_t cap = 2 * ((size_t)nL / minleaf + 1) + nLG + 16;
+    DBuf<uint32_t> nstart(ctx, cap), nend(ctx, cap), nleft(ctx, cap);
+    DBuf<uint32_t> frontier(ctx, cap), frontier2(ctx, cap), splitflag(ctx, cap), splitdim(ctx, cap), fexcl(ctx, cap);
+    DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL), fidx(ctx, nL), rootidx(ctx, nL);
+    DBuf<unsigned long long> mm(ctx, 6 * cap);
+    VR_LAUNCH(ctx, k_pt_roots, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, gflag.p, gexcl.p, sexcl.p, NG, ntot, nstart.p, nend.p, nleft.p, frontier.p);
+    VR_LAUNCH(ctx, k_pt_iota, grid_for(nL, T), T, 0, perm.p, nL);
+    uint32_t nF = nLG, nnodes = nLG;
+    std::vector<uint32_t> level_off{0u, nLG};
+    const int rb = bits_for_u64v(nL > 1 ? nL - 1 : 1);
+    PtCols C{gs.x.p, gs.y.p, gs.z.p};
+    uint32_t *fr = frontier.p, *fr2 = frontier2.p;
+    {
+        KScope kb(ctx, "ptree.build");
+        for (int level = 0; level < 64; level++) {
+            VR_CUDA(cudaMemsetAsync(heads.p, 0, sizeof(uint32_t) * nL, ctx->stream));
+            VR_LAUNCH(ctx, k_pt_heads, grid_for(nF, T), T, 0, fr, nF, nstart.p, heads.p);
+            exclusive_scan_u32(ctx, heads.p, hexcl.p, nL, nullptr);
+            VR_LAUNCH(ctx, k_pt_fidx, grid_for(nL, T), T, 0, heads.p, hexcl.p, nL, fidx.p);
+            if (level == 0) VR_CUDA(cudaMemcpyAsync(rootidx.p, fidx.p, sizeof(uint32_t) * nL, cudaMemcpyDeviceToDevice, ctx->stream));
+            VR_LAUNCH(ctx, k_pt_mm_init, grid_for((size_t)6 * nF, T), T, 0, mm.p, nF);
+            VR_LAUNCH(ctx, k_pt_minmax, grid_for(nL, T), T, 0, C, slot_of.p, perm.p, fidx.p, fr, nstart.p, nend.p, nL, (uint32_t)bucket, mm.p);
+            VR_LAUNCH(ctx, k_pt_choose, grid_for(nF, T), T, 0, fr, nF, nstart.p, nend.p, (uint32_t)bucket, mm.p, splitflag.p, splitdim.p);
+            exclusive_scan_u32(ctx, splitflag.p, fexcl.p, nF, total.p);
+            uint32_t nsplit = 0;
+            VR_CUDA(cudaMemcpyAsync(&nsplit, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (nsplit == 0) break;
+            VR_REQUIRE((size_t)nnodes + 2 * (size_t)nsplit <= cap, VRGPU_ECUDA, "kd-tree node capacity exceeded");
+            VR_LAUNCH(ctx, k_pt_level_keys, grid_for(nL, T), T, 0, perm.p, fidx.p, splitflag.p, splitdim.p, rank.p, nL, rb, keys.p);
+            radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nL, rb + bits_for_u64v(nF > 1 ? nF - 1 : 1));
+            VR_LAUNCH(ctx, k_pt_children, grid_for(nF, T), T, 0, fr, nF, splitflag.p, fexcl.p, nnodes, nstart.p, nend.p, nleft.p, fr2);
+            nnodes += 2 * nsplit;
+            nF += nsplit;
+            level_off.push_back(nnodes);
+            std::swap(fr, fr2);
+        }
+    }
+
+    // ---- tree-ordered columns, monopoles, opening radii ----
+    DBuf<double> tx(ctx, nL), ty(ctx, nL), tz(ctx, nL), tm(ctx, nL);
+    DBuf<double> sx(ctx, nnodes), sy(ctx, nnodes), sz(ctx, nnodes), sm(ctx, nnodes), r2max(ctx, nnodes);
+    DBuf<unsigned long long> bmax(ctx, nnodes);
+    PtNodes N{nstart.p, nend.p, nleft.p, sx.p, sy.p, sz.p, sm.p, bmax.p, r2max.p};
+    {
+        KScope k(ctx, "ptree.moments");
+        VR_LAUNCH(ctx, k_pt_gather_tree, grid_for(nL, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, perm.p, slot_of.p, nL, tx.p, ty.p, tz.p, tm.p);
+        VR_LAUNCH(ctx, k_pt_leaf_sums, grid_for(nnodes, T), T, 0, N, nnodes, tx.p, ty.p, tz.p, tm.p);
+        for (size_t l = level_off.size() - 1; l-- > 0;) {
+            const uint32_t n0 = level_off[l], n1 = level_off[l + 1];
+            if (n1 > n0) VR_LAUNCH(ctx, k_pt_inner_sums, grid_for(n1 - n0, T), T, 0, N, n0, n1);
+        }
+        VR_LAUNCH(ctx, k_pt_cm, grid_for(nnodes, T), T, 0, N, nnodes);
+        VR_LAUNCH(ctx, k_pt_bmax, grid_for(nL, T), T, 0, N, rootidx.p, nL, tx.p, ty.p, tz.p);
+        VR_LAUNCH(ctx, k_pt_r2max, grid_for(nnodes, T), T, 0, N, nnodes, theta);
+    }
+    // ---- walk ----
+    DBuf<unsigned long long> ninter(ctx, 1);
+    DBuf<unsigned int> overflow(ctx, 1);
+    VR_CUDA(cudaMemsetAsync(ninter.p, 0, sizeof(unsigned long long), ctx->stream));
+    VR_CUDA(cudaMemsetAsync(overflow.p, 0, sizeof(unsigned int), ctx->stream));
+    {
+        KScope k(ctx, "ptree.walk");
+        VR_LAUNCH(ctx, k_pt_walk, grid_for(nL, 128), 128, 0, N, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p, phi,
+                  ninter.p, overflow.p);
+    }
+    unsigned long long hi = 0;
+    unsigned int hov = 0;
+    VR_CUDA(cudaMemcpyAsync(&hi, ninter.p, sizeof(hi), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(&hov, overflow.p, sizeof(hov), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    VR_REQUIRE(hov == 0, VRGPU_ECUDA, "kd-tree walk stack overflow");
+    ctx->stats.n_tree_interactions += (long long)hi;
+    ctx->stats.n_tree_nodes += (long long)nnodes;
+}
+
+} // namespace vrgpu

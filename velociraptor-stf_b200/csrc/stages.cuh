@@ -21,7 +21,13 @@ void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngro
 void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
                    int &changed, long long &n_marginal);
 
-// multi-GPU state teardown (multigpu.cu)
+// multi-GPU (multigpu.cu)
 void mg_destroy(vrgpu_ctx *ctx);
+void mg_unique_id(char *out128);
+void mg_init(vrgpu_ctx *ctx, int nranks, int rank, const char *id128);
+int mg_nranks(const vrgpu_ctx *ctx);
+int mg_rank(const vrgpu_ctx *ctx);
+void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_hi, const vrgpu_search_opts *o, DBuf<long long> &pfof_out,
+               long long &ngroups);
 
 } // namespace vrgpu

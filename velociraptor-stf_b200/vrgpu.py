@@ -60,7 +60,7 @@ class Stats(C.Structure):
                                           "unbind_ms", "d2h_ms", "total_ms")] + \
                [(k, C.c_longlong) for k in ("n_cells", "n_groups3d", "n_groups_final", "n_grouped",
                                             "n_pairs_potential", "n_marginal", "h2d_bytes", "d2h_bytes",
-                                            "kernel_launches")]
+                                            "kernel_launches", "n_tree_interactions", "n_tree_nodes")]
 
     def asdict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -125,6 +125,10 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_particles_release.argtypes = [C.c_void_p]
     L.vrgpu_search_full_set_resident.argtypes = [C.c_void_p, C.POINTER(SearchOpts), P_ll]
     L.vrgpu_resident_pfof.argtypes = [C.c_void_p, P_ll]
+    L.vrgpu_dist_unique_id.argtypes = [C.c_char_p]
+    L.vrgpu_dist_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
+    L.vrgpu_dist_search_full_set.argtypes = [C.c_void_p, View, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll, P_ll]
+    L.vrgpu_dist_search_full_set_resident.argtypes = [C.c_void_p, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll]
     L.vrgpu_stream.argtypes = [C.c_void_p]
     L.vrgpu_stream.restype = C.c_void_p
     L.vrgpu_kernel_times.argtypes = [C.c_void_p]
@@ -138,7 +142,8 @@ def load_library(path: str = LIB_PATH):
 EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_version", "vrgpu_get_stats", "vrgpu_fof3d",
                     "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
-                    "vrgpu_resident_pfof", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset"]
+                    "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
+                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset"]
 
 
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
@@ -284,6 +289,23 @@ class Context:
         self._check(self.lib.vrgpu_resident_pfof(self.h, pfof.ctypes.data_as(C.POINTER(C.c_longlong))))
         return pfof
 
+    # ---- multi-GPU (one process per GPU; replaces the MPI build of SearchFullSet) ----
+    def dist_init(self, nranks: int, rank: int, unique_id: bytes | None):
+        self._check(self.lib.vrgpu_dist_init(self.h, nranks, rank, unique_id))
+
+    def dist_search_full_set(self, parts, slab_lo, slab_hi, opts: SearchOpts):
+        n = parts.shape[0]
+        pfof = np.zeros(n, dtype=np.int64)
+        ng = C.c_longlong(0)
+        self._check(self.lib.vrgpu_dist_search_full_set(self.h, view_of(parts), slab_lo, slab_hi, C.byref(opts),
+                                                        pfof.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
+        return pfof, int(ng.value)
+
+    def dist_search_full_set_resident(self, slab_lo, slab_hi, opts: SearchOpts) -> int:
+        ng = C.c_longlong(0)
+        self._check(self.lib.vrgpu_dist_search_full_set_resident(self.h, slab_lo, slab_hi, C.byref(opts), C.byref(ng)))
+        return int(ng.value)
+
     # ---- measurement hooks ----
     def stream(self) -> int:
         return int(self.lib.vrgpu_stream(self.h) or 0)
@@ -297,6 +319,15 @@ class Context:
 
     def kernel_times_reset(self):
         self.lib.vrgpu_kernel_times_reset(self.h)
+
+
+def dist_unique_id() -> bytes:
+    """128-byte NCCL id created on rank 0; broadcast it to every rank before Context.dist_init."""
+    buf = C.create_string_buffer(128)
+    rc = load_library().vrgpu_dist_unique_id(buf)
+    if rc != 0:
+        raise VrgpuError(rc, "vrgpu_dist_unique_id failed (NCCL unavailable?)")
+    return buf.raw
 
 
 def search_opts(period, param1, halo_min_size=20, fofbgtype=5, ellhalo6dxfac=1.0, ellhalo6dvfac=1.25, bound_halos=0,
