@@ -15,6 +15,19 @@
 #include "stf.h"
 #include <chrono>
 
+#ifdef VRREF_USE_GPU
+/* libvrref_gpu.so: the SAME bridge, but the three entry points resolve to the B200 host adaptor
+ * (velociraptor-stf_b200/host/vrgpu_adaptor.cxx) instead of the reference's own bodies -- the drop-in exercised through the
+ * reference's real Options / NBody::Particle / StrucLevelData types. */
+Int_t *SearchFullSetGPU(Options &opt, const Int_t nbodies, vector<NBody::Particle> &Part, Int_t &numgroups);
+int CheckUnboundGroupsGPU(Options opt, const Int_t nbodies, NBody::Particle *Part, Int_t &ngroup, Int_t *&pfof, Int_t *numingroup = NULL,
+                          Int_t **pglist = NULL, int ireorder = 1, Int_t *groupflag = NULL);
+void PotentialGPU(Options &opt, Int_t nbodies, NBody::Particle *Part);
+#define SearchFullSet SearchFullSetGPU
+#define CheckUnboundGroups CheckUnboundGroupsGPU
+#define Potential PotentialGPU
+#endif
+
 using namespace std;
 using namespace NBody;
 

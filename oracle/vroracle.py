@@ -96,7 +96,7 @@ class Ref:
     """The reference itself (oracle/_ref/libvrref*.so)."""
 
     def __init__(self, variant: str = "serial"):
-        name = {"serial": "libvrref.so", "omp": "libvrref_omp.so", "pp": "libvrref_pp.so"}[variant]
+        name = {"serial": "libvrref.so", "omp": "libvrref_omp.so", "pp": "libvrref_pp.so", "gpu": "libvrref_gpu.so"}[variant]
         path = os.path.join(HERE, "_ref", name)
         if not os.path.exists(path):
             raise FileNotFoundError(path + " (run `make -C oracle ref` where /root/reference exists)")
@@ -117,7 +117,7 @@ class Ref:
 
     @staticmethod
     def available(variant: str = "serial") -> bool:
-        name = {"serial": "libvrref.so", "omp": "libvrref_omp.so", "pp": "libvrref_pp.so"}[variant]
+        name = {"serial": "libvrref.so", "omp": "libvrref_omp.so", "pp": "libvrref_pp.so", "gpu": "libvrref_gpu.so"}[variant]
         return os.path.exists(os.path.join(HERE, "_ref", name))
 
     def unbindnum(self) -> int:

@@ -1,0 +1,230 @@
+/* velociraptor-stf_b200/host/vrgpu_adaptor.cxx -- the reference-side host adaptor.
+ *
+ * Replacement bodies, with the reference's own signatures (src/proto.h:203,273,279), for the three entry points the
+ * B200 path takes over:
+ *
+ *     Int_t *SearchFullSet(Options&, const Int_t, vector<Particle>&, Int_t&)          src/search.cxx:24
+ *     int    CheckUnboundGroups(Options, const Int_t, Particle*, Int_t&, Int_t*&, ...)  src/unbind.cxx:196
+ *     void   Potential(Options&, Int_t, Particle*)                                      src/unbind.cxx:1607
+ *
+ * They marshal nothing: libvrgpu reads the caller's NBody::Particle array through a strided view (vrgpu_view).  This
+ * file is compiled against the reference's headers (stf.h) by whoever builds the reference with the GPU path; it is
+ * plain host C++ on top of the C ABI in include/vrgpu.h.  To avoid duplicate symbols when it is linked NEXT TO the
+ * reference's own search.cxx / unbind.cxx (as oracle/Makefile does for the parity test), the functions carry the
+ * suffix GPU unless VRGPU_REPLACE_REFERENCE_SYMBOLS is defined (INTEGRATION.md shows both ways).
+ *
+ * Error behaviour follows the reference: a message on cerr and exit(), e.g. src/search.cxx:503-517.
+ */
+#include "stf.h"
+
+#include "vrgpu.h"
+
+#include <cstddef>
+#include <cstring>
+
+#ifdef VRGPU_REPLACE_REFERENCE_SYMBOLS
+#define VRGPU_NAME(x) x
+#else
+#define VRGPU_NAME(x) x##GPU
+#endif
+
+using namespace std;
+using namespace NBody;
+
+static_assert(sizeof(Int_t) == sizeof(long long), "the GPU path needs the default LONGINT build (Int_t == long long)");
+static_assert(sizeof(Double_t) == sizeof(double), "the GPU path needs the default double precision build");
+
+namespace {
+
+vrgpu_ctx *g_ctx = NULL;
+
+[[noreturn]] void die(const char *what, int rc)
+{
+    cerr << "vrgpu: " << what << " failed (" << rc << "): " << (g_ctx ? vrgpu_last_error(g_ctx) : "no context") << endl;
+    exit(9);
+}
+
+vrgpu_ctx *context()
+{
+    if (g_ctx == NULL) {
+        int rc = vrgpu_init(-1, &g_ctx);
+        if (rc != VRGPU_OK) {
+            cerr << "vrgpu: no usable B200 / CUDA device (code " << rc << "); there is no CPU fallback in this build" << endl;
+            exit(9);
+        }
+    }
+    return g_ctx;
+}
+
+/* Field offsets of NBody::Particle, found by probing one object (mass and pid have no address-returning accessor). */
+struct Layout { size_t pos, vel, mass, pid; };
+const Layout &layout()
+{
+    static Layout L;
+    static bool done = false;
+    if (done) return L;
+    Particle p;
+    memset((void *)&p, 0, sizeof(Particle));
+    const unsigned char *base = reinterpret_cast<const unsigned char *>(&p);
+    L.pos = reinterpret_cast<const unsigned char *>(p.GetPosition()) - base;
+    L.vel = reinterpret_cast<const unsigned char *>(p.GetVelocity()) - base;
+    const double magic = 1.2345678901234567e77;
+    p.SetMass(magic);
+    p.SetPID((PARTPIDTYPE)0x5a5a5a5a1234567LL);
+    L.mass = L.pid = (size_t)-1;
+    for (size_t o = 0; o + 8 <= sizeof(Particle); o += 8) {
+        double d;
+        long long q;
+        memcpy(&d, base + o, 8);
+        memcpy(&q, base + o, 8);
+        if (d == magic) L.mass = o;
+        if (q == 0x5a5a5a5a1234567LL) L.pid = o;
+    }
+    if (L.mass == (size_t)-1 || L.pid == (size_t)-1 || sizeof(Particle) % 8 != 0) {
+        cerr << "vrgpu: unsupported NBody::Particle layout (SINGLEPRECISION / NOMASS / LOWPRECISIONPOS builds are not supported)" << endl;
+        exit(9);
+    }
+    done = true;
+    return L;
+}
+
+vrgpu_view view_of(const Particle *Part, Int_t n)
+{
+    const Layout &L = layout();
+    vrgpu_view v;
+    v.base = Part;
+    v.stride = sizeof(Particle);
+    v.off_pos = L.pos; v.off_vel = L.vel; v.off_mass = L.mass; v.off_pid = L.pid;
+    v.n = n;
+    return v;
+}
+
+vrgpu_unbind_opts unbind_opts_of(const Options &opt)
+{
+    vrgpu_unbind_opts u;
+    memset(&u, 0, sizeof u);
+    u.G = opt.G;
+    u.eps = opt.uinfo.eps;
+    u.Eratio = opt.uinfo.Eratio;
+    u.minEfrac = opt.uinfo.minEfrac;
+    u.unbindtype = opt.uinfo.unbindtype;
+    u.bgpot = opt.uinfo.bgpot;
+    u.fracpotref = opt.uinfo.fracpotref;
+    u.maxunbindfrac = opt.uinfo.maxunbindfrac;
+    u.maxunboundfracforiterativeunbind = opt.uinfo.maxunboundfracforiterativeunbind;
+    u.maxallowedunboundfrac = opt.uinfo.maxallowedunboundfrac;
+    u.theta = opt.uinfo.TreeThetaOpen;
+    u.bucket = opt.uinfo.BucketSize;
+    u.min_size = opt.MinSize;
+    u.pp_threshold = UNBINDNUM;   /* allvars.h:210 */
+    u.large_threshold = 1000;     /* ompunbindnum, ompvar.h:26 */
+    u.marginal_tol = 1e-6;
+    return u;
+}
+
+} // namespace
+
+/* SearchFullSet, DM-only path (src/search.cxx:24-854).  Same contract: returns new Int_t[nbodies] indexed by the
+ * particle's array index (caller delete[]s it, main.cxx:427), ids 1..numgroups by size, fills level 0 of the global
+ * psldata (search.cxx:64,740-760), leaves the particles in input order with grouped ones unwrapped across the period. */
+Int_t *VRGPU_NAME(SearchFullSet)(Options &opt, const Int_t nbodies, vector<Particle> &Part, Int_t &numgroups)
+{
+    if (opt.partsearchtype != PSTALL && opt.partsearchtype != PSTDARK) {
+        cerr << "vrgpu: only Particle_search_type all / dark matter is implemented on the GPU path" << endl;
+        exit(9);
+    }
+    if (opt.iKeepFOF && opt.fofbgtype <= FOF6D) {
+        cerr << "vrgpu: Keep_FOF with a 6DFOF field search is not implemented on the GPU path" << endl;
+        exit(9);
+    }
+    if (!(opt.fofbgtype == FOF3D || opt.fofbgtype == FOF6D || opt.fofbgtype == FOF6DADAPTIVE)) {
+        cerr << "vrgpu: FoF_Field_search_type must be 5 (3DFOF), 4 (6DFOF) or 3 (adaptive 6DFOF) on the GPU path" << endl;
+        exit(9);
+    }
+    vrgpu_search_opts so;
+    memset(&so, 0, sizeof so);
+    so.period = opt.p;
+    so.param1 = (opt.ellxscale * opt.ellxscale) * (opt.ellphys * opt.ellphys) * (opt.ellhalophysfac * opt.ellhalophysfac); /* search.cxx:77 */
+    so.halo_min_size = opt.HaloMinSize;
+    so.fofbgtype = opt.fofbgtype;
+    so.ellhalo6dxfac = opt.ellhalo6dxfac;
+    so.ellhalo6dvfac = opt.ellhalo6dvfac;
+    so.bound_halos = opt.iBoundHalos;
+    so.unbind = unbind_opts_of(opt);
+    Int_t *pfof = new Int_t[nbodies > 0 ? nbodies : 1];
+    long long ng = 0;
+    int rc = vrgpu_search_full_set(context(), view_of(Part.data(), nbodies), &so, reinterpret_cast<long long *>(pfof), &ng);
+    if (rc != VRGPU_OK) die("vrgpu_search_full_set", rc);
+    numgroups = ng;
+    /* the reference rewrites the scratch id field to the array index (KDTree construction, search.cxx:692-693) */
+    for (Int_t i = 0; i < nbodies; i++) Part[i].SetID(i);
+    /* hierarchy level 0 (search.cxx:64, 740-760) */
+    psldata = new StrucLevelData;
+    psldata->Allocate(numgroups);
+    psldata->Initialize();
+    for (Int_t i = 0; i < nbodies; i++) {
+        if (pfof[i] > 0 && psldata->gidhead[pfof[i]] == NULL) {
+            psldata->gidhead[pfof[i]] = &pfof[i];
+            psldata->Phead[pfof[i]] = &Part[i];
+            psldata->gidparenthead[pfof[i]] = &pfof[i];
+            psldata->giduberparenthead[pfof[i]] = &pfof[i];
+            psldata->stypeinlevel[pfof[i]] = HALOSTYPE;
+        }
+    }
+    psldata->stype = HALOSTYPE;
+    return pfof;
+}
+
+/* CheckUnboundGroups (src/unbind.cxx:196-304): pfof updated in place (0 = unbound), ids compacted / re-ordered when
+ * ireorder, ngroup updated, optional numingroup / pglist refreshed with the surviving members, returns 1 if anything
+ * changed.  The originals in Part are untouched, as in the reference (it works on copies). */
+int VRGPU_NAME(CheckUnboundGroups)(Options opt, const Int_t nbodies, Particle *Part, Int_t &ngroup, Int_t *&pfof, Int_t *numingroup,
+                                   Int_t **pglist, int ireorder, Int_t *groupflag)
+{
+    if (ireorder != 1) {
+        cerr << "vrgpu: CheckUnboundGroups with ireorder=0 is not implemented on the GPU path" << endl;
+        exit(9);
+    }
+    vrgpu_unbind_opts u = unbind_opts_of(opt);
+    const Int_t ngroup_in = ngroup;
+    long long ng = ngroup;
+    int changed = 0;
+    long long nmarginal = 0;
+    int rc = vrgpu_unbind(context(), view_of(Part, nbodies), reinterpret_cast<long long *>(pfof), &ng, &u, &changed, &nmarginal);
+    if (rc != VRGPU_OK) die("vrgpu_unbind", rc);
+    ngroup = ng;
+    if (numingroup != NULL) {
+        for (Int_t g = 0; g <= ngroup_in; g++) numingroup[g] = 0;
+        for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) numingroup[pfof[i]]++;
+    }
+    if (pglist != NULL && numingroup != NULL) {
+        /* lists are re-filled with the surviving indices (unbind.cxx:142-144); the caller's arrays are large enough
+         * because groups only shrink */
+        Int_t *fill = new Int_t[ngroup + 1];
+        for (Int_t g = 0; g <= ngroup; g++) fill[g] = 0;
+        for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) pglist[pfof[i]][fill[pfof[i]]++] = i;
+        delete[] fill;
+    }
+    if (groupflag != NULL) {
+        cerr << "vrgpu: groupflag is not carried through the GPU unbinding (ids are re-ordered)" << endl;
+        exit(9);
+    }
+    return changed;
+}
+
+/* Potential (src/unbind.cxx:1607-1741): kd-tree monopole potential of ONE set of particles, written to Part[j].phi. */
+void VRGPU_NAME(Potential)(Options &opt, Int_t nbodies, Particle *Part)
+{
+    if (nbodies <= 0) return;
+    long long offsets[2] = {0, nbodies};
+    long long *index = new long long[nbodies];
+    double *phi = new double[nbodies];
+    for (Int_t i = 0; i < nbodies; i++) index[i] = i;
+    /* Potential() always uses the tree: pp_threshold 0 sends every group with n > 0 to it */
+    int rc = vrgpu_potential(context(), view_of(Part, nbodies), 1, offsets, index, opt.G, opt.uinfo.eps, opt.uinfo.TreeThetaOpen,
+                             opt.uinfo.BucketSize, 0, phi);
+    if (rc != VRGPU_OK) die("vrgpu_potential", rc);
+    for (Int_t i = 0; i < nbodies; i++) Part[i].SetPotential(phi[i]);
+    delete[] phi;
+    delete[] index;
+}
