@@ -86,6 +86,7 @@ typedef struct {
     long long n_cells, n_groups3d, n_groups_final, n_grouped, n_pairs_potential, n_marginal;
     long long h2d_bytes, d2h_bytes, kernel_launches;
     long long n_tree_interactions, n_tree_nodes; /* kd-tree potential: cell + leaf-particle interactions, nodes built */
+    long long n_link_queue;                      /* 3DFOF: dense cell pairs finished by the warp-per-pair kernel */
 } vrgpu_stats;
 
 /* Create / destroy a context on CUDA device `device` (-1 = current device). */

@@ -141,6 +141,85 @@ __device__ __forceinline__ bool pair_links(double ax, double ay, double az, doub
     return d2 < b2;
 }
 
+// Try to unite cell `cell` (particles [a0,a1), grid coordinates ix,iy,iz) with neighbour cell B reached through the cell
+// offset (ddx,ddy,ddz); sc packs the periodic image code (s+1 per axis, 2 bits each).  Whole warp cooperates; stops at the
+// first linking pair.
+__device__ __forceinline__ void try_link_cells(const LinkParams &P, const uint32_t cell, const uint32_t a0, const uint32_t a1, const int ix,
+                                               const int iy, const int iz, const uint32_t B, const int ddx, const int ddy, const int ddz,
+                                               const int sc, const unsigned lane)
+{
+    const uint32_t na = a1 - a0;
+    uint32_t ra = 0, rb = 0;
+    if (lane == 0) { ra = uf_find(P.parent, cell); rb = uf_find(P.parent, B); }
+    ra = __shfl_sync(0xffffffffu, ra, 0);
+    rb = __shfl_sync(0xffffffffu, rb, 0);
+    if (ra == rb) return;
+    const double shx = (double)((sc & 3) - 1) * P.period, shy = (double)(((sc >> 2) & 3) - 1) * P.period,
+                 shz = (double)(((sc >> 4) & 3) - 1) * P.period;
+    const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
+    const uint32_t b0 = P.cell_start[B], b1 = P.cell_start[B + 1];
+    const uint32_t nbp = b1 - b0;
+    bool linked = false;
+    const uint64_t npairs = (uint64_t)na * nbp;
+    if (npairs <= 4096) {
+        for (uint32_t p0 = 0; p0 < (uint32_t)npairs && !linked; p0 += 32) {
+            uint32_t p = p0 + lane;
+            bool hit = false;
+            if (p < (uint32_t)npairs) {
+                uint32_t ia = a0 + p / nbp, ib = b0 + p % nbp;
+                double ax = P.sx[ia], ay = P.sy[ia], az = P.sz[ia];
+                double bx = P.sx[ib], by = P.sy[ib], bz = P.sz[ib];
+                if (!wrapped) hit = pair_links(ax, ay, az, bx, by, bz, P.b2);
+                else
+                    hit = pair_links(__dadd_rn(ax, shx), __dadd_rn(ay, shy), __dadd_rn(az, shz), bx, by, bz, P.b2) ||
+                          pair_links(__dsub_rn(bx, shx), __dsub_rn(by, shy), __dsub_rn(bz, shz), ax, ay, az, P.b2);
+            }
+            linked = __any_sync(0xffffffffu, hit);
+        }
+    } else {
+        // big cell pair: only particles of A whose distance to B's box is below b can link
+        const double blox = P.lox + (double)(ix + ddx) * P.cx, bloy = P.loy + (double)(iy + ddy) * P.cy,
+                     bloz = P.loz + (double)(iz + ddz) * P.cz;
+        const double margin = 1e-6 * P.cx;
+        const double b2m = P.b2 * (1.0 + 1e-6);
+        for (uint32_t abase = a0; abase < a1 && !linked; abase += 32) {
+            uint32_t ia = abase + lane;
+            double ax = 0, ay = 0, az = 0;
+            bool near = false;
+            if (ia < a1) {
+                ax = P.sx[ia]; ay = P.sy[ia]; az = P.sz[ia];
+                double gx = ddx > 0 ? blox - ax : (ddx < 0 ? ax - (blox + P.cx) : 0.0);
+                double gy = ddy > 0 ? bloy - ay : (ddy < 0 ? ay - (bloy + P.cy) : 0.0);
+                double gz = ddz > 0 ? bloz - az : (ddz < 0 ? az - (bloz + P.cz) : 0.0);
+                gx = fmax(gx - margin, 0.0); gy = fmax(gy - margin, 0.0); gz = fmax(gz - margin, 0.0);
+                near = gx * gx + gy * gy + gz * gz < b2m;
+            }
+            unsigned nm = __ballot_sync(0xffffffffu, near);
+            while (nm && !linked) {
+                const int s = __ffs(nm) - 1;
+                nm &= nm - 1;
+                const double tx = __shfl_sync(0xffffffffu, ax, s), ty = __shfl_sync(0xffffffffu, ay, s),
+                             tz = __shfl_sync(0xffffffffu, az, s);
+                const double txs = __dadd_rn(tx, shx), tys = __dadd_rn(ty, shy), tzs = __dadd_rn(tz, shz);
+                for (uint32_t bb = b0; bb < b1 && !linked; bb += 32) {
+                    uint32_t ib = bb + lane;
+                    bool hit = false;
+                    if (ib < b1) {
+                        double bx = P.sx[ib], by = P.sy[ib], bz = P.sz[ib];
+                        if (!wrapped) hit = pair_links(tx, ty, tz, bx, by, bz, P.b2);
+                        else
+                            hit = pair_links(txs, tys, tzs, bx, by, bz, P.b2) ||
+                                  pair_links(__dsub_rn(bx, shx), __dsub_rn(by, shy), __dsub_rn(bz, shz), tx, ty, tz, P.b2);
+                    }
+                    linked = __any_sync(0xffffffffu, hit);
+                }
+            }
+        }
+    }
+    if (linked && lane == 0) uf_union(P.parent, cell, B);
+    __syncwarp();
+}
+
 // One warp per cell.  off_begin/off_end select the slice of the 62 half-space offsets handled by this launch:
 // the 13 face/edge/corner neighbours first, the 49 second-shell ones afterwards (by then most are already united).
 __global__ void __launch_bounds__(256) k_link_cells(LinkParams P, int off_begin, int off_end)
@@ -187,77 +266,241 @@ __global__ void __launch_bounds__(256) k_link_cells(LinkParams P, int off_begin,
                 const int sc = __shfl_sync(0xffffffffu, scode, src);
                 const int ddx = __shfl_sync(0xffffffffu, dx, src), ddy = __shfl_sync(0xffffffffu, dy, src),
                           ddz = __shfl_sync(0xffffffffu, dz, src);
-                uint32_t ra = 0, rb = 0;
-                if (lane == 0) { ra = uf_find(P.parent, cell); rb = uf_find(P.parent, B); }
-                ra = __shfl_sync(0xffffffffu, ra, 0);
-                rb = __shfl_sync(0xffffffffu, rb, 0);
-                if (ra == rb) continue;
-                const double shx = (double)((sc & 3) - 1) * P.period, shy = (double)(((sc >> 2) & 3) - 1) * P.period,
-                             shz = (double)(((sc >> 4) & 3) - 1) * P.period;
-                const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
-                const uint32_t b0 = P.cell_start[B], b1 = P.cell_start[B + 1];
-                const uint32_t nbp = b1 - b0;
-                bool linked = false;
-                const uint64_t npairs = (uint64_t)na * nbp;
-                if (npairs <= 4096) {
-                    for (uint32_t p0 = 0; p0 < (uint32_t)npairs && !linked; p0 += 32) {
-                        uint32_t p = p0 + lane;
-                        bool hit = false;
-                        if (p < (uint32_t)npairs) {
-                            uint32_t ia = a0 + p / nbp, ib = b0 + p % nbp;
-                            double ax = P.sx[ia], ay = P.sy[ia], az = P.sz[ia];
-                            double bx = P.sx[ib], by = P.sy[ib], bz = P.sz[ib];
-                            if (!wrapped) hit = pair_links(ax, ay, az, bx, by, bz, P.b2);
-                            else
-                                hit = pair_links(__dadd_rn(ax, shx), __dadd_rn(ay, shy), __dadd_rn(az, shz), bx, by, bz, P.b2) ||
-                                      pair_links(__dsub_rn(bx, shx), __dsub_rn(by, shy), __dsub_rn(bz, shz), ax, ay, az, P.b2);
-                        }
-                        linked = __any_sync(0xffffffffu, hit);
-                    }
-                } else {
-                    // big cell pair: only particles of A whose distance to B's box is below b can link
-                    const double blox = P.lox + (double)(ix + ddx) * P.cx, bloy = P.loy + (double)(iy + ddy) * P.cy,
-                                 bloz = P.loz + (double)(iz + ddz) * P.cz;
-                    const double margin = 1e-6 * P.cx;
-                    const double b2m = P.b2 * (1.0 + 1e-6);
-                    for (uint32_t abase = a0; abase < a1 && !linked; abase += 32) {
-                        uint32_t ia = abase + lane;
-                        double ax = 0, ay = 0, az = 0;
-                        bool near = false;
-                        if (ia < a1) {
-                            ax = P.sx[ia]; ay = P.sy[ia]; az = P.sz[ia];
-                            double gx = ddx > 0 ? blox - ax : (ddx < 0 ? ax - (blox + P.cx) : 0.0);
-                            double gy = ddy > 0 ? bloy - ay : (ddy < 0 ? ay - (bloy + P.cy) : 0.0);
-                            double gz = ddz > 0 ? bloz - az : (ddz < 0 ? az - (bloz + P.cz) : 0.0);
-                            gx = fmax(gx - margin, 0.0); gy = fmax(gy - margin, 0.0); gz = fmax(gz - margin, 0.0);
-                            near = gx * gx + gy * gy + gz * gz < b2m;
-                        }
-                        unsigned nm = __ballot_sync(0xffffffffu, near);
-                        while (nm && !linked) {
-                            const int s = __ffs(nm) - 1;
-                            nm &= nm - 1;
-                            const double tx = __shfl_sync(0xffffffffu, ax, s), ty = __shfl_sync(0xffffffffu, ay, s),
-                                         tz = __shfl_sync(0xffffffffu, az, s);
-                            const double txs = __dadd_rn(tx, shx), tys = __dadd_rn(ty, shy), tzs = __dadd_rn(tz, shz);
-                            for (uint32_t bb = b0; bb < b1 && !linked; bb += 32) {
-                                uint32_t ib = bb + lane;
-                                bool hit = false;
-                                if (ib < b1) {
-                                    double bx = P.sx[ib], by = P.sy[ib], bz = P.sz[ib];
-                                    if (!wrapped) hit = pair_links(tx, ty, tz, bx, by, bz, P.b2);
-                                    else
-                                        hit = pair_links(txs, tys, tzs, bx, by, bz, P.b2) ||
-                                              pair_links(__dsub_rn(bx, shx), __dsub_rn(by, shy), __dsub_rn(bz, shz), tx, ty, tz, P.b2);
-                                }
-                                linked = __any_sync(0xffffffffu, hit);
-                            }
-                        }
-                    }
-                }
-                if (linked && lane == 0) uf_union(P.parent, cell, B);
-                __syncwarp();
+                try_link_cells(P, cell, a0, a1, ix, iy, iz, B, ddx, ddy, ddz, sc, lane);
             }
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// row-table linker.  Cells are sorted by key = (iz*ncy + iy)*ncx + ix, so the cells of one (iy,iz) ROW are contiguous
+// and ordered by ix.  A dense table row -> [first,last) cell (4 B x 2 per row; 39 MB at 256^3, L2 resident) turns the 62
+// neighbour-cell hash probes of a cell into 12 row look-ups + short scans (the 5 x-neighbours of a row are adjacent).
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t ROW_NONE = 0xffffffffu;
+
+__global__ void k_row_table(const uint64_t *__restrict__ cell_key, uint32_t ncells, uint64_t ncx, uint32_t *__restrict__ row_first,
+                            uint32_t *__restrict__ row_last)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const uint64_t r = cell_key[c] / ncx;
+    if (c == 0 || cell_key[c - 1] / ncx != r) row_first[r] = c;
+    if (c == ncells - 1 || cell_key[c + 1] / ncx != r) row_last[r] = c + 1;
+}
+
+// reach = 1: only the 13 adjacent half-space cells (cheap first pass that unites most of a halo), reach = 2: all 62.
+__global__ void __launch_bounds__(256) k_link_rows(LinkParams P, const uint32_t *__restrict__ row_first, const uint32_t *__restrict__ row_last,
+                                                   int reach)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t warps_total = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t ncx = (uint64_t)P.ncx;
+    for (uint32_t cell = warp_global; cell < P.ncells; cell += warps_total) {
+        const uint64_t key = P.cell_key[cell];
+        const uint64_t row = key / ncx;
+        const int ix = (int)(key - row * ncx);
+        const int iz = (int)(row / (uint64_t)P.ncy);
+        const int iy = (int)(row - (uint64_t)iz * (uint64_t)P.ncy);
+        const uint32_t a0 = P.cell_start[cell], a1 = P.cell_start[cell + 1];
+        // lane -> (role, segment): role 0..11 = neighbour rows of the half space, role 12 = own row (dx > 0);
+        // segment 0 = the part of the x-interval inside [0,ncx), segment 1 = the part that wraps (periodic x only)
+        const int role = (int)(lane & 15), seg = (int)(lane >> 4);
+        int dy = 0, dz = 0;
+        bool ok = role <= 12;
+        if (role < 5) { dz = 1; dy = role - 2; }
+        else if (role < 10) { dz = 2; dy = role - 7; }
+        else if (role < 12) { dz = 0; dy = role - 9; }
+        if (ok && (abs(dy) > reach || dz > reach)) ok = false;
+        int xlo = role == 12 ? ix + 1 : ix - reach, xhi = ix + reach; // unwrapped x-interval
+        int xoff = 0, sx = 0, sy = 0, sz = 0;
+        if (ok) {
+            if (seg == 0) { xlo = max(xlo, 0); xhi = min(xhi, P.ncx - 1); }
+            else if (!P.perx) ok = false;
+            else if (xlo < 0) { xhi = min(xhi, -1) + P.ncx; xlo += P.ncx; xoff = -P.ncx; sx = 1; }
+            else if (xhi >= P.ncx) { xlo = max(xlo, P.ncx) - P.ncx; xhi -= P.ncx; xoff = P.ncx; sx = -1; }
+            else ok = false;
+            if (xlo > xhi) ok = false;
+        }
+        int ny = iy + dy, nz = iz + dz;
+        if (ok) {
+            if (ny < 0) { if (P.pery) { ny += P.ncy; sy = 1; } else ok = false; }
+            else if (ny >= P.ncy) { if (P.pery) { ny -= P.ncy; sy = -1; } else ok = false; }
+            if (nz >= P.ncz) { if (P.perz) { nz -= P.ncz; sz = -1; } else ok = false; }
+        }
+        uint32_t c0 = 0, c1 = 0;
+        uint64_t rowbase = 0;
+        if (ok) {
+            const uint64_t r = (uint64_t)nz * (uint64_t)P.ncy + (uint64_t)ny;
+            rowbase = r * ncx;
+            uint32_t f = row_first[r];
+            if (f != ROW_NONE) {
+                uint32_t l = row_last[r];
+                const uint64_t klo = rowbase + (uint64_t)xlo, khi = rowbase + (uint64_t)xhi;
+                if (role == 12 && seg == 0) f = cell + 1; // own row, forward: the next cells in the array
+                else {
+                    // lower bound of klo in cell_key[f, l)
+                    uint32_t lo = f, hi = l;
+                    while (lo < hi) {
+                        uint32_t mid = (lo + hi) >> 1;
+                        if (__ldg(&P.cell_key[mid]) < klo) lo = mid + 1; else hi = mid;
+                    }
+                    f = lo;
+                }
+                uint32_t e = f;
+                while (e < l && __ldg(&P.cell_key[e]) <= khi) e++;
+                c0 = f; c1 = e;
+            }
+        }
+        const int scode = (sx + 1) | ((sy + 1) << 2) | ((sz + 1) << 4);
+        unsigned has = __ballot_sync(0xffffffffu, c0 < c1);
+        while (has) {
+            const int src = __ffs(has) - 1;
+            const uint32_t B = __shfl_sync(0xffffffffu, c0, src);
+            const int sc = __shfl_sync(0xffffffffu, scode, src);
+            const int ddy = __shfl_sync(0xffffffffu, dy, src), ddz = __shfl_sync(0xffffffffu, dz, src);
+            const int xo = __shfl_sync(0xffffffffu, xoff, src);
+            const unsigned long long rb = __shfl_sync(0xffffffffu, (unsigned long long)rowbase, src);
+            const int ddx = (int)(P.cell_key[B] - rb) + xo - ix;
+            if ((int)lane == src) c0++;
+            try_link_cells(P, cell, a0, a1, ix, iy, iz, B, ddx, ddy, ddz, sc, lane);
+            has = __ballot_sync(0xffffffffu, c0 < c1);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// thread-per-cell linker.  Most non-empty cells of a cosmological box hold ONE particle and have no neighbour at all, so a
+// warp per cell spends hundreds of instructions on bookkeeping for nothing (ncu, profiles/r01b: 5.8e9 warp instructions,
+// 1 % of them fp64).  Here every THREAD owns a cell: it walks its 12 neighbour rows + its own row through the row table,
+// and for every neighbour cell in a different set it tests up to 16 pairs inline (enough for sparse cells and for most
+// dense neighbours, which link at the first try); only cell pairs that are still undecided go to a queue that a
+// warp-per-pair kernel finishes with the exhaustive test.
+// ---------------------------------------------------------------------------------------------------
+struct LinkQueue {
+    uint32_t *a, *b, *meta;     // meta: sc (6 bits) | (ddx+2)<<6 | (ddy+2)<<9 | (ddz+2)<<12
+    unsigned int *count;
+    uint32_t capacity;
+};
+
+__global__ void k_cell_coords(const uint64_t *__restrict__ cell_key, uint32_t ncells, uint64_t ncx, uint32_t *__restrict__ cell_row,
+                              int *__restrict__ cell_ix, uint32_t *__restrict__ row_first, uint32_t *__restrict__ row_last)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const uint64_t key = cell_key[c];
+    const uint64_t r = key / ncx;
+    cell_row[c] = (uint32_t)r;
+    cell_ix[c] = (int)(key - r * ncx);
+    if (c == 0 || cell_key[c - 1] / ncx != r) row_first[r] = c;
+    if (c == ncells - 1 || cell_key[c + 1] / ncx != r) row_last[r] = c + 1;
+}
+
+__global__ void __launch_bounds__(128) k_link_thread(LinkParams P, const uint32_t *__restrict__ cell_row, const int *__restrict__ cell_ix,
+                                                     const uint32_t *__restrict__ row_first, const uint32_t *__restrict__ row_last, int reach,
+                                                     LinkQueue Q)
+{
+    const uint32_t cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= P.ncells) return;
+    const uint32_t row = cell_row[cell];
+    const int ix = cell_ix[cell];
+    const int iz = (int)(row / (uint32_t)P.ncy);
+    const int iy = (int)(row - (uint32_t)iz * (uint32_t)P.ncy);
+    const uint32_t a0 = P.cell_start[cell], a1 = P.cell_start[cell + 1];
+    const uint32_t na = a1 - a0;
+    uint32_t ra = uf_find(P.parent, cell);
+    // own row first (dx > 0), then dz = 0 / dy > 0, then dz = 1, 2
+    for (int role = 0; role < 13; role++) {
+        int dy, dz;
+        if (role == 0) { dy = 0; dz = 0; }
+        else if (role < 3) { dz = 0; dy = role; }
+        else if (role < 8) { dz = 1; dy = role - 5; }
+        else { dz = 2; dy = role - 10; }
+        if (abs(dy) > reach || dz > reach) continue;
+        int ny = iy + dy, nz = iz + dz, sy = 0, sz = 0;
+        if (ny < 0) { if (!P.pery) continue; ny += P.ncy; sy = 1; }
+        else if (ny >= P.ncy) { if (!P.pery) continue; ny -= P.ncy; sy = -1; }
+        if (nz >= P.ncz) { if (!P.perz) continue; nz -= P.ncz; sz = -1; }
+        const uint32_t r = (uint32_t)nz * (uint32_t)P.ncy + (uint32_t)ny;
+        const uint32_t rf = row_first[r];
+        if (rf == ROW_NONE) continue;
+        const uint32_t rl = row_last[r];
+        const int x0 = role == 0 ? ix + 1 : ix - reach, x1 = ix + reach; // unwrapped interval
+        for (int seg = 0; seg < 2; seg++) {
+            int xlo = x0, xhi = x1, xoff = 0, sx = 0;
+            if (seg == 0) { xlo = max(xlo, 0); xhi = min(xhi, P.ncx - 1); }
+            else {
+                if (!P.perx) break;
+                if (x0 < 0) { xhi = min(x1, -1) + P.ncx; xlo = x0 + P.ncx; xoff = -P.ncx; sx = 1; }
+                else if (x1 >= P.ncx) { xlo = max(x0, P.ncx) - P.ncx; xhi = x1 - P.ncx; xoff = P.ncx; sx = -1; }
+                else break;
+            }
+            if (xlo > xhi) continue;
+            uint32_t c;
+            if (role == 0 && seg == 0) c = cell + 1;
+            else {
+                uint32_t lo = rf, hi = rl;
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (__ldg(&cell_ix[mid]) < xlo) lo = mid + 1; else hi = mid;
+                }
+                c = lo;
+            }
+            const int sc = (sx + 1) | ((sy + 1) << 2) | ((sz + 1) << 4);
+            const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
+            const double shx = (double)sx * P.period, shy = (double)sy * P.period, shz = (double)sz * P.period;
+            for (; c < rl; c++) {
+                const int bx = __ldg(&cell_ix[c]);
+                if (bx > xhi) break;
+                const uint32_t B = c;
+                const uint32_t rb = uf_find(P.parent, B);
+                if (rb == ra) continue;
+                const uint32_t b0 = P.cell_start[B], b1 = P.cell_start[B + 1];
+                const uint32_t nb = b1 - b0;
+                // inline trial: all pairs when there are few, else the first 4 x 4
+                const uint32_t ta = na * nb <= 16u ? na : min(na, 4u), tb = na * nb <= 16u ? nb : min(nb, 4u);
+                bool linked = false;
+                for (uint32_t i = 0; i < ta && !linked; i++) {
+                    const double ax = P.sx[a0 + i], ay = P.sy[a0 + i], az = P.sz[a0 + i];
+                    for (uint32_t j = 0; j < tb && !linked; j++) {
+                        const double qx = P.sx[b0 + j], qy = P.sy[b0 + j], qz = P.sz[b0 + j];
+                        if (!wrapped) linked = pair_links(ax, ay, az, qx, qy, qz, P.b2);
+                        else
+                            linked = pair_links(__dadd_rn(ax, shx), __dadd_rn(ay, shy), __dadd_rn(az, shz), qx, qy, qz, P.b2) ||
+                                     pair_links(__dsub_rn(qx, shx), __dsub_rn(qy, shy), __dsub_rn(qz, shz), ax, ay, az, P.b2);
+                    }
+                }
+                if (linked) {
+                    uf_union(P.parent, cell, B);
+                    ra = uf_find(P.parent, cell);
+                } else if (na * nb > 16u) {
+                    const unsigned int slot = atomicAdd(Q.count, 1u);
+                    if (slot < Q.capacity) {
+                        Q.a[slot] = cell;
+                        Q.b[slot] = B;
+                        Q.meta[slot] = (uint32_t)sc | ((uint32_t)(bx + xoff - ix + 2) << 6) | ((uint32_t)(dy + 2) << 9) | ((uint32_t)(dz + 2) << 12);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// one warp per undecided cell pair: the exhaustive test
+__global__ void __launch_bounds__(256) k_link_queue(LinkParams P, const uint32_t *__restrict__ cell_row, const int *__restrict__ cell_ix,
+                                                    LinkQueue Q, uint32_t nq)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t warps_total = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < nq; e += warps_total) {
+        const uint32_t cell = Q.a[e], B = Q.b[e], m = Q.meta[e];
+        const uint32_t row = cell_row[cell];
+        const int ix = cell_ix[cell];
+        const int iz = (int)(row / (uint32_t)P.ncy);
+        const int iy = (int)(row - (uint32_t)iz * (uint32_t)P.ncy);
+        try_link_cells(P, cell, P.cell_start[cell], P.cell_start[cell + 1], ix, iy, iz, B, (int)((m >> 6) & 7) - 2, (int)((m >> 9) & 7) - 2,
+                       (int)((m >> 12) & 7) - 2, (int)(m & 63), lane);
     }
 }
 
@@ -525,12 +768,19 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
     DBuf<uint32_t> parent(ctx, ncells);
     {
         StageTimer t(ctx);
+        const uint64_t nrows = (uint64_t)g.nc[1] * (uint64_t)g.nc[2];
+        const bool use_rows = nrows <= (1ull << 29);
         size_t h = 1;
-        while (h < 2 * (size_t)ncells) h <<= 1;
+        if (!use_rows) while (h < 2 * (size_t)ncells) h <<= 1;
         DBuf<uint64_t> hkeys(ctx, h);
         DBuf<uint32_t> hvals(ctx, h);
-        { KScope k(ctx, "fof3d.hash_build"); VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
-        VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), parent.p); }
+        if (use_rows) {
+            VR_LAUNCH(ctx, k_uf_init, grid_for(ncells, T), T, 0, parent.p, ncells);
+        } else {
+            KScope k(ctx, "fof3d.hash_build");
+            VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
+            VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), parent.p);
+        }
         LinkParams L{};
         L.sx = S.sx.p; L.sy = S.sy.p; L.sz = S.sz.p;
         L.cell_start = S.cell_start.p; L.cell_key = S.cell_key.p; L.ncells = ncells;
@@ -544,8 +794,38 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
         unsigned warps_needed = ncells;
         unsigned blocks = std::min<unsigned>((warps_needed + 7) / 8, (unsigned)ctx->sm_count * 32u);
         blocks = std::max(blocks, 1u);
-        { KScope k(ctx, "fof3d.link_cells"); VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 0, 13);
-        VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 13, 62); }
+        if (use_rows) {
+            // dense row table (L2 resident at 256^3) + thread-per-cell linking, undecided dense pairs finished by warps
+            DBuf<uint32_t> row_first(ctx, nrows), row_last(ctx, nrows), cell_row(ctx, ncells);
+            DBuf<int> cell_ix(ctx, ncells);
+            const uint32_t qcap = (uint32_t)std::min<size_t>((size_t)8 * ncells + 1024, (size_t)0x7fffffff);
+            DBuf<uint32_t> qa(ctx, qcap), qb(ctx, qcap), qm(ctx, qcap);
+            DBuf<unsigned int> qcount(ctx, 1);
+            LinkQueue Q{qa.p, qb.p, qm.p, qcount.p, qcap};
+            KScope k(ctx, "fof3d.link_cells");
+            VR_CUDA(cudaMemsetAsync(row_first.p, 0xff, sizeof(uint32_t) * nrows, ctx->stream));
+            VR_LAUNCH(ctx, k_cell_coords, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, (uint64_t)g.nc[0], cell_row.p, cell_ix.p, row_first.p,
+                      row_last.p);
+            for (int reach = 1; reach <= 2; reach++) {
+                VR_CUDA(cudaMemsetAsync(qcount.p, 0, sizeof(unsigned int), ctx->stream));
+                VR_LAUNCH(ctx, k_link_thread, grid_for(ncells, 128), 128, 0, L, cell_row.p, cell_ix.p, row_first.p, row_last.p, reach, Q);
+                unsigned int nq = 0;
+                VR_CUDA(cudaMemcpyAsync(&nq, qcount.p, sizeof(nq), cudaMemcpyDeviceToHost, ctx->stream));
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                if (nq > qcap) {
+                    // queue overflow (pathological density): the warp-per-cell kernel redoes this reach exhaustively
+                    VR_LAUNCH(ctx, k_link_rows, blocks, 256, 0, L, row_first.p, row_last.p, reach);
+                } else if (nq) {
+                    const unsigned qblocks = std::max(1u, std::min<unsigned>((nq + 7) / 8, (unsigned)ctx->sm_count * 32u));
+                    VR_LAUNCH(ctx, k_link_queue, qblocks, 256, 0, L, cell_row.p, cell_ix.p, Q, nq);
+                }
+                ctx->stats.n_link_queue += nq;
+            }
+        } else {
+            KScope k(ctx, "fof3d.link_cells");
+            VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 0, 13);
+            VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 13, 62);
+        }
         S.root.alloc(ctx, ncells);
         { KScope k(ctx, "fof3d.flatten"); VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); }
         ctx->stats.link_ms += t.stop();

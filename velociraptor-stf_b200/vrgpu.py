@@ -60,7 +60,7 @@ class Stats(C.Structure):
                                           "unbind_ms", "d2h_ms", "total_ms")] + \
                [(k, C.c_longlong) for k in ("n_cells", "n_groups3d", "n_groups_final", "n_grouped",
                                             "n_pairs_potential", "n_marginal", "h2d_bytes", "d2h_bytes",
-                                            "kernel_launches", "n_tree_interactions", "n_tree_nodes")]
+                                            "kernel_launches", "n_tree_interactions", "n_tree_nodes", "n_link_queue")]
 
     def asdict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
