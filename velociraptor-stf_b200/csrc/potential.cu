@@ -11,14 +11,19 @@
 
 namespace vrgpu {
 
-constexpr int PT = 256;
+constexpr int PT = 256; // threads per CTA
+constexpr int PI = 4;   // slots per thread (register tiling: every shared-memory j serves PI pair evaluations)
+constexpr int PS = PT * PI;
 
+// 1/sqrt(r2): hardware seed (rsqrt.approx.f64 = MUFU.RSQ64H on the high word, ~2^-22) + one fp64 Newton step (4 DP
+// instructions, relative error ~1e-13); zero / denormal / huge arguments take the exact path (inf for r2 == 0, like the
+// reference).
 __device__ __forceinline__ double rsqrt_refined(double r2)
 {
-    float f = (float)r2;
-    double y = (double)rsqrtf(f);
-    if (!(f > 0.0f) || !(f < 3.0e38f)) return 1.0 / sqrt(r2); // zero / denormal / huge: exact path (inf for r2 == 0, like the reference)
-    double h = 0.5 * r2;
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(r2));
+    if (!(r2 > 1e-290) || !(r2 < 1e290)) return 1.0 / sqrt(r2);
+    const double h = 0.5 * r2;
     y = y * (1.5 - h * y * y);
     return y;
 }
@@ -28,54 +33,69 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
                                                          const uint32_t *__restrict__ off, uint32_t ntot, double G, double eps2,
                                                          long long pp_threshold, double *__restrict__ phi)
 {
-    __shared__ double sx[PT], sy[PT], sz[PT], sm[PT];
+    __shared__ double2 sxy[PT], szm[PT]; // 16-byte shared loads: two per j instead of four
     __shared__ uint32_t sg[PT];
-    const uint32_t s_first = blockIdx.x * PT;
-    const uint32_t s = s_first + threadIdx.x;
-    const uint32_t s_last = min(ntot, s_first + PT) - 1;
-    const bool active = s < ntot;
-    uint32_t g = 0;
-    double xi = 0, yi = 0, zi = 0, mi = 0;
-    bool mine = false;
-    if (active) {
-        g = gid[s];
-        xi = x[s]; yi = y[s]; zi = z[s]; mi = m[s];
-        uint32_t sz_g = off[g + 1] - off[g];
-        mine = pp_threshold < 0 || (long long)sz_g <= pp_threshold;
+    const uint32_t s_first = blockIdx.x * PS;
+    const uint32_t s_last = min(ntot, s_first + PS) - 1;
+    uint32_t s[PI], g[PI];
+    double xi[PI], yi[PI], zi[PI], mi[PI], acc[PI];
+    bool mine[PI];
+    bool any_mine = false;
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        s[k] = s_first + k * PT + threadIdx.x;
+        g[k] = 0; xi[k] = yi[k] = zi[k] = mi[k] = 0; acc[k] = 0; mine[k] = false;
+        if (s[k] < ntot) {
+            g[k] = gid[s[k]];
+            xi[k] = x[s[k]]; yi[k] = y[s[k]]; zi[k] = z[s[k]]; mi[k] = m[s[k]];
+            const uint32_t sz_g = off[g[k] + 1] - off[g[k]];
+            mine[k] = pp_threshold < 0 || (long long)sz_g <= pp_threshold;
+        }
+        any_mine = any_mine || mine[k];
     }
-    if (!__syncthreads_or(mine)) return;
+    if (!__syncthreads_or(any_mine)) return;
     const uint32_t g_first = gid[s_first], g_last = gid[s_last];
     const uint32_t j0 = off[g_first], j1 = off[g_last + 1];
-    const bool uniform = g_first == g_last;
-    double acc = 0.0;
+    const bool uniform = g_first == g_last; // the whole CTA sits inside one group (implies every slot is `mine`)
     for (uint32_t jb = j0; jb < j1; jb += PT) {
-        uint32_t j = jb + threadIdx.x;
-        if (j < j1) { sx[threadIdx.x] = x[j]; sy[threadIdx.x] = y[j]; sz[threadIdx.x] = z[j]; sm[threadIdx.x] = m[j]; sg[threadIdx.x] = gid[j]; }
-        else { sg[threadIdx.x] = 0; sm[threadIdx.x] = 0; sx[threadIdx.x] = 0; sy[threadIdx.x] = 0; sz[threadIdx.x] = 0; }
+        const uint32_t j = jb + threadIdx.x;
+        if (j < j1) { sxy[threadIdx.x] = make_double2(x[j], y[j]); szm[threadIdx.x] = make_double2(z[j], m[j]); sg[threadIdx.x] = gid[j]; }
+        else { sg[threadIdx.x] = 0; sxy[threadIdx.x] = make_double2(0, 0); szm[threadIdx.x] = make_double2(0, 0); }
         __syncthreads();
-        if (mine) {
-            const int cnt = (int)min((uint32_t)PT, j1 - jb);
-            if (uniform) {
+        const int cnt = (int)min((uint32_t)PT, j1 - jb);
+        // a tile that holds none of this CTA's own slots needs no self-exclusion test at all
+        const bool has_self = jb < s_first + PS && jb + PT > s_first;
+        if (uniform && !has_self) {
 #pragma unroll 4
-                for (int jj = 0; jj < cnt; jj++) {
-                    double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
-                    double r2 = dx * dx + dy * dy + dz * dz + eps2;
-                    double w = (jb + jj != s) ? sm[jj] : 0.0;
-                    double ri = (jb + jj != s) ? rsqrt_refined(r2) : 0.0;
-                    acc += w * ri;
+            for (int jj = 0; jj < cnt; jj++) {
+                const double2 qa = sxy[jj], qb = szm[jj];
+                const double qx = qa.x, qy = qa.y, qz = qb.x, qm = qb.y;
+#pragma unroll
+                for (int k = 0; k < PI; k++) {
+                    const double dx = xi[k] - qx, dy = yi[k] - qy, dz = zi[k] - qz;
+                    const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+                    acc[k] = fma(qm, rsqrt_refined(r2), acc[k]);
                 }
-            } else {
-                for (int jj = 0; jj < cnt; jj++) {
-                    if (sg[jj] != g || jb + jj == s) continue;
-                    double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
-                    double r2 = dx * dx + dy * dy + dz * dz + eps2;
-                    acc += sm[jj] * rsqrt_refined(r2);
+            }
+        } else {
+            for (int jj = 0; jj < cnt; jj++) {
+                const double2 qa = sxy[jj], qb = szm[jj];
+                const double qx = qa.x, qy = qa.y, qz = qb.x, qm = qb.y;
+                const uint32_t qg = sg[jj];
+#pragma unroll
+                for (int k = 0; k < PI; k++) {
+                    if (!mine[k] || qg != g[k] || jb + jj == s[k]) continue;
+                    const double dx = xi[k] - qx, dy = yi[k] - qy, dz = zi[k] - qz;
+                    const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+                    acc[k] = fma(qm, rsqrt_refined(r2), acc[k]);
                 }
             }
         }
         __syncthreads();
     }
-    if (mine) phi[s] = -G * mi * acc;
+#pragma unroll
+    for (int k = 0; k < PI; k++)
+        if (mine[k]) phi[s[k]] = -G * mi[k] * acc[k];
 }
 
 __global__ void k_count_pairs(const uint32_t *__restrict__ off, uint32_t ngroups, long long pp_threshold, unsigned long long *__restrict__ out)
@@ -96,7 +116,7 @@ unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G
     DBuf<unsigned long long> np(ctx, 1);
     VR_CUDA(cudaMemsetAsync(np.p, 0, sizeof(unsigned long long), ctx->stream));
     VR_LAUNCH(ctx, k_count_pairs, grid_for((size_t)gs.ngroups, 256), 256, 0, gs.off.p, (uint32_t)gs.ngroups, pp_threshold, np.p);
-    VR_LAUNCH(ctx, k_potential_direct, grid_for(gs.ntot, PT), PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G,
+    VR_LAUNCH(ctx, k_potential_direct, grid_for(gs.ntot, PS), PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G,
               eps * eps, pp_threshold, phi);
     unsigned long long h = 0;
     VR_CUDA(cudaMemcpyAsync(&h, np.p, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
