@@ -204,6 +204,7 @@ void vrgpu_destroy(vrgpu_ctx *ctx)
     ctx->evpool.clear();
     ctx->pool.release_all();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -110,6 +110,7 @@ struct vrgpu_ctx {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr; // host->device staging copies, overlapped with the unpack kernel
     std::string err;
     vrgpu::Pool pool;
     vrgpu_stats stats{};
