@@ -31,7 +31,7 @@ __device__ __forceinline__ double rsqrt_refined(double r2)
 __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                                                          const double *__restrict__ m, const uint32_t *__restrict__ gid,
                                                          const uint32_t *__restrict__ off, uint32_t ntot, double G, double eps2,
-                                                         long long pp_threshold, double *__restrict__ phi)
+                                                         long long pp_threshold, uint32_t sym_min, double *__restrict__ phi)
 {
     __shared__ double2 sxy[PT], szm[PT]; // 16-byte shared loads: two per j instead of four
     __shared__ uint32_t sg[PT];
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
             g[k] = gid[s[k]];
             xi[k] = x[s[k]]; yi[k] = y[s[k]]; zi[k] = z[s[k]]; mi[k] = m[s[k]];
             const uint32_t sz_g = off[g[k] + 1] - off[g[k]];
-            mine[k] = pp_threshold < 0 || (long long)sz_g <= pp_threshold;
+            mine[k] = (pp_threshold < 0 || (long long)sz_g <= pp_threshold) && sz_g < sym_min;
         }
         any_mine = any_mine || mine[k];
     }
@@ -98,6 +98,141 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
         if (mine[k]) phi[s[k]] = -G * mi[k] * acc[k];
 }
 
+// ---------------------------------------------------------------------------------------------------
+// symmetric direct sum for big groups: every unordered TILE pair (I <= J) of a group is one CTA.  The 1/r of a particle
+// pair is evaluated once and credited to both particles: acc_i in registers, the j side accumulated per warp in shared memory
+// and over the CTA through shared memory (lanes rotate over the j of a 32-block, so no shuffles are needed).  ~49 DP
+// instructions per 256 ordered pairs instead of 88.
+// Partial sums of different CTAs meet in global fp64 atomics, so the last bits of phi depend on the arrival order
+// (relative 1e-16; DESIGN.md "determinism").
+// ---------------------------------------------------------------------------------------------------
+constexpr int SYM_TILE = PT * PI;         // 1024 slots
+constexpr uint32_t SYM_MIN = 4 * SYM_TILE; // groups at least this large take the symmetric kernel
+
+__global__ void k_sym_count(const uint32_t *__restrict__ off, uint32_t ngroups, long long pp_threshold, unsigned long long *__restrict__ npairs)
+{
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; // entry g holds group g (entry 0 unused)
+    if (g > ngroups) return;
+    unsigned long long c = 0;
+    if (g >= 1) {
+        const uint32_t n = off[g + 1] - off[g];
+        if (n >= SYM_MIN && (pp_threshold < 0 || (long long)n <= pp_threshold)) {
+            const unsigned long long nt = (n + SYM_TILE - 1) / SYM_TILE;
+            c = nt * (nt + 1) / 2;
+        }
+    }
+    npairs[g] = c;
+}
+
+__global__ void __launch_bounds__(PT) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                                                      const double *__restrict__ m, const uint32_t *__restrict__ off, uint32_t ngroups,
+                                                      const unsigned long long *__restrict__ pair_start /* exclusive scan, ngroups+2 */,
+                                                      double eps2, double *__restrict__ phiacc)
+{
+    __shared__ double2 sxy[PT], szm[PT];
+    __shared__ double sacc[PT / 32][PT];
+    __shared__ uint32_t s_g;
+    const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    // which group: largest g with pair_start[g] <= blockIdx.x
+    if (threadIdx.x == 0) {
+        uint32_t lo = 1, hi = ngroups;
+        const unsigned long long b = blockIdx.x;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (pair_start[mid] <= b) lo = mid; else hi = mid - 1;
+        }
+        s_g = lo;
+    }
+    __syncthreads();
+    const uint32_t g = s_g;
+    const uint32_t g0 = off[g], n = off[g + 1] - g0;
+    const uint32_t nt = (n + SYM_TILE - 1) / SYM_TILE;
+    // triangular decode: t = I*nt - I*(I-1)/2 + (J - I)
+    const unsigned long long t = blockIdx.x - pair_start[g];
+    uint32_t I = (uint32_t)floor(((2.0 * nt + 1.0) - sqrt((2.0 * nt + 1.0) * (2.0 * nt + 1.0) - 8.0 * (double)t)) * 0.5);
+    while ((unsigned long long)I * nt - (unsigned long long)I * (I - 1) / 2 > t) I--;
+    while ((unsigned long long)(I + 1) * nt - (unsigned long long)(I + 1) * I / 2 <= t) I++;
+    const uint32_t J = I + (uint32_t)(t - ((unsigned long long)I * nt - (unsigned long long)I * (I - 1) / 2));
+    const uint32_t i_base = g0 + I * SYM_TILE, j_base = g0 + J * SYM_TILE, g_end = g0 + n;
+    const uint32_t j_end = min(g_end, j_base + SYM_TILE);
+    const bool diag = I == J;
+
+    uint32_t si[PI];
+    double xi[PI], yi[PI], zi[PI], mi[PI], acc[PI];
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        si[k] = i_base + k * PT + threadIdx.x;
+        acc[k] = 0;
+        if (si[k] < g_end) { xi[k] = x[si[k]]; yi[k] = y[si[k]]; zi[k] = z[si[k]]; mi[k] = m[si[k]]; }
+        else { xi[k] = 1e100; yi[k] = 1e100; zi[k] = 1e100; mi[k] = 0; } // padding: weightless and far away
+    }
+    for (uint32_t jb = j_base; jb < j_end; jb += PT) {
+        const uint32_t j = jb + threadIdx.x;
+        if (j < j_end) { sxy[threadIdx.x] = make_double2(x[j], y[j]); szm[threadIdx.x] = make_double2(z[j], m[j]); }
+        else { sxy[threadIdx.x] = make_double2(-1e100, -1e100); szm[threadIdx.x] = make_double2(-1e100, 0.0); }
+#pragma unroll
+        for (int ww = 0; ww < PT / 32; ww++) sacc[ww][threadIdx.x] = 0.0;
+        __syncthreads();
+        const int cnt = (int)min((uint32_t)PT, j_end - jb);
+        if (!diag) {
+            // rotation: at step s lane l works on j = 32*blk + ((l + s) & 31), so the 32 lanes always hold 32 DIFFERENT j:
+            // the j-side partial goes straight into the warp's shared row without any cross-lane reduction
+            const int nblk = (cnt + 31) >> 5;
+            for (int blk = 0; blk < nblk; blk++) {
+#pragma unroll 2
+                for (int st = 0; st < 32; st++) {
+                    const int jj = (blk << 5) + (int)((lane + st) & 31);
+                    const double2 qa = sxy[jj], qb = szm[jj];
+                    double tj = 0;
+#pragma unroll
+                    for (int k = 0; k < PI; k++) {
+                        const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
+                        const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+                        const double ri = rsqrt_refined(r2);
+                        acc[k] = fma(qb.y, ri, acc[k]);
+                        tj = fma(mi[k], ri, tj);
+                    }
+                    sacc[w][jj] += tj;
+                    __syncwarp();
+                }
+            }
+            __syncthreads();
+            if ((int)threadIdx.x < cnt) {
+                double s = 0;
+#pragma unroll
+                for (int ww = 0; ww < PT / 32; ww++) s += sacc[ww][threadIdx.x];
+                atomicAdd(&phiacc[jb + threadIdx.x], s);
+            }
+        } else {
+            for (int jj = 0; jj < cnt; jj++) {
+                const double2 qa = sxy[jj], qb = szm[jj];
+                const uint32_t sj = jb + jj;
+#pragma unroll
+                for (int k = 0; k < PI; k++) {
+                    if (sj == si[k]) continue;
+                    const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
+                    const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+                    acc[k] = fma(qb.y, rsqrt_refined(r2), acc[k]);
+                }
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < PI; k++)
+        if (si[k] < g_end) atomicAdd(&phiacc[si[k]], acc[k]);
+}
+
+__global__ void k_sym_finish(const double *__restrict__ phiacc, const double *__restrict__ m, const uint32_t *__restrict__ gid,
+                             const uint32_t *__restrict__ off, uint32_t ntot, double G, long long pp_threshold, double *__restrict__ phi)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    const uint32_t g = gid[s];
+    const uint32_t n = off[g + 1] - off[g];
+    if (n >= SYM_MIN && (pp_threshold < 0 || (long long)n <= pp_threshold)) phi[s] = -G * m[s] * phiacc[s];
+}
+
 __global__ void k_count_pairs(const uint32_t *__restrict__ off, uint32_t ngroups, long long pp_threshold, unsigned long long *__restrict__ out)
 {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x + 1;
@@ -110,14 +245,32 @@ __global__ void k_count_pairs(const uint32_t *__restrict__ off, uint32_t ngroups
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
 }
 
-unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, long long pp_threshold, double *phi)
+unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G_, double eps, long long pp_threshold, double *phi)
 {
     if (gs.ntot == 0) return 0;
     DBuf<unsigned long long> np(ctx, 1);
     VR_CUDA(cudaMemsetAsync(np.p, 0, sizeof(unsigned long long), ctx->stream));
     VR_LAUNCH(ctx, k_count_pairs, grid_for((size_t)gs.ngroups, 256), 256, 0, gs.off.p, (uint32_t)gs.ngroups, pp_threshold, np.p);
-    VR_LAUNCH(ctx, k_potential_direct, grid_for(gs.ntot, PS), PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G,
-              eps * eps, pp_threshold, phi);
+    // big groups: symmetric tile-pair kernel; everything else: the tiled kernel
+    const uint32_t G = (uint32_t)gs.ngroups;
+    DBuf<unsigned long long> npairs(ctx, (size_t)G + 2), pstart(ctx, (size_t)G + 2), ptotal(ctx, 1);
+    VR_CUDA(cudaMemsetAsync(npairs.p, 0, sizeof(unsigned long long) * ((size_t)G + 2), ctx->stream));
+    VR_LAUNCH(ctx, k_sym_count, grid_for((size_t)G + 1, 256), 256, 0, gs.off.p, G, pp_threshold, npairs.p);
+    exclusive_scan_u64(ctx, npairs.p, pstart.p, (size_t)G + 2, ptotal.p);
+    unsigned long long nwork = 0;
+    VR_CUDA(cudaMemcpyAsync(&nwork, ptotal.p, sizeof(nwork), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    VR_REQUIRE(nwork < 0x7fffffffull, VRGPU_EUNSUPPORTED, "direct sum: too many tile pairs (use the tree for groups this large)");
+    { KScope k(ctx, "potential.direct.tiled");
+    VR_LAUNCH(ctx, k_potential_direct, grid_for(gs.ntot, PS), PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G_,
+              eps * eps, pp_threshold, nwork ? SYM_MIN : 0xffffffffu, phi); }
+    if (nwork) {
+        KScope k(ctx, "potential.direct.sym");
+        DBuf<double> phiacc(ctx, gs.ntot);
+        VR_CUDA(cudaMemsetAsync(phiacc.p, 0, sizeof(double) * gs.ntot, ctx->stream));
+        VR_LAUNCH(ctx, k_potential_sym, (unsigned)nwork, PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p, eps * eps, phiacc.p);
+        VR_LAUNCH(ctx, k_sym_finish, grid_for(gs.ntot, 256), 256, 0, phiacc.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G_, pp_threshold, phi);
+    }
     unsigned long long h = 0;
     VR_CUDA(cudaMemcpyAsync(&h, np.p, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
