@@ -98,3 +98,19 @@ def test_search_full_set_6dfof_unbind(gpu_ctx, oracle):
     if ndiff == 0:
         assert ng == want["ngroups"] and np.array_equal(got, want["pfof"])
     assert np.array_equal(parts["pos"], o6["pos"]) and np.array_equal(parts["vel"], o6["vel"])
+
+
+def test_pinned_caller_memory_gets_identical_writeback(gpu_ctx):
+    """Page-locked caller records take the zero-copy write-back kernels; pageable ones the staged host scatter."""
+    import vrgpu
+    nside = 40
+    d = vrsynth.make_box(nside ** 3, 17)
+    ell = vrsynth.BOX / nside
+    so = vrgpu.search_opts(vrsynth.BOX, (ell * ell) * (0.2 * 0.2) * (1.0 * 1.0), halo_min_size=20, fofbgtype=3, bound_halos=1)
+    a = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"], pinned=False)
+    b = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"], pinned=True)
+    pa, na = gpu_ctx.search_full_set(a, so)
+    pb, nb = gpu_ctx.search_full_set(b, so)
+    assert na == nb and np.array_equal(pa, pb)
+    assert np.array_equal(a["pos"], b["pos"]) and np.array_equal(a["vel"], b["vel"])
+    assert not np.array_equal(a["pos"], d["pos"])  # something was unwrapped / re-rounded

@@ -54,9 +54,25 @@ struct CallTimer {
 };
 
 // write a compact (index, xyz) list back into the caller's (writable) view
+__global__ void k_scatter_direct(unsigned char *__restrict__ base, size_t stride, size_t off_field, const uint32_t *__restrict__ idx,
+                                 const double *__restrict__ xyz, size_t cnt)
+{
+    size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= cnt) return;
+    double *p = reinterpret_cast<double *>(base + (size_t)idx[k] * stride + off_field);
+    p[0] = xyz[3 * k]; p[1] = xyz[3 * k + 1]; p[2] = xyz[3 * k + 2];
+}
+
 void scatter_positions_to_host(vrgpu_ctx *ctx, const vrgpu_view &view, size_t off_field, const uint32_t *idx_dev, const double *xyz_dev, size_t cnt)
 {
     if (cnt == 0) return;
+    if (void *dev = mapped_host_pointer(view.base)) {
+        // page-locked caller memory: the device writes the moved positions straight into the records
+        VR_LAUNCH(ctx, k_scatter_direct, grid_for(cnt, 256), 256, 0, static_cast<unsigned char *>(dev), view.stride, off_field, idx_dev, xyz_dev, cnt);
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->stats.d2h_bytes += (long long)(cnt * 24);
+        return;
+    }
     std::vector<uint32_t> idx(cnt);
     std::vector<double> xyz(3 * cnt);
     VR_CUDA(cudaMemcpyAsync(idx.data(), idx_dev, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));

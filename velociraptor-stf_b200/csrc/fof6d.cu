@@ -56,12 +56,22 @@ __global__ void __launch_bounds__(256) k_group_dispersion(const double *__restri
                 px = __dmul_rn(vx[s], mm); py = __dmul_rn(vy[s], mm); pz = __dmul_rn(vz[s], mm);
             }
             const int cnt = (int)min(32u, s1 - base);
-            for (int t = 0; t < cnt; t++) {
-                sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
-                sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
-                sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
-                sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
-            }
+            if (cnt == 32) {
+                // full chunk: unrolled, so the shuffles run ahead and only the dependent DADD chain remains
+#pragma unroll
+                for (int t = 0; t < 32; t++) {
+                    sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
+                    sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
+                    sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
+                    sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
+                }
+            } else
+                for (int t = 0; t < cnt; t++) {
+                    sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
+                    sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
+                    sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
+                    sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
+                }
         }
         const double mx = __ddiv_rn(sx, sm), my = __ddiv_rn(sy, sm), mz = __ddiv_rn(sz, sm);
         double acc = 0;
@@ -75,11 +85,19 @@ __global__ void __launch_bounds__(256) k_group_dispersion(const double *__restri
                 d = __dsub_rn(vz[s], mz); tz = __dmul_rn(__dmul_rn(d, d), mm);
             }
             const int cnt = (int)min(32u, s1 - base);
-            for (int t = 0; t < cnt; t++) {
-                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
-                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
-                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
-            }
+            if (cnt == 32) {
+#pragma unroll
+                for (int t = 0; t < 32; t++) {
+                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
+                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
+                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
+                }
+            } else
+                for (int t = 0; t < cnt; t++) {
+                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
+                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
+                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
+                }
         }
         if (lane == 0) vs2[g] = __dmul_rn(__dmul_rn(__ddiv_rn(acc, sm), vfac), vfac);
     }
@@ -620,11 +638,42 @@ __global__ void k_pack_phase(const double *__restrict__ pos, const double *__res
     for (int k = 0; k < 3; k++) { out[6 * s + k] = pos[3 * i + k]; out[6 * s + 3 + k] = vel[3 * i + k]; }
 }
 
+// zero-copy variant: when the caller's records are page-locked (pinned / registered and mapped), the device stores the
+// updated coordinates straight into them over PCIe -- no staging copy and no host scatter loop
+__global__ void k_writeback_direct(unsigned char *__restrict__ base, size_t stride, size_t off_pos, size_t off_vel,
+                                   const double *__restrict__ pos, const double *__restrict__ vel, const long long *__restrict__ pfof, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || pfof[i] <= 0) return;
+    double *p = reinterpret_cast<double *>(base + i * stride + off_pos);
+    p[0] = pos[3 * i]; p[1] = pos[3 * i + 1]; p[2] = pos[3 * i + 2];
+    if (vel) {
+        double *v = reinterpret_cast<double *>(base + i * stride + off_vel);
+        v[0] = vel[3 * i]; v[1] = vel[3 * i + 1]; v[2] = vel[3 * i + 2];
+    }
+}
+
+// device-visible alias of a page-locked host pointer, or nullptr for pageable memory
+void *mapped_host_pointer(const void *p)
+{
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (at.type == cudaMemoryTypeHost && at.devicePointer) return at.devicePointer;
+    return nullptr;
+}
+
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev)
 {
     if (P.n == 0) return;
     VR_REQUIRE(P.has_vel && view.off_vel != VRGPU_NOFIELD, VRGPU_EINVAL, "write-back needs velocities in the view");
     const int T = 256;
+    if (void *dev = mapped_host_pointer(view.base)) {
+        VR_LAUNCH(ctx, k_writeback_direct, grid_for(P.n, T), T, 0, static_cast<unsigned char *>(dev), view.stride, view.off_pos, view.off_vel,
+                  P.pos.p, P.vel.p, pfof_dev, P.n);
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->stats.d2h_bytes += (long long)ctx->stats.n_grouped * 48;
+        return;
+    }
     DBuf<uint32_t> flags(ctx, P.n), excl(ctx, P.n), total(ctx, 1);
     VR_LAUNCH(ctx, k_flag_pos, grid_for(P.n, T), T, 0, pfof_dev, P.n, flags.p);
     exclusive_scan_u32(ctx, flags.p, excl.p, P.n, total.p);

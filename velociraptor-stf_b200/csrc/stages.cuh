@@ -12,6 +12,9 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
 // write pos+vel of every particle with pfof_dev[i] > 0 back into the caller's writable view
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 
+// device-visible alias of a page-locked host pointer, or nullptr for pageable memory (fof6d.cu)
+void *mapped_host_pointer(const void *p);
+
 // potentials for host-side CSR groups (vrgpu_potential)
 void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
                         const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,
