@@ -32,6 +32,19 @@ sys.path.insert(0, os.path.join(ROOT, "velociraptor-stf_b200"))
 
 import numpy as np  # noqa: E402
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, data)
+    else:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+
+
 METRIC = "fof_unbind_throughput"
 UNIT = "Mparticles/s"
 
@@ -181,7 +194,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -294,7 +307,7 @@ def run_ours(args):
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "roofline_all": roof_all,
             "stage_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
             "cpu_baseline": cpu}
-    print(json.dumps(line), flush=True)
+    emit(line)
     ctx.close()
 
 
@@ -383,7 +396,7 @@ def run_ours_multi(args, rank, world, local):
                 "e2e": {"value": n / (float(np.mean(e2e)) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(tot[1].item()),
                         "d2h_bytes_per_step": int(tot[2].item()), "ms_per_step": float(np.mean(e2e)), "ngroups": ng_e},
                 "gpu_launches": int(tot[0].item()), "clocks": clocks, "roofline": roof, "kernel_ms_rank0": kms, "cpu_baseline": None}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     dist.destroy_process_group()
 
@@ -400,6 +413,12 @@ def main():
     ap.add_argument("--cpu-nside", type=int, default=0, help="box side of the bounded CPU sample (default 128)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # exactly ONE line on stdout: libraries (NCCL prints its version banner) write to fd 1 too, so everything except the
+    # final JSON goes to stderr
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
