@@ -171,6 +171,8 @@ void *vrgpu_stream(vrgpu_ctx *ctx);
 /* Per-kernel device times accumulated since the last reset: one line per kernel group,
  * "<name> <milliseconds> <launch-brackets>\n".  Returns a pointer owned by the context. */
 const char *vrgpu_kernel_times(vrgpu_ctx *ctx);
+/* measured fp64 FMA throughput of the device in TFLOP/s (denominator of the potential kernels' roofline) */
+int vrgpu_measure_fp64_tflops(vrgpu_ctx *ctx, double *tflops_out);
 void vrgpu_kernel_times_reset(vrgpu_ctx *ctx);
 
 #ifdef __cplusplus

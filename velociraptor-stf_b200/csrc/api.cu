@@ -528,6 +528,14 @@ const char *vrgpu_kernel_times(vrgpu_ctx *ctx)
     return ctx->ktimes_text.c_str();
 }
 
+int vrgpu_measure_fp64_tflops(vrgpu_ctx *ctx, double *tflops_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(tflops_out, VRGPU_EINVAL, "null pointer");
+        *tflops_out = measure_fp64_tflops(ctx);
+    });
+}
+
 void vrgpu_kernel_times_reset(vrgpu_ctx *ctx)
 {
     if (!ctx) return;

@@ -9,6 +9,8 @@
 // streamed through shared memory in tiles of 256.  FP64-pipe bound: ~14 DP instructions per pair.
 #include "groups.cuh"
 
+#include <algorithm>
+
 namespace vrgpu {
 
 constexpr int PT = 256; // threads per CTA
@@ -277,4 +279,44 @@ unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G
     return h;
 }
 
+} // namespace vrgpu
+
+// ---------------------------------------------------------------------------------------------------
+// FP64 pipe microbenchmark (roofline denominator for the potential kernels; MEASURED_PEAKS.json has no fp64 figure)
+// ---------------------------------------------------------------------------------------------------
+namespace vrgpu {
+__global__ void __launch_bounds__(256) k_dfma_peak(double *out, int iters, double a, double b)
+{
+    double r0 = threadIdx.x, r1 = r0 + 1, r2 = r0 + 2, r3 = r0 + 3, r4 = r0 + 4, r5 = r0 + 5, r6 = r0 + 6, r7 = r0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            r0 = fma(r0, a, b); r1 = fma(r1, a, b); r2 = fma(r2, a, b); r3 = fma(r3, a, b);
+            r4 = fma(r4, a, b); r5 = fma(r5, a, b); r6 = fma(r6, a, b); r7 = fma(r7, a, b);
+        }
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r0 + r1 + r2 + r3 + r4 + r5 + r6 + r7;
+}
+
+double measure_fp64_tflops(vrgpu_ctx *ctx)
+{
+    const int blocks = ctx->sm_count * 8, iters = 2048;
+    DBuf<double> out(ctx, (size_t)blocks * 256);
+    VR_LAUNCH(ctx, k_dfma_peak, blocks, 256, 0, out.p, 64, 0.999999, 1e-9); // warm-up
+    cudaEvent_t a = KScope::get(ctx), b = KScope::get(ctx);
+    double best = 0;
+    for (int rep = 0; rep < 3; rep++) {
+        VR_CUDA(cudaEventRecord(a, ctx->stream));
+        VR_LAUNCH(ctx, k_dfma_peak, blocks, 256, 0, out.p, iters, 0.999999, 1e-9);
+        VR_CUDA(cudaEventRecord(b, ctx->stream));
+        VR_CUDA(cudaEventSynchronize(b));
+        float ms = 0;
+        VR_CUDA(cudaEventElapsedTime(&ms, a, b));
+        const double flops = 2.0 * 8 * 16 * (double)iters * 256.0 * blocks;
+        best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    ctx->evpool.push_back(a);
+    ctx->evpool.push_back(b);
+    return best;
+}
 } // namespace vrgpu

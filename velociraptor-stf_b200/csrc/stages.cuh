@@ -15,6 +15,9 @@ void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticl
 // device-visible alias of a page-locked host pointer, or nullptr for pageable memory (fof6d.cu)
 void *mapped_host_pointer(const void *p);
 
+// DFMA throughput of the device in TFLOP/s (potential.cu)
+double measure_fp64_tflops(vrgpu_ctx *ctx);
+
 // potentials for host-side CSR groups (vrgpu_potential)
 void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
                         const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,

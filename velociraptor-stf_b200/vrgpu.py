@@ -133,6 +133,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_stream.restype = C.c_void_p
     L.vrgpu_kernel_times.argtypes = [C.c_void_p]
     L.vrgpu_kernel_times.restype = C.c_char_p
+    L.vrgpu_measure_fp64_tflops.argtypes = [C.c_void_p, P_d]
     L.vrgpu_kernel_times_reset.argtypes = [C.c_void_p]
     L.vrgpu_kernel_times_reset.restype = None
     _lib = L
@@ -143,7 +144,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
-                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset"]
+                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops"]
 
 
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
@@ -316,6 +317,11 @@ class Context:
             name, ms, cnt = line.split()
             out[name] = {"ms": float(ms), "count": int(cnt)}
         return out
+
+    def measure_fp64_tflops(self) -> float:
+        v = C.c_double(0)
+        self._check(self.lib.vrgpu_measure_fp64_tflops(self.h, C.byref(v)))
+        return float(v.value)
 
     def kernel_times_reset(self):
         self.lib.vrgpu_kernel_times_reset(self.h)
