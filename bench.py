@@ -59,9 +59,22 @@ FLOPS_PER_ORDERED_PAIR = 8.0      # F_pp = 8 n (n-1) per group (16 flops per uno
 FP64_PEAK_TFLOPS_NOMINAL = 40.0   # B200 vector FP64 (vendor figure; not in MEASURED_PEAKS.json)
 
 
-def workload_name(nside: int, fofbgtype: int, pp: int) -> str:
+def workload_name(nside, fofbgtype: int, pp: int) -> str:
     stages = "3DFOF" + ("+6DFOF" if fofbgtype <= 4 else "") + ("+direct-sum unbinding" if pp < 0 else "+tree/direct unbinding")
+    if ZOOM_NPART:
+        return (f"{stages} on a zoom-style single halo of {ZOOM_NPART} particles (NFW c=7 + 10% in subclumps, one 3D group, "
+                f"L=100, b=0.2 of the mean spacing, seed 105)")
     return f"{stages} on a {nside}^3 synthetic clustered periodic DM box (L=100, b=0.2, seed {seed_for(nside)})"
+
+
+ZOOM_NPART = 0   # --single-halo N: BASELINE.json configs[4] (set in main)
+
+
+def make_input(nside):
+    import vrsynth
+    if ZOOM_NPART:
+        return vrsynth.make_box(ZOOM_NPART, 105, single_halo=True)
+    return vrsynth.make_box(nside ** 3, seed_for(nside))
 
 
 def seed_for(nside: int) -> int:
@@ -214,8 +227,8 @@ def run_ours(args):
         return run_ours_multi(args, rank, world, local)
 
     nside = args.nside
-    n = nside ** 3
-    d = vrsynth.make_box(n, seed_for(nside))
+    d = make_input(nside)
+    n = d["n"]
     ctx = vrgpu.Context(local)
     so = make_search_opts(vrgpu, nside, args.fofbgtype, args.pp_threshold)
     pristine = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"])
@@ -273,7 +286,7 @@ def run_ours(args):
     fp64_peak = ctx.measure_fp64_tflops()   # DFMA microbenchmark on this GPU (MEASURED_PEAKS.json has no fp64 figure)
     traffic_tab = {}
     tpath = os.path.join(ROOT, "profiles", "r01c_traffic.json")
-    if os.path.exists(tpath) and nside == 256:
+    if os.path.exists(tpath) and nside == 256 and not ZOOM_NPART and args.fofbgtype == 5 and args.pp_threshold < 0:
         traffic_tab = json.load(open(tpath)).get("dram_bytes_per_launch", {})
     kernel_of = {"potential.direct": "k_potential_sym", "fof3d.link_cells": "k_link_thread"}
     groups = {k: v for k, v in ktimes.items() if k != "copy_pristine"}
@@ -424,7 +437,13 @@ def main():
     ap.add_argument("--pp-threshold", type=int, default=-1, help="<0: direct sum for every group (configs[1]); 150 = reference UNBINDNUM")
     ap.add_argument("--cpu-nside", type=int, default=0, help="box side of the bounded CPU sample (default 128)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--single-halo", type=int, default=0, metavar="NPART",
+                    help="zoom-style input (configs[4]): ONE halo of NPART particles instead of the clustered box (1 GPU)")
     args = ap.parse_args()
+    if args.single_halo:
+        global ZOOM_NPART
+        ZOOM_NPART = args.single_halo
+        args.nside = float(args.single_halo) ** (1.0 / 3.0)   # only its mean spacing L/nside enters (the linking length)
     # exactly ONE line on stdout: libraries (NCCL prints its version banner) write to fd 1 too, so everything except the
     # final JSON goes to stderr
     global _REAL_STDOUT

@@ -130,13 +130,87 @@ def main():
     pbox = [None] * world
     dist.all_gather_object(pbox, (own, pf))
     ok = True
+    want, ngw = orc.fof3d(d["pos"], b, L, minsize, d["pid"])
     if rank == 0:
         full = np.zeros(nside ** 3, dtype=np.int64)
         for o, p in pbox:
             full[o] = p
-        want, ngw = orc.fof3d(d["pos"], b, L, minsize, d["pid"])
         ok = bool(np.array_equal(full, want)) and len(allrec) == ngw
         print(f"[dist_model] world={world} nside={nside} groups={len(allrec)} oracle={ngw} boundary comps={len(U)} edges={len(alle)} -> {'OK' if ok else 'FAIL'}")
+
+    # ---- placement of the per-group stages (mg_place_groups): straddling or costly groups to the least loaded rank in
+    #      size order, small single-rank groups stay; then consolidation, unbinding per group, global renumbering ----
+    G = len(allrec)
+    gsize = np.zeros(G, dtype=np.int64); ghome = np.full(G, -1, dtype=np.int64)
+    for g, j in enumerate(order):
+        s_, m_, k_, ref_, r_ = allrec[j]
+        gsize[g] = s_
+        ghome[g] = -1 if k_ == 1 else r_
+    BIG = 200                                   # scaled down with the box (2048 in the device code)
+    cost = lambda n: 0.55e-3 * n * n if n <= 150 else 0.45 * n * np.log2(n + 1.0) + 2.0 * n
+    load = np.zeros(world)
+    for g in range(G):
+        if ghome[g] >= 0 and gsize[g] < BIG:
+            load[ghome[g]] += cost(gsize[g])
+    dest_of = np.full(G + 1, -1, dtype=np.int64)
+    for g in range(G):
+        dd = ghome[g]
+        if dd < 0 or gsize[g] >= BIG:
+            dd = int(np.argmin(load)); load[dd] += cost(gsize[g])
+        dest_of[g + 1] = dd
+    dest = dest_of[pf]
+    vel, mass = d["vel"][own], d["mass"][own]
+    exports = [None] * world
+    for t in range(world):
+        m = (dest == t) & (t != rank)
+        exports[t] = (pos[m], vel[m], mass[m], pid[m], pf[m], own[m])
+    xbox = [None] * world
+    dist.all_gather_object(xbox, exports)
+    keep = (dest < 0) | (dest == rank)
+    wpos = [pos]; wvel = [vel]; wmass = [mass]; wpid = [pid]; wpf = [np.where(keep, pf, 0)]; wown = [own]
+    for s_ in range(world):
+        if s_ == rank:
+            continue
+        e = xbox[s_][rank]
+        wpos.append(e[0]); wvel.append(e[1]); wmass.append(e[2]); wpid.append(e[3]); wpf.append(e[4]); wown.append(e[5])
+    wpos, wvel, wmass, wpid, wpf, wown = (np.concatenate(a) for a in (wpos, wvel, wmass, wpid, wpf, wown))
+    present = np.unique(wpf[wpf > 0])
+    local_id = np.zeros(G + 1, dtype=np.int64); local_id[present] = np.arange(1, len(present) + 1)
+    wl = local_id[wpf]
+    # members in pid order within a group (what by_pid=true does on the device): sort the working set by pid
+    o_pid = np.argsort(wpid, kind="stable")
+    wpos, wvel, wmass, wpid, wl, wown = wpos[o_pid], wvel[o_pid], wmass[o_pid], wpid[o_pid], wl[o_pid], wown[o_pid]
+    uo = vroracle.unbind_opts_from(vroracle.default_opts(), pp_threshold=150, sortflag_mode=0)
+    wposu = orc.adjust_for_period(wpos, L, wl, len(present)) if len(present) else wpos
+    res_u = orc.unbind(wposu, wvel, wmass, wl, len(present), uo, wpid, 1e-6) if len(present) else {"pfof": wl, "ngroups": 0, "n_marginal": 0}
+    fl = res_u["pfof"]
+    frec = []
+    for g in range(1, int(res_u["ngroups"]) + 1):
+        m = fl == g
+        frec.append((int(m.sum()), int(wpid[m].min()), g))
+    fbox = [None] * world
+    dist.all_gather_object(fbox, frec)
+    fall = [(s_, m_, g_, r_) for r_, lst in enumerate(fbox) for (s_, m_, g_) in lst]
+    forder = sorted(range(len(fall)), key=lambda j: (-fall[j][0], fall[j][1]))
+    fgid = {(fall[j][3], fall[j][2]): g for g, j in enumerate(forder, start=1)}
+    fglob = np.array([fgid[(rank, int(x))] if x > 0 else 0 for x in fl], dtype=np.int64)
+    hbox = [None] * world
+    dist.all_gather_object(hbox, (wown, fglob, wl > 0, int(res_u["n_marginal"])))
+    if rank == 0:
+        full2 = np.zeros(nside ** 3, dtype=np.int64); seen = np.zeros(nside ** 3, dtype=np.int64)
+        nmarg = 0
+        for o_, f_, held, nm in hbox:
+            full2[o_[held]] = f_[held]
+            np.add.at(seen, o_[held], 1)
+            nmarg += nm
+        posw = orc.adjust_for_period(d["pos"], L, want, ngw)
+        ref_u = orc.unbind(posw, d["vel"], d["mass"], want, ngw, uo, d["pid"], 1e-6)
+        once = bool(np.array_equal(seen, (want > 0).astype(np.int64)))      # every grouped particle consolidated exactly once
+        ndiff = int(np.count_nonzero((full2 > 0) != (ref_u["pfof"] > 0)))
+        same = ndiff <= nmarg + ref_u["n_marginal"] and (ndiff > 0 or (np.array_equal(full2, ref_u["pfof"]) and len(fall) == ref_u["ngroups"]))
+        print(f"[dist_model] placement: loads={np.round(load / max(load.max(), 1e-30), 3).tolist()} consolidated once={once} "
+              f"unbound parity diffs={ndiff} (marginal {nmarg}) groups={len(fall)} oracle={ref_u['ngroups']} -> {'OK' if once and same else 'FAIL'}")
+        ok = ok and once and same
     res = [ok]
     dist.broadcast_object_list(res, src=0)
     dist.destroy_process_group()

@@ -103,3 +103,30 @@ def test_unbind(ref, oracle, nside, seed, unbindtype):
     assert np.all(np.any(bound[:, ~agree] == wb[~agree], axis=0))
     assert int(np.count_nonzero(~agree)) < 0.01 * np.count_nonzero(pf > 0) + 50
     assert all(v["changed"] == want["changed"] for v in variants)
+
+
+def test_single_halo_search_full_set(ref, oracle):
+    """Zoom-style input (BASELINE.json configs[4], scaled down): one 3D group; adaptive 6DFOF splits it in phase space and the
+    large-group branch of Unbind (n > ompunbindnum, tree potential) does the removal."""
+    import vroracle
+    n = 30000
+    d = vrsynth.make_box(n, 105, single_halo=True)
+    rng = np.random.default_rng(2)
+    d["pos"] = np.mod(d["pos"] + rng.random(d["pos"].shape) * 1e-7, vrsynth.BOX)   # no tied kd-tree medians
+    nside = float(n) ** (1.0 / 3.0)
+    ro = _opts(vroracle, nside, fofbgtype=3, bound_halos=1)
+    r = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], ro)
+    cr, _ = vrsynth.canonical_groups(r["pfof"], d["pid"])
+    ell = vrsynth.BOX / nside
+    b = float(np.sqrt((ell * ell) * (0.2 * 0.2) * (1.0 * 1.0)))
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    assert ng == 1
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    o6 = oracle.fof6d(pos, d["vel"], d["mass"], pf, ng, b, 1.25, 3, 20, d["pid"])
+    assert o6["ngroups"] > 1
+    uo = vroracle.unbind_opts_from(ro, 150, sortflag_mode=0)
+    got = oracle.unbind(o6["pos"], o6["vel"], d["mass"], o6["pfof"], o6["ngroups"], uo, d["pid"], 1e-6)
+    ndiff = int(np.count_nonzero((got["pfof"] > 0) != (cr > 0)))
+    assert ndiff <= got["n_marginal"]
+    if ndiff == 0:
+        assert got["ngroups"] == r["ngroups"] and np.array_equal(got["pfof"], cr)

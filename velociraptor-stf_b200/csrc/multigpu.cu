@@ -320,23 +320,18 @@ __global__ void k_mg_scatter_ids(const uint64_t *__restrict__ rec, const uint32_
     else if (j >= my0 && j < my1) gid_cell[(uint32_t)ref] = gid_of[j];
 }
 __global__ void k_mg_write_pfof(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ bidx, const uint32_t *__restrict__ R,
-                                const uint32_t *__restrict__ gid_u, const uint32_t *__restrict__ gid_cell, size_t n_own, long long *__restrict__ pfof,
-                                uint32_t *__restrict__ owner_u /* may be null */, const uint64_t *__restrict__ U, int *__restrict__ dest)
+                                const uint32_t *__restrict__ gid_u, const uint32_t *__restrict__ gid_cell, size_t n_own, long long *__restrict__ pfof)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_own) return;
     const uint32_t c = comp[i];
     const uint32_t u = bidx[c];
-    uint32_t g;
-    int d = -1;
-    if (u != MG_NONE) {
-        const uint32_t r = R[u];
-        g = gid_u[r];
-        if (g) d = (int)(U[r] >> 32); // the rank holding the root label consolidates the group
-    } else g = gid_cell[c];
-    pfof[i] = g;
-    if (dest) dest[i] = d;
-    (void)owner_u;
+    pfof[i] = u != MG_NONE ? gid_u[R[u]] : gid_cell[c];
+}
+__global__ void k_mg_dest_of(const long long *__restrict__ pfof, const int *__restrict__ dest_of_gid, size_t n_own, int *__restrict__ dest)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_own) dest[i] = dest_of_gid[pfof[i]];
 }
 
 } // namespace
@@ -349,6 +344,7 @@ struct GlobalOrder {
     DBuf<uint64_t> rec;      // gathered records (3 words each), rank order
     DBuf<uint32_t> gid_of;   // global id of every gathered record
     uint32_t total = 0, my0 = 0, my1 = 0;
+    std::vector<uint32_t> rank_first; // first record of every rank (nranks + 1 entries)
 };
 
 // all-gather this rank's candidate records and order ALL of them by (size desc, min pid asc)
@@ -359,7 +355,12 @@ void mg_global_order(vrgpu_ctx *ctx, const uint64_t *myrec, size_t nmine, Global
     std::vector<size_t> counts;
     allgatherv_u64(ctx, myrec, 3 * nmine, O.rec, counts);
     size_t tot = 0, before = 0;
-    for (int r = 0; r < M.nranks; r++) { if (r < M.rank) before += counts[r] / 3; tot += counts[r] / 3; }
+    O.rank_first.assign(M.nranks + 1, 0);
+    for (int r = 0; r < M.nranks; r++) {
+        if (r < M.rank) before += counts[r] / 3;
+        tot += counts[r] / 3;
+        O.rank_first[r + 1] = (uint32_t)std::min<size_t>(tot, 0xffffffffull);
+    }
     VR_REQUIRE(tot < 0xfffffff0ull, VRGPU_EUNSUPPORTED, "more than 2^32 groups");
     O.total = (uint32_t)tot;
     O.my0 = (uint32_t)before;
@@ -375,8 +376,12 @@ void mg_global_order(vrgpu_ctx *ctx, const uint64_t *myrec, size_t nmine, Global
 
 struct StageA {
     DBuf<long long> pfof;    // global 3D group id of every owned particle
-    DBuf<int> dest;          // rank that consolidates the particle's group (-1: stays here / ungrouped)
+    DBuf<int> dest;          // rank that consolidates the particle's group (-1: ungrouped); filled by mg_place_groups
     long long ngroups = 0;
+    // replicated on every rank, indexed by global id - 1: member count, and the rank holding ALL members (-1 when the group
+    // straddles a slab face)
+    std::vector<uint32_t> gsize;
+    std::vector<int> ghome;
     size_t n_ghost = 0, n_edges = 0, n_boundary = 0;
 };
 
@@ -561,10 +566,66 @@ void mg_fof3d(vrgpu_ctx *ctx, const DeviceParticles &P, double slab_lo, double s
     }
     A.ngroups = O.total;
     A.pfof.alloc(ctx, n_own + 1);
-    A.dest.alloc(ctx, n_own + 1);
     if (n_own)
-        VR_LAUNCH(ctx, k_mg_write_pfof, grid_for(n_own, T), T, 0, comp.p, bidx.p, R.p, gid_u.p, gid_cell.p, n_own, A.pfof.p, (uint32_t *)nullptr, U.p, A.dest.p);
+        VR_LAUNCH(ctx, k_mg_write_pfof, grid_for(n_own, T), T, 0, comp.p, bidx.p, R.p, gid_u.p, gid_cell.p, n_own, A.pfof.p);
+    // host copy of the global catalogue (size, home rank) for the placement of the per-group stages
+    A.gsize.assign(O.total, 0);
+    A.ghome.assign(O.total, -1);
+    if (O.total) {
+        std::vector<uint64_t> hrec(3 * (size_t)O.total);
+        std::vector<uint32_t> hgid(O.total);
+        VR_CUDA(cudaMemcpyAsync(hrec.data(), O.rec.p, hrec.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(hgid.data(), O.gid_of.p, hgid.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        int r = 0;
+        for (uint32_t j = 0; j < O.total; j++) {
+            while (j >= O.rank_first[r + 1]) r++;
+            const uint32_t g = hgid[j];
+            if (g == 0 || g > O.total) continue;
+            A.gsize[g - 1] = (uint32_t)hrec[3 * (size_t)j];
+            A.ghome[g - 1] = (hrec[3 * (size_t)j + 2] >> 63) ? -1 : r;
+        }
+    }
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
+}
+
+// Placement of the per-group stages (6DFOF, potentials, unbinding are independent per 3D group; the reference's
+// MPIGroupExchange sends a group to the task holding most of it, mpiroutines.cxx:2548).  Here: groups that straddle a face
+// or whose estimated cost matters go to the least loaded rank in size order (longest-processing-time rule); small groups
+// held by one rank stay where they are and only enter as that rank's base load.  Every rank computes the same table.
+void mg_place_groups(vrgpu_ctx *ctx, StageA &A, size_t n_own, const vrgpu_search_opts *o)
+{
+    MultiGpu &M = *ctx->mg;
+    const int T = 256;
+    const int N = M.nranks;
+    const size_t G = A.gsize.size();
+    const bool six = o->fofbgtype <= 4;
+    const bool unbind = o->bound_halos >= 1;
+    const long long pp = o->unbind.pp_threshold;
+    auto cost = [&](double n) {
+        double c = 0;
+        if (six) c += 6.0 * n;                                                    // ns, measured orders of magnitude
+        if (unbind) c += (pp < 0 || n <= (double)pp) ? 0.55e-3 * n * n : 0.45 * n * std::log2(n + 1.0) + 2.0 * n;
+        return c;
+    };
+    const uint32_t BIG = 2048;
+    std::vector<double> load(N, 0.0);
+    for (size_t g = 0; g < G; g++)
+        if (A.ghome[g] >= 0 && A.gsize[g] < BIG) load[A.ghome[g]] += cost(A.gsize[g]);
+    std::vector<int> hdest(G + 1, -1);
+    for (size_t g = 0; g < G; g++) { // global ids are in size order already
+        int d = A.ghome[g];
+        if (d < 0 || A.gsize[g] >= BIG) {
+            d = (int)(std::min_element(load.begin(), load.end()) - load.begin());
+            load[d] += cost(A.gsize[g]);
+        }
+        hdest[g + 1] = d;
+    }
+    DBuf<int> ddest(ctx, G + 1);
+    VR_CUDA(cudaMemcpyAsync(ddest.p, hdest.data(), (G + 1) * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    A.dest.alloc(ctx, n_own + 1);
+    if (n_own) VR_LAUNCH(ctx, k_mg_dest_of, grid_for(n_own, T), T, 0, A.pfof.p, ddest.p, n_own, A.dest.p);
+    VR_CUDA(cudaStreamSynchronize(ctx->stream)); // hdest / ddest go out of scope
 }
 
 } // namespace
@@ -678,6 +739,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
     }
     VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "6DFOF / unbinding need velocities");
     KScope kall(ctx, "mg.consolidate_total");
+    mg_place_groups(ctx, A, n_own, o);
 
     // ---- consolidate every boundary group on the rank of its root label (MPIGroupExchange) ----
     std::vector<DBuf<uint32_t>> eidx(N);
