@@ -48,3 +48,34 @@ def test_single_halo_search_full_set(gpu_ctx, oracle, fofbgtype, pp):
     if ndiff == 0:
         assert ngot == want["ngroups"] and np.array_equal(got, want["pfof"])
     assert np.array_equal(parts["pos"], pos) and np.array_equal(parts["vel"], vel)
+
+
+@pytest.mark.parametrize("pattern", ["zero_mean", "zero_axis", "ties", "equal_mass_drift", "mixed_mass"])
+def test_big_group_dispersion_is_bit_exact(gpu_ctx, oracle, pattern):
+    """The velocity dispersion of a large group is a left-to-right fp64 sum in the reference (search.cxx:480-493); groups
+    above 4096 members take the integer-scan evaluation (csrc/seqsum.h).  Membership and the scaled/unscaled coordinates
+    (Q3) depend on every bit of it, so comparing those with the oracle pins the sum."""
+    import vrgpu
+    n = 30000
+    rng = np.random.default_rng({"zero_mean": 1, "zero_axis": 2, "ties": 3, "equal_mass_drift": 4, "mixed_mass": 5}[pattern])
+    pos = rng.normal(size=(n, 3)) * 0.3 + 50.0
+    vel = rng.normal(size=(n, 3)) * 200.0
+    mass = np.full(n, float(np.float32(0.0207)))
+    if pattern == "zero_axis":
+        vel[:, 0] = 0.0
+    elif pattern == "ties":
+        vel = np.round(vel * 2.0) / 2.0
+        mass[:] = 0.5
+    elif pattern == "equal_mass_drift":
+        vel += np.array([700.0, -300.0, 50.0])
+    elif pattern == "mixed_mass":
+        mass = mass * (1.0 + (rng.random(n) < 0.1) * 7.0) * rng.choice([1.0, 1e-3, 1e3], size=n)
+    vel = vel.astype(np.float32).astype(np.float64)
+    pf3 = np.ones(n, dtype=np.int64)
+    pid = np.arange(1, n + 1, dtype=np.int64)
+    for mode in (3, 4):
+        want = oracle.fof6d(pos, vel, mass, pf3, 1, 0.05, 1.25, mode, 20, pid)
+        parts = vrgpu.particles_from_arrays(pos, vel, mass, pid)
+        got, ng = gpu_ctx.fof6d(parts, pf3, 1, 0.05, 1.25, mode, 20)
+        assert ng == want["ngroups"] and np.array_equal(got, want["pfof"])
+        assert np.array_equal(parts["vel"], want["vel"]) and np.array_equal(parts["pos"], want["pos"])

@@ -21,6 +21,7 @@
 //      ReorderGroupIDs, canonicalised).
 #include "groups.cuh"
 #include "stages.cuh"
+#include "seqsum.h"
 #include "ufhash.cuh"
 
 #include <algorithm>
@@ -35,8 +36,141 @@ constexpr uint64_t CMASK = (1ull << CBITS) - 1;
 // ---------------------------------------------------------------------------------------------------
 // per-group velocity scale
 // ---------------------------------------------------------------------------------------------------
+// Sequential-order sums.  The reference accumulates left to right (search.cxx:443-493) and 6DFOF membership depends on
+// every bit of the dispersion, so the order is kept.  Groups below SQ_MIN members: one warp per group running the
+// dependent DADD chain.  Larger groups: one CTA per group evaluating the same chain with the exact integer scan of
+// seqsum.h (windows of SQ_W terms; plain adds only where the running sum changes binade).
+// ---------------------------------------------------------------------------------------------------
+constexpr int SQ_NT = 512, SQ_PER = 8, SQ_W = SQ_NT * SQ_PER;
+constexpr uint32_t SQ_MIN = 4096;
+
+struct SeqShared {
+    SeqMap wtot[SQ_NT / 32];
+    double s;
+    unsigned int firstbad;
+};
+
+// All SQ_NT threads of the CTA call this with the same arguments; term(k) is the k-th addend; every thread gets the sum.
+template <class Term> __device__ double block_seqsum(Term term, unsigned long long n, double s0, SeqShared &sh)
+{
+    const unsigned tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    unsigned long long pos = 0;
+    double s = s0;
+    unsigned stretch = 32;
+    while (pos < n) {
+        long long S0;
+        int eu;
+        if (seq_decode_sum(s, S0, eu)) {
+            const unsigned w = (unsigned)min((unsigned long long)SQ_W, n - pos);
+            const unsigned k0 = tid * SQ_PER;
+            SeqMap tm[SQ_PER];
+            SeqMap inc = seq_identity();
+#pragma unroll
+            for (int j = 0; j < SQ_PER; j++) {
+                tm[j] = (k0 + j < w) ? seq_term_map(term(pos + k0 + j), eu) : seq_identity();
+                inc = seq_compose(inc, tm[j]);
+            }
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                SeqMap o;
+                o.e = __shfl_up_sync(0xffffffffu, inc.e, d);
+                o.o = __shfl_up_sync(0xffffffffu, inc.o, d);
+                if ((int)lane >= d) inc = seq_compose(o, inc);
+            }
+            if (lane == 31) sh.wtot[wid] = inc;
+            if (tid == 0) sh.firstbad = w;
+            __syncthreads();
+            SeqMap pre = seq_identity();
+            for (unsigned q = 0; q < wid; q++) pre = seq_compose(pre, sh.wtot[q]);
+            SeqMap ex;
+            ex.e = __shfl_up_sync(0xffffffffu, inc.e, 1);
+            ex.o = __shfl_up_sync(0xffffffffu, inc.o, 1);
+            if (lane == 0) ex = seq_identity();
+            pre = seq_compose(pre, ex);
+            long long S = seq_apply(S0, pre), Sb = 0;
+            unsigned bad = w;
+#pragma unroll
+            for (int j = 0; j < SQ_PER; j++) {
+                if (k0 + j < w && bad == w) {
+                    const long long Sn = seq_apply(S, tm[j]);
+                    if (!seq_in_binade(Sn)) { bad = k0 + j; Sb = S; }
+                    else S = Sn;
+                }
+            }
+            if (bad < w) atomicMin(&sh.firstbad, bad);
+            __syncthreads();
+            const unsigned fb = sh.firstbad;
+            if (fb == w) {
+                if (tid == (w - 1) / SQ_PER) sh.s = seq_encode_sum(S, eu);
+            } else if (bad == fb)
+                sh.s = fb > 0 ? seq_encode_sum(Sb, eu) : s;
+            __syncthreads();
+            s = sh.s;
+            if (fb == w) {
+                pos += w;
+                stretch = 32;
+                continue;
+            }
+            pos += fb;
+            stretch = fb >= 64 ? 32u : min(stretch * 2u, 4096u);
+        } else
+            stretch = min(stretch * 2u, 4096u);
+        // plain adds across the change of binade (or while the sum is zero / subnormal / not finite)
+        const unsigned c = (unsigned)min((unsigned long long)stretch, n - pos);
+        __syncthreads(); // everybody has read sh.s
+        if (tid == 0) {
+            double a = s;
+            for (unsigned k = 0; k < c; k++) a = __dadd_rn(a, term(pos + k));
+            sh.s = a;
+        }
+        __syncthreads();
+        s = sh.s;
+        pos += c;
+    }
+    __syncthreads();
+    return s;
+}
+
+struct TermMomentum { // m v of member k (search.cxx:482-484)
+    const double *v, *m;
+    __device__ double operator()(unsigned long long k) const { return __dmul_rn(v[k], m[k]); }
+};
+struct TermMass {
+    const double *m;
+    __device__ double operator()(unsigned long long k) const { return m[k]; }
+};
+struct TermDispersion { // pow(v_c - vmean_c, 2) * m for c = x, y, z of member k/3 (search.cxx:489)
+    const double *vx, *vy, *vz, *m;
+    double mx, my, mz;
+    __device__ double operator()(unsigned long long k) const
+    {
+        const unsigned long long i = k / 3ull;
+        const unsigned c = (unsigned)(k - 3ull * i);
+        const double d = __dsub_rn(c == 0 ? vx[i] : (c == 1 ? vy[i] : vz[i]), c == 0 ? mx : (c == 1 ? my : mz));
+        return __dmul_rn(__dmul_rn(d, d), m[i]);
+    }
+};
+
 // FOF6DADAPTIVE (search.cxx:480-493): vmean = sum(m v)/sum(m); vscale2 = sum_k pow(v_k - vmean_k, 2) m / sum(m) * vfac^2.
-// One warp per group; all lanes carry the same sequential sums (the chain is the reference's order).
+// One CTA per group of at least SQ_MIN members (group ids are size-descending: the other CTAs leave at once).
+__global__ void __launch_bounds__(SQ_NT) k_group_dispersion_big(const double *__restrict__ vx, const double *__restrict__ vy,
+                                                                const double *__restrict__ vz, const double *__restrict__ m,
+                                                                const uint32_t *__restrict__ off, double vfac, double *__restrict__ vs2)
+{
+    __shared__ SeqShared sh;
+    const uint32_t g = blockIdx.x + 1;
+    const uint32_t s0 = off[g], n = off[g + 1] - s0;
+    if (n < SQ_MIN) return;
+    const double sx = block_seqsum(TermMomentum{vx + s0, m + s0}, n, 0.0, sh);
+    const double sy = block_seqsum(TermMomentum{vy + s0, m + s0}, n, 0.0, sh);
+    const double sz = block_seqsum(TermMomentum{vz + s0, m + s0}, n, 0.0, sh);
+    const double sm = block_seqsum(TermMass{m + s0}, n, 0.0, sh);
+    const TermDispersion td{vx + s0, vy + s0, vz + s0, m + s0, __ddiv_rn(sx, sm), __ddiv_rn(sy, sm), __ddiv_rn(sz, sm)};
+    const double acc = block_seqsum(td, 3ull * n, 0.0, sh);
+    if (threadIdx.x == 0) vs2[g] = __dmul_rn(__dmul_rn(__ddiv_rn(acc, sm), vfac), vfac);
+}
+
+// Groups below SQ_MIN members.  One warp per group; all lanes carry the same sequential sums.
 __global__ void __launch_bounds__(256) k_group_dispersion(const double *__restrict__ vx, const double *__restrict__ vy,
                                                           const double *__restrict__ vz, const double *__restrict__ m,
                                                           const uint32_t *__restrict__ off, uint32_t ngroups, double vfac,
@@ -44,9 +178,9 @@ __global__ void __launch_bounds__(256) k_group_dispersion(const double *__restri
 {
     const unsigned lane = threadIdx.x & 31;
     const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
-    // big groups first: group ids are size-descending, so a plain grid-stride already starts the long chains early
     for (uint32_t g = 1 + wg; g <= ngroups; g += nw) {
         const uint32_t s0 = off[g], s1 = off[g + 1];
+        if (s1 - s0 >= SQ_MIN) continue; // k_group_dispersion_big
         double sx = 0, sy = 0, sz = 0, sm = 0;
         for (uint32_t base = s0; base < s1; base += 32) {
             const uint32_t s = base + lane;
@@ -56,22 +190,12 @@ __global__ void __launch_bounds__(256) k_group_dispersion(const double *__restri
                 px = __dmul_rn(vx[s], mm); py = __dmul_rn(vy[s], mm); pz = __dmul_rn(vz[s], mm);
             }
             const int cnt = (int)min(32u, s1 - base);
-            if (cnt == 32) {
-                // full chunk: unrolled, so the shuffles run ahead and only the dependent DADD chain remains
-#pragma unroll
-                for (int t = 0; t < 32; t++) {
-                    sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
-                    sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
-                    sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
-                    sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
-                }
-            } else
-                for (int t = 0; t < cnt; t++) {
-                    sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
-                    sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
-                    sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
-                    sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
-                }
+            for (int t = 0; t < cnt; t++) {
+                sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
+                sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
+                sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
+                sm = __dadd_rn(sm, __shfl_sync(0xffffffffu, mm, t));
+            }
         }
         const double mx = __ddiv_rn(sx, sm), my = __ddiv_rn(sy, sm), mz = __ddiv_rn(sz, sm);
         double acc = 0;
@@ -85,64 +209,31 @@ __global__ void __launch_bounds__(256) k_group_dispersion(const double *__restri
                 d = __dsub_rn(vz[s], mz); tz = __dmul_rn(__dmul_rn(d, d), mm);
             }
             const int cnt = (int)min(32u, s1 - base);
-            if (cnt == 32) {
-#pragma unroll
-                for (int t = 0; t < 32; t++) {
-                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
-                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
-                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
-                }
-            } else
-                for (int t = 0; t < cnt; t++) {
-                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
-                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
-                    acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
-                }
+            for (int t = 0; t < cnt; t++) {
+                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
+                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
+                acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
+            }
         }
         if (lane == 0) vs2[g] = __dmul_rn(__dmul_rn(__ddiv_rn(acc, sm), vfac), vfac);
     }
 }
 
 // FOF6D single scale (search.cxx:443-470) INCLUDING quirk Q1: the mass normalisation is ONE particle's mass (the
-// particle that follows the largest group in the group-sorted array).  One warp; result broadcast to every chunk.
-__global__ void k_single_dispersion(const double *__restrict__ vx, const double *__restrict__ vy, const double *__restrict__ vz,
-                                    const double *__restrict__ m, uint32_t n1, double mnorm, double vfac, uint32_t nchunks,
-                                    double *__restrict__ vs2)
+// particle that follows the largest group in the group-sorted array).  One CTA; result broadcast to every chunk.
+__global__ void __launch_bounds__(SQ_NT) k_single_dispersion(const double *__restrict__ vx, const double *__restrict__ vy,
+                                                             const double *__restrict__ vz, const double *__restrict__ m, uint32_t n1,
+                                                             double mnorm, double vfac, uint32_t nchunks, double *__restrict__ vs2)
 {
-    const unsigned lane = threadIdx.x & 31;
-    double sx = 0, sy = 0, sz = 0;
-    for (uint32_t base = 0; base < n1; base += 32) {
-        const uint32_t s = base + lane;
-        double px = 0, py = 0, pz = 0;
-        if (s < n1) { const double mm = m[s]; px = __dmul_rn(vx[s], mm); py = __dmul_rn(vy[s], mm); pz = __dmul_rn(vz[s], mm); }
-        const int cnt = (int)min(32u, n1 - base);
-        for (int t = 0; t < cnt; t++) {
-            sx = __dadd_rn(sx, __shfl_sync(0xffffffffu, px, t));
-            sy = __dadd_rn(sy, __shfl_sync(0xffffffffu, py, t));
-            sz = __dadd_rn(sz, __shfl_sync(0xffffffffu, pz, t));
-        }
-    }
-    const double mx = __ddiv_rn(sx, mnorm), my = __ddiv_rn(sy, mnorm), mz = __ddiv_rn(sz, mnorm);
-    double acc = 0;
-    for (uint32_t base = 0; base < n1; base += 32) {
-        const uint32_t s = base + lane;
-        double tx = 0, ty = 0, tz = 0;
-        if (s < n1) {
-            const double mm = m[s];
-            double d = __dsub_rn(vx[s], mx); tx = __dmul_rn(__dmul_rn(d, d), mm);
-            d = __dsub_rn(vy[s], my); ty = __dmul_rn(__dmul_rn(d, d), mm);
-            d = __dsub_rn(vz[s], mz); tz = __dmul_rn(__dmul_rn(d, d), mm);
-        }
-        const int cnt = (int)min(32u, n1 - base);
-        for (int t = 0; t < cnt; t++) {
-            acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tx, t));
-            acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ty, t));
-            acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, tz, t));
-        }
-    }
+    __shared__ SeqShared sh;
+    const double sx = block_seqsum(TermMomentum{vx, m}, n1, 0.0, sh);
+    const double sy = block_seqsum(TermMomentum{vy, m}, n1, 0.0, sh);
+    const double sz = block_seqsum(TermMomentum{vz, m}, n1, 0.0, sh);
+    const TermDispersion td{vx, vy, vz, m, __ddiv_rn(sx, mnorm), __ddiv_rn(sy, mnorm), __ddiv_rn(sz, mnorm)};
+    double acc = block_seqsum(td, 3ull * n1, 0.0, sh);
     if (mnorm > 0) acc = __ddiv_rn(acc, mnorm);
     acc = __dmul_rn(acc, __dmul_rn(vfac, vfac)); // search.cxx:464
-    for (uint32_t g = 1 + lane; g <= nchunks; g += 32) vs2[g] = acc;
+    for (uint32_t g = 1 + threadIdx.x; g <= nchunks; g += blockDim.x) vs2[g] = acc;
 }
 
 // ScalePhase (search.cxx:565-568) on the group-major columns; optionally the un-scaled values (search.cxx:573-575,
@@ -501,16 +592,17 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
             }
             // group 1 is chunk 1 unless it was itself merged (then its members are no longer contiguous: use the 3D layout)
             if (nchunks >= 2 || ngroups3d == 1) {
-                VR_LAUNCH(ctx, k_single_dispersion, 1, 32, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
+                VR_LAUNCH(ctx, k_single_dispersion, 1, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
             } else {
                 GroupSet g0;
                 build_groupset(ctx, pfof3d_dev, P.n, ngroups3d, g0);
                 gather_groupset(ctx, P, g0, true, true);
-                VR_LAUNCH(ctx, k_single_dispersion, 1, 32, 0, g0.vx.p, g0.vy.p, g0.vz.p, g0.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
+                VR_LAUNCH(ctx, k_single_dispersion, 1, SQ_NT, 0, g0.vx.p, g0.vy.p, g0.vz.p, g0.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
                 VR_CUDA(cudaStreamSynchronize(ctx->stream));
             }
         } else {
             const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 8u));
+            VR_LAUNCH(ctx, k_group_dispersion_big, G, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, vfac, vs2.p);
             VR_LAUNCH(ctx, k_group_dispersion, grid, T, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, G, vfac, vs2.p);
         }
     }

@@ -13,9 +13,9 @@
 //     segment are the left child.  Finished leaves carry key (index, 0) and keep their place;
 //   * node monopoles bottom-up (leaf sums sequentially in tree order, parents = sum of children: deterministic),
 //     Bmax by ordered-integer atomicMax along every particle's root-to-leaf path, cR2max = 4/3 Bmax^2 / theta^2;
-//   * walk: one thread per particle (tree order, so a warp walks neighbouring paths), explicit stack, MarkCell's
-//     opening test r2 < cR2max evaluated in the reference's operation order, monopole and leaf terms accumulated in
-//     fp64 in visiting order.
+//   * walk: one warp per 32 particles consecutive in tree order; the warp walks the union of its lanes' paths without a
+//     stack (64-byte node records with a "next" link), each lane applying MarkCell's opening test r2 < cR2max in the
+//     reference's operation order and accumulating monopole and leaf terms in fp64 in the reference's visiting order.
 // Node MEMBERSHIP equals the reference's whenever the coordinates along a split dimension are distinct at the median
 // (the reference's quickselect leaves the choice among exactly equal coordinates to its swap sequence; here the tie
 // goes to the lower member index) -- see DESIGN.md "tree parity".
@@ -291,47 +291,93 @@ __device__ __forceinline__ double pt_rsqrt(double r2)
 }
 
 // ---- walk (MarkCell, unbind.cxx:24-44 + the sums at :1710-1723) ---------------------------------------------
-constexpr int PT_STACK = 96;
-__global__ void __launch_bounds__(128) k_pt_walk(PtNodes N, const uint32_t *__restrict__ rootidx, uint32_t nL, const double *__restrict__ tx,
-                                                 const double *__restrict__ ty, const double *__restrict__ tz, const double *__restrict__ tm,
-                                                 double G, double eps2, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of,
-                                                 double *__restrict__ phi, unsigned long long *__restrict__ ninter, unsigned int *__restrict__ overflow)
+// One 64-byte record per node, and a "next" link (the node that follows the whole subtree in the reference's
+// left-before-right recursion) so the walk needs no stack.
+struct __align__(16) PtNode64 {
+    double cx, cy, cz, r2max;
+    double sm;
+    uint32_t left, start;
+    uint32_t end, next;
+    uint32_t pad[2];
+};
+static_assert(sizeof(PtNode64) == 64, "node record is 4 x 16 bytes");
+
+__global__ void k_pt_next(const uint32_t *__restrict__ left, uint32_t *__restrict__ next, uint32_t n0, uint32_t n1)
+{
+    const uint32_t nd = n0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= n1) return;
+    const uint32_t l = left[nd];
+    if (l == NOCHILD) return;
+    next[l] = l + 1;
+    next[l + 1] = next[nd];
+}
+__global__ void k_pt_pack(PtNodes N, const uint32_t *__restrict__ next, uint32_t nnodes, PtNode64 *__restrict__ out)
+{
+    const uint32_t nd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (nd >= nnodes) return;
+    PtNode64 r;
+    r.cx = N.sx[nd]; r.cy = N.sy[nd]; r.cz = N.sz[nd]; r.r2max = N.r2max[nd]; r.sm = N.sm[nd];
+    r.left = N.left[nd]; r.start = N.start[nd]; r.end = N.end[nd]; r.next = next[nd];
+    r.pad[0] = r.pad[1] = 0;
+    out[nd] = r;
+}
+
+// One warp walks the tree ONCE for its 32 particles (consecutive in tree order, so their walks overlap almost entirely):
+// the warp descends wherever any of its lanes opens a node; a lane that accepts a node's monopole idles until the walk
+// leaves that subtree (cur == the node's next link).  Every lane therefore sees exactly the nodes, in exactly the order,
+// of the reference's per-particle recursion, and node records are fetched once per warp instead of once per lane.
+constexpr uint32_t PT_ACTIVE = 0xfffffffeu;
+__global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ nodes, const uint32_t *__restrict__ rootidx, uint32_t nL,
+                                                 const double *__restrict__ tx, const double *__restrict__ ty, const double *__restrict__ tz,
+                                                 const double *__restrict__ tm, double G, double eps2, const uint32_t *__restrict__ perm,
+                                                 const uint32_t *__restrict__ slot_of, double *__restrict__ phi,
+                                                 unsigned long long *__restrict__ ninter)
 {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = p < nL;
+    const uint32_t myroot = valid ? rootidx[p] : NOCHILD;
+    double x = 0, y = 0, z = 0, mj = 0;
+    if (valid) { x = tx[p]; y = ty[p]; z = tz[p]; mj = tm[p]; }
+    double acc = 0.0;
     unsigned long long cnt = 0;
-    if (p < nL) {
-        const double x = tx[p], y = ty[p], z = tz[p], mj = tm[p];
-        uint32_t stack[PT_STACK];
-        int sp = 0;
-        stack[sp++] = rootidx[p];
-        double acc = 0.0;
-        while (sp > 0) {
-            const uint32_t nd = stack[--sp];
-            const double dx = __dsub_rn(N.sx[nd], x), dy = __dsub_rn(N.sy[nd], y), dz = __dsub_rn(N.sz[nd], z);
+    unsigned todo = __ballot_sync(0xffffffffu, valid);
+    while (todo) {
+        const uint32_t root = __shfl_sync(0xffffffffu, myroot, __ffs(todo) - 1);
+        const bool mine = valid && myroot == root;
+        todo &= ~__ballot_sync(0xffffffffu, mine);
+        uint32_t cur = root, wait = PT_ACTIVE;
+        while (cur != NOCHILD) {
+            const double2 *q = reinterpret_cast<const double2 *>(nodes + cur);
+            const double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+            const uint2 d = __ldg(reinterpret_cast<const uint2 *>(q + 3));
+            const uint32_t left = (uint32_t)(__double_as_longlong(c.y) & 0xffffffffll);
+            const uint32_t start = (uint32_t)((unsigned long long)__double_as_longlong(c.y) >> 32);
+            const uint32_t end = d.x, next = d.y;
+            if (wait == cur) wait = PT_ACTIVE;
+            const bool act = mine && wait == PT_ACTIVE;
+            const double dx = __dsub_rn(a.x, x), dy = __dsub_rn(a.y, y), dz = __dsub_rn(b.x, z);
             const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-            if (r2 < N.r2max[nd]) {
-                const uint32_t lc = N.left[nd];
-                if (lc != NOCHILD) {
-                    if (sp + 2 > PT_STACK) { atomicAdd(overflow, 1u); break; }
-                    stack[sp++] = lc + 1; // right is visited after left
-                    stack[sp++] = lc;
-                } else {
-                    const uint32_t s = N.start[nd], e = N.end[nd];
-                    for (uint32_t l = s; l < e; l++) {
-                        if (l == p) continue;
-                        const double ax = __dsub_rn(x, tx[l]), ay = __dsub_rn(y, ty[l]), az = __dsub_rn(z, tz[l]);
-                        const double q2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)), eps2);
-                        acc -= (mj * tm[l]) * pt_rsqrt(q2);
-                        cnt++;
-                    }
-                }
-            } else {
-                acc -= mj * (N.sm[nd] * pt_rsqrt(r2 + eps2));
+            const bool open = act && r2 < b.y;
+            if (act && !open) {
+                acc -= mj * (c.x * pt_rsqrt(r2 + eps2));
                 cnt++;
+                wait = next;
             }
+            if (!__any_sync(0xffffffffu, open)) { cur = next; continue; }
+            if (left != NOCHILD) { cur = left; continue; }
+            for (uint32_t l = start; l < end; l++) {
+                const double lx = __ldg(tx + l), ly = __ldg(ty + l), lz = __ldg(tz + l), lm = __ldg(tm + l);
+                if (open && l != p) {
+                    const double ax = __dsub_rn(x, lx), ay = __dsub_rn(y, ly), az = __dsub_rn(z, lz);
+                    const double q2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)), eps2);
+                    acc -= (mj * lm) * pt_rsqrt(q2);
+                    cnt++;
+                }
+            }
+            cur = next;
         }
-        phi[slot_of[perm[p]]] = acc * G;
     }
+    if (valid) phi[slot_of[perm[p]]] = acc * G;
     for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(ninter, cnt);
 }
@@ -451,20 +497,23 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     }
     // ---- walk ----
     DBuf<unsigned long long> ninter(ctx, 1);
-    DBuf<unsigned int> overflow(ctx, 1);
+    DBuf<PtNode64> packed(ctx, nnodes);
     VR_CUDA(cudaMemsetAsync(ninter.p, 0, sizeof(unsigned long long), ctx->stream));
-    VR_CUDA(cudaMemsetAsync(overflow.p, 0, sizeof(unsigned int), ctx->stream));
     {
         KScope k(ctx, "ptree.walk");
-        VR_LAUNCH(ctx, k_pt_walk, grid_for(nL, 128), 128, 0, N, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p, phi,
-                  ninter.p, overflow.p);
+        DBuf<uint32_t> next(ctx, nnodes);
+        VR_CUDA(cudaMemsetAsync(next.p, 0xff, sizeof(uint32_t) * nLG, ctx->stream)); // roots: nothing follows
+        for (size_t l = 0; l + 1 < level_off.size(); l++) {
+            const uint32_t n0 = level_off[l], n1 = level_off[l + 1];
+            if (n1 > n0) VR_LAUNCH(ctx, k_pt_next, grid_for(n1 - n0, T), T, 0, nleft.p, next.p, n0, n1);
+        }
+        VR_LAUNCH(ctx, k_pt_pack, grid_for(nnodes, T), T, 0, N, next.p, nnodes, packed.p);
+        VR_LAUNCH(ctx, k_pt_walk, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
+                  phi, ninter.p);
     }
     unsigned long long hi = 0;
-    unsigned int hov = 0;
     VR_CUDA(cudaMemcpyAsync(&hi, ninter.p, sizeof(hi), cudaMemcpyDeviceToHost, ctx->stream));
-    VR_CUDA(cudaMemcpyAsync(&hov, overflow.p, sizeof(hov), cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
-    VR_REQUIRE(hov == 0, VRGPU_ECUDA, "kd-tree walk stack overflow");
     ctx->stats.n_tree_interactions += (long long)hi;
     ctx->stats.n_tree_nodes += (long long)nnodes;
 }

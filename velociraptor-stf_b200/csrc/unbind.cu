@@ -78,12 +78,49 @@ __device__ __forceinline__ void member_energy(const UbArrays &A, const UbParams 
 }
 
 // CM velocity and mass of every group (unbind.cxx:447-455): one warp per group, fixed reduction shape
+constexpr uint32_t CM_BIG = 32768; // members from which a whole CTA sums one group (fixed order: deterministic)
+
+__global__ void __launch_bounds__(1024) k_group_cm_big(UbArrays A)
+{
+    __shared__ double red[4][32];
+    const uint32_t g = blockIdx.x + 1;
+    const uint32_t s0 = A.off[g], s1 = A.off[g + 1];
+    if (s1 - s0 < CM_BIG) return;
+    const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    double sm = 0, sx = 0, sy = 0, sz = 0;
+    for (uint32_t s = s0 + threadIdx.x; s < s1; s += 1024) {
+        const double m = A.m[s];
+        sm += m; sx += A.vx[s] * m; sy += A.vy[s] * m; sz += A.vz[s] * m;
+    }
+    for (int o = 16; o; o >>= 1) {
+        sm += __shfl_xor_sync(0xffffffffu, sm, o); sx += __shfl_xor_sync(0xffffffffu, sx, o);
+        sy += __shfl_xor_sync(0xffffffffu, sy, o); sz += __shfl_xor_sync(0xffffffffu, sz, o);
+    }
+    if (lane == 0) { red[0][wid] = sm; red[1][wid] = sx; red[2][wid] = sy; red[3][wid] = sz; }
+    __syncthreads();
+    if (wid == 0) {
+        sm = red[0][lane]; sx = red[1][lane]; sy = red[2][lane]; sz = red[3][lane];
+        for (int o = 16; o; o >>= 1) {
+            sm += __shfl_xor_sync(0xffffffffu, sm, o); sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            sy += __shfl_xor_sync(0xffffffffu, sy, o); sz += __shfl_xor_sync(0xffffffffu, sz, o);
+        }
+        if (lane == 0) {
+            const double inv = 1.0 / sm;
+            A.gmass[g] = sm;
+            A.cmvel[3 * g] = sx * inv; A.cmvel[3 * g + 1] = sy * inv; A.cmvel[3 * g + 2] = sz * inv;
+            A.ning[g] = s1 - s0;
+            A.status[g] = 0;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) k_group_cm(UbArrays A, uint32_t ngroups)
 {
     const unsigned lane = threadIdx.x & 31;
     const uint32_t wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t g = 1 + wg; g <= ngroups; g += nw) {
         uint32_t s0 = A.off[g], s1 = A.off[g + 1];
+        if (s1 - s0 >= CM_BIG) continue; // k_group_cm_big
         double sm = 0, sx = 0, sy = 0, sz = 0;
         for (uint32_t s = s0 + lane; s < s1; s += 32) {
             double m = A.m[s];
@@ -532,6 +569,7 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
     const unsigned warp_grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 16u));
 
     { KScope k(ctx, "unbind.cm_frame"); VR_LAUNCH(ctx, k_init_slots, grid_for(ntot, T), T, 0, A, ntot);
+    VR_LAUNCH(ctx, k_group_cm_big, G, 1024, 0, A);
     VR_LAUNCH(ctx, k_group_cm, warp_grid, T, 0, A, G); }
 
     // ---- phase A ----
