@@ -8,6 +8,7 @@
 // groups or be a slice of one big group); the j-range it has to visit is [off[g_first], off[g_last + 1]) and is
 // streamed through shared memory in tiles of 256.  FP64-pipe bound: ~14 DP instructions per pair.
 #include "groups.cuh"
+#include "rsqrt.cuh"
 
 #include <algorithm>
 
@@ -16,19 +17,6 @@ namespace vrgpu {
 constexpr int PT = 256; // threads per CTA
 constexpr int PI = 4;   // slots per thread (register tiling: every shared-memory j serves PI pair evaluations)
 constexpr int PS = PT * PI;
-
-// 1/sqrt(r2): hardware seed (rsqrt.approx.f64 = MUFU.RSQ64H on the high word, ~2^-22) + one fp64 Newton step (4 DP
-// instructions, relative error ~1e-13); zero / denormal / huge arguments take the exact path (inf for r2 == 0, like the
-// reference).
-__device__ __forceinline__ double rsqrt_refined(double r2)
-{
-    double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(r2));
-    if (!(r2 > 1e-290) || !(r2 < 1e290)) return 1.0 / sqrt(r2);
-    const double h = 0.5 * r2;
-    y = y * (1.5 - h * y * y);
-    return y;
-}
 
 __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                                                          const double *__restrict__ m, const uint32_t *__restrict__ gid,
@@ -72,12 +60,22 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
             for (int jj = 0; jj < cnt; jj++) {
                 const double2 qa = sxy[jj], qb = szm[jj];
                 const double qx = qa.x, qy = qa.y, qz = qb.x, qm = qb.y;
+                double r2[PI], ri[PI];
+                bool odd = false;
 #pragma unroll
                 for (int k = 0; k < PI; k++) {
                     const double dx = xi[k] - qx, dy = yi[k] - qy, dz = zi[k] - qz;
-                    const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-                    acc[k] = fma(qm, rsqrt_refined(r2), acc[k]);
+                    r2[k] = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+                    ri[k] = rsqrt_fast(r2[k]);
+                    odd |= rsqrt_out_of_range(r2[k]);
                 }
+                if (odd) {
+#pragma unroll
+                    for (int k = 0; k < PI; k++)
+                        if (rsqrt_out_of_range(r2[k])) ri[k] = 1.0 / sqrt(r2[k]);
+                }
+#pragma unroll
+                for (int k = 0; k < PI; k++) acc[k] = fma(qm, ri[k], acc[k]);
             }
         } else {
             for (int jj = 0; jj < cnt; jj++) {
@@ -185,14 +183,24 @@ __global__ void __launch_bounds__(PT) k_potential_sym(const double *__restrict__
                 for (int st = 0; st < 32; st++) {
                     const int jj = (blk << 5) + (int)((lane + st) & 31);
                     const double2 qa = sxy[jj], qb = szm[jj];
-                    double tj = 0;
+                    double tj = 0, r2[PI], ri[PI];
+                    bool odd = false;
 #pragma unroll
                     for (int k = 0; k < PI; k++) {
                         const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
-                        const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-                        const double ri = rsqrt_refined(r2);
-                        acc[k] = fma(qb.y, ri, acc[k]);
-                        tj = fma(mi[k], ri, tj);
+                        r2[k] = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+                        ri[k] = rsqrt_fast(r2[k]);
+                        odd |= rsqrt_out_of_range(r2[k]);
+                    }
+                    if (odd) {
+#pragma unroll
+                        for (int k = 0; k < PI; k++)
+                            if (rsqrt_out_of_range(r2[k])) ri[k] = 1.0 / sqrt(r2[k]);
+                    }
+#pragma unroll
+                    for (int k = 0; k < PI; k++) {
+                        acc[k] = fma(qb.y, ri[k], acc[k]);
+                        tj = fma(mi[k], ri[k], tj);
                     }
                     sacc[w][jj] += tj;
                     __syncwarp();

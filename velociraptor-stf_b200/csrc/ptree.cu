@@ -20,6 +20,7 @@
 // (the reference's quickselect leaves the choice among exactly equal coordinates to its swap sequence; here the tie
 // goes to the lower member index) -- see DESIGN.md "tree parity".
 #include "groups.cuh"
+#include "rsqrt.cuh"
 #include "ufhash.cuh"
 
 #include <algorithm>
@@ -100,10 +101,13 @@ __global__ void k_pt_iota(uint32_t *__restrict__ a, uint32_t n)
 }
 
 // ---- one level ----------------------------------------------------------------------------------------
-__global__ void k_pt_heads(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ nstart, uint32_t *__restrict__ heads)
+__global__ void k_pt_heads(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ nstart, uint32_t nAct,
+                           uint32_t *__restrict__ heads)
 {
     uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < nF) heads[nstart[frontier[f]]] = 1u;
+    if (f >= nF) return;
+    const uint32_t s = nstart[frontier[f]];
+    if (s < nAct) heads[s] = 1u;
 }
 // fidx[pos] = index of the frontier entry that contains pos (exclusive scan of heads, + head - 1)
 __global__ void k_pt_fidx(const uint32_t *__restrict__ heads, const uint32_t *__restrict__ excl, uint32_t nL, uint32_t *__restrict__ fidx)
@@ -170,10 +174,10 @@ __global__ void k_pt_choose(const uint32_t *__restrict__ frontier, uint32_t nF, 
 
 __global__ void k_pt_level_keys(const uint32_t *__restrict__ perm, const uint32_t *__restrict__ fidx, const uint32_t *__restrict__ splitflag,
                                 const uint32_t *__restrict__ splitdim, const uint32_t *__restrict__ rank /* 3 x nL */, uint32_t nL,
-                                int rb, uint64_t *__restrict__ keys)
+                                uint32_t nAct, int rb, uint64_t *__restrict__ keys)
 {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= nL) return;
+    if (p >= nAct) return;
     const uint32_t f = fidx[p];
     uint32_t lo = 0;
     if (splitflag[f]) lo = rank[(size_t)splitdim[f] * nL + perm[p]];
@@ -279,16 +283,6 @@ __global__ void k_pt_r2max(PtNodes N, uint32_t nnodes, double theta)
     N.r2max[nd] = __ddiv_rn(__dmul_rn(__dmul_rn(4.0 / 3.0, xdiff), xdiff), __dmul_rn(theta, theta));
 }
 
-__device__ __forceinline__ double pt_rsqrt(double r2)
-{
-    float f = (float)r2;
-    if (!(f > 0.0f) || !(f < 3.0e38f)) return 1.0 / sqrt(r2);
-    double y = (double)rsqrtf(f);
-    const double h = 0.5 * r2;
-    y = y * (1.5 - h * y * y);
-    y = y * (1.5 - h * y * y); // second step: ~1e-16, so the sum is dominated by fp64 accumulation error only
-    return y;
-}
 
 // ---- walk (MarkCell, unbind.cxx:24-44 + the sums at :1710-1723) ---------------------------------------------
 // One 64-byte record per node, and a "next" link (the node that follows the whole subtree in the reference's
@@ -359,7 +353,7 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
             const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
             const bool open = act && r2 < b.y;
             if (act && !open) {
-                acc -= mj * (c.x * pt_rsqrt(r2 + eps2));
+                acc -= mj * (c.x * rsqrt_refined(r2 + eps2));
                 cnt++;
                 wait = next;
             }
@@ -370,7 +364,7 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
                 if (open && l != p) {
                     const double ax = __dsub_rn(x, lx), ay = __dsub_rn(y, ly), az = __dsub_rn(z, lz);
                     const double q2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)), eps2);
-                    acc -= (mj * lm) * pt_rsqrt(q2);
+                    acc -= (mj * lm) * rsqrt_refined(q2);
                     cnt++;
                 }
             }
@@ -448,19 +442,37 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     VR_LAUNCH(ctx, k_pt_iota, grid_for(nL, T), T, 0, perm.p, nL);
     uint32_t nF = nLG, nnodes = nLG;
     std::vector<uint32_t> level_off{0u, nLG};
+    // A group's largest node at level l holds ceil(n / 2^l) particles (median splits), so the group is finished once that
+    // is <= bucket: the per-particle passes of a level only cover positions below the end of the last unfinished group
+    // (groups come in size order from the search stages, so this prefix shrinks level by level).
+    std::vector<uint32_t> gstart(nLG), gend(nLG);
+    VR_CUDA(cudaMemcpyAsync(gstart.data(), nstart.p, sizeof(uint32_t) * nLG, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(gend.data(), nend.p, sizeof(uint32_t) * nLG, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    auto active_prefix = [&](int level) {
+        uint32_t top = 0;
+        for (uint32_t r = 0; r < nLG; r++) {
+            const uint64_t n = gend[r] - gstart[r];
+            const uint64_t big = level < 40 ? ((n + (1ull << level) - 1) >> level) : 1;
+            if (big > (uint64_t)bucket) top = std::max(top, gend[r]);
+        }
+        return top;
+    };
     const int rb = bits_for_u64v(nL > 1 ? nL - 1 : 1);
     PtCols C{gs.x.p, gs.y.p, gs.z.p};
     uint32_t *fr = frontier.p, *fr2 = frontier2.p;
     {
         KScope kb(ctx, "ptree.build");
         for (int level = 0; level < 64; level++) {
-            VR_CUDA(cudaMemsetAsync(heads.p, 0, sizeof(uint32_t) * nL, ctx->stream));
-            VR_LAUNCH(ctx, k_pt_heads, grid_for(nF, T), T, 0, fr, nF, nstart.p, heads.p);
-            exclusive_scan_u32(ctx, heads.p, hexcl.p, nL, nullptr);
-            VR_LAUNCH(ctx, k_pt_fidx, grid_for(nL, T), T, 0, heads.p, hexcl.p, nL, fidx.p);
+            const uint32_t nAct = level == 0 ? nL : active_prefix(level);
+            if (nAct == 0) break;
+            VR_CUDA(cudaMemsetAsync(heads.p, 0, sizeof(uint32_t) * nAct, ctx->stream));
+            VR_LAUNCH(ctx, k_pt_heads, grid_for(nF, T), T, 0, fr, nF, nstart.p, nAct, heads.p);
+            exclusive_scan_u32(ctx, heads.p, hexcl.p, nAct, nullptr);
+            VR_LAUNCH(ctx, k_pt_fidx, grid_for(nAct, T), T, 0, heads.p, hexcl.p, nAct, fidx.p);
             if (level == 0) VR_CUDA(cudaMemcpyAsync(rootidx.p, fidx.p, sizeof(uint32_t) * nL, cudaMemcpyDeviceToDevice, ctx->stream));
             VR_LAUNCH(ctx, k_pt_mm_init, grid_for((size_t)6 * nF, T), T, 0, mm.p, nF);
-            VR_LAUNCH(ctx, k_pt_minmax, grid_for(nL, T), T, 0, C, slot_of.p, perm.p, fidx.p, fr, nstart.p, nend.p, nL, (uint32_t)bucket, mm.p);
+            VR_LAUNCH(ctx, k_pt_minmax, grid_for(nAct, T), T, 0, C, slot_of.p, perm.p, fidx.p, fr, nstart.p, nend.p, nAct, (uint32_t)bucket, mm.p);
             VR_LAUNCH(ctx, k_pt_choose, grid_for(nF, T), T, 0, fr, nF, nstart.p, nend.p, (uint32_t)bucket, mm.p, splitflag.p, splitdim.p);
             exclusive_scan_u32(ctx, splitflag.p, fexcl.p, nF, total.p);
             uint32_t nsplit = 0;
@@ -468,8 +480,8 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             VR_CUDA(cudaStreamSynchronize(ctx->stream));
             if (nsplit == 0) break;
             VR_REQUIRE((size_t)nnodes + 2 * (size_t)nsplit <= cap, VRGPU_ECUDA, "kd-tree node capacity exceeded");
-            VR_LAUNCH(ctx, k_pt_level_keys, grid_for(nL, T), T, 0, perm.p, fidx.p, splitflag.p, splitdim.p, rank.p, nL, rb, keys.p);
-            radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nL, rb + bits_for_u64v(nF > 1 ? nF - 1 : 1));
+            VR_LAUNCH(ctx, k_pt_level_keys, grid_for(nAct, T), T, 0, perm.p, fidx.p, splitflag.p, splitdim.p, rank.p, nL, nAct, rb, keys.p);
+            radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nAct, rb + bits_for_u64v(nF > 1 ? nF - 1 : 1));
             VR_LAUNCH(ctx, k_pt_children, grid_for(nF, T), T, 0, fr, nF, splitflag.p, fexcl.p, nnodes, nstart.p, nend.p, nleft.p, fr2);
             nnodes += 2 * nsplit;
             nF += nsplit;
