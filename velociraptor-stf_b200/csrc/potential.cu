@@ -61,18 +61,18 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
                 const double2 qa = sxy[jj], qb = szm[jj];
                 const double qx = qa.x, qy = qa.y, qz = qb.x, qm = qb.y;
                 double r2[PI], ri[PI];
-                bool odd = false;
+                unsigned worst = 0;
 #pragma unroll
                 for (int k = 0; k < PI; k++) {
                     const double dx = xi[k] - qx, dy = yi[k] - qy, dz = zi[k] - qz;
                     r2[k] = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-                    ri[k] = rsqrt_fast(r2[k]);
-                    odd |= rsqrt_out_of_range(r2[k]);
+                    const double y0 = rsqrt_seed(r2[k]);
+                    worst = max(worst, (unsigned)__double2hiint(y0));
+                    ri[k] = rsqrt_newton(r2[k], y0);
                 }
-                if (odd) {
+                if (worst >= 0x5f300000u) {
 #pragma unroll
-                    for (int k = 0; k < PI; k++)
-                        if (rsqrt_out_of_range(r2[k])) ri[k] = 1.0 / sqrt(r2[k]);
+                    for (int k = 0; k < PI; k++) ri[k] = rsqrt_refined(r2[k]);
                 }
 #pragma unroll
                 for (int k = 0; k < PI; k++) acc[k] = fma(qm, ri[k], acc[k]);
@@ -101,8 +101,8 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
 // ---------------------------------------------------------------------------------------------------
 // symmetric direct sum for big groups: every unordered TILE pair (I <= J) of a group is one CTA.  The 1/r of a particle
 // pair is evaluated once and credited to both particles: acc_i in registers, the j side accumulated per warp in shared memory
-// and over the CTA through shared memory (lanes rotate over the j of a 32-block, so no shuffles are needed).  ~49 DP
-// instructions per 256 ordered pairs instead of 88.
+// and over the CTA through shared memory (lanes rotate over the j of a 32-block, so no shuffles are needed).  45 FP64-pipe
+// instructions per 4 unordered pairs (3 DADD + 3 DFMA + 3 Newton + 2 accumulate each, + 1 for the j side).
 // Partial sums of different CTAs meet in global fp64 atomics, so the last bits of phi depend on the arrival order
 // (relative 1e-16; DESIGN.md "determinism").
 // ---------------------------------------------------------------------------------------------------
@@ -124,7 +124,8 @@ __global__ void k_sym_count(const uint32_t *__restrict__ off, uint32_t ngroups, 
     npairs[g] = c;
 }
 
-__global__ void __launch_bounds__(PT) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+// 3 CTAs per SM (80 registers) and no unrolling of the rotation loop measured best (profiles/r01f)
+__global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                                                       const double *__restrict__ m, const uint32_t *__restrict__ off, uint32_t ngroups,
                                                       const unsigned long long *__restrict__ pair_start /* exclusive scan, ngroups+2 */,
                                                       double eps2, double *__restrict__ phiacc)
@@ -179,23 +180,23 @@ __global__ void __launch_bounds__(PT) k_potential_sym(const double *__restrict__
             // the j-side partial goes straight into the warp's shared row without any cross-lane reduction
             const int nblk = (cnt + 31) >> 5;
             for (int blk = 0; blk < nblk; blk++) {
-#pragma unroll 2
+#pragma unroll 1
                 for (int st = 0; st < 32; st++) {
                     const int jj = (blk << 5) + (int)((lane + st) & 31);
                     const double2 qa = sxy[jj], qb = szm[jj];
                     double tj = 0, r2[PI], ri[PI];
-                    bool odd = false;
+                    unsigned worst = 0;
 #pragma unroll
                     for (int k = 0; k < PI; k++) {
                         const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
                         r2[k] = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-                        ri[k] = rsqrt_fast(r2[k]);
-                        odd |= rsqrt_out_of_range(r2[k]);
+                        const double y0 = rsqrt_seed(r2[k]);
+                        worst = max(worst, (unsigned)__double2hiint(y0));
+                        ri[k] = rsqrt_newton(r2[k], y0);
                     }
-                    if (odd) {
+                    if (worst >= 0x5f300000u) {
 #pragma unroll
-                        for (int k = 0; k < PI; k++)
-                            if (rsqrt_out_of_range(r2[k])) ri[k] = 1.0 / sqrt(r2[k]);
+                        for (int k = 0; k < PI; k++) ri[k] = rsqrt_refined(r2[k]);
                     }
 #pragma unroll
                     for (int k = 0; k < PI; k++) {

@@ -4,26 +4,28 @@
 namespace vrgpu {
 
 // 1/sqrt(r2): hardware seed (rsqrt.approx.f64 = MUFU.RSQ64H on the high word, ~2^-22) + one fp64 Newton step written so
-// that only THREE instructions go to the FP64 pipe (t = r2*y0, e = 1 - t*y0, y = y0 + (y0/2)*e with y0/2 formed by an
-// integer decrement of the exponent); relative error ~1e-13.  Valid for normal r2 in [2^-963, 2^963): the callers test
-// rsqrt_out_of_range() -- an integer compare on the high word, not an FP64-pipe DSETP -- and patch the rare zero /
-// denormal / huge / non-finite arguments with the exact 1/sqrt (inf for r2 == 0, like the reference).
-__device__ __forceinline__ double rsqrt_fast(double r2)
+// that only THREE instructions go to the FP64 pipe: with h = r2/2 (an integer decrement of the exponent),
+// t = h*y0, e = 1/2 - t*y0, y = y0 + y0*e; relative error ~1e-13.  Valid for finite r2 >= 2^-1000: the callers test
+// rsqrt_seed_bad(y0) -- an integer compare on the seed's high word, not an FP64-pipe DSETP; it catches r2 zero, denormal,
+// tiny or NaN -- and patch those rare arguments with the exact 1/sqrt (inf for r2 == 0, like the reference).
+__device__ __forceinline__ double rsqrt_seed(double r2)
 {
     double y0;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(r2));
-    const double hy0 = __hiloint2double(__double2hiint(y0) - 0x00100000, __double2loint(y0));
-    const double t = r2 * y0;
-    const double e = fma(-t, y0, 1.0);
-    return fma(hy0, e, y0);
+    return y0;
 }
-__device__ __forceinline__ bool rsqrt_out_of_range(double r2)
+__device__ __forceinline__ bool rsqrt_seed_bad(double y0) { return (unsigned)__double2hiint(y0) >= 0x5f300000u; } // y0 > 2^500, inf, nan
+__device__ __forceinline__ double rsqrt_newton(double r2, double y0)
 {
-    return (unsigned)(__double2hiint(r2) - 0x03c00000) >= (0x7c200000u - 0x03c00000u);
+    const double h = __hiloint2double(__double2hiint(r2) - 0x00100000, __double2loint(r2));
+    const double t = h * y0;
+    const double e = fma(-t, y0, 0.5);
+    return fma(y0, e, y0);
 }
 __device__ __forceinline__ double rsqrt_refined(double r2)
 {
-    return rsqrt_out_of_range(r2) ? 1.0 / sqrt(r2) : rsqrt_fast(r2);
+    const double y0 = rsqrt_seed(r2);
+    return rsqrt_seed_bad(y0) ? 1.0 / sqrt(r2) : rsqrt_newton(r2, y0);
 }
 
 } // namespace vrgpu

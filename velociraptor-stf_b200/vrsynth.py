@@ -149,3 +149,88 @@ def canonical_groups(pfof: np.ndarray, pid: np.ndarray | None = None):
     out = np.zeros(n, dtype=np.int64)
     out[g] = rank[inv]
     return out, cnt[order]
+
+
+# ------------------------------------------------------------------------------------------------------
+# slab-wise generator: the same clustered box for ANY partition into x-slabs (multi-GPU runs at 512^3 / 1024^3, where no
+# rank can hold the whole box).  Every halo and every background bin has its own random stream, so a rank generates only
+# what can reach its slab.
+# ------------------------------------------------------------------------------------------------------
+SLAB_BINS = 64          # background is drawn per x-bin of width box/64: slab faces must be multiples of that
+
+
+def _scramble_pid(i: np.ndarray, n: int) -> np.ndarray:
+    """Bijection of [0, n) (n a power of two times an odd number is fine: the multiplier is coprime with n)."""
+    a = 2654435761
+    while np.gcd(a, n) != 1:
+        a += 2
+    return (i.astype(np.uint64) * np.uint64(a) + np.uint64(12345)) % np.uint64(n)
+
+
+def make_slab(n: int, seed: int, lo: float, hi: float, box: float = BOX, conc: float = 5.0, frac: float = 0.5):
+    """Particles of the n-particle clustered box whose x lies in [lo, hi); same statistics as make_box (NOT the same
+    realisation).  The union over any set of slabs tiling [0, box) with faces on multiples of box/64 is one fixed particle
+    set.  pid is a scrambled global index (1..n) and the particles come sorted by pid, so array order == pid order on
+    every rank and for the whole box alike."""
+    rng0 = np.random.default_rng(seed)
+    m = particle_mass(n, box)
+    sizes = halo_sizes(n, rng0, frac)
+    nh = len(sizes)
+    nhp = int(sizes.sum())
+    centres = rng0.random((nh, 3)) * box
+    bulk = rng0.normal(0.0, 300.0, size=(nh, 3))
+    mass_h = sizes * m
+    r200 = (3.0 * mass_h / (800.0 * np.pi * RHO_CRIT)) ** (1.0 / 3.0)
+    sigv = np.sqrt(G_CODE * mass_h / (2.0 * r200))
+    first = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64)
+    mt, rt = _nfw_inverse_table(conc)
+    # halos that can reach [lo, hi) (periodic in x); float32 rounding moves a particle by < 1e-5
+    cx = centres[:, 0]
+    pad = r200 + 1e-3
+    inside = (cx >= lo) & (cx < hi)
+    dlo = np.abs(cx - lo); dlo = np.minimum(dlo, box - dlo)
+    dhi = np.abs(cx - hi); dhi = np.minimum(dhi, box - dhi)
+    sel = np.flatnonzero(inside | (np.minimum(dlo, dhi) <= pad))
+    P, V, I = [], [], []
+    top = np.float64(np.nextafter(np.float32(box), np.float32(0)))
+
+    def keep(pos, vel, idx):
+        pos = np.mod(pos, box).astype(np.float32).astype(np.float64)
+        pos[pos >= box] = top
+        k = (pos[:, 0] >= lo) & (pos[:, 0] < hi)
+        if k.any():
+            P.append(pos[k]); V.append(vel[k].astype(np.float32).astype(np.float64)); I.append(idx[k])
+
+    for h in sel:
+        s = int(sizes[h])
+        rng = np.random.default_rng([seed, 1, int(h)])
+        u = rng.random(s)
+        d = rng.normal(size=(s, 3))
+        w = rng.normal(size=(s, 3))
+        d /= np.linalg.norm(d, axis=1)[:, None]
+        pos = centres[h] + (np.interp(u, mt, rt) * r200[h])[:, None] * d
+        keep(pos, bulk[h] + w * sigv[h], first[h] + np.arange(s, dtype=np.int64))
+    nbg = n - nhp
+    per = nbg // SLAB_BINS
+    extra = nbg - per * SLAB_BINS
+    wbin = box / SLAB_BINS
+    b0 = int(np.floor(lo / wbin + 1e-9)) - 1          # one bin further left: float32 rounding can reach the bin's upper edge
+    b1 = int(np.ceil(hi / wbin - 1e-9))
+    for bb in sorted({b % SLAB_BINS for b in range(b0, b1)}):
+        cnt = per + (1 if bb < extra else 0)
+        if cnt == 0:
+            continue
+        rng = np.random.default_rng([seed, 2, bb])
+        pos = rng.random((cnt, 3)) * np.array([wbin, box, box]) + np.array([bb * wbin, 0.0, 0.0])
+        vel = rng.normal(0.0, 50.0, size=(cnt, 3))
+        start = nhp + bb * per + min(bb, extra)
+        keep(pos, vel, start + np.arange(cnt, dtype=np.int64))
+    if P:
+        pos = np.concatenate(P); vel = np.concatenate(V); idx = np.concatenate(I)
+    else:
+        pos = np.zeros((0, 3)); vel = np.zeros((0, 3)); idx = np.zeros(0, dtype=np.int64)
+    pid = _scramble_pid(idx, n).astype(np.int64) + 1
+    o = np.argsort(pid, kind="stable")
+    nn = len(pid)
+    return {"pos": np.ascontiguousarray(pos[o]), "vel": np.ascontiguousarray(vel[o]), "mass": np.full(nn, np.float64(np.float32(m))),
+            "pid": np.ascontiguousarray(pid[o]), "box": box, "n": nn, "seed": seed, "n_total": n}
