@@ -64,16 +64,20 @@ def workload_name(nside, fofbgtype: int, pp: int) -> str:
     if ZOOM_NPART:
         return (f"{stages} on a zoom-style single halo of {ZOOM_NPART} particles (NFW c=7 + 10% in subclumps, one 3D group, "
                 f"L=100, b=0.2 of the mean spacing, seed 105)")
-    return f"{stages} on a {nside}^3 synthetic clustered periodic DM box (L=100, b=0.2, seed {seed_for(nside)})"
+    gen = ", slab-wise generator" if nside >= SLAB_GENERATOR_FROM else ""
+    return f"{stages} on a {nside}^3 synthetic clustered periodic DM box (L=100, b=0.2, seed {seed_for(nside)}{gen})"
 
 
 ZOOM_NPART = 0   # --single-halo N: BASELINE.json configs[4] (set in main)
+SLAB_GENERATOR_FROM = 512   # boxes from this side on come from vrsynth.make_slab: every rank draws only its own x-slab
 
 
 def make_input(nside):
     import vrsynth
     if ZOOM_NPART:
         return vrsynth.make_box(ZOOM_NPART, 105, single_halo=True)
+    if nside >= SLAB_GENERATOR_FROM:
+        return vrsynth.make_slab(nside ** 3, seed_for(nside), 0.0, vrsynth.BOX)
     return vrsynth.make_box(nside ** 3, seed_for(nside))
 
 
@@ -304,8 +308,17 @@ def run_ours(args):
             roof_all[k] = {"bound": "fp64", "achieved": a, "peak": fp64_peak, "unit": "TFLOP/s", "frac": a / fp64_peak, "ms": ms,
                            "peak_kind": "measured DFMA microbenchmark (vendor vector figure 40)",
                            "note": "algorithmic 8 flops per ordered pair; the symmetric kernel issues 11.25 FP64-pipe instructions per unordered pair"}
+        elif k == "ptree.walk" and st_last["n_tree_interactions"] > 0:
+            # F_tree = 12 flops per accepted cell / visited leaf particle, counted by the kernel
+            a = 12.0 * st_last["n_tree_interactions"] / (ms * 1e-3) / 1e12
+            roof_all[k] = {"bound": "fp64", "achieved": a, "peak": fp64_peak, "unit": "TFLOP/s", "frac": a / fp64_peak, "ms": ms,
+                           "interactions": int(st_last["n_tree_interactions"]), "tree_nodes": int(st_last["n_tree_nodes"]),
+                           "ginteractions_per_s": st_last["n_tree_interactions"] / (ms * 1e-3) / 1e9,
+                           "peak_kind": "measured DFMA microbenchmark (vendor vector figure 40)"}
         else:
             roof_all[k] = {"ms": ms}
+    if dom == "potential.tree" and "ptree.walk" in roof_all:
+        dom = "ptree.walk" if roof_all["ptree.walk"]["ms"] >= roof_all.get("ptree.build", {"ms": 0})["ms"] else "ptree.build"
     roofline = dict(roof_all.get(dom, {}))
     roofline.update({"kernel": dom, "traffic": traffic_tab.get(kernel_of.get(dom, ""), None),
                      "traffic_source": "profiles/r01c_summary.md (ncu --set full, per launch)" if traffic_tab else None,
@@ -346,14 +359,20 @@ def run_ours_multi(args, rank, world, local):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     nside = args.nside
     n = nside ** 3
-    d = vrsynth.make_box(n, seed_for(nside))
     L = vrsynth.BOX
     lo, hi = L * rank / world, L * (rank + 1) / world
-    x = d["pos"][:, 0]
-    sel = np.flatnonzero((x >= lo) & (x < hi))
-    parts = vrgpu.particles_from_arrays(d["pos"][sel], d["vel"][sel], d["mass"][sel], d["pid"][sel], pinned=True)
-    n_loc = len(sel)
-    del d, x
+    if nside >= SLAB_GENERATOR_FROM:
+        d = vrsynth.make_slab(n, seed_for(nside), lo, hi)
+        parts = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"], pinned=True)
+        n_loc = d["n"]
+        del d
+    else:
+        d = vrsynth.make_box(n, seed_for(nside))
+        x = d["pos"][:, 0]
+        sel = np.flatnonzero((x >= lo) & (x < hi))
+        parts = vrgpu.particles_from_arrays(d["pos"][sel], d["vel"][sel], d["mass"][sel], d["pid"][sel], pinned=True)
+        n_loc = len(sel)
+        del d, x
     ctx = vrgpu.Context(local)
     uid = [vrgpu.dist_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)

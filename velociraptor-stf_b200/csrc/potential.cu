@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
 {
     __shared__ double2 sxy[PT], szm[PT]; // 16-byte shared loads: two per j instead of four
     __shared__ uint32_t sg[PT];
+    __shared__ uint32_t s_lo, s_hi;
     const uint32_t s_first = blockIdx.x * PS;
     const uint32_t s_last = min(ntot, s_first + PS) - 1;
     uint32_t s[PI], g[PI];
@@ -43,11 +44,28 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
         }
         any_mine = any_mine || mine[k];
     }
+    // the j range runs from the first to the last group this CTA actually serves: a CTA that holds the tail of a group
+    // left to the symmetric kernel must not walk that (possibly huge) group
+    if (threadIdx.x == 0) { s_lo = 0xffffffffu; s_hi = 0u; }
     if (!__syncthreads_or(any_mine)) return;
-    const uint32_t g_first = gid[s_first], g_last = gid[s_last];
+#pragma unroll
+    for (int k = 0; k < PI; k++)
+        if (mine[k]) { atomicMin(&s_lo, s[k]); atomicMax(&s_hi, s[k]); }
+    __syncthreads();
+    const uint32_t g_first = gid[s_lo], g_last = gid[s_hi];
     const uint32_t j0 = off[g_first], j1 = off[g_last + 1];
-    const bool uniform = g_first == g_last; // the whole CTA sits inside one group (implies every slot is `mine`)
+    const bool uniform = gid[s_first] == gid[s_last]; // the whole CTA sits inside one group (implies every slot is `mine`)
     for (uint32_t jb = j0; jb < j1; jb += PT) {
+        // a tile that lies wholly inside a group this kernel does not serve (ids in arbitrary order) is skipped
+        {
+            const uint32_t ga = gid[jb];
+            const uint32_t ea = off[ga + 1], na = ea - off[ga];
+            const bool served = (pp_threshold < 0 || (long long)na <= pp_threshold) && na < sym_min;
+            if (!served && ea >= jb + PT) {
+                jb = j0 + ((ea - j0) / PT) * PT - PT; // the loop increment then lands on the tile that holds the group's end
+                continue;
+            }
+        }
         const uint32_t j = jb + threadIdx.x;
         if (j < j1) { sxy[threadIdx.x] = make_double2(x[j], y[j]); szm[threadIdx.x] = make_double2(z[j], m[j]); sg[threadIdx.x] = gid[j]; }
         else { sg[threadIdx.x] = 0; sxy[threadIdx.x] = make_double2(0, 0); szm[threadIdx.x] = make_double2(0, 0); }
