@@ -111,6 +111,7 @@ struct vrgpu_ctx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr; // host->device staging copies, overlapped with the unpack kernel
+    void *stage_host[2] = {nullptr, nullptr}; // page-locked staging for results that go to pageable caller memory
     std::string err;
     vrgpu::Pool pool;
     vrgpu_stats stats{};

@@ -1,5 +1,7 @@
 // velociraptor-stf_b200/csrc/fof.cuh -- device-resident state shared by the FOF / unbinding stages.
 #pragma once
+
+#include <functional>
 #include "common.cuh"
 
 namespace vrgpu {
@@ -44,6 +46,10 @@ struct Fof3dState {
 // helpers in api.cu / io.cu
 void upload_view(vrgpu_ctx *ctx, const vrgpu_view &view, bool need_vel, bool need_mass, bool need_pid, DeviceParticles &out);
 void download_i64(vrgpu_ctx *ctx, const long long *dev, long long *host, size_t n);
+// device -> host in page-locked chunks; consume(chunk, byte offset, length, part, nparts) runs on up to 4 host threads per
+// chunk while the next chunk is in flight; chunk boundaries fall on multiples of `granule` bytes
+void staged_download(vrgpu_ctx *ctx, const void *dev, size_t bytes, size_t granule,
+                     const std::function<void(const unsigned char *, size_t, size_t, int, int)> &consume);
 
 // stages
 void fof3d_device(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double period, long long minsize, Fof3dState &S);

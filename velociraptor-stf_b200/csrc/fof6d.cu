@@ -25,6 +25,8 @@
 #include "ufhash.cuh"
 
 #include <algorithm>
+#include <cstring>
+#include <thread>
 #include <cmath>
 
 namespace vrgpu {
@@ -721,13 +723,13 @@ __global__ void k_flag_pos(const long long *__restrict__ pfof, size_t n, uint32_
     if (i < n) flags[i] = pfof[i] > 0 ? 1u : 0u;
 }
 __global__ void k_pack_phase(const double *__restrict__ pos, const double *__restrict__ vel, const uint32_t *__restrict__ flags,
-                             const uint32_t *__restrict__ excl, size_t n, uint32_t *__restrict__ oidx, double *__restrict__ out)
+                             const uint32_t *__restrict__ excl, size_t n, double *__restrict__ out /* 7 words per record */)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || !flags[i]) return;
     const size_t s = excl[i];
-    oidx[s] = (uint32_t)i;
-    for (int k = 0; k < 3; k++) { out[6 * s + k] = pos[3 * i + k]; out[6 * s + 3 + k] = vel[3 * i + k]; }
+    out[7 * s] = __longlong_as_double((long long)i);
+    for (int k = 0; k < 3; k++) { out[7 * s + 1 + k] = pos[3 * i + k]; out[7 * s + 4 + k] = vel[3 * i + k]; }
 }
 
 // zero-copy variant: when the caller's records are page-locked (pinned / registered and mapped), the device stores the
@@ -735,14 +737,14 @@ __global__ void k_pack_phase(const double *__restrict__ pos, const double *__res
 __global__ void k_writeback_direct(unsigned char *__restrict__ base, size_t stride, size_t off_pos, size_t off_vel,
                                    const double *__restrict__ pos, const double *__restrict__ vel, const long long *__restrict__ pfof, size_t n)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // six consecutive lanes store the six words of one record: when velocity follows position in the record (NBody::Particle)
+    // the 48 bytes leave as one or two PCIe writes instead of six
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = t / 6;
+    const unsigned w = (unsigned)(t - 6 * i);
     if (i >= n || pfof[i] <= 0) return;
-    double *p = reinterpret_cast<double *>(base + i * stride + off_pos);
-    p[0] = pos[3 * i]; p[1] = pos[3 * i + 1]; p[2] = pos[3 * i + 2];
-    if (vel) {
-        double *v = reinterpret_cast<double *>(base + i * stride + off_vel);
-        v[0] = vel[3 * i]; v[1] = vel[3 * i + 1]; v[2] = vel[3 * i + 2];
-    }
+    if (w < 3) *reinterpret_cast<double *>(base + i * stride + off_pos + 8 * w) = pos[3 * i + w];
+    else if (vel) *reinterpret_cast<double *>(base + i * stride + off_vel + 8 * (w - 3)) = vel[3 * i + (w - 3)];
 }
 
 // device-visible alias of a page-locked host pointer, or nullptr for pageable memory
@@ -760,7 +762,8 @@ void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticl
     VR_REQUIRE(P.has_vel && view.off_vel != VRGPU_NOFIELD, VRGPU_EINVAL, "write-back needs velocities in the view");
     const int T = 256;
     if (void *dev = mapped_host_pointer(view.base)) {
-        VR_LAUNCH(ctx, k_writeback_direct, grid_for(P.n, T), T, 0, static_cast<unsigned char *>(dev), view.stride, view.off_pos, view.off_vel,
+        KScope kwb(ctx, "io.writeback");
+        VR_LAUNCH(ctx, k_writeback_direct, grid_for(6 * P.n, T), T, 0, static_cast<unsigned char *>(dev), view.stride, view.off_pos, view.off_vel,
                   P.pos.p, P.vel.p, pfof_dev, P.n);
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->stats.d2h_bytes += (long long)ctx->stats.n_grouped * 48;
@@ -773,22 +776,25 @@ void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticl
     VR_CUDA(cudaMemcpyAsync(&cnt, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
     if (cnt == 0) return;
-    DBuf<uint32_t> oidx(ctx, cnt);
-    DBuf<double> out(ctx, 6 * (size_t)cnt);
-    VR_LAUNCH(ctx, k_pack_phase, grid_for(P.n, T), T, 0, P.pos.p, P.vel.p, flags.p, excl.p, P.n, oidx.p, out.p);
-    std::vector<uint32_t> hidx(cnt);
-    std::vector<double> hq(6 * (size_t)cnt);
-    VR_CUDA(cudaMemcpyAsync(hidx.data(), oidx.p, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    VR_CUDA(cudaMemcpyAsync(hq.data(), out.p, 6 * (size_t)cnt * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    VR_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->stats.d2h_bytes += (long long)cnt * 52;
+    // pageable caller memory: 56-byte records (index, pos, vel) come back through the page-locked staging buffers and
+    // host threads scatter them into the caller's records
+    DBuf<double> out(ctx, 7 * (size_t)cnt);
+    VR_LAUNCH(ctx, k_pack_phase, grid_for(P.n, T), T, 0, P.pos.p, P.vel.p, flags.p, excl.p, P.n, out.p);
     unsigned char *base = const_cast<unsigned char *>(static_cast<const unsigned char *>(view.base));
-    for (size_t k = 0; k < cnt; k++) {
-        unsigned char *rec = base + (size_t)hidx[k] * view.stride;
-        double *p = reinterpret_cast<double *>(rec + view.off_pos);
-        double *v = reinterpret_cast<double *>(rec + view.off_vel);
-        for (int a = 0; a < 3; a++) { p[a] = hq[6 * k + a]; v[a] = hq[6 * k + 3 + a]; }
-    }
+    const size_t stride = view.stride, op = view.off_pos, ov = view.off_vel;
+    staged_download(ctx, out.p, (size_t)cnt * 56, 56, [=](const unsigned char *chunk, size_t, size_t len, int part, int nparts) {
+        const size_t nrec = len / 56, k0 = nrec * part / nparts, k1 = nrec * (part + 1) / nparts;
+        for (size_t k = k0; k < k1; k++) {
+            const double *r = reinterpret_cast<const double *>(chunk + 56 * k);
+            unsigned long long i;
+            memcpy(&i, r, 8);
+            unsigned char *rec = base + (size_t)i * stride;
+            double *p = reinterpret_cast<double *>(rec + op);
+            double *v = reinterpret_cast<double *>(rec + ov);
+            p[0] = r[1]; p[1] = r[2]; p[2] = r[3];
+            v[0] = r[4]; v[1] = r[5]; v[2] = r[6];
+        }
+    });
 }
 
 } // namespace vrgpu

@@ -5,6 +5,11 @@
 // buffered) into device staging buffers and unpacked there by k_unpack on the context stream.
 #include "fof.cuh"
 
+#include <algorithm>
+#include <cstring>
+#include <functional>
+#include <thread>
+
 namespace vrgpu {
 
 struct UnpackArgs {
@@ -65,6 +70,7 @@ void upload_view(vrgpu_ctx *ctx, const vrgpu_view &v, bool need_vel, bool need_m
     // memory; the driver bounces pageable memory itself) and unpacked on the context stream while the next chunk is in
     // flight.  Reading the caller's records zero-copy from the kernel instead measured 21 GB/s (profiles/r01a).
     if (!ctx->copy_stream) VR_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    KScope kup(ctx, "io.upload");
     const size_t chunk_bytes = (size_t)64 << 20;
     size_t per = chunk_bytes / v.stride;
     if (per < 1) per = 1;
@@ -97,12 +103,64 @@ void upload_view(vrgpu_ctx *ctx, const vrgpu_view &v, bool need_vel, bool need_m
     for (int k = 0; k < 2; k++) { ctx->evpool.push_back(ready[k]); ctx->evpool.push_back(freed[k]); }
 }
 
+// Results go back in 32 MB chunks through two page-locked staging buffers: the DMA of chunk k+1 runs while host threads
+// consume chunk k (copy / scatter it into the caller's pageable, usually never touched memory -- `new Int_t[n]`,
+// vector<Particle>).  A plain cudaMemcpy into such memory measured 4.9 GB/s (profiles/r01f).
+void staged_download(vrgpu_ctx *ctx, const void *dev, size_t bytes, size_t granule,
+                     const std::function<void(const unsigned char *chunk, size_t offset, size_t len, int part, int nparts)> &consume)
+{
+    if (bytes == 0) return;
+    size_t chunk = (size_t)32 << 20;
+    chunk -= chunk % granule;
+    if (!ctx->stage_host[0]) {
+        VR_CUDA(cudaHostAlloc(&ctx->stage_host[0], (size_t)32 << 20, cudaHostAllocDefault));
+        VR_CUDA(cudaHostAlloc(&ctx->stage_host[1], (size_t)32 << 20, cudaHostAllocDefault));
+    }
+    cudaEvent_t done[2] = {KScope::get(ctx), KScope::get(ctx)};
+    const unsigned char *src = static_cast<const unsigned char *>(dev);
+    const size_t nchunks = (bytes + chunk - 1) / chunk;
+    auto issue = [&](size_t c) {
+        const size_t o = c * chunk, len = std::min(chunk, bytes - o);
+        VR_CUDA(cudaMemcpyAsync(ctx->stage_host[c & 1], src + o, len, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaEventRecord(done[c & 1], ctx->stream));
+    };
+    issue(0);
+    for (size_t c = 0; c < nchunks; c++) {
+        VR_CUDA(cudaEventSynchronize(done[c & 1]));
+        if (c + 1 < nchunks) issue(c + 1);
+        const size_t o = c * chunk, len = std::min(chunk, bytes - o);
+        const unsigned char *from = static_cast<const unsigned char *>(ctx->stage_host[c & 1]);
+        const int nt = len > ((size_t)1 << 20) ? 4 : 1;
+        std::thread th[4];
+        for (int t = 1; t < nt; t++) th[t] = std::thread([&, t] { consume(from, o, len, t, nt); });
+        consume(from, o, len, 0, nt);
+        for (int t = 1; t < nt; t++) th[t].join();
+    }
+    ctx->evpool.push_back(done[0]);
+    ctx->evpool.push_back(done[1]);
+    ctx->stats.d2h_bytes += (long long)bytes;
+}
+
 void download_i64(vrgpu_ctx *ctx, const long long *dev, long long *host, size_t n)
 {
     if (n == 0) return;
-    VR_CUDA(cudaMemcpyAsync(host, dev, n * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
-    VR_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->stats.d2h_bytes += (long long)(n * sizeof(long long));
+    KScope kdn(ctx, "io.download");
+    const size_t bytes = n * sizeof(long long);
+    cudaPointerAttributes at{};
+    const bool locked = cudaPointerGetAttributes(&at, host) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (locked || bytes < ((size_t)4 << 20)) {
+        VR_CUDA(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->stats.d2h_bytes += (long long)bytes;
+        return;
+    }
+    unsigned char *dst = reinterpret_cast<unsigned char *>(host);
+    staged_download(ctx, dev, bytes, 4096, [dst](const unsigned char *chunk, size_t offset, size_t len, int part, int nparts) {
+        const size_t per = ((len / nparts) + 4095) & ~(size_t)4095;
+        const size_t a0 = std::min(len, (size_t)part * per), a1 = std::min(len, (size_t)(part + 1) * per);
+        if (a1 > a0) memcpy(dst + offset + a0, chunk + a0, a1 - a0);
+    });
 }
 
 } // namespace vrgpu
