@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(PT) k_potential_direct(const double *__restric
 // Partial sums of different CTAs meet in global fp64 atomics, so the last bits of phi depend on the arrival order
 // (relative 1e-16; DESIGN.md "determinism").
 // ---------------------------------------------------------------------------------------------------
-constexpr int SYM_TILE = PT * PI;         // 1024 slots
+constexpr int SYM_PT = 128, SYM_PI = 8;    // threads per CTA, i-slots per thread of the symmetric kernel
+constexpr int SYM_TILE = SYM_PT * SYM_PI; // 1024 slots
 constexpr uint32_t SYM_MIN = 4 * SYM_TILE; // groups at least this large take the symmetric kernel
 
 __global__ void k_sym_count(const uint32_t *__restrict__ off, uint32_t ngroups, long long pp_threshold, unsigned long long *__restrict__ npairs)
@@ -142,14 +143,18 @@ __global__ void k_sym_count(const uint32_t *__restrict__ off, uint32_t ngroups, 
     npairs[g] = c;
 }
 
-// 3 CTAs per SM (80 registers) and no unrolling of the rotation loop measured best (profiles/r01f)
-__global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+// 128 threads x 8 slots, 3 CTAs per SM (168 registers) and no unrolling of the rotation loop measured best: more slots per
+// thread amortise the shared-memory traffic and loop overhead of a rotation step over more FP64 work (256 x 4: 106 ms,
+// 128 x 8: 99.5 ms at 256^3)
+template <int SPT, int SPI, int MINB>
+__global__ void __launch_bounds__(SPT, MINB) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                                                       const double *__restrict__ m, const uint32_t *__restrict__ off, uint32_t ngroups,
                                                       const unsigned long long *__restrict__ pair_start /* exclusive scan, ngroups+2 */,
                                                       double eps2, double *__restrict__ phiacc)
 {
-    __shared__ double2 sxy[PT], szm[PT];
-    __shared__ double sacc[PT / 32][PT];
+    static_assert(SPT * SPI == SYM_TILE, "tile size is fixed");
+    __shared__ double2 sxy[SPT], szm[SPT];
+    __shared__ double sacc[SPT / 32][SPT];
     __shared__ uint32_t s_g;
     const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     // which group: largest g with pair_start[g] <= blockIdx.x
@@ -176,23 +181,23 @@ __global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restric
     const uint32_t j_end = min(g_end, j_base + SYM_TILE);
     const bool diag = I == J;
 
-    uint32_t si[PI];
-    double xi[PI], yi[PI], zi[PI], mi[PI], acc[PI];
+    uint32_t si[SPI];
+    double xi[SPI], yi[SPI], zi[SPI], mi[SPI], acc[SPI];
 #pragma unroll
-    for (int k = 0; k < PI; k++) {
-        si[k] = i_base + k * PT + threadIdx.x;
+    for (int k = 0; k < SPI; k++) {
+        si[k] = i_base + k * SPT + threadIdx.x;
         acc[k] = 0;
         if (si[k] < g_end) { xi[k] = x[si[k]]; yi[k] = y[si[k]]; zi[k] = z[si[k]]; mi[k] = m[si[k]]; }
         else { xi[k] = 1e100; yi[k] = 1e100; zi[k] = 1e100; mi[k] = 0; } // padding: weightless and far away
     }
-    for (uint32_t jb = j_base; jb < j_end; jb += PT) {
+    for (uint32_t jb = j_base; jb < j_end; jb += SPT) {
         const uint32_t j = jb + threadIdx.x;
         if (j < j_end) { sxy[threadIdx.x] = make_double2(x[j], y[j]); szm[threadIdx.x] = make_double2(z[j], m[j]); }
         else { sxy[threadIdx.x] = make_double2(-1e100, -1e100); szm[threadIdx.x] = make_double2(-1e100, 0.0); }
 #pragma unroll
-        for (int ww = 0; ww < PT / 32; ww++) sacc[ww][threadIdx.x] = 0.0;
+        for (int ww = 0; ww < SPT / 32; ww++) sacc[ww][threadIdx.x] = 0.0;
         __syncthreads();
-        const int cnt = (int)min((uint32_t)PT, j_end - jb);
+        const int cnt = (int)min((uint32_t)SPT, j_end - jb);
         if (!diag) {
             // rotation: at step s lane l works on j = 32*blk + ((l + s) & 31), so the 32 lanes always hold 32 DIFFERENT j:
             // the j-side partial goes straight into the warp's shared row without any cross-lane reduction
@@ -202,10 +207,10 @@ __global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restric
                 for (int st = 0; st < 32; st++) {
                     const int jj = (blk << 5) + (int)((lane + st) & 31);
                     const double2 qa = sxy[jj], qb = szm[jj];
-                    double tj = 0, r2[PI], ri[PI];
+                    double tj = 0, r2[SPI], ri[SPI];
                     unsigned worst = 0;
 #pragma unroll
-                    for (int k = 0; k < PI; k++) {
+                    for (int k = 0; k < SPI; k++) {
                         const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
                         r2[k] = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
                         const double y0 = rsqrt_seed(r2[k]);
@@ -214,10 +219,10 @@ __global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restric
                     }
                     if (worst >= 0x5f300000u) {
 #pragma unroll
-                        for (int k = 0; k < PI; k++) ri[k] = rsqrt_refined(r2[k]);
+                        for (int k = 0; k < SPI; k++) ri[k] = rsqrt_refined(r2[k]);
                     }
 #pragma unroll
-                    for (int k = 0; k < PI; k++) {
+                    for (int k = 0; k < SPI; k++) {
                         acc[k] = fma(qb.y, ri[k], acc[k]);
                         tj = fma(mi[k], ri[k], tj);
                     }
@@ -229,7 +234,7 @@ __global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restric
             if ((int)threadIdx.x < cnt) {
                 double s = 0;
 #pragma unroll
-                for (int ww = 0; ww < PT / 32; ww++) s += sacc[ww][threadIdx.x];
+                for (int ww = 0; ww < SPT / 32; ww++) s += sacc[ww][threadIdx.x];
                 atomicAdd(&phiacc[jb + threadIdx.x], s);
             }
         } else {
@@ -237,7 +242,7 @@ __global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restric
                 const double2 qa = sxy[jj], qb = szm[jj];
                 const uint32_t sj = jb + jj;
 #pragma unroll
-                for (int k = 0; k < PI; k++) {
+                for (int k = 0; k < SPI; k++) {
                     if (sj == si[k]) continue;
                     const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
                     const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
@@ -248,7 +253,7 @@ __global__ void __launch_bounds__(PT, 3) k_potential_sym(const double *__restric
         __syncthreads();
     }
 #pragma unroll
-    for (int k = 0; k < PI; k++)
+    for (int k = 0; k < SPI; k++)
         if (si[k] < g_end) atomicAdd(&phiacc[si[k]], acc[k]);
 }
 
@@ -297,7 +302,8 @@ unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G
         KScope k(ctx, "potential.direct.sym");
         DBuf<double> phiacc(ctx, gs.ntot);
         VR_CUDA(cudaMemsetAsync(phiacc.p, 0, sizeof(double) * gs.ntot, ctx->stream));
-        VR_LAUNCH(ctx, k_potential_sym, (unsigned)nwork, PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p, eps * eps, phiacc.p);
+        VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
+                  eps * eps, phiacc.p);
         VR_LAUNCH(ctx, k_sym_finish, grid_for(gs.ntot, 256), 256, 0, phiacc.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G_, pp_threshold, phi);
     }
     unsigned long long h = 0;
