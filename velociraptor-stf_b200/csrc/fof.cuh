@@ -46,7 +46,7 @@ struct Fof3dState {
 // helpers in api.cu / io.cu
 void upload_view(vrgpu_ctx *ctx, const vrgpu_view &view, bool need_vel, bool need_mass, bool need_pid, DeviceParticles &out);
 void download_i64(vrgpu_ctx *ctx, const long long *dev, long long *host, size_t n);
-// device -> host in page-locked chunks; consume(chunk, byte offset, length, part, nparts) runs on up to 4 host threads per
+// device -> host in page-locked chunks; consume(chunk, byte offset, length, part, nparts) runs on up to 8 host threads per
 // chunk while the next chunk is in flight; chunk boundaries fall on multiples of `granule` bytes
 void staged_download(vrgpu_ctx *ctx, const void *dev, size_t bytes, size_t granule,
                      const std::function<void(const unsigned char *, size_t, size_t, int, int)> &consume);
