@@ -870,12 +870,25 @@ void fof3d_label(vrgpu_ctx *ctx, const DeviceParticles &P, long long minsize, Fo
 // ---------------------------------------------------------------------------------------------------
 // AdjustStructureForPeriod (src/search.cxx:856-895)
 // ---------------------------------------------------------------------------------------------------
-__global__ void k_group_first(const long long *__restrict__ pfof, size_t n, uint32_t *__restrict__ first)
+// first member (lowest index) of every group; the big groups (low ids) are reduced per CTA in shared memory first
+constexpr int GF_IDS = 4096, GF_THREADS = 512;
+__global__ void __launch_bounds__(GF_THREADS) k_group_first(const long long *__restrict__ pfof, size_t n, uint32_t *__restrict__ first)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    long long g = pfof[i];
-    if (g > 0) atomicMin(&first[g], (uint32_t)i);
+    __shared__ uint32_t sf[GF_IDS];
+    for (int k = threadIdx.x; k < GF_IDS; k += GF_THREADS) sf[k] = 0xffffffffu;
+    __syncthreads();
+    const size_t per = (n + gridDim.x - 1) / gridDim.x;
+    const size_t i0 = (size_t)blockIdx.x * per, i1 = min(n, i0 + per);
+    for (size_t i = i0 + threadIdx.x; i < i1; i += GF_THREADS) {
+        const long long g = pfof[i];
+        if (g > 0) {
+            if (g <= GF_IDS) atomicMin(&sf[g - 1], (uint32_t)i);
+            else atomicMin(&first[g], (uint32_t)i);
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < GF_IDS; k += GF_THREADS)
+        if (sf[k] != 0xffffffffu) atomicMin(&first[k + 1], sf[k]);
 }
 
 __global__ void k_adjust_period(double *__restrict__ pos, const long long *__restrict__ pfof, size_t n, const uint32_t *__restrict__ first,
@@ -937,7 +950,8 @@ size_t adjust_for_period_device(vrgpu_ctx *ctx, DeviceParticles &P, const long l
         VR_LAUNCH(ctx, k_group_minpid, grid_for(P.n, T), T, 0, pfof_dev, P.pid.p, P.n, minpid.p);
         VR_LAUNCH(ctx, k_group_first_by_pid, grid_for(P.n, T), T, 0, pfof_dev, P.pid.p, P.n, minpid.p, first.p);
     } else
-        VR_LAUNCH(ctx, k_group_first, grid_for(P.n, T), T, 0, pfof_dev, P.n, first.p);
+        VR_LAUNCH(ctx, k_group_first, (unsigned)std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count * 4, (P.n + GF_THREADS - 1) / GF_THREADS)), GF_THREADS,
+                  0, pfof_dev, P.n, first.p);
     // worst case every grouped particle moves; allocate for n (lists are compacted by the atomic counter)
     moved_idx.alloc(ctx, P.n);
     moved_xyz.alloc(ctx, 3 * P.n);

@@ -1,17 +1,35 @@
 // velociraptor-stf_b200/csrc/groups.cu -- group-major layout (see groups.cuh).
 #include "groups.cuh"
 
+#include <algorithm>
+
 namespace vrgpu {
 
-__global__ void k_flag_grouped(const long long *__restrict__ pfof, size_t n, long long ngroups, uint32_t *__restrict__ flags,
-                               uint32_t *__restrict__ count, unsigned int *__restrict__ nbad)
+// Group ids come in size order from the search stages, so the low ids are the big groups: their counters are kept per CTA
+// in shared memory (a hot global counter serialises ~10^5 atomics), every CTA walks a contiguous chunk of the array.
+constexpr int PRIV_IDS = 4096, PRIV_THREADS = 512;
+
+__global__ void __launch_bounds__(PRIV_THREADS) k_flag_grouped(const long long *__restrict__ pfof, size_t n, long long ngroups,
+                                                                uint32_t *__restrict__ flags, uint32_t *__restrict__ count,
+                                                                unsigned int *__restrict__ nbad)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    long long g = pfof[i];
-    if (g < 0 || g > ngroups) { atomicAdd(nbad, 1u); g = 0; }
-    flags[i] = g > 0 ? 1u : 0u;
-    if (g > 0) atomicAdd(&count[g], 1u);
+    __shared__ uint32_t sc[PRIV_IDS];
+    for (int k = threadIdx.x; k < PRIV_IDS; k += PRIV_THREADS) sc[k] = 0;
+    __syncthreads();
+    const size_t per = (n + gridDim.x - 1) / gridDim.x;
+    const size_t i0 = (size_t)blockIdx.x * per, i1 = min(n, i0 + per);
+    for (size_t i = i0 + threadIdx.x; i < i1; i += PRIV_THREADS) {
+        long long g = pfof[i];
+        if (g < 0 || g > ngroups) { atomicAdd(nbad, 1u); g = 0; }
+        flags[i] = g > 0 ? 1u : 0u;
+        if (g > 0) {
+            if (g <= PRIV_IDS) atomicAdd(&sc[g - 1], 1u);
+            else atomicAdd(&count[g], 1u);
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < PRIV_IDS; k += PRIV_THREADS)
+        if (sc[k]) atomicAdd(&count[k + 1], sc[k]);
 }
 
 __global__ void k_compact_grouped(const long long *__restrict__ pfof, const uint32_t *__restrict__ flags, const uint32_t *__restrict__ excl,
@@ -62,7 +80,8 @@ void build_groupset(vrgpu_ctx *ctx, const long long *pfof_dev, size_t n, long lo
     DBuf<unsigned int> nbad(ctx, 1);
     VR_CUDA(cudaMemsetAsync(count.p, 0, sizeof(uint32_t) * ((size_t)ngroups + 2), ctx->stream));
     VR_CUDA(cudaMemsetAsync(nbad.p, 0, sizeof(unsigned int), ctx->stream));
-    VR_LAUNCH(ctx, k_flag_grouped, grid_for(n, T), T, 0, pfof_dev, n, ngroups, flags.p, count.p, nbad.p);
+    VR_LAUNCH(ctx, k_flag_grouped, (unsigned)std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count * 4, (n + PRIV_THREADS - 1) / PRIV_THREADS)), PRIV_THREADS, 0,
+              pfof_dev, n, ngroups, flags.p, count.p, nbad.p);
     exclusive_scan_u32(ctx, flags.p, excl.p, n, total.p);
     // off[g] = sum of count[0..g-1]; count[0] == 0 so off[0] = off[1] = 0
     exclusive_scan_u32(ctx, count.p, gs.off.p, (size_t)ngroups + 2, nullptr);

@@ -4,7 +4,8 @@
 // Radix pass = 3 launches over tiles of RS_TILE elements:
 //   rs_hist     per-tile digit histogram (warp-aggregated shared atomics)  -> table[digit][tile]
 //   rs_scan     one CTA per digit: exclusive scan of its row, row total    -> table (in place), totals[digit]
-//   rs_scatter  re-read tile, stable in-tile ranks via __match_any_sync, write to final positions
+//   rs_scatter  re-read tile, stable in-tile ranks via __match_any_sync, order the tile by digit in shared memory,
+//               write each digit's run to its final position with coalesced stores
 // Algorithmic traffic per pass: 8 B (hist) + 12 B read + 12 B write per element.
 #include "common.cuh"
 
@@ -68,14 +69,23 @@ __global__ void __launch_bounds__(256) rs_scan(uint32_t *__restrict__ table, uin
     if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
 }
 
+// The tile is first ordered by digit in shared memory (stable: warp-major, then load order), then written out with
+// consecutive threads on consecutive addresses: a digit's run of a tile (16 elements on average) leaves as whole sectors
+// instead of one 8-byte + one 4-byte store per element to 256 different places.
+constexpr size_t RS_SMEM = (size_t)RS_TILE * 12 + (size_t)RS_WARPS * RS_BINS * 4 + 2 * RS_BINS * 4 + 64;
+
 __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                                                          uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, size_t n,
                                                          int shift, const uint32_t *__restrict__ table, uint32_t ntiles,
                                                          const uint32_t *__restrict__ totals)
 {
-    __shared__ uint32_t whist[RS_WARPS][RS_BINS];
-    __shared__ uint32_t dbase[RS_BINS];
-    __shared__ uint32_t wsum[RS_WARPS];
+    extern __shared__ __align__(16) unsigned char rs_smem[];
+    uint64_t *skey = reinterpret_cast<uint64_t *>(rs_smem);
+    uint32_t *sval = reinterpret_cast<uint32_t *>(skey + RS_TILE);
+    uint32_t(*whist)[RS_BINS] = reinterpret_cast<uint32_t(*)[RS_BINS]>(sval + RS_TILE);
+    uint32_t *dbase = reinterpret_cast<uint32_t *>(whist + RS_WARPS); // global start of digit d
+    uint32_t *gadj = dbase + RS_BINS;                                  // global position of tile-local index 0 of digit d
+    uint32_t *wsum = gadj + RS_BINS;
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int w = 0; w < RS_WARPS; w++) whist[w][threadIdx.x] = 0;
     // exclusive scan of the 256 digit totals -> dbase
@@ -97,7 +107,8 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const uint64_t *__restr
     uint64_t k[RS_ITEMS];
     uint32_t v[RS_ITEMS];
     uint16_t rank[RS_ITEMS];
-    const size_t wbase = (size_t)blockIdx.x * RS_TILE + (size_t)warp * (RS_ITEMS * 32);
+    const size_t tbase = (size_t)blockIdx.x * RS_TILE;
+    const size_t wbase = tbase + (size_t)warp * (RS_ITEMS * 32);
     const unsigned lt = (1u << lane) - 1u;
 #pragma unroll
     for (int r = 0; r < RS_ITEMS; r++) {
@@ -118,15 +129,31 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const uint64_t *__restr
     }
     __syncthreads();
     {
-        // thread d owns digit d: turn per-warp counts into global write bases
-        unsigned d = threadIdx.x;
-        uint32_t running = dbase[d] + table[(size_t)d * ntiles + blockIdx.x];
+        // thread d owns digit d: tile-local start of the digit (exclusive scan over digits), per-warp offsets inside it
+        const unsigned d = threadIdx.x;
+        uint32_t tot = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) tot += whist[w][d];
+        uint32_t x = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= (unsigned)o) x += y;
+        }
+        __syncthreads(); // wsum is reused
+        if (lane == 31) wsum[warp] = x;
+        __syncthreads();
+        uint32_t woff = 0;
+        for (unsigned w = 0; w < warp; w++) woff += wsum[w];
+        const uint32_t tstart = woff + x - tot;
+        uint32_t running = tstart;
 #pragma unroll
         for (int w = 0; w < RS_WARPS; w++) {
             uint32_t t = whist[w][d];
             whist[w][d] = running;
             running += t;
         }
+        gadj[d] = dbase[d] + table[(size_t)d * ntiles + blockIdx.x] - tstart;
     }
     __syncthreads();
 #pragma unroll
@@ -134,10 +161,18 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const uint64_t *__restr
         size_t i = wbase + (size_t)r * 32 + lane;
         if (i < n) {
             unsigned digit = (unsigned)((k[r] >> shift) & (RS_BINS - 1));
-            uint32_t pos = whist[warp][digit] + rank[r];
-            keys_out[pos] = k[r];
-            vals_out[pos] = v[r];
+            uint32_t lp = whist[warp][digit] + rank[r];
+            skey[lp] = k[r];
+            sval[lp] = v[r];
         }
+    }
+    __syncthreads();
+    const uint32_t cnt = (uint32_t)min((size_t)RS_TILE, n - tbase);
+    for (uint32_t idx = threadIdx.x; idx < cnt; idx += RS_THREADS) {
+        const uint64_t key = skey[idx];
+        const uint32_t pos = gadj[(unsigned)((key >> shift) & (RS_BINS - 1))] + idx;
+        keys_out[pos] = key;
+        vals_out[pos] = sval[idx];
     }
 }
 
@@ -152,11 +187,12 @@ void radix_sort_pairs(vrgpu_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t *
     uint64_t *kin = keys, *kout = keys_tmp;
     uint32_t *vin = vals, *vout = vals_tmp;
     int npass = (nbits + RS_BITS - 1) / RS_BITS;
+    VR_CUDA(cudaFuncSetAttribute(rs_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SMEM));
     for (int p = 0; p < npass; p++) {
         int shift = p * RS_BITS;
         VR_LAUNCH(ctx, rs_hist, ntiles, RS_THREADS, 0, kin, n, shift, table.p, ntiles);
         VR_LAUNCH(ctx, rs_scan, RS_BINS, 256, 0, table.p, ntiles, totals.p);
-        VR_LAUNCH(ctx, rs_scatter, ntiles, RS_THREADS, 0, kin, vin, kout, vout, n, shift, table.p, ntiles, totals.p);
+        VR_LAUNCH(ctx, rs_scatter, ntiles, RS_THREADS, RS_SMEM, kin, vin, kout, vout, n, shift, table.p, ntiles, totals.p);
         std::swap(kin, kout);
         std::swap(vin, vout);
     }

@@ -479,22 +479,39 @@ __global__ void k_iota_u32(uint32_t *a, uint32_t n)
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) a[i] = i;
 }
+// slots are group-major, so the lanes of a warp hold runs of equal group id: one segmented reduction per run, then one
+// atomic per (warp, group) instead of one per member
 __global__ void k_new_group_stats(const UbArrays A, const uint32_t *__restrict__ idx, const long long *__restrict__ pid, uint32_t ntot,
                                   uint32_t *__restrict__ newsize, unsigned long long *__restrict__ minpid, unsigned long long *__restrict__ nmarg)
 {
-    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31;
     bool mg = false;
+    uint32_t g = 0xffffffffu, cnt = 0;
+    unsigned long long p = ~0ull;
     if (s < ntot) {
         mg = A.marg[s];
+        g = A.gid[s];
         if (A.alive[s]) {
-            uint32_t g = A.gid[s];
-            uint32_t i = idx[s];
-            atomicAdd(&newsize[g], 1u);
-            atomicMin(&minpid[g], pid ? (unsigned long long)pid[i] : (unsigned long long)i);
+            const uint32_t i = idx[s];
+            cnt = 1;
+            p = pid ? (unsigned long long)pid[i] : (unsigned long long)i;
         }
     }
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t go = __shfl_down_sync(0xffffffffu, g, o);
+        const uint32_t co = __shfl_down_sync(0xffffffffu, cnt, o);
+        const unsigned long long po = __shfl_down_sync(0xffffffffu, p, o);
+        if (lane + o < 32 && go == g) { cnt += co; p = po < p ? po : p; }
+    }
+    const uint32_t gprev = __shfl_up_sync(0xffffffffu, g, 1);
+    if (s < ntot && cnt > 0 && (lane == 0 || gprev != g)) {
+        atomicAdd(&newsize[g], cnt);
+        atomicMin(&minpid[g], p);
+    }
     unsigned b = __ballot_sync(0xffffffffu, mg);
-    if ((threadIdx.x & 31) == 0 && b) atomicAdd(nmarg, (unsigned long long)__popc(b));
+    if (lane == 0 && b) atomicAdd(nmarg, (unsigned long long)__popc(b));
 }
 __global__ void k_write_unbound(const UbArrays A, const uint32_t *__restrict__ idx, const uint32_t *__restrict__ gid_of, uint32_t ntot,
                                 long long *__restrict__ pfof)
