@@ -291,7 +291,7 @@ def run_ours(args):
     peaks, peaks_kind = measured_peaks()
     fp64_peak = ctx.measure_fp64_tflops()   # DFMA microbenchmark on this GPU (MEASURED_PEAKS.json has no fp64 figure)
     traffic_tab = {}
-    tpath = os.path.join(ROOT, "profiles", "r01c_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r01f_traffic.json")
     if os.path.exists(tpath) and nside == 256 and not ZOOM_NPART and args.fofbgtype == 5 and args.pp_threshold < 0:
         traffic_tab = json.load(open(tpath)).get("dram_bytes_per_launch", {})
     kernel_of = {"potential.direct": "k_potential_sym", "fof3d.link_cells": "k_link_thread"}
@@ -323,7 +323,7 @@ def run_ours(args):
         dom = "ptree.walk" if roof_all["ptree.walk"]["ms"] >= roof_all.get("ptree.build", {"ms": 0})["ms"] else "ptree.build"
     roofline = dict(roof_all.get(dom, {}))
     roofline.update({"kernel": dom, "traffic": traffic_tab.get(kernel_of.get(dom, ""), None),
-                     "traffic_source": "profiles/r01c_summary.md (ncu --set full, per launch)" if traffic_tab else None,
+                     "traffic_source": "profiles/r01f_summary.md (ncu --set full, per launch)" if traffic_tab else None,
                      "peak_kind": roofline.get("peak_kind", peaks_kind)})
     for k, name in kernel_of.items():
         if k in roof_all and name in traffic_tab:

@@ -512,25 +512,35 @@ __global__ void k_flatten(uint32_t *__restrict__ parent, uint32_t ncells, uint32
 }
 
 // per cell: add its particle count / min pid / min original index into its root's records
+// cells are in spatial order, so neighbouring lanes often share a root: one atomic triple per (warp, root)
 __global__ void k_group_stats(const uint32_t *__restrict__ root, const uint32_t *__restrict__ cell_start, uint32_t ncells,
                               const uint32_t *__restrict__ order, const long long *__restrict__ pid, uint32_t *__restrict__ gsize,
                               unsigned long long *__restrict__ gminpid, uint32_t *__restrict__ gminidx)
 {
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncells) return;
-    uint32_t s = cell_start[c], e = cell_start[c + 1];
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = c < ncells;
     unsigned long long mp = ~0ull;
-    uint32_t mi = 0xffffffffu;
-    for (uint32_t k = s; k < e; k++) {
-        uint32_t i = order[k];
-        unsigned long long p = pid ? (unsigned long long)pid[i] : (unsigned long long)i;
-        mp = p < mp ? p : mp;
-        mi = i < mi ? i : mi;
+    uint32_t mi = 0xffffffffu, cnt = 0, r = 0xffffffffu;
+    if (valid) {
+        const uint32_t s = cell_start[c], e = cell_start[c + 1];
+        for (uint32_t k = s; k < e; k++) {
+            const uint32_t i = order[k];
+            const unsigned long long p = pid ? (unsigned long long)pid[i] : (unsigned long long)i;
+            mp = p < mp ? p : mp;
+            mi = i < mi ? i : mi;
+        }
+        cnt = e - s;
+        r = root[c];
     }
-    uint32_t r = root[c];
-    atomicAdd(&gsize[r], e - s);
-    atomicMin(&gminpid[r], mp);
-    atomicMin(&gminidx[r], mi);
+    const unsigned peers = __match_any_sync(0xffffffffu, r);
+    const uint32_t tot = __reduce_add_sync(peers, cnt);
+    const uint32_t mi_min = __reduce_min_sync(peers, mi);
+    const unsigned long long mp_min = warp_min_u64(peers, mp);
+    if (valid && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+        atomicAdd(&gsize[r], tot);
+        atomicMin(&gminpid[r], mp_min);
+        atomicMin(&gminidx[r], mi_min);
+    }
 }
 
 __global__ void k_flag_groups(const uint32_t *__restrict__ root, const uint32_t *__restrict__ gsize, uint32_t ncells, uint32_t minsize,

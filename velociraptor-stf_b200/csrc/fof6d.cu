@@ -494,16 +494,26 @@ __global__ void __launch_bounds__(L6_WARPS * 32) k_link6(Link6 L)
 // ---------------------------------------------------------------------------------------------------
 // labels
 // ---------------------------------------------------------------------------------------------------
+// particles are in (group, cell) order, so a warp mostly holds members of one component: one atomic per (warp, root)
 __global__ void k_comp_stats(const uint32_t *__restrict__ root, const uint32_t *__restrict__ ord, const uint32_t *__restrict__ idx,
                              const long long *__restrict__ pid, uint32_t ntot, uint32_t *__restrict__ csize,
                              unsigned long long *__restrict__ cminpid)
 {
-    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= ntot) return;
-    const uint32_t r = root[p];
-    const uint32_t i = idx[ord[p]];
-    atomicAdd(&csize[r], 1u);
-    atomicMin(&cminpid[r], pid ? (unsigned long long)pid[i] : (unsigned long long)i);
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = p < ntot;
+    uint32_t r = 0xffffffffu;
+    unsigned long long v = ~0ull;
+    if (valid) {
+        r = root[p];
+        const uint32_t i = idx[ord[p]];
+        v = pid ? (unsigned long long)pid[i] : (unsigned long long)i;
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, r);
+    const unsigned long long mn = warp_min_u64(peers, v);
+    if (valid && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+        atomicAdd(&csize[r], (uint32_t)__popc(peers));
+        atomicMin(&cminpid[r], mn);
+    }
 }
 
 __global__ void k_write_pfof6(const uint32_t *__restrict__ root, const uint32_t *__restrict__ ord, const uint32_t *__restrict__ idx,

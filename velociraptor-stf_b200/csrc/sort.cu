@@ -12,7 +12,7 @@
 namespace vrgpu {
 
 constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
+constexpr int RS_ITEMS = 8;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 4096
 constexpr int RS_BITS = 8;
 constexpr int RS_BINS = 1 << RS_BITS;

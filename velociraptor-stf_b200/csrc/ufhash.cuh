@@ -97,4 +97,14 @@ static inline int bits_for_u64v(uint64_t v)
     return b < 1 ? 1 : b;
 }
 
+// minimum of a 64-bit value over the lanes named in `peers` (every lane of the group passes the same mask, as returned
+// by __match_any_sync)
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned peers, unsigned long long v)
+{
+    const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
+    const unsigned mh = __reduce_min_sync(peers, hi);
+    const unsigned ml = __reduce_min_sync(peers, hi == mh ? lo : 0xffffffffu);
+    return ((unsigned long long)mh << 32) | ml;
+}
+
 } // namespace vrgpu
