@@ -397,7 +397,7 @@ __global__ void k_cell_coords(const uint64_t *__restrict__ cell_key, uint32_t nc
     if (c == ncells - 1 || cell_key[c + 1] / ncx != r) row_last[r] = c + 1;
 }
 
-__global__ void __launch_bounds__(128) k_link_thread(LinkParams P, const uint32_t *__restrict__ cell_row, const int *__restrict__ cell_ix,
+__global__ void __launch_bounds__(128, 12) k_link_thread(LinkParams P, const uint32_t *__restrict__ cell_row, const int *__restrict__ cell_ix,
                                                      const uint32_t *__restrict__ row_first, const uint32_t *__restrict__ row_last, int reach,
                                                      LinkQueue Q)
 {
