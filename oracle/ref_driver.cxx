@@ -7,6 +7,7 @@
  *   vrref_search_full_set  -> SearchFullSet                       (src/search.cxx:24)
  *   vrref_potential        -> Potential(Options&,Int_t,Particle*) (src/unbind.cxx:1607)
  *   vrref_unbind           -> CheckUnboundGroups                  (src/unbind.cxx:196)
+ *   vrref_binding_energy   -> GetBindingEnergy                    (src/substructureproperties.cxx:3884)
  *
  * It is compiled against the reference headers where they lie and linked with the reference's own
  * objects into oracle/_ref/libvrref*.so (see oracle/Makefile).  Nothing here re-implements the
@@ -213,6 +214,51 @@ long long vrref_unbind(long long n, const double *pos, const double *vel, const 
     for (long long i = 0; i < n; i++) pfof[i] = pf[i];
     delete[] pf;
     return ng;
+}
+
+/* GetBindingEnergy on GROUP-ORDERED flat arrays: group g = 1..ngroup owns numingroup[g] consecutive particles (the layout
+ * SortAccordingtoBindingEnergy builds, substructureproperties.cxx:4279-4290).  gcmvel[3*g..] is stored into pdata[g].gcmvel
+ * (what GetCM would have left there).  Outputs per particle: potential and binding energy (Particle::rho); per group: T,
+ * Pot, Efrac and the positions inside the group of the minimum-potential and most-bound particles. */
+void vrref_binding_energy(long long n, const double *pos, const double *vel, const double *mass, long long ngroup,
+                          const long long *numingroup_in /* ngroup + 1 */, const double *gcmvel, const vrref_opts *o, double *phi_out,
+                          double *E_out, double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out, long long *ibound_out)
+{
+    Options opt;
+    fill_options(opt, o);
+    opt.ParticleTypeForRefenceFrame = -1;
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, mass, NULL); /* pid = id = position in the group-ordered array */
+    Int_t *pfof = new Int_t[n];
+    Int_t *numingroup = new Int_t[ngroup + 1];
+    Int_t *noffset = new Int_t[ngroup + 1];
+    numingroup[0] = 0;
+    for (long long g = 1; g <= ngroup; g++) numingroup[g] = numingroup_in[g];
+    if (ngroup >= 1) noffset[0] = noffset[1] = 0;
+    for (long long g = 2; g <= ngroup; g++) noffset[g] = noffset[g - 1] + numingroup[g - 1];
+    for (long long g = 1; g <= ngroup; g++)
+        for (Int_t j = 0; j < numingroup[g]; j++) pfof[noffset[g] + j] = g;
+    PropData *pdata = new PropData[ngroup + 1];
+    for (long long g = 1; g <= ngroup; g++) {
+        pdata[g].num = numingroup[g];
+        for (int k = 0; k < 3; k++) pdata[g].gcmvel[k] = gcmvel[3 * g + k];
+        pdata[g].T = pdata[g].Pot = pdata[g].Efrac = 0;
+    }
+    streambuf *old = NULL;
+    stringstream sink;
+    if (!o->verbose) old = cout.rdbuf(sink.rdbuf());
+    GetBindingEnergy(opt, n, P.data(), ngroup, pfof, numingroup, pdata, noffset);
+    if (old) cout.rdbuf(old);
+    for (long long i = 0; i < n; i++) { phi_out[i] = P[i].GetPotential(); E_out[i] = P[i].GetDensity(); }
+    for (long long g = 1; g <= ngroup; g++) {
+        T_out[g] = pdata[g].T; Pot_out[g] = pdata[g].Pot; Efrac_out[g] = pdata[g].Efrac;
+        iminpot_out[g] = pdata[g].iminpot - noffset[g];
+        ibound_out[g] = pdata[g].ibound - noffset[g];
+    }
+    delete[] pdata;
+    delete[] pfof;
+    delete[] numingroup;
+    delete[] noffset;
 }
 
 } /* extern "C" */

@@ -815,3 +815,71 @@ long long vro_unbind(long long n, const double *pos, const double *vel, const do
     free(gmass); free(cmvel); free(c.marg); free(gp); free(off); free(num);
     return ng;
 }
+
+
+/* ------------------------------------------------------------------------------------------------------
+ * GetBindingEnergy (substructureproperties.cxx:3884-4255), default reference frame.  See vr_oracle.h.
+ * ------------------------------------------------------------------------------------------------------ */
+void vro_binding_energy(long long n, const double *pos, const double *vel, const double *mass, long long ngroups,
+                        const long long *off, const double *gcmvel, double G, double eps, double theta, int bucket,
+                        long long large_threshold, double *phi, double *E, double *T_out, double *Pot_out, double *Efrac_out,
+                        long long *iminpot_out, long long *ibound_out)
+{
+    const double eps2 = eps * eps;
+    for (i64 j = 0; j < n; j++) { phi[j] = 0.0; E[j] = 0.0; }
+    for (i64 g = 1; g <= ngroups; g++) {
+        const i64 o = off[g], ng = off[g + 1] - off[g];
+        double Pot = 0.0, Tsum = 0.0, Efrac = 0.0;
+        if (ng <= 0) { T_out[g] = Pot_out[g] = Efrac_out[g] = 0.0; iminpot_out[g] = ibound_out[g] = 0; continue; }
+        const int large = ng >= large_threshold;
+        if (!large) {
+            /* :3922-3940 pair loop, potentials accumulate in place, pdata.Pot sums the pairs */
+            for (i64 j = 0; j < ng; j++)
+                for (i64 k = j + 1; k < ng; k++) {
+                    double r2 = 0.;
+                    for (int d = 0; d < 3; d++) r2 += pow(pos[3 * (o + j) + d] - pos[3 * (o + k) + d], 2.0);
+                    r2 += eps2;
+                    r2 = 1.0 / sqrt(r2);
+                    double pot = -G * (mass[o + j] * mass[o + k]) * r2;
+                    Pot += pot;
+                    phi[o + j] = phi[o + j] + pot;
+                    phi[o + k] = phi[o + k] + pot;
+                }
+        } else {
+            /* :4060-4073 Potential() on the group's slice */
+            vro_potential_tree(ng, pos + 3 * o, mass + o, G, eps, theta, bucket, phi + o, NULL);
+        }
+        /* minimum potential particle: first strict minimum (:4003-4016 / :4150-4163) */
+        {
+            double potmin = phi[o];
+            i64 ipotmin = 0;
+            for (i64 j = 0; j < ng; j++)
+                if (phi[o + j] < potmin) { potmin = phi[o + j]; ipotmin = j; }
+            iminpot_out[g] = ipotmin;
+        }
+        /* kinetic energies in the frame GetCM left in gcmvel (:4025-4052 small, :4166-4209 large) */
+        for (i64 j = 0; j < ng; j++) {
+            double v2 = 0.;
+            for (int d = 0; d < 3; d++) v2 += pow(vel[3 * (o + j) + d] - gcmvel[3 * g + d], 2.0);
+            double Ti = 0.5 * mass[o + j] * v2;
+            if (large) {
+                Pot += phi[o + j];
+                E[o + j] = phi[o + j] + Ti;
+            } else
+                E[o + j] = Ti + phi[o + j];
+            Tsum += Ti;
+            if (E[o + j] < 0.0) Efrac += 1.0;
+        }
+        T_out[g] = Tsum;
+        Pot_out[g] = Pot;
+        Efrac_out[g] = Efrac / (double)ng;
+        /* most bound particle: first strict minimum of E (:4216-4226) */
+        {
+            double Emost = E[o];
+            i64 imost = 0;
+            for (i64 j = 0; j < ng; j++)
+                if (E[o + j] < Emost) { Emost = E[o + j]; imost = j; }
+            ibound_out[g] = imost;
+        }
+    }
+}

@@ -69,6 +69,20 @@ long long vro_unbind(long long n, const double *pos, const double *vel, const do
                      long long ngroups, const vro_unbind_opts *opts, const long long *pid, double marginal_tol,
                      long long *n_marginal_out, double *phi_out, int *changed_out);
 
+/* GetBindingEnergy (substructureproperties.cxx:3884-4255) for the default frame (uinfo.cmvelreftype = CMVELREF,
+ * ParticleTypeForRefenceFrame = -1, masses stored): SURVEY 8f row f1, the third potential evaluation of every group.
+ * Particles are GROUP ORDERED: group g = 1..ngroups owns [off[g], off[g+1]) with off[1] = 0 (the layout
+ * SortAccordingtoBindingEnergy hands over, :4279-4290); gcmvel[3*g..] is the kinetic reference velocity GetCM left in
+ * pdata[g].gcmvel.  Groups below large_threshold (ompunbindnum, ompvar.h:27) take the pair loop (:3922-3940) -- and
+ * their Pot is the sum over PAIRS; larger groups take Potential() and their Pot is the sum over PARTICLES (:4184: twice
+ * the pair sum; reproduced as is).  Outputs: phi[n] (Particle::phi), E[n] = T_i + phi_i (Particle::rho, :4037/:4186),
+ * per group T, Pot, Efrac (bound fraction), index within the group of the minimum-potential particle (:4003-4016) and of
+ * the most bound particle (:4216-4226). */
+void vro_binding_energy(long long n, const double *pos, const double *vel, const double *mass, long long ngroups,
+                        const long long *off /* ngroups + 2 */, const double *gcmvel /* 3 * (ngroups + 1) */, double G,
+                        double eps, double theta, int bucket, long long large_threshold, double *phi_out, double *E_out,
+                        double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out, long long *ibound_out);
+
 #ifdef __cplusplus
 }
 #endif

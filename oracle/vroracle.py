@@ -113,6 +113,10 @@ class Ref:
         L.vrref_unbind.restype = c_ll
         L.vrref_unbind.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, C.POINTER(RefOpts), P_ll, c_ll,
                                    C.POINTER(C.c_int), P_dbl]
+        if hasattr(L, "vrref_binding_energy"):
+            L.vrref_binding_energy.restype = None
+            L.vrref_binding_energy.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, c_ll, P_ll, P_dbl, C.POINTER(RefOpts), P_dbl, P_dbl,
+                                               P_dbl, P_dbl, P_dbl, P_ll, P_ll]
         assert L.vrref_sizeof_particle() == 96
 
     @staticmethod
@@ -165,6 +169,20 @@ class Ref:
         return {"pfof": pf, "ngroups": int(ng), "changed": int(ch.value), "seconds": sec.value}
 
 
+    def binding_energy(self, pos, vel, mass, numingroup, gcmvel, opts: RefOpts):
+        """GetBindingEnergy on group-ordered particles; numingroup[g], gcmvel[g] for g = 1..G (index 0 unused)."""
+        pos = _f64(pos); vel = _f64(vel); mass = _f64(mass)
+        num = _i64(numingroup)
+        gc = _f64(gcmvel)
+        n, G = pos.shape[0], num.shape[0] - 1
+        phi = np.zeros(n); E = np.zeros(n)
+        T = np.zeros(G + 1); Pot = np.zeros(G + 1); Ef = np.zeros(G + 1)
+        imin = np.zeros(G + 1, dtype=np.int64); ib = np.zeros(G + 1, dtype=np.int64)
+        self.lib.vrref_binding_energy(n, _pd(pos), _pd(vel), _pd(mass), G, _pl(num), _pd(gc), C.byref(opts), _pd(phi), _pd(E),
+                                      _pd(T), _pd(Pot), _pd(Ef), _pl(imin), _pl(ib))
+        return {"phi": phi, "E": E, "T": T, "Pot": Pot, "Efrac": Ef, "iminpot": imin, "ibound": ib}
+
+
 class UnbindOpts(C.Structure):
     """Mirror of vro_unbind_opts (oracle/vr_oracle.h)."""
     _fields_ = [
@@ -214,6 +232,9 @@ class Oracle:
         L.vro_unbind.restype = c_ll
         L.vro_unbind.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, P_ll, c_ll, C.POINTER(UnbindOpts), P_ll, c_dbl,
                                  P_ll, P_dbl, C.POINTER(C.c_int)]
+        L.vro_binding_energy.restype = None
+        L.vro_binding_energy.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, c_ll, P_ll, P_dbl, c_dbl, c_dbl, c_dbl, C.c_int, c_ll,
+                                         P_dbl, P_dbl, P_dbl, P_dbl, P_dbl, P_ll, P_ll]
 
     def fof3d(self, pos, b, period=None, minsize=20, pid=None):
         pos = _f64(pos)
@@ -265,3 +286,18 @@ class Oracle:
         ng = self.lib.vro_unbind(n, _pd(pos), _pd(vel), _pd(mass), _pl(pf), ngroups, C.byref(uopts), _pl(pid),
                                  marginal_tol, C.byref(nm), _pd(phi), C.byref(ch))
         return {"pfof": pf, "ngroups": int(ng), "n_marginal": int(nm.value), "phi": phi, "changed": int(ch.value)}
+
+    def binding_energy(self, pos, vel, mass, numingroup, gcmvel, G, eps=0.0, theta=0.5, bucket=8, large_threshold=1000):
+        """GetBindingEnergy (substructureproperties.cxx:3884) on group-ordered particles (see vr_oracle.h)."""
+        pos = _f64(pos); vel = _f64(vel); mass = _f64(mass)
+        num = _i64(numingroup)
+        gc = _f64(gcmvel)
+        n, ng = pos.shape[0], num.shape[0] - 1
+        off = np.zeros(ng + 2, dtype=np.int64)
+        off[2:] = np.cumsum(num[1:])
+        phi = np.zeros(n); E = np.zeros(n)
+        T = np.zeros(ng + 1); Pot = np.zeros(ng + 1); Ef = np.zeros(ng + 1)
+        imin = np.zeros(ng + 1, dtype=np.int64); ib = np.zeros(ng + 1, dtype=np.int64)
+        self.lib.vro_binding_energy(n, _pd(pos), _pd(vel), _pd(mass), ng, _pl(off), _pd(gc), G, eps, theta, bucket,
+                                    large_threshold, _pd(phi), _pd(E), _pd(T), _pd(Pot), _pd(Ef), _pl(imin), _pl(ib))
+        return {"phi": phi, "E": E, "T": T, "Pot": Pot, "Efrac": Ef, "iminpot": imin, "ibound": ib}

@@ -8,6 +8,9 @@ Each file holds the float32-exact inputs and the reference's outputs:
   pfof_unb   SearchFullSet, type 5 + Bound_halos=1 (CheckUnboundGroups: direct sum n<=150, tree above)
   phi_tree   Potential() (kd-tree monopole, theta 0.5, bucket 8) of the largest 3D group, member order = index order
   pos_out    positions after the type-5 run (AdjustStructureForPeriod applied)
+
+binding/be_s5.npz: GetBindingEnergy on a group-ordered set holding one group above ompunbindnum (tree branch)
+and a handful below (pair loop): inputs pos/vel/mass/num/gcmvel, reference outputs phi, E, T, Pot, Efrac, iminpot, ibound.
 """
 import os
 import sys
@@ -45,5 +48,31 @@ def main():
         print(name, "groups 3d/6d/unbound:", int(c5.max()), int(c3.max()), int(cu.max()), "largest", len(sel))
 
 
+def binding_energy_case():
+    ref = vroracle.Ref("serial")
+    rng = np.random.default_rng(5)
+    sizes = [1400, 600, 151, 150, 40, 20]
+    pos, vel = [], []
+    for k, s in enumerate(sizes):
+        c = rng.random(3) * 80 + 10
+        r = rng.random(s) ** 1.5 * (0.2 + 0.1 * k)
+        u = rng.normal(size=(s, 3))
+        pos.append(c + r[:, None] * u / np.linalg.norm(u, axis=1)[:, None])
+        vel.append(rng.normal(0, 300, 3) + rng.normal(size=(s, 3)) * (60 + 20 * k))
+    pos = np.concatenate(pos); vel = np.concatenate(vel).astype(np.float32).astype(np.float64)
+    mass = (0.02 * (1 + (rng.random(len(pos)) < 0.2))).astype(np.float32).astype(np.float64)
+    num = np.array([0] + sizes, dtype=np.int64)
+    start = np.concatenate([[0, 0], np.cumsum(sizes)])
+    gcm = np.zeros((len(sizes) + 1, 3))
+    for g in range(1, len(sizes) + 1):
+        sl = slice(start[g], start[g + 1])
+        gcm[g] = (vel[sl] * mass[sl, None]).sum(0) / mass[sl].sum()
+    r = ref.binding_energy(pos, vel, mass, num, gcm, vroracle.default_opts())
+    os.makedirs(os.path.join(HERE, "binding"), exist_ok=True)
+    np.savez_compressed(os.path.join(HERE, "binding", "be_s5.npz"), pos=pos, vel=vel, mass=mass, num=num, gcmvel=gcm, **r)
+    print("be_s5", "groups", len(sizes), "Efrac", np.round(r["Efrac"][1:], 3))
+
+
 if __name__ == "__main__":
+    binding_energy_case()
     main()

@@ -81,3 +81,17 @@ def test_oracle_tree_potential(oracle, path):
     # and the monopole tree agrees with the direct sum to its truncation error (~1e-2 at theta=0.5)
     pp = oracle.potential_pp(pos, d["mass"][sel], 43.0211349, 0.0)
     assert np.max(np.abs(phi / pp - 1.0)) < 5e-2
+
+
+def test_oracle_binding_energy(oracle):
+    """GetBindingEnergy restatement against the reference's own outputs (be_s5.npz)."""
+    import vroracle
+    z = np.load(os.path.join(HERE, "golden", "binding", "be_s5.npz"))
+    ro = vroracle.default_opts()
+    got = oracle.binding_energy(z["pos"], z["vel"], z["mass"], z["num"], z["gcmvel"], ro.G, ro.eps, ro.TreeThetaOpen, ro.BucketSize, 1000)
+    small = np.repeat(z["num"][1:] < 1000, z["num"][1:])
+    assert np.array_equal(got["phi"][small], z["phi"][small]) and np.array_equal(got["E"][small], z["E"][small])
+    assert np.max(np.abs(got["phi"][~small] / z["phi"][~small] - 1.0)) < 1e-12
+    assert np.allclose(got["T"], z["T"], rtol=1e-12) and np.allclose(got["Pot"], z["Pot"], rtol=1e-11)
+    assert np.array_equal(got["Efrac"], z["Efrac"])
+    assert np.array_equal(got["iminpot"], z["iminpot"]) and np.array_equal(got["ibound"], z["ibound"])

@@ -130,3 +130,47 @@ def test_single_halo_search_full_set(ref, oracle):
     assert ndiff <= got["n_marginal"]
     if ndiff == 0:
         assert got["ngroups"] == r["ngroups"] and np.array_equal(got["pfof"], cr)
+
+
+def test_binding_energy(ref, oracle):
+    """SURVEY 8f row f1 (next row after the hot path): GetBindingEnergy (substructureproperties.cxx:3884-4255) -- pair-loop
+    potentials below ompunbindnum, Potential() above, kinetic energies in the frame left by GetCM, bound fraction, minimum
+    potential and most bound particles.  Group-ordered input as SortAccordingtoBindingEnergy hands it over."""
+    import vroracle
+    nside = 48
+    d = vrsynth.make_box(nside ** 3, 21)
+    rng = np.random.default_rng(4)
+    pos0 = np.mod(d["pos"] + rng.random(d["pos"].shape) * 1e-7, vrsynth.BOX)      # no tied kd-tree medians
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(pos0, b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(pos0, vrsynth.BOX, pf, ng)
+    order = np.argsort(pf, kind="stable")
+    order = order[pf[order] > 0]
+    gp, gv, gm = pos[order], d["vel"][order], d["mass"][order]
+    num = np.bincount(pf, minlength=ng + 1).astype(np.int64)
+    num[0] = 0
+    assert num[1] >= 1000 and num[-1] < 1000                                        # both branches are exercised
+    gcm = np.zeros((ng + 1, 3))
+    start = np.concatenate([[0, 0], np.cumsum(num[1:])])
+    for g in range(1, ng + 1):
+        sl = slice(start[g], start[g + 1])
+        gcm[g] = (gv[sl] * gm[sl, None]).sum(0) / gm[sl].sum()
+    ro = vroracle.default_opts()
+    want = ref.binding_energy(gp, gv, gm, num, gcm, ro)
+    got = oracle.binding_energy(gp, gv, gm, num, gcm, ro.G, ro.eps, ro.TreeThetaOpen, ro.BucketSize, 1000)
+    small = np.repeat(num[1:] < 1000, num[1:])
+    assert np.array_equal(got["phi"][small], want["phi"][small])                     # pair loop: bit exact
+    assert np.array_equal(got["E"][small], want["E"][small])
+    assert np.max(np.abs(got["phi"][~small] / want["phi"][~small] - 1.0)) < 1e-12    # tree: same tree, fp reassociation only
+    assert np.allclose(got["E"], want["E"], rtol=1e-11, atol=1e-9 * np.abs(want["phi"]).max())
+    gs = num[1:] < 1000
+    assert np.array_equal(got["T"][1:][gs], want["T"][1:][gs]) and np.array_equal(got["Pot"][1:][gs], want["Pot"][1:][gs])
+    assert np.allclose(got["T"][1:], want["T"][1:], rtol=1e-12) and np.allclose(got["Pot"][1:], want["Pot"][1:], rtol=1e-11)
+    assert np.array_equal(got["Efrac"][1:], want["Efrac"][1:])
+    assert np.array_equal(got["iminpot"][1:], want["iminpot"][1:]) and np.array_equal(got["ibound"][1:], want["ibound"][1:])
+    # the quirk the GPU row will have to keep: Pot of a large group counts every pair twice, Pot of a small one once
+    g_small = int(np.flatnonzero(gs)[0]) + 1
+    sl = slice(start[g_small], start[g_small + 1])
+    assert abs(want["Pot"][g_small] / (0.5 * want["phi"][sl].sum()) - 1.0) < 1e-12
+    sl = slice(start[1], start[2])
+    assert abs(want["Pot"][1] / want["phi"][sl].sum() - 1.0) < 1e-12
