@@ -124,6 +124,20 @@ int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const lo
                     const long long *index, double G, double eps, double theta, int bucket,
                     long long pp_threshold, double *phi_out);
 
+/* Binding energies of finished groups.  Replaces GetBindingEnergy
+ * (src/substructureproperties.cxx:3884-4255) for the default reference frame (ParticleTypeForRefenceFrame = -1, no
+ * per-type mass weights).  The view holds the particles in group order: group g (0-based) = records
+ * [offsets[g], offsets[g+1]), offsets[0] = 0 (the reference's numingroup / noffset); gcmvel[3*g..] = pdata[].gcmvel.
+ * Groups below large_threshold (ompunbindnum, 1000) use the pair sum (:3922-3940), the others Potential() (:4060-4073).
+ * Per particle (may be NULL): phi_out (Particle::SetPotential), E_out (kinetic + potential, what the reference leaves in
+ * Particle::SetDensity).  Per group: T, Pot (pair sum for small groups, sum of the members' potentials for large ones --
+ * the reference's own convention), Efrac, and the member offsets inside the group of the minimum potential (:4003-4016)
+ * and the most bound particle (:4216-4241). */
+int vrgpu_binding_energy(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const double *gcmvel,
+                         double G, double eps, double theta, int bucket, long long large_threshold, double *phi_out,
+                         double *E_out, double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out,
+                         long long *ibound_out);
+
 /* CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729).  pfof in/out (0 = unbound), group ids
  * re-ordered by size when anything changed (ireorder=1).  *changed_out = the reference's return flag. */
 int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long long *ngroups_inout,

@@ -24,6 +24,9 @@ Int_t *SearchFullSetGPU(Options &opt, const Int_t nbodies, vector<NBody::Particl
 int CheckUnboundGroupsGPU(Options opt, const Int_t nbodies, NBody::Particle *Part, Int_t &ngroup, Int_t *&pfof, Int_t *numingroup = NULL,
                           Int_t **pglist = NULL, int ireorder = 1, Int_t *groupflag = NULL);
 void PotentialGPU(Options &opt, Int_t nbodies, NBody::Particle *Part);
+void GetBindingEnergyGPU(Options &opt, const Int_t nbodies, NBody::Particle *Part, Int_t ngroup, Int_t *&pfof, Int_t *&numingroup,
+                         PropData *&pdata, Int_t *&noffset);
+#define GetBindingEnergy GetBindingEnergyGPU
 #define SearchFullSet SearchFullSetGPU
 #define CheckUnboundGroups CheckUnboundGroupsGPU
 #define Potential PotentialGPU

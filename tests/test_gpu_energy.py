@@ -1,0 +1,136 @@
+"""GPU parity: vrgpu_binding_energy against the reference's own GetBindingEnergy outputs
+(tests/golden/binding/be_s5.npz, substructureproperties.cxx:3884-4255) and against the oracle restatement
+(oracle/vr_oracle.c: vro_binding_energy, pinned to the reference in tests/test_oracle_vs_ref.py).
+
+Tolerances: potentials and energies 1e-10 relative to the group's potential scale (BASELINE.json asks 1e-6); T and Pot 1e-11;
+Efrac may differ by the members whose |E| is below the tolerance; the minimum-potential / most-bound member must hold a
+value within the tolerance of the reference's minimum.
+
+NOT YET RUN ON A GPU: the entry point was written after round 1's GPU budget was spent, so these tests are switched on
+with VRGPU_RUN_UNVERIFIED=1 until their first green run on a B200 (then the switch goes away)."""
+import os
+
+import numpy as np
+import pytest
+
+import vrsynth
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
+                                 reason="vrgpu_binding_energy has not had its first GPU run (set VRGPU_RUN_UNVERIFIED=1)")]
+HERE = os.path.dirname(os.path.abspath(__file__))
+TOL = 1e-10
+
+
+def _compare(got, want, sizes):
+    """want: dict with per-particle phi, E and per-group T, Pot, Efrac, iminpot, ibound for the groups in `sizes` (0-based)."""
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    for g, n in enumerate(sizes):
+        if n == 0:
+            assert got["T"][g] == 0 and got["Pot"][g] == 0 and got["Efrac"][g] == 0
+            continue
+        sl = slice(off[g], off[g + 1])
+        scale = np.max(np.abs(want["phi"][sl]))
+        assert np.max(np.abs(got["phi"][sl] - want["phi"][sl])) <= TOL * scale, g
+        assert np.max(np.abs(got["E"][sl] - want["E"][sl])) <= TOL * scale, g
+        assert abs(got["T"][g] - want["T"][g]) <= 1e-11 * abs(want["T"][g]), g
+        assert abs(got["Pot"][g] - want["Pot"][g]) <= 1e-10 * abs(want["Pot"][g]), g
+        marginal = int(np.count_nonzero(np.abs(want["E"][sl]) <= TOL * scale))
+        assert abs(got["Efrac"][g] - want["Efrac"][g]) * n <= marginal + 1e-9, g
+        for key, arr in (("iminpot", "phi"), ("ibound", "E")):
+            j = int(got[key][g])
+            assert 0 <= j < n
+            assert want[arr][sl][j] <= want[arr][sl].min() + TOL * scale, (g, key)
+            if np.count_nonzero(want[arr][sl] <= want[arr][sl].min() + TOL * scale) == 1:
+                assert j == int(want[key][g]), (g, key)
+
+
+def test_binding_energy_golden(gpu_ctx):
+    import vrgpu
+    import vroracle
+    z = np.load(os.path.join(HERE, "golden", "binding", "be_s5.npz"))
+    ro = vroracle.default_opts()
+    sizes = z["num"][1:]
+    parts = vrgpu.particles_from_arrays(z["pos"], z["vel"], z["mass"])
+    got = gpu_ctx.binding_energy(parts, np.concatenate([[0], np.cumsum(sizes)]), z["gcmvel"][1:], ro.G, ro.eps, ro.TreeThetaOpen,
+                                 ro.BucketSize, 1000)
+    want = {k: (z[k] if k in ("phi", "E") else z[k][1:]) for k in ("phi", "E", "T", "Pot", "Efrac", "iminpot", "ibound")}
+    _compare(got, want, sizes)
+
+
+def _group_ordered(d, pfof, ng):
+    order = np.argsort(pfof, kind="stable")
+    order = order[pfof[order] > 0]
+    num = np.bincount(pfof, minlength=ng + 1)
+    num[0] = 0
+    pos, vel, mass = d["pos"][order], d["vel"][order], d["mass"][order]
+    start = np.concatenate([[0, 0], np.cumsum(num[1:])])
+    gcm = np.zeros((ng + 1, 3))
+    for g in range(1, ng + 1):
+        sl = slice(start[g], start[g + 1])
+        gcm[g] = (vel[sl] * mass[sl, None]).sum(0) / mass[sl].sum()
+    return pos, vel, mass, num, gcm
+
+
+@pytest.mark.parametrize("nside,seed,large", [(48, 21, 1000), (64, 4, 300)])
+def test_binding_energy_box_matches_oracle(gpu_ctx, oracle, nside, seed, large):
+    """Every FOF group of a synthetic box, laid out the way GetBindingEnergy receives them (sorted by group id)."""
+    import vrgpu
+    import vroracle
+    d = vrsynth.make_box(nside ** 3, seed)
+    ell = vrsynth.BOX / nside
+    b = float(np.sqrt((ell * ell) * (0.2 * 0.2) * (1.0 * 1.0)))
+    pfof, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    d["pos"] = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pfof, ng)
+    pos, vel, mass, num, gcm = _group_ordered(d, pfof, ng)
+    ro = vroracle.default_opts()
+    want = oracle.binding_energy(pos, vel, mass, num, gcm, ro.G, ro.eps, ro.TreeThetaOpen, ro.BucketSize, large)
+    want = {k: (want[k] if k in ("phi", "E") else want[k][1:]) for k in ("phi", "E", "T", "Pot", "Efrac", "iminpot", "ibound")}
+    parts = vrgpu.particles_from_arrays(pos, vel, mass)
+    got = gpu_ctx.binding_energy(parts, np.concatenate([[0], np.cumsum(num[1:])]), gcm[1:], ro.G, ro.eps, ro.TreeThetaOpen,
+                                 ro.BucketSize, large)
+    assert num[1:].max() >= large > num[1:].min()  # both branches taken
+    _compare(got, want, num[1:])
+
+
+def test_binding_energy_edge_cases(gpu_ctx, oracle):
+    """An empty group between two others, a group reduced by a whole CTA (>= 32768 members), trailing records that belong
+    to no group, and no groups at all."""
+    import vrgpu
+    import vroracle
+    rng = np.random.default_rng(8)
+    sizes = np.array([40000, 0, 25, 1000, 999])
+    ntot = int(sizes.sum())
+    r = rng.random(ntot + 50) ** 1.5
+    u = rng.normal(size=(ntot + 50, 3))
+    pos = 50.0 + r[:, None] * u / np.linalg.norm(u, axis=1)[:, None]
+    vel = rng.normal(0, 150, (ntot + 50, 3))
+    mass = 0.5 + rng.random(ntot + 50)
+    num = np.concatenate([[0], sizes])
+    gcm = rng.normal(0, 10, (len(sizes) + 1, 3))
+    ro = vroracle.default_opts()
+    want = oracle.binding_energy(pos[:ntot], vel[:ntot], mass[:ntot], num, gcm, ro.G, ro.eps, ro.TreeThetaOpen, ro.BucketSize, 1000)
+    want = {k: (want[k] if k in ("phi", "E") else want[k][1:]) for k in ("phi", "E", "T", "Pot", "Efrac", "iminpot", "ibound")}
+    parts = vrgpu.particles_from_arrays(pos, vel, mass)
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    got = gpu_ctx.binding_energy(parts, off, gcm[1:], ro.G, ro.eps, ro.TreeThetaOpen, ro.BucketSize, 1000)
+    _compare(got, want, sizes)
+    none = gpu_ctx.binding_energy(parts, np.array([0]), np.zeros((0, 3)), ro.G)
+    assert none["T"].size == 0
+    with pytest.raises(vrgpu.VrgpuError):
+        gpu_ctx.binding_energy(parts, np.array([0, ntot + 51]), gcm[1:2], ro.G)
+
+
+def test_binding_energy_through_reference_types(ref):
+    """The adaptor's GetBindingEnergy body (host/vrgpu_adaptor.cxx) against the reference's, both driven through the
+    reference's own Options / Particle / PropData by the same bridge (oracle/ref_driver.cxx)."""
+    import vroracle
+    if not vroracle.Ref.available("gpu"):
+        pytest.skip("oracle/_ref/libvrref_gpu.so not built")
+    refgpu = vroracle.Ref("gpu")
+    z = np.load(os.path.join(HERE, "golden", "binding", "be_s5.npz"))
+    o = vroracle.default_opts()
+    want = ref.binding_energy(z["pos"], z["vel"], z["mass"], z["num"], z["gcmvel"], o)
+    got = refgpu.binding_energy(z["pos"], z["vel"], z["mass"], z["num"], z["gcmvel"], o)
+    strip = lambda r: {k: (r[k] if k in ("phi", "E") else r[k][1:]) for k in ("phi", "E", "T", "Pot", "Efrac", "iminpot", "ibound")}
+    _compare(strip(got), strip(want), z["num"][1:])

@@ -326,6 +326,26 @@ int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const lo
     });
 }
 
+int vrgpu_binding_energy(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const double *gcmvel, double G,
+                         double eps, double theta, int bucket, long long large_threshold, double *phi_out, double *E_out, double *T_out,
+                         double *Pot_out, double *Efrac_out, long long *iminpot_out, long long *ibound_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(ngroups >= 0 && offsets, VRGPU_EINVAL, "bad arguments");
+        CallTimer ct(ctx);
+        if (ngroups == 0) return;
+        VR_REQUIRE(gcmvel && T_out && Pot_out && Efrac_out && iminpot_out && ibound_out, VRGPU_EINVAL, "null per-group array");
+        DeviceParticles P;
+        {
+            StageTimer t(ctx);
+            upload_view(ctx, view, true, true, false, P);
+            ctx->stats.h2d_ms += t.stop();
+        }
+        binding_energy_host(ctx, P, ngroups, offsets, gcmvel, G, eps, theta, bucket, large_threshold, phi_out, E_out, T_out, Pot_out,
+                            Efrac_out, iminpot_out, ibound_out);
+    });
+}
+
 int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long long *ngroups_inout, const vrgpu_unbind_opts *opts,
                  int *changed_out, long long *n_marginal_out)
 {

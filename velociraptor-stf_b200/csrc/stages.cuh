@@ -23,6 +23,12 @@ void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngro
                         const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,
                         double *phi_out_host);
 
+// GetBindingEnergy (src/substructureproperties.cxx:3884-4255) for group-ordered particles (energy.cu)
+void binding_energy_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                         const double *gcmvel_host, double G, double eps, double theta, int bucket, long long large_threshold,
+                         double *phi_out, double *E_out, double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out,
+                         long long *ibound_out);
+
 // CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729) on device-resident particles
 void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
                    int &changed, long long &n_marginal);

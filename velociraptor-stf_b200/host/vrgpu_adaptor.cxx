@@ -1,11 +1,12 @@
 /* velociraptor-stf_b200/host/vrgpu_adaptor.cxx -- the reference-side host adaptor.
  *
- * Replacement bodies, with the reference's own signatures (src/proto.h:203,273,279), for the three entry points the
- * B200 path takes over:
+ * Replacement bodies, with the reference's own signatures (src/proto.h), for the entry points the B200 path takes over:
  *
  *     Int_t *SearchFullSet(Options&, const Int_t, vector<Particle>&, Int_t&)          src/search.cxx:24
  *     int    CheckUnboundGroups(Options, const Int_t, Particle*, Int_t&, Int_t*&, ...)  src/unbind.cxx:196
  *     void   Potential(Options&, Int_t, Particle*)                                      src/unbind.cxx:1607
+ *     void   GetBindingEnergy(Options&, const Int_t, Particle*, Int_t, Int_t*&, Int_t*&, PropData*&, Int_t*&)
+ *                                                                    src/substructureproperties.cxx:3884  (row f1, next)
  *
  * They marshal nothing: libvrgpu reads the caller's NBody::Particle array through a strided view (vrgpu_view).  This
  * file is compiled against the reference's headers (stf.h) by whoever builds the reference with the GPU path; it is
@@ -227,4 +228,67 @@ void VRGPU_NAME(Potential)(Options &opt, Int_t nbodies, Particle *Part)
     for (Int_t i = 0; i < nbodies; i++) Part[i].SetPotential(phi[i]);
     delete[] phi;
     delete[] index;
+}
+
+/* GetBindingEnergy (src/substructureproperties.cxx:3884-4255), default frame.  Part is in group order (numingroup /
+ * noffset), pdata[].gcmvel holds the frame GetCM left.  Writes what the reference writes: Part[].phi (SetPotential),
+ * the total energy in Part[].rho (SetDensity), pdata[].T / Pot / Efrac, iminpot + gposminpot / gvelminpot, ibound +
+ * gposmbp / gvelmbp.  Builds with GASON / STARON / NOMASS, the minimum-potential frame (cmvelreftype = POTREF), a
+ * restricted ParticleTypeForRefenceFrame and pre-loaded potentials (icalculatepotential = 0) stay on the CPU path. */
+void VRGPU_NAME(GetBindingEnergy)(Options &opt, const Int_t nbodies, Particle *Part, Int_t ngroup, Int_t *&pfof, Int_t *&numingroup,
+                                  PropData *&pdata, Int_t *&noffset)
+{
+#if defined(GASON) || defined(STARON) || defined(NOMASS)
+#error "the GPU GetBindingEnergy covers the dark-matter build only (no GASON / STARON / NOMASS)"
+#endif
+    (void)pfof;
+    if (opt.uinfo.cmvelreftype == POTREF || opt.ParticleTypeForRefenceFrame != -1 || !opt.uinfo.icalculatepotential) {
+        cerr << "vrgpu: GetBindingEnergy on the GPU path needs the CM frame, all particle types and Calculate potential on" << endl;
+        exit(9);
+    }
+    if (ngroup <= 0) return;
+    long long *offsets = new long long[ngroup + 1];
+    double *gcmvel = new double[3 * ngroup];
+    Int_t ntot = 0;
+    for (Int_t g = 1; g <= ngroup; g++) {
+        if (noffset[g] != ntot) {
+            cerr << "vrgpu: GetBindingEnergy expects particles sorted by group (noffset[" << g << "] = " << noffset[g] << ", expected " << ntot << ")" << endl;
+            exit(9);
+        }
+        offsets[g - 1] = ntot;
+        ntot += numingroup[g];
+        for (int k = 0; k < 3; k++) gcmvel[3 * (g - 1) + k] = pdata[g].gcmvel[k];
+    }
+    offsets[ngroup] = ntot;
+    if (ntot > nbodies) {
+        cerr << "vrgpu: GetBindingEnergy: numingroup sums past nbodies" << endl;
+        exit(9);
+    }
+    double *phi = new double[ntot > 0 ? ntot : 1], *E = new double[ntot > 0 ? ntot : 1];
+    double *T = new double[ngroup], *Pot = new double[ngroup], *Efrac = new double[ngroup];
+    long long *iminpot = new long long[ngroup], *ibound = new long long[ngroup];
+    int rc = vrgpu_binding_energy(context(), view_of(Part, ntot), ngroup, offsets, gcmvel, opt.G, opt.uinfo.eps, opt.uinfo.TreeThetaOpen,
+                                  opt.uinfo.BucketSize, ompunbindnum, phi, E, T, Pot, Efrac, iminpot, ibound);
+    if (rc != VRGPU_OK) die("vrgpu_binding_energy", rc);
+    for (Int_t i = 0; i < ntot; i++) {
+        Part[i].SetPotential(phi[i]);
+        Part[i].SetDensity(E[i]);
+    }
+    for (Int_t g = 1; g <= ngroup; g++) {
+        if (numingroup[g] <= 0) continue;
+        pdata[g].T = T[g - 1];
+        pdata[g].Pot = Pot[g - 1];
+        pdata[g].Efrac = Efrac[g - 1];
+        const Particle &pmin = Part[noffset[g] + iminpot[g - 1]], &pmb = Part[noffset[g] + ibound[g - 1]];
+        pdata[g].iminpot = pmin.GetPID();
+        pdata[g].ibound = pmb.GetPID();
+        for (int k = 0; k < 3; k++) {
+            pdata[g].gposminpot[k] = pmin.GetPosition(k);
+            pdata[g].gvelminpot[k] = pmin.GetVelocity(k);
+            pdata[g].gposmbp[k] = pmb.GetPosition(k);
+            pdata[g].gvelmbp[k] = pmb.GetVelocity(k);
+        }
+    }
+    delete[] ibound; delete[] iminpot; delete[] Efrac; delete[] Pot; delete[] T; delete[] E; delete[] phi;
+    delete[] gcmvel; delete[] offsets;
 }

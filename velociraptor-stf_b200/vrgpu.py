@@ -119,6 +119,8 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_fof6d.argtypes = [C.c_void_p, View, P_ll, C.c_longlong, C.c_double, C.c_double, C.c_int, C.c_longlong, P_ll, P_ll]
     L.vrgpu_potential.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_ll, C.c_double, C.c_double, C.c_double, C.c_int,
                                   C.c_longlong, P_d]
+    L.vrgpu_binding_energy.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_d, C.c_double, C.c_double, C.c_double, C.c_int,
+                                       C.c_longlong, P_d, P_d, P_d, P_d, P_d, P_ll, P_ll]
     L.vrgpu_unbind.argtypes = [C.c_void_p, View, P_ll, P_ll, C.POINTER(UnbindOpts), C.POINTER(C.c_int), P_ll]
     L.vrgpu_search_full_set.argtypes = [C.c_void_p, View, C.POINTER(SearchOpts), P_ll, P_ll]
     L.vrgpu_particles_upload.argtypes = [C.c_void_p, View]
@@ -144,7 +146,8 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
-                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops"]
+                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops",
+                    "vrgpu_binding_energy"]
 
 
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
@@ -253,6 +256,21 @@ class Context:
         self._check(self.lib.vrgpu_potential(self.h, view_of(parts), ng, offsets.ctypes.data_as(P), index.ctypes.data_as(P),
                                              G, eps, theta, bucket, pp_threshold, phi.ctypes.data_as(C.POINTER(C.c_double))))
         return phi
+
+    def binding_energy(self, parts, offsets, gcmvel, G, eps=0.0, theta=0.5, bucket=8, large_threshold=1000):
+        """GetBindingEnergy (substructureproperties.cxx:3884-4255) for group-ordered particles; group g = parts[offsets[g]:offsets[g+1]]."""
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        gcmvel = np.ascontiguousarray(gcmvel, dtype=np.float64)
+        ng = offsets.shape[0] - 1
+        ntot = int(offsets[-1])
+        r = {"phi": np.zeros(ntot), "E": np.zeros(ntot), "T": np.zeros(ng), "Pot": np.zeros(ng), "Efrac": np.zeros(ng),
+             "iminpot": np.zeros(ng, dtype=np.int64), "ibound": np.zeros(ng, dtype=np.int64)}
+        D, LL = C.POINTER(C.c_double), C.POINTER(C.c_longlong)
+        self._check(self.lib.vrgpu_binding_energy(self.h, view_of(parts), ng, offsets.ctypes.data_as(LL), gcmvel.ctypes.data_as(D), G, eps,
+                                                  theta, bucket, large_threshold, r["phi"].ctypes.data_as(D), r["E"].ctypes.data_as(D),
+                                                  r["T"].ctypes.data_as(D), r["Pot"].ctypes.data_as(D), r["Efrac"].ctypes.data_as(D),
+                                                  r["iminpot"].ctypes.data_as(LL), r["ibound"].ctypes.data_as(LL)))
+        return r
 
     def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
         """CheckUnboundGroups (unbind.cxx:196)."""
