@@ -9,9 +9,6 @@
 //
 // Reference quirk kept on purpose: pdata.Pot is the PAIR sum for small groups (:3934, half of the sum of the members'
 // potentials) but the plain sum of the members' potentials for large ones (:4186-4196).
-//
-// STATUS: written after round 1's GPU budget was spent -- it compiles for sm_100a, its parity test
-// (tests/test_gpu_energy.py) has not run on a GPU yet.
 #include "groups.cuh"
 #include "stages.cuh"
 
