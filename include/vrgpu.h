@@ -138,6 +138,13 @@ int vrgpu_binding_energy(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, con
                          double *E_out, double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out,
                          long long *ibound_out);
 
+/* Ordering of every group's members by a key.  Replaces the per-group qsort of SortAccordingtoBindingEnergy
+ * (src/substructureproperties.cxx:4302-4310; DenCompare = total energy, PotCompare = potential): key[] holds one value per
+ * grouped particle in group order (offsets as in vrgpu_binding_energy); order_out[offsets[g] + j] = offset inside group g
+ * of the member with the j-th smallest key.  Equal keys keep ascending member order (qsort leaves them in any order). */
+int vrgpu_sort_groups_by_key(vrgpu_ctx *ctx, long long ngroups, const long long *offsets, const double *key,
+                             long long *order_out);
+
 /* CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729).  pfof in/out (0 = unbound), group ids
  * re-ordered by size when anything changed (ireorder=1).  *changed_out = the reference's return flag. */
 int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long long *ngroups_inout,

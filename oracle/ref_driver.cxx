@@ -8,6 +8,7 @@
  *   vrref_potential        -> Potential(Options&,Int_t,Particle*) (src/unbind.cxx:1607)
  *   vrref_unbind           -> CheckUnboundGroups                  (src/unbind.cxx:196)
  *   vrref_binding_energy   -> GetBindingEnergy                    (src/substructureproperties.cxx:3884)
+ *   vrref_sort_by_binding_energy -> SortAccordingtoBindingEnergy   (src/substructureproperties.cxx:4256)
  *
  * It is compiled against the reference headers where they lie and linked with the reference's own
  * objects into oracle/_ref/libvrref*.so (see oracle/Makefile).  Nothing here re-implements the
@@ -26,6 +27,7 @@ int CheckUnboundGroupsGPU(Options opt, const Int_t nbodies, NBody::Particle *Par
 void PotentialGPU(Options &opt, Int_t nbodies, NBody::Particle *Part);
 void GetBindingEnergyGPU(Options &opt, const Int_t nbodies, NBody::Particle *Part, Int_t ngroup, Int_t *&pfof, Int_t *&numingroup,
                          PropData *&pdata, Int_t *&noffset);
+void SortGroupParticlesGPU(Options &opt, NBody::Particle *Part, Int_t ngroup, Int_t *numingroup, Int_t *noffset, PropData *pdata);
 #define GetBindingEnergy GetBindingEnergyGPU
 #define SearchFullSet SearchFullSetGPU
 #define CheckUnboundGroups CheckUnboundGroupsGPU
@@ -67,6 +69,8 @@ typedef struct {
     double TreeThetaOpen;     /* uinfo.TreeThetaOpen                               */
     int BucketSize;           /* uinfo.BucketSize                                  */
     int verbose;
+    int iterate_cm;           /* Options::iIterateCM (allvars.h:714, default 1)    */
+    int sort_by_binding_energy; /* Options::iSortByBindingEnergy (allvars.h:750, default 1) */
 } vrref_opts;
 
 static void fill_options(Options &opt, const vrref_opts *o)
@@ -104,6 +108,8 @@ static void fill_options(Options &opt, const vrref_opts *o)
     opt.uinfo.BucketSize = o->BucketSize;
     opt.uinfo.icalculatepotential = true;
     opt.uinfo.unbindflag = 1;
+    opt.iIterateCM = o->iterate_cm;
+    opt.iSortByBindingEnergy = o->sort_by_binding_energy;
 }
 
 static void fill_particles(vector<Particle> &P, long long n, const double *pos, const double *vel,
@@ -262,6 +268,76 @@ void vrref_binding_energy(long long n, const double *pos, const double *vel, con
     delete[] pfof;
     delete[] numingroup;
     delete[] noffset;
+}
+
+/* SortAccordingtoBindingEnergy (src/substructureproperties.cxx:4256-4352): pfof by particle index in, per group the PIDs
+ * and total energies in the order the reference leaves the particles in, numingroup and pglist[g][numingroup[g]]
+ * (= pdata[g].iunbound) out.  libvrref.so runs the reference's function whole.  libvrref_gpu.so runs the flow a
+ * maintainer gets after the INTEGRATION.md patch: particles brought into group order, the reference's own GetCM, then
+ * GetBindingEnergy and the per-group sort on the B200 (the other property calculations of the reference do not feed the
+ * ordering and are left out of this harness). */
+void vrref_sort_by_binding_energy(long long n, const double *pos, const double *vel, const double *mass, const long long *pid,
+                                  const long long *pfof_in, long long ngroup, const vrref_opts *o, long long *pid_sorted,
+                                  double *E_sorted, long long *numingroup_out /* ngroup + 1 */, long long *iunbound_out /* ngroup + 1 */)
+{
+    Options opt;
+    fill_options(opt, o);
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, mass, pid);
+    Int_t *pfof = new Int_t[n > 0 ? n : 1];
+    Int_t *numingroup = new Int_t[ngroup + 1];
+    for (long long g = 0; g <= ngroup; g++) numingroup[g] = 0;
+    for (long long i = 0; i < n; i++) { pfof[i] = pfof_in[i]; if (pfof[i] > 0) numingroup[pfof[i]]++; }
+    PropData *pdata = new PropData[ngroup + 1];
+    /* every group is a field halo: what CopyHierarchy (search.cxx:3658-3659) records for level-0 objects */
+    for (long long g = 0; g <= ngroup; g++) pdata[g].hostid = pdata[g].directhostid = GROUPNOPARENT;
+    streambuf *old = NULL;
+    stringstream sink;
+    if (!o->verbose) old = cout.rdbuf(sink.rdbuf());
+    long long k = 0;
+#ifdef VRREF_USE_GPU
+    Int_t *noffset = new Int_t[ngroup + 2];
+    noffset[0] = 0;
+    if (ngroup >= 1) noffset[1] = 0;
+    for (long long g = 2; g <= ngroup + 1; g++) noffset[g] = noffset[g - 1] + numingroup[g - 1];
+    {
+        /* group order: grouped particles by ascending group id, members by ascending index, the rest behind them */
+        vector<Particle> Q(n);
+        vector<Int_t> fill(noffset, noffset + ngroup + 2);
+        Int_t rest = ngroup >= 1 ? noffset[ngroup + 1] : 0;
+        for (long long i = 0; i < n; i++) Q[pfof[i] > 0 ? fill[pfof[i]]++ : rest++] = P[i];
+        P.swap(Q);
+    }
+    for (long long g = 1; g <= ngroup; g++) pdata[g].num = numingroup[g];
+    GetCM(opt, n, P.data(), ngroup, pfof, numingroup, pdata, noffset);
+    GetBindingEnergy(opt, n, P.data(), ngroup, pfof, numingroup, pdata, noffset);
+    SortGroupParticlesGPU(opt, P.data(), ngroup, numingroup, noffset, pdata);
+    for (long long g = 1; g <= ngroup; g++) {
+        for (Int_t j = 0; j < numingroup[g]; j++, k++) {
+            pid_sorted[k] = P[noffset[g] + j].GetPID();
+            E_sorted[k] = P[noffset[g] + j].GetDensity();
+        }
+        iunbound_out[g] = pdata[g].iunbound;
+    }
+    delete[] noffset;
+#else
+    Int_t **pglist = SortAccordingtoBindingEnergy(opt, n, P.data(), ngroup, pfof, numingroup, pdata);
+    for (long long g = 1; g <= ngroup; g++) {
+        for (Int_t j = 0; j < numingroup[g]; j++, k++) {
+            pid_sorted[k] = P[pglist[g][j]].GetPID();
+            E_sorted[k] = P[pglist[g][j]].GetDensity();
+        }
+        iunbound_out[g] = pglist[g][numingroup[g] > 0 ? numingroup[g] : 0];
+        delete[] pglist[g];
+    }
+    delete[] pglist;
+#endif
+    if (old) cout.rdbuf(old);
+    numingroup_out[0] = 0;
+    for (long long g = 1; g <= ngroup; g++) numingroup_out[g] = numingroup[g];
+    delete[] pdata;
+    delete[] numingroup;
+    delete[] pfof;
 }
 
 } /* extern "C" */

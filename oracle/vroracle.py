@@ -36,6 +36,7 @@ class RefOpts(C.Structure):
         ("fracpotref", c_dbl), ("Npotref", c_ll),
         ("maxunbindfrac", c_dbl), ("maxunboundfracforiterativeunbind", c_dbl), ("maxallowedunboundfrac", c_dbl),
         ("TreeThetaOpen", c_dbl), ("BucketSize", C.c_int), ("verbose", C.c_int),
+        ("iterate_cm", C.c_int), ("sort_by_binding_energy", C.c_int),
     ]
 
 
@@ -69,6 +70,8 @@ def default_opts(**kw) -> RefOpts:
     o.TreeThetaOpen = 0.5
     o.BucketSize = 8
     o.verbose = 0
+    o.iterate_cm = 1
+    o.sort_by_binding_energy = 1
     for k, v in kw.items():
         if not hasattr(o, k):
             raise AttributeError(k)
@@ -117,6 +120,10 @@ class Ref:
             L.vrref_binding_energy.restype = None
             L.vrref_binding_energy.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, c_ll, P_ll, P_dbl, C.POINTER(RefOpts), P_dbl, P_dbl,
                                                P_dbl, P_dbl, P_dbl, P_ll, P_ll]
+        if hasattr(L, "vrref_sort_by_binding_energy"):
+            L.vrref_sort_by_binding_energy.restype = None
+            L.vrref_sort_by_binding_energy.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, P_ll, P_ll, c_ll, C.POINTER(RefOpts), P_ll, P_dbl,
+                                                       P_ll, P_ll]
         assert L.vrref_sizeof_particle() == 96
 
     @staticmethod
@@ -181,6 +188,20 @@ class Ref:
         self.lib.vrref_binding_energy(n, _pd(pos), _pd(vel), _pd(mass), G, _pl(num), _pd(gc), C.byref(opts), _pd(phi), _pd(E),
                                       _pd(T), _pd(Pot), _pd(Ef), _pl(imin), _pl(ib))
         return {"phi": phi, "E": E, "T": T, "Pot": Pot, "Efrac": Ef, "iminpot": imin, "ibound": ib}
+
+
+    def sort_by_binding_energy(self, pos, vel, mass, pid, pfof, ngroups, opts: RefOpts):
+        """SortAccordingtoBindingEnergy (substructureproperties.cxx:4256): per group the PIDs / energies in the final particle
+        order, numingroup[0..G] and iunbound[0..G] (pglist[g][numingroup[g]])."""
+        pos = _f64(pos); vel = _f64(vel); mass = _f64(mass)
+        pid = _i64(pid); pf = _i64(pfof)
+        n = pos.shape[0]
+        ps = np.zeros(n, dtype=np.int64); Es = np.zeros(n)
+        num = np.zeros(ngroups + 1, dtype=np.int64); iu = np.zeros(ngroups + 1, dtype=np.int64)
+        self.lib.vrref_sort_by_binding_energy(n, _pd(pos), _pd(vel), _pd(mass), _pl(pid), _pl(pf), ngroups, C.byref(opts), _pl(ps),
+                                              _pd(Es), _pl(num), _pl(iu))
+        ntot = int(num.sum())
+        return {"pid": ps[:ntot], "E": Es[:ntot], "numingroup": num, "iunbound": iu}
 
 
 class UnbindOpts(C.Structure):

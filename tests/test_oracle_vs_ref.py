@@ -174,3 +174,52 @@ def test_binding_energy(ref, oracle):
     assert abs(want["Pot"][g_small] / (0.5 * want["phi"][sl].sum()) - 1.0) < 1e-12
     sl = slice(start[1], start[2])
     assert abs(want["Pot"][1] / want["phi"][sl].sum() - 1.0) < 1e-12
+
+
+@pytest.mark.parametrize("by_energy", [1, 0])
+def test_sort_by_binding_energy(ref, oracle, by_energy):
+    """Second half of row f1: the particle order SortAccordingtoBindingEnergy (substructureproperties.cxx:4256-4352) leaves
+    in every group -- ascending total energy (or potential) -- and pglist[g][n] = first unbound position.  The whole
+    reference function runs (GetCM, GetProperties, GetBindingEnergy, qsort); the oracle side is vro_binding_energy on the
+    group-ordered particles plus an argsort.  Iterate_cm = 0 so that the frame is the plain mass-weighted mean velocity."""
+    import vroracle
+    nside = 48
+    d = vrsynth.make_box(nside ** 3, 21)
+    rng = np.random.default_rng(4)
+    pos0 = np.mod(d["pos"] + rng.random(d["pos"].shape) * 1e-7, vrsynth.BOX)
+    pf, ng = oracle.fof3d(pos0, 0.2 * vrsynth.BOX / nside, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(pos0, vrsynth.BOX, pf, ng)
+    # GetProperties moves the particles into the CM frame and back before GetBindingEnergy runs (1e-14 position noise); a
+    # softening keeps the potential of the closest pairs insensitive to it
+    ro = vroracle.default_opts(period=vrsynth.BOX, iterate_cm=0, sort_by_binding_energy=by_energy, eps=0.01)
+    want = ref.sort_by_binding_energy(pos, d["vel"], d["mass"], d["pid"], pf, ng, ro)
+    num = np.bincount(pf, minlength=ng + 1).astype(np.int64)
+    num[0] = 0
+    assert np.array_equal(want["numingroup"], num)
+    order = np.argsort(pf, kind="stable")
+    order = order[pf[order] > 0]
+    gp, gv, gm, gpid = pos[order], d["vel"][order], d["mass"][order], d["pid"][order]
+    off = np.concatenate([[0], np.cumsum(num[1:])])
+    mv = gv * gm[:, None]
+    gcm = np.concatenate([np.zeros((1, 3)), np.add.reduceat(mv, off[:-1], axis=0) / np.add.reduceat(gm, off[:-1])[:, None]])
+    got = oracle.binding_energy(gp, gv, gm, num, gcm, ro.G, ro.eps, ro.TreeThetaOpen, ro.BucketSize, 1000)
+    nswapped = 0
+    for g in range(1, ng + 1):
+        sl = slice(off[g - 1], off[g])
+        E, key = got["E"][sl], (got["E"][sl] if by_energy else got["phi"][sl])
+        o = np.argsort(key, kind="stable")
+        scale = np.abs(got["phi"][sl]).max()
+        # same members, same energies (frame and potentials agree to rounding), same order up to near-equal keys
+        wp, wE = want["pid"][sl], want["E"][sl]
+        assert np.array_equal(np.sort(wp), np.sort(gpid[sl]))
+        back = np.argsort(gpid[sl])
+        mine = back[np.searchsorted(gpid[sl][back], wp)]       # member offsets in the reference's order
+        # GetProperties runs before GetBindingEnergy and rotates every group into its (iterated) principal-axis frame and
+        # back (GetGlobalSpatialMorphology / RotParticles, :3121-3150, :3560-3598) with a matrix that is orthogonal only to
+        # the iteration's tolerance: the reference's own energies carry that noise (1e-10 typically, 1e-5 seen)
+        assert np.max(np.abs(E[mine] - wE)) <= 1e-4 * scale
+        assert np.all(np.diff(key[mine]) >= -2e-4 * scale)
+        nswapped += int(np.count_nonzero(mine != o))
+        first_unbound = np.flatnonzero(wE > 0)
+        assert want["iunbound"][g] == (first_unbound[0] if first_unbound.size else num[g])
+    assert nswapped <= 2e-3 * off[-1]

@@ -346,6 +346,17 @@ int vrgpu_binding_energy(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, con
     });
 }
 
+int vrgpu_sort_groups_by_key(vrgpu_ctx *ctx, long long ngroups, const long long *offsets, const double *key, long long *order_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(ngroups >= 0 && offsets, VRGPU_EINVAL, "bad arguments");
+        CallTimer ct(ctx);
+        if (ngroups == 0 || offsets[ngroups] == 0) return;
+        VR_REQUIRE(key && order_out, VRGPU_EINVAL, "null key / order array");
+        sort_groups_host(ctx, ngroups, offsets, key, order_out);
+    });
+}
+
 int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long long *ngroups_inout, const vrgpu_unbind_opts *opts,
                  int *changed_out, long long *n_marginal_out)
 {

@@ -236,4 +236,79 @@ void binding_energy_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngr
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Per-group ordering by a key (SortAccordingtoBindingEnergy's qsort by DenCompare / PotCompare,
+// substructureproperties.cxx:4302-4310): two stable LSD radix sorts -- by the order-preserving image of the key, then by
+// group id -- leave every group's members in ascending key order, equal keys in ascending member order.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t en_ordered_bits(double d)
+{
+    const uint64_t u = (uint64_t)__double_as_longlong(d);
+    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+__global__ void k_en_sortkeys(const double *__restrict__ key, uint32_t ntot, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    keys[s] = en_ordered_bits(__dadd_rn(key[s], 0.0)); // -0.0 + 0.0 = +0.0: the two zeros compare equal, like in DenCompare
+    vals[s] = s;
+}
+__global__ void k_en_gidkeys(const uint32_t *__restrict__ gid, const uint32_t *__restrict__ vals, uint32_t ntot, uint64_t *__restrict__ keys)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < ntot) keys[p] = gid[vals[p]];
+}
+// position p of the sorted list lies in the same group as slot p (groups are contiguous and keep their sizes)
+__global__ void k_en_order_out(const uint32_t *__restrict__ vals, const uint32_t *__restrict__ gid, const uint32_t *__restrict__ off,
+                               uint32_t ntot, long long *__restrict__ order)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < ntot) order[p] = (long long)(vals[p] - off[gid[p]]);
+}
+
+void sort_groups_host(vrgpu_ctx *ctx, long long ngroups, const long long *offsets_host, const double *key_host, long long *order_out)
+{
+    const long long ntot = offsets_host[ngroups];
+    VR_REQUIRE(offsets_host[0] == 0, VRGPU_EINVAL, "offsets[0] must be 0");
+    VR_REQUIRE(ntot >= 0 && ntot < 0xfffffff0LL && ngroups < 0x7fffffffLL, VRGPU_EINVAL, "too many grouped particles");
+    if (ntot == 0) return;
+    const int T = 256;
+    const uint32_t NG = (uint32_t)ngroups, N = (uint32_t)ntot;
+    std::vector<uint32_t> off((size_t)ngroups + 2);
+    off[0] = 0;
+    for (long long g = 0; g <= ngroups; g++) {
+        VR_REQUIRE(g == 0 || offsets_host[g] >= offsets_host[g - 1], VRGPU_EINVAL, "offsets must be non-decreasing");
+        off[(size_t)g + 1] = (uint32_t)offsets_host[g];
+    }
+    DBuf<uint32_t> doff(ctx, off.size()), gid(ctx, N), vals(ctx, N), vals_tmp(ctx, N);
+    DBuf<uint64_t> keys(ctx, N), keys_tmp(ctx, N);
+    DBuf<double> key(ctx, N);
+    DBuf<long long> order(ctx, N);
+    {
+        StageTimer t(ctx);
+        KScope k(ctx, "io.upload");
+        VR_CUDA(cudaMemcpyAsync(doff.p, off.data(), off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(key.p, key_host, (size_t)N * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        ctx->stats.h2d_bytes += (long long)(off.size() * sizeof(uint32_t) + (size_t)N * sizeof(double));
+        ctx->stats.h2d_ms += t.stop();
+    }
+    {
+        KScope k(ctx, "energy.sort");
+        const unsigned warp_grid = std::max(1u, std::min<unsigned>(grid_for((size_t)NG * 32, T), (unsigned)ctx->sm_count * 16u));
+        VR_LAUNCH(ctx, k_en_gid, warp_grid, T, 0, doff.p, NG, gid.p);
+        VR_LAUNCH(ctx, k_en_sortkeys, grid_for(N, T), T, 0, key.p, N, keys.p, vals.p);
+        radix_sort_pairs(ctx, keys.p, vals.p, keys_tmp.p, vals_tmp.p, N, 64);
+        VR_LAUNCH(ctx, k_en_gidkeys, grid_for(N, T), T, 0, gid.p, vals.p, N, keys.p);
+        int gbits = 1;
+        while ((1ull << gbits) <= (unsigned long long)NG) gbits++;
+        radix_sort_pairs(ctx, keys.p, vals.p, keys_tmp.p, vals_tmp.p, N, gbits);
+        VR_LAUNCH(ctx, k_en_order_out, grid_for(N, T), T, 0, vals.p, gid.p, doff.p, N, order.p);
+    }
+    {
+        StageTimer t(ctx);
+        download_i64(ctx, order.p, order_out, N);
+        ctx->stats.d2h_ms += t.stop();
+    }
+}
+
 } // namespace vrgpu

@@ -29,6 +29,9 @@ void binding_energy_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngr
                          double *phi_out, double *E_out, double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out,
                          long long *ibound_out);
 
+// per-group ascending order of a host key array (the qsort of SortAccordingtoBindingEnergy, substructureproperties.cxx:4302-4310)
+void sort_groups_host(vrgpu_ctx *ctx, long long ngroups, const long long *offsets_host, const double *key_host, long long *order_out);
+
 // CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729) on device-resident particles
 void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
                    int &changed, long long &n_marginal);

@@ -6,7 +6,9 @@
  *     int    CheckUnboundGroups(Options, const Int_t, Particle*, Int_t&, Int_t*&, ...)  src/unbind.cxx:196
  *     void   Potential(Options&, Int_t, Particle*)                                      src/unbind.cxx:1607
  *     void   GetBindingEnergy(Options&, const Int_t, Particle*, Int_t, Int_t*&, Int_t*&, PropData*&, Int_t*&)
- *                                                                    src/substructureproperties.cxx:3884  (row f1, next)
+ *                                                                    src/substructureproperties.cxx:3884  (row f1)
+ *     void   SortGroupParticlesGPU(Options&, Particle*, Int_t, Int_t*, Int_t*, PropData*)
+ *                        the per-group qsort inside SortAccordingtoBindingEnergy, substructureproperties.cxx:4302-4316
  *
  * They marshal nothing: libvrgpu reads the caller's NBody::Particle array through a strided view (vrgpu_view).  This
  * file is compiled against the reference's headers (stf.h) by whoever builds the reference with the GPU path; it is
@@ -291,4 +293,42 @@ void VRGPU_NAME(GetBindingEnergy)(Options &opt, const Int_t nbodies, Particle *P
     }
     delete[] ibound; delete[] iminpot; delete[] Efrac; delete[] Pot; delete[] T; delete[] E; delete[] phi;
     delete[] gcmvel; delete[] offsets;
+}
+
+/* The per-group sort of SortAccordingtoBindingEnergy (src/substructureproperties.cxx:4302-4316): every group's particles
+ * re-arranged in ascending total energy (Sort_by_binding_energy = 1: the value GetBindingEnergy left in
+ * Particle::GetDensity, DenCompare) or ascending potential (PotCompare); pdata[].iunbound = position of the first
+ * member with positive energy, the group size if there is none.  The keys go to the device, the ordering comes back and
+ * the 96-byte records are permuted here, group by group.  Equal keys keep their order (qsort leaves them in any order). */
+void SortGroupParticlesGPU(Options &opt, Particle *Part, Int_t ngroup, Int_t *numingroup, Int_t *noffset, PropData *pdata)
+{
+    if (ngroup <= 0) return;
+    long long *offsets = new long long[ngroup + 1];
+    Int_t ntot = 0, nmax = 0;
+    for (Int_t g = 1; g <= ngroup; g++) {
+        if (noffset[g] != ntot) {
+            cerr << "vrgpu: SortGroupParticles expects particles sorted by group (noffset[" << g << "] = " << noffset[g] << ", expected " << ntot << ")" << endl;
+            exit(9);
+        }
+        offsets[g - 1] = ntot;
+        ntot += numingroup[g];
+        if (numingroup[g] > nmax) nmax = numingroup[g];
+    }
+    offsets[ngroup] = ntot;
+    double *key = new double[ntot > 0 ? ntot : 1];
+    long long *order = new long long[ntot > 0 ? ntot : 1];
+    for (Int_t i = 0; i < ntot; i++) key[i] = opt.iSortByBindingEnergy ? Part[i].GetDensity() : Part[i].GetPotential();
+    int rc = vrgpu_sort_groups_by_key(context(), ngroup, offsets, key, order);
+    if (rc != VRGPU_OK) die("vrgpu_sort_groups_by_key", rc);
+    vector<Particle> tmp(nmax > 0 ? nmax : 1);
+    for (Int_t g = 1; g <= ngroup; g++) {
+        const Int_t n = numingroup[g], o = noffset[g];
+        for (Int_t j = 0; j < n; j++) tmp[j] = Part[o + j];
+        for (Int_t j = 0; j < n; j++) Part[o + j] = tmp[order[o + j]];
+        pdata[g].iunbound = n;
+        for (Int_t j = 0; j < n; j++) if (Part[o + j].GetDensity() > 0) { pdata[g].iunbound = j; break; }
+    }
+    delete[] order;
+    delete[] key;
+    delete[] offsets;
 }

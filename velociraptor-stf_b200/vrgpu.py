@@ -121,6 +121,7 @@ def load_library(path: str = LIB_PATH):
                                   C.c_longlong, P_d]
     L.vrgpu_binding_energy.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_d, C.c_double, C.c_double, C.c_double, C.c_int,
                                        C.c_longlong, P_d, P_d, P_d, P_d, P_d, P_ll, P_ll]
+    L.vrgpu_sort_groups_by_key.argtypes = [C.c_void_p, C.c_longlong, P_ll, P_d, P_ll]
     L.vrgpu_unbind.argtypes = [C.c_void_p, View, P_ll, P_ll, C.POINTER(UnbindOpts), C.POINTER(C.c_int), P_ll]
     L.vrgpu_search_full_set.argtypes = [C.c_void_p, View, C.POINTER(SearchOpts), P_ll, P_ll]
     L.vrgpu_particles_upload.argtypes = [C.c_void_p, View]
@@ -147,7 +148,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
                     "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops",
-                    "vrgpu_binding_energy"]
+                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key"]
 
 
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
@@ -271,6 +272,15 @@ class Context:
                                                   r["T"].ctypes.data_as(D), r["Pot"].ctypes.data_as(D), r["Efrac"].ctypes.data_as(D),
                                                   r["iminpot"].ctypes.data_as(LL), r["ibound"].ctypes.data_as(LL)))
         return r
+
+    def sort_groups_by_key(self, offsets, key):
+        """Per-group ascending order of key (the qsort of SortAccordingtoBindingEnergy, substructureproperties.cxx:4302-4310)."""
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        key = np.ascontiguousarray(key, dtype=np.float64)
+        order = np.zeros(int(offsets[-1]), dtype=np.int64)
+        self._check(self.lib.vrgpu_sort_groups_by_key(self.h, offsets.shape[0] - 1, offsets.ctypes.data_as(C.POINTER(C.c_longlong)),
+                                                      key.ctypes.data_as(C.POINTER(C.c_double)), order.ctypes.data_as(C.POINTER(C.c_longlong))))
+        return order
 
     def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
         """CheckUnboundGroups (unbind.cxx:196)."""
