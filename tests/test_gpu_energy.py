@@ -140,7 +140,6 @@ UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
                                 reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 
 
-@UNVERIFIED
 def test_sort_groups_by_key(gpu_ctx):
     """vrgpu_sort_groups_by_key: the per-group qsort of SortAccordingtoBindingEnergy (substructureproperties.cxx:4302-4310)."""
     rng = np.random.default_rng(2)
