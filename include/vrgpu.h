@@ -145,6 +145,14 @@ int vrgpu_binding_energy(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, con
 int vrgpu_sort_groups_by_key(vrgpu_ctx *ctx, long long ngroups, const long long *offsets, const double *key,
                              long long *order_out);
 
+/* Group sizes and member lists.  Replaces BuildNumInGroup + BuildPGList
+ * (src/buildandsortarrays.cxx:11-16, 26-43): numingroup_out[0..ngroups] (entry 0 = 0), index_out = the members of group 1,
+ * then group 2, ... each in ascending particle index, i.e. pglist[g] = index_out + numingroup_out[1] + ... +
+ * numingroup_out[g-1]; index_out must hold n entries (only *ngrouped_out are written).  pfof == NULL takes the labels the
+ * last vrgpu_search_full_set_resident / vrgpu_dist_search_full_set_resident call left on the device (n, ngroups ignored). */
+int vrgpu_build_pglist(vrgpu_ctx *ctx, const long long *pfof, long long n, long long ngroups, long long *numingroup_out,
+                       long long *index_out, long long *ngrouped_out);
+
 /* CheckUnboundGroups + Unbind (src/unbind.cxx:196-304, 320-729).  pfof in/out (0 = unbound), group ids
  * re-ordered by size when anything changed (ireorder=1).  *changed_out = the reference's return flag. */
 int vrgpu_unbind(vrgpu_ctx *ctx, vrgpu_view view, long long *pfof_inout, long long *ngroups_inout,

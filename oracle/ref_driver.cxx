@@ -9,6 +9,7 @@
  *   vrref_unbind           -> CheckUnboundGroups                  (src/unbind.cxx:196)
  *   vrref_binding_energy   -> GetBindingEnergy                    (src/substructureproperties.cxx:3884)
  *   vrref_sort_by_binding_energy -> SortAccordingtoBindingEnergy   (src/substructureproperties.cxx:4256)
+ *   vrref_build_pglist     -> BuildNumInGroup + BuildPGList        (src/buildandsortarrays.cxx:11, 26)
  *
  * It is compiled against the reference headers where they lie and linked with the reference's own
  * objects into oracle/_ref/libvrref*.so (see oracle/Makefile).  Nothing here re-implements the
@@ -28,6 +29,10 @@ void PotentialGPU(Options &opt, Int_t nbodies, NBody::Particle *Part);
 void GetBindingEnergyGPU(Options &opt, const Int_t nbodies, NBody::Particle *Part, Int_t ngroup, Int_t *&pfof, Int_t *&numingroup,
                          PropData *&pdata, Int_t *&noffset);
 void SortGroupParticlesGPU(Options &opt, NBody::Particle *Part, Int_t ngroup, Int_t *numingroup, Int_t *noffset, PropData *pdata);
+Int_t *BuildNumInGroupGPU(const Int_t nbodies, const Int_t numgroups, Int_t *pfof);
+Int_t **BuildPGListGPU(const Int_t nbodies, const Int_t numgroups, Int_t *numingroup, Int_t *pfof);
+#define BuildNumInGroup BuildNumInGroupGPU
+#define BuildPGList BuildPGListGPU
 #define GetBindingEnergy GetBindingEnergyGPU
 #define SearchFullSet SearchFullSetGPU
 #define CheckUnboundGroups CheckUnboundGroupsGPU
@@ -338,6 +343,26 @@ void vrref_sort_by_binding_energy(long long n, const double *pos, const double *
     delete[] pdata;
     delete[] numingroup;
     delete[] pfof;
+}
+
+/* BuildNumInGroup + BuildPGList (src/buildandsortarrays.cxx:11-16, 26-43): sizes[0..ngroups] and the lists of group 1, 2, ...
+ * written one after the other into index_out (n entries available); returns the number of grouped particles. */
+long long vrref_build_pglist(long long n, const long long *pfof_in, long long ngroups, long long *numingroup_out, long long *index_out)
+{
+    Int_t *pfof = new Int_t[n > 0 ? n : 1];
+    for (long long i = 0; i < n; i++) pfof[i] = pfof_in[i];
+    Int_t *numingroup = BuildNumInGroup(n, ngroups, pfof);
+    Int_t **pglist = BuildPGList(n, ngroups, numingroup, pfof);
+    long long k = 0;
+    for (long long g = 0; g <= ngroups; g++) numingroup_out[g] = numingroup[g];
+    for (long long g = 1; g <= ngroups; g++) {
+        for (Int_t j = 0; j < numingroup[g]; j++) index_out[k++] = pglist[g][j];
+        if (pglist[g] != NULL) delete[] pglist[g];
+    }
+    delete[] pglist;
+    delete[] numingroup;
+    delete[] pfof;
+    return k;
 }
 
 } /* extern "C" */

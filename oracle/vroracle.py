@@ -124,6 +124,9 @@ class Ref:
             L.vrref_sort_by_binding_energy.restype = None
             L.vrref_sort_by_binding_energy.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, P_ll, P_ll, c_ll, C.POINTER(RefOpts), P_ll, P_dbl,
                                                        P_ll, P_ll]
+        if hasattr(L, "vrref_build_pglist"):
+            L.vrref_build_pglist.restype = c_ll
+            L.vrref_build_pglist.argtypes = [c_ll, P_ll, c_ll, P_ll, P_ll]
         assert L.vrref_sizeof_particle() == 96
 
     @staticmethod
@@ -202,6 +205,15 @@ class Ref:
                                               _pd(Es), _pl(num), _pl(iu))
         ntot = int(num.sum())
         return {"pid": ps[:ntot], "E": Es[:ntot], "numingroup": num, "iunbound": iu}
+
+
+    def build_pglist(self, pfof, ngroups):
+        """BuildNumInGroup + BuildPGList (buildandsortarrays.cxx:11, 26): (numingroup[0..G], concatenated member lists)."""
+        pf = _i64(pfof)
+        num = np.zeros(ngroups + 1, dtype=np.int64)
+        index = np.zeros(max(pf.shape[0], 1), dtype=np.int64)
+        k = self.lib.vrref_build_pglist(pf.shape[0], _pl(pf), ngroups, _pl(num), _pl(index))
+        return num, index[:k]
 
 
 class UnbindOpts(C.Structure):

@@ -194,3 +194,51 @@ def test_sort_by_binding_energy_through_reference_types(ref, oracle, by_energy):
         if by_energy:
             assert abs(int(got["iunbound"][g]) - int(want["iunbound"][g])) <= marginal
     assert nswapped <= 2e-3 * off[-1]
+
+
+@UNVERIFIED
+def test_build_pglist(gpu_ctx):
+    """vrgpu_build_pglist (row f3): BuildNumInGroup + BuildPGList (buildandsortarrays.cxx:11-16, 26-43) -- sizes by group id,
+    members in ascending particle index; from host labels and from the labels a resident search left on the device."""
+    import vrgpu
+    rng = np.random.default_rng(6)
+    n, ng = 300000, 3000
+    pf = rng.integers(0, ng + 1, n).astype(np.int64)
+    pf[pf == 7] = 0
+    pf[rng.random(n) < 0.5] = 0
+    num, index = gpu_ctx.build_pglist(pf, ng)
+    want_num = np.bincount(pf, minlength=ng + 1)
+    want_num[0] = 0
+    order = np.argsort(pf, kind="stable")
+    assert np.array_equal(num, want_num)
+    assert np.array_equal(index, order[pf[order] > 0])
+    num, index = gpu_ctx.build_pglist(np.zeros(100, dtype=np.int64), 0)
+    assert index.size == 0 and num[0] == 0
+    # resident labels
+    nside = 40
+    d = vrsynth.make_box(nside ** 3, 9)
+    ell = vrsynth.BOX / nside
+    parts = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"])
+    gpu_ctx.particles_upload(parts)
+    ngr = gpu_ctx.search_full_set_resident(vrgpu.search_opts(vrsynth.BOX, (ell * ell) * (0.2 * 0.2), halo_min_size=20, fofbgtype=5))
+    pfr = gpu_ctx.resident_pfof(len(parts))
+    num, index = gpu_ctx.build_pglist(None, ngr, n_resident=len(parts))
+    order = np.argsort(pfr, kind="stable")
+    assert np.array_equal(num[1:], np.bincount(pfr, minlength=ngr + 1)[1:])
+    assert np.array_equal(index, order[pfr[order] > 0])
+    gpu_ctx.particles_release()
+
+
+@UNVERIFIED
+def test_build_pglist_through_reference_types(ref):
+    import vroracle
+    if not vroracle.Ref.available("gpu"):
+        pytest.skip("oracle/_ref/libvrref_gpu.so not built")
+    refgpu = vroracle.Ref("gpu")
+    rng = np.random.default_rng(16)
+    n, ng = 200000, 1500
+    pf = rng.integers(0, ng + 1, n).astype(np.int64)
+    pf[rng.random(n) < 0.3] = 0
+    wn, wi = ref.build_pglist(pf, ng)
+    gn, gi = refgpu.build_pglist(pf, ng)
+    assert np.array_equal(gn, wn) and np.array_equal(gi, wi)

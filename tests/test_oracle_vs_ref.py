@@ -223,3 +223,19 @@ def test_sort_by_binding_energy(ref, oracle, by_energy):
         first_unbound = np.flatnonzero(wE > 0)
         assert want["iunbound"][g] == (first_unbound[0] if first_unbound.size else num[g])
     assert nswapped <= 2e-3 * off[-1]
+
+
+def test_build_pglist(ref):
+    """the convention of BuildNumInGroup + BuildPGList (buildandsortarrays.cxx:11-16, 26-43) that the device
+    path reproduces -- sizes by group id, members in ascending particle index, empty groups allowed."""
+    rng = np.random.default_rng(6)
+    n, ng = 50000, 300
+    pf = rng.integers(0, ng + 1, n).astype(np.int64)
+    pf[pf == 7] = 0                                   # an empty group
+    pf[rng.random(n) < 0.5] = 0
+    num, index = ref.build_pglist(pf, ng)
+    want_num = np.bincount(pf, minlength=ng + 1)
+    want_num[0] = 0
+    order = np.argsort(pf, kind="stable")
+    assert np.array_equal(num, want_num) and num[7] == 0
+    assert np.array_equal(index, order[pf[order] > 0])

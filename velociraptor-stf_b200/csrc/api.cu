@@ -1,5 +1,6 @@
 // velociraptor-stf_b200/csrc/api.cu -- the extern "C" boundary of libvrgpu.so (see include/vrgpu.h).
 #include "fof.cuh"
+#include "groups.cuh"
 #include "stages.cuh"
 
 #include <chrono>
@@ -354,6 +355,29 @@ int vrgpu_sort_groups_by_key(vrgpu_ctx *ctx, long long ngroups, const long long 
         if (ngroups == 0 || offsets[ngroups] == 0) return;
         VR_REQUIRE(key && order_out, VRGPU_EINVAL, "null key / order array");
         sort_groups_host(ctx, ngroups, offsets, key, order_out);
+    });
+}
+
+int vrgpu_build_pglist(vrgpu_ctx *ctx, const long long *pfof, long long n, long long ngroups, long long *numingroup_out,
+                       long long *index_out, long long *ngrouped_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(numingroup_out && index_out && ngrouped_out, VRGPU_EINVAL, "null output pointer");
+        CallTimer ct(ctx);
+        if (pfof == nullptr) {
+            VR_REQUIRE(ctx->resident && ctx->resident->pfof.p, VRGPU_EINVAL, "no resident result");
+            *ngrouped_out = pglist_device(ctx, ctx->resident->pfof.p, ctx->resident->pristine.n, ctx->resident->ngroups, numingroup_out, index_out);
+            return;
+        }
+        VR_REQUIRE(n >= 0 && ngroups >= 0, VRGPU_EINVAL, "negative count");
+        DBuf<long long> pf;
+        {
+            StageTimer t(ctx);
+            upload_i64(ctx, pfof, (size_t)n, pf);
+            ctx->stats.h2d_ms += t.stop();
+        }
+        *ngrouped_out = pglist_device(ctx, pf.p, (size_t)n, ngroups, numingroup_out, index_out);
+        if (ngroups > 0 && n == 0) for (long long g = 0; g <= ngroups; g++) numingroup_out[g] = 0;
     });
 }
 

@@ -118,4 +118,43 @@ void gather_groupset(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &gs, boo
               want_mass ? gs.m.p : (double *)nullptr);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Group sizes and member lists for the host (BuildNumInGroup + BuildPGList, src/buildandsortarrays.cxx:11-16, 26-43):
+// the group-major slot order IS the concatenation of pglist[1], pglist[2], ... (members in ascending particle index).
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_pglist_sizes(const uint32_t *__restrict__ off, uint32_t ngroups, long long *__restrict__ numingroup)
+{
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g <= ngroups) numingroup[g] = g == 0 ? 0ll : (long long)(off[g + 1] - off[g]);
+}
+__global__ void k_pglist_index(const uint32_t *__restrict__ idx, size_t ntot, long long *__restrict__ index)
+{
+    const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < ntot) index[s] = (long long)idx[s];
+}
+
+long long pglist_device(vrgpu_ctx *ctx, const long long *pfof_dev, size_t n, long long ngroups, long long *numingroup_out,
+                        long long *index_out)
+{
+    const int T = 256;
+    if (ngroups <= 0 || n == 0) {
+        if (numingroup_out) numingroup_out[0] = 0;
+        return 0;
+    }
+    GroupSet gs;
+    { KScope k(ctx, "pglist.regroup"); build_groupset(ctx, pfof_dev, n, ngroups, gs); }
+    const size_t G1 = (size_t)ngroups + 1;
+    DBuf<long long> num(ctx, G1), index(ctx, gs.ntot ? gs.ntot : 1);
+    {
+        KScope k(ctx, "pglist.widen");
+        VR_LAUNCH(ctx, k_pglist_sizes, grid_for(G1, T), T, 0, gs.off.p, (uint32_t)ngroups, num.p);
+        if (gs.ntot) VR_LAUNCH(ctx, k_pglist_index, grid_for(gs.ntot, T), T, 0, gs.idx.p, gs.ntot, index.p);
+    }
+    StageTimer t(ctx);
+    if (numingroup_out) download_i64(ctx, num.p, numingroup_out, G1);
+    if (index_out && gs.ntot) download_i64(ctx, index.p, index_out, gs.ntot);
+    ctx->stats.d2h_ms += t.stop();
+    return (long long)gs.ntot;
+}
+
 } // namespace vrgpu

@@ -7,6 +7,8 @@
  *     void   Potential(Options&, Int_t, Particle*)                                      src/unbind.cxx:1607
  *     void   GetBindingEnergy(Options&, const Int_t, Particle*, Int_t, Int_t*&, Int_t*&, PropData*&, Int_t*&)
  *                                                                    src/substructureproperties.cxx:3884  (row f1)
+ *     Int_t *BuildNumInGroup(const Int_t, const Int_t, Int_t*)                src/buildandsortarrays.cxx:11  (row f3)
+ *     Int_t **BuildPGList(const Int_t, const Int_t, Int_t*, Int_t*)           src/buildandsortarrays.cxx:26  (row f3)
  *     void   SortGroupParticlesGPU(Options&, Particle*, Int_t, Int_t*, Int_t*, PropData*)
  *                        the per-group qsort inside SortAccordingtoBindingEnergy, substructureproperties.cxx:4302-4316
  *
@@ -331,4 +333,41 @@ void SortGroupParticlesGPU(Options &opt, Particle *Part, Int_t ngroup, Int_t *nu
     delete[] order;
     delete[] key;
     delete[] offsets;
+}
+
+/* BuildNumInGroup (src/buildandsortarrays.cxx:11-16): new Int_t[numgroups + 1], entry 0 = 0.  When pfof is the array the
+ * last SearchFullSet returned, a caller that also needs the lists should call BuildPGList below, which refreshes the
+ * sizes in the same device pass. */
+Int_t *VRGPU_NAME(BuildNumInGroup)(const Int_t nbodies, const Int_t numgroups, Int_t *pfof)
+{
+    Int_t *numingroup = new Int_t[numgroups + 1];
+    Int_t *index = new Int_t[nbodies > 0 ? nbodies : 1];
+    long long ngrouped = 0;
+    int rc = vrgpu_build_pglist(context(), reinterpret_cast<long long *>(pfof), nbodies, numgroups, reinterpret_cast<long long *>(numingroup),
+                                reinterpret_cast<long long *>(index), &ngrouped);
+    if (rc != VRGPU_OK) die("vrgpu_build_pglist", rc);
+    delete[] index;
+    return numingroup;
+}
+
+/* BuildPGList (src/buildandsortarrays.cxx:26-43): pglist[g] = new Int_t[numingroup[g]] holding the members of group g in
+ * ascending particle index, NULL for empty groups; numingroup is re-counted, as the reference does. */
+Int_t **VRGPU_NAME(BuildPGList)(const Int_t nbodies, const Int_t numgroups, Int_t *numingroup, Int_t *pfof)
+{
+    Int_t **pglist = new Int_t *[numgroups + 1];
+    Int_t *index = new Int_t[nbodies > 0 ? nbodies : 1];
+    long long ngrouped = 0;
+    int rc = vrgpu_build_pglist(context(), reinterpret_cast<long long *>(pfof), nbodies, numgroups, reinterpret_cast<long long *>(numingroup),
+                                reinterpret_cast<long long *>(index), &ngrouped);
+    if (rc != VRGPU_OK) die("vrgpu_build_pglist", rc);
+    Int_t at = 0;
+    for (Int_t g = 1; g <= numgroups; g++) {
+        pglist[g] = NULL;
+        if (numingroup[g] <= 0) continue;
+        pglist[g] = new Int_t[numingroup[g]];
+        memcpy(pglist[g], index + at, sizeof(Int_t) * (size_t)numingroup[g]);
+        at += numingroup[g];
+    }
+    delete[] index;
+    return pglist;
 }

@@ -122,6 +122,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_binding_energy.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_d, C.c_double, C.c_double, C.c_double, C.c_int,
                                        C.c_longlong, P_d, P_d, P_d, P_d, P_d, P_ll, P_ll]
     L.vrgpu_sort_groups_by_key.argtypes = [C.c_void_p, C.c_longlong, P_ll, P_d, P_ll]
+    L.vrgpu_build_pglist.argtypes = [C.c_void_p, P_ll, C.c_longlong, C.c_longlong, P_ll, P_ll, P_ll]
     L.vrgpu_unbind.argtypes = [C.c_void_p, View, P_ll, P_ll, C.POINTER(UnbindOpts), C.POINTER(C.c_int), P_ll]
     L.vrgpu_search_full_set.argtypes = [C.c_void_p, View, C.POINTER(SearchOpts), P_ll, P_ll]
     L.vrgpu_particles_upload.argtypes = [C.c_void_p, View]
@@ -148,7 +149,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
                     "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops",
-                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key"]
+                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist"]
 
 
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
@@ -281,6 +282,23 @@ class Context:
         self._check(self.lib.vrgpu_sort_groups_by_key(self.h, offsets.shape[0] - 1, offsets.ctypes.data_as(C.POINTER(C.c_longlong)),
                                                       key.ctypes.data_as(C.POINTER(C.c_double)), order.ctypes.data_as(C.POINTER(C.c_longlong))))
         return order
+
+    def build_pglist(self, pfof=None, ngroups=0, n_resident=0):
+        """BuildNumInGroup + BuildPGList (buildandsortarrays.cxx:11-16, 26-43): returns (numingroup[0..G], index) with the
+        members of group 1, 2, ... concatenated in ascending particle index.  pfof=None: the resident labels (pass the
+        resident particle count as n_resident and the group count as ngroups to size the outputs)."""
+        LL = C.POINTER(C.c_longlong)
+        if pfof is None:
+            n, pf = int(n_resident), None
+        else:
+            pf = np.ascontiguousarray(pfof, dtype=np.int64)
+            n = pf.shape[0]
+        num = np.zeros(int(ngroups) + 1, dtype=np.int64)
+        index = np.zeros(max(n, 1), dtype=np.int64)
+        ntot = C.c_longlong(0)
+        self._check(self.lib.vrgpu_build_pglist(self.h, pf.ctypes.data_as(LL) if pf is not None else None, n, int(ngroups),
+                                                num.ctypes.data_as(LL), index.ctypes.data_as(LL), C.byref(ntot)))
+        return num, index[:int(ntot.value)]
 
     def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
         """CheckUnboundGroups (unbind.cxx:196)."""
