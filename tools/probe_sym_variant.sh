@@ -1,0 +1,18 @@
+#!/bin/bash
+# First GPU call of the next measuring session: parity of the experimental rotation-step variant of k_potential_sym
+# (VRGPU_SYM_VARIANT=1, csrc/potential.cu) and its time against the measured default, plus the tests that were written
+# after round 1's GPU minutes ran out.  Usage: gpurun --timeout 900 -- 'bash tools/probe_sym_variant.sh'
+set -u
+mkdir -p gpurun_out
+{
+  echo "== gated tests (first GPU run)"
+  VRGPU_RUN_UNVERIFIED=1 timeout 300 python -m pytest tests/test_gpu_energy.py -q -m gpu 2>&1 | tail -5
+  for v in 0 1; do
+    echo "== VRGPU_SYM_VARIANT=$v: parity"
+    VRGPU_SYM_VARIANT=$v timeout 600 python -m pytest tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -3
+    echo "== VRGPU_SYM_VARIANT=$v: bench (default config)"
+    VRGPU_SYM_VARIANT=$v timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -1 > gpurun_out/probe_sym_v$v.json
+    python tools/bench_summary.py gpurun_out/probe_sym_v$v.json | head -8
+  done
+} > gpurun_out/probe_sym_variant.log 2>&1
+tail -40 gpurun_out/probe_sym_variant.log
