@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 {
   echo "== gated tests (first GPU run)"
   VRGPU_RUN_UNVERIFIED=1 timeout 300 python -m pytest tests/test_gpu_energy.py -q -m gpu 2>&1 | tail -5
-  for v in 0 1; do
+  for v in 0 1 2; do
     echo "== VRGPU_SYM_VARIANT=$v: parity"
     VRGPU_SYM_VARIANT=$v timeout 600 python -m pytest tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -3
     echo "== VRGPU_SYM_VARIANT=$v: bench (default config)"

@@ -153,7 +153,7 @@ __global__ void k_sym_count(const uint32_t *__restrict__ off, uint32_t ngroups, 
 // __syncwarp) and 9 % on the first DADD that waits for the step's shared loads.  VAR = 1 (a) splits the j-side sum into
 // two chains, (b) keeps the running j-side sum in a register that rotates from lane to lane with the j it belongs to
 // (one shuffle per step, one plain shared store per 32 steps instead of an RMW per step), (c) loads the next step's j
-// from shared memory before the current step's arithmetic.
+// from shared memory before the current step's arithmetic.  VAR = 2 is (a) + (b) without (c).
 template <int SPT, int SPI, int MINB, int VAR = 0>
 __global__ void __launch_bounds__(SPT, MINB) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                                                       const double *__restrict__ m, const uint32_t *__restrict__ off, uint32_t ngroups,
@@ -206,14 +206,16 @@ __global__ void __launch_bounds__(SPT, MINB) k_potential_sym(const double *__res
         for (int ww = 0; ww < SPT / 32; ww++) sacc[ww][threadIdx.x] = 0.0;
         __syncthreads();
         const int cnt = (int)min((uint32_t)SPT, j_end - jb);
-        if (VAR == 1 && !diag) {
+        if (VAR >= 1 && !diag) {
             const int nstep = ((cnt + 31) >> 5) << 5;
             double2 qa = sxy[lane], qb = szm[lane]; // step s works on jj = (s & ~31) + ((lane + s) & 31)
             double trot = 0; // j-side sum of the j this lane is working on; it travels with j (lane l -> lane l - 1 per step)
 #pragma unroll 1
             for (int s = 0; s < nstep; s++) {
-                const int jn = (((s + 1) & ~31) + (int)((lane + s + 1) & 31)) & (SPT - 1); // wraps on the last step (value unused)
+                // VAR 1: the next step's j is loaded now; VAR 2: no prefetch (this step's j is loaded here)
+                const int jn = (((s + (VAR == 1 ? 1 : 0)) & ~31) + (int)((lane + s + (VAR == 1 ? 1 : 0)) & 31)) & (SPT - 1); // wraps on the last step (value unused)
                 const double2 qan = sxy[jn], qbn = szm[jn];
+                if (VAR == 2) { qa = qan; qb = qbn; }
                 double r2[SPI], ri[SPI];
                 unsigned worst = 0;
 #pragma unroll
@@ -358,6 +360,9 @@ unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G
         static const int variant = [] { const char *e = getenv("VRGPU_SYM_VARIANT"); return e ? atoi(e) : 0; }();
         if (variant == 1)
             VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3, 1>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
+                      eps * eps, phiacc.p);
+        else if (variant == 2)
+            VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3, 2>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
                       eps * eps, phiacc.p);
         else
         VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
