@@ -787,9 +787,18 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
         VR_CUDA(cudaMemcpyAsync(W.pos.p, P.pos.p, 3 * n_own * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(W.vel.p, P.vel.p, 3 * n_own * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
         if (P.has_mass) VR_CUDA(cudaMemcpyAsync(W.mass.p, P.mass.p, n_own * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
-        else { std::vector<double> one(n_own, 1.0); VR_CUDA(cudaMemcpy(W.mass.p, one.data(), n_own * sizeof(double), cudaMemcpyHostToDevice)); }
+        else { // (stream-ordered like everything else: the pool may hand out memory whose last use is still queued on ctx->stream)
+            std::vector<double> one(n_own, 1.0);
+            VR_CUDA(cudaMemcpyAsync(W.mass.p, one.data(), n_own * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        }
         if (P.has_pid) VR_CUDA(cudaMemcpyAsync(W.pid.p, P.pid.p, n_own * sizeof(long long), cudaMemcpyDeviceToDevice, ctx->stream));
-        else { std::vector<long long> id(n_own); std::iota(id.begin(), id.end(), 0ll); VR_CUDA(cudaMemcpy(W.pid.p, id.data(), n_own * sizeof(long long), cudaMemcpyHostToDevice)); }
+        else {
+            std::vector<long long> id(n_own);
+            std::iota(id.begin(), id.end(), 0ll);
+            VR_CUDA(cudaMemcpyAsync(W.pid.p, id.data(), n_own * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        }
         VR_LAUNCH(ctx, k_mg_own_work_labels, grid_for(n_own, T), T, 0, A.pfof.p, A.dest.p, n_own, me, pfw.p);
     }
     for (int s = 0; s < N; s++) {
