@@ -14,5 +14,11 @@ mkdir -p gpurun_out
     VRGPU_SYM_VARIANT=$v timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -1 > gpurun_out/probe_sym_v$v.json
     python tools/bench_summary.py gpurun_out/probe_sym_v$v.json | head -8
   done
+  for w in 0 1; do
+    echo "== VRGPU_WALK_PREFETCH=$w: tree parity + bench (256^3, 6DFOF + tree unbinding)"
+    VRGPU_WALK_PREFETCH=$w timeout 600 python -m pytest tests/test_gpu_tree.py -q -m gpu 2>&1 | tail -2
+    VRGPU_WALK_PREFETCH=$w timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --fofbgtype 3 --pp-threshold 150 2>/dev/null | tail -1 > gpurun_out/probe_walk_p$w.json
+    python tools/bench_summary.py gpurun_out/probe_walk_p$w.json | head -8
+  done
 } > gpurun_out/probe_sym_variant.log 2>&1
 tail -40 gpurun_out/probe_sym_variant.log
