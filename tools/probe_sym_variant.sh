@@ -1,7 +1,7 @@
 #!/bin/bash
 # First GPU call of the next measuring session: parity of the experimental rotation-step variant of k_potential_sym
 # (VRGPU_SYM_VARIANT=1, csrc/potential.cu) and its time against the measured default, plus the tests that were written
-# after round 1's GPU minutes ran out.  Usage: gpurun --timeout 900 -- 'bash tools/probe_sym_variant.sh'
+# after round 1's GPU minutes ran out.  Also: the candidate-queue 3D linker (VRGPU_LINK_VARIANT=1|2, csrc/link2.cuh).  Usage: gpurun --timeout 900 -- 'bash tools/probe_sym_variant.sh'
 set -u
 mkdir -p gpurun_out
 {
@@ -19,6 +19,12 @@ mkdir -p gpurun_out
     VRGPU_WALK_PREFETCH=$w timeout 600 python -m pytest tests/test_gpu_tree.py -q -m gpu 2>&1 | tail -2
     VRGPU_WALK_PREFETCH=$w timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --fofbgtype 3 --pp-threshold 150 2>/dev/null | tail -1 > gpurun_out/probe_walk_p$w.json
     python tools/bench_summary.py gpurun_out/probe_walk_p$w.json | head -8
+  done
+  for v in 0 1 2; do
+    echo "== VRGPU_LINK_VARIANT=$v: 3DFOF parity (single GPU, drop-in, 2 ranks) + bench (default config; look at fof3d.link_cells)"
+    VRGPU_LINK_VARIANT=$v timeout 600 python -m pytest tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py tests/test_gpu_multi.py -q -m gpu 2>&1 | tail -3
+    VRGPU_LINK_VARIANT=$v timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -1 > gpurun_out/probe_link_v$v.json
+    python tools/bench_summary.py gpurun_out/probe_link_v$v.json | head -12
   done
 } > gpurun_out/probe_sym_variant.log 2>&1
 tail -40 gpurun_out/probe_sym_variant.log
