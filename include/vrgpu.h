@@ -202,6 +202,9 @@ void *vrgpu_stream(vrgpu_ctx *ctx);
 const char *vrgpu_kernel_times(vrgpu_ctx *ctx);
 /* measured fp64 FMA throughput of the device in TFLOP/s (denominator of the potential kernels' roofline) */
 int vrgpu_measure_fp64_tflops(vrgpu_ctx *ctx, double *tflops_out);
+/* microbenchmark: out4[0] vector DFMA alone, out4[1] tensor-core DMMA (mma.sync m8n8k4 f64) alone, out4[2] / out4[3] the
+ * DFMA / DMMA rates when one kernel issues both -- TFLOP/s; tells whether the two share a pipe on this device */
+int vrgpu_probe_fp64_pipes(vrgpu_ctx *ctx, double *out4);
 void vrgpu_kernel_times_reset(vrgpu_ctx *ctx);
 
 #ifdef __cplusplus

@@ -592,6 +592,14 @@ int vrgpu_measure_fp64_tflops(vrgpu_ctx *ctx, double *tflops_out)
     });
 }
 
+int vrgpu_probe_fp64_pipes(vrgpu_ctx *ctx, double *out4)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(out4, VRGPU_EINVAL, "null pointer");
+        probe_fp64_pipes(ctx, out4);
+    });
+}
+
 void vrgpu_kernel_times_reset(vrgpu_ctx *ctx)
 {
     if (!ctx) return;

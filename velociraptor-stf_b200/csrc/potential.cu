@@ -415,4 +415,62 @@ double measure_fp64_tflops(vrgpu_ctx *ctx)
     ctx->evpool.push_back(b);
     return best;
 }
+
+// Probe for the next design step of the direct sum: does the fp64 tensor-core instruction
+// (mma.sync m8n8k4 f64, 512 flops per warp instruction) run beside the vector DFMA pipe or on it?  If beside, the
+// r^2 = |xi|^2 + |xj|^2 - 2 xi.xj part of a tile pair (6 of the 11 fp64 instructions per particle pair) can move to
+// it.  mode 0: DFMA only, 1: DMMA only, 2: both in one instruction stream (same counts as 0 and 1 together).
+template <int MODE> __global__ void __launch_bounds__(256) k_fp64_pipes(double *out, int iters, double a, double b)
+{
+    double r0 = threadIdx.x, r1 = r0 + 1, r2 = r0 + 2, r3 = r0 + 3, r4 = r0 + 4, r5 = r0 + 5, r6 = r0 + 6, r7 = r0 + 7;
+    double c0 = r0, c1 = r1, c2 = r2, c3 = r3, c4 = r4, c5 = r5, c6 = r6, c7 = r7; // four independent DMMA accumulator pairs
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            if (MODE != 1) {
+                r0 = fma(r0, a, b); r1 = fma(r1, a, b); r2 = fma(r2, a, b); r3 = fma(r3, a, b);
+                r4 = fma(r4, a, b); r5 = fma(r5, a, b); r6 = fma(r6, a, b); r7 = fma(r7, a, b);
+            }
+            if (MODE != 0) {
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c2), "+d"(c3) : "d"(a), "d"(b));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c4), "+d"(c5) : "d"(a), "d"(b));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c6), "+d"(c7) : "d"(a), "d"(b));
+            }
+        }
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r0 + r1 + r2 + r3 + r4 + r5 + r6 + r7 + c0 + c1 + c2 + c3 + c4 + c5 + c6 + c7;
+}
+
+// out[0]: DFMA-only TFLOP/s, out[1]: DMMA-only TFLOP/s, out[2] / out[3]: DFMA / DMMA TFLOP/s when both are issued together
+void probe_fp64_pipes(vrgpu_ctx *ctx, double out4[4])
+{
+    const int blocks = ctx->sm_count * 8, iters = 1024;
+    DBuf<double> out(ctx, (size_t)blocks * 256);
+    cudaEvent_t a = KScope::get(ctx), b = KScope::get(ctx);
+    double ms_mode[3] = {0, 0, 0};
+    for (int mode = 0; mode < 3; mode++) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; rep++) { // rep 0 is the warm-up
+            VR_CUDA(cudaEventRecord(a, ctx->stream));
+            if (mode == 0) VR_LAUNCH(ctx, k_fp64_pipes<0>, blocks, 256, 0, out.p, iters, 0.999999, 1e-9);
+            else if (mode == 1) VR_LAUNCH(ctx, k_fp64_pipes<1>, blocks, 256, 0, out.p, iters, 0.999999, 1e-9);
+            else VR_LAUNCH(ctx, k_fp64_pipes<2>, blocks, 256, 0, out.p, iters, 0.999999, 1e-9);
+            VR_CUDA(cudaEventRecord(b, ctx->stream));
+            VR_CUDA(cudaEventSynchronize(b));
+            float ms = 0;
+            VR_CUDA(cudaEventElapsedTime(&ms, a, b));
+            if (rep) best = std::min(best, ms);
+        }
+        ms_mode[mode] = best;
+    }
+    ctx->evpool.push_back(a);
+    ctx->evpool.push_back(b);
+    const double dfma_flops = 2.0 * 8 * 16 * (double)iters * 256.0 * blocks;
+    const double dmma_flops = 512.0 * 4 * 16 * (double)iters * 8.0 * blocks; // 512 flops per warp instruction, 8 warps per block
+    out4[0] = dfma_flops / (ms_mode[0] * 1e-3) / 1e12;
+    out4[1] = dmma_flops / (ms_mode[1] * 1e-3) / 1e12;
+    out4[2] = dfma_flops / (ms_mode[2] * 1e-3) / 1e12;
+    out4[3] = dmma_flops / (ms_mode[2] * 1e-3) / 1e12;
+}
 } // namespace vrgpu

@@ -17,6 +17,7 @@ void *mapped_host_pointer(const void *p);
 
 // DFMA throughput of the device in TFLOP/s (potential.cu)
 double measure_fp64_tflops(vrgpu_ctx *ctx);
+void probe_fp64_pipes(vrgpu_ctx *ctx, double out4[4]);
 
 // potentials for host-side CSR groups (vrgpu_potential)
 void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,

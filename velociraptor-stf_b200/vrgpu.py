@@ -138,6 +138,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_kernel_times.argtypes = [C.c_void_p]
     L.vrgpu_kernel_times.restype = C.c_char_p
     L.vrgpu_measure_fp64_tflops.argtypes = [C.c_void_p, P_d]
+    L.vrgpu_probe_fp64_pipes.argtypes = [C.c_void_p, P_d]
     L.vrgpu_kernel_times_reset.argtypes = [C.c_void_p]
     L.vrgpu_kernel_times_reset.restype = None
     _lib = L
@@ -148,7 +149,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
-                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops",
+                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes",
                     "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist"]
 
 
@@ -368,6 +369,11 @@ class Context:
         v = C.c_double(0)
         self._check(self.lib.vrgpu_measure_fp64_tflops(self.h, C.byref(v)))
         return float(v.value)
+
+    def probe_fp64_pipes(self) -> dict:
+        v = (C.c_double * 4)()
+        self._check(self.lib.vrgpu_probe_fp64_pipes(self.h, v))
+        return {"dfma_alone": v[0], "dmma_alone": v[1], "dfma_mixed": v[2], "dmma_mixed": v[3]}
 
     def kernel_times_reset(self):
         self.lib.vrgpu_kernel_times_reset(self.h)
