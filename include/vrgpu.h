@@ -53,7 +53,7 @@ typedef struct {
     double Eratio;             /* UnbindInfo::Eratio                                                */
     double minEfrac;           /* UnbindInfo::minEfrac                                              */
     int unbindtype;            /* UnbindInfo::unbindtype 0 = USYSANDPART, 1 = UPART                 */
-    int bgpot;                 /* UnbindInfo::bgpot; only 1 (keep background potential) implemented */
+    int bgpot;                 /* UnbindInfo::bgpot; 1 keep the background potential, 0 take removed particles' pair terms off */
     double fracpotref;         /* UnbindInfo::fracpotref; only 1.0 (whole-group CM frame)           */
     double maxunbindfrac;      /* UnbindInfo::maxunbindfrac (0.5)                                   */
     double maxunboundfracforiterativeunbind; /* (0.95)                                              */

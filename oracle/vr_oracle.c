@@ -683,10 +683,11 @@ static void unbind_group(uctx *c, i64 *ning_io, upart *gp, double *cmvel, double
             for (int k = 0; k < 3; k++) cmvel[k] *= temp;
             *gmass -= temp2;
         }
-        if (o->bgpot == 0) {
-            /* unbind.cxx:587-605 / 674-688: remove the pair terms of every removed particle.  (The large-group
-             * branch re-runs Potential() instead when nEplus >= 2 ln n, unbind.cxx:583-585; that variant is not
-             * restated: bgpot==0 with large groups is reported as unsupported by the callers.) */
+        /* unbind.cxx:587-605 / 674-688: take off the pair terms of every removed particle.  The large-group loop does
+         * that only for nEplus < 2 ln n (unbind.cxx:583); otherwise it calls Potential() on the member list BEFORE the
+         * removal (unbind.cxx:585 precedes RemoveUnboundParticles at :607), i.e. it re-evaluates the potentials the
+         * members already carry, so nothing changes here. */
+        if (o->bgpot == 0 && (!large || (double)nEplus < 2.0 * log((double)ning))) {
             for (i64 k = 0; k < nEplus; k++) {
                 i64 ik = gp[nEplusid[k]].idx;
                 for (i64 j = 0; j < ning; j++) {

@@ -3,6 +3,8 @@
 Tolerances (BASELINE.json north_star): potentials 1e-6 relative -- the direct sum is asserted at 1e-10; bound sets
 identical except for particles whose |E| <= 1e-6 |phi| (marginal), whose count is reported by both sides.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -63,6 +65,37 @@ def test_unbind_matches_oracle(gpu_ctx, oracle, nside, seed, unbindtype):
     assert got["changed"] == want["changed"]
     ndiff = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
     # bound sets identical except marginal particles (none expected at these sizes)
+    assert ndiff <= want["n_marginal"] + got["n_marginal"]
+    if ndiff == 0:
+        assert got["ngroups"] == want["ngroups"]
+        assert np.array_equal(got["pfof"], want["pfof"])
+
+
+UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
+                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
+
+
+@UNVERIFIED
+@pytest.mark.parametrize("nside,seed,unbindtype", [(32, 7, 0), (48, 3, 0), (48, 9, 1)])
+def test_unbind_without_background_potential(gpu_ctx, oracle, nside, seed, unbindtype):
+    """Keep_background_potential=0 (examples/sample.cfg, genesis2019_configuration.cfg; unbind.cxx:672-690): members lose the
+    pair terms shared with removed particles before the next energy evaluation.  The oracle's version of this option is
+    pinned to the compiled reference in test_oracle_vs_ref.py::test_unbind."""
+    import vrgpu
+    import vroracle
+    d = vrsynth.make_box(nside ** 3, seed)
+    pf, ng, pos, _ = _fof_groups(oracle, d, nside)
+    ro = vroracle.default_opts(unbindtype=unbindtype, bgpot=0)
+    uo = vroracle.unbind_opts_from(ro, pp_threshold=-1, sortflag_mode=0)
+    want = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, uo, d["pid"], 1e-6)
+    keep = oracle.unbind(pos, d["vel"], d["mass"], pf, ng,
+                         vroracle.unbind_opts_from(vroracle.default_opts(unbindtype=unbindtype), pp_threshold=-1, sortflag_mode=0),
+                         d["pid"], 1e-6)
+    assert np.count_nonzero((want["pfof"] > 0) != (keep["pfof"] > 0)) > 0   # the option changes the answer on this box
+    parts = vrgpu.particles_from_arrays(pos, d["vel"], d["mass"], d["pid"])
+    got = gpu_ctx.unbind(parts, pf, ng, vrgpu.default_unbind_opts(unbindtype=unbindtype, pp_threshold=-1, bgpot=0))
+    assert got["changed"] == want["changed"]
+    ndiff = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
     assert ndiff <= want["n_marginal"] + got["n_marginal"]
     if ndiff == 0:
         assert got["ngroups"] == want["ngroups"]

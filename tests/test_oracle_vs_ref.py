@@ -77,8 +77,9 @@ def test_tree_potential(ref, oracle, n):
         assert np.max(np.abs(got / want - 1.0)) < 1e-12
 
 
-@pytest.mark.parametrize("nside,seed,unbindtype", [(32, 7, 0), (40, 3, 1), (24, 2, 0)])
-def test_unbind(ref, oracle, nside, seed, unbindtype):
+@pytest.mark.parametrize("nside,seed,unbindtype,bgpot", [(32, 7, 0, 1), (40, 3, 1, 1), (24, 2, 0, 1),
+                                                         (32, 7, 0, 0), (40, 3, 1, 0), (48, 5, 0, 0)])
+def test_unbind(ref, oracle, nside, seed, unbindtype, bgpot):
     """CheckUnboundGroups.  The reference reads `oldnumingroup` uninitialised in its small-group loop (unbind.cxx:643,700;
     SURVEY Q10), so groups that need a second removal pass depend on stack garbage.  The oracle is run with the three
     possible behaviours (garbage 0, garbage huge, intended per-group initialisation); every particle on which the three
@@ -88,7 +89,8 @@ def test_unbind(ref, oracle, nside, seed, unbindtype):
     b = 0.2 * vrsynth.BOX / nside
     pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
     pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
-    ro = vroracle.default_opts(unbindtype=unbindtype)
+    # bgpot = 0 (Keep_background_potential=0, examples/sample.cfg): removed particles' pair terms leave the potentials
+    ro = vroracle.default_opts(unbindtype=unbindtype, bgpot=bgpot)
     want = ref.unbind(pos, d["vel"], d["mass"], pf, ng, ro)
     wb = want["pfof"] > 0
     variants = []

@@ -8,7 +8,7 @@ mkdir -p gpurun_out
   echo "== fp64 pipes: does DMMA (mma.sync m8n8k4 f64) run beside the vector DFMA pipe?  (TFLOP/s)"
   timeout 120 python -c "import sys; sys.path.insert(0, 'velociraptor-stf_b200'); import vrgpu; print(vrgpu.Context(0).probe_fp64_pipes())" 2>&1 | tail -1
   echo "== gated tests (first GPU run)"
-  VRGPU_RUN_UNVERIFIED=1 timeout 300 python -m pytest tests/test_gpu_energy.py -q -m gpu 2>&1 | tail -5
+  VRGPU_RUN_UNVERIFIED=1 timeout 600 python -m pytest tests/test_gpu_energy.py tests/test_gpu_unbind.py -q -m gpu 2>&1 | tail -5
   for v in 0 1 2; do
     echo "== VRGPU_SYM_VARIANT=$v: parity"
     VRGPU_SYM_VARIANT=$v timeout 600 python -m pytest tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -3

@@ -336,7 +336,17 @@ __device__ __forceinline__ double ub_block_max(double v, double *scratch)
     return r;
 }
 
-__global__ void __launch_bounds__(UB_T) k_unbind_small(UbArrays A, UbParams P, uint32_t ngroups)
+// Keep_background_potential = 0 (unbind.cxx:672-690): before the unbound tail leaves, every member loses the pair terms it
+// shares with the removed particles.  The terms are taken off one removed particle after the other, in the order of
+// nEplusid[] (from the tail of the arrangement towards its head), with the reference's operation order, so the updated
+// potentials -- and with them every later energy comparison -- are the reference's bit for bit.
+struct UbBg {
+    const double *x, *y, *z; // group-major positions
+    double *phi;             // the potentials k_unbind_small reads through A.phi (same buffer)
+    double G, eps2;
+};
+
+template <bool BG0> __global__ void __launch_bounds__(UB_T) k_unbind_small(UbArrays A, UbParams P, uint32_t ngroups, UbBg B)
 {
     __shared__ double sE[UB_CAP];
     __shared__ uint32_t sid[UB_CAP];
@@ -453,6 +463,28 @@ __global__ void __launch_bounds__(UB_T) k_unbind_small(UbArrays A, UbParams P, u
             cx *= temp; cy *= temp; cz *= temp;
             mass -= sm;
         }
+        if (BG0) {
+            const uint32_t nrm = (uint32_t)nEplus;
+            for (uint32_t j = tid; j < n; j += UB_T) {
+                const uint32_t sj = sid[j];
+                const double xj = B.x[sj], yj = B.y[sj], zj = B.z[sj], mj = A.m[sj];
+                double ph = B.phi[sj];
+                for (uint32_t k = 0; k < nrm; k++) {
+                    const uint32_t pk = n - 1 - k; // nEplusid[k] (FillUnboundArrays, unbind.cxx:62-98)
+                    if (pk == j) continue;
+                    const uint32_t sk = sid[pk];
+                    const double dx = __dsub_rn(B.x[sk], xj), dy = __dsub_rn(B.y[sk], yj), dz = __dsub_rn(B.z[sk], zj);
+                    double r2 = __dmul_rn(dx, dx);
+                    r2 = __dadd_rn(r2, __dmul_rn(dy, dy));
+                    r2 = __dadd_rn(r2, __dmul_rn(dz, dz));
+                    r2 = __dadd_rn(r2, B.eps2);
+                    const double rinv = __ddiv_rn(1.0, __dsqrt_rn(r2));
+                    ph = __dadd_rn(ph, __dmul_rn(__dmul_rn(B.G, __dmul_rn(A.m[sk], mj)), rinv));
+                }
+                B.phi[sj] = ph;
+            }
+            __syncthreads();
+        }
         n -= (uint32_t)nEplus;
         if ((double)nEplus < P.maxallowed * (double)n) break; // unbind.cxx:695-697
         sortflag = false;
@@ -545,7 +577,16 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
     n_marginal = 0;
     if (ngroups <= 0 || P.n == 0) return;
     VR_REQUIRE(o.fracpotref == 1.0, VRGPU_EUNSUPPORTED, "only Frac_pot_ref=1 (whole-group CM frame) is implemented");
-    VR_REQUIRE(o.bgpot == 1, VRGPU_EUNSUPPORTED, "only Keep_background_potential=1 is implemented");
+    VR_REQUIRE(o.bgpot == 0 || o.bgpot == 1, VRGPU_EINVAL, "Keep_background_potential must be 0 or 1");
+    // Keep_background_potential = 0 in the large-group loop (unbind.cxx:577-606): pair terms are taken off only when
+    // nEplus < 2 ln n, and a pass happens only when nEplus >= maxallowedunboundfrac * n (FillUnboundArrays), so with
+    // maxallowedunboundfrac * n >= 2 ln n for every n >= ompunbindnum (the defaults: 25 >= 13.8) that branch never runs;
+    // the other branch re-evaluates Potential() over the still complete member list, i.e. the values it already has.
+    if (o.bgpot == 0) {
+        const double a = o.maxallowedunboundfrac, Tl = (double)o.large_threshold; // a n - 2 ln n grows with n from n = 2 / a on
+        VR_REQUIRE(a > 0 && Tl >= 2.0 / a && a * Tl >= 2.0 * std::log(Tl), VRGPU_EUNSUPPORTED,
+                   "Keep_background_potential=0 needs maxallowedunboundfrac * ompunbindnum >= 2 ln(ompunbindnum) (pair-term branch of the large-group loop)");
+    }
     VR_REQUIRE(o.large_threshold >= 1 && o.large_threshold <= UB_CAP, VRGPU_EUNSUPPORTED, "large_threshold must be in [1, 2048]");
     VR_REQUIRE(o.unbindtype == 0 || o.unbindtype == 1, VRGPU_EINVAL, "unbindtype must be 0 or 1");
     VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "unbinding needs velocities");
@@ -616,7 +657,12 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
         }
     }
     // ---- phase B ----
-    { KScope k(ctx, "unbind.small_groups"); VR_LAUNCH(ctx, k_unbind_small, G, UB_T, 0, A, Pm, G); }
+    {
+        KScope k(ctx, "unbind.small_groups");
+        UbBg Bg{gs.x.p, gs.y.p, gs.z.p, phi.p, o.G, o.eps * o.eps};
+        if (o.bgpot == 0) VR_LAUNCH(ctx, k_unbind_small<true>, G, UB_T, 0, A, Pm, G, Bg);
+        else VR_LAUNCH(ctx, k_unbind_small<false>, G, UB_T, 0, A, Pm, G, Bg);
+    }
 
     // ---- results ----
     DBuf<uint32_t> newsize(ctx, G1), iota(ctx, G1), gid_of(ctx, G1);
