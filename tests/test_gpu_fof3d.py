@@ -3,6 +3,8 @@
 Bar: bit-exact canonical membership (integer/index work).  The oracle itself is pinned against the compiled
 reference in test_oracle_vs_ref.py / tests/golden.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -61,6 +63,22 @@ def test_fof3d_known_answers(gpu_ctx):
     parts = vrgpu.particles_from_arrays(np.zeros((0, 3)))
     pf, ng = gpu_ctx.fof3d(parts, b, L, 2)
     assert ng == 0 and pf.shape == (0,)
+
+
+@pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
+                    reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
+def test_fof3d_edge_cases(gpu_ctx, oracle):
+    """Corners of the domain (tests/edge_cases.py): the oracle is pinned to the compiled reference on exactly these inputs
+    (test_oracle_vs_ref.py::test_fof3d_edge_cases_vs_kdtree_fof)."""
+    import edge_cases
+    import vrgpu
+    for name, (pos, period, minsize) in edge_cases.cases().items():
+        pid = np.arange(len(pos))
+        parts = vrgpu.particles_from_arrays(pos, pid=pid)
+        pf, ng = gpu_ctx.fof3d(parts, edge_cases.B, period, minsize)
+        want, no = oracle.fof3d(pos, edge_cases.B, period, minsize, pid)
+        assert ng == no, name
+        assert np.array_equal(pf, want), name
 
 
 def test_fof3d_size_order_and_ties(gpu_ctx):

@@ -111,6 +111,20 @@ def test_link2_dense_cells_use_the_dense_queue(emul, oracle):
         assert ng == no == 1 and np.array_equal(got, want) and np.all(got == 1)
 
 
+def test_link2_edge_cases(emul, oracle):
+    """Corners of the domain (tests/edge_cases.py; the oracle is pinned to the compiled reference on the same inputs in
+    test_oracle_vs_ref.py): coincident particles, particles on the faces, minsize boundaries, one cell, corner chains."""
+    import edge_cases
+    for name, (pos, period, minsize) in edge_cases.cases().items():
+        pid = np.arange(len(pos))
+        want, no = oracle.fof3d(pos, edge_cases.B, period, minsize, pid)
+        for mode in (0, 1, 2):
+            root, _ = emul(pos, edge_cases.B, period, mode, 3)
+            got, ng = canonical(root, pid, minsize)
+            assert ng == no, name
+            assert np.array_equal(got, want), name
+
+
 def test_link2_known_answers(emul):
     L, b = 100.0, 1.0
     pos = np.array([[10.0, 10.0, 10.0], [11.0, 10.0, 10.0], [0.0, 50.0, 50.0], [np.nextafter(1.0, 0.0), 50.0, 50.0]])

@@ -27,6 +27,32 @@ def test_fof3d_vs_kdtree_fof(ref, oracle, nside, seed):
     assert nr == no and np.array_equal(cr, po)
 
 
+def test_fof3d_edge_cases_vs_kdtree_fof(ref, oracle):
+    """Corners of the domain (tests/edge_cases.py) through the reference's own KDTree::FOF and the oracle."""
+    import edge_cases
+    for name, (pos, period, minsize) in edge_cases.cases().items():
+        pid = np.arange(len(pos))
+        pr, nr = ref.kdfof(pos, None, 3, edge_cases.B, period, minsize, 16)
+        cr, _ = vrsynth.canonical_groups(pr, pid)
+        po, no = oracle.fof3d(pos, edge_cases.B, period, minsize, pid)
+        assert nr == no, name
+        assert np.array_equal(cr, po), name
+
+
+def test_single_leaf_tree_ignores_periodicity(ref, oracle):
+    """Reference quirk (DESIGN.md Q15): the periodic images are applied by SplitNode::FOFSearchBallPeriodic only
+    (KDSplitNode.cxx:1496-1540; the leaf version, KDLeafNode.cxx:824-827, forwards to the open search), so an input of at most
+    BucketSize particles is linked as an OPEN box.  The oracle and the library wrap regardless of the particle count."""
+    pos = np.array([[0.0, 70.0, 70.0]] * 2 + [[100.0, 70.0, 70.0]] * 3)
+    pr, nr = ref.kdfof(pos, None, 3, 1.0, 100.0, 2, 16)
+    assert nr == 2 and len(set(pr[:2])) == 1 and len(set(pr[2:])) == 1 and pr[0] != pr[2]
+    po, no = oracle.fof3d(pos, 1.0, 100.0, 2, np.arange(5))
+    assert no == 1 and np.all(po == 1)
+    # with a split node in the tree (bucket size 2) the reference wraps too
+    pr, nr = ref.kdfof(pos, None, 3, 1.0, 100.0, 2, 2)
+    assert nr == 1 and np.all(pr == 1)
+
+
 def test_fof6d_direct_tree_call(ref, oracle):
     """KDTree::FOF on a 6-D tree (TPHS) == oracle 6-D link of pre-scaled coordinates."""
     rng = np.random.default_rng(2)
