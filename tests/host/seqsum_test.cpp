@@ -78,10 +78,125 @@ static double plain_sum(const std::vector<double> &t, double s0)
     return s;
 }
 
+// The many-window evaluation of seqsum.h (mirrors k_seq_approx / k_seq_spec / k_seq_walk in fof6d.cu): summaries built
+// under a predicted unit, one walker; windows whose summary does not apply take the windowed (always exact) path.
+// `skew` perturbs the approximate prefix sums the prediction is taken from, `flip` corrupts every flip-th prediction.
+static long g_fast = 0, g_slow = 0;
+struct VecTerm {
+    const std::vector<double> *t;
+    double operator()(unsigned long long k) const { return (*t)[(size_t)k]; }
+};
+static double spec_sum(const std::vector<double> &t, double s0, size_t W, double skew, int flip)
+{
+    const size_t n = t.size(), nwin = (n + W - 1) / W;
+    std::vector<double> start(nwin);
+    {
+        // inexact on purpose: per-window sums accumulated from the END of the window, prefix in long double
+        long double run = s0;
+        for (size_t k = 0; k < nwin; k++) {
+            start[k] = (double)run * (1.0 + skew);
+            double ws = 0;
+            for (size_t j = std::min(n, (k + 1) * W); j-- > k * W;) ws += t[j];
+            run += ws;
+        }
+    }
+    std::vector<SeqSpec> spec(nwin);
+    for (size_t k = 0; k < nwin; k++) {
+        int eu = seq_predict_unit(start[k]);
+        if (flip && k % (size_t)flip == (size_t)flip - 1 && eu != SEQ_NOSPEC) eu += (k & 1) ? 1 : -1;
+        spec[k] = seq_spec_serial(VecTerm{&t}, k * W, (unsigned)std::min(W, n - k * W), eu);
+    }
+    double s = s0;
+    for (size_t k = 0; k < nwin; k++) {
+        long long S;
+        int eu;
+        if (seq_decode_sum(s, S, eu) && seq_spec_step(spec[k], S, eu)) {
+            s = seq_encode_sum(S, eu);
+            g_fast++;
+        } else {
+            std::vector<double> w(t.begin() + (long)(k * W), t.begin() + (long)std::min(n, (k + 1) * W));
+            s = windowed_sum(w, s, 512, 8);
+            g_slow++;
+        }
+    }
+    return s;
+}
+
+// k_seq_spec's decomposition (NT virtual threads of PER terms: per-thread composite, exclusive prefix over threads, extreme
+// prefix increments per thread, reduction) against the serial construction of seqsum.h
+static SeqSpec spec_blocked(const std::vector<double> &t, size_t first, unsigned w, int eu, int NT, int PER)
+{
+    SeqSpec r{};
+    r.eu = SEQ_NOSPEC;
+    if (eu == SEQ_NOSPEC) return r;
+    std::vector<SeqMap> tm((size_t)NT * PER), inc(NT);
+    bool small = true;
+    for (int th = 0; th < NT; th++) {
+        inc[th] = seq_identity();
+        for (int j = 0; j < PER; j++) {
+            const size_t k = (size_t)th * PER + j;
+            tm[k] = k < w ? seq_term_map(t[first + k], eu) : seq_identity();
+            small = small && seq_term_small(tm[k]);
+            inc[th] = seq_compose(inc[th], tm[k]);
+        }
+    }
+    if (!small) return r;
+    r.total = seq_identity();
+    r.mine = r.mino = SEQ_HI;
+    r.maxe = r.maxo = -SEQ_HI;
+    SeqMap pre = seq_identity();
+    for (int th = 0; th < NT; th++) {
+        SeqMap p = pre;
+        for (int j = 0; j < PER; j++) {
+            const size_t k = (size_t)th * PER + j;
+            if (k < w) {
+                p = seq_compose(p, tm[k]);
+                r.mine = std::min(r.mine, p.e); r.maxe = std::max(r.maxe, p.e);
+                r.mino = std::min(r.mino, p.o); r.maxo = std::max(r.maxo, p.o);
+            }
+        }
+        pre = seq_compose(pre, inc[th]);
+    }
+    r.total = pre;
+    r.eu = eu;
+    return r;
+}
+static int check_spec_shapes(const char *name, const std::vector<double> &t)
+{
+    int bad = 0;
+    const size_t n = t.size();
+    double run = 0;
+    for (size_t first = 0; first < n; first += 4096) {
+        const unsigned w = (unsigned)std::min<size_t>(4096, n - first);
+        const int eu = seq_predict_unit(run);
+        const SeqSpec a = seq_spec_serial(VecTerm{&t}, first, w, eu), b = spec_blocked(t, first, w, eu, 512, 8);
+        if (a.eu != b.eu || (a.eu != SEQ_NOSPEC && (a.total.e != b.total.e || a.total.o != b.total.o || a.mine != b.mine || a.maxe != b.maxe ||
+                                                     a.mino != b.mino || a.maxo != b.maxo))) {
+            printf("FAIL %-28s summary of window %zu differs between the serial and the blocked construction\n", name, first / 4096);
+            bad++;
+            break;
+        }
+        for (unsigned k = 0; k < w; k++) run += t[first + k];
+    }
+    return bad;
+}
+
 static int check(const char *name, const std::vector<double> &t, double s0 = 0.0)
 {
     const double want = plain_sum(t, s0);
-    int bad = 0;
+    int bad = check_spec_shapes(name, t);
+    {
+        const long f0 = g_fast, sl0 = g_slow;
+        const struct { size_t W; double skew; int flip; } sc[] = {{4096, 0.0, 0}, {4096, 1e-3, 0}, {1000, -0.3, 0}, {4096, 0.0, 3}, {37, 0.0, 0}};
+        for (auto &c : sc) {
+            const double got = spec_sum(t, s0, c.W, c.skew, c.flip);
+            if (seq_bits(got) != seq_bits(want) && !(got != got && want != want)) {
+                printf("FAIL %-28s many-window W=%zu skew=%g flip=%d n=%zu want %.17g got %.17g\n", name, c.W, c.skew, c.flip, t.size(), want, got);
+                bad++;
+            }
+        }
+        if (getenv("SEQSUM_VERBOSE")) printf("%-28s many-window: %ld fast, %ld slow windows\n", name, g_fast - f0, g_slow - sl0);
+    }
     const long w0 = g_windows, sc0 = g_scan_terms, se0 = g_serial_terms;
     const int cfg[][2] = {{512, 8}, {32, 4}, {7, 3}, {1, 1}};
     for (auto &c : cfg) {
@@ -109,7 +224,13 @@ int main()
         std::vector<double> t(n);
         // dispersion-like: m * (v - vbar)^2, float32-exact inputs
         for (auto &x : t) { const double v = (double)(float)(300.0 * N(rng)), m = (double)(float)0.0207; x = (v * v) * m; }
-        bad += check("squares*mass", t);
+        {
+            const long f0 = g_fast, sl0 = g_slow;
+            bad += check("squares*mass", t);
+            // exact prediction, W = 4096 is the first of the five shapes; over all five at least 60 % of the windows must
+            // take the one-step path on a dispersion-like sum (the skewed / corrupted shapes lose theirs on purpose)
+            if ((g_fast - f0) * 10 < (g_fast - f0 + g_slow - sl0) * 6) { printf("FAIL squares*mass: only %ld of %ld windows took the summary\n", g_fast - f0, g_fast - f0 + g_slow - sl0); bad++; }
+        }
         // momentum-like: m * v with a drift
         for (auto &x : t) { const double v = (double)(float)(250.0 + 900.0 * N(rng)); x = v * 0.0207; }
         bad += check("drifting signed", t);
@@ -150,6 +271,7 @@ int main()
     }
     printf("windows %ld, scan terms %ld, serial terms %ld (%.3f%%)\n", g_windows, g_scan_terms, g_serial_terms,
            100.0 * (double)g_serial_terms / (double)(g_serial_terms + g_scan_terms + 1));
+    printf("many-window evaluation: %ld windows in one step, %ld the slow way\n", g_fast, g_slow);
     printf(bad ? "seqsum: %d FAILURES\n" : "seqsum: all sequences bit-identical\n", bad);
     return bad ? 1 : 0;
 }

@@ -2,6 +2,8 @@
 particle, so the large-group branches are the ones exercised -- 6DFOF of a single big group with its own dispersion
 (search.cxx:472-499, 520-579), kd-tree potentials (unbind.cxx:1607-1741) and the one-pass removal of groups above
 ompunbindnum (unbind.cxx:552-639)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -50,12 +52,24 @@ def test_single_halo_search_full_set(gpu_ctx, oracle, fofbgtype, pp):
     assert np.array_equal(parts["pos"], pos) and np.array_equal(parts["vel"], vel)
 
 
+UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
+                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
+
+
 @pytest.mark.parametrize("pattern", ["zero_mean", "zero_axis", "ties", "equal_mass_drift", "mixed_mass"])
-def test_big_group_dispersion_is_bit_exact(gpu_ctx, oracle, pattern):
-    """The velocity dispersion of a large group is a left-to-right fp64 sum in the reference (search.cxx:480-493); groups
+@pytest.mark.parametrize("multi_min", [0, pytest.param(8192, marks=UNVERIFIED)])
+def test_big_group_dispersion_is_bit_exact(gpu_ctx, oracle, pattern, multi_min, monkeypatch):
+    """multi_min = 8192 sends the group through the many-window evaluation (VRGPU_DISP_MULTI_MIN, csrc/seqsum.h "Many windows
+    at once": summaries under a predicted unit + one walker) -- the same bit-exact bar.
+
+    The velocity dispersion of a large group is a left-to-right fp64 sum in the reference (search.cxx:480-493); groups
     above 4096 members take the integer-scan evaluation (csrc/seqsum.h).  Membership and the scaled/unscaled coordinates
     (Q3) depend on every bit of it, so comparing those with the oracle pins the sum."""
     import vrgpu
+    if multi_min:
+        monkeypatch.setenv("VRGPU_DISP_MULTI_MIN", str(multi_min))
+    else:
+        monkeypatch.delenv("VRGPU_DISP_MULTI_MIN", raising=False)
     n = 30000
     rng = np.random.default_rng({"zero_mean": 1, "zero_axis": 2, "ties": 3, "equal_mass_drift": 4, "mixed_mass": 5}[pattern])
     pos = rng.normal(size=(n, 3)) * 0.3 + 50.0

@@ -25,8 +25,10 @@
 #include "ufhash.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
+#include <vector>
 #include <cmath>
 
 namespace vrgpu {
@@ -153,16 +155,247 @@ struct TermDispersion { // pow(v_c - vmean_c, 2) * m for c = x, y, z of member k
     }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// Many-window evaluation of one long sequential sum (seqsum.h, "Many windows at once"): EXPERIMENT for the next measuring
+// session, used only when VRGPU_DISP_MULTI_MIN names a member count (fof6d_device).  block_seqsum walks the windows of a
+// group one after the other inside one CTA -- 295 ms for the 1.8 10^7-member group of the zoom configuration.  Here
+//   k_seq_approx  one CTA per window: ordinary (inexact) sum of its terms;
+//   k_seq_prefix  running sum at every window start (inexact; only its exponent is used: the predicted unit);
+//   k_seq_spec    one CTA per window: the window's summary under the predicted unit (block scan of the term maps);
+//   k_seq_walk    one CTA: thread 0 steps over the summaries (512 staged in shared memory at a time); a window whose
+//                 summary does not apply is evaluated by the whole CTA with block_seqsum, exactly as before.
+// The result is the sequential sum bit for bit whatever the predictions are (tests/host/seqsum_test.cpp runs the same
+// logic with skewed and corrupted predictions).
+// ---------------------------------------------------------------------------------------------------
+static_assert(SQ_W <= (int)SEQ_SPEC_MAXTERMS, "a summarised window must not exceed SEQ_SPEC_MAXTERMS terms");
+
+template <class Term> struct TermShift {
+    Term t;
+    unsigned long long base;
+    __device__ double operator()(unsigned long long k) const { return t(base + k); }
+};
+struct TermMomentumD { // as TermMomentum
+    const double *v, *m;
+    __device__ double operator()(unsigned long long k) const { return __dmul_rn(v[k], m[k]); }
+};
+struct TermDispersionD { // as TermDispersion, means read from device memory (they are sequential sums themselves)
+    const double *vx, *vy, *vz, *m;
+    const double *mean; // 3
+    __device__ double operator()(unsigned long long k) const
+    {
+        const unsigned long long i = k / 3ull;
+        const unsigned c = (unsigned)(k - 3ull * i);
+        const double d = __dsub_rn(c == 0 ? vx[i] : (c == 1 ? vy[i] : vz[i]), mean[c]);
+        return __dmul_rn(__dmul_rn(d, d), m[i]);
+    }
+};
+
+template <class Term> __global__ void __launch_bounds__(SQ_NT) k_seq_approx(Term term, unsigned long long n, double *__restrict__ wsum)
+{
+    __shared__ double part[SQ_NT / 32];
+    const unsigned long long first = (unsigned long long)blockIdx.x * SQ_W;
+    const unsigned w = (unsigned)min((unsigned long long)SQ_W, n - first);
+    double a = 0.0;
+    for (unsigned k = threadIdx.x; k < w; k += SQ_NT) a += term(first + k);
+    for (int o = 16; o; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int q = 0; q < SQ_NT / 32; q++) t += part[q];
+        wsum[blockIdx.x] = t;
+    }
+}
+
+__global__ void k_seq_prefix(const double *__restrict__ wsum, unsigned nwin, const double *__restrict__ s0, double *__restrict__ start)
+{
+    if (blockIdx.x || threadIdx.x) return;
+    double run = s0 ? *s0 : 0.0;
+    for (unsigned k = 0; k < nwin; k++) { start[k] = run; run += wsum[k]; }
+}
+
+template <class Term> __global__ void __launch_bounds__(SQ_NT) k_seq_spec(Term term, unsigned long long n, const double *__restrict__ start,
+                                                                          SeqSpec *__restrict__ spec)
+{
+    __shared__ SeqMap wtot[SQ_NT / 32];
+    __shared__ long long red[4][SQ_NT / 32];
+    __shared__ int s_small;
+    const unsigned tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const unsigned long long first = (unsigned long long)blockIdx.x * SQ_W;
+    const unsigned w = (unsigned)min((unsigned long long)SQ_W, n - first);
+    const int eu = seq_predict_unit(start[blockIdx.x]);
+    if (eu == SEQ_NOSPEC) { // uniform over the CTA
+        if (tid == 0) { SeqSpec z{}; z.eu = SEQ_NOSPEC; spec[blockIdx.x] = z; }
+        return;
+    }
+    if (tid == 0) s_small = 1;
+    __syncthreads();
+    const unsigned k0 = tid * SQ_PER;
+    SeqMap tm[SQ_PER];
+    SeqMap inc = seq_identity();
+    bool small = true;
+#pragma unroll
+    for (int j = 0; j < SQ_PER; j++) {
+        tm[j] = (k0 + j < w) ? seq_term_map(term(first + k0 + j), eu) : seq_identity();
+        small = small && seq_term_small(tm[j]);
+        inc = seq_compose(inc, tm[j]);
+    }
+    if (!small) s_small = 0; // benign race: every writer stores 0
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        SeqMap o;
+        o.e = __shfl_up_sync(0xffffffffu, inc.e, d);
+        o.o = __shfl_up_sync(0xffffffffu, inc.o, d);
+        if ((int)lane >= d) inc = seq_compose(o, inc);
+    }
+    if (lane == 31) wtot[wid] = inc;
+    __syncthreads();
+    if (!s_small) { // a term that is not small against the predicted sum: no summary (additions could wrap)
+        if (tid == 0) { SeqSpec z{}; z.eu = SEQ_NOSPEC; spec[blockIdx.x] = z; }
+        return;
+    }
+    SeqMap pre = seq_identity();
+    for (unsigned q = 0; q < wid; q++) pre = seq_compose(pre, wtot[q]);
+    SeqMap ex;
+    ex.e = __shfl_up_sync(0xffffffffu, inc.e, 1);
+    ex.o = __shfl_up_sync(0xffffffffu, inc.o, 1);
+    if (lane == 0) ex = seq_identity();
+    pre = seq_compose(pre, ex);
+    // extreme prefix increments of this thread's terms
+    long long mine = SEQ_HI, maxe = -SEQ_HI, mino = SEQ_HI, maxo = -SEQ_HI;
+#pragma unroll
+    for (int j = 0; j < SQ_PER; j++) {
+        if (k0 + j < w) {
+            pre = seq_compose(pre, tm[j]);
+            mine = min(mine, pre.e); maxe = max(maxe, pre.e);
+            mino = min(mino, pre.o); maxo = max(maxo, pre.o);
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        mine = min(mine, __shfl_xor_sync(0xffffffffu, mine, o)); maxe = max(maxe, __shfl_xor_sync(0xffffffffu, maxe, o));
+        mino = min(mino, __shfl_xor_sync(0xffffffffu, mino, o)); maxo = max(maxo, __shfl_xor_sync(0xffffffffu, maxo, o));
+    }
+    if (lane == 0) { red[0][wid] = mine; red[1][wid] = maxe; red[2][wid] = mino; red[3][wid] = maxo; }
+    __syncthreads();
+    if (tid == 0) {
+        SeqSpec r{};
+        r.total = seq_identity();
+        for (int q = 0; q < SQ_NT / 32; q++) r.total = seq_compose(r.total, wtot[q]);
+        r.mine = red[0][0]; r.maxe = red[1][0]; r.mino = red[2][0]; r.maxo = red[3][0];
+        for (int q = 1; q < SQ_NT / 32; q++) {
+            r.mine = min(r.mine, red[0][q]); r.maxe = max(r.maxe, red[1][q]);
+            r.mino = min(r.mino, red[2][q]); r.maxo = max(r.maxo, red[3][q]);
+        }
+        r.eu = eu;
+        spec[blockIdx.x] = r;
+    }
+}
+
+template <class Term> __global__ void __launch_bounds__(SQ_NT) k_seq_walk(Term term, unsigned long long n, const double *__restrict__ s0,
+                                                                          const SeqSpec *__restrict__ spec, unsigned nwin, double *__restrict__ out,
+                                                                          unsigned int *__restrict__ nslow)
+{
+    __shared__ SeqShared sh;
+    __shared__ SeqSpec buf[SQ_NT];
+    __shared__ unsigned s_taken;
+    const unsigned tid = threadIdx.x;
+    double s = s0 ? *s0 : 0.0;
+    unsigned k = 0, slow = 0;
+    while (k < nwin) {
+        const unsigned cnt = min((unsigned)SQ_NT, nwin - k);
+        if (tid < cnt) buf[tid] = spec[k + tid];
+        __syncthreads();
+        if (tid == 0) {
+            unsigned j = 0;
+            long long S;
+            int eu;
+            if (seq_decode_sum(s, S, eu)) {
+                while (j < cnt && seq_spec_step(buf[j], S, eu)) j++;
+                if (j) s = seq_encode_sum(S, eu);
+            }
+            sh.s = s;
+            s_taken = j;
+        }
+        __syncthreads();
+        s = sh.s;
+        const unsigned j = s_taken;
+        __syncthreads(); // everybody has read sh.s / s_taken before block_seqsum reuses sh
+        k += j;
+        if (j < cnt) { // the summary of window k does not apply: the exact windowed evaluation
+            const unsigned long long first = (unsigned long long)k * SQ_W;
+            s = block_seqsum(TermShift<Term>{term, first}, min((unsigned long long)SQ_W, n - first), s, sh);
+            k++;
+            slow++;
+        }
+    }
+    if (tid == 0) {
+        *out = s;
+        if (nslow) atomicAdd(nslow, slow);
+    }
+}
+
+// host side: enqueue the four launches; *out (device) receives fl(...fl(fl(*s0 + t0) + t1)...), s0 == nullptr means 0
+struct SeqScratch {
+    DBuf<double> wsum, start;
+    DBuf<SeqSpec> spec;
+    DBuf<unsigned int> nslow;
+    unsigned cap = 0;
+};
+template <class Term> static void seq_multi_sum(vrgpu_ctx *ctx, SeqScratch &sc, Term term, unsigned long long n, const double *s0_dev, double *out_dev)
+{
+    const unsigned nwin = (unsigned)((n + SQ_W - 1) / SQ_W);
+    VR_REQUIRE(nwin >= 1 && nwin <= sc.cap, VRGPU_ECUDA, "seq_multi_sum: scratch too small");
+    VR_LAUNCH(ctx, k_seq_approx<Term>, nwin, SQ_NT, 0, term, n, sc.wsum.p);
+    VR_LAUNCH(ctx, k_seq_prefix, 1, 32, 0, sc.wsum.p, nwin, s0_dev, sc.start.p);
+    VR_LAUNCH(ctx, k_seq_spec<Term>, nwin, SQ_NT, 0, term, n, sc.start.p, sc.spec.p);
+    VR_LAUNCH(ctx, k_seq_walk<Term>, 1, SQ_NT, 0, term, n, s0_dev, sc.spec.p, nwin, out_dev, sc.nslow.p);
+}
+
+// r = {sum m vx, sum m vy, sum m vz, sum m}  ->  mean[c] = r[c] / norm   (norm = r[3], or the single-scale mnorm of quirk Q1)
+__global__ void k_seq_means(const double *__restrict__ r, double mnorm, int use_mnorm, double *__restrict__ mean)
+{
+    if (blockIdx.x || threadIdx.x) return;
+    const double d = use_mnorm ? mnorm : r[3];
+    mean[0] = __ddiv_rn(r[0], d); mean[1] = __ddiv_rn(r[1], d); mean[2] = __ddiv_rn(r[2], d);
+}
+// adaptive: vs2[g] = acc / sm * vfac * vfac (search.cxx:489-493); single scale: acc / mnorm (if > 0) * (vfac * vfac) for every chunk
+__global__ void k_seq_finish(const double *__restrict__ r, double vfac, double mnorm, int single, uint32_t g_first, uint32_t g_count,
+                             double *__restrict__ vs2)
+{
+    double acc = r[4];
+    if (!single) acc = __dmul_rn(__dmul_rn(__ddiv_rn(acc, r[3]), vfac), vfac);
+    else {
+        if (mnorm > 0) acc = __ddiv_rn(acc, mnorm);
+        acc = __dmul_rn(acc, __dmul_rn(vfac, vfac));
+    }
+    for (uint32_t g = g_first + blockIdx.x * blockDim.x + threadIdx.x; g < g_first + g_count; g += gridDim.x * blockDim.x) vs2[g] = acc;
+}
+
+// the dispersion of ONE member range [vx, vx + n) ... through the many-window path; vs2[g_first .. g_first + g_count) receive it
+static void dispersion_multi(vrgpu_ctx *ctx, SeqScratch &sc, DBuf<double> &r /* 8 */, const double *vx, const double *vy, const double *vz,
+                             const double *m, unsigned long long n, double vfac, bool single, double mnorm, uint32_t g_first, uint32_t g_count,
+                             double *vs2)
+{
+    seq_multi_sum(ctx, sc, TermMomentumD{vx, m}, n, nullptr, r.p + 0);
+    seq_multi_sum(ctx, sc, TermMomentumD{vy, m}, n, nullptr, r.p + 1);
+    seq_multi_sum(ctx, sc, TermMomentumD{vz, m}, n, nullptr, r.p + 2);
+    if (!single) seq_multi_sum(ctx, sc, TermMass{m}, n, nullptr, r.p + 3);
+    VR_LAUNCH(ctx, k_seq_means, 1, 32, 0, r.p, mnorm, single ? 1 : 0, r.p + 5);
+    seq_multi_sum(ctx, sc, TermDispersionD{vx, vy, vz, m, r.p + 5}, 3ull * n, nullptr, r.p + 4);
+    VR_LAUNCH(ctx, k_seq_finish, 1, 256, 0, r.p, vfac, mnorm, single ? 1 : 0, g_first, g_count, vs2);
+}
+
 // FOF6DADAPTIVE (search.cxx:480-493): vmean = sum(m v)/sum(m); vscale2 = sum_k pow(v_k - vmean_k, 2) m / sum(m) * vfac^2.
 // One CTA per group of at least SQ_MIN members (group ids are size-descending: the other CTAs leave at once).
 __global__ void __launch_bounds__(SQ_NT) k_group_dispersion_big(const double *__restrict__ vx, const double *__restrict__ vy,
                                                                 const double *__restrict__ vz, const double *__restrict__ m,
-                                                                const uint32_t *__restrict__ off, double vfac, double *__restrict__ vs2)
+                                                                const uint32_t *__restrict__ off, double vfac, double *__restrict__ vs2,
+                                                                uint32_t nskip /* leading groups done by the many-window path */)
 {
     __shared__ SeqShared sh;
     const uint32_t g = blockIdx.x + 1;
     const uint32_t s0 = off[g], n = off[g + 1] - s0;
-    if (n < SQ_MIN) return;
+    if (n < SQ_MIN || g <= nskip) return;
     const double sx = block_seqsum(TermMomentum{vx + s0, m + s0}, n, 0.0, sh);
     const double sy = block_seqsum(TermMomentum{vy + s0, m + s0}, n, 0.0, sh);
     const double sz = block_seqsum(TermMomentum{vz + s0, m + s0}, n, 0.0, sh);
@@ -596,6 +829,18 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
     DBuf<double> vs2(ctx, (size_t)G + 2);
     {
         KScope k(ctx, "fof6d.dispersion");
+        // experiment (off unless the variable is set): groups of at least this many members go through the many-window path
+        long long multi_min = 0;
+        if (const char *e = getenv("VRGPU_DISP_MULTI_MIN")) multi_min = atoll(e);
+        SeqScratch sc;
+        DBuf<double> seqr;
+        auto prepare_multi = [&](unsigned long long nmax) {
+            sc.cap = (unsigned)((3ull * nmax + SQ_W - 1) / SQ_W);
+            sc.wsum.alloc(ctx, sc.cap); sc.start.alloc(ctx, sc.cap); sc.spec.alloc(ctx, sc.cap); sc.nslow.alloc(ctx, 1);
+            seqr.alloc(ctx, 8);
+            VR_CUDA(cudaMemsetAsync(sc.nslow.p, 0, sizeof(unsigned int), ctx->stream));
+            VR_CUDA(cudaMemsetAsync(seqr.p, 0, 8 * sizeof(double), ctx->stream));
+        };
         if (mode == 4) {
             double mnorm = 1.0;
             if (P.has_mass) {
@@ -603,7 +848,10 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
                 VR_CUDA(cudaStreamSynchronize(ctx->stream));
             }
             // group 1 is chunk 1 unless it was itself merged (then its members are no longer contiguous: use the 3D layout)
-            if (nchunks >= 2 || ngroups3d == 1) {
+            if ((nchunks >= 2 || ngroups3d == 1) && multi_min > 0 && (long long)n_first >= multi_min) {
+                prepare_multi((unsigned long long)n_first);
+                dispersion_multi(ctx, sc, seqr, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, (unsigned long long)n_first, vfac, true, mnorm, 1u, G, vs2.p);
+            } else if (nchunks >= 2 || ngroups3d == 1) {
                 VR_LAUNCH(ctx, k_single_dispersion, 1, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, (uint32_t)n_first, mnorm, vfac, G, vs2.p);
             } else {
                 GroupSet g0;
@@ -614,7 +862,24 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
             }
         } else {
             const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 8u));
-            VR_LAUNCH(ctx, k_group_dispersion_big, G, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, vfac, vs2.p);
+            // the groups come in size order: the leading ones (at most 64) may take the many-window path
+            uint32_t nskip = 0;
+            if (multi_min > 0) {
+                const uint32_t look = std::min<uint32_t>(G, 64u);
+                std::vector<uint32_t> hoff((size_t)look + 2);
+                VR_CUDA(cudaMemcpyAsync(hoff.data(), gs.off.p, sizeof(uint32_t) * ((size_t)look + 2), cudaMemcpyDeviceToHost, ctx->stream));
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                while (nskip < look && (long long)(hoff[nskip + 2] - hoff[nskip + 1]) >= multi_min) nskip++;
+                if (nskip) {
+                    prepare_multi((unsigned long long)(hoff[2] - hoff[1]));
+                    for (uint32_t g = 1; g <= nskip; g++) {
+                        const uint32_t s0 = hoff[g];
+                        dispersion_multi(ctx, sc, seqr, gs.vx.p + s0, gs.vy.p + s0, gs.vz.p + s0, gs.m.p + s0, (unsigned long long)(hoff[g + 1] - s0),
+                                         vfac, false, 0.0, g, 1u, vs2.p);
+                    }
+                }
+            }
+            VR_LAUNCH(ctx, k_group_dispersion_big, G, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, vfac, vs2.p, nskip);
             VR_LAUNCH(ctx, k_group_dispersion, grid, T, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, G, vfac, vs2.p);
         }
     }

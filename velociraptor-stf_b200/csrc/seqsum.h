@@ -141,4 +141,76 @@ VR_HD SeqMap seq_compose(const SeqMap &f, const SeqMap &h)
 }
 VR_HD long long seq_apply(long long S, const SeqMap &a) { return seq_add(S, (S & 1) ? a.o : a.e); }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Many windows at once.  One CTA per group walks its windows one after the other (block_seqsum in fof6d.cu), which is a
+// serial chain of ~n/4096 block scans: 0.3 s for a group of 2 10^7 members.  For such groups the windows are SUMMARISED
+// in parallel instead, each under a PREDICTED unit 2^eu (taken from an ordinary, inexact parallel prefix sum of the
+// terms), and one thread then walks the summaries:
+//   * the summary holds the composed map of the window and, for an even and for an odd incoming S, the smallest and the
+//     largest prefix increment inside the window;
+//   * a window may be taken in one step iff the running sum really has the predicted unit and S + smallest, S + largest
+//     both stay inside the binade with the sign of S (then every prefix does: the prefixes of one parity lie between their
+//     extremes) -- exactly the condition under which block_seqsum would have accepted the whole window;
+//   * otherwise (wrong prediction, change of binade inside the window, a term that is not small against the sum, sum
+//     zero / subnormal / not finite) the window is evaluated the slow, always exact way.
+// A window is summarised only if every increment is below 2^50 in magnitude: with at most 2^12 terms no prefix can then
+// reach 2^62, so none of the integer additions can wrap.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int SEQ_NOSPEC = 0x7fffffff;      // SeqSpec::eu of a window without a usable summary
+constexpr long long SEQ_SPEC_MAXINC = 1ll << 50;
+constexpr unsigned SEQ_SPEC_MAXTERMS = 1u << 12;
+
+struct SeqSpec {
+    SeqMap total;                       // composed map of the whole window
+    long long mine, maxe, mino, maxo;   // extreme prefix increments (over the non-empty prefixes) for an even / odd incoming S
+    int eu;                             // unit exponent the summary was built for, or SEQ_NOSPEC
+    int pad;
+};
+
+VR_HD bool seq_term_small(const SeqMap &m)
+{
+    return m.e > -SEQ_SPEC_MAXINC && m.e < SEQ_SPEC_MAXINC && m.o > -SEQ_SPEC_MAXINC && m.o < SEQ_SPEC_MAXINC;
+}
+
+// unit exponent predicted from an approximate value of the running sum (SEQ_NOSPEC if that value is not a normal number)
+VR_HD int seq_predict_unit(double approx)
+{
+    long long S;
+    int eu;
+    return seq_decode_sum(approx, S, eu) ? eu : SEQ_NOSPEC;
+}
+
+// one step of the walk: true (and S advanced over the whole window) iff the summary applies to the sum S * 2^eu
+VR_HD bool seq_spec_step(const SeqSpec &w, long long &S, int eu)
+{
+    if (w.eu == SEQ_NOSPEC || w.eu != eu) return false;
+    const bool odd = (S & 1) != 0;
+    const long long lo = S + (odd ? w.mino : w.mine), hi = S + (odd ? w.maxo : w.maxe); // |S| < 2^53, |increments| < 2^62
+    if (!seq_in_binade(lo) || !seq_in_binade(hi) || ((lo < 0) != (S < 0)) || ((hi < 0) != (S < 0))) return false;
+    S = seq_apply(S, w.total);
+    return true;
+}
+
+// serial construction of a summary (host tests; the device builds the same numbers with a block scan)
+template <class Term> VR_HD SeqSpec seq_spec_serial(Term term, unsigned long long first, unsigned count, int eu)
+{
+    SeqSpec w;
+    w.total = seq_identity();
+    w.mine = w.mino = SEQ_HI;
+    w.maxe = w.maxo = -SEQ_HI;
+    w.eu = eu;
+    w.pad = 0;
+    if (eu == SEQ_NOSPEC || count == 0 || count > SEQ_SPEC_MAXTERMS) { w.eu = SEQ_NOSPEC; return w; }
+    for (unsigned k = 0; k < count; k++) {
+        const SeqMap m = seq_term_map(term(first + k), eu);
+        if (!seq_term_small(m)) { w.eu = SEQ_NOSPEC; return w; }
+        w.total = seq_compose(w.total, m);
+        w.mine = w.total.e < w.mine ? w.total.e : w.mine;
+        w.maxe = w.total.e > w.maxe ? w.total.e : w.maxe;
+        w.mino = w.total.o < w.mino ? w.total.o : w.mino;
+        w.maxo = w.total.o > w.maxo ? w.total.o : w.maxo;
+    }
+    return w;
+}
+
 } // namespace vrgpu
