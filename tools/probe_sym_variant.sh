@@ -33,5 +33,11 @@ mkdir -p gpurun_out
     VRGPU_DISP_MULTI_MIN=$m timeout 900 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --single-halo 20000000 --fofbgtype 3 --pp-threshold 150 2>/dev/null | tail -1 > gpurun_out/probe_disp_m$m.json
     python tools/bench_summary.py gpurun_out/probe_disp_m$m.json | head -8
   done
+  for a in 0 1; do
+    echo "== VRGPU_ASYNC_WRITEBACK=$a: 6DFOF parity incl. pinned write-back + e2e of 256^3 6DFOF + tree unbinding (look at e2e and io.writeback)"
+    VRGPU_ASYNC_WRITEBACK=$a timeout 600 python -m pytest tests/test_gpu_fof6d.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -2
+    VRGPU_ASYNC_WRITEBACK=$a timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --fofbgtype 3 --pp-threshold 150 2>/dev/null | tail -1 > gpurun_out/probe_wb_a$a.json
+    python tools/bench_summary.py gpurun_out/probe_wb_a$a.json | head -4
+  done
 } > gpurun_out/probe_sym_variant.log 2>&1
 tail -40 gpurun_out/probe_sym_variant.log

@@ -127,6 +127,19 @@ void run_search(vrgpu_ctx *ctx, DeviceParticles &P, const vrgpu_search_opts *o, 
 {
     const bool six = o->fofbgtype <= 4;
     const bool unbind = o->bound_halos >= 1;
+    // the asynchronous write-back (experiment, see below) reads pf3_keep / P until `ev`: joined on every way out
+    DBuf<long long> pf3_keep;
+    struct WbJoin {
+        vrgpu_ctx *ctx;
+        cudaEvent_t ev = nullptr;
+        ~WbJoin()
+        {
+            if (!ev) return;
+            cudaStreamWaitEvent(ctx->stream, ev, 0);
+            cudaEventSynchronize(ev);
+            ctx->evpool.push_back(ev);
+        }
+    } wb{ctx};
     Fof3dState S;
     fof3d_device(ctx, P, std::sqrt(o->param1), o->period, o->halo_min_size, S);
     ng = S.ngroups;
@@ -156,9 +169,15 @@ void run_search(vrgpu_ctx *ctx, DeviceParticles &P, const vrgpu_search_opts *o, 
         long long ng6 = fof6d_device(ctx, P, pf.p, ng, std::sqrt(param1), o->ellhalo6dvfac, o->fofbgtype, o->halo_min_size, pf6.p, true);
         ctx->stats.fof6d_ms += t.stop();
         if (view) {
-            StageTimer t2(ctx);
-            writeback_phase(ctx, *view, P, pf.p);
-            ctx->stats.d2h_ms += t2.stop();
+            // experiment (off by default): the write-back runs on the copy stream beside the unbinding stage
+            static const bool async_wb = [] { const char *e = getenv("VRGPU_ASYNC_WRITEBACK"); return e && atoi(e) == 1; }();
+            if (async_wb) wb.ev = writeback_phase_async(ctx, *view, P, pf.p);
+            if (wb.ev) pf3_keep = std::move(pf); // read by the copy stream until wb.ev
+            else {
+                StageTimer t2(ctx);
+                writeback_phase(ctx, *view, P, pf.p);
+                ctx->stats.d2h_ms += t2.stop();
+            }
         }
         pf = std::move(pf6);
         ng = ng6;

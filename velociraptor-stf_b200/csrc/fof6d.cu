@@ -1031,6 +1031,35 @@ void *mapped_host_pointer(const void *p)
     return nullptr;
 }
 
+// EXPERIMENT (VRGPU_ASYNC_WRITEBACK=1, run_search in api.cu): the zero-copy write-back of the 6DFOF coordinates on the copy
+// stream, so that its PCIe stores (204 ms at 512^3, 26 ms at 256^3: profiles/r01f) run beside the unbinding stage instead
+// of in front of it.  Returns the event that marks its end (nullptr when the caller's memory is not page-locked: the
+// caller then takes the synchronous path); the inputs (P.pos, P.vel, pfof_dev) must stay untouched until that event.
+cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev)
+{
+    if (P.n == 0) return nullptr;
+    VR_REQUIRE(P.has_vel && view.off_vel != VRGPU_NOFIELD, VRGPU_EINVAL, "write-back needs velocities in the view");
+    void *dev = mapped_host_pointer(view.base);
+    if (!dev) return nullptr;
+    if (!ctx->copy_stream) VR_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    cudaEvent_t ready = KScope::get(ctx), a = KScope::get(ctx), b = KScope::get(ctx);
+    VR_CUDA(cudaEventRecord(ready, ctx->stream));              // everything that produced pos / vel / pfof
+    VR_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ready, 0));
+    VR_CUDA(cudaEventRecord(a, ctx->copy_stream));
+    k_writeback_direct<<<grid_for(6 * P.n, 256), 256, 0, ctx->copy_stream>>>(static_cast<unsigned char *>(dev), view.stride, view.off_pos,
+                                                                              view.off_vel, P.pos.p, P.vel.p, pfof_dev, P.n);
+    ctx->stats.kernel_launches++;
+    VR_CUDA(cudaGetLastError());
+    VR_CUDA(cudaEventRecord(b, ctx->copy_stream));
+    cudaEvent_t done = KScope::get(ctx);
+    VR_CUDA(cudaEventRecord(done, ctx->copy_stream));
+    if (ctx->ktiming) ctx->kpending.push_back({"io.writeback", a, b}); // recycled by resolve_ktimes
+    else { ctx->evpool.push_back(a); ctx->evpool.push_back(b); }
+    ctx->evpool.push_back(ready);
+    ctx->stats.d2h_bytes += (long long)ctx->stats.n_grouped * 48;
+    return done; // the caller waits on it and hands it back to ctx->evpool
+}
+
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev)
 {
     if (P.n == 0) return;

@@ -11,6 +11,7 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
 
 // write pos+vel of every particle with pfof_dev[i] > 0 back into the caller's writable view
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
+cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 
 // device-visible alias of a page-locked host pointer, or nullptr for pageable memory (fof6d.cu)
 void *mapped_host_pointer(const void *p);
