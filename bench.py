@@ -274,11 +274,14 @@ def run_ours(args):
     h2d = d2h = 0
     ctx.kernel_times_reset()
     e2e_warm = max(1, args.warmup)
+    # the caller's result buffer: page-locked and reused (default), or a fresh pageable array per call as the adaptor's
+    # `new Int_t[n]` (main.cxx:427 delete[]s it) -- the latter costs ~9 ms more at 256^3 (profiles/r01f)
+    out_buf = vrgpu.pinned_i64(n) if args.e2e_out == "pinned" else None
     for it in range(e2e_warm + args.steps):   # untimed warm-up calls first, like the resident arm
         parts[:] = pristine                    # the call rewrites positions in place (AdjustStructureForPeriod): restore, untimed
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        pf, ng_e = ctx.search_full_set(parts, so)
+        pf, ng_e = ctx.search_full_set(parts, so, out=out_buf)
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) * 1e3
         if it >= e2e_warm:
@@ -342,6 +345,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": workload_name(nside, args.fofbgtype, args.pp_threshold), "n_particles": n, "ngroups": ng,
                        "l2": "inputs (1.07 GB of columns at 256^3) larger than the 126 MB L2; no explicit flush",
+                       "e2e_buffers": f"particle records page-locked; pfof_out {'page-locked, reused' if args.e2e_out == 'pinned' else 'fresh pageable array per call'}",
                        "parallelism": "1 GPU"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": float(np.mean(e2e_ms)), "ngroups": ng_e, "io_ms_per_step": e2e_io},
@@ -413,10 +417,11 @@ def run_ours_multi(args, rank, world, local):
     # ---- e2e arm: host particles of the slab in, global ids out ----
     e2e = []
     e2e_warm = max(1, args.warmup)
+    out_buf = vrgpu.pinned_i64(parts.shape[0]) if args.e2e_out == "pinned" else None
     for it in range(e2e_warm + args.steps):
         barrier()
         t0 = time.perf_counter()
-        pf, ng_e = ctx.dist_search_full_set(parts, lo, hi, so)
+        pf, ng_e = ctx.dist_search_full_set(parts, lo, hi, so, out=out_buf)
         torch.cuda.synchronize()
         dt = torch.tensor([(time.perf_counter() - t0) * 1e3], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
@@ -440,6 +445,7 @@ def run_ours_multi(args, rank, world, local):
                 "data": "synthetic",
                 "config": {"workload": workload_name(nside, args.fofbgtype, args.pp_threshold), "n_particles": n, "ngroups": ng,
                            "l2": "inputs larger than the 126 MB L2; no explicit flush",
+                           "e2e_buffers": f"particle records page-locked; pfof_out {'page-locked, reused' if args.e2e_out == 'pinned' else 'fresh pageable array per call'}",
                            "parallelism": f"{world} x-slabs, ghost exchange + boundary union-find + group consolidation over NCCL"},
                 "e2e": {"value": n / (float(np.mean(e2e)) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(tot[1].item()),
                         "d2h_bytes_per_step": int(tot[2].item()), "ms_per_step": float(np.mean(e2e)), "ngroups": ng_e},
@@ -460,6 +466,8 @@ def main():
     ap.add_argument("--pp-threshold", type=int, default=-1, help="<0: direct sum for every group (configs[1]); 150 = reference UNBINDNUM")
     ap.add_argument("--cpu-nside", type=int, default=0, help="box side of the bounded CPU sample (default 128)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-out", default="pinned", choices=["pinned", "pageable"],
+                    help="result buffer of the end-to-end arm: reused page-locked array, or a fresh pageable one per call")
     ap.add_argument("--single-halo", type=int, default=0, metavar="NPART",
                     help="zoom-style input (configs[4]): ONE halo of NPART particles instead of the clustered box (1 GPU)")
     args = ap.parse_args()

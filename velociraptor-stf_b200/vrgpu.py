@@ -153,6 +153,18 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist"]
 
 
+def pinned_i64(n: int) -> np.ndarray:
+    """A page-locked int64 host array (through torch), e.g. a reusable pfof_out buffer for the search calls."""
+    import torch
+    t = torch.empty(max(int(n), 1), dtype=torch.int64).pin_memory()
+    a = t.numpy()[:n]
+    _pinned_keepalive.append(t)
+    return a
+
+
+_pinned_keepalive = []
+
+
 def particles_from_arrays(pos, vel=None, mass=None, pid=None, pinned: bool = False) -> np.ndarray:
     """Build the reference's 96-byte AoS (what SearchFullSet receives as vector<Particle>) from columns.
     pinned=True allocates the records in page-locked host memory through torch (zero-copy upload path)."""
@@ -341,9 +353,9 @@ class Context:
     def dist_init(self, nranks: int, rank: int, unique_id: bytes | None):
         self._check(self.lib.vrgpu_dist_init(self.h, nranks, rank, unique_id))
 
-    def dist_search_full_set(self, parts, slab_lo, slab_hi, opts: SearchOpts):
+    def dist_search_full_set(self, parts, slab_lo, slab_hi, opts: SearchOpts, out=None):
         n = parts.shape[0]
-        pfof = np.zeros(n, dtype=np.int64)
+        pfof = out if out is not None else np.zeros(n, dtype=np.int64)
         ng = C.c_longlong(0)
         self._check(self.lib.vrgpu_dist_search_full_set(self.h, view_of(parts), slab_lo, slab_hi, C.byref(opts),
                                                         pfof.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
