@@ -10,6 +10,7 @@
  *   vrref_binding_energy   -> GetBindingEnergy                    (src/substructureproperties.cxx:3884)
  *   vrref_sort_by_binding_energy -> SortAccordingtoBindingEnergy   (src/substructureproperties.cxx:4256)
  *   vrref_build_pglist     -> BuildNumInGroup + BuildPGList        (src/buildandsortarrays.cxx:11, 26)
+ *   vrref_fofcriterion6d   -> NBody::KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) (NBodylib/src/KDTree/KDFOF.cxx:133)
  *
  * It is compiled against the reference headers where they lie and linked with the reference's own
  * objects into oracle/_ref/libvrref*.so (see oracle/Makefile).  Nothing here re-implements the
@@ -161,6 +162,30 @@ long long vrref_kdfof(long long n, const double *pos, const double *vel, int ndi
     else tree = new KDTree(P.data(), n, bucket_size, tree->TPHYS, tree->KEPAN, 100, 0, 0, 0, pp);
     Int_t ng = 0;
     Int_t *pfof = tree->FOF(fdist, ng, minnum, 1);
+    delete tree; /* restores input order */
+    for (long long i = 0; i < n; i++) pfof_out[i] = pfof[i];
+    delete[] pfof;
+    return ng;
+}
+
+/* Direct call of KDTree::FOFCriterion(FOF6d, params, ng, minsize, order = 1, ipcheckflag = 1, FOFcheckbg) on a physical
+ * tree, exactly as the 6D core search of SearchSubset does (search.cxx:1607-1611): params[1] = params[6] = p6,
+ * params[2] = params[7] = p7, params[9] = p9, params[0] = tree type; the particles' potential field carries the mask. */
+long long vrref_fofcriterion6d(long long n, const double *pos, const double *vel, const double *pot, double p6, double p7,
+                               double p9, long long minsize, int bucket_size, long long *pfof_out)
+{
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, NULL, NULL);
+    for (long long i = 0; i < n; i++) P[i].SetPotential(pot[i]);
+    KDTree *tree = new KDTree(P.data(), n, bucket_size, tree->TPHYS, tree->KEPAN, 100);
+    Double_t param[20];
+    for (int k = 0; k < 20; k++) param[k] = 0;
+    param[0] = tree->GetTreeType();
+    param[1] = param[6] = p6;
+    param[2] = param[7] = p7;
+    param[9] = p9;
+    Int_t ng = 0;
+    Int_t *pfof = tree->FOFCriterion(FOF6d, param, ng, minsize, 1, 1, FOFcheckbg);
     delete tree; /* restores input order */
     for (long long i = 0; i < n; i++) pfof_out[i] = pfof[i];
     delete[] pfof;

@@ -53,6 +53,18 @@ static inline int pair_links(const double *ti, const double *xj, const double *v
     return d2 < r2max;
 }
 
+/* FOF6d (NBodylib/src/KDTree/FOFFunc.h:48-55), the comparison function of the 6D core search (search.cxx:1607-1611):
+ * total += dx_j^2/params[6]; total += dv_j^2/params[7] for j = 0..2 in this order, link iff total < 1. */
+static inline int pair_links_fof6d(const double *xi, const double *xj, const double *vi, const double *vj, const double *crit)
+{
+    double total = 0;
+    for (int j = 0; j < 3; j++) {
+        total += (xi[j] - xj[j]) * (xi[j] - xj[j]) / crit[0];
+        total += (vi[j] - vj[j]) * (vi[j] - vj[j]) / crit[1];
+    }
+    return total < 1;
+}
+
 typedef struct { i64 key; i64 idx; } keyidx;
 static int cmp_keyidx(const void *a, const void *b)
 {
@@ -63,10 +75,18 @@ static int cmp_keyidx(const void *a, const void *b)
 
 /* Exact neighbour search on a uniform grid over the first three coordinates + union-find.
  * x: n*3 positions, v: n*3 velocities or NULL, r2max: squared linking length, period: 0 for open. */
+static void fof_link_crit(i64 n, const double *x, const double *v, double r2max, double period, const double *crit, i64 *parent);
 static void fof_link(i64 n, const double *x, const double *v, double r2max, double period, i64 *parent)
+{
+    fof_link_crit(n, x, v, r2max, period, NULL, parent);
+}
+/* crit != NULL: the pair predicate is FOF6d with {params[6], params[7]} = crit (open box only); a linked pair has
+ * |dx_j| < sqrt(params[6]) on every axis, which sizes the grid. */
+static void fof_link_crit(i64 n, const double *x, const double *v, double r2max, double period, const double *crit, i64 *parent)
 {
     for (i64 i = 0; i < n; i++) parent[i] = i;
     if (n < 2) return;
+    if (crit) r2max = crit[0];
     double r = sqrt(r2max) * (1.0 + 1e-9);
     double lo[3], hi[3], cs[3];
     int nc[3];
@@ -168,7 +188,9 @@ static void fof_link(i64 n, const double *x, const double *v, double r2max, doub
                         if (ck == me && wrapped && bq == a) continue;
                         if (uf_find(parent, i) == uf_find(parent, j)) continue;
                         int linked;
-                        if (!wrapped) {
+                        if (crit) {
+                            linked = pair_links_fof6d(&x[3 * i], &x[3 * j], &v[3 * i], &v[3 * j], crit);
+                        } else if (!wrapped) {
                             linked = pair_links(&x[3 * i], &x[3 * j], v ? &v[3 * i] : NULL, v ? &v[3 * j] : NULL, r2max);
                         } else {
                             /* target i imaged towards j, and target j imaged towards i (either BFS order can occur) */
@@ -232,6 +254,34 @@ long long vro_fof3d(long long n, const double *pos, double b, const double *peri
     fof_link(n, pos, NULL, b * b, period ? period[0] : 0.0, parent);
     i64 ng = label_groups(n, parent, minsize, pid, pfof_out, 0);
     free(parent);
+    return ng;
+}
+
+/* KDTree::FOFCriterion(FOF6d, params, numgroups, minsize, order = 1, ipcheckflag = 1, FOFcheckbg) as the 6D core search calls
+ * it (search.cxx:1607-1611, 1664; KDFOF.cxx:133-240): particles whose potential field is >= params[9] are left out
+ * (FOFcheckbg, fofalgo.cxx:205-208), the others are linked by FOF6d; groups below minsize dissolve; ids by size descending
+ * with the canonical min-pid tie break.  The tree only prunes with a lower bound of the position part of `total`
+ * (KDSplitNode.cxx:894-925 with params[1] == params[6]), so the groups are the connected components of the predicate. */
+long long vro_fof_criterion6d(long long n, const double *pos, const double *vel, const double *pot, double p6, double p7,
+                              double p9, long long minsize, const long long *pid, long long *pfof_out)
+{
+    if (n <= 0) return 0;
+    i64 na = 0;
+    i64 *act = (i64 *)malloc(sizeof(i64) * (size_t)n);
+    for (i64 i = 0; i < n; i++) { pfof_out[i] = 0; if (pot[i] < p9) act[na++] = i; }
+    if (na == 0) { free(act); return 0; }
+    double *x = (double *)malloc(sizeof(double) * 3 * (size_t)na), *v = (double *)malloc(sizeof(double) * 3 * (size_t)na);
+    i64 *cp = (i64 *)malloc(sizeof(i64) * (size_t)na), *parent = (i64 *)malloc(sizeof(i64) * (size_t)na);
+    i64 *out = (i64 *)malloc(sizeof(i64) * (size_t)na);
+    for (i64 a = 0; a < na; a++) {
+        for (int k = 0; k < 3; k++) { x[3 * a + k] = pos[3 * act[a] + k]; v[3 * a + k] = vel[3 * act[a] + k]; }
+        cp[a] = pid ? pid[act[a]] : act[a];
+    }
+    const double crit[2] = {p6, p7};
+    fof_link_crit(na, x, v, 0.0, 0.0, crit, parent);
+    i64 ng = label_groups(na, parent, minsize, cp, out, 0);
+    for (i64 a = 0; a < na; a++) pfof_out[act[a]] = out[a];
+    free(out); free(parent); free(cp); free(v); free(x); free(act);
     return ng;
 }
 

@@ -42,6 +42,12 @@ typedef struct {
 long long vro_fof3d(long long n, const double *pos, double b, const double *period, long long minsize,
                     const long long *pid, long long *pfof_out);
 
+/* KDTree::FOFCriterion with FOF6d + FOFcheckbg, the linking step of the 6D core search (search.cxx:1607-1611, 1664;
+ * SURVEY section 8 row f2): particles with pot[i] >= p9 are left out, the others link iff
+ * sum_j dx_j^2/p6 + dv_j^2/p7 < 1 (FOFFunc.h:48-55, that summation order).  Open box.  Returns G. */
+long long vro_fof_criterion6d(long long n, const double *pos, const double *vel, const double *pot, double p6, double p7,
+                              double p9, long long minsize, const long long *pid, long long *pfof_out);
+
 /* AdjustStructureForPeriod (search.cxx:856-895): pos modified in place. */
 void vro_adjust_for_period(long long n, double *pos, double period, const long long *pfof, long long ngroups);
 

@@ -146,6 +146,17 @@ class Ref:
         ng = self.lib.vrref_kdfof(n, _pd(pos), _pd(vel), ndim, fdist, _pd(per), minnum, bucket, _pl(out))
         return out, int(ng)
 
+    def fofcriterion6d(self, pos, vel, pot, p6, p7, p9=0.5, minsize=20, bucket=16):
+        """KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) as called by the 6D core search (search.cxx:1607-1611)."""
+        pos = _f64(pos); vel = _f64(vel); pot = _f64(pot)
+        n = pos.shape[0]
+        out = np.zeros(n, dtype=np.int64)
+        f = self.lib.vrref_fofcriterion6d
+        f.restype = c_ll
+        f.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, c_dbl, c_dbl, c_dbl, c_ll, C.c_int, P_ll]
+        ng = f(n, _pd(pos), _pd(vel), _pd(pot), p6, p7, p9, minsize, bucket, _pl(out))
+        return out, int(ng)
+
     def search_full_set(self, pos, vel, mass, pid, opts: RefOpts):
         pos = _f64(pos).copy()
         vel = _f64(vel).copy()
@@ -276,6 +287,17 @@ class Oracle:
         pid = _i64(pid) if pid is not None else None
         out = np.zeros(n, dtype=np.int64)
         ng = self.lib.vro_fof3d(n, _pd(pos), b, _pd(per), minsize, _pl(pid), _pl(out))
+        return out, int(ng)
+
+    def fof_criterion6d(self, pos, vel, pot, p6, p7, p9=0.5, minsize=20, pid=None):
+        pos = _f64(pos); vel = _f64(vel); pot = _f64(pot)
+        n = pos.shape[0]
+        pid = _i64(pid) if pid is not None else None
+        out = np.zeros(n, dtype=np.int64)
+        f = self.lib.vro_fof_criterion6d
+        f.restype = c_ll
+        f.argtypes = [c_ll, P_dbl, P_dbl, P_dbl, c_dbl, c_dbl, c_dbl, c_ll, P_ll, P_ll]
+        ng = f(n, _pd(pos), _pd(vel), _pd(pot), p6, p7, p9, minsize, _pl(pid), _pl(out))
         return out, int(ng)
 
     def adjust_for_period(self, pos, period, pfof, ngroups):

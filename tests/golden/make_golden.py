@@ -9,6 +9,9 @@ Each file holds the float32-exact inputs and the reference's outputs:
   phi_tree   Potential() (kd-tree monopole, theta 0.5, bucket 8) of the largest 3D group, member order = index order
   pos_out    positions after the type-5 run (AdjustStructureForPeriod applied)
 
+core/core_s3.npz (SURVEY 8f row f2, linking step): KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) on a halo with two cores in its CM
+frame, three iterations of shrinking linking lengths: inputs pos/vel/pot, per iteration p6, p7, minsize and the canonical ids.
+
 binding/be_s5.npz: GetBindingEnergy on a group-ordered set holding one group above ompunbindnum (tree branch)
 and a handful below (pair loop): inputs pos/vel/mass/num/gcmvel, reference outputs phi, E, T, Pot, Efrac, iminpot, ibound.
 """
@@ -48,6 +51,23 @@ def main():
         print(name, "groups 3d/6d/unbound:", int(c5.max()), int(c3.max()), int(cu.max()), "largest", len(sel))
 
 
+def core_search_case():
+    ref = vroracle.Ref("serial")
+    n, seed = 12000, 3
+    pos, vel, pot = vrsynth.halo_with_cores(n, seed)
+    pid = np.arange(n)
+    p6, p7 = vrsynth.core_search_lengths(pos, vel)
+    out = dict(pos=pos.astype(np.float32), vel=vel.astype(np.float32), pot=pot, p9=0.5, minsize=max(20, int(n * 0.005)))
+    for it in range(3):
+        pr, nr = ref.fofcriterion6d(pos, vel, pot, p6, p7, 0.5, out["minsize"], 16)
+        cr, _ = vrsynth.canonical_groups(pr, pid)
+        out[f"p6_{it}"] = p6; out[f"p7_{it}"] = p7; out[f"pfof_{it}"] = cr.astype(np.int32); out[f"ng_{it}"] = nr
+        print("core search iteration", it, "groups", nr, "largest", int(np.bincount(cr)[1:].max()) if nr else 0)
+        p6 *= 0.75 ** 2; p7 *= 0.75 ** 2
+    os.makedirs(os.path.join(HERE, "core"), exist_ok=True)
+    np.savez_compressed(os.path.join(HERE, "core", "core_s3.npz"), **out)
+
+
 def binding_energy_case():
     ref = vroracle.Ref("serial")
     rng = np.random.default_rng(5)
@@ -74,5 +94,9 @@ def binding_energy_case():
 
 
 if __name__ == "__main__":
-    binding_energy_case()
-    main()
+    if "core" in sys.argv[1:]:
+        core_search_case()
+    else:
+        core_search_case()
+        binding_energy_case()
+        main()

@@ -95,3 +95,15 @@ def test_oracle_binding_energy(oracle):
     assert np.allclose(got["T"], z["T"], rtol=1e-12) and np.allclose(got["Pot"], z["Pot"], rtol=1e-11)
     assert np.array_equal(got["Efrac"], z["Efrac"])
     assert np.array_equal(got["iminpot"], z["iminpot"]) and np.array_equal(got["ibound"], z["ibound"])
+
+
+def test_oracle_core_search_linking_golden(oracle):
+    """SURVEY section 8 row f2, linking step (KDTree::FOFCriterion with FOF6d + FOFcheckbg): travelling fixture made from
+    the compiled reference by tests/golden/make_golden.py."""
+    z = np.load(os.path.join(HERE, "golden", "core", "core_s3.npz"))
+    pos, vel, pot = z["pos"].astype(np.float64), z["vel"].astype(np.float64), z["pot"]
+    pid = np.arange(len(pos))
+    for it in range(3):
+        pf, ng = oracle.fof_criterion6d(pos, vel, pot, float(z[f"p6_{it}"]), float(z[f"p7_{it}"]), float(z["p9"]), int(z["minsize"]), pid)
+        assert ng == int(z[f"ng_{it}"])
+        assert np.array_equal(pf, z[f"pfof_{it}"].astype(np.int64))

@@ -53,6 +53,27 @@ def test_single_leaf_tree_ignores_periodicity(ref, oracle):
     assert nr == 1 and np.all(pr == 1)
 
 
+@pytest.mark.parametrize("n,seed", [(6000, 1), (20000, 2)])
+def test_fof_criterion_6d_core_search(ref, oracle, n, seed):
+    """SURVEY section 8 row f2, linking step: KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) with the linking lengths of the 6D
+    core search and of its iterations (search.cxx:1586-1598, 1640-1650: both lengths shrink by the *_faciter factors)."""
+    pos, vel, pot = vrsynth.halo_with_cores(n, seed)
+    pid = np.arange(n)
+    p6, p7 = vrsynth.core_search_lengths(pos, vel)
+    found = 0
+    for it in range(3):
+        minsize = max(20, int(n * 0.005))
+        pr, nr = ref.fofcriterion6d(pos, vel, pot, p6, p7, 0.5, minsize, 16)
+        cr, _ = vrsynth.canonical_groups(pr, pid)
+        po, no = oracle.fof_criterion6d(pos, vel, pot, p6, p7, 0.5, minsize, pid)
+        assert nr == no, (it, nr, no)
+        assert np.array_equal(cr, po), it
+        assert np.all(po[pot >= 0.5] == 0)                           # FOFcheckbg keeps tagged particles out
+        found = max(found, no)
+        p6 *= 0.75 ** 2; p7 *= 0.75 ** 2
+    assert found >= 2                                                # the two cores separate at some iteration
+
+
 def test_fof6d_direct_tree_call(ref, oracle):
     """KDTree::FOF on a 6-D tree (TPHS) == oracle 6-D link of pre-scaled coordinates."""
     rng = np.random.default_rng(2)

@@ -234,3 +234,31 @@ def make_slab(n: int, seed: int, lo: float, hi: float, box: float = BOX, conc: f
     nn = len(pid)
     return {"pos": np.ascontiguousarray(pos[o]), "vel": np.ascontiguousarray(vel[o]), "mass": np.full(nn, np.float64(np.float32(m))),
             "pid": np.ascontiguousarray(pid[o]), "box": box, "n": nn, "seed": seed, "n_total": n}
+
+
+def halo_with_cores(n, seed):
+    """One halo in its CM frame with two dense, cold cores (a merger remnant) and a few already-tagged substructure
+    particles -- the input of the 6D core search (search.cxx:1531-1700)."""
+    rng = np.random.default_rng(seed)
+    n1, n2 = n // 6, n // 10
+    nb = n - n1 - n2
+    r = 0.8 * rng.random(nb) ** 1.2
+    d = rng.normal(size=(nb, 3)); d /= np.linalg.norm(d, axis=1)[:, None]
+    pos = [r[:, None] * d, np.array([0.25, 0.0, 0.0]) + 0.03 * rng.normal(size=(n1, 3)),
+           np.array([-0.3, 0.1, 0.0]) + 0.025 * rng.normal(size=(n2, 3))]
+    vel = [250.0 * rng.normal(size=(nb, 3)), np.array([150.0, 0, 0]) + 40.0 * rng.normal(size=(n1, 3)),
+           np.array([-200.0, 50.0, 0]) + 35.0 * rng.normal(size=(n2, 3))]
+    pos = np.concatenate(pos); vel = np.concatenate(vel)
+    pos = pos.astype(np.float32).astype(np.float64); vel = vel.astype(np.float32).astype(np.float64)
+    tagged = rng.random(n) < 0.03                      # pfof > 0: Partsubset[i].SetPotential(pfof) (search.cxx:1605)
+    pot = np.where(tagged, rng.integers(1, 5, size=n).astype(np.float64), 0.0)
+    return pos, vel, pot
+
+
+def core_search_lengths(pos, vel):
+    """params[6], params[7] of the first 6D core search of such a halo: a fraction of the mean inter-particle spacing and
+    of the velocity dispersion, in the manner of search.cxx:1586-1598."""
+    n = len(pos)
+    ell = 0.2 * (4.0 / 3.0 * np.pi * 0.8 ** 3 / n) ** (1.0 / 3.0) * 3.0
+    sig2 = float(np.mean(np.sum((vel - vel.mean(axis=0)) ** 2, axis=1)) / 3.0)
+    return (ell * 0.6) ** 2, sig2 * 0.5 ** 2
