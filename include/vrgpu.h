@@ -116,6 +116,15 @@ int vrgpu_adjust_for_period(vrgpu_ctx *ctx, vrgpu_view view, double period, cons
 int vrgpu_fof6d(vrgpu_ctx *ctx, vrgpu_view view, const long long *pfof3d, long long ngroups3d, double b6,
                 double vfac, int mode, long long minsize, long long *pfof_out, long long *ngroups_out);
 
+/* Replaces NBody::KDTree::FOFCriterion(FOF6d, params, numgroups, minsize, order = 1, ipcheckflag = 1, FOFcheckbg)
+ * (NBodylib/src/KDTree/KDFOF.cxx:133-240) as the 6D core search of SearchSubset calls it (src/search.cxx:1607-1611 and
+ * :1664): particles i with check[i] >= check_below are left out (FOFcheckbg, src/fofalgo.cxx:205-208;
+ * check == NULL keeps everyone), the others link iff sum_j dx_j^2/xlink2 + dv_j^2/vlink2 < 1 (FOFFunc.h:48-55: params[6],
+ * params[7]); groups below minsize dissolve; pfof_out[i] by particle index, ids 1..G by size descending (min pid breaks ties).
+ * Open box (the subset is in its halo's centre-of-mass frame). */
+int vrgpu_fof_criterion6d(vrgpu_ctx *ctx, vrgpu_view view, const double *check, double check_below, double xlink2, double vlink2,
+                          long long minsize, long long *pfof_out, long long *ngroups_out);
+
 /* Potentials of groups given in CSR form (offsets[G+1], index[offsets[G]] = particle index in the view).
  * Replaces the direct-sum loop of Unbind (src/unbind.cxx:398-416) for n <= pp_threshold and
  * Potential() (src/unbind.cxx:1607-1741; kd-tree of KDTree.cxx:438-507, bucket, theta) above it.

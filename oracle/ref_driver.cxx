@@ -32,6 +32,7 @@ void GetBindingEnergyGPU(Options &opt, const Int_t nbodies, NBody::Particle *Par
 void SortGroupParticlesGPU(Options &opt, NBody::Particle *Part, Int_t ngroup, Int_t *numingroup, Int_t *noffset, PropData *pdata);
 Int_t *BuildNumInGroupGPU(const Int_t nbodies, const Int_t numgroups, Int_t *pfof);
 Int_t **BuildPGListGPU(const Int_t nbodies, const Int_t numgroups, Int_t *numingroup, Int_t *pfof);
+Int_t *FOFCriterion6DCoreGPU(NBody::Particle *Partsubset, Int_t nsubset, Double_t *param, Int_t &numgroups, Int_t minsize);
 #define BuildNumInGroup BuildNumInGroupGPU
 #define BuildPGList BuildPGListGPU
 #define GetBindingEnergy GetBindingEnergyGPU
@@ -185,7 +186,12 @@ long long vrref_fofcriterion6d(long long n, const double *pos, const double *vel
     param[2] = param[7] = p7;
     param[9] = p9;
     Int_t ng = 0;
+#ifdef VRREF_USE_GPU
+    /* the drop-in body gets the particles as the tree left them (reordered, ids = input index) */
+    Int_t *pfof = FOFCriterion6DCoreGPU(P.data(), n, param, ng, minsize);
+#else
     Int_t *pfof = tree->FOFCriterion(FOF6d, param, ng, minsize, 1, 1, FOFcheckbg);
+#endif
     delete tree; /* restores input order */
     for (long long i = 0; i < n; i++) pfof_out[i] = pfof[i];
     delete[] pfof;

@@ -1,6 +1,8 @@
 """GPU: the drop-in boundary exercised through the reference's OWN types.  oracle/_ref/libvrref_gpu.so links the
 reference's objects with velociraptor-stf_b200/host/vrgpu_adaptor.cxx (SearchFullSet / CheckUnboundGroups / Potential bodies on
 top of the C ABI); the same bridge functions of libvrref.so run the reference's CPU bodies.  Same inputs, same Options."""
+import os
+
 import numpy as np
 import pytest
 
@@ -61,3 +63,21 @@ def test_potential_through_reference_types(ref, refgpu):
     want = ref.potential(pos, mass, o)
     got = refgpu.potential(pos, mass, o)
     assert np.max(np.abs(got / want - 1.0)) < 1e-10
+
+
+@pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
+                    reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
+def test_core_search_linking_through_reference_types(ref, refgpu):
+    """Row f2, linking step: the adaptor body FOFCriterion6DCoreGPU receives the reference's own Particle array in the order
+    its KDTree left it (ids = input index, potential field = the FOFcheckbg mask) and must return what
+    tree->FOFCriterion(FOF6d, ..., FOFcheckbg) returns (search.cxx:1611), up to the canonical order of equal-sized groups."""
+    n = 15000
+    pos, vel, pot = vrsynth.halo_with_cores(n, 6)
+    pid = np.arange(n)
+    p6, p7 = vrsynth.core_search_lengths(pos, vel)
+    for it in range(3):
+        want, nw = ref.fofcriterion6d(pos, vel, pot, p6, p7, 0.5, 75, 16)
+        got, ng = refgpu.fofcriterion6d(pos, vel, pot, p6, p7, 0.5, 75, 16)
+        cw, _ = vrsynth.canonical_groups(want, pid)
+        assert ng == nw and np.array_equal(got, cw)
+        p6 *= 0.75 ** 2; p7 *= 0.75 ** 2

@@ -18,7 +18,7 @@ pipes() {
 }
 gated() {
   echo "== gated tests (first GPU run): binding-energy sort adaptor, pglist, Keep_background_potential=0, 3DFOF edge cases, many-window dispersion"
-  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py -q -m gpu 2>&1 | tail -8
+  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -8
 }
 sym() {
   for v in 0 1 2; do

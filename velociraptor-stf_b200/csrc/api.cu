@@ -327,6 +327,41 @@ int vrgpu_fof6d(vrgpu_ctx *ctx, vrgpu_view view, const long long *pfof3d, long l
     });
 }
 
+int vrgpu_fof_criterion6d(vrgpu_ctx *ctx, vrgpu_view view, const double *check, double check_below, double xlink2, double vlink2,
+                          long long minsize, long long *pfof_out, long long *ngroups_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(pfof_out && ngroups_out, VRGPU_EINVAL, "null pointer");
+        CallTimer ct(ctx);
+        DeviceParticles P;
+        {
+            StageTimer t(ctx);
+            upload_view(ctx, view, true, false, true, P);
+            ctx->stats.h2d_ms += t.stop();
+        }
+        DBuf<double> chk;
+        if (check && P.n) {
+            chk.alloc(ctx, P.n);
+            VR_CUDA(cudaMemcpyAsync(chk.p, check, P.n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+            ctx->stats.h2d_bytes += (long long)(P.n * sizeof(double));
+        }
+        DBuf<long long> pf(ctx, P.n ? P.n : 1);
+        long long ng = 0;
+        {
+            StageTimer t(ctx);
+            ng = fof_criterion6d_device(ctx, P, check ? chk.p : nullptr, check_below, xlink2, vlink2, minsize, pf.p);
+            ctx->stats.fof6d_ms += t.stop();
+        }
+        {
+            StageTimer t(ctx);
+            download_i64(ctx, pf.p, pfof_out, P.n);
+            ctx->stats.d2h_ms += t.stop();
+        }
+        *ngroups_out = ng;
+        ctx->stats.n_groups_final = ng;
+    });
+}
+
 int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const long long *index, double G,
                     double eps, double theta, int bucket, long long pp_threshold, double *phi_out)
 {

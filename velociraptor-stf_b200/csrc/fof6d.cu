@@ -592,6 +592,7 @@ struct Link6 {
     const uint32_t *uni;        // per cell: common root of all its particles, or NONE32
     const uint32_t *chunk_start; // exclusive scan of per-cell 32-particle chunk counts
     uint32_t nchunks;
+    double p6, p7, ip6, ip7;    // criterion predicate only (FOF6d: params[6], params[7] and their reciprocals)
 };
 
 __device__ __forceinline__ bool links6(double ax, double ay, double az, double avx, double avy, double avz, double bx, double by,
@@ -604,8 +605,37 @@ __device__ __forceinline__ bool links6(double ax, double ay, double az, double a
     return __dadd_rn(d2, v2) < 1.0;
 }
 
+// FOF6d (NBodylib/src/KDTree/FOFFunc.h:48-55), the comparison function of KDTree::FOFCriterion in the 6D core search
+// (search.cxx:1607-1611): total += dx_j^2/params[6]; total += dv_j^2/params[7], j = 0..2 in this
+// order, link iff total < 1.  The six IEEE divisions are only spent on pairs within 1e-9 of the threshold; everything
+// else is decided by the same sum taken with reciprocals (which differs from the exact one by a few 1e-16).
+__device__ __forceinline__ bool links6_fof6d(const Link6 &L, double ax, double ay, double az, double avx, double avy, double avz, double bx,
+                                             double by, double bz, double bvx, double bvy, double bvz)
+{
+    const double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by), dz = __dsub_rn(az, bz);
+    const double ux = __dsub_rn(avx, bvx), uy = __dsub_rn(avy, bvy), uz = __dsub_rn(avz, bvz);
+    const double x2 = __dmul_rn(dx, dx), y2 = __dmul_rn(dy, dy), z2 = __dmul_rn(dz, dz);
+    const double a2 = __dmul_rn(ux, ux), b2 = __dmul_rn(uy, uy), c2 = __dmul_rn(uz, uz);
+    const double approx = (x2 + y2 + z2) * L.ip6 + (a2 + b2 + c2) * L.ip7;
+    if (approx < 1.0 - 1e-9) return true;
+    if (approx > 1.0 + 1e-9) return false;
+    double total = 0.0;
+    total = __dadd_rn(total, __ddiv_rn(x2, L.p6)); total = __dadd_rn(total, __ddiv_rn(a2, L.p7));
+    total = __dadd_rn(total, __ddiv_rn(y2, L.p6)); total = __dadd_rn(total, __ddiv_rn(b2, L.p7));
+    total = __dadd_rn(total, __ddiv_rn(z2, L.p6)); total = __dadd_rn(total, __ddiv_rn(c2, L.p7));
+    return total < 1.0;
+}
+// CRIT = false: the scaled-coordinate predicate of the 6DFOF stage; CRIT = true: FOF6d on unscaled coordinates
+template <bool CRIT>
+__device__ __forceinline__ bool links6p(const Link6 &L, double ax, double ay, double az, double avx, double avy, double avz, double bx, double by,
+                                        double bz, double bvx, double bvy, double bvz)
+{
+    if (CRIT) return links6_fof6d(L, ax, ay, az, avx, avy, avz, bx, by, bz, bvx, bvy, bvz);
+    return links6(ax, ay, az, avx, avy, avz, bx, by, bz, bvx, bvy, bvz);
+}
+
 // seeding: every particle against (up to) the first 32 particles of its own cell that precede it; stop at the first link
-__global__ void __launch_bounds__(256) k_seed6(Link6 L)
+template <bool CRIT = false> __global__ void __launch_bounds__(256) k_seed6(Link6 L)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= L.ntot) return;
@@ -615,7 +645,7 @@ __global__ void __launch_bounds__(256) k_seed6(Link6 L)
     const size_t n = L.ntot;
     const double ax = L.q[i], ay = L.q[n + i], az = L.q[2 * n + i], avx = L.q[3 * n + i], avy = L.q[4 * n + i], avz = L.q[5 * n + i];
     for (uint32_t j = a0; j < jend; j++) {
-        if (links6(ax, ay, az, avx, avy, avz, L.q[j], L.q[n + j], L.q[2 * n + j], L.q[3 * n + j], L.q[4 * n + j], L.q[5 * n + j])) {
+        if (links6p<CRIT>(L, ax, ay, az, avx, avy, avz, L.q[j], L.q[n + j], L.q[2 * n + j], L.q[3 * n + j], L.q[4 * n + j], L.q[5 * n + j])) {
             uf_union(L.parent, i, j);
             return;
         }
@@ -641,7 +671,7 @@ __global__ void __launch_bounds__(256) k_cell_uniform(const uint32_t *__restrict
 constexpr int L6_WARPS = 8;
 
 // exhaustive pass: one warp per 32-particle chunk of a cell; 13 forward neighbour cells + the cell itself.
-__global__ void __launch_bounds__(L6_WARPS * 32) k_link6(Link6 L)
+template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_link6(Link6 L)
 {
     __shared__ double tq[L6_WARPS][6][32];
     __shared__ uint32_t tr[L6_WARPS][32];
@@ -713,7 +743,7 @@ __global__ void __launch_bounds__(L6_WARPS * 32) k_link6(Link6 L)
                         const uint32_t jx = tb + jj;
                         if (self && jx <= i) continue;
                         if (tr[w][jj] == ri) continue;
-                        if (links6(ax, ay, az, avx, avy, avz, tq[w][0][jj], tq[w][1][jj], tq[w][2][jj], tq[w][3][jj], tq[w][4][jj], tq[w][5][jj])) {
+                        if (links6p<CRIT>(L, ax, ay, az, avx, avy, avz, tq[w][0][jj], tq[w][1][jj], tq[w][2][jj], tq[w][3][jj], tq[w][4][jj], tq[w][5][jj])) {
                             uf_union(L.parent, i, jx);
                             ri = uf_find(L.parent, i);
                         }
@@ -769,6 +799,133 @@ __global__ void k_first_ungrouped(const long long *__restrict__ pfof, size_t n, 
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && pfof[i] == 0) atomicMin(first, (unsigned int)i);
+}
+
+// binning coordinates of the criterion search
+__global__ void k_bin_coords(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z, uint32_t n, double inv,
+                             double *__restrict__ bx, double *__restrict__ by, double *__restrict__ bz)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    bx[s] = x[s] * inv; by[s] = y[s] * inv; bz[s] = z[s] * inv;
+}
+
+// Back half shared by the 6DFOF stage and the criterion search: cells of edge 1 in the BINNING coordinates, particle-level
+// union-find (seed pass, uniform-cell flags, exhaustive pass), canonical labels.  crit == nullptr: gs holds the scaled
+// phase-space columns, which are both the binning coordinates and the predicate's input.  crit != nullptr ({params[6],
+// params[7]}): gs holds unscaled columns, the binning coordinates are x / (sqrt(params[6]) (1 + 1e-9)) -- a linked pair has
+// |dx_j| < sqrt(params[6]) on every axis, so it lies in adjacent cells -- and the predicate is FOF6d.
+static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &gs, uint32_t G, long long minsize, long long *pfof6d_dev,
+                            const double *crit)
+{
+    const int T = 256;
+    const uint32_t ntot = (uint32_t)gs.ntot;
+    DBuf<double> bx, by, bz;
+    const double *kx = gs.x.p, *ky = gs.y.p, *kz = gs.z.p;
+    if (crit) {
+        bx.alloc(ctx, ntot); by.alloc(ctx, ntot); bz.alloc(ctx, ntot);
+        const double inv = 1.0 / (std::sqrt(crit[0]) * (1.0 + 1e-9));
+        VR_LAUNCH(ctx, k_bin_coords, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, ntot, inv, bx.p, by.p, bz.p);
+        kx = bx.p; ky = by.p; kz = bz.p;
+    }
+    // ---- cells of edge 1 in scaled position space ----
+    DBuf<uint64_t> keys(ctx, ntot), keys_tmp(ctx, ntot);
+    DBuf<uint32_t> ord(ctx, ntot), ord_tmp(ctx, ntot);
+    DBuf<double> q(ctx, 6 * (size_t)ntot);
+    DBuf<uint32_t> cell_of(ctx, ntot), cell_start, nchunk, chunk_start;
+    DBuf<uint64_t> cell_key;
+    uint32_t ncells = 0, nwork = 0;
+    {
+        KScope k(ctx, "fof6d.cells");
+        DBuf<unsigned long long> mm(ctx, 6);
+        unsigned long long init[6] = {~0ull, ~0ull, ~0ull, 0ull, 0ull, 0ull};
+        VR_CUDA(cudaMemcpyAsync(mm.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+        VR_LAUNCH(ctx, k_minmax3, std::min<unsigned>(grid_for(ntot, T), (unsigned)ctx->sm_count * 8u), T, 0, kx, ky, kz, ntot, mm.p);
+        unsigned long long enc[6];
+        VR_CUDA(cudaMemcpyAsync(enc, mm.p, sizeof(enc), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        CellOrigin o{};
+        for (int a = 0; a < 3; a++) {
+            const double lo = ord_dbl_host(enc[a]), hi = ord_dbl_host(enc[3 + a]);
+            VR_REQUIRE(std::isfinite(lo) && std::isfinite(hi), VRGPU_EINVAL, "non-finite scaled positions in 6DFOF (zero velocity dispersion?)");
+            o.c0[a] = (long long)std::floor(lo);
+            VR_REQUIRE((long long)std::floor(hi) - o.c0[a] <= (long long)CMASK, VRGPU_EUNSUPPORTED,
+                       "6DFOF: extent / linking length exceeds 16384 cells per axis");
+        }
+        VR_REQUIRE(bits_for_u64v(G) + 3 * CBITS <= 64, VRGPU_EUNSUPPORTED, "6DFOF: too many 3D groups for the cell key");
+        VR_LAUNCH(ctx, k_keys6, grid_for(ntot, T), T, 0, kx, ky, kz, gs.gid.p, ntot, o, keys.p, ord.p);
+        radix_sort_pairs(ctx, keys.p, ord.p, keys_tmp.p, ord_tmp.p, ntot, bits_for_u64v(G) + 3 * CBITS);
+        VR_LAUNCH(ctx, k_gather6, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.vx.p, gs.vy.p, gs.vz.p, ord.p, ntot, q.p);
+        DBuf<uint32_t> flags(ctx, ntot), excl(ctx, ntot), total(ctx, 1);
+        VR_LAUNCH(ctx, k_flag_heads6, grid_for(ntot, T), T, 0, keys.p, ntot, flags.p);
+        exclusive_scan_u32(ctx, flags.p, excl.p, ntot, total.p);
+        VR_CUDA(cudaMemcpyAsync(&ncells, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        cell_start.alloc(ctx, (size_t)ncells + 1);
+        cell_key.alloc(ctx, ncells);
+        VR_LAUNCH(ctx, k_fill_cells6, grid_for(ntot, T), T, 0, keys.p, flags.p, excl.p, ntot, cell_of.p, cell_start.p, cell_key.p, ncells);
+        nchunk.alloc(ctx, ncells);
+        chunk_start.alloc(ctx, ncells);
+        VR_LAUNCH(ctx, k_chunk_counts, grid_for(ncells, T), T, 0, cell_start.p, ncells, nchunk.p);
+        exclusive_scan_u32(ctx, nchunk.p, chunk_start.p, ncells, total.p);
+        VR_CUDA(cudaMemcpyAsync(&nwork, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    keys.reset(); keys_tmp.reset(); ord_tmp.reset();
+    bx.reset(); by.reset(); bz.reset();
+    // the group-major columns are no longer needed (q holds the sorted copy)
+    gs.x.reset(); gs.y.reset(); gs.z.reset(); gs.vx.reset(); gs.vy.reset(); gs.vz.reset(); gs.m.reset();
+
+    // ---- union-find over particles ----
+    DBuf<uint32_t> parent(ctx, ntot), root(ctx, ntot), uni(ctx, ncells);
+    {
+        size_t h = 1;
+        while (h < 2 * (size_t)ncells) h <<= 1;
+        DBuf<uint64_t> hkeys(ctx, h);
+        DBuf<uint32_t> hvals(ctx, h);
+        Link6 L{};
+        L.q = q.p; L.ntot = ntot; L.cell_of = cell_of.p; L.cell_start = cell_start.p; L.cell_key = cell_key.p; L.ncells = ncells;
+        L.hkeys = hkeys.p; L.hvals = hvals.p; L.hmask = (uint32_t)(h - 1); L.parent = parent.p; L.uni = uni.p;
+        L.chunk_start = chunk_start.p; L.nchunks = nwork;
+        if (crit) { L.p6 = crit[0]; L.p7 = crit[1]; L.ip6 = 1.0 / crit[0]; L.ip7 = 1.0 / crit[1]; }
+        {
+            KScope k(ctx, "fof6d.hash_build");
+            VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
+            VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), (uint32_t *)nullptr);
+            VR_LAUNCH(ctx, k_uf_init, grid_for(ntot, T), T, 0, parent.p, ntot);
+        }
+        {
+            KScope k(ctx, "fof6d.seed");
+            if (crit) VR_LAUNCH(ctx, k_seed6<true>, grid_for(ntot, T), T, 0, L);
+            else VR_LAUNCH(ctx, k_seed6<false>, grid_for(ntot, T), T, 0, L);
+            VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, parent.p);
+            const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)ncells * 32, T), (unsigned)ctx->sm_count * 16u));
+            VR_LAUNCH(ctx, k_cell_uniform, grid, T, 0, parent.p, cell_start.p, ncells, uni.p);
+        }
+        {
+            KScope k(ctx, "fof6d.link");
+            const unsigned grid = std::max(1u, std::min<unsigned>((nwork + L6_WARPS - 1) / L6_WARPS, (unsigned)ctx->sm_count * 32u));
+            if (crit) VR_LAUNCH(ctx, k_link6<true>, grid, L6_WARPS * 32, 0, L);
+            else VR_LAUNCH(ctx, k_link6<false>, grid, L6_WARPS * 32, 0, L);
+            VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, root.p);
+        }
+    }
+
+    // ---- labels: (size desc, min pid asc) over all chunks ----
+    uint32_t ng = 0;
+    {
+        KScope k(ctx, "fof6d.labels");
+        DBuf<uint32_t> csize(ctx, ntot), gid_of(ctx, ntot);
+        DBuf<unsigned long long> cminpid(ctx, ntot);
+        VR_CUDA(cudaMemsetAsync(csize.p, 0, sizeof(uint32_t) * ntot, ctx->stream));
+        VR_CUDA(cudaMemsetAsync(cminpid.p, 0xff, sizeof(unsigned long long) * ntot, ctx->stream));
+        VR_LAUNCH(ctx, k_comp_stats, grid_for(ntot, T), T, 0, root.p, ord.p, gs.idx.p, P.has_pid ? P.pid.p : (const long long *)nullptr, ntot,
+                  csize.p, cminpid.p);
+        uint32_t ms = minsize < 1 ? 1u : (minsize > 0xffffffffLL ? 0xffffffffu : (uint32_t)minsize);
+        ng = order_groups(ctx, root.p, csize.p, cminpid.p, ntot, ms, gid_of.p);
+        VR_LAUNCH(ctx, k_write_pfof6, grid_for(ntot, T), T, 0, root.p, ord.p, gs.idx.p, gid_of.p, ntot, pfof6d_dev);
+    }
+    return (long long)ng;
 }
 
 long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof3d_dev, long long ngroups3d, double b6, double vfac,
@@ -893,100 +1050,38 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
                   ntot, xs, xsinv, apply_q3 ? P.pos.p : (double *)nullptr, apply_q3 ? P.vel.p : (double *)nullptr);
     }
 
-    // ---- cells of edge 1 in scaled position space ----
-    DBuf<uint64_t> keys(ctx, ntot), keys_tmp(ctx, ntot);
-    DBuf<uint32_t> ord(ctx, ntot), ord_tmp(ctx, ntot);
-    DBuf<double> q(ctx, 6 * (size_t)ntot);
-    DBuf<uint32_t> cell_of(ctx, ntot), cell_start, nchunk, chunk_start;
-    DBuf<uint64_t> cell_key;
-    uint32_t ncells = 0, nwork = 0;
-    {
-        KScope k(ctx, "fof6d.cells");
-        DBuf<unsigned long long> mm(ctx, 6);
-        unsigned long long init[6] = {~0ull, ~0ull, ~0ull, 0ull, 0ull, 0ull};
-        VR_CUDA(cudaMemcpyAsync(mm.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
-        VR_LAUNCH(ctx, k_minmax3, std::min<unsigned>(grid_for(ntot, T), (unsigned)ctx->sm_count * 8u), T, 0, gs.x.p, gs.y.p, gs.z.p, ntot, mm.p);
-        unsigned long long enc[6];
-        VR_CUDA(cudaMemcpyAsync(enc, mm.p, sizeof(enc), cudaMemcpyDeviceToHost, ctx->stream));
-        VR_CUDA(cudaStreamSynchronize(ctx->stream));
-        CellOrigin o{};
-        for (int a = 0; a < 3; a++) {
-            const double lo = ord_dbl_host(enc[a]), hi = ord_dbl_host(enc[3 + a]);
-            VR_REQUIRE(std::isfinite(lo) && std::isfinite(hi), VRGPU_EINVAL, "non-finite scaled positions in 6DFOF (zero velocity dispersion?)");
-            o.c0[a] = (long long)std::floor(lo);
-            VR_REQUIRE((long long)std::floor(hi) - o.c0[a] <= (long long)CMASK, VRGPU_EUNSUPPORTED,
-                       "6DFOF: extent / linking length exceeds 16384 cells per axis");
-        }
-        VR_REQUIRE(bits_for_u64v(G) + 3 * CBITS <= 64, VRGPU_EUNSUPPORTED, "6DFOF: too many 3D groups for the cell key");
-        VR_LAUNCH(ctx, k_keys6, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.gid.p, ntot, o, keys.p, ord.p);
-        radix_sort_pairs(ctx, keys.p, ord.p, keys_tmp.p, ord_tmp.p, ntot, bits_for_u64v(G) + 3 * CBITS);
-        VR_LAUNCH(ctx, k_gather6, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.vx.p, gs.vy.p, gs.vz.p, ord.p, ntot, q.p);
-        DBuf<uint32_t> flags(ctx, ntot), excl(ctx, ntot), total(ctx, 1);
-        VR_LAUNCH(ctx, k_flag_heads6, grid_for(ntot, T), T, 0, keys.p, ntot, flags.p);
-        exclusive_scan_u32(ctx, flags.p, excl.p, ntot, total.p);
-        VR_CUDA(cudaMemcpyAsync(&ncells, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-        VR_CUDA(cudaStreamSynchronize(ctx->stream));
-        cell_start.alloc(ctx, (size_t)ncells + 1);
-        cell_key.alloc(ctx, ncells);
-        VR_LAUNCH(ctx, k_fill_cells6, grid_for(ntot, T), T, 0, keys.p, flags.p, excl.p, ntot, cell_of.p, cell_start.p, cell_key.p, ncells);
-        nchunk.alloc(ctx, ncells);
-        chunk_start.alloc(ctx, ncells);
-        VR_LAUNCH(ctx, k_chunk_counts, grid_for(ncells, T), T, 0, cell_start.p, ncells, nchunk.p);
-        exclusive_scan_u32(ctx, nchunk.p, chunk_start.p, ncells, total.p);
-        VR_CUDA(cudaMemcpyAsync(&nwork, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-        VR_CUDA(cudaStreamSynchronize(ctx->stream));
-    }
-    keys.reset(); keys_tmp.reset(); ord_tmp.reset();
-    // the group-major columns are no longer needed (q holds the sorted copy)
-    gs.x.reset(); gs.y.reset(); gs.z.reset(); gs.vx.reset(); gs.vy.reset(); gs.vz.reset(); gs.m.reset();
+    return link6_back(ctx, P, gs, G, minsize, pfof6d_dev, nullptr);
+}
 
-    // ---- union-find over particles ----
-    DBuf<uint32_t> parent(ctx, ntot), root(ctx, ntot), uni(ctx, ncells);
-    {
-        size_t h = 1;
-        while (h < 2 * (size_t)ncells) h <<= 1;
-        DBuf<uint64_t> hkeys(ctx, h);
-        DBuf<uint32_t> hvals(ctx, h);
-        Link6 L{};
-        L.q = q.p; L.ntot = ntot; L.cell_of = cell_of.p; L.cell_start = cell_start.p; L.cell_key = cell_key.p; L.ncells = ncells;
-        L.hkeys = hkeys.p; L.hvals = hvals.p; L.hmask = (uint32_t)(h - 1); L.parent = parent.p; L.uni = uni.p;
-        L.chunk_start = chunk_start.p; L.nchunks = nwork;
-        {
-            KScope k(ctx, "fof6d.hash_build");
-            VR_LAUNCH(ctx, k_hash_fill, grid_for(h, T), T, 0, hkeys.p, h);
-            VR_LAUNCH(ctx, k_hash_insert, grid_for(ncells, T), T, 0, cell_key.p, ncells, hkeys.p, hvals.p, (uint32_t)(h - 1), (uint32_t *)nullptr);
-            VR_LAUNCH(ctx, k_uf_init, grid_for(ntot, T), T, 0, parent.p, ntot);
-        }
-        {
-            KScope k(ctx, "fof6d.seed");
-            VR_LAUNCH(ctx, k_seed6, grid_for(ntot, T), T, 0, L);
-            VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, parent.p);
-            const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)ncells * 32, T), (unsigned)ctx->sm_count * 16u));
-            VR_LAUNCH(ctx, k_cell_uniform, grid, T, 0, parent.p, cell_start.p, ncells, uni.p);
-        }
-        {
-            KScope k(ctx, "fof6d.link");
-            const unsigned grid = std::max(1u, std::min<unsigned>((nwork + L6_WARPS - 1) / L6_WARPS, (unsigned)ctx->sm_count * 32u));
-            VR_LAUNCH(ctx, k_link6, grid, L6_WARPS * 32, 0, L);
-            VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, root.p);
-        }
-    }
+// ---------------------------------------------------------------------------------------------------
+// KDTree::FOFCriterion(FOF6d, params, numgroups, minsize, order = 1, ipcheckflag = 1, FOFcheckbg): the linking step of the
+// 6D core search (search.cxx:1607-1611, 1664; KDFOF.cxx:133-240).  Particles whose check value
+// is >= check_below are left out (FOFcheckbg, fofalgo.cxx:205-208); the others are the single "group" handed to the
+// particle-level union-find with the FOF6d predicate.  The reference's tree only prunes with a lower bound of the
+// position part of the sum, so its groups are the connected components of the predicate.
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_check_mask(const double *__restrict__ check, size_t n, double below, long long *__restrict__ one)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) one[i] = (!check || check[i] < below) ? 1ll : 0ll;
+}
 
-    // ---- labels: (size desc, min pid asc) over all chunks ----
-    uint32_t ng = 0;
-    {
-        KScope k(ctx, "fof6d.labels");
-        DBuf<uint32_t> csize(ctx, ntot), gid_of(ctx, ntot);
-        DBuf<unsigned long long> cminpid(ctx, ntot);
-        VR_CUDA(cudaMemsetAsync(csize.p, 0, sizeof(uint32_t) * ntot, ctx->stream));
-        VR_CUDA(cudaMemsetAsync(cminpid.p, 0xff, sizeof(unsigned long long) * ntot, ctx->stream));
-        VR_LAUNCH(ctx, k_comp_stats, grid_for(ntot, T), T, 0, root.p, ord.p, gs.idx.p, P.has_pid ? P.pid.p : (const long long *)nullptr, ntot,
-                  csize.p, cminpid.p);
-        uint32_t ms = minsize < 1 ? 1u : (minsize > 0xffffffffLL ? 0xffffffffu : (uint32_t)minsize);
-        ng = order_groups(ctx, root.p, csize.p, cminpid.p, ntot, ms, gid_of.p);
-        VR_LAUNCH(ctx, k_write_pfof6, grid_for(ntot, T), T, 0, root.p, ord.p, gs.idx.p, gid_of.p, ntot, pfof6d_dev);
-    }
-    return (long long)ng;
+long long fof_criterion6d_device(vrgpu_ctx *ctx, const DeviceParticles &P, const double *check_dev, double check_below, double p6, double p7,
+                                 long long minsize, long long *pfof_dev)
+{
+    VR_REQUIRE(p6 > 0 && p7 > 0 && std::isfinite(p6) && std::isfinite(p7), VRGPU_EINVAL, "linking lengths must be positive and finite");
+    VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "the 6D criterion needs velocities");
+    const int T = 256;
+    VR_CUDA(cudaMemsetAsync(pfof_dev, 0, sizeof(long long) * (P.n ? P.n : 1), ctx->stream));
+    if (P.n == 0) return 0;
+    DBuf<long long> one(ctx, P.n);
+    VR_LAUNCH(ctx, k_check_mask, grid_for(P.n, T), T, 0, check_dev, P.n, check_below, one.p);
+    GroupSet gs;
+    build_groupset(ctx, one.p, P.n, 1, gs);
+    if (gs.ntot == 0) return 0;
+    gather_groupset(ctx, P, gs, true, false);
+    const double crit[2] = {p6, p7};
+    return link6_back(ctx, P, gs, 1u, minsize, pfof_dev, crit);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -10,6 +10,8 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
                        int mode, long long minsize, long long *pfof6d_dev, bool apply_q3);
 
 // write pos+vel of every particle with pfof_dev[i] > 0 back into the caller's writable view
+long long fof_criterion6d_device(vrgpu_ctx *ctx, const DeviceParticles &P, const double *check_dev, double check_below, double p6, double p7,
+                                 long long minsize, long long *pfof_dev);
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 

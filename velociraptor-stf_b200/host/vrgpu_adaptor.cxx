@@ -9,6 +9,8 @@
  *                                                                    src/substructureproperties.cxx:3884  (row f1)
  *     Int_t *BuildNumInGroup(const Int_t, const Int_t, Int_t*)                src/buildandsortarrays.cxx:11  (row f3)
  *     Int_t **BuildPGList(const Int_t, const Int_t, Int_t*, Int_t*)           src/buildandsortarrays.cxx:26  (row f3)
+ *     Int_t *FOFCriterion6DCore(Particle*, Int_t, Double_t*, Int_t&, Int_t)      tree->FOFCriterion(FOF6d, ..., FOFcheckbg) of the
+ *                        6D core search, src/search.cxx:1611 and :1664 (NBodylib/src/KDTree/KDFOF.cxx:133)      (row f2)
  *     void   SortGroupParticlesGPU(Options&, Particle*, Int_t, Int_t*, Int_t*, PropData*)
  *                        the per-group qsort inside SortAccordingtoBindingEnergy, substructureproperties.cxx:4302-4316
  *
@@ -370,4 +372,27 @@ Int_t **VRGPU_NAME(BuildPGList)(const Int_t nbodies, const Int_t numgroups, Int_
     }
     delete[] index;
     return pglist;
+}
+
+/* Row f2, linking step.  The 6D core search of SearchSubset (src/search.cxx:1531-1700) calls
+ *     pfofbg = tree->FOFCriterion(fofcmp = FOF6d, param, numgroupsbg, minsize, iorder = 1, icheck = 1, FOFcheckbg);
+ * at :1611 and, inside its loop over shrinking linking lengths, at :1664.  This body takes the same particles (in whatever
+ * order the tree left them), the same param[] (param[6], param[7]: squared linking lengths, param[9]: the FOFcheckbg
+ * threshold on the particles' potential field) and returns the same thing: a new Int_t[nsubset] indexed by particle ID
+ * (KDFOF.cxx:153-156), 0 = no group, ids 1..numgroups by size descending. */
+Int_t *VRGPU_NAME(FOFCriterion6DCore)(Particle *Partsubset, Int_t nsubset, Double_t *param, Int_t &numgroups, Int_t minsize)
+{
+    Int_t *pfof = new Int_t[nsubset > 0 ? nsubset : 1];
+    numgroups = 0;
+    if (nsubset <= 0) return pfof;
+    vector<double> check((size_t)nsubset);
+    for (Int_t i = 0; i < nsubset; i++) check[i] = Partsubset[i].GetPotential();
+    vector<long long> byindex((size_t)nsubset);
+    long long ng = 0;
+    int rc = vrgpu_fof_criterion6d(context(), view_of(Partsubset, nsubset), check.data(), param[9], param[6], param[7], minsize, byindex.data(),
+                                   &ng);
+    if (rc != VRGPU_OK) die("vrgpu_fof_criterion6d", rc);
+    for (Int_t i = 0; i < nsubset; i++) pfof[Partsubset[i].GetID()] = byindex[i];
+    numgroups = ng;
+    return pfof;
 }

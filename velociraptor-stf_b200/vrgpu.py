@@ -133,6 +133,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_dist_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
     L.vrgpu_dist_search_full_set.argtypes = [C.c_void_p, View, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll, P_ll]
     L.vrgpu_dist_search_full_set_resident.argtypes = [C.c_void_p, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll]
+    L.vrgpu_fof_criterion6d.argtypes = [C.c_void_p, View, P_d, C.c_double, C.c_double, C.c_double, C.c_longlong, P_ll, P_ll]
     L.vrgpu_stream.argtypes = [C.c_void_p]
     L.vrgpu_stream.restype = C.c_void_p
     L.vrgpu_kernel_times.argtypes = [C.c_void_p]
@@ -149,7 +150,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
-                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes",
+                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes", "vrgpu_fof_criterion6d",
                     "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist"]
 
 
@@ -312,6 +313,16 @@ class Context:
         self._check(self.lib.vrgpu_build_pglist(self.h, pf.ctypes.data_as(LL) if pf is not None else None, n, int(ngroups),
                                                 num.ctypes.data_as(LL), index.ctypes.data_as(LL), C.byref(ntot)))
         return num, index[:int(ntot.value)]
+
+    def fof_criterion6d(self, parts, check, xlink2, vlink2, check_below=0.5, minsize=20):
+        """KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg): the linking step of the 6D core search (search.cxx:1607-1611)."""
+        n = parts.shape[0]
+        pf = np.zeros(n, dtype=np.int64)
+        ng = C.c_longlong(0)
+        chk = None if check is None else np.ascontiguousarray(check, dtype=np.float64)
+        self._check(self.lib.vrgpu_fof_criterion6d(self.h, view_of(parts), None if chk is None else chk.ctypes.data_as(C.POINTER(C.c_double)),
+                                                   check_below, xlink2, vlink2, minsize, pf.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
+        return pf, int(ng.value)
 
     def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
         """CheckUnboundGroups (unbind.cxx:196)."""
