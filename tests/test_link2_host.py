@@ -153,3 +153,33 @@ def test_link2_slab_open_along_x(emul, oracle):
     got, ng = canonical(root, pid, 20)
     want, no = oracle.fof3d(pos, b, vrsynth.BOX, 20, pid)
     assert ng == no and np.array_equal(got, want)
+
+
+def test_link2_random_small_inputs(emul, oracle):
+    """300 random small inputs: clustered points in boxes only a few linking lengths wide (so that most neighbour rows wrap
+    and the same cell is reached through several periodic images), periodic and open, every emulated thread order."""
+    rng = np.random.default_rng(2026)
+    for trial in range(300):
+        b = float(rng.choice([0.5, 1.0, 1.7]))
+        L = float(b * rng.uniform(4.7, 14.0))          # 8.1 .. 24 fine cells per axis (the library needs at least 8)
+        nc = int(np.ceil(L / (b / np.sqrt(3.0) * (1.0 - 1e-8))))
+        if nc < 8:
+            continue
+        n = int(rng.integers(1, 400))
+        centres = rng.random((int(rng.integers(1, 6)), 3)) * L
+        pos = centres[rng.integers(0, len(centres), size=n)] + rng.normal(size=(n, 3)) * b * rng.uniform(0.2, 1.5)
+        if rng.random() < 0.3:                          # some exactly coincident particles and some on the faces
+            pos[: n // 4] = pos[n // 4: 2 * (n // 4)][: n // 4] if n >= 8 else pos[: n // 4]
+        pos = np.mod(pos, L)
+        if rng.random() < 0.2 and n > 3:
+            pos[rng.integers(0, n, size=3), rng.integers(0, 3, size=3)] = rng.choice([0.0, L], size=3)
+        pos = pos.astype(np.float32).astype(np.float64)
+        pos = np.clip(pos, 0.0, L)
+        periodic = rng.random() < 0.7
+        minsize = int(rng.integers(1, 6))
+        pid = np.arange(n)
+        want, no = oracle.fof3d(pos, b, L if periodic else None, minsize, pid)
+        root, _ = emul(pos, b, L if periodic else None, int(trial % 3), trial)
+        got, ng = canonical(root, pid, minsize)
+        assert ng == no, (trial, n, b, L, periodic)
+        assert np.array_equal(got, want), (trial, n, b, L, periodic)
