@@ -547,6 +547,28 @@ static void mark_cell(twalk *w, i64 nid, const double *xpos)
     }
 }
 
+/* The arrangement BuildNodes leaves behind: perm_out[i] = input index of the particle at tree position i; node_out
+ * (may be NULL, 2 entries per node, capacity node_cap nodes) receives [start, end) of every node in the pre-order of
+ * GetNodeList.  Returns the number of nodes.  (Test hook for the device build's tie handling.) */
+long long vro_tree_order(long long n, const double *pos, int bucket, long long *perm_out, long long *node_out, long long node_cap)
+{
+    if (n <= 0) return 0;
+    tbuild t;
+    t.pos = pos;
+    t.bucket = bucket;
+    t.perm = perm_out;
+    for (i64 i = 0; i < n; i++) t.perm[i] = i;
+    t.cap = 2 * n / (bucket > 0 ? bucket : 1) + 64;
+    t.nodes = (tnode *)malloc(sizeof(tnode) * (size_t)t.cap);
+    t.nnodes = 0;
+    build_nodes(&t, 0, n);
+    if (node_out)
+        for (i64 j = 0; j < t.nnodes && j < node_cap; j++) { node_out[2 * j] = t.nodes[j].start; node_out[2 * j + 1] = t.nodes[j].end; }
+    i64 nn = t.nnodes;
+    free(t.nodes);
+    return nn;
+}
+
 void vro_potential_tree(long long n, const double *pos, const double *mass, double G, double eps, double theta,
                         int bucket, double *phi_out, long long *interactions_out)
 {

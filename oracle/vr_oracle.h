@@ -67,6 +67,9 @@ void vro_potential_pp(long long n, const double *pos, const double *mass, double
 void vro_potential_tree(long long n, const double *pos, const double *mass, double G, double eps, double theta,
                         int bucket, double *phi_out, long long *interactions_out);
 
+/* Tree order and node ranges of the kd-tree vro_potential_tree builds (KDTree.cxx:304-337, 438-507). */
+long long vro_tree_order(long long n, const double *pos, int bucket, long long *perm_out, long long *node_out, long long node_cap);
+
 /* CheckUnboundGroups + Unbind (unbind.cxx:196-304, 320-729) for fracpotref==1.
  * pfof in/out (0 = unbound), returns the new number of groups, ids re-ordered (size desc, min pid asc) when
  * anything changed.  n_marginal_out (may be NULL): number of grouped particles whose |E| <= tol*|phi| at the

@@ -323,6 +323,17 @@ class Oracle:
         self.lib.vro_potential_pp(pos.shape[0], _pd(pos), _pd(mass), G, eps, _pd(phi))
         return phi
 
+    def tree_order(self, pos, bucket=8):
+        """(perm, nodes): tree position -> input index, and [start, end) of every node in pre-order."""
+        pos = _f64(pos)
+        n = pos.shape[0]
+        perm = np.zeros(n, dtype=np.int64)
+        cap = 4 * n // max(1, bucket) + 64
+        nodes = np.zeros((cap, 2), dtype=np.int64)
+        self.lib.vro_tree_order.restype = c_ll
+        nn = self.lib.vro_tree_order(c_ll(n), _pd(pos), C.c_int(bucket), _pl(perm), _pl(nodes), c_ll(cap))
+        return perm, nodes[:int(nn)]
+
     def potential_tree(self, pos, mass, G, eps=0.0, theta=0.5, bucket=8):
         pos = _f64(pos); mass = _f64(mass)
         phi = np.zeros(pos.shape[0])

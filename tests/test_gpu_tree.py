@@ -5,6 +5,8 @@ Tolerance: BASELINE.json asks 1e-6 relative "against its tree at identical setti
 coordinates are distinct (node membership is then unique).  With exactly tied coordinates at a median the reference's
 quickselect picks by swap history; the GPU build picks the lower member index, so a few cells differ by one particle:
 that case is measured separately and bounded by the monopole truncation error."""
+import os
+
 import numpy as np
 import pytest
 
@@ -12,6 +14,8 @@ import vrsynth
 
 pytestmark = pytest.mark.gpu
 G = 43.0211349
+UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
+                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 
 
 def _clustered(n, rng, scale=1.0):
@@ -76,6 +80,47 @@ def test_tree_with_tied_coordinates(gpu_ctx, oracle):
     print("tied-coordinate case: frac(|dphi/phi| > 1e-6) =", float(np.mean(rel > 1e-6)), "max", float(rel.max()))
     assert np.max(np.abs(phi / pp - 1.0)) < 5e-2
     assert rel.max() < 1e-2  # same order as the tree's own truncation error; NOT the 1e-10 of the tie-free case
+
+
+@UNVERIFIED
+@pytest.mark.parametrize("n,scale", [(30000, 0.5), (200000, 0.05), (1500, 0.001)])
+def test_tree_with_tied_coordinates_exact(gpu_ctx, oracle, monkeypatch, n, scale):
+    """VRGPU_TREE_TIES=1 (csrc/qsel.cuh): every node is arranged by the reference's own MedianPos iterations, so the tied
+    case meets the bar of the tie-free one -- same cells opened, same leaves, potentials at 1e-10.  The emulation of the
+    same per-thread source is pinned against the oracle's arrangement on the CPU (tests/test_qsel_host.py)."""
+    import vrgpu
+    monkeypatch.setenv("VRGPU_TREE_TIES", "1")
+    rng = np.random.default_rng(8)
+    pos = _clustered(n, rng, scale).astype(np.float32).astype(np.float64)
+    assert min(len(np.unique(pos[:, d])) for d in range(3)) < n
+    mass = 0.5 + rng.random(n)
+    parts = vrgpu.particles_from_arrays(pos, mass=mass)
+    eps = 1e-3
+    phi = gpu_ctx.potential(parts, np.array([0, n]), np.arange(n), G, eps=eps, pp_threshold=150)
+    ref, ninter = oracle.potential_tree(pos, mass, G, eps, 0.5, 8)
+    assert gpu_ctx.stats()["n_tree_interactions"] == ninter
+    assert np.max(np.abs(phi / ref - 1.0)) < 1e-10
+
+
+@UNVERIFIED
+def test_tree_exact_ties_many_groups(gpu_ctx, oracle, monkeypatch):
+    """Several groups built in the same launches (sizes on both sides of QS_SMALL = 2048 and of the direct-sum threshold),
+    and a second bucket size."""
+    import vrgpu
+    monkeypatch.setenv("VRGPU_TREE_TIES", "1")
+    rng = np.random.default_rng(9)
+    sizes = [9000, 5000, 2500, 2049, 2048, 151, 150, 40]
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    pos = np.concatenate([_clustered(s, rng, 0.02).astype(np.float32).astype(np.float64) + 3.0 * k for k, s in enumerate(sizes)])
+    n = len(pos)
+    mass = np.ones(n)
+    parts = vrgpu.particles_from_arrays(pos, mass=mass)
+    for bucket in (8, 16):
+        phi = gpu_ctx.potential(parts, off, np.arange(n), G, eps=1e-3, theta=0.5, bucket=bucket, pp_threshold=150)
+        for g, s in enumerate(sizes):
+            sel = slice(off[g], off[g + 1])
+            ref = oracle.potential_tree(pos[sel], mass[sel], G, 1e-3, 0.5, bucket)[0] if s > 150 else oracle.potential_pp(pos[sel], mass[sel], G, 1e-3)
+            assert np.max(np.abs(phi[sel] / ref - 1.0)) < 1e-10, (bucket, g)
 
 
 def test_unbind_with_tree_potentials(gpu_ctx, oracle):

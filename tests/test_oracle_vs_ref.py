@@ -124,6 +124,22 @@ def test_tree_potential(ref, oracle, n):
         assert np.max(np.abs(got / want - 1.0)) < 1e-12
 
 
+@pytest.mark.parametrize("n,sigma", [(3000, 0.5), (30000, 0.5), (100000, 0.02)])
+def test_tree_potential_with_tied_coordinates(ref, oracle, n, sigma):
+    """float32-quantised positions: medians fall inside runs of exactly equal coordinates, so node membership follows from
+    the swap history of KDTree::MedianPos (KDTree.cxx:304-337).  The oracle's transcription reproduces it: same leaves, same
+    cells, every potential bit for bit.  (tests/test_qsel_host.py holds the device build's exact-ties variant to the same
+    arrangement.)"""
+    import vroracle
+    rng = np.random.default_rng(3)
+    pos = (50 + rng.normal(size=(n, 3)) * sigma).astype(np.float32).astype(np.float64)
+    assert min(len(np.unique(pos[:, d])) for d in range(3)) < n
+    mass = np.ones(n)
+    want = ref.potential(pos, mass, vroracle.default_opts(eps=1e-3))
+    got, _ = oracle.potential_tree(pos, mass, G, 1e-3, 0.5, 8)
+    assert np.array_equal(got, want)
+
+
 @pytest.mark.parametrize("nside,seed,unbindtype,bgpot", [(32, 7, 0, 1), (40, 3, 1, 1), (24, 2, 0, 1),
                                                          (32, 7, 0, 0), (40, 3, 1, 0), (48, 5, 0, 0)])
 def test_unbind(ref, oracle, nside, seed, unbindtype, bgpot):

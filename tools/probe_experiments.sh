@@ -3,10 +3,10 @@
 # parity and its time against the measured default, plus the tests written after round 1's GPU minutes ran out.
 # Usage: gpurun --timeout 2400 -- 'bash tools/probe_experiments.sh'            (everything, about half an hour)
 #        gpurun --timeout 900  -- 'bash tools/probe_experiments.sh pipes gated sym'   (chosen sections)
-# Sections: pipes gated sym walk link disp wb.  Log: gpurun_out/probe_experiments.log, bench lines: gpurun_out/probe_*.json
+# Sections: pipes gated sym walk link disp wb ties.  Log: gpurun_out/probe_experiments.log, bench lines: gpurun_out/probe_*.json
 set -u
 mkdir -p gpurun_out
-SECTIONS="${*:-pipes gated sym walk link disp wb}"
+SECTIONS="${*:-pipes gated ties sym walk link disp wb}"
 bench() { # bench <out.json> <args...>: one bench line, CPU baseline skipped
   local out=$1; shift
   timeout 900 python bench.py --steps 5 --warmup 3 --no-cpu-baseline "$@" 2>/dev/null | tail -1 > "$out"
@@ -17,8 +17,8 @@ pipes() {
   timeout 120 python -c "import sys; sys.path.insert(0, 'velociraptor-stf_b200'); import vrgpu; print(vrgpu.Context(0).probe_fp64_pipes())" 2>&1 | tail -1
 }
 gated() {
-  echo "== gated tests (first GPU run): binding-energy sort adaptor, pglist, Keep_background_potential=0, 3DFOF edge cases, many-window dispersion"
-  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -8
+  echo "== gated tests (first GPU run): binding-energy sort adaptor, pglist, Keep_background_potential=0, 3DFOF edge cases, many-window dispersion, exact tree ties"
+  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -8
 }
 sym() {
   for v in 0 1 2; do
@@ -54,9 +54,19 @@ wb() {
     VRGPU_ASYNC_WRITEBACK=$a bench gpurun_out/probe_wb_a$a.json --fofbgtype 3 --pp-threshold 150
   done
 }
+ties() {
+  echo "== VRGPU_TREE_TIES=1: the reference's quickselect arrangement (qsel.cuh): tied-coordinate parity at 1e-10, then the whole tree + unbinding suites under it"
+  VRGPU_RUN_UNVERIFIED=1 timeout 600 python -m pytest tests/test_gpu_tree.py -q -m gpu -k "exact" 2>&1 | tail -4
+  VRGPU_TREE_TIES=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -4
+  for t in 0 1; do
+    echo "== VRGPU_TREE_TIES=$t bench (256^3, 6DFOF + tree unbinding; look at ptree.build), then the 2e7 single halo"
+    VRGPU_TREE_TIES=$t bench gpurun_out/probe_ties_t$t.json --fofbgtype 3 --pp-threshold 150
+    VRGPU_TREE_TIES=$t bench gpurun_out/probe_ties_zoom_t$t.json --single-halo 20000000 --fofbgtype 3 --pp-threshold 150
+  done
+}
 {
   for s in $SECTIONS; do
-    case $s in pipes|gated|sym|walk|link|disp|wb) $s ;; *) echo "unknown section $s" ;; esac
+    case $s in pipes|gated|sym|walk|link|disp|wb|ties) $s ;; *) echo "unknown section $s" ;; esac
   done
 } > gpurun_out/probe_experiments.log 2>&1
 tail -60 gpurun_out/probe_experiments.log

@@ -20,6 +20,7 @@
 // (the reference's quickselect leaves the choice among exactly equal coordinates to its swap sequence; here the tie
 // goes to the lower member index) -- see DESIGN.md "tree parity".
 #include "groups.cuh"
+#include "qsel.cuh"
 #include "rsqrt.cuh"
 #include "ufhash.cuh"
 
@@ -203,6 +204,62 @@ __global__ void k_pt_children(const uint32_t *__restrict__ frontier, uint32_t nF
     nstart[r] = mid; nend[r] = e; nleft[r] = NOCHILD;
     next_frontier[f + k] = l;
     next_frontier[f + k + 1] = r;
+}
+
+// ---- VRGPU_TREE_TIES=1: the reference's quickselect arrangement instead of the sort (qsel.cuh) ---------------------
+__global__ void k_qs_init(qsel::Level L)
+{
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < L.nF) qsel::init_thread(L, f);
+}
+__global__ void k_qs_begin(qsel::Level L)
+{
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < L.nF) qsel::begin_thread(L, f);
+}
+__global__ void k_qs_flag(qsel::Level L)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < L.nAct) qsel::flag_thread(L, p);
+}
+__global__ void k_qs_scatter(qsel::Level L)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < L.nAct) qsel::scatter_thread(L, p);
+}
+__global__ void k_qs_match(qsel::Level L)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < L.nAct) qsel::match_thread(L, p);
+}
+__global__ void k_qs_end(qsel::Level L)
+{
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < L.nF) qsel::end_thread(L, f);
+}
+// nodes of at most QS_SMALL particles: a copy of the node in shared memory, MedianPos itself on one thread
+constexpr int QS_SMALL_THREADS = 64;
+constexpr size_t QS_SMALL_SMEM = (size_t)qsel::QS_SMALL * (sizeof(double) + sizeof(uint32_t));
+__global__ void __launch_bounds__(QS_SMALL_THREADS) k_qs_small(qsel::Level L)
+{
+    extern __shared__ __align__(8) unsigned char qs_smem[];
+    double *val = reinterpret_cast<double *>(qs_smem);
+    uint32_t *idx = reinterpret_cast<uint32_t *>(val + qsel::QS_SMALL);
+    for (uint32_t f = blockIdx.x; f < L.nF; f += gridDim.x) {
+        uint32_t s, e;
+        if (!qsel::small_node(L, f, s, e)) continue; // the same answer for the whole CTA
+        const uint32_t n = e - s, d = L.splitdim[f];
+        for (uint32_t i = threadIdx.x; i < n; i += QS_SMALL_THREADS) {
+            const uint32_t m = L.perm[s + i];
+            idx[i] = m;
+            val[i] = qsel::coord(L, d, m);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) qsel::select_serial(val, idx, qsel::median_index(s, e) - s, n);
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < n; i += QS_SMALL_THREADS) L.perm[s + i] = idx[i];
+        __syncthreads();
+    }
 }
 
 } // namespace
@@ -428,10 +485,13 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     DBuf<uint32_t> slot_of(ctx, nL);
     VR_LAUNCH(ctx, k_pt_compact, grid_for(ntot, T), T, 0, flags.p, sexcl.p, ntot, slot_of.p);
 
+    // VRGPU_TREE_TIES=1 (read per call): arrange every node with the reference's own selection, see qsel.cuh
+    const bool exact_ties = [] { const char *e = getenv("VRGPU_TREE_TIES"); return e && atoi(e) == 1; }();
+
     // ---- ranks along the three axes (ties: lower member first) ----
-    DBuf<uint32_t> rank(ctx, 3 * (size_t)nL), perm(ctx, nL), vtmp(ctx, nL);
-    DBuf<uint64_t> keys(ctx, nL), ktmp(ctx, nL);
-    {
+    DBuf<uint32_t> rank(ctx, exact_ties ? 1 : 3 * (size_t)nL), perm(ctx, nL), vtmp(ctx, exact_ties ? 1 : nL);
+    DBuf<uint64_t> keys(ctx, exact_ties ? 1 : nL), ktmp(ctx, exact_ties ? 1 : nL);
+    if (!exact_ties) {
         KScope k(ctx, "ptree.ranks");
         const double *cols[3] = {gs.x.p, gs.y.p, gs.z.p};
         for (int d = 0; d < 3; d++) {
@@ -448,6 +508,12 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     DBuf<uint32_t> frontier(ctx, cap), frontier2(ctx, cap), splitflag(ctx, cap), splitdim(ctx, cap), fexcl(ctx, cap);
     DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL), fidx(ctx, nL), rootidx(ctx, nL);
     DBuf<unsigned long long> mm(ctx, 6 * cap);
+    // selection state of the exact-ties variant
+    DBuf<uint32_t> qlo(ctx, exact_ties ? cap : 1), qhi(ctx, exact_ties ? cap : 1), qnp(ctx, exact_ties ? cap : 1);
+    DBuf<double> qpiv(ctx, exact_ties ? cap : 1);
+    DBuf<unsigned long long> qflags(ctx, exact_ties ? nL : 1), qscan(ctx, exact_ties ? nL : 1);
+    DBuf<uint32_t> qA(ctx, exact_ties ? nL : 1), qB(ctx, exact_ties ? nL : 1);
+    DBuf<unsigned int> qact(ctx, 1);
     VR_LAUNCH(ctx, k_pt_roots, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, gflag.p, gexcl.p, sexcl.p, NG, ntot, nstart.p, nend.p, nleft.p, frontier.p);
     VR_LAUNCH(ctx, k_pt_iota, grid_for(nL, T), T, 0, perm.p, nL);
     uint32_t nF = nLG, nnodes = nLG;
@@ -490,8 +556,29 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             VR_CUDA(cudaStreamSynchronize(ctx->stream));
             if (nsplit == 0) break;
             VR_REQUIRE((size_t)nnodes + 2 * (size_t)nsplit <= cap, VRGPU_ECUDA, "kd-tree node capacity exceeded");
-            VR_LAUNCH(ctx, k_pt_level_keys, grid_for(nAct, T), T, 0, perm.p, fidx.p, splitflag.p, splitdim.p, rank.p, nL, nAct, rb, keys.p);
-            radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nAct, rb + bits_for_u64v(nF > 1 ? nF - 1 : 1));
+            if (exact_ties) {
+                qsel::Level L{gs.x.p, gs.y.p, gs.z.p, slot_of.p, perm.p, fidx.p, fr, nstart.p, nend.p, splitflag.p, splitdim.p,
+                              qlo.p, qhi.p, qnp.p, qpiv.p, qflags.p, qscan.p, qA.p, qB.p, qact.p, nF, nAct};
+                VR_CUDA(cudaMemsetAsync(qact.p, 0, sizeof(unsigned int), ctx->stream));
+                VR_LAUNCH(ctx, k_qs_init, grid_for(nF, T), T, 0, L);
+                VR_LAUNCH(ctx, k_qs_small, (unsigned)std::min<size_t>(nF, (size_t)148 * 64), QS_SMALL_THREADS, QS_SMALL_SMEM, L);
+                for (;;) { // one iteration of MedianPos for every node above QS_SMALL that is not finished
+                    unsigned int nrun = 0;
+                    VR_CUDA(cudaMemcpyAsync(&nrun, qact.p, sizeof(nrun), cudaMemcpyDeviceToHost, ctx->stream));
+                    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                    if (nrun == 0) break;
+                    VR_CUDA(cudaMemsetAsync(qact.p, 0, sizeof(unsigned int), ctx->stream));
+                    VR_LAUNCH(ctx, k_qs_begin, grid_for(nF, T), T, 0, L);
+                    VR_LAUNCH(ctx, k_qs_flag, grid_for(nAct, T), T, 0, L);
+                    exclusive_scan_u64(ctx, qflags.p, qscan.p, nAct, nullptr);
+                    VR_LAUNCH(ctx, k_qs_scatter, grid_for(nAct, T), T, 0, L);
+                    VR_LAUNCH(ctx, k_qs_match, grid_for(nAct, T), T, 0, L);
+                    VR_LAUNCH(ctx, k_qs_end, grid_for(nF, T), T, 0, L);
+                }
+            } else {
+                VR_LAUNCH(ctx, k_pt_level_keys, grid_for(nAct, T), T, 0, perm.p, fidx.p, splitflag.p, splitdim.p, rank.p, nL, nAct, rb, keys.p);
+                radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nAct, rb + bits_for_u64v(nF > 1 ? nF - 1 : 1));
+            }
             VR_LAUNCH(ctx, k_pt_children, grid_for(nF, T), T, 0, fr, nF, splitflag.p, fexcl.p, nnodes, nstart.p, nend.p, nleft.p, fr2);
             nnodes += 2 * nsplit;
             nF += nsplit;
