@@ -2,7 +2,7 @@
 //
 // Test infrastructure.  The per-thread functions of qsel.cuh are compiled here by g++ and run once per "thread" in a
 // chosen order (forward, reverse or shuffled: the result must not depend on the schedule inside a launch); the steps
-// around them (frontier, heads -> frontier index, min / max -> split dimension, children) are plain host restatements of
+// around them (frontier, min / max -> split dimension, the two scans of a round, children) are plain host restatements of
 // the level loop in ptree.cu (potential_tree).  Input: several groups back to back (group g = positions
 // [goff[g], goff[g+1])), each a root node.  Output: the final arrangement (tree position -> input index) and every
 // node's [start, end), which tests/test_qsel_host.py compares with the oracle's BuildNodes restatement group by group.
@@ -33,12 +33,12 @@ struct Order {
 
 // small_limit: nodes of at most this many particles take select_serial (QS_SMALL on the device; the tests also pass 0 and
 // a few particles so that both paths see every size).  stats_out: [0] levels, [1] rounds, [2] nodes, [3] serial selections,
-// [4] largest number of rounds in one level.  Returns the number of nodes, or < 0 on error.
+// [4] largest number of rounds in one level, [5] work items over all rounds.  Returns the number of nodes, or < 0 on error.
 extern "C" long long qsel_emul(const double *pos, long long n, const long long *goff, long long ngroups, int bucket, int order_mode,
                                unsigned seed, unsigned small_limit, long long *perm_out, long long *node_out, long long node_cap,
                                long long *stats_out)
 {
-    for (int k = 0; k < 5; k++) stats_out[k] = 0;
+    for (int k = 0; k < 6; k++) stats_out[k] = 0;
     if (n <= 0 || ngroups <= 0) return 0;
     if (n >= 0x7fffffffll) return -1;
     std::mt19937_64 rng(seed);
@@ -55,14 +55,11 @@ extern "C" long long qsel_emul(const double *pos, long long n, const long long *
         nleft.push_back(0xffffffffu);
         frontier.push_back((uint32_t)g);
     }
-    std::vector<uint32_t> fidx(nL), A(nL), B(nL);
-    std::vector<unsigned long long> flags(nL), scan(nL);
+    std::vector<uint32_t> A(nL + 1), B(nL + 1), wf(nL + 1);
+    std::vector<unsigned long long> flags(nL + 1), scan(nL + 1);
 
     for (int level = 0; level < 64; level++) {
         const uint32_t nF = (uint32_t)frontier.size();
-        // heads -> frontier index of every position (k_pt_heads, scan, k_pt_fidx)
-        for (uint32_t f = 0; f < nF; f++)
-            for (uint32_t p = nstart[frontier[f]]; p < nend[frontier[f]]; p++) fidx[p] = f;
         // min / max -> split flag and dimension (k_pt_minmax, k_pt_choose)
         std::vector<uint32_t> splitflag(nF), splitdim(nF);
         uint32_t nsplit = 0;
@@ -85,12 +82,11 @@ extern "C" long long qsel_emul(const double *pos, long long n, const long long *
         stats_out[0]++;
 
         // ---- the selection (potential_tree, exact_ties branch) ----
-        std::vector<uint32_t> lo(nF), hi(nF), npair(nF);
+        std::vector<uint32_t> lo(nF), hi(nF), npair(nF), len(nF), woff(nF);
         std::vector<double> pivot(nF);
-        unsigned int nactive = 0;
-        Level L{x.data(), y.data(), z.data(), slot_of.data(), perm.data(), fidx.data(), frontier.data(), nstart.data(), nend.data(),
-                splitflag.data(), splitdim.data(), lo.data(), hi.data(), npair.data(), pivot.data(), flags.data(), scan.data(),
-                A.data(), B.data(), &nactive, nF, nL};
+        Level L{x.data(), y.data(), z.data(), slot_of.data(), perm.data(), frontier.data(), nstart.data(), nend.data(), splitflag.data(),
+                splitdim.data(), lo.data(), hi.data(), npair.data(), len.data(), woff.data(), pivot.data(), wf.data(), flags.data(),
+                scan.data(), A.data(), B.data(), nF, 0u};
         // init_thread uses the compile-time QS_SMALL; the emulation takes the limit as a parameter instead
         for (uint32_t f : Order(nF, order_mode, rng).idx) {
             const uint32_t s = nstart[frontier[f]], e = nend[frontier[f]];
@@ -101,7 +97,7 @@ extern "C" long long qsel_emul(const double *pos, long long n, const long long *
             } else {
                 lo[f] = big ? s : 0u;
                 hi[f] = big ? e : 0u;
-                if (big && running(s, e)) nactive++;
+                len[f] = big && running(s, e) ? e - s - 1u : 0u;
             }
         }
         // k_qs_small
@@ -118,15 +114,19 @@ extern "C" long long qsel_emul(const double *pos, long long n, const long long *
             stats_out[3]++;
         }
         long long rounds = 0;
-        while (nactive) {
-            nactive = 0;
+        for (;;) {
+            uint32_t run = 0;
+            for (uint32_t f = 0; f < nF; f++) { woff[f] = run; run += len[f]; }
+            L.W = run;
+            if (L.W == 0) break;
             rounds++;
+            stats_out[5] += L.W;
             for (uint32_t f : Order(nF, order_mode, rng).idx) begin_thread(L, f);
-            for (uint32_t p : Order(nL, order_mode, rng).idx) flag_thread(L, p);
-            unsigned long long run = 0;
-            for (uint32_t p = 0; p < nL; p++) { scan[p] = run; run += flags[p]; }
-            for (uint32_t p : Order(nL, order_mode, rng).idx) scatter_thread(L, p);
-            for (uint32_t p : Order(nL, order_mode, rng).idx) match_thread(L, p);
+            for (uint32_t w : Order(L.W + 1, order_mode, rng).idx) flag_thread(L, w);
+            unsigned long long acc = 0;
+            for (uint32_t w = 0; w <= L.W; w++) { scan[w] = acc; acc += flags[w]; }
+            for (uint32_t w : Order(L.W, order_mode, rng).idx) scatter_thread(L, w);
+            for (uint32_t w : Order(L.W, order_mode, rng).idx) match_thread(L, w);
             for (uint32_t f : Order(nF, order_mode, rng).idx) end_thread(L, f);
             if (rounds > 100000) return -3;
         }

@@ -31,7 +31,7 @@ def emul(tmp_path_factory):
         perm = np.zeros(n, dtype=np.int64)
         cap = 4 * n // max(1, bucket) + 64 + len(goff)
         nodes = np.zeros((cap, 2), dtype=np.int64)
-        stats = np.zeros(5, dtype=np.int64)
+        stats = np.zeros(6, dtype=np.int64)
         nn = lib.qsel_emul(pos.ctypes.data_as(pd), n, goff.ctypes.data_as(pll), len(goff) - 1, bucket, order_mode, seed, small_limit,
                            perm.ctypes.data_as(pll), nodes.ctypes.data_as(pll), cap, stats.ctypes.data_as(pll))
         assert nn >= 0, f"emulation failed with {nn}"
@@ -105,6 +105,7 @@ def test_distinct_coordinates(emul, oracle):
     pos = rng.random((20000, 3)) * 100.0
     stats = _check(emul, oracle, pos, [0, 12000, 20000], order_mode=2, seed=2)
     assert stats[4] < 200                    # rounds per level stay logarithmic
+    assert stats[5] < 6 * 20000 * 4          # work items: a few n per level with nodes above QS_SMALL (4 such levels), not rounds x n
 
 
 def test_random_small_inputs(emul, oracle):

@@ -219,18 +219,18 @@ __global__ void k_qs_begin(qsel::Level L)
 }
 __global__ void k_qs_flag(qsel::Level L)
 {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p < L.nAct) qsel::flag_thread(L, p);
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < L.W + 1u) qsel::flag_thread(L, w);
 }
 __global__ void k_qs_scatter(qsel::Level L)
 {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p < L.nAct) qsel::scatter_thread(L, p);
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < L.W) qsel::scatter_thread(L, w);
 }
 __global__ void k_qs_match(qsel::Level L)
 {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p < L.nAct) qsel::match_thread(L, p);
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < L.W) qsel::match_thread(L, w);
 }
 __global__ void k_qs_end(qsel::Level L)
 {
@@ -509,11 +509,11 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL), fidx(ctx, nL), rootidx(ctx, nL);
     DBuf<unsigned long long> mm(ctx, 6 * cap);
     // selection state of the exact-ties variant
-    DBuf<uint32_t> qlo(ctx, exact_ties ? cap : 1), qhi(ctx, exact_ties ? cap : 1), qnp(ctx, exact_ties ? cap : 1);
-    DBuf<double> qpiv(ctx, exact_ties ? cap : 1);
-    DBuf<unsigned long long> qflags(ctx, exact_ties ? nL : 1), qscan(ctx, exact_ties ? nL : 1);
-    DBuf<uint32_t> qA(ctx, exact_ties ? nL : 1), qB(ctx, exact_ties ? nL : 1);
-    DBuf<unsigned int> qact(ctx, 1);
+    const size_t qcap = exact_ties ? cap : 1, qn = exact_ties ? (size_t)nL + 1 : 1;
+    DBuf<uint32_t> qlo(ctx, qcap), qhi(ctx, qcap), qnp(ctx, qcap), qlen(ctx, qcap), qwoff(ctx, qcap), qtotal(ctx, 1);
+    DBuf<double> qpiv(ctx, qcap);
+    DBuf<unsigned long long> qflags(ctx, qn), qscan(ctx, qn);
+    DBuf<uint32_t> qwf(ctx, qn), qA(ctx, qn), qB(ctx, qn);
     VR_LAUNCH(ctx, k_pt_roots, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, gflag.p, gexcl.p, sexcl.p, NG, ntot, nstart.p, nend.p, nleft.p, frontier.p);
     VR_LAUNCH(ctx, k_pt_iota, grid_for(nL, T), T, 0, perm.p, nL);
     uint32_t nF = nLG, nnodes = nLG;
@@ -557,22 +557,20 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             if (nsplit == 0) break;
             VR_REQUIRE((size_t)nnodes + 2 * (size_t)nsplit <= cap, VRGPU_ECUDA, "kd-tree node capacity exceeded");
             if (exact_ties) {
-                qsel::Level L{gs.x.p, gs.y.p, gs.z.p, slot_of.p, perm.p, fidx.p, fr, nstart.p, nend.p, splitflag.p, splitdim.p,
-                              qlo.p, qhi.p, qnp.p, qpiv.p, qflags.p, qscan.p, qA.p, qB.p, qact.p, nF, nAct};
-                VR_CUDA(cudaMemsetAsync(qact.p, 0, sizeof(unsigned int), ctx->stream));
+                qsel::Level L{gs.x.p, gs.y.p, gs.z.p, slot_of.p, perm.p, fr, nstart.p, nend.p, splitflag.p, splitdim.p, qlo.p, qhi.p,
+                              qnp.p, qlen.p, qwoff.p, qpiv.p, qwf.p, qflags.p, qscan.p, qA.p, qB.p, nF, 0u};
                 VR_LAUNCH(ctx, k_qs_init, grid_for(nF, T), T, 0, L);
                 VR_LAUNCH(ctx, k_qs_small, (unsigned)std::min<size_t>(nF, (size_t)148 * 64), QS_SMALL_THREADS, QS_SMALL_SMEM, L);
                 for (;;) { // one iteration of MedianPos for every node above QS_SMALL that is not finished
-                    unsigned int nrun = 0;
-                    VR_CUDA(cudaMemcpyAsync(&nrun, qact.p, sizeof(nrun), cudaMemcpyDeviceToHost, ctx->stream));
+                    exclusive_scan_u32(ctx, qlen.p, qwoff.p, nF, qtotal.p);
+                    VR_CUDA(cudaMemcpyAsync(&L.W, qtotal.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
                     VR_CUDA(cudaStreamSynchronize(ctx->stream));
-                    if (nrun == 0) break;
-                    VR_CUDA(cudaMemsetAsync(qact.p, 0, sizeof(unsigned int), ctx->stream));
+                    if (L.W == 0) break;
                     VR_LAUNCH(ctx, k_qs_begin, grid_for(nF, T), T, 0, L);
-                    VR_LAUNCH(ctx, k_qs_flag, grid_for(nAct, T), T, 0, L);
-                    exclusive_scan_u64(ctx, qflags.p, qscan.p, nAct, nullptr);
-                    VR_LAUNCH(ctx, k_qs_scatter, grid_for(nAct, T), T, 0, L);
-                    VR_LAUNCH(ctx, k_qs_match, grid_for(nAct, T), T, 0, L);
+                    VR_LAUNCH(ctx, k_qs_flag, grid_for((size_t)L.W + 1, T), T, 0, L);
+                    exclusive_scan_u64(ctx, qflags.p, qscan.p, (size_t)L.W + 1, nullptr);
+                    VR_LAUNCH(ctx, k_qs_scatter, grid_for(L.W, T), T, 0, L);
+                    VR_LAUNCH(ctx, k_qs_match, grid_for(L.W, T), T, 0, L);
                     VR_LAUNCH(ctx, k_qs_end, grid_for(nF, T), T, 0, L);
                 }
             } else {

@@ -20,9 +20,12 @@
 // transcription of MedianPos; tests/host/qsel_emul.cpp runs the per-thread functions below (the same source the kernels
 // of ptree.cu call) level by level and compares the whole arrangement with the oracle's tree.
 //
-// All splitting nodes of a level above QS_SMALL particles advance together, one "round" = one iteration of each (five
-// launches and one 64-bit scan; the ranks inside A and B come from an exclusive scan of the packed flags).  Nodes of at
-// most QS_SMALL particles are selected by one thread each on a copy in shared memory (select_serial: the literal loop).
+// All splitting nodes of a level above QS_SMALL particles advance together, one "round" = one iteration of each.  The work
+// items of a round are the scanned positions of the selections that still run, laid back to back (an exclusive scan of the
+// remaining lengths gives every selection its first item and the host the launch size), so a round costs what MedianPos
+// itself touches -- about 3.4 n per node over all rounds -- and not rounds x n.  Five launches and two scans per round;
+// the ranks inside A and B come from one exclusive scan of the packed 64-bit flags.  Nodes of at most QS_SMALL particles
+// are selected by one thread each on a copy in shared memory (select_serial: the literal loop).
 #pragma once
 #include <stdint.h>
 
@@ -41,24 +44,20 @@ struct Level {
     const double *x, *y, *z;      // group-major columns
     const uint32_t *slot_of;      // compact member index -> slot in the columns
     uint32_t *perm;               // tree position -> compact member index (rearranged in place)
-    const uint32_t *fidx;         // tree position -> frontier index (positions < nAct)
     const uint32_t *frontier;     // frontier index -> node
     const uint32_t *nstart, *nend;
     const uint32_t *splitflag, *splitdim;
     uint32_t *lo, *hi, *npair;    // per frontier entry: remaining range [lo, hi) of the selection, M of the round
+    uint32_t *len;                // per frontier entry: positions scanned in the coming round (hi - lo - 1, 0 when finished)
+    const uint32_t *woff;         // exclusive scan of len: the entry's first work item
     double *pivot;                // per frontier entry: x of the round
-    unsigned long long *flags;    // per position: (value >= x) | (value <= x) << 32
-    const unsigned long long *scan; // exclusive scan of flags
-    uint32_t *A, *B;              // per node, stored from position lo
-    unsigned int *nactive;        // selections that need another round
-    uint32_t nF, nAct;
+    // per work item w (the work items of a round are the scanned positions of all running selections, back to back)
+    uint32_t *wf;                 // frontier entry of the item
+    unsigned long long *flags;    // (value >= x) | (value <= x) << 32; W + 1 entries, the last one zero
+    const unsigned long long *scan; // exclusive scan of flags (W + 1 entries: scan[W] = totals)
+    uint32_t *A, *B;              // per entry, stored from work item woff[f]
+    uint32_t nF, W;
 };
-
-#if defined(__CUDACC__)
-QS_HD void count_active(unsigned int *c) { atomicAdd(c, 1u); }
-#else
-QS_HD void count_active(unsigned int *c) { (*c)++; }
-#endif
 
 QS_HD double coord(const Level &L, uint32_t d, uint32_t member)
 {
@@ -70,6 +69,18 @@ QS_HD bool running(uint32_t lo, uint32_t hi) { return lo + 1u < hi; } // MedianP
 QS_HD uint32_t lo32(unsigned long long v) { return (uint32_t)(v & 0xffffffffull); }
 QS_HD uint32_t hi32(unsigned long long v) { return (uint32_t)(v >> 32); }
 
+// the last entry f with woff[f] <= w: entries without work share their offset with the next one, so this is the entry
+// that owns work item w (w < W, woff[0] == 0)
+QS_HD uint32_t find_entry(const uint32_t *woff, uint32_t nF, uint32_t w)
+{
+    uint32_t a = 0u, b = nF;
+    while (b - a > 1u) {
+        const uint32_t m = a + (b - a) / 2u;
+        if (woff[m] <= w) a = m; else b = m;
+    }
+    return a;
+}
+
 // ---- per frontier entry: start of a level ------------------------------------------------------------------------
 QS_HD void init_thread(const Level &L, uint32_t f)
 {
@@ -78,7 +89,7 @@ QS_HD void init_thread(const Level &L, uint32_t f)
     const bool big = L.splitflag[f] && e - s > QS_SMALL;
     L.lo[f] = big ? s : 0u;
     L.hi[f] = big ? e : 0u;
-    if (big && running(s, e)) count_active(L.nactive);
+    L.len[f] = big && running(s, e) ? e - s - 1u : 0u;
 }
 
 // ---- per frontier entry: pivot of the round ----------------------------------------------------------------------
@@ -95,47 +106,45 @@ QS_HD void begin_thread(const Level &L, uint32_t f)
     L.npair[f] = 0u;
 }
 
-// ---- per position: where the two scans stop ----------------------------------------------------------------------
-QS_HD void flag_thread(const Level &L, uint32_t p)
+// ---- per work item (W + 1 threads): where the two scans stop -----------------------------------------------------
+QS_HD void flag_thread(const Level &L, uint32_t w)
 {
-    const uint32_t f = L.fidx[p];
-    const uint32_t lo = L.lo[f], hi = L.hi[f];
-    unsigned long long fl = 0ull;
-    if (running(lo, hi) && p >= lo && p < hi - 1u) {
-        const double v = coord(L, L.splitdim[f], L.perm[p]), x = L.pivot[f];
-        fl = (v >= x ? 1ull : 0ull) | (v <= x ? (1ull << 32) : 0ull);
-    }
-    L.flags[p] = fl;
+    if (w >= L.W) { L.flags[w] = 0ull; return; }
+    const uint32_t f = find_entry(L.woff, L.nF, w);
+    const uint32_t p = L.lo[f] + (w - L.woff[f]);
+    const double v = coord(L, L.splitdim[f], L.perm[p]), x = L.pivot[f];
+    L.flags[w] = (v >= x ? 1ull : 0ull) | (v <= x ? (1ull << 32) : 0ull);
+    L.wf[w] = f;
 }
 
-// ---- per position: A and B ---------------------------------------------------------------------------------------
-QS_HD void scatter_thread(const Level &L, uint32_t p)
+// ---- per work item: A and B --------------------------------------------------------------------------------------
+QS_HD void scatter_thread(const Level &L, uint32_t w)
 {
-    const unsigned long long fl = L.flags[p];
+    const unsigned long long fl = L.flags[w];
     if (fl == 0ull) return;
-    const uint32_t f = L.fidx[p];
-    const uint32_t lo = L.lo[f], hi = L.hi[f];
-    const unsigned long long s0 = L.scan[lo], s1 = L.scan[hi - 1u], sp = L.scan[p];
-    if (lo32(fl)) L.A[lo + (lo32(sp) - lo32(s0))] = p;
-    if (hi32(fl)) L.B[lo + ((hi32(s1) - hi32(s0)) - 1u - (hi32(sp) - hi32(s0)))] = p;
+    const uint32_t f = L.wf[w];
+    const uint32_t base = L.woff[f];
+    const uint32_t p = L.lo[f] + (w - base);
+    const unsigned long long s0 = L.scan[base], s1 = L.scan[base + L.len[f]], sw = L.scan[w];
+    if (lo32(fl)) L.A[base + (lo32(sw) - lo32(s0))] = p;
+    if (hi32(fl)) L.B[base + ((hi32(s1) - hi32(s0)) - 1u - (hi32(sw) - hi32(s0)))] = p;
 }
 
-// ---- per position, read as pair number m = p - lo: the swaps -----------------------------------------------------
-QS_HD void match_thread(const Level &L, uint32_t p)
+// ---- per work item, read as pair number m = w - woff[f]: the swaps -----------------------------------------------
+QS_HD void match_thread(const Level &L, uint32_t w)
 {
-    const uint32_t f = L.fidx[p];
-    const uint32_t lo = L.lo[f], hi = L.hi[f];
-    if (!running(lo, hi) || p < lo || p >= hi - 1u) return;
-    const unsigned long long s0 = L.scan[lo], s1 = L.scan[hi - 1u];
+    const uint32_t f = L.wf[w];
+    const uint32_t base = L.woff[f];
+    const unsigned long long s0 = L.scan[base], s1 = L.scan[base + L.len[f]];
     const uint32_t nA = lo32(s1) - lo32(s0), nB = hi32(s1) - hi32(s0);
-    const uint32_t mm = nA < nB ? nA : nB, m = p - lo;
+    const uint32_t mm = nA < nB ? nA : nB, m = w - base;
     if (m >= mm) return;
-    const uint32_t a = L.A[p], b = L.B[p];
+    const uint32_t a = L.A[w], b = L.B[w];
     if (!(a < b)) return;
     const uint32_t pa = L.perm[a], pb = L.perm[b];
     L.perm[a] = pb;
     L.perm[b] = pa;
-    if (m + 1u == mm || !(L.A[p + 1u] < L.B[p + 1u])) L.npair[f] = m + 1u;
+    if (m + 1u == mm || !(L.A[w + 1u] < L.B[w + 1u])) L.npair[f] = m + 1u;
 }
 
 // ---- per frontier entry: the pivot goes to its place, the range shrinks ------------------------------------------
@@ -145,12 +154,13 @@ QS_HD void end_thread(const Level &L, uint32_t f)
     if (!running(lo, hi)) return;
     const uint32_t nd = L.frontier[f];
     const uint32_t k = median_index(L.nstart[nd], L.nend[nd]);
-    const unsigned long long s0 = L.scan[lo], s1 = L.scan[hi - 1u];
+    const uint32_t base = L.woff[f];
+    const unsigned long long s0 = L.scan[base], s1 = L.scan[base + L.len[f]];
     const uint32_t nA = lo32(s1) - lo32(s0);
     const uint32_t M = L.npair[f];
     uint32_t istar;
-    if (M < nA && (M == 0u || L.A[lo + M] < L.B[lo + M - 1u])) istar = L.A[lo + M];
-    else if (M > 0u) istar = L.B[lo + M - 1u];
+    if (M < nA && (M == 0u || L.A[base + M] < L.B[base + M - 1u])) istar = L.A[base + M];
+    else if (M > 0u) istar = L.B[base + M - 1u];
     else istar = hi - 1u;
     const uint32_t pv = L.perm[hi - 1u], pi = L.perm[istar];
     L.perm[hi - 1u] = pi;
@@ -160,7 +170,7 @@ QS_HD void end_thread(const Level &L, uint32_t f)
     if (istar <= k) nlo = istar + 1u;
     L.lo[f] = nlo;
     L.hi[f] = nhi;
-    if (running(nlo, nhi)) count_active(L.nactive);
+    L.len[f] = running(nlo, nhi) ? nhi - nlo - 1u : 0u;
 }
 
 // ---- small nodes: MedianPos itself on (value, member) pairs of one node, k relative to the node's start -----------
