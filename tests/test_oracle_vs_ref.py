@@ -170,6 +170,30 @@ def test_unbind(ref, oracle, nside, seed, unbindtype, bgpot):
     assert all(v["changed"] == want["changed"] for v in variants)
 
 
+def test_search_full_set_with_unbinding_keeps_member_order(ref, oracle):
+    """SearchFullSet with Bound_halos=1 on a float32-exact box (kd-tree medians tie): the oracle stages chained the way the
+    library chains them (3DFOF -> AdjustStructureForPeriod -> CheckUnboundGroups, group members in index order) give the
+    reference's bound sets EXACTLY when oldnumingroup is carried from group to group as the serial build does (Q10), so
+    the member order handed to Potential() -- which decides the arrangement at tied medians -- is the reference's.  The
+    intended-semantics variant (what the GPU implements) differs on a handful of particles: that difference is Q10's, not
+    the tree's."""
+    import vroracle
+    nside = 40
+    d = vrsynth.make_box(nside ** 3, 31)
+    o = vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, fofbgtype=5, bound_halos=1, omp_fof=0)
+    want = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], o)
+    cw, _ = vrsynth.canonical_groups(want["pfof"], d["pid"])
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    assert int(np.sum(np.bincount(pf)[1:] > 150)) > 20            # plenty of groups take the tree
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    carried = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=1, oldn_init=0), d["pid"], 1e-6)
+    assert carried["ngroups"] == want["ngroups"] and np.array_equal(carried["pfof"], cw)
+    intended = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=0), d["pid"], 1e-6)
+    nd = int(np.count_nonzero((intended["pfof"] > 0) != (cw > 0)))
+    assert 0 < nd <= 0.002 * np.count_nonzero(cw > 0)
+
+
 def test_single_halo_search_full_set(ref, oracle):
     """Zoom-style input (BASELINE.json configs[4], scaled down): one 3D group; adaptive 6DFOF splits it in phase space and the
     large-group branch of Unbind (n > ompunbindnum, tree potential) does the removal."""
