@@ -11,6 +11,7 @@
  *   vrref_sort_by_binding_energy -> SortAccordingtoBindingEnergy   (src/substructureproperties.cxx:4256)
  *   vrref_build_pglist     -> BuildNumInGroup + BuildPGList        (src/buildandsortarrays.cxx:11, 26)
  *   vrref_fofcriterion6d   -> NBody::KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) (NBodylib/src/KDTree/KDFOF.cxx:133)
+ *   vrref_velocity_density -> GetVelocityDensity                   (src/localfield.cxx:18; row f4, oracle side only)
  *
  * It is compiled against the reference headers where they lie and linked with the reference's own
  * objects into oracle/_ref/libvrref*.so (see oracle/Makefile).  Nothing here re-implements the
@@ -223,6 +224,41 @@ long long vrref_search_full_set(long long n, double *pos, double *vel, const dou
     }
     delete[] pfof;
     return ng;
+}
+
+/* GetVelocityDensity (localfield.cxx:18) with tree == NULL, as SearchSubSub calls it for the particles of one structure
+ * (search.cxx:2646): the routine builds its own physical tree (bucket Options::Bsize, Epanechnikov kernel table of 1000
+ * entries, period Options::p) and deletes it again, which restores the input order.  approx = Options::
+ * iLocalVelDenApproxCalcFlag (1, the default: one neighbour search per leaf node; 0: one per particle).  type (may be NULL)
+ * sets Particle::type -- this build defines STRUCDEN, so particles of type 0 get no density.  den_out in input order. */
+void vrref_velocity_density(long long n, const double *pos, const double *vel, const int *type, double period, int bsize,
+                            int nsearch, int nvel, int approx, double *den_out)
+{
+    Options opt;
+    opt.p = period;
+    opt.Bsize = bsize;
+    opt.Nsearch = nsearch;
+    opt.Nvel = nvel;
+    opt.iLocalVelDenApproxCalcFlag = approx;
+    opt.iBaryonSearch = 0;
+    opt.partsearchtype = PSTALL;
+    opt.iverbose = 0;
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, NULL, NULL);
+    if (type) for (long long i = 0; i < n; i++) P[i].SetType(type[i]);
+    stringstream sink;
+    streambuf *old = cout.rdbuf(sink.rdbuf());
+    if (approx) GetVelocityDensity(opt, n, P.data(), NULL);
+    else {
+        /* GetVelocityDensityExact never builds a tree itself (it dereferences the NULL pointer): hand it one, as
+         * SearchFullSet does with its FOF tree (search.cxx:232), built the way the approximative routine would */
+        Double_t per[3] = {period, period, period};
+        KDTree *tree = new KDTree(P.data(), n, bsize, tree->TPHYS, tree->KEPAN, 1000, 0, 0, 0, period > 0 ? per : NULL);
+        GetVelocityDensity(opt, n, P.data(), tree);
+        delete tree;
+    }
+    cout.rdbuf(old);
+    for (long long i = 0; i < n; i++) den_out[P[i].GetID()] = P[i].GetDensity();
 }
 
 /* Tree potential of one group (Potential(), unbind.cxx:1607).  phi_out in input order. */

@@ -18,6 +18,9 @@
 typedef long long i64;
 
 #define NCMAX 320
+#ifndef M_1_PI
+#define M_1_PI 0.31830988618379067154 /* 1/pi, as <math.h> defines it outside strict C11 */
+#endif
 
 /* ------------------------------------------------------------------------------------------------ */
 /* union-find                                                                                       */
@@ -567,6 +570,202 @@ long long vro_tree_order(long long n, const double *pos, int bucket, long long *
     i64 nn = t.nnodes;
     free(t.nodes);
     return nn;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Row f4, oracle side: GetVelocityDensity (localfield.cxx:18) as SearchSubSub calls it for one
+ * structure (tree == NULL): a physical kd-tree with bucket Options::Bsize and the Epanechnikov kernel table of 1000
+ * entries (localfield.cxx:765, KDTree.cxx:592-631), then
+ *   approx = 1 (GetVelocityDensityApproximative, localfield.cxx:726-897, the default): per LEAF of that tree the centre
+ *     of its typed particles, the Nsearch nearest particles of that centre, and for every typed particle of the leaf the
+ *     Nvel nearest of those in velocity (itself excluded);
+ *   approx = 0 (GetVelocityDensityExact, localfield.cxx:485-586): the Nsearch nearest particles of every typed particle
+ *     (itself excluded) and the Nvel nearest of those in velocity;
+ * and KDTree::CalcSmoothLocalValue (KDCalcSmoothQuantities.cxx:1704-1719) on the velocity distances, largest first.
+ * Neighbour sets are taken as the Nsearch smallest squared distances (the reference's tree search returns the same set
+ * unless the Nsearch-th and (Nsearch+1)-th distances are exactly equal), periodic domains through the reference's own
+ * sequence of reflected searches (nearest_pos).
+ * ------------------------------------------------------------------------------------------------------------------- */
+typedef struct { double d2; i64 id; } nnrec;
+static int cmp_nnrec(const void *a, const void *b)
+{
+    const nnrec *x = (const nnrec *)a, *y = (const nnrec *)b;
+    if (x->d2 < y->d2) return -1;
+    if (x->d2 > y->d2) return 1;
+    return (x->id > y->id) - (x->id < y->id);
+}
+static int cmp_dbl_desc(const void *a, const void *b)
+{
+    double x = *(const double *)a, y = *(const double *)b;
+    return (x < y) - (x > y);
+}
+/* the K smallest records (by distance, then id) to the front of a[0..m), in order */
+static void smallest_first(nnrec *a, i64 m, i64 K)
+{
+    if (K >= m) { qsort(a, (size_t)m, sizeof(nnrec), cmp_nnrec); return; }
+    i64 lo = 0, hi = m - 1;
+    while (lo < hi) { /* quickselect for position K - 1 */
+        nnrec pv = a[lo + (hi - lo) / 2];
+        i64 i = lo, j = hi;
+        while (i <= j) {
+            while (cmp_nnrec(&a[i], &pv) < 0) i++;
+            while (cmp_nnrec(&a[j], &pv) > 0) j--;
+            if (i <= j) { nnrec w = a[i]; a[i] = a[j]; a[j] = w; i++; j--; }
+        }
+        if (K - 1 <= j) hi = j;
+        else if (K - 1 >= i) lo = i;
+        else break;
+    }
+    qsort(a, (size_t)K, sizeof(nnrec), cmp_nnrec);
+}
+/* offer the squared distances of all particles to the point q to the list of the K smallest (work[0..K) sorted,
+ * work[K..K+n) scratch) -- what one tree search does to the reference's priority queue */
+static void offer_all(i64 n, const double *tp, const double *q, i64 K, nnrec *work)
+{
+    for (i64 i = 0; i < n; i++) {
+        double d2 = 0;
+        for (int k = 0; k < 3; k++) d2 += (q[k] - tp[3 * i + k]) * (q[k] - tp[3 * i + k]);
+        work[K + i].d2 = d2;
+        work[K + i].id = i;
+    }
+    smallest_first(work, K + n, K);
+}
+/* the nsearch nearest particles (tree order ids, -1 = none) of position c.
+ * Open domain, target < 0: KDTree::FindNearestPos (KDFindNearest.cxx:559-571).  Open domain, target >= 0: KDTree::
+ * FindNearest(target, ...) (:289-340), which leaves out the target and every particle at distance exactly zero
+ * (KDLeafNode.cxx:19-21).
+ * Periodic domain: SplitNode::FindNearestPosPeriodic (KDSplitNode.cxx:1008-1040) searches from the point itself and then
+ * from up to seven reflected points, each search offering every particle to the same queue (so a particle can enter
+ * twice, under two images); a reflection is searched only if the current largest queued distance reaches past the
+ * faces it crosses -- for the one-face reflections sqrt(r2max) > distance, for the two- and three-face ones the test
+ * compares the SQUARED radius with the distance (r2max > sqrt(sum of squared face distances)), reproduced here.  With a
+ * target the queue holds one more entry and the smallest is dropped at the end (KDFindNearest.cxx:292, 356-357). */
+static void nearest_pos(i64 n, const double *tp, const double *c, double period, i64 nsearch, nnrec *work, i64 *ids, i64 target)
+{
+    if (!(period > 0)) {
+        i64 m = 0;
+        for (i64 i = 0; i < n; i++) {
+            if (i == target) continue;
+            double d2 = 0;
+            for (int k = 0; k < 3; k++) d2 += (c[k] - tp[3 * i + k]) * (c[k] - tp[3 * i + k]);
+            if (target >= 0 && !(d2 > 0)) continue;
+            work[m].d2 = d2;
+            work[m].id = i;
+            m++;
+        }
+        smallest_first(work, m, nsearch);
+        for (i64 k = 0; k < nsearch; k++) ids[k] = k < m ? work[k].id : -1;
+        return;
+    }
+    const i64 K = nsearch + (target >= 0 ? 1 : 0);
+    for (i64 k = 0; k < K; k++) { work[k].d2 = 1e32; work[k].id = -1; } /* MAXVALUE, Precision.h:39 */
+    offer_all(n, tp, c, K, work);
+    double xp[3], sval;
+    for (int k = 0; k < 3; k++) {                                  /* PeriodicReflection1D, DistFunc.h:326-332 */
+        for (int j = 0; j < 3; j++) xp[j] = c[j];
+        if (c[k] < period / 2.0) { xp[k] = c[k] + period; sval = c[k]; }
+        else { xp[k] = c[k] - period; sval = -xp[k]; }
+        if (sqrt(work[K - 1].d2) > sval) offer_all(n, tp, xp, K, work);
+    }
+    static const int pairs[3][2] = {{0, 1}, {0, 2}, {1, 2}};
+    for (int q = 0; q <= 3; q++) {                                 /* PeriodicReflection2D x3, then ND (:338-355) */
+        for (int j = 0; j < 3; j++) xp[j] = c[j];
+        sval = 0;
+        for (int a = 0; a < (q < 3 ? 2 : 3); a++) {
+            const int k = q < 3 ? pairs[q][a] : a;
+            if (c[k] < period / 2.0) { xp[k] = c[k] + period; sval += c[k] * c[k]; }
+            else { xp[k] = c[k] - period; sval += xp[k] * xp[k]; }
+        }
+        sval = sqrt(sval);
+        if (work[K - 1].d2 > sval) offer_all(n, tp, xp, K, work);
+    }
+    for (i64 k = 0; k < nsearch; k++) ids[k] = work[k + (K - nsearch)].id;
+}
+/* CalcSmoothLocalValue on nvel squared distances sorted largest first, unit weights, ND = 3 */
+static double smooth_local_value(const double *v2desc, i64 nvel, const double *kernel, int kernres)
+{
+    double hi = 0.5 * sqrt(v2desc[0]);
+    double norm = 1.0 / pow(hi, 3.0);
+    double delta = 2.0 / (double)(kernres - 1);
+    double value = 0;
+    for (i64 j = 0; j < nvel; j++) {
+        double rij = sqrt(v2desc[j]);
+        double r = rij / hi;
+        i64 i = (i64)(rij / hi * 0.5 * (kernres - 1));
+        double w = i < kernres - 1 ? kernel[i] + (kernel[i + 1] - kernel[i]) * (r - delta * i) / delta : kernel[i];
+        value += w * norm * 1.0;
+    }
+    return value;
+}
+long long vro_velocity_density(long long n, const double *pos, const double *vel, const int *type, double period, int bsize,
+                               int nsearch, int nvel, int approx, double *den_out)
+{
+    for (i64 i = 0; i < n; i++) den_out[i] = 0.;
+    if (n <= 0) return 0;
+    if (nsearch > n - 1 || nvel > nsearch - 1) return -1;
+    /* kernel table: KDTree::KernelConstruction, ND = 3, KEPAN, kernres = 1000 */
+    const int kernres = 1000;
+    double *kernel = (double *)malloc(sizeof(double) * kernres);
+    {
+        const int ND = 3;
+        double kernnorm = 1.0 / ND * pow(M_1_PI, ND / 2.) * tgamma(ND / 2. + 1.);
+        kernnorm *= ND * (ND + 2.) * pow(0.5, ND + 1.);
+        double delta = 2.0 / (double)(kernres - 1);
+        for (int i = 0; i < kernres; i++) {
+            double rh = i * delta / 1.0 * 0.5;
+            kernel[i] = kernnorm * (rh <= 1.0 ? (1.0 - rh * rh) : 0.);
+        }
+    }
+    tbuild t;
+    t.pos = pos;
+    t.bucket = bsize;
+    t.perm = (i64 *)malloc(sizeof(i64) * (size_t)n);
+    for (i64 i = 0; i < n; i++) t.perm[i] = i;
+    t.cap = 2 * n / (bsize > 0 ? bsize : 1) + 64;
+    t.nodes = (tnode *)malloc(sizeof(tnode) * (size_t)t.cap);
+    t.nnodes = 0;
+    build_nodes(&t, 0, n);
+    double *tp = (double *)malloc(sizeof(double) * 3 * (size_t)n), *tv = (double *)malloc(sizeof(double) * 3 * (size_t)n);
+    int *tt = (int *)malloc(sizeof(int) * (size_t)n);
+    for (i64 i = 0; i < n; i++) {
+        for (int k = 0; k < 3; k++) { tp[3 * i + k] = pos[3 * t.perm[i] + k]; tv[3 * i + k] = vel[3 * t.perm[i] + k]; }
+        tt[i] = type ? type[t.perm[i]] : 1;
+    }
+    nnrec *work = (nnrec *)malloc(sizeof(nnrec) * (size_t)(n + nsearch + 2));
+    i64 *ids = (i64 *)malloc(sizeof(i64) * (size_t)nsearch);
+    double *v2 = (double *)malloc(sizeof(double) * (size_t)nsearch);
+    i64 nleaf = 0;
+    for (i64 nd = 0; nd < t.nnodes; nd++) {
+        if (t.nodes[nd].left >= 0) continue;
+        nleaf++;
+        const i64 s = t.nodes[nd].start, e = t.nodes[nd].end;
+        if (approx) {
+            i64 num = 0;
+            double cm[3] = {0, 0, 0};
+            for (i64 j = s; j < e; j++) if (tt[j] != 0) { num++; for (int k = 0; k < 3; k++) cm[k] += tp[3 * j + k]; }
+            if (num == 0) continue;
+            for (int k = 0; k < 3; k++) cm[k] /= (float)num;
+            nearest_pos(n, tp, cm, period, nsearch, work, ids, -1);
+        }
+        for (i64 j = s; j < e; j++) {
+            if (tt[j] == 0) continue;
+            if (!approx) nearest_pos(n, tp, tp + 3 * j, period, nsearch, work, ids, j);
+            i64 m = 0;
+            for (i64 k = 0; k < nsearch; k++) {
+                i64 id = ids[k];
+                if (id < 0 || (approx && id == j)) continue;
+                double d = 0;
+                for (int c = 0; c < 3; c++) d += (tv[3 * j + c] - tv[3 * id + c]) * (tv[3 * j + c] - tv[3 * id + c]);
+                v2[m++] = d;
+            }
+            /* the priority queue keeps the nvel smallest; CalcSmoothLocalValue pops them largest first */
+            qsort(v2, (size_t)m, sizeof(double), cmp_dbl_desc);
+            if (m < nvel) continue; /* fewer usable neighbours than Nvel (coincident particles): left at zero */
+            den_out[t.perm[j]] = smooth_local_value(v2 + (m - nvel), nvel, kernel, kernres);
+        }
+    }
+    free(v2); free(ids); free(work); free(tt); free(tv); free(tp); free(t.nodes); free(t.perm); free(kernel);
+    return nleaf;
 }
 
 void vro_potential_tree(long long n, const double *pos, const double *mass, double G, double eps, double theta,

@@ -70,6 +70,11 @@ void vro_potential_tree(long long n, const double *pos, const double *mass, doub
 /* Tree order and node ranges of the kd-tree vro_potential_tree builds (KDTree.cxx:304-337, 438-507). */
 long long vro_tree_order(long long n, const double *pos, int bucket, long long *perm_out, long long *node_out, long long node_cap);
 
+/* Row f4, oracle side only: GetVelocityDensity (localfield.cxx:18) for one structure, approx = iLocalVelDenApproxCalcFlag.
+ * type may be NULL (all particles typed).  Returns the number of leaf nodes, < 0 if nsearch / nvel do not fit n. */
+long long vro_velocity_density(long long n, const double *pos, const double *vel, const int *type, double period, int bsize,
+                               int nsearch, int nvel, int approx, double *den_out);
+
 /* CheckUnboundGroups + Unbind (unbind.cxx:196-304, 320-729) for fracpotref==1.
  * pfof in/out (0 = unbound), returns the new number of groups, ids re-ordered (size desc, min pid asc) when
  * anything changed.  n_marginal_out (may be NULL): number of grouped particles whose |E| <= tol*|phi| at the

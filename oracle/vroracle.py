@@ -169,6 +169,17 @@ class Ref:
                                             C.byref(sec))
         return {"pfof": out, "ngroups": int(ng), "pos": pos, "vel": vel, "seconds": sec.value}
 
+    def velocity_density(self, pos, vel, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None):
+        """GetVelocityDensity (localfield.cxx:18) with tree == NULL; densities in input order."""
+        pos = _f64(pos); vel = _f64(vel)
+        n = pos.shape[0]
+        den = np.zeros(n)
+        tp = None if ptype is None else np.ascontiguousarray(ptype, dtype=np.int32)
+        self.lib.vrref_velocity_density.restype = None
+        self.lib.vrref_velocity_density(c_ll(n), _pd(pos), _pd(vel), None if tp is None else tp.ctypes.data_as(C.POINTER(C.c_int)),
+                                        c_dbl(period), C.c_int(bsize), C.c_int(nsearch), C.c_int(nvel), C.c_int(approx), _pd(den))
+        return den
+
     def potential(self, pos, mass, opts: RefOpts):
         pos = _f64(pos)
         mass = _f64(mass)
@@ -322,6 +333,19 @@ class Oracle:
         phi = np.zeros(pos.shape[0])
         self.lib.vro_potential_pp(pos.shape[0], _pd(pos), _pd(mass), G, eps, _pd(phi))
         return phi
+
+    def velocity_density(self, pos, vel, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None):
+        """Row f4, oracle side: GetVelocityDensity for one structure; densities in input order."""
+        pos = _f64(pos); vel = _f64(vel)
+        n = pos.shape[0]
+        den = np.zeros(n)
+        tp = None if ptype is None else np.ascontiguousarray(ptype, dtype=np.int32)
+        self.lib.vro_velocity_density.restype = c_ll
+        rc = self.lib.vro_velocity_density(c_ll(n), _pd(pos), _pd(vel), None if tp is None else tp.ctypes.data_as(C.POINTER(C.c_int)),
+                                           c_dbl(period), C.c_int(bsize), C.c_int(nsearch), C.c_int(nvel), C.c_int(approx), _pd(den))
+        if rc < 0:
+            raise ValueError("nsearch / nvel do not fit the particle count")
+        return den
 
     def tree_order(self, pos, bucket=8):
         """(perm, nodes): tree position -> input index, and [start, end) of every node in pre-order."""

@@ -12,6 +12,10 @@ Each file holds the float32-exact inputs and the reference's outputs:
 core/core_s3.npz (SURVEY 8f row f2, linking step): KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) on a halo with two cores in its CM
 frame, three iterations of shrinking linking lengths: inputs pos/vel/pot, per iteration p6, p7, minsize and the canonical ids.
 
+veldens/vd_s9.npz (oracle side): GetVelocityDensity on one structure of 6000 float32-exact particles (a halo with two
+cores; a fifth of the particles of type 0, which STRUCDEN builds skip): densities of the approximative (per-leaf) and of the exact
+(per-particle) neighbour search, Nsearch 256 / Nvel 32 / bucket 16, and of a periodic box with Nsearch 64 / Nvel 8 / bucket 8.
+
 binding/be_s5.npz: GetBindingEnergy on a group-ordered set holding one group above ompunbindnum (tree branch)
 and a handful below (pair loop): inputs pos/vel/mass/num/gcmvel, reference outputs phi, E, T, Pot, Efrac, iminpot, ibound.
 """
@@ -68,6 +72,25 @@ def core_search_case():
     np.savez_compressed(os.path.join(HERE, "core", "core_s3.npz"), **out)
 
 
+def velocity_density_case():
+    ref = vroracle.Ref("serial")
+    n, seed = 6000, 9
+    pos, vel, _ = vrsynth.halo_with_cores(n, seed)
+    pos = pos.astype(np.float32).astype(np.float64); vel = vel.astype(np.float32).astype(np.float64)
+    rng = np.random.default_rng(seed)
+    ptype = (rng.random(n) < 0.8).astype(np.int32)
+    out = dict(pos=pos.astype(np.float32), vel=vel.astype(np.float32), ptype=ptype.astype(np.int8))
+    out["den_approx"] = ref.velocity_density(pos, vel, 0.0, 16, 256, 32, 1, ptype)
+    out["den_exact"] = ref.velocity_density(pos, vel, 0.0, 16, 256, 32, 0, ptype)
+    box = np.mod(pos * 40.0, 100.0).astype(np.float32).astype(np.float64)
+    out["box"] = box.astype(np.float32)
+    out["den_box_approx"] = ref.velocity_density(box, vel, 100.0, 8, 64, 8, 1, None)
+    out["den_box_exact"] = ref.velocity_density(box, vel, 100.0, 8, 64, 8, 0, None)
+    os.makedirs(os.path.join(HERE, "veldens"), exist_ok=True)
+    np.savez_compressed(os.path.join(HERE, "veldens", "vd_s9.npz"), **out)
+    print("vd_s9", "typed", int(ptype.sum()), "median density", float(np.median(out["den_approx"][ptype > 0])))
+
+
 def binding_energy_case():
     ref = vroracle.Ref("serial")
     rng = np.random.default_rng(5)
@@ -96,7 +119,10 @@ def binding_energy_case():
 if __name__ == "__main__":
     if "core" in sys.argv[1:]:
         core_search_case()
+    elif "veldens" in sys.argv[1:]:
+        velocity_density_case()
     else:
         core_search_case()
+        velocity_density_case()
         binding_energy_case()
         main()

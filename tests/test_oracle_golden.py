@@ -107,3 +107,18 @@ def test_oracle_core_search_linking_golden(oracle):
         pf, ng = oracle.fof_criterion6d(pos, vel, pot, float(z[f"p6_{it}"]), float(z[f"p7_{it}"]), float(z["p9"]), int(z["minsize"]), pid)
         assert ng == int(z[f"ng_{it}"])
         assert np.array_equal(pf, z[f"pfof_{it}"].astype(np.int64))
+
+
+def test_oracle_velocity_density_golden(oracle):
+    """SURVEY section 8 row f4, oracle side (GetVelocityDensity, localfield.cxx:18): travelling fixture made from the compiled
+    reference by tests/golden/make_golden.py veldens.  Bit for bit: the restatement builds the reference's own tree (leaf
+    membership follows MedianPos), takes the same neighbour sets and sums the kernel in the same order."""
+    z = np.load(os.path.join(HERE, "golden", "veldens", "vd_s9.npz"))
+    pos, vel, ptype = z["pos"].astype(np.float64), z["vel"].astype(np.float64), z["ptype"].astype(np.int32)
+    for approx, key in ((1, "den_approx"), (0, "den_exact")):
+        den = oracle.velocity_density(pos, vel, 0.0, 16, 256, 32, approx, ptype)
+        assert np.array_equal(den, z[key]), key
+        assert np.all(den[ptype == 0] == 0) and np.all(den[ptype > 0] > 0)
+    box = z["box"].astype(np.float64)
+    for approx, key in ((1, "den_box_approx"), (0, "den_box_exact")):
+        assert np.array_equal(oracle.velocity_density(box, vel, 100.0, 8, 64, 8, approx, None), z[key]), key

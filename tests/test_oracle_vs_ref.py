@@ -328,3 +328,23 @@ def test_build_pglist(ref):
     order = np.argsort(pf, kind="stable")
     assert np.array_equal(num, want_num) and num[7] == 0
     assert np.array_equal(index, order[pf[order] > 0])
+
+
+@pytest.mark.parametrize("approx", [1, 0])
+def test_velocity_density(ref, oracle, approx):
+    """SURVEY section 8 row f4, oracle side: GetVelocityDensity for one structure (localfield.cxx:18; approx = the default
+    per-leaf neighbour search, 0 = per particle).  Open and periodic domain, a type mask, float32-tied coordinates (leaf
+    membership then follows MedianPos' swap history), small Nsearch / Nvel / bucket.  Bit for bit."""
+    rng = np.random.default_rng(5)
+    n = 4000
+    vel = rng.normal(size=(n, 3)) * 100
+    clump = 50 + rng.normal(size=(n, 3)) * 0.5
+    box = np.mod(50 + rng.normal(size=(n, 3)) * 30, 100.0)
+    tied = (50 + rng.normal(size=(n, 3)) * 0.01).astype(np.float32).astype(np.float64)
+    ptype = (rng.random(n) < 0.7).astype(np.int32)
+    for pos, kw in ((clump, {}), (box, dict(period=100.0)), (tied, {}), (box, dict(period=100.0, ptype=ptype)),
+                    (clump, dict(nsearch=64, nvel=8, bsize=8)), (clump[:300], {})):
+        want = ref.velocity_density(pos, vel[:len(pos)], approx=approx, **kw)
+        got = oracle.velocity_density(pos, vel[:len(pos)], approx=approx, **kw)
+        assert np.array_equal(got, want)
+        assert np.count_nonzero(want) == (int(kw["ptype"].sum()) if "ptype" in kw else len(pos))
