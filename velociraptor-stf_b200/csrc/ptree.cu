@@ -20,6 +20,7 @@
 // (the reference's quickselect leaves the choice among exactly equal coordinates to its swap sequence; here the tie
 // goes to the lower member index) -- see DESIGN.md "tree parity".
 #include "groups.cuh"
+#include "ptree.cuh"
 #include "qsel.cuh"
 #include "rsqrt.cuh"
 #include "ufhash.cuh"
@@ -463,13 +464,19 @@ __global__ void k_pt_mm_init(unsigned long long *__restrict__ mm, uint32_t nF)
 }
 } // namespace
 
-void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, double theta, int bucket, long long pp_threshold, double *phi)
+// The build shared by the potentials (below) and the local velocity density (veldens.cu): members of the groups above
+// pp_threshold in tree order (t.perm over compact member indices, t.slot_of to the group-major columns) and the nodes over
+// them, numbered level by level (right child = left + 1).  False when no group qualifies.
+bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_threshold, bool exact_ties, PtTree &t)
 {
-    if (gs.ntot == 0 || gs.ngroups == 0 || pp_threshold < 0) return;
+    t.nL = t.nLG = t.nnodes = 0;
+    t.level_off.clear();
+    if (gs.ntot == 0 || gs.ngroups == 0 || pp_threshold < 0) return false;
     VR_REQUIRE(bucket >= 1, VRGPU_EINVAL, "BucketSize must be >= 1");
-    VR_REQUIRE(theta > 0, VRGPU_EINVAL, "TreeThetaOpen must be positive");
     const int T = 256;
     const uint32_t ntot = (uint32_t)gs.ntot, NG = (uint32_t)gs.ngroups;
+    DBuf<uint32_t> &slot_of = t.slot_of, &perm = t.perm, &nstart = t.nstart, &nend = t.nend, &nleft = t.nleft, &rootidx = t.rootidx;
+    std::vector<uint32_t> &level_off = t.level_off;
 
     // ---- large groups -> compact positions ----
     DBuf<uint32_t> flags(ctx, ntot), sexcl(ctx, ntot), total(ctx, 2), gflag(ctx, (size_t)NG + 1), gexcl(ctx, (size_t)NG + 1);
@@ -481,15 +488,14 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     VR_CUDA(cudaMemcpyAsync(h2, total.p, sizeof(h2), cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
     const uint32_t nL = h2[0], nLG = h2[1];
-    if (nL == 0) return;
-    DBuf<uint32_t> slot_of(ctx, nL);
+    if (nL == 0) return false;
+    slot_of.alloc(ctx, nL);
     VR_LAUNCH(ctx, k_pt_compact, grid_for(ntot, T), T, 0, flags.p, sexcl.p, ntot, slot_of.p);
 
-    // VRGPU_TREE_TIES=1 (read per call): arrange every node with the reference's own selection, see qsel.cuh
-    const bool exact_ties = [] { const char *e = getenv("VRGPU_TREE_TIES"); return e && atoi(e) == 1; }();
-
-    // ---- ranks along the three axes (ties: lower member first) ----
-    DBuf<uint32_t> rank(ctx, exact_ties ? 1 : 3 * (size_t)nL), perm(ctx, nL), vtmp(ctx, exact_ties ? 1 : nL);
+    // ---- ranks along the three axes (ties: lower member first); exact_ties arranges every node with the reference's own
+    // selection instead (qsel.cuh) and needs none ----
+    perm.alloc(ctx, nL);
+    DBuf<uint32_t> rank(ctx, exact_ties ? 1 : 3 * (size_t)nL), vtmp(ctx, exact_ties ? 1 : nL);
     DBuf<uint64_t> keys(ctx, exact_ties ? 1 : nL), ktmp(ctx, exact_ties ? 1 : nL);
     if (!exact_ties) {
         KScope k(ctx, "ptree.ranks");
@@ -504,9 +510,10 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     // ---- nodes ----
     const uint32_t minleaf = std::max(1u, ((uint32_t)bucket + 1u) / 2u);
     const size_t cap = 2 * ((size_t)nL / minleaf + 1) + nLG + 16;
-    DBuf<uint32_t> nstart(ctx, cap), nend(ctx, cap), nleft(ctx, cap);
+    nstart.alloc(ctx, cap); nend.alloc(ctx, cap); nleft.alloc(ctx, cap);
+    rootidx.alloc(ctx, nL);
     DBuf<uint32_t> frontier(ctx, cap), frontier2(ctx, cap), splitflag(ctx, cap), splitdim(ctx, cap), fexcl(ctx, cap);
-    DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL), fidx(ctx, nL), rootidx(ctx, nL);
+    DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL), fidx(ctx, nL);
     DBuf<unsigned long long> mm(ctx, 6 * cap);
     // selection state of the exact-ties variant
     const size_t qcap = exact_ties ? cap : 1, qn = exact_ties ? (size_t)nL + 1 : 1;
@@ -517,7 +524,7 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     VR_LAUNCH(ctx, k_pt_roots, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, gflag.p, gexcl.p, sexcl.p, NG, ntot, nstart.p, nend.p, nleft.p, frontier.p);
     VR_LAUNCH(ctx, k_pt_iota, grid_for(nL, T), T, 0, perm.p, nL);
     uint32_t nF = nLG, nnodes = nLG;
-    std::vector<uint32_t> level_off{0u, nLG};
+    level_off.assign({0u, nLG});
     // A group's largest node at level l holds ceil(n / 2^l) particles (median splits), so the group is finished once that
     // is <= bucket: the per-particle passes of a level only cover positions below the end of the last unfinished group
     // (groups come in size order from the search stages, so this prefix shrinks level by level).
@@ -584,6 +591,24 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             std::swap(fr, fr2);
         }
     }
+    t.nL = nL;
+    t.nLG = nLG;
+    t.nnodes = nnodes;
+    return true;
+}
+
+void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, double theta, int bucket, long long pp_threshold, double *phi)
+{
+    if (gs.ntot == 0 || gs.ngroups == 0 || pp_threshold < 0) return;
+    VR_REQUIRE(theta > 0, VRGPU_EINVAL, "TreeThetaOpen must be positive");
+    // VRGPU_TREE_TIES=1 (read per call): arrange every node with the reference's own selection, see qsel.cuh
+    const bool exact_ties = [] { const char *e = getenv("VRGPU_TREE_TIES"); return e && atoi(e) == 1; }();
+    PtTree t;
+    if (!pt_build(ctx, gs, bucket, pp_threshold, exact_ties, t)) return;
+    const int T = 256;
+    const uint32_t nL = t.nL, nLG = t.nLG, nnodes = t.nnodes;
+    DBuf<uint32_t> &slot_of = t.slot_of, &perm = t.perm, &nstart = t.nstart, &nend = t.nend, &nleft = t.nleft, &rootidx = t.rootidx;
+    const std::vector<uint32_t> &level_off = t.level_off;
 
     // ---- tree-ordered columns, monopoles, opening radii ----
     DBuf<double> tx(ctx, nL), ty(ctx, nL), tz(ctx, nL), tm(ctx, nL);
