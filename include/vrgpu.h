@@ -125,6 +125,16 @@ int vrgpu_fof6d(vrgpu_ctx *ctx, vrgpu_view view, const long long *pfof3d, long l
 int vrgpu_fof_criterion6d(vrgpu_ctx *ctx, vrgpu_view view, const double *check, double check_below, double xlink2, double vlink2,
                           long long minsize, long long *pfof_out, long long *ngroups_out);
 
+/* Local velocity density of the particles of one structure.  Replaces GetVelocityDensity (src/localfield.cxx:18) as
+ * SearchSubSub calls it with tree == NULL (src/search.cxx:2646): a physical kd-tree with bucket
+ * bsize (Options::Bsize), per leaf (approx = 1, Options::iLocalVelDenApproxCalcFlag, the default; localfield.cxx:726-897) or
+ * per particle (approx = 0; :485-586) the nsearch nearest particles in position, of those the nvel nearest in velocity,
+ * and KDTree::CalcSmoothLocalValue with the Epanechnikov table of 1000 entries.  type (may be NULL = all 1): Particle::type,
+ * particles of type 0 get density 0 (the reference's STRUCDEN builds skip them).  period 0 = open domain; a periodic
+ * domain follows the reference's sequence of reflected searches.  density_out[i] by particle index. */
+int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, double period, int bsize, int nsearch, int nvel,
+                           int approx, double *density_out);
+
 /* Potentials of groups given in CSR form (offsets[G+1], index[offsets[G]] = particle index in the view).
  * Replaces the direct-sum loop of Unbind (src/unbind.cxx:398-416) for n <= pp_threshold and
  * Potential() (src/unbind.cxx:1607-1741; kd-tree of KDTree.cxx:438-507, bucket, theta) above it.

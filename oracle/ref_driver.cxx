@@ -34,6 +34,8 @@ void SortGroupParticlesGPU(Options &opt, NBody::Particle *Part, Int_t ngroup, In
 Int_t *BuildNumInGroupGPU(const Int_t nbodies, const Int_t numgroups, Int_t *pfof);
 Int_t **BuildPGListGPU(const Int_t nbodies, const Int_t numgroups, Int_t *numingroup, Int_t *pfof);
 Int_t *FOFCriterion6DCoreGPU(NBody::Particle *Partsubset, Int_t nsubset, Double_t *param, Int_t &numgroups, Int_t minsize);
+void GetVelocityDensityGPU(Options &opt, const Int_t nbodies, NBody::Particle *Part, NBody::KDTree *tree);
+#define GetVelocityDensity GetVelocityDensityGPU
 #define BuildNumInGroup BuildNumInGroupGPU
 #define BuildPGList BuildPGListGPU
 #define GetBindingEnergy GetBindingEnergyGPU

@@ -17,8 +17,8 @@ pipes() {
   timeout 120 python -c "import sys; sys.path.insert(0, 'velociraptor-stf_b200'); import vrgpu; print(vrgpu.Context(0).probe_fp64_pipes())" 2>&1 | tail -1
 }
 gated() {
-  echo "== gated tests (first GPU run): binding-energy sort adaptor, pglist, Keep_background_potential=0, 3DFOF edge cases, many-window dispersion, exact tree ties"
-  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -8
+  echo "== gated tests (first GPU run): binding-energy sort adaptor, pglist, Keep_background_potential=0, 3DFOF edge cases, many-window dispersion, exact tree ties, local velocity density"
+  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_veldens.py tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -8
 }
 sym() {
   for v in 0 1 2; do

@@ -362,6 +362,37 @@ int vrgpu_fof_criterion6d(vrgpu_ctx *ctx, vrgpu_view view, const double *check, 
     });
 }
 
+int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, double period, int bsize, int nsearch, int nvel, int approx,
+                           double *density_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(density_out, VRGPU_EINVAL, "null pointer");
+        CallTimer ct(ctx);
+        DeviceParticles P;
+        {
+            StageTimer t(ctx);
+            upload_view(ctx, view, true, false, false, P);
+            ctx->stats.h2d_ms += t.stop();
+        }
+        if (P.n == 0) return;
+        DBuf<int> tp;
+        if (type) {
+            tp.alloc(ctx, P.n);
+            VR_CUDA(cudaMemcpyAsync(tp.p, type, P.n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+            ctx->stats.h2d_bytes += (long long)(P.n * sizeof(int));
+        }
+        DBuf<double> den(ctx, P.n);
+        velocity_density_device(ctx, P, type ? tp.p : nullptr, period, bsize, nsearch, nvel, approx, den.p);
+        {
+            StageTimer t(ctx);
+            VR_CUDA(cudaMemcpyAsync(density_out, den.p, P.n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            ctx->stats.d2h_bytes += (long long)(P.n * sizeof(double));
+            ctx->stats.d2h_ms += t.stop();
+        }
+    });
+}
+
 int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const long long *index, double G,
                     double eps, double theta, int bucket, long long pp_threshold, double *phi_out)
 {

@@ -15,6 +15,10 @@ long long fof_criterion6d_device(vrgpu_ctx *ctx, const DeviceParticles &P, const
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 
+// GetVelocityDensity (src/localfield.cxx:18) for one structure; type_dev (original order) may be null; den_dev in original order (veldens.cu)
+void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int *type_dev, double period, int bsize, int nsearch, int nvel,
+                             int approx, double *den_dev);
+
 // device-visible alias of a page-locked host pointer, or nullptr for pageable memory (fof6d.cu)
 void *mapped_host_pointer(const void *p);
 

@@ -11,6 +11,7 @@
  *     Int_t **BuildPGList(const Int_t, const Int_t, Int_t*, Int_t*)           src/buildandsortarrays.cxx:26  (row f3)
  *     Int_t *FOFCriterion6DCore(Particle*, Int_t, Double_t*, Int_t&, Int_t)      tree->FOFCriterion(FOF6d, ..., FOFcheckbg) of the
  *                        6D core search, src/search.cxx:1611 and :1664 (NBodylib/src/KDTree/KDFOF.cxx:133)      (row f2)
+ *     void   GetVelocityDensity(Options&, const Int_t, Particle*, KDTree*)               src/localfield.cxx:18   (row f4)
  *     void   SortGroupParticlesGPU(Options&, Particle*, Int_t, Int_t*, Int_t*, PropData*)
  *                        the per-group qsort inside SortAccordingtoBindingEnergy, substructureproperties.cxx:4302-4316
  *
@@ -395,4 +396,34 @@ Int_t *VRGPU_NAME(FOFCriterion6DCore)(Particle *Partsubset, Int_t nsubset, Doubl
     for (Int_t i = 0; i < nsubset; i++) pfof[Partsubset[i].GetID()] = byindex[i];
     numgroups = ng;
     return pfof;
+}
+
+/* Row f4.  GetVelocityDensity (src/localfield.cxx:18): Particle::density of every particle (of every particle with type != 0
+ * in STRUCDEN builds) from Options::Nsearch position neighbours and Options::Nvel velocity neighbours, per leaf of the kd-tree
+ * with bucket Options::Bsize (iLocalVelDenApproxCalcFlag, the default) or per particle.  The library builds the tree the
+ * routine would build for tree == NULL (the call of SearchSubSub, search.cxx:2646).  A tree handed in by the caller
+ * (search.cxx:232, :384: the FOF tree over the same particles) is not read: the particles then arrive in that tree's order,
+ * the rebuilt tree has the same leaves wherever the split coordinates are distinct, and the leaf centres are summed in a
+ * different order (last-bit differences).  Not covered: the MPI import / export of neighbours (single task only) and the
+ * baryon search variant that restricts neighbours by type (iBaryonSearch == 1 with PSTALL). */
+void VRGPU_NAME(GetVelocityDensity)(Options &opt, const Int_t nbodies, Particle *Part, KDTree *tree)
+{
+    (void)tree;
+    if (nbodies <= 0) return;
+    if (opt.iBaryonSearch == 1 && opt.partsearchtype == PSTALL) {
+        cerr << "vrgpu: GetVelocityDensity with a type-restricted neighbour search (Baryon_searchflag=1, all particle types) is not supported" << endl;
+        exit(9);
+    }
+    vector<double> den((size_t)nbodies);
+    const int *tp = NULL;
+#ifdef STRUCDEN
+    vector<int> type((size_t)nbodies);
+    for (Int_t i = 0; i < nbodies; i++) type[i] = Part[i].GetType();
+    tp = type.data();
+#endif
+    int rc = vrgpu_velocity_density(context(), view_of(Part, nbodies), tp, opt.p > 0 ? (double)opt.p : 0.0, (int)opt.Bsize, (int)opt.Nsearch,
+                                    (int)opt.Nvel, opt.iLocalVelDenApproxCalcFlag ? 1 : 0, den.data());
+    if (rc != VRGPU_OK) die("vrgpu_velocity_density", rc);
+    for (Int_t i = 0; i < nbodies; i++)
+        if (!tp || tp[i] != 0) Part[i].SetDensity(den[i]);
 }

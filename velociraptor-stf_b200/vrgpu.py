@@ -134,6 +134,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_dist_search_full_set.argtypes = [C.c_void_p, View, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll, P_ll]
     L.vrgpu_dist_search_full_set_resident.argtypes = [C.c_void_p, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll]
     L.vrgpu_fof_criterion6d.argtypes = [C.c_void_p, View, P_d, C.c_double, C.c_double, C.c_double, C.c_longlong, P_ll, P_ll]
+    L.vrgpu_velocity_density.argtypes = [C.c_void_p, View, C.POINTER(C.c_int), C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, P_d]
     L.vrgpu_stream.argtypes = [C.c_void_p]
     L.vrgpu_stream.restype = C.c_void_p
     L.vrgpu_kernel_times.argtypes = [C.c_void_p]
@@ -150,7 +151,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_adjust_for_period", "vrgpu_fof6d", "vrgpu_potential", "vrgpu_unbind", "vrgpu_search_full_set",
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
-                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes", "vrgpu_fof_criterion6d",
+                    "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes", "vrgpu_fof_criterion6d", "vrgpu_velocity_density",
                     "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist"]
 
 
@@ -323,6 +324,15 @@ class Context:
         self._check(self.lib.vrgpu_fof_criterion6d(self.h, view_of(parts), None if chk is None else chk.ctypes.data_as(C.POINTER(C.c_double)),
                                                    check_below, xlink2, vlink2, minsize, pf.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
         return pf, int(ng.value)
+
+    def velocity_density(self, parts, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None):
+        """GetVelocityDensity (localfield.cxx:18) for the particles of one structure; densities by particle index."""
+        n = parts.shape[0]
+        den = np.zeros(n, dtype=np.float64)
+        tp = None if ptype is None else np.ascontiguousarray(ptype, dtype=np.int32)
+        self._check(self.lib.vrgpu_velocity_density(self.h, view_of(parts), None if tp is None else tp.ctypes.data_as(C.POINTER(C.c_int)),
+                                                    float(period or 0.0), bsize, nsearch, nvel, approx, den.ctypes.data_as(C.POINTER(C.c_double))))
+        return den
 
     def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
         """CheckUnboundGroups (unbind.cxx:196)."""
