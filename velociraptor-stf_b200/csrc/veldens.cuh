@@ -24,9 +24,11 @@
 
 #if defined(__CUDACC__)
 #define VD_HD __device__ __forceinline__
+#define VD_MEMBER __device__ __forceinline__
 #else
 #include <math.h>
 #define VD_HD static inline
+#define VD_MEMBER inline
 #endif
 
 namespace vrgpu {
@@ -83,9 +85,9 @@ struct Params {
     int approx;
     // one batch of queries: [q0, q1) are leaf indices (approx) or tree positions (exact)
     uint32_t q0, q1;
-    double *heap_d2;                // (q1 - q0) * K, K = nsearch (+1 for a periodic target search)
+    double *heap_d2;                // (nsearch + 1) * (q1 - q0): entry i of slot s at [i * (q1 - q0) + s]
     uint32_t *heap_id;
-    uint32_t *nn;                   // (q1 - q0) * nsearch: the neighbours, NONE where there are fewer
+    uint32_t *nn;                   // nsearch * (q1 - q0), same layout: the neighbours, NONE where there are fewer
     // kernel table (KDTree::KernelConstruction, KDTree.cxx:592-631)
     const double *kernel;
     int kernres;
@@ -114,14 +116,19 @@ VD_HD void leaf_thread(const Params &P, uint32_t l)
 }
 
 // ---- the queue: a binary max-heap of K (distance, id) pairs --------------------------------------------------------------
+// Entry i of the queue of query slot s lives at [i * stride + s] (stride = queries of the batch): the threads of a warp own
+// consecutive slots, so their accesses to the same heap position -- the top above all -- fall into consecutive words.
 struct Heap {
     double *d2;
     uint32_t *id;
     uint32_t K;
+    size_t stride;
+    VD_MEMBER double &D(uint32_t i) const { return d2[i * stride]; }
+    VD_MEMBER uint32_t &I(uint32_t i) const { return id[i * stride]; }
 };
 VD_HD void heap_init(const Heap &H)
 {
-    for (uint32_t i = 0; i < H.K; i++) { H.d2[i] = MAXVALUE; H.id[i] = NONE; }
+    for (uint32_t i = 0; i < H.K; i++) { H.D(i) = MAXVALUE; H.I(i) = NONE; }
 }
 // Entries are ordered by (distance, id): of several particles at exactly the Nsearch-th distance (float32 coordinates
 // produce such ties) the ones with the lower tree position are kept, whatever the order of the walk -- the oracle's rule.
@@ -132,12 +139,12 @@ VD_HD void heap_replace_top(const Heap &H, double d2, uint32_t id)
     for (;;) {
         const uint32_t l = 2 * i + 1, r = l + 1;
         if (l >= H.K) break;
-        const uint32_t c = (r < H.K && after(H.d2[r], H.id[r], H.d2[l], H.id[l])) ? r : l;
-        if (!after(H.d2[c], H.id[c], d2, id)) break;
-        H.d2[i] = H.d2[c]; H.id[i] = H.id[c];
+        const uint32_t c = (r < H.K && after(H.D(r), H.I(r), H.D(l), H.I(l))) ? r : l;
+        if (!after(H.D(c), H.I(c), d2, id)) break;
+        H.D(i) = H.D(c); H.I(i) = H.I(c);
         i = c;
     }
-    H.d2[i] = d2; H.id[i] = id;
+    H.D(i) = d2; H.I(i) = id;
 }
 
 // squared distance from q to the bounding box of node nd, in the operation order of a particle distance
@@ -163,7 +170,7 @@ VD_HD void search_from(const Params &P, const Heap &H, const double *q, uint32_t
     stack[sp++] = P.root;
     while (sp > 0) {
         const uint32_t nd = stack[--sp];
-        if (box_d2(P, nd, q) > H.d2[0]) continue;
+        if (box_d2(P, nd, q) > H.D(0)) continue;
         const uint32_t l = P.nleft[nd];
         if (l == NONE) {
             for (uint32_t i = P.nstart[nd]; i < P.nend[nd]; i++) {
@@ -171,7 +178,7 @@ VD_HD void search_from(const Params &P, const Heap &H, const double *q, uint32_t
                 const double dx = fsub(q[0], P.tx[i]), dy = fsub(q[1], P.ty[i]), dz = fsub(q[2], P.tz[i]);
                 const double d2 = fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz));
                 if (target != NONE && !(d2 > 0)) continue;
-                if (after(H.d2[0], H.id[0], d2, i)) heap_replace_top(H, d2, i);
+                if (after(H.D(0), H.I(0), d2, i)) heap_replace_top(H, d2, i);
             }
             continue;
         }
@@ -186,7 +193,8 @@ VD_HD void search_from(const Params &P, const Heap &H, const double *q, uint32_t
 VD_HD void knn_thread(const Params &P, uint32_t q)
 {
     const uint32_t slot = q - P.q0;
-    uint32_t *out = P.nn + (size_t)slot * P.nsearch;
+    const size_t stride = P.q1 - P.q0;
+    uint32_t *out = P.nn + slot;                                   // neighbour k at out[k * stride]
     double c[3];
     uint32_t target = NONE;
     if (P.approx) {
@@ -199,11 +207,11 @@ VD_HD void knn_thread(const Params &P, uint32_t q)
     }
     const bool periodic = P.period > 0;
     const uint32_t K = P.nsearch + ((periodic && target != NONE) ? 1u : 0u);
-    Heap H{P.heap_d2 + (size_t)slot * (P.nsearch + 1u), P.heap_id + (size_t)slot * (P.nsearch + 1u), K};
+    Heap H{P.heap_d2 + slot, P.heap_id + slot, K, stride};
     heap_init(H);
     if (!periodic) {
         search_from(P, H, c, target);
-        for (uint32_t k = 0; k < P.nsearch; k++) out[k] = H.id[k];
+        for (uint32_t k = 0; k < P.nsearch; k++) out[k * stride] = H.I(k);
         return;
     }
     // SplitNode::FindNearestPosPeriodic (KDSplitNode.cxx:1008-1040): the point, then its reflections, each behind its gate
@@ -214,7 +222,7 @@ VD_HD void knn_thread(const Params &P, uint32_t q)
         xp[0] = c[0]; xp[1] = c[1]; xp[2] = c[2];
         if (c[k] < half) { xp[k] = fadd(c[k], P.period); sval = c[k]; }
         else { xp[k] = fsub(c[k], P.period); sval = -xp[k]; }
-        if (fsqrt(H.d2[0]) > sval) search_from(P, H, xp, NONE);
+        if (fsqrt(H.D(0)) > sval) search_from(P, H, xp, NONE);
     }
     for (int r = 0; r <= 3; r++) {                                 // PeriodicReflection2D (0,1) (0,2) (1,2), then ND
         xp[0] = c[0]; xp[1] = c[1]; xp[2] = c[2];
@@ -226,17 +234,17 @@ VD_HD void knn_thread(const Params &P, uint32_t q)
             else { xp[k] = fsub(c[k], P.period); sval = fadd(sval, fmul(xp[k], xp[k])); }
         }
         sval = fsqrt(sval);
-        if (H.d2[0] > sval) search_from(P, H, xp, NONE);            // the squared radius against a distance: Q16
+        if (H.D(0) > sval) search_from(P, H, xp, NONE);            // the squared radius against a distance: Q16
     }
     if (target == NONE) {
-        for (uint32_t k = 0; k < P.nsearch; k++) out[k] = H.id[k];
+        for (uint32_t k = 0; k < P.nsearch; k++) out[k * stride] = H.I(k);
         return;
     }
     // KDFindNearest.cxx:292, 356-357: the queue holds Nsearch + 1 entries and the smallest is not loaded
     uint32_t imin = 0;
-    for (uint32_t k = 1; k < K; k++) if (H.d2[k] < H.d2[imin] || (H.d2[k] == H.d2[imin] && H.id[k] < H.id[imin])) imin = k;
+    for (uint32_t k = 1; k < K; k++) if (after(H.D(imin), H.I(imin), H.D(k), H.I(k))) imin = k;
     uint32_t m = 0;
-    for (uint32_t k = 0; k < K; k++) if (k != imin) out[m++] = H.id[k];
+    for (uint32_t k = 0; k < K; k++) if (k != imin) out[(m++) * stride] = H.I(k);
 }
 
 // ---- velocity step + kernel sum, one typed particle ------------------------------------------------------------------------
@@ -246,14 +254,15 @@ VD_HD void density_thread(const Params &P, uint32_t j)
     if (q < P.q0 || q >= P.q1) return;
     P.den[j] = 0.0;
     if (P.ttype[j] == 0) return;
-    const uint32_t *ids = P.nn + (size_t)(q - P.q0) * P.nsearch;
+    const uint32_t *ids = P.nn + (q - P.q0);
+    const size_t stride = P.q1 - P.q0;
     double h[MAXVEL];
     const uint32_t nv = P.nvel;
     for (uint32_t k = 0; k < nv; k++) h[k] = MAXVALUE;
     uint32_t m = 0;
     const double vx = P.tvx[j], vy = P.tvy[j], vz = P.tvz[j];
     for (uint32_t k = 0; k < P.nsearch; k++) {
-        const uint32_t id = ids[k];
+        const uint32_t id = ids[k * stride];
         if (id == NONE || (P.approx && id == j)) continue;
         const double ax = fsub(vx, P.tvx[id]), ay = fsub(vy, P.tvy[id]), az = fsub(vz, P.tvz[id]);
         const double v2 = fadd(fadd(fmul(ax, ax), fmul(ay, ay)), fmul(az, az));
