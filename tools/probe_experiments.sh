@@ -3,10 +3,10 @@
 # parity and its time against the measured default, plus the tests written after round 1's GPU minutes ran out.
 # Usage: gpurun --timeout 2400 -- 'bash tools/probe_experiments.sh'            (everything, about half an hour)
 #        gpurun --timeout 900  -- 'bash tools/probe_experiments.sh pipes gated sym'   (chosen sections)
-# Sections: pipes gated sym walk link disp wb ties.  Log: gpurun_out/probe_experiments.log, bench lines: gpurun_out/probe_*.json
+# Sections: pipes gated sym walk link disp wb ties veldens.  Log: gpurun_out/probe_experiments.log, bench lines: gpurun_out/probe_*.json
 set -u
 mkdir -p gpurun_out
-SECTIONS="${*:-pipes gated ties sym walk link disp wb}"
+SECTIONS="${*:-pipes gated ties veldens sym walk link disp wb}"
 bench() { # bench <out.json> <args...>: one bench line, CPU baseline skipped
   local out=$1; shift
   timeout 900 python bench.py --steps 5 --warmup 3 --no-cpu-baseline "$@" 2>/dev/null | tail -1 > "$out"
@@ -54,6 +54,10 @@ wb() {
     VRGPU_ASYNC_WRITEBACK=$a bench gpurun_out/probe_wb_a$a.json --fofbgtype 3 --pp-threshold 150
   done
 }
+veldens() {
+  echo "== row f4: vrgpu_velocity_density on one structure of 1e6 particles (per-leaf search), with the reference's OpenMP build on a sample"
+  timeout 900 python tools/bench_veldens.py 1000000 3 --cpu 2>&1 | tail -1 | tee gpurun_out/probe_veldens.json
+}
 ties() {
   echo "== VRGPU_TREE_TIES=1: the reference's quickselect arrangement (qsel.cuh): tied-coordinate parity at 1e-10, then the whole tree + unbinding suites under it"
   VRGPU_RUN_UNVERIFIED=1 timeout 600 python -m pytest tests/test_gpu_tree.py -q -m gpu -k "exact" 2>&1 | tail -4
@@ -66,7 +70,7 @@ ties() {
 }
 {
   for s in $SECTIONS; do
-    case $s in pipes|gated|sym|walk|link|disp|wb|ties) $s ;; *) echo "unknown section $s" ;; esac
+    case $s in pipes|gated|sym|walk|link|disp|wb|ties|veldens) $s ;; *) echo "unknown section $s" ;; esac
   done
 } > gpurun_out/probe_experiments.log 2>&1
 tail -60 gpurun_out/probe_experiments.log
