@@ -57,6 +57,8 @@ wb() {
 veldens() {
   echo "== row f4: vrgpu_velocity_density on one structure of 1e6 particles (per-leaf search), with the reference's OpenMP build on a sample"
   timeout 900 python tools/bench_veldens.py 1000000 3 --cpu 2>&1 | tail -1 | tee gpurun_out/probe_veldens.json
+  echo "== the same with the sort-based tree (separates a failure of the search from one of the exact-ties build; densities then agree to ~1e-9, not 1e-12)"
+  VRGPU_VD_SORT_TREE=1 timeout 900 python tools/bench_veldens.py 200000 1 --cpu 2>&1 | tail -1
 }
 ties() {
   echo "== VRGPU_TREE_TIES=1: the reference's quickselect arrangement (qsel.cuh): tied-coordinate parity at 1e-10, then the whole tree + unbinding suites under it"

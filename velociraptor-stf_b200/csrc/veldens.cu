@@ -16,6 +16,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 namespace vrgpu {
@@ -146,7 +147,10 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
     PtTree t;
     {
         KScope k(ctx, "veldens.tree");
-        const bool ok = pt_build(ctx, gs, bsize, 0, true, t);
+        // VRGPU_VD_SORT_TREE=1 (debugging aid): the sort-based build instead of the reference's selection -- the same leaves
+        // wherever split coordinates are distinct, members of a leaf in another order (leaf centres differ in the last bits)
+        const bool sort_tree = [] { const char *e = getenv("VRGPU_VD_SORT_TREE"); return e && atoi(e) == 1; }();
+        const bool ok = pt_build(ctx, gs, bsize, 0, !sort_tree, t);
         VR_REQUIRE(ok && t.nL == n && t.nLG == 1, VRGPU_ECUDA, "velocity density: tree build failed");
     }
     const uint32_t nnodes = t.nnodes;
