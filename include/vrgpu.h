@@ -131,9 +131,12 @@ int vrgpu_fof_criterion6d(vrgpu_ctx *ctx, vrgpu_view view, const double *check, 
  * per particle (approx = 0; :485-586) the nsearch nearest particles in position, of those the nvel nearest in velocity,
  * and KDTree::CalcSmoothLocalValue with the Epanechnikov table of 1000 entries.  type (may be NULL = all 1): Particle::type,
  * particles of type 0 get density 0 (the reference's STRUCDEN builds skip them).  period 0 = open domain; a periodic
- * domain follows the reference's sequence of reflected searches.  density_out[i] by particle index. */
-int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, double period, int bsize, int nsearch, int nvel,
-                           int approx, double *density_out);
+ * domain follows the reference's sequence of reflected searches.  density_out[i] by particle index.
+ * leaf_offsets (may be NULL; nleaves + 1 entries from 0 to n): for a caller that holds its own kd-tree over the same particles
+ * (SearchFullSet passes its FOF tree, src/search.cxx:232) -- the particles are then in that tree's order and leaf l is the index
+ * range [leaf_offsets[l], leaf_offsets[l+1]); the per-leaf search uses these leaves instead of rebuilding the tree's. */
+int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, const long long *leaf_offsets, long long nleaves, double period,
+                           int bsize, int nsearch, int nvel, int approx, double *density_out);
 
 /* Potentials of groups given in CSR form (offsets[G+1], index[offsets[G]] = particle index in the view).
  * Replaces the direct-sum loop of Unbind (src/unbind.cxx:398-416) for n <= pp_threshold and

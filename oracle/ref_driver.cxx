@@ -231,7 +231,8 @@ long long vrref_search_full_set(long long n, double *pos, double *vel, const dou
 /* GetVelocityDensity (localfield.cxx:18) with tree == NULL, as SearchSubSub calls it for the particles of one structure
  * (search.cxx:2646): the routine builds its own physical tree (bucket Options::Bsize, Epanechnikov kernel table of 1000
  * entries, period Options::p) and deletes it again, which restores the input order.  approx = Options::
- * iLocalVelDenApproxCalcFlag (1, the default: one neighbour search per leaf node; 0: one per particle).  type (may be NULL)
+ * iLocalVelDenApproxCalcFlag (1, the default: one neighbour search per leaf node; 0: one per particle); approx = 2 is the
+ * per-leaf search with the tree built by the caller and handed in (search.cxx:232).  type (may be NULL)
  * sets Particle::type -- this build defines STRUCDEN, so particles of type 0 get no density.  den_out in input order. */
 void vrref_velocity_density(long long n, const double *pos, const double *vel, const int *type, double period, int bsize,
                             int nsearch, int nvel, int approx, double *den_out)
@@ -250,8 +251,10 @@ void vrref_velocity_density(long long n, const double *pos, const double *vel, c
     if (type) for (long long i = 0; i < n; i++) P[i].SetType(type[i]);
     stringstream sink;
     streambuf *old = cout.rdbuf(sink.rdbuf());
-    if (approx) GetVelocityDensity(opt, n, P.data(), NULL);
+    if (approx == 1) GetVelocityDensity(opt, n, P.data(), NULL);
     else {
+        /* approx == 2: the per-leaf search on a tree the caller holds, as SearchFullSet calls it (search.cxx:232) */
+        opt.iLocalVelDenApproxCalcFlag = approx ? 1 : 0;
         /* GetVelocityDensityExact never builds a tree itself (it dereferences the NULL pointer): hand it one, as
          * SearchFullSet does with its FOF tree (search.cxx:232), built the way the approximative routine would */
         Double_t per[3] = {period, period, period};

@@ -76,8 +76,9 @@ void bbox(const Tree &t, uint32_t nd, const std::vector<double> &tx, const std::
 } // namespace
 
 // stats_out: [0] leaves, [1] batches.  Returns 0, or < 0 for arguments the device call rejects as well.
-extern "C" int veldens_emul(const double *pos, const double *vel, const int *type, long long n64, double period, int bsize, int nsearch,
-                            int nvel, int approx, unsigned batch, double *den_out, long long *stats_out)
+// leaf_off (may be null; nleaves + 1 offsets): leaves of a tree the caller holds, the particles being in that tree's order.
+extern "C" int veldens_emul(const double *pos, const double *vel, const int *type, long long n64, const long long *leaf_off, long long nleaves,
+                            double period, int bsize, int nsearch, int nvel, int approx, unsigned batch, double *den_out, long long *stats_out)
 {
     stats_out[0] = stats_out[1] = 0;
     if (n64 <= 0) return 0;
@@ -103,7 +104,8 @@ extern "C" int veldens_emul(const double *pos, const double *vel, const int *typ
     bbox(t, 0, tx, ty, tz, bb);
     std::vector<uint32_t> leaf;
     for (uint32_t nd = 0; nd < nnodes; nd++) if (t.nleft[nd] == NONE) leaf.push_back(nd);
-    const uint32_t nleaf = (uint32_t)leaf.size();
+    const bool caller_leaves = approx && leaf_off && nleaves > 0;
+    const uint32_t nleaf = caller_leaves ? (uint32_t)nleaves : (uint32_t)leaf.size();
     stats_out[0] = nleaf;
 
     // KDTree::KernelConstruction (KDTree.cxx:592-631), ND = 3, Epanechnikov, 1000 entries -- as epanechnikov_table in veldens.cu
@@ -129,7 +131,13 @@ extern "C" int veldens_emul(const double *pos, const double *vel, const int *typ
     P.leaf = leaf.data(); P.leaf_of = leaf_of.data(); P.cm = cm.data(); P.cnum = cnum.data(); P.nleaf = nleaf;
     P.period = period; P.nsearch = (uint32_t)nsearch; P.nvel = (uint32_t)nvel; P.approx = approx ? 1 : 0;
     P.kernel = kernel.data(); P.kernres = kernres; P.den = den.data();
-    for (uint32_t l = 0; l < nleaf; l++) leaf_thread(P, l);
+    if (caller_leaves) {
+        std::vector<uint32_t> leaf_of_orig(n);
+        CallerLeaves C{pos, type, leaf_off, nleaf, leaf_of_orig.data(), cm.data(), cnum.data()};
+        for (uint32_t l = 0; l < nleaf; l++) caller_leaf_thread(C, l);
+        for (uint32_t p = 0; p < n; p++) leaf_of[p] = leaf_of_orig[t.perm[p]];   // k_vd_map_leaf_of
+    } else
+        for (uint32_t l = 0; l < nleaf; l++) leaf_thread(P, l);
 
     const uint32_t nq = approx ? nleaf : n;
     const uint32_t nb = batch ? batch : nq;

@@ -53,6 +53,23 @@ def test_velocity_density_golden(gpu_ctx):
         _agree(gpu_ctx.velocity_density(box, period=100.0, bsize=8, nsearch=64, nvel=8, approx=approx), z[key])
 
 
+def test_velocity_density_on_the_callers_leaves(gpu_ctx, oracle):
+    """SearchFullSet's call (search.cxx:232): particles in the order of the caller's tree, that tree's leaf boundaries passed on"""
+    import vrgpu
+    from test_veldens_host import caller_tree
+    rng = np.random.default_rng(21)
+    n = 20000
+    pos = (50 + rng.normal(size=(n, 3)) * 0.01).astype(np.float32).astype(np.float64)
+    vel = rng.normal(size=(n, 3)) * 100
+    ptype = (rng.random(n) < 0.8).astype(np.int32)
+    want = oracle.velocity_density(pos, vel, ptype=ptype)
+    perm, off = caller_tree(oracle, pos, 16)
+    got = gpu_ctx.velocity_density(vrgpu.particles_from_arrays(pos[perm], vel[perm]), ptype=ptype[perm], leaf_offsets=off)
+    _agree(got, want[perm])
+    with pytest.raises(vrgpu.VrgpuError):
+        gpu_ctx.velocity_density(vrgpu.particles_from_arrays(pos[perm], vel[perm]), leaf_offsets=off[:-1])   # does not reach n
+
+
 def test_velocity_density_rejects_what_it_does_not_cover(gpu_ctx):
     import vrgpu
     rng = np.random.default_rng(1)
@@ -74,7 +91,7 @@ def test_velocity_density_through_reference_types(ref):
     pos = 50 + rng.normal(size=(n, 3)) * 0.5
     vel = rng.normal(size=(n, 3)) * 100
     ptype = (rng.random(n) < 0.8).astype(np.int32)
-    for approx in (1, 0):
+    for approx in (1, 0, 2):          # 2: the caller builds the tree and hands it in (search.cxx:232)
         want = ref.velocity_density(pos, vel, approx=approx, ptype=ptype)
         got = refgpu.velocity_density(pos, vel, approx=approx, ptype=ptype)
         _agree(got, want)

@@ -22,16 +22,18 @@ def emul(tmp_path_factory):
     lib = C.CDLL(so)
     pd, pi, pll = C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_longlong)
     lib.veldens_emul.restype = C.c_int
-    lib.veldens_emul.argtypes = [pd, pd, pi, C.c_longlong, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, pd, pll]
+    lib.veldens_emul.argtypes = [pd, pd, pi, C.c_longlong, pll, C.c_longlong, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, pd, pll]
 
-    def run(pos, vel, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None, batch=0):
+    def run(pos, vel, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None, batch=0, leaf_offsets=None):
         pos = np.ascontiguousarray(pos, dtype=np.float64)
         vel = np.ascontiguousarray(vel, dtype=np.float64)
         n = pos.shape[0]
         tp = None if ptype is None else np.ascontiguousarray(ptype, dtype=np.int32)
         den = np.zeros(n)
         stats = np.zeros(2, dtype=np.int64)
-        rc = lib.veldens_emul(pos.ctypes.data_as(pd), vel.ctypes.data_as(pd), None if tp is None else tp.ctypes.data_as(pi), n, period,
+        lo = None if leaf_offsets is None else np.ascontiguousarray(leaf_offsets, dtype=np.int64)
+        rc = lib.veldens_emul(pos.ctypes.data_as(pd), vel.ctypes.data_as(pd), None if tp is None else tp.ctypes.data_as(pi), n,
+                              None if lo is None else lo.ctypes.data_as(pll), 0 if lo is None else len(lo) - 1, period,
                               bsize, nsearch, nvel, approx, batch, den.ctypes.data_as(pd), stats.ctypes.data_as(pll))
         assert rc == 0, f"emulation failed with {rc}"
         return den, stats
@@ -95,3 +97,31 @@ def test_batches_and_golden(emul):
     for approx, key in ((1, "den_box_approx"), (0, "den_box_exact")):
         got, _ = emul(box, vel, period=100.0, bsize=8, nsearch=64, nvel=8, approx=approx, batch=500)
         _agree(got, z[key])
+
+
+def caller_tree(oracle, pos, bsize):
+    """what a caller that holds the reference's tree over the particles has: the tree order and the leaf boundaries"""
+    perm, nodes = oracle.tree_order(pos, bsize)
+    leaves = nodes[(nodes[:, 1] - nodes[:, 0]) <= bsize]
+    leaves = leaves[np.argsort(leaves[:, 0])]
+    assert leaves[0, 0] == 0 and np.array_equal(leaves[1:, 0], leaves[:-1, 1]) and leaves[-1, 1] == len(pos)
+    return perm, np.concatenate([[0], leaves[:, 1]])
+
+
+def test_leaves_of_the_callers_tree(emul, oracle):
+    """SearchFullSet hands GetVelocityDensity its FOF tree (search.cxx:232): particles in tree order, leaves = that tree's.
+    With tied coordinates a rebuilt tree would have other leaves; with the caller's leaf boundaries the densities are the
+    reference's (which are the same whether it builds the tree itself or receives it: checked in test_oracle_vs_ref.py)."""
+    rng = np.random.default_rng(21)
+    n = 5000
+    pos = (50 + rng.normal(size=(n, 3)) * 0.01).astype(np.float32).astype(np.float64)
+    vel = rng.normal(size=(n, 3)) * 100
+    ptype = (rng.random(n) < 0.8).astype(np.int32)
+    want = oracle.velocity_density(pos, vel, ptype=ptype)
+    perm, off = caller_tree(oracle, pos, 16)
+    got, stats = emul(pos[perm], vel[perm], ptype=ptype[perm], leaf_offsets=off)
+    assert stats[0] == len(off) - 1
+    _agree(got, want[perm])
+    # without the boundaries the rebuilt tree groups the tied particles differently: some densities move
+    rebuilt, _ = emul(pos[perm], vel[perm], ptype=ptype[perm])
+    assert np.count_nonzero(np.abs(rebuilt / np.where(want[perm] == 0, 1, want[perm]) - 1.0) > 1e-9) > 0

@@ -362,11 +362,17 @@ int vrgpu_fof_criterion6d(vrgpu_ctx *ctx, vrgpu_view view, const double *check, 
     });
 }
 
-int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, double period, int bsize, int nsearch, int nvel, int approx,
-                           double *density_out)
+int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, const long long *leaf_offsets, long long nleaves, double period,
+                           int bsize, int nsearch, int nvel, int approx, double *density_out)
 {
     return guarded(ctx, [&] {
         VR_REQUIRE(density_out, VRGPU_EINVAL, "null pointer");
+        if (leaf_offsets) {
+            VR_REQUIRE(nleaves > 0 && nleaves < 0x7fffffffll && leaf_offsets[0] == 0 && leaf_offsets[nleaves] == (long long)view.n, VRGPU_EINVAL,
+                       "leaf offsets must run from 0 to the number of particles");
+            for (long long l = 0; l < nleaves; l++)
+                VR_REQUIRE(leaf_offsets[l] <= leaf_offsets[l + 1], VRGPU_EINVAL, "leaf offsets must not decrease");
+        }
         CallTimer ct(ctx);
         DeviceParticles P;
         {
@@ -381,8 +387,15 @@ int vrgpu_velocity_density(vrgpu_ctx *ctx, vrgpu_view view, const int *type, dou
             VR_CUDA(cudaMemcpyAsync(tp.p, type, P.n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
             ctx->stats.h2d_bytes += (long long)(P.n * sizeof(int));
         }
+        DBuf<long long> loff;
+        if (leaf_offsets) {
+            loff.alloc(ctx, (size_t)nleaves + 1);
+            VR_CUDA(cudaMemcpyAsync(loff.p, leaf_offsets, ((size_t)nleaves + 1) * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream));
+            ctx->stats.h2d_bytes += (long long)(((size_t)nleaves + 1) * sizeof(long long));
+        }
         DBuf<double> den(ctx, P.n);
-        velocity_density_device(ctx, P, type ? tp.p : nullptr, period, bsize, nsearch, nvel, approx, den.p);
+        velocity_density_device(ctx, P, type ? tp.p : nullptr, leaf_offsets ? loff.p : nullptr, leaf_offsets ? nleaves : 0, period, bsize, nsearch,
+                                nvel, approx, den.p);
         {
             StageTimer t(ctx);
             VR_CUDA(cudaMemcpyAsync(density_out, den.p, P.n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));

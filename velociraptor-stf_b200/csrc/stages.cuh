@@ -16,8 +16,9 @@ void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticl
 cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 
 // GetVelocityDensity (src/localfield.cxx:18) for one structure; type_dev (original order) may be null; den_dev in original order (veldens.cu)
-void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int *type_dev, double period, int bsize, int nsearch, int nvel,
-                             int approx, double *den_dev);
+// leaf_off_dev (ncaller_leaves + 1 offsets into the caller's order, may be null): leaves of the caller's own tree for the per-leaf search
+void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int *type_dev, const long long *leaf_off_dev, long long ncaller_leaves,
+                             double period, int bsize, int nsearch, int nvel, int approx, double *den_dev);
 
 // device-visible alias of a page-locked host pointer, or nullptr for pageable memory (fof6d.cu)
 void *mapped_host_pointer(const void *p);

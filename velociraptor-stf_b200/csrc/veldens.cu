@@ -86,6 +86,18 @@ __global__ void k_vd_leaves(veldens::Params P)
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l < P.nleaf) veldens::leaf_thread(P, l);
 }
+__global__ void k_vd_caller_leaves(veldens::CallerLeaves C)
+{
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < C.nleaf) veldens::caller_leaf_thread(C, l);
+}
+// tree position -> caller's leaf
+__global__ void k_vd_map_leaf_of(const uint32_t *__restrict__ leaf_of_orig, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of,
+                                 const uint32_t *__restrict__ idx, uint32_t n, uint32_t *__restrict__ leaf_of)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) leaf_of[p] = leaf_of_orig[idx[slot_of[perm[p]]]];
+}
 __global__ void __launch_bounds__(128) k_vd_knn(veldens::Params P)
 {
     const uint32_t q = P.q0 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -121,8 +133,8 @@ static std::vector<double> epanechnikov_table(int kernres)
     return k;
 }
 
-void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int *type_dev, double period, int bsize, int nsearch, int nvel,
-                             int approx, double *den_dev)
+void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int *type_dev, const long long *leaf_off_dev, long long ncaller_leaves,
+                             double period, int bsize, int nsearch, int nvel, int approx, double *den_dev)
 {
     const int T = 256;
     VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "the velocity density needs velocities");
@@ -177,6 +189,9 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
         leaf.alloc(ctx, nleaf);
         VR_LAUNCH(ctx, k_vd_leaf_list, grid_for(nnodes, T), T, 0, flags.p, excl.p, nnodes, leaf.p);
     }
+    // leaves of the caller's tree instead of our own (per-leaf search only; the search itself still walks our tree)
+    const bool caller_leaves = approx && leaf_off_dev && ncaller_leaves > 0;
+    if (caller_leaves) nleaf = (uint32_t)ncaller_leaves;
     DBuf<double> cm(ctx, 3 * (size_t)nleaf), kernel(ctx, 1000);
     DBuf<uint32_t> cnum(ctx, nleaf);
     const std::vector<double> ktab = epanechnikov_table(1000);
@@ -189,7 +204,12 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
     V.leaf = leaf.p; V.leaf_of = leaf_of.p; V.cm = cm.p; V.cnum = cnum.p; V.nleaf = nleaf;
     V.period = period; V.nsearch = (uint32_t)nsearch; V.nvel = (uint32_t)nvel; V.approx = approx ? 1 : 0;
     V.kernel = kernel.p; V.kernres = 1000; V.den = den.p;
-    VR_LAUNCH(ctx, k_vd_leaves, grid_for(nleaf, T), T, 0, V);
+    if (caller_leaves) {
+        DBuf<uint32_t> leaf_of_orig(ctx, n);
+        veldens::CallerLeaves C{P.pos.p, type_dev, leaf_off_dev, nleaf, leaf_of_orig.p, cm.p, cnum.p};
+        VR_LAUNCH(ctx, k_vd_caller_leaves, grid_for(nleaf, T), T, 0, C);
+        VR_LAUNCH(ctx, k_vd_map_leaf_of, grid_for(n, T), T, 0, leaf_of_orig.p, t.perm.p, t.slot_of.p, gs.idx.p, n, leaf_of.p);
+    } else VR_LAUNCH(ctx, k_vd_leaves, grid_for(nleaf, T), T, 0, V);
 
     // ---- queries in batches: the queues take (Nsearch + 1) * 12 bytes and the result Nsearch * 4 bytes per query ----
     const uint32_t nq = approx ? nleaf : n;

@@ -115,6 +115,36 @@ VD_HD void leaf_thread(const Params &P, uint32_t l)
     P.cm[3 * l] = cx; P.cm[3 * l + 1] = cy; P.cm[3 * l + 2] = cz;
 }
 
+// Leaves handed in by the caller (the reference passes its FOF tree over the same particles, search.cxx:232: the particles
+// are then in that tree's order and leaf l is the index range [off[l], off[l+1])): centre and typed count from the caller's
+// array in the caller's order, exactly the sums of localfield.cxx:791-806 on that tree.
+struct CallerLeaves {
+    const double *pos;              // packed xyz in the caller's order
+    const int *type;                // caller's order, may be null (all typed)
+    const long long *off;           // nleaf + 1
+    uint32_t nleaf;
+    uint32_t *leaf_of_orig;         // caller index -> leaf
+    double *cm;
+    uint32_t *cnum;
+};
+VD_HD void caller_leaf_thread(const CallerLeaves &C, uint32_t l)
+{
+    uint32_t num = 0;
+    double cx = 0, cy = 0, cz = 0;
+    for (long long i = C.off[l]; i < C.off[l + 1]; i++) {
+        C.leaf_of_orig[i] = l;
+        if (C.type && C.type[i] == 0) continue;
+        num++;
+        cx = fadd(cx, C.pos[3 * i]); cy = fadd(cy, C.pos[3 * i + 1]); cz = fadd(cz, C.pos[3 * i + 2]);
+    }
+    C.cnum[l] = num;
+    if (num) {
+        const double d = (double)(float)num;
+        cx = fdiv(cx, d); cy = fdiv(cy, d); cz = fdiv(cz, d);
+    }
+    C.cm[3 * l] = cx; C.cm[3 * l + 1] = cy; C.cm[3 * l + 2] = cz;
+}
+
 // ---- the queue: a binary max-heap of K (distance, id) pairs --------------------------------------------------------------
 // Entry i of the queue of query slot s lives at [i * stride + s] (stride = queries of the batch): the threads of a warp own
 // consecutive slots, so their accesses to the same heap position -- the top above all -- fall into consecutive words.

@@ -401,14 +401,13 @@ Int_t *VRGPU_NAME(FOFCriterion6DCore)(Particle *Partsubset, Int_t nsubset, Doubl
 /* Row f4.  GetVelocityDensity (src/localfield.cxx:18): Particle::density of every particle (of every particle with type != 0
  * in STRUCDEN builds) from Options::Nsearch position neighbours and Options::Nvel velocity neighbours, per leaf of the kd-tree
  * with bucket Options::Bsize (iLocalVelDenApproxCalcFlag, the default) or per particle.  The library builds the tree the
- * routine would build for tree == NULL (the call of SearchSubSub, search.cxx:2646).  A tree handed in by the caller
- * (search.cxx:232, :384: the FOF tree over the same particles) is not read: the particles then arrive in that tree's order,
- * the rebuilt tree has the same leaves wherever the split coordinates are distinct, and the leaf centres are summed in a
- * different order (last-bit differences).  Not covered: the MPI import / export of neighbours (single task only) and the
+ * routine would build for tree == NULL (the call of SearchSubSub, search.cxx:2646).  From a tree handed in by the caller
+ * (search.cxx:232, :384: the FOF tree over the same particles, which are then in that tree's order) the body reads the leaf
+ * boundaries the way the reference itself does (FindLeafNode, localfield.cxx:772-781) and passes them on, so the per-leaf
+ * search runs on the caller's leaves.  Not covered: the MPI import / export of neighbours (single task only) and the
  * baryon search variant that restricts neighbours by type (iBaryonSearch == 1 with PSTALL). */
 void VRGPU_NAME(GetVelocityDensity)(Options &opt, const Int_t nbodies, Particle *Part, KDTree *tree)
 {
-    (void)tree;
     if (nbodies <= 0) return;
     if (opt.iBaryonSearch == 1 && opt.partsearchtype == PSTALL) {
         cerr << "vrgpu: GetVelocityDensity with a type-restricted neighbour search (Baryon_searchflag=1, all particle types) is not supported" << endl;
@@ -421,8 +420,17 @@ void VRGPU_NAME(GetVelocityDensity)(Options &opt, const Int_t nbodies, Particle 
     for (Int_t i = 0; i < nbodies; i++) type[i] = Part[i].GetType();
     tp = type.data();
 #endif
-    int rc = vrgpu_velocity_density(context(), view_of(Part, nbodies), tp, opt.p > 0 ? (double)opt.p : 0.0, (int)opt.Bsize, (int)opt.Nsearch,
-                                    (int)opt.Nvel, opt.iLocalVelDenApproxCalcFlag ? 1 : 0, den.data());
+    vector<long long> leafoff;
+    if (tree != NULL && opt.iLocalVelDenApproxCalcFlag) {
+        leafoff.push_back(0);
+        for (Int_t ipart = 0; ipart < nbodies;) {
+            ipart += tree->FindLeafNode(ipart)->GetCount();
+            leafoff.push_back(ipart);
+        }
+    }
+    int rc = vrgpu_velocity_density(context(), view_of(Part, nbodies), tp, leafoff.empty() ? NULL : leafoff.data(),
+                                    leafoff.empty() ? 0 : (long long)leafoff.size() - 1, opt.p > 0 ? (double)opt.p : 0.0, (int)opt.Bsize,
+                                    (int)opt.Nsearch, (int)opt.Nvel, opt.iLocalVelDenApproxCalcFlag ? 1 : 0, den.data());
     if (rc != VRGPU_OK) die("vrgpu_velocity_density", rc);
     for (Int_t i = 0; i < nbodies; i++)
         if (!tp || tp[i] != 0) Part[i].SetDensity(den[i]);

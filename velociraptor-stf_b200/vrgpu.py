@@ -134,7 +134,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_dist_search_full_set.argtypes = [C.c_void_p, View, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll, P_ll]
     L.vrgpu_dist_search_full_set_resident.argtypes = [C.c_void_p, C.c_double, C.c_double, C.POINTER(SearchOpts), P_ll]
     L.vrgpu_fof_criterion6d.argtypes = [C.c_void_p, View, P_d, C.c_double, C.c_double, C.c_double, C.c_longlong, P_ll, P_ll]
-    L.vrgpu_velocity_density.argtypes = [C.c_void_p, View, C.POINTER(C.c_int), C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, P_d]
+    L.vrgpu_velocity_density.argtypes = [C.c_void_p, View, C.POINTER(C.c_int), P_ll, C.c_longlong, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, P_d]
     L.vrgpu_stream.argtypes = [C.c_void_p]
     L.vrgpu_stream.restype = C.c_void_p
     L.vrgpu_kernel_times.argtypes = [C.c_void_p]
@@ -325,13 +325,17 @@ class Context:
                                                    check_below, xlink2, vlink2, minsize, pf.ctypes.data_as(C.POINTER(C.c_longlong)), C.byref(ng)))
         return pf, int(ng.value)
 
-    def velocity_density(self, parts, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None):
-        """GetVelocityDensity (localfield.cxx:18) for the particles of one structure; densities by particle index."""
+    def velocity_density(self, parts, period=0.0, bsize=16, nsearch=256, nvel=32, approx=1, ptype=None, leaf_offsets=None):
+        """GetVelocityDensity (localfield.cxx:18) for the particles of one structure; densities by particle index.
+        leaf_offsets: leaves of the caller's own tree (particles in that tree's order), see include/vrgpu.h."""
         n = parts.shape[0]
         den = np.zeros(n, dtype=np.float64)
         tp = None if ptype is None else np.ascontiguousarray(ptype, dtype=np.int32)
+        lo = None if leaf_offsets is None else np.ascontiguousarray(leaf_offsets, dtype=np.int64)
         self._check(self.lib.vrgpu_velocity_density(self.h, view_of(parts), None if tp is None else tp.ctypes.data_as(C.POINTER(C.c_int)),
-                                                    float(period or 0.0), bsize, nsearch, nvel, approx, den.ctypes.data_as(C.POINTER(C.c_double))))
+                                                    None if lo is None else lo.ctypes.data_as(C.POINTER(C.c_longlong)),
+                                                    0 if lo is None else len(lo) - 1, float(period or 0.0), bsize, nsearch, nvel, approx,
+                                                    den.ctypes.data_as(C.POINTER(C.c_double))))
         return den
 
     def unbind(self, parts, pfof, ngroups, opts: UnbindOpts):
