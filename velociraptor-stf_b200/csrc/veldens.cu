@@ -105,8 +105,9 @@ __global__ void __launch_bounds__(128) k_vd_knn(veldens::Params P)
 }
 __global__ void __launch_bounds__(128) k_vd_density(veldens::Params P)
 {
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < P.n) veldens::density_thread(P, j);
+    // per-leaf search: any particle can belong to a leaf of the batch; per-particle search: the batch IS a range of particles
+    const uint32_t j = (P.approx ? 0u : P.q0) + blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < (P.approx ? P.n : P.q1)) veldens::density_thread(P, j);
 }
 __global__ void k_vd_scatter(const double *__restrict__ den, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of,
                              const uint32_t *__restrict__ idx, uint32_t n, double *__restrict__ out)
@@ -222,7 +223,7 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
         V.q0 = q0;
         V.q1 = (uint32_t)std::min<size_t>(nq, (size_t)q0 + batch);
         { KScope k(ctx, "veldens.search"); VR_LAUNCH(ctx, k_vd_knn, grid_for(V.q1 - V.q0, 128), 128, 0, V); }
-        { KScope k(ctx, "veldens.density"); VR_LAUNCH(ctx, k_vd_density, grid_for(n, 128), 128, 0, V); }
+        { KScope k(ctx, "veldens.density"); VR_LAUNCH(ctx, k_vd_density, grid_for(approx ? n : V.q1 - V.q0, 128), 128, 0, V); }
     }
     VR_LAUNCH(ctx, k_vd_scatter, grid_for(n, T), T, 0, den.p, t.perm.p, t.slot_of.p, gs.idx.p, n, den_dev);
 }
