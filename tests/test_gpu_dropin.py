@@ -67,8 +67,6 @@ def test_potential_through_reference_types(ref, refgpu):
     assert np.max(np.abs(got / want - 1.0)) < 1e-10
 
 
-@pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                    reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 def test_core_search_linking_through_reference_types(ref, refgpu):
     """Row f2, linking step: the adaptor body FOFCriterion6DCoreGPU receives the reference's own Particle array in the order
     its KDTree left it (ids = input index, potential field = the FOFcheckbg mask) and must return what

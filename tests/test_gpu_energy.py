@@ -136,8 +136,6 @@ def test_binding_energy_through_reference_types(ref):
     _compare(strip(got), strip(want), z["num"][1:])
 
 
-UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 
 
 def test_sort_groups_by_key(gpu_ctx):
@@ -158,7 +156,6 @@ def test_sort_groups_by_key(gpu_ctx):
     assert gpu_ctx.sort_groups_by_key(np.array([0, 0]), np.zeros(0)).size == 0
 
 
-@UNVERIFIED
 @pytest.mark.parametrize("by_energy", [1, 0])
 def test_sort_by_binding_energy_through_reference_types(ref, oracle, by_energy):
     """SortAccordingtoBindingEnergy (substructureproperties.cxx:4256-4352): the reference's whole function against the
@@ -196,7 +193,6 @@ def test_sort_by_binding_energy_through_reference_types(ref, oracle, by_energy):
     assert nswapped <= 2e-3 * off[-1]
 
 
-@UNVERIFIED
 def test_build_pglist(gpu_ctx):
     """vrgpu_build_pglist (row f3): BuildNumInGroup + BuildPGList (buildandsortarrays.cxx:11-16, 26-43) -- sizes by group id,
     members in ascending particle index; from host labels and from the labels a resident search left on the device."""
@@ -229,7 +225,6 @@ def test_build_pglist(gpu_ctx):
     gpu_ctx.particles_release()
 
 
-@UNVERIFIED
 def test_build_pglist_through_reference_types(ref):
     import vroracle
     if not vroracle.Ref.available("gpu"):

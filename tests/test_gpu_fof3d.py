@@ -65,8 +65,6 @@ def test_fof3d_known_answers(gpu_ctx):
     assert ng == 0 and pf.shape == (0,)
 
 
-@pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                    reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 def test_fof3d_edge_cases(gpu_ctx, oracle):
     """Corners of the domain (tests/edge_cases.py): the oracle is pinned to the compiled reference on exactly these inputs
     (test_oracle_vs_ref.py::test_fof3d_edge_cases_vs_kdtree_fof)."""

@@ -116,8 +116,6 @@ def test_pinned_caller_memory_gets_identical_writeback(gpu_ctx):
     assert not np.array_equal(a["pos"], d["pos"])  # something was unwrapped / re-rounded
 
 
-@pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                    reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 def test_core_search_linking(gpu_ctx, oracle):
     """SURVEY section 8 row f2, linking step: vrgpu_fof_criterion6d against the travelling fixture made from the reference's
     KDTree::FOFCriterion(FOF6d, ..., FOFcheckbg) (tests/golden/core) and against the oracle on two more halos, three

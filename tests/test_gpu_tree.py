@@ -14,8 +14,6 @@ import vrsynth
 
 pytestmark = pytest.mark.gpu
 G = 43.0211349
-UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 
 
 def _clustered(n, rng, scale=1.0):
@@ -82,7 +80,6 @@ def test_tree_with_tied_coordinates(gpu_ctx, oracle):
     assert rel.max() < 1e-2  # same order as the tree's own truncation error; NOT the 1e-10 of the tie-free case
 
 
-@UNVERIFIED
 @pytest.mark.parametrize("n,scale", [(30000, 0.5), (200000, 0.05), (1500, 0.001)])
 def test_tree_with_tied_coordinates_exact(gpu_ctx, oracle, monkeypatch, n, scale):
     """VRGPU_TREE_TIES=1 (csrc/qsel.cuh): every node is arranged by the reference's own MedianPos iterations, so the tied
@@ -102,7 +99,6 @@ def test_tree_with_tied_coordinates_exact(gpu_ctx, oracle, monkeypatch, n, scale
     assert np.max(np.abs(phi / ref - 1.0)) < 1e-10
 
 
-@UNVERIFIED
 def test_tree_exact_ties_many_groups(gpu_ctx, oracle, monkeypatch):
     """Several groups built in the same launches (sizes on both sides of QS_SMALL = 2048 and of the direct-sum threshold),
     and a second bucket size."""

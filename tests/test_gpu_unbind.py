@@ -71,11 +71,8 @@ def test_unbind_matches_oracle(gpu_ctx, oracle, nside, seed, unbindtype):
         assert np.array_equal(got["pfof"], want["pfof"])
 
 
-UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 
 
-@UNVERIFIED
 @pytest.mark.parametrize("nside,seed,unbindtype", [(32, 7, 0), (48, 3, 0), (48, 9, 1)])
 def test_unbind_without_background_potential(gpu_ctx, oracle, nside, seed, unbindtype):
     """Keep_background_potential=0 (examples/sample.cfg, genesis2019_configuration.cfg; unbind.cxx:672-690): members lose the

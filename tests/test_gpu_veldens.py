@@ -2,15 +2,13 @@
 GetVelocityDensity (localfield.cxx:18), which is bit-identical to the compiled reference (tests/test_oracle_vs_ref.py), and
 against the travelling fixture made from the reference.  Tolerance 1e-12 relative: every operation follows the reference's
 order; the one exception is its pow(h, 3.0), cubed here with a single rounding.  The same per-thread source passes
-these comparisons as a host emulation (tests/test_veldens_host.py); these tests wait for their first GPU run."""
+these comparisons as a host emulation (tests/test_veldens_host.py); first green on the B200 in round 2."""
 import os
 
 import numpy as np
 import pytest
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                                 reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")]
+pytestmark = [pytest.mark.gpu]
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 

@@ -52,12 +52,10 @@ def test_single_halo_search_full_set(gpu_ctx, oracle, fofbgtype, pp):
     assert np.array_equal(parts["pos"], pos) and np.array_equal(parts["vel"], vel)
 
 
-UNVERIFIED = pytest.mark.skipif(os.environ.get("VRGPU_RUN_UNVERIFIED") != "1",
-                                reason="written after round 1's GPU minutes were spent; first GPU run pending (VRGPU_RUN_UNVERIFIED=1)")
 
 
 @pytest.mark.parametrize("pattern", ["zero_mean", "zero_axis", "ties", "equal_mass_drift", "mixed_mass"])
-@pytest.mark.parametrize("multi_min", [0, pytest.param(8192, marks=UNVERIFIED)])
+@pytest.mark.parametrize("multi_min", [0, 8192])
 def test_big_group_dispersion_is_bit_exact(gpu_ctx, oracle, pattern, multi_min, monkeypatch):
     """multi_min = 8192 sends the group through the many-window evaluation (VRGPU_DISP_MULTI_MIN, csrc/seqsum.h "Many windows
     at once": summaries under a predicted unit + one walker) -- the same bit-exact bar.

@@ -18,7 +18,8 @@ pipes() {
 }
 gated() {
   echo "== gated tests (first GPU run): binding-energy sort adaptor, pglist, Keep_background_potential=0, 3DFOF edge cases, many-window dispersion, exact tree ties, local velocity density"
-  VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_veldens.py tests/test_gpu_energy.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -8
+  VRGPU_RUN_UNVERIFIED=1 timeout 1200 python -m pytest tests -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/gated_pytest.log 2>&1
+  tail -40 gpurun_out/gated_pytest.log
 }
 sym() {
   for v in 0 1 2; do
@@ -62,8 +63,8 @@ veldens() {
 }
 ties() {
   echo "== VRGPU_TREE_TIES=1: the reference's quickselect arrangement (qsel.cuh): tied-coordinate parity at 1e-10, then the whole tree + unbinding suites under it"
-  VRGPU_RUN_UNVERIFIED=1 timeout 600 python -m pytest tests/test_gpu_tree.py -q -m gpu -k "exact" 2>&1 | tail -4
-  VRGPU_TREE_TIES=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py -q -m gpu 2>&1 | tail -4
+  VRGPU_TREE_TIES=1 VRGPU_RUN_UNVERIFIED=1 timeout 900 python -m pytest tests/test_gpu_tree.py tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py tests/test_gpu_energy.py -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/ties_pytest.log 2>&1
+  tail -30 gpurun_out/ties_pytest.log
   for t in 0 1; do
     echo "== VRGPU_TREE_TIES=$t bench (256^3, 6DFOF + tree unbinding; look at ptree.build), then the 2e7 single halo"
     VRGPU_TREE_TIES=$t bench gpurun_out/probe_ties_t$t.json --fofbgtype 3 --pp-threshold 150

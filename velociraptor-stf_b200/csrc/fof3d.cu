@@ -19,7 +19,6 @@
 #include "fof.cuh"
 #include "groups.cuh"
 #include "ufhash.cuh"
-#include "link2.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -505,36 +504,6 @@ __global__ void __launch_bounds__(256) k_link_queue(LinkParams P, const uint32_t
     }
 }
 
-// ---------------------------------------------------------------------------------------------------
-// candidate-queue linker (link2.cuh; VRGPU_LINK_VARIANT=1|2, never launched by default)
-// ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_link2_coords(const uint64_t *__restrict__ cell_key, uint32_t ncells, uint64_t ncx,
-                                                      uint32_t *__restrict__ cell_row, int *__restrict__ cell_ix, link2::RowRange *__restrict__ rows)
-{
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c < ncells) link2::coords_thread(cell_key, ncells, ncx, c, cell_row, cell_ix, rows);
-}
-
-// grid: (cells / 256, rows of the half space): a warp holds 32 consecutive cells and one row offset
-__global__ void __launch_bounds__(256) k_link2_emit(link2::Params P, int reach, int filter, link2::Queue C)
-{
-    const uint32_t cell = blockIdx.x * blockDim.x + threadIdx.x;
-    if (cell < P.ncells) link2::emit_thread(P, cell, (int)blockIdx.y, reach, filter != 0, C);
-}
-
-__global__ void __launch_bounds__(256) k_link2_compress(uint32_t *__restrict__ parent, uint32_t ncells)
-{
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c < ncells) link2::compress_thread(parent, c);
-}
-
-// one thread per candidate; the count is read on the device, so no host round trip separates emit from pairs
-__global__ void __launch_bounds__(256) k_link2_pairs(link2::Params P, link2::Queue C, link2::Queue Q)
-{
-    const uint32_t n = min(*C.count, C.capacity);
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) link2::pair_thread(P, e, C, Q);
-}
-
 __global__ void k_flatten(uint32_t *__restrict__ parent, uint32_t ncells, uint32_t *__restrict__ root)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -835,53 +804,7 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
         unsigned warps_needed = ncells;
         unsigned blocks = std::min<unsigned>((warps_needed + 7) / 8, (unsigned)ctx->sm_count * 32u);
         blocks = std::max(blocks, 1u);
-        static const int link_variant = [] { const char *e = getenv("VRGPU_LINK_VARIANT"); return e ? atoi(e) : 0; }();
-        if (use_rows && link_variant >= 1) {
-            // experiment (link2.cuh): candidate queue, one short uniform thread per (cell, row) and per candidate
-            DBuf<link2::RowRange> rows(ctx, nrows);
-            DBuf<uint32_t> cell_row(ctx, ncells);
-            DBuf<int> cell_ix(ctx, ncells);
-            const uint32_t qcap = (uint32_t)std::min<size_t>((size_t)8 * ncells + 1024, (size_t)0x7fffffff);
-            DBuf<uint32_t> ca(ctx, qcap), cb(ctx, qcap), cm(ctx, qcap), qa(ctx, qcap), qb(ctx, qcap), qm(ctx, qcap);
-            DBuf<unsigned int> counts(ctx, 2);
-            link2::Queue C{ca.p, cb.p, cm.p, counts.p, qcap};
-            link2::Queue Q2{qa.p, qb.p, qm.p, counts.p + 1, qcap};
-            LinkQueue Q{qa.p, qb.p, qm.p, counts.p + 1, qcap};
-            link2::Params P2{};
-            P2.sx = S.sx.p; P2.sy = S.sy.p; P2.sz = S.sz.p;
-            P2.cell_start = S.cell_start.p; P2.cell_row = cell_row.p; P2.cell_ix = cell_ix.p; P2.rows = rows.p;
-            P2.parent = parent.p; P2.ncells = ncells;
-            P2.ncx = g.nc[0]; P2.ncy = g.nc[1]; P2.ncz = g.nc[2];
-            P2.period = g.period; P2.b2 = b * b;
-            P2.perx = g.periodic[0]; P2.pery = g.periodic[1]; P2.perz = g.periodic[2];
-            KScope k(ctx, "fof3d.link_cells");
-            VR_CUDA(cudaMemsetAsync(rows.p, 0xff, sizeof(link2::RowRange) * nrows, ctx->stream));
-            VR_LAUNCH(ctx, k_link2_coords, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, (uint64_t)g.nc[0], cell_row.p, cell_ix.p, rows.p);
-            for (int reach = 1; reach <= 2; reach++) {
-                VR_CUDA(cudaMemsetAsync(counts.p, 0, 2 * sizeof(unsigned int), ctx->stream));
-                if (reach == 2) VR_LAUNCH(ctx, k_link2_compress, grid_for(ncells, T), T, 0, parent.p, ncells);
-                const dim3 egrid(grid_for(ncells, 256), (unsigned)link2::roles_for(reach));
-                VR_LAUNCH(ctx, k_link2_emit, egrid, 256, 0, P2, reach, (int)(reach == 2 && link_variant == 1), C);
-                VR_LAUNCH(ctx, k_link2_pairs, (unsigned)ctx->sm_count * 8u, 256, 0, P2, C, Q2);
-                unsigned int hc[2] = {0, 0};
-                VR_CUDA(cudaMemcpyAsync(hc, counts.p, sizeof(hc), cudaMemcpyDeviceToHost, ctx->stream));
-                VR_CUDA(cudaStreamSynchronize(ctx->stream));
-                if (hc[0] > qcap || hc[1] > qcap) {
-                    // a queue overflowed (pathological density): the warp-per-cell kernel redoes this reach exhaustively
-                    DBuf<uint32_t> row_first(ctx, nrows), row_last(ctx, nrows), crow(ctx, ncells);
-                    DBuf<int> cix(ctx, ncells);
-                    VR_CUDA(cudaMemsetAsync(row_first.p, 0xff, sizeof(uint32_t) * nrows, ctx->stream));
-                    VR_LAUNCH(ctx, k_cell_coords, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, (uint64_t)g.nc[0], crow.p, cix.p, row_first.p,
-                              row_last.p);
-                    VR_LAUNCH(ctx, k_link_rows, blocks, 256, 0, L, row_first.p, row_last.p, reach);
-                    VR_CUDA(cudaStreamSynchronize(ctx->stream)); // the temporaries go back to the pool after their last use
-                } else if (hc[1]) {
-                    const unsigned qblocks = std::max(1u, std::min<unsigned>((hc[1] + 7) / 8, (unsigned)ctx->sm_count * 32u));
-                    VR_LAUNCH(ctx, k_link_queue, qblocks, 256, 0, L, cell_row.p, cell_ix.p, Q, hc[1]);
-                }
-                ctx->stats.n_link_queue += hc[1];
-            }
-        } else if (use_rows) {
+        if (use_rows) {
             // dense row table (L2 resident at 256^3) + thread-per-cell linking, undecided dense pairs finished by warps
             DBuf<uint32_t> row_first(ctx, nrows), row_last(ctx, nrows), cell_row(ctx, ncells);
             DBuf<int> cell_ix(ctx, ncells);

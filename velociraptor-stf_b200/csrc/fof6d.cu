@@ -986,8 +986,9 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
     DBuf<double> vs2(ctx, (size_t)G + 2);
     {
         KScope k(ctx, "fof6d.dispersion");
-        // experiment (off unless the variable is set): groups of at least this many members go through the many-window path
-        long long multi_min = 0;
+        // groups of at least this many members may go through the many-window path (measured on the 2e7-particle halo:
+        // 292 -> 107 ms, profiles/r02a_probe.md); VRGPU_DISP_MULTI_MIN=0 switches it off
+        long long multi_min = 65536;
         if (const char *e = getenv("VRGPU_DISP_MULTI_MIN")) multi_min = atoll(e);
         SeqScratch sc;
         DBuf<double> seqr;
@@ -1026,7 +1027,17 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
                 std::vector<uint32_t> hoff((size_t)look + 2);
                 VR_CUDA(cudaMemcpyAsync(hoff.data(), gs.off.p, sizeof(uint32_t) * ((size_t)look + 2), cudaMemcpyDeviceToHost, ctx->stream));
                 VR_CUDA(cudaStreamSynchronize(ctx->stream));
-                while (nskip < look && (long long)(hoff[nskip + 2] - hoff[nskip + 1]) >= multi_min) nskip++;
+                // The one-CTA-per-group kernel runs all remaining groups at once, so it costs what its LARGEST group costs
+                // (14.6 ns per member); the many-window path runs its groups one after the other (5.3 ns per member + ~0.15 ms
+                // of launches each).  Take the prefix that minimises the sum.
+                uint32_t elig = 0;
+                while (elig < look && (long long)(hoff[elig + 2] - hoff[elig + 1]) >= multi_min) elig++;
+                double best = 14.6e-6 * (double)(hoff[2] - hoff[1]), acc = 0.0;
+                for (uint32_t k = 1; k <= elig; k++) {
+                    acc += 5.3e-6 * (double)(hoff[k + 1] - hoff[k]) + 0.15;
+                    const double rest = k < look ? 14.6e-6 * (double)(hoff[k + 2] - hoff[k + 1]) : 0.0;
+                    if (acc + rest < best) { best = acc + rest; nskip = k; }
+                }
                 if (nskip) {
                     prepare_multi((unsigned long long)(hoff[2] - hoff[1]));
                     for (uint32_t g = 1; g <= nskip; g++) {

@@ -147,14 +147,9 @@ __global__ void k_sym_count(const uint32_t *__restrict__ off, uint32_t ngroups, 
 // 128 threads x 8 slots, 3 CTAs per SM (168 registers) and no unrolling of the rotation loop measured best: more slots per
 // thread amortise the shared-memory traffic and loop overhead of a rotation step over more FP64 work (256 x 4: 106 ms,
 // 128 x 8: 99.5 ms at 256^3)
-// VAR = 1 is an EXPERIMENT for the next measuring session (never launched unless VRGPU_SYM_VARIANT=1, see
-// potential_direct): the per-instruction stall samples of profiles/r01f (gpurun_out/prof_r01f2) put 31 % of the samples on
-// the tail of a rotation step (the 8-deep dependent chain of the j-side sum, the shared read-modify-write and the
-// __syncwarp) and 9 % on the first DADD that waits for the step's shared loads.  VAR = 1 (a) splits the j-side sum into
-// two chains, (b) keeps the running j-side sum in a register that rotates from lane to lane with the j it belongs to
-// (one shuffle per step, one plain shared store per 32 steps instead of an RMW per step), (c) loads the next step's j
-// from shared memory before the current step's arithmetic.  VAR = 2 is (a) + (b) without (c).
-template <int SPT, int SPI, int MINB, int VAR = 0>
+// Measured and dropped (profiles/r02a_probe.md): a j-side sum that rotates through the lanes with a register shuffle
+// instead of the shared read-modify-write, with and without a prefetch of the next step's j -- both 2-3 % slower.
+template <int SPT, int SPI, int MINB>
 __global__ void __launch_bounds__(SPT, MINB) k_potential_sym(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                                                       const double *__restrict__ m, const uint32_t *__restrict__ off, uint32_t ngroups,
                                                       const unsigned long long *__restrict__ pair_start /* exclusive scan, ngroups+2 */,
@@ -206,54 +201,7 @@ __global__ void __launch_bounds__(SPT, MINB) k_potential_sym(const double *__res
         for (int ww = 0; ww < SPT / 32; ww++) sacc[ww][threadIdx.x] = 0.0;
         __syncthreads();
         const int cnt = (int)min((uint32_t)SPT, j_end - jb);
-        if (VAR >= 1 && !diag) {
-            const int nstep = ((cnt + 31) >> 5) << 5;
-            double2 qa = sxy[lane], qb = szm[lane]; // step s works on jj = (s & ~31) + ((lane + s) & 31)
-            double trot = 0; // j-side sum of the j this lane is working on; it travels with j (lane l -> lane l - 1 per step)
-#pragma unroll 1
-            for (int s = 0; s < nstep; s++) {
-                // VAR 1: the next step's j is loaded now; VAR 2: no prefetch (this step's j is loaded here)
-                const int jn = (((s + (VAR == 1 ? 1 : 0)) & ~31) + (int)((lane + s + (VAR == 1 ? 1 : 0)) & 31)) & (SPT - 1); // wraps on the last step (value unused)
-                const double2 qan = sxy[jn], qbn = szm[jn];
-                if (VAR == 2) { qa = qan; qb = qbn; }
-                double r2[SPI], ri[SPI];
-                unsigned worst = 0;
-#pragma unroll
-                for (int k = 0; k < SPI; k++) {
-                    const double dx = xi[k] - qa.x, dy = yi[k] - qa.y, dz = zi[k] - qb.x;
-                    r2[k] = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-                    const double y0 = rsqrt_seed(r2[k]);
-                    worst = max(worst, (unsigned)__double2hiint(y0));
-                    ri[k] = rsqrt_newton(r2[k], y0);
-                }
-                if (worst >= 0x5f300000u) {
-#pragma unroll
-                    for (int k = 0; k < SPI; k++) ri[k] = rsqrt_refined(r2[k]);
-                }
-                double ta = 0, tb = 0;
-#pragma unroll
-                for (int k = 0; k < SPI; k += 2) {
-                    acc[k] = fma(qb.y, ri[k], acc[k]);
-                    acc[k + 1] = fma(qb.y, ri[k + 1], acc[k + 1]);
-                    ta = fma(mi[k], ri[k], ta);
-                    tb = fma(mi[k + 1], ri[k + 1], tb);
-                }
-                trot += ta + tb;
-                trot = __shfl_sync(0xffffffffu, trot, (lane + 1) & 31); // after 32 steps lane l holds the sum of j = 32*blk + l
-                if ((s & 31) == 31) {
-                    sacc[w][(s & ~31) + (int)lane] = trot;
-                    trot = 0;
-                }
-                qa = qan; qb = qbn;
-            }
-            __syncthreads();
-            if ((int)threadIdx.x < cnt) {
-                double t = 0;
-#pragma unroll
-                for (int ww = 0; ww < SPT / 32; ww++) t += sacc[ww][threadIdx.x];
-                atomicAdd(&phiacc[jb + threadIdx.x], t);
-            }
-        } else if (!diag) {
+        if (!diag) {
             // rotation: at step s lane l works on j = 32*blk + ((l + s) & 31), so the 32 lanes always hold 32 DIFFERENT j:
             // the j-side partial goes straight into the warp's shared row without any cross-lane reduction
             const int nblk = (cnt + 31) >> 5;
@@ -357,14 +305,6 @@ unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G
         KScope k(ctx, "potential.direct.sym");
         DBuf<double> phiacc(ctx, gs.ntot);
         VR_CUDA(cudaMemsetAsync(phiacc.p, 0, sizeof(double) * gs.ntot, ctx->stream));
-        static const int variant = [] { const char *e = getenv("VRGPU_SYM_VARIANT"); return e ? atoi(e) : 0; }();
-        if (variant == 1)
-            VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3, 1>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
-                      eps * eps, phiacc.p);
-        else if (variant == 2)
-            VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3, 2>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
-                      eps * eps, phiacc.p);
-        else
         VR_LAUNCH(ctx, (k_potential_sym<SYM_PT, SYM_PI, 3>), (unsigned)nwork, SYM_PT, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, gs.off.p, G, pstart.p,
                   eps * eps, phiacc.p);
         VR_LAUNCH(ctx, k_sym_finish, grid_for(gs.ntot, 256), 256, 0, phiacc.p, gs.m.p, gs.gid.p, gs.off.p, (uint32_t)gs.ntot, G_, pp_threshold, phi);

@@ -380,11 +380,7 @@ __global__ void k_pt_pack(PtNodes N, const uint32_t *__restrict__ next, uint32_t
 // leaves that subtree (cur == the node's next link).  Every lane therefore sees exactly the nodes, in exactly the order,
 // of the reference's per-particle recursion, and node records are fetched once per warp instead of once per lane.
 constexpr uint32_t PT_ACTIVE = 0xfffffffeu;
-// PF = true is an EXPERIMENT for the next measuring session (VRGPU_WALK_PREFETCH=1, never launched by default): the stall
-// samples of profiles/r01h put 19 % of the walk on the first use of the node record (the successor is known only after
-// the opening test, so the record's L2 latency is exposed once per visited node); PF issues prefetch.global.L1 for
-// both possible successors (`left` and `next`) as soon as the current record has arrived.
-template <bool PF = false>
+// Measured and dropped (profiles/r02a_probe.md): prefetch.global.L1 of both possible successors of a node -- 10 % slower.
 __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ nodes, const uint32_t *__restrict__ rootidx, uint32_t nL,
                                                  const double *__restrict__ tx, const double *__restrict__ ty, const double *__restrict__ tz,
                                                  const double *__restrict__ tm, double G, double eps2, const uint32_t *__restrict__ perm,
@@ -411,10 +407,6 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
             const uint32_t left = (uint32_t)(__double_as_longlong(c.y) & 0xffffffffll);
             const uint32_t start = (uint32_t)((unsigned long long)__double_as_longlong(c.y) >> 32);
             const uint32_t end = d.x, next = d.y;
-            if (PF) {
-                if (next != NOCHILD) asm volatile("prefetch.global.L1 [%0];" ::"l"(nodes + next));
-                if (left != NOCHILD) asm volatile("prefetch.global.L1 [%0];" ::"l"(nodes + left));
-            }
             if (wait == cur) wait = PT_ACTIVE;
             const bool act = mine && wait == PT_ACTIVE;
             const double dx = __dsub_rn(a.x, x), dy = __dsub_rn(a.y, y), dz = __dsub_rn(b.x, z);
@@ -640,12 +632,7 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             if (n1 > n0) VR_LAUNCH(ctx, k_pt_next, grid_for(n1 - n0, T), T, 0, nleft.p, next.p, n0, n1);
         }
         VR_LAUNCH(ctx, k_pt_pack, grid_for(nnodes, T), T, 0, N, next.p, nnodes, packed.p);
-        static const bool walk_prefetch = [] { const char *e = getenv("VRGPU_WALK_PREFETCH"); return e && atoi(e) == 1; }();
-        if (walk_prefetch)
-            VR_LAUNCH(ctx, k_pt_walk<true>, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p,
-                      slot_of.p, phi, ninter.p);
-        else
-        VR_LAUNCH(ctx, k_pt_walk<false>, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
+        VR_LAUNCH(ctx, k_pt_walk, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
                   phi, ninter.p);
     }
     unsigned long long hi = 0;
