@@ -146,6 +146,16 @@ int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const lo
                     const long long *index, double G, double eps, double theta, int bucket,
                     long long pp_threshold, double *phi_out);
 
+/* The particle order of the reference's kd-tree.  Replaces what NBody::KDTree::KDTree / BuildNodes leave in the
+ * particle array they are built on (NBodylib/src/KDTree/KDTree.cxx:637-674, 438-507): split dimension = largest spread (first
+ * wins), median index start + (size-1)/2 found by MedianPos (:304-337, a quickselect whose swap sequence decides the order --
+ * and, among exactly equal coordinates, the membership -- of both halves), leaves of at most `bucket` particles.  Every group
+ * of the CSR (as in vrgpu_potential; no empty groups) is a tree of its own: perm_out[offsets[g] + j] = offset inside group g of
+ * the member that sits at tree position j.  The potentials (vrgpu_potential, vrgpu_unbind) and the local velocity density use
+ * this build; the entry point exists so that parity with the reference's arrangement can be checked directly. */
+int vrgpu_tree_order(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const long long *index, int bucket,
+                     long long *perm_out);
+
 /* Binding energies of finished groups.  Replaces GetBindingEnergy
  * (src/substructureproperties.cxx:3884-4255) for the default reference frame (ParticleTypeForRefenceFrame = -1, no
  * per-type mass weights).  The view holds the particles in group order: group g (0-based) = records

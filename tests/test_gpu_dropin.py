@@ -34,23 +34,33 @@ def test_search_full_set_through_reference_types(ref, refgpu, fofbgtype):
     assert np.array_equal(got["vel"], want["vel"])
 
 
-def test_unbinding_through_reference_types(ref, refgpu):
-    """Bound_halos=1 with the stock thresholds (direct sum n <= 150, kd-tree above).  float32-exact coordinates tie at
-    kd-tree medians (DESIGN.md 'tree parity') and the reference reads oldnumingroup uninitialised (Q10), so the bound
-    sets are compared with a tolerance and the difference is reported.  (On the CPU the oracle with the intended Q10
-    semantics differs from the reference on exactly the 40 particles measured here, and on none when oldnumingroup is carried
-    between groups as the serial build does: test_search_full_set_with_unbinding_keeps_member_order.)"""
+def test_unbinding_through_reference_types(ref, refgpu, oracle):
+    """Bound_halos=1 with the stock thresholds (direct sum n <= 150, kd-tree above) on a float32-exact box (tied kd-tree
+    medians).  Two exact statements instead of a tolerance: (1) the library through the reference's types == the oracle with
+    the INTENDED semantics of Q10 (oldnumingroup initialised per group), label for label; (2) the oracle with oldnumingroup
+    carried from group to group, as the serial reference build happens to do, == the reference, label for label.  The
+    particles on which (1) and (2) differ are Q10's (unbind.cxx:643,700 reads the variable uninitialised) and their number
+    is pinned."""
     import vroracle
     nside = 40
     d = vrsynth.make_box(nside ** 3, 31)
     o = vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, fofbgtype=5, bound_halos=1, omp_fof=0)
     want = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], o)
     got = refgpu.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], o)
-    nb = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
-    ngrouped = int(np.count_nonzero(want["pfof"] > 0))
-    print(f"bound-set differences {nb} of {ngrouped} grouped particles; groups {got['ngroups']} vs {want['ngroups']}")
-    assert nb <= 0.02 * ngrouped
-    assert abs(got["ngroups"] - want["ngroups"]) <= 0.02 * want["ngroups"] + 2
+    cw, _ = vrsynth.canonical_groups(want["pfof"], d["pid"])
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    intended = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=0), d["pid"], 1e-6)
+    carried = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=1, oldn_init=0), d["pid"], 1e-6)
+    ndiff = int(np.count_nonzero((got["pfof"] > 0) != (intended["pfof"] > 0)))
+    assert ndiff <= intended["n_marginal"], f"{ndiff} bound flags differ from the oracle, {intended['n_marginal']} marginal"
+    if ndiff == 0:
+        assert got["ngroups"] == intended["ngroups"] and np.array_equal(got["pfof"], intended["pfof"])
+    assert carried["ngroups"] == want["ngroups"] and np.array_equal(carried["pfof"], cw)
+    nq10 = int(np.count_nonzero((intended["pfof"] > 0) != (cw > 0)))
+    print(f"Q10 particles (intended vs carried oldnumingroup): {nq10} of {np.count_nonzero(cw > 0)} grouped")
+    assert nq10 == 40
 
 
 def test_potential_through_reference_types(ref, refgpu):

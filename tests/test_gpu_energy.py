@@ -75,9 +75,7 @@ def test_binding_energy_box_matches_oracle(gpu_ctx, oracle, nside, seed, large):
     import vrgpu
     import vroracle
     d = vrsynth.make_box(nside ** 3, seed)
-    # float32-exact coordinates tie at kd-tree medians, where the reference's quickselect and the device build may split a
-    # cell differently (tests/test_gpu_tree.py measures that case on its own): de-quantise, as tests/test_oracle_vs_ref.py does
-    d["pos"] = np.mod(d["pos"] + np.random.default_rng(seed).random(d["pos"].shape) * 1e-7, vrsynth.BOX)
+    # float32-exact coordinates as generated: tied kd-tree medians included (the device build runs the reference's selection)
     ell = vrsynth.BOX / nside
     b = float(np.sqrt((ell * ell) * (0.2 * 0.2) * (1.0 * 1.0)))
     pfof, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
@@ -168,7 +166,7 @@ def test_sort_by_binding_energy_through_reference_types(ref, oracle, by_energy):
     refgpu = vroracle.Ref("gpu")
     nside = 48
     d = vrsynth.make_box(nside ** 3, 21)
-    pos0 = np.mod(d["pos"] + np.random.default_rng(4).random(d["pos"].shape) * 1e-7, vrsynth.BOX)
+    pos0 = d["pos"]
     pf, ng = oracle.fof3d(pos0, 0.2 * vrsynth.BOX / nside, vrsynth.BOX, 20, d["pid"])
     pos = oracle.adjust_for_period(pos0, vrsynth.BOX, pf, ng)
     ro = vroracle.default_opts(period=vrsynth.BOX, iterate_cm=1, sort_by_binding_energy=by_energy, eps=0.01)

@@ -1,10 +1,10 @@
-"""GPU parity: kd-tree monopole potentials (vrgpu_potential with n > pp_threshold) against the oracle restatement of
-Potential() (unbind.cxx:1607-1741), which itself is pinned to the reference at 1e-12 (tests/test_oracle_vs_ref.py).
+"""GPU parity: the kd-tree build (vrgpu_tree_order) and the kd-tree monopole potentials (vrgpu_potential with
+n > pp_threshold, row a15) against the oracle restatement of BuildNodes / MedianPos (KDTree.cxx:438-507, 304-337) and of Potential()
+(unbind.cxx:1607-1741), which itself is pinned to the compiled reference bit for bit on tied inputs (tests/test_oracle_vs_ref.py).
 
-Tolerance: BASELINE.json asks 1e-6 relative "against its tree at identical settings"; asserted here at 1e-10 on inputs whose
-coordinates are distinct (node membership is then unique).  With exactly tied coordinates at a median the reference's
-quickselect picks by swap history; the GPU build picks the lower member index, so a few cells differ by one particle:
-that case is measured separately and bounded by the monopole truncation error."""
+Tolerance: BASELINE.json asks 1e-6 relative "against its tree at identical settings"; asserted here at 1e-10 with IDENTICAL
+interaction counts, on distinct coordinates and on float32-quantised ones alike: the device build runs the reference's
+quickselect swap for swap, so node membership and particle order are the reference's for every input (bit-exact arrangement)."""
 import os
 
 import numpy as np
@@ -60,50 +60,63 @@ def test_tree_settings(gpu_ctx, oracle, theta, bucket):
     assert np.max(np.abs(phi / ref - 1.0)) < 1e-10
 
 
-def test_tree_with_tied_coordinates(gpu_ctx, oracle):
-    """float32-quantised positions (what a Gadget snapshot holds): ties at split medians make the reference's node
-    membership depend on its quickselect history.  Most particles still agree to 1e-10; the rest stay inside the
-    monopole truncation error."""
+def _quantised(n, rng, scale):
+    return _clustered(n, rng, scale).astype(np.float32).astype(np.float64)
+
+
+@pytest.mark.parametrize("n,scale,bucket", [(9, 1.0, 8), (40, 0.5, 8), (1500, 0.001, 8), (2048, 0.01, 8), (2049, 0.01, 8), (6000, 0.01, 16),
+                                            (30000, 0.5, 8), (200000, 0.05, 8), (1000000, 0.2, 8)])
+def test_tree_order_is_the_references(gpu_ctx, oracle, n, scale, bucket):
+    """Row a2: the particle order BuildNodes leaves, position for position (sizes on both sides of the 2048-particle
+    shared-memory subtree, float32-quantised coordinates with exactly tied values along every axis from ~10^4 on)."""
     import vrgpu
     rng = np.random.default_rng(8)
-    n = 30000
-    pos = _clustered(n, rng, 0.5).astype(np.float32).astype(np.float64)
-    mass = np.ones(n)
-    parts = vrgpu.particles_from_arrays(pos, mass=mass)
-    eps = 1e-3  # coincident float32 positions exist: keep every term finite
-    phi = gpu_ctx.potential(parts, np.array([0, n]), np.arange(n), G, eps=eps, pp_threshold=150)
-    ref, _ = oracle.potential_tree(pos, mass, G, eps, 0.5, 8)
-    pp = oracle.potential_pp(pos, mass, G, eps)
-    rel = np.abs(phi / ref - 1.0)
-    print("tied-coordinate case: frac(|dphi/phi| > 1e-6) =", float(np.mean(rel > 1e-6)), "max", float(rel.max()))
-    assert np.max(np.abs(phi / pp - 1.0)) < 5e-2
-    assert rel.max() < 1e-2  # same order as the tree's own truncation error; NOT the 1e-10 of the tie-free case
+    pos = _quantised(n, rng, scale)
+    parts = vrgpu.particles_from_arrays(pos)
+    got = gpu_ctx.tree_order(parts, np.array([0, n]), np.arange(n), bucket=bucket)
+    want, _ = oracle.tree_order(pos, bucket)
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, f"{bad.size} of {n} tree positions differ, first at {bad[:5]}"
+
+
+def test_tree_order_many_groups_any_order(gpu_ctx, oracle):
+    """Several trees in the same launches, group sizes in no particular order, members handed over through an index list."""
+    import vrgpu
+    rng = np.random.default_rng(9)
+    sizes = [700, 9000, 30, 5000, 2500, 2049, 2048, 151, 150, 40, 20000, 3]
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    pos = np.concatenate([_quantised(s, rng, 0.02) + 3.0 * k for k, s in enumerate(sizes)])
+    n = len(pos)
+    shuffle = rng.permutation(n)                      # the view holds the particles in another order than the groups
+    parts = vrgpu.particles_from_arrays(pos[shuffle])
+    index = np.argsort(shuffle)                       # index[k] = where group-ordered particle k sits in the view
+    got = gpu_ctx.tree_order(parts, off, index, bucket=8)
+    for g, s in enumerate(sizes):
+        want, _ = oracle.tree_order(pos[off[g]:off[g + 1]], 8)
+        assert np.array_equal(got[off[g]:off[g + 1]], want), (g, s)
 
 
 @pytest.mark.parametrize("n,scale", [(30000, 0.5), (200000, 0.05), (1500, 0.001)])
-def test_tree_with_tied_coordinates_exact(gpu_ctx, oracle, monkeypatch, n, scale):
-    """VRGPU_TREE_TIES=1 (csrc/qsel.cuh): every node is arranged by the reference's own MedianPos iterations, so the tied
-    case meets the bar of the tie-free one -- same cells opened, same leaves, potentials at 1e-10.  The emulation of the
-    same per-thread source is pinned against the oracle's arrangement on the CPU (tests/test_qsel_host.py)."""
+def test_tree_with_tied_coordinates(gpu_ctx, oracle, n, scale):
+    """float32-quantised positions (what a Gadget snapshot holds, gadgetio.cxx:258,770): ties at split medians make the
+    reference's node membership depend on its quickselect history.  Same cells opened, same leaves, potentials at 1e-10."""
     import vrgpu
-    monkeypatch.setenv("VRGPU_TREE_TIES", "1")
     rng = np.random.default_rng(8)
-    pos = _clustered(n, rng, scale).astype(np.float32).astype(np.float64)
+    pos = _quantised(n, rng, scale)
     assert min(len(np.unique(pos[:, d])) for d in range(3)) < n
     mass = 0.5 + rng.random(n)
     parts = vrgpu.particles_from_arrays(pos, mass=mass)
-    eps = 1e-3
+    eps = 1e-3  # coincident float32 positions exist: keep every term finite
     phi = gpu_ctx.potential(parts, np.array([0, n]), np.arange(n), G, eps=eps, pp_threshold=150)
     ref, ninter = oracle.potential_tree(pos, mass, G, eps, 0.5, 8)
     assert gpu_ctx.stats()["n_tree_interactions"] == ninter
     assert np.max(np.abs(phi / ref - 1.0)) < 1e-10
 
 
-def test_tree_exact_ties_many_groups(gpu_ctx, oracle, monkeypatch):
-    """Several groups built in the same launches (sizes on both sides of QS_SMALL = 2048 and of the direct-sum threshold),
-    and a second bucket size."""
+def test_tree_ties_many_groups(gpu_ctx, oracle):
+    """Several groups built in the same launches (sizes on both sides of the 2048-particle subtree limit and of the direct-sum
+    threshold), and a second bucket size."""
     import vrgpu
-    monkeypatch.setenv("VRGPU_TREE_TIES", "1")
     rng = np.random.default_rng(9)
     sizes = [9000, 5000, 2500, 2049, 2048, 151, 150, 40]
     off = np.concatenate([[0], np.cumsum(sizes)])
@@ -125,9 +138,7 @@ def test_unbind_with_tree_potentials(gpu_ctx, oracle):
     import vroracle
     nside = 64
     d = vrsynth.make_box(nside ** 3, 7)
-    # de-quantise so that kd-tree membership is unique (see test_tree_with_tied_coordinates)
-    rng = np.random.default_rng(1)
-    pos0 = np.mod(d["pos"] + rng.random(d["pos"].shape) * 1e-7, vrsynth.BOX)
+    pos0 = d["pos"]                                   # float32-quantised, as generated: tied coordinates included
     b = 0.2 * vrsynth.BOX / nside
     pf, ng = oracle.fof3d(pos0, b, vrsynth.BOX, 20, d["pid"])
     pos = oracle.adjust_for_period(pos0, vrsynth.BOX, pf, ng)

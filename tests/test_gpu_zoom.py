@@ -14,9 +14,6 @@ pytestmark = pytest.mark.gpu
 
 def _inputs(n, seed=105):
     d = vrsynth.make_box(n, seed, single_halo=True)
-    # de-quantise: float32-exact coordinates tie at kd-tree medians (see test_gpu_tree.test_tree_with_tied_coordinates)
-    rng = np.random.default_rng(2)
-    d["pos"] = np.mod(d["pos"] + rng.random(d["pos"].shape) * 1e-7, vrsynth.BOX)
     ell = vrsynth.BOX / float(n) ** (1.0 / 3.0)
     return d, ell
 

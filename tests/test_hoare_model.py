@@ -152,3 +152,63 @@ def test_recursive_build_matches_with_ties():
         ties = sum(1 for (s, m, e, d) in na if pos[pa[m - 1], d] == pos[pa[m], d])
         if n >= 1000:
             assert ties > 0                                                 # medians do fall inside runs of equal coordinates
+
+
+def select_device_form(perm, X, k, start, end, nt=8):
+    """The iteration with the index arithmetic of the device kernels (csrc/ptree.cu, k_kd_big / ks_warp_select): both lists
+    ASCENDING, B read from its end (B_desc[m] = B_asc[nB-1-m]), M by an nt-ary search for the first failing pair, hi exclusive."""
+    p = perm
+    lo, hi = start, end
+    while lo + 1 < hi:
+        x = X[p[k]]
+        top = hi - 1
+        p[top], p[k] = p[k], p[top]
+        pos = np.arange(lo, top)
+        v = X[p[pos]]
+        An, Bn = pos[v >= x], pos[v <= x]
+        nA, nB = len(An), len(Bn)
+        mm = min(nA, nB)
+        a, b = 0, mm
+        while a < b:                                                        # k_kd_big's search
+            step = (b - a + nt - 1) // nt
+            first = nt
+            for t in range(nt):
+                m = a + t * step
+                if m < b and not (An[m] < Bn[nB - 1 - m]):
+                    first = t
+                    break
+            if first == nt:
+                a = a + ((b - a - 1) // step) * step + 1
+            else:
+                b, a = a + first * step, (a + (first - 1) * step + 1 if first else a)
+        M = a
+        M2 = 0                                                              # ks_warp_select's chunked count with early exit
+        for base in range(0, mm, 32):
+            c = sum(1 for m in range(base, min(base + 32, mm)) if An[m] < Bn[nB - 1 - m])
+            M2 += c
+            if c < 32:
+                break
+        assert M == M2
+        for m in range(M):
+            ia, ib = An[m], Bn[nB - 1 - m]
+            p[ia], p[ib] = p[ib], p[ia]
+        if M < nA and (M == 0 or An[M] < Bn[nB - M]):
+            istar = int(An[M])
+        elif M > 0:
+            istar = int(Bn[nB - M])
+        else:
+            istar = top
+        p[istar], p[top] = p[top], p[istar]
+        if istar >= k:
+            hi = istar
+        if istar <= k:
+            lo = istar + 1
+
+
+@pytest.mark.parametrize("nt", [2, 8, 1024])
+def test_device_index_arithmetic_reproduces_quickselect(nt):
+    for X, start, end, k, perm0 in _cases():
+        p1, p2 = perm0.copy(), perm0.copy()
+        select_reference(p1, X, k, start, end)
+        select_device_form(p2, X, k, start, end, nt=nt)
+        assert np.array_equal(p1, p2)

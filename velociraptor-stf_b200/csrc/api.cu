@@ -425,6 +425,25 @@ int vrgpu_potential(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const lo
     });
 }
 
+int vrgpu_tree_order(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const long long *index, int bucket,
+                     long long *perm_out)
+{
+    return guarded(ctx, [&] {
+        VR_REQUIRE(ngroups >= 0 && offsets && perm_out, VRGPU_EINVAL, "bad arguments");
+        CallTimer ct(ctx);
+        if (ngroups == 0) return;
+        VR_REQUIRE(offsets[ngroups] >= 0 && (offsets[ngroups] == 0 || index), VRGPU_EINVAL, "bad CSR");
+        for (long long g = 0; g < ngroups; g++) VR_REQUIRE(offsets[g + 1] > offsets[g], VRGPU_EINVAL, "empty group");
+        DeviceParticles P;
+        {
+            StageTimer t(ctx);
+            upload_view(ctx, view, false, false, false, P);
+            ctx->stats.h2d_ms += t.stop();
+        }
+        tree_order_csr_host(ctx, P, ngroups, offsets, index, bucket, perm_out);
+    });
+}
+
 int vrgpu_binding_energy(vrgpu_ctx *ctx, vrgpu_view view, long long ngroups, const long long *offsets, const double *gcmvel, double G,
                          double eps, double theta, int bucket, long long large_threshold, double *phi_out, double *E_out, double *T_out,
                          double *Pot_out, double *Efrac_out, long long *iminpot_out, long long *ibound_out)

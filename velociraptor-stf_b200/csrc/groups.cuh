@@ -35,6 +35,10 @@ unsigned long long potential_direct(vrgpu_ctx *ctx, const GroupSet &gs, double G
 void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, double theta, int bucket, long long pp_threshold,
                     double *phi);
 
+// the particle order NBody::KDTree::BuildNodes leaves in every group (bucket = leaf size): out[slot] = offset inside its group of
+// the member that sits at that tree position
+void tree_order_device(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long *out_dev);
+
 // BuildNumInGroup + BuildPGList (src/buildandsortarrays.cxx:11-16, 26-43) from device labels: numingroup_out[0..ngroups],
 // index_out = members of group 1, 2, ... in ascending particle index; returns the number of grouped particles
 long long pglist_device(vrgpu_ctx *ctx, const long long *pfof_dev, size_t n, long long ngroups, long long *numingroup_out,

@@ -5,23 +5,20 @@
 // spread (first wins), median index k = start + (size-1)/2, left child = the k-start+1 smallest along that dimension,
 // leaf when size <= BucketSize).
 //
-// Device design: every group above the direct-sum threshold is built in the SAME launches, level by level.
-//   * ranks: three global radix sorts give every particle its rank along x, y, z (ties -> member order);
-//   * a level = the "frontier" of current nodes, ordered by start.  Per level: segment index per particle (head flags +
-//     scan), per-node min/max per axis (ordered-integer atomics), split dimension, then ONE stable radix sort on the
-//     key (frontier index, rank along the node's split dimension) -- after it the first k-start+1 particles of each
-//     segment are the left child.  Finished leaves carry key (index, 0) and keep their place;
+// Device design: every group above the direct-sum threshold is built in the SAME launches.
+//   * nodes: the tree's shape follows from the group sizes alone (left child = ceil(size / 2) particles), so the node
+//     arrays are laid down first, level by level, without touching a particle;
+//   * arrangement: MedianPos itself (the reference's quickselect, swap for swap -- see "the reference's arrangement"
+//     below): nodes above 2048 particles by one CTA each in global memory, every subtree of at most 2048 particles by one
+//     CTA in shared memory.  Node membership AND particle order are the reference's for every input, tied coordinates
+//     (float32 snapshots) included;
 //   * node monopoles bottom-up (leaf sums sequentially in tree order, parents = sum of children: deterministic),
 //     Bmax by ordered-integer atomicMax along every particle's root-to-leaf path, cR2max = 4/3 Bmax^2 / theta^2;
 //   * walk: one warp per 32 particles consecutive in tree order; the warp walks the union of its lanes' paths without a
 //     stack (64-byte node records with a "next" link), each lane applying MarkCell's opening test r2 < cR2max in the
 //     reference's operation order and accumulating monopole and leaf terms in fp64 in the reference's visiting order.
-// Node MEMBERSHIP equals the reference's whenever the coordinates along a split dimension are distinct at the median
-// (the reference's quickselect leaves the choice among exactly equal coordinates to its swap sequence; here the tie
-// goes to the lower member index) -- see DESIGN.md "tree parity".
 #include "groups.cuh"
 #include "ptree.cuh"
-#include "qsel.cuh"
 #include "rsqrt.cuh"
 #include "ufhash.cuh"
 
@@ -83,27 +80,13 @@ __global__ void k_pt_roots(const uint32_t *__restrict__ off, const uint32_t *__r
     frontier[r] = r;
 }
 
-// ---- ranks along each axis --------------------------------------------------------------------------
-__global__ void k_pt_coord_keys(const double *__restrict__ c, const uint32_t *__restrict__ slot_of, uint32_t nL,
-                                uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
-{
-    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= nL) return;
-    keys[p] = pt_ord(c[slot_of[p]]);
-    vals[p] = p;
-}
-__global__ void k_pt_rank(const uint32_t *__restrict__ vals, uint32_t nL, uint32_t *__restrict__ rank)
-{
-    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p < nL) rank[vals[p]] = p;
-}
 __global__ void k_pt_iota(uint32_t *__restrict__ a, uint32_t n)
 {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p < n) a[p] = p;
 }
 
-// ---- one level ----------------------------------------------------------------------------------------
+// ---- tree position -> root node (head flags + scan) ---------------------------------------------------------
 __global__ void k_pt_heads(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ nstart, uint32_t nAct,
                            uint32_t *__restrict__ heads)
 {
@@ -119,147 +102,367 @@ __global__ void k_pt_fidx(const uint32_t *__restrict__ heads, const uint32_t *__
     if (p < nL) fidx[p] = excl[p] + heads[p] - 1u;
 }
 
-struct PtCols { const double *x, *y, *z; };
+// ---- the reference's arrangement: MedianPos itself (KDTree.cxx:304-337) on every node --------------------------------
+// BuildNodes splits a node with a quickselect (Hoare partition about the element AT the median index).  Which of several
+// particles with exactly equal split coordinate go left, and in which order every particle is handed to the next level,
+// follows from its swap sequence; float32 snapshots have such ties at most levels of a big group, and node membership
+// decides which cells the walk opens.  So the build runs MedianPos, not a sort.  One iteration on the positions [lo, hi)
+// of a node (pivot index k, pivot value x) is data parallel (tests/test_hoare_model.py pins this form against the literal
+// loop):
+//     swap p[k] <-> p[hi-1]
+//     A = positions of [lo, hi-1) with value >= x, ascending (where the upward scan stops)
+//     B = positions of [lo, hi-1) with value <= x, descending (where the downward scan stops)
+//     M = number of m with A[m] < B[m] (a prefix: A increases, B decreases);  swap p[A[m]] <-> p[B[m]] for m < M
+//     i* = A[M] if it exists and (M == 0 or A[M] < B[M-1]), else B[M-1] if M > 0, else hi-1;  swap p[i*] <-> p[hi-1]
+//     hi = i* if i* >= k;  lo = i* + 1 if i* <= k;  repeat while lo + 1 < hi
+// The tree SHAPE is a function of the group sizes alone (left child = ceil(size / 2) particles), so the node arrays are laid
+// down first; then every node above KD_SMALL particles is arranged by one CTA in global memory, level by level, and every
+// subtree of at most KD_SMALL particles is finished by one CTA in shared memory (one warp per node, sub-level by sub-level).
+// Particles travel as 32-byte records (x, y, z, member), so a scan reads one sector per particle and a swap moves two.
+constexpr uint32_t KD_SMALL = 2048;
+struct __align__(16) KdRec { double x, y, z; uint32_t member, pad; };
+static_assert(sizeof(KdRec) == 32, "one 32-byte sector per particle");
 
-// min / max per axis of every frontier node that will split (size > bucket)
-__global__ void __launch_bounds__(256) k_pt_minmax(PtCols C, const uint32_t *__restrict__ slot_of, const uint32_t *__restrict__ perm,
-                                                   const uint32_t *__restrict__ fidx, const uint32_t *__restrict__ frontier,
-                                                   const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend, uint32_t nL,
-                                                   uint32_t bucket, unsigned long long *__restrict__ mm /* 6 per frontier entry */)
+__global__ void k_kd_init_rec(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                              const uint32_t *__restrict__ slot_of, uint32_t nL, KdRec *__restrict__ rec)
 {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t f = NOCHILD;
-    double v[3] = {0, 0, 0};
-    if (p < nL) {
-        f = fidx[p];
-        const uint32_t nd = frontier[f];
-        if (nend[nd] - nstart[nd] > bucket) {
-            const uint32_t s = slot_of[perm[p]];
-            v[0] = C.x[s]; v[1] = C.y[s]; v[2] = C.z[s];
-        } else f = NOCHILD;
-    }
-    const uint32_t f0 = __shfl_sync(0xffffffffu, f, 0);
-    if (__all_sync(0xffffffffu, f == f0)) {
-        if (f0 == NOCHILD) return;
-        for (int k = 0; k < 3; k++) {
-            double mn = v[k], mx = v[k];
-            for (int o = 16; o; o >>= 1) {
-                mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-            }
-            if ((threadIdx.x & 31) == 0) { atomicMin(&mm[6 * (size_t)f0 + k], pt_ord(mn)); atomicMax(&mm[6 * (size_t)f0 + 3 + k], pt_ord(mx)); }
-        }
-    } else if (f != NOCHILD) {
-        for (int k = 0; k < 3; k++) { atomicMin(&mm[6 * (size_t)f + k], pt_ord(v[k])); atomicMax(&mm[6 * (size_t)f + 3 + k], pt_ord(v[k])); }
-    }
+    if (p >= nL) return;
+    const uint32_t s = slot_of[p];
+    KdRec r;
+    r.x = x[s]; r.y = y[s]; r.z = z[s]; r.member = p; r.pad = 0;
+    rec[p] = r;
+}
+__global__ void k_kd_perm(const KdRec *__restrict__ rec, uint32_t nL, uint32_t *__restrict__ perm)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < nL) perm[p] = rec[p].member;
 }
 
-// split flag + split dimension (KDTree.cxx:438-507: largest spread, the first dimension wins a tie)
-__global__ void k_pt_choose(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ nstart,
-                            const uint32_t *__restrict__ nend, uint32_t bucket, const unsigned long long *__restrict__ mm,
-                            uint32_t *__restrict__ splitflag, uint32_t *__restrict__ splitdim)
+// skeleton, one level: which nodes split; the nodes above KD_SMALL go to this level's list of CTA-arranged nodes, roots that
+// fit shared memory to the list of subtrees
+__global__ void k_kd_level_flags(const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend, uint32_t n0, uint32_t n1, uint32_t bucket,
+                                 int root_level, uint32_t *__restrict__ flags, uint32_t *__restrict__ big_list, uint32_t *__restrict__ sub_list,
+                                 uint32_t *__restrict__ counters /* [0] big of this level, [1] subtrees */)
 {
-    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= nF) return;
-    const uint32_t nd = frontier[f];
-    const bool sp = nend[nd] - nstart[nd] > bucket;
-    splitflag[f] = sp ? 1u : 0u;
-    uint32_t d = 0;
-    if (sp) {
-        double best = __dsub_rn(pt_unord(mm[6 * (size_t)f + 3]), pt_unord(mm[6 * (size_t)f]));
-        for (int k = 1; k < 3; k++) {
-            double s = __dsub_rn(pt_unord(mm[6 * (size_t)f + 3 + k]), pt_unord(mm[6 * (size_t)f + k]));
-            if (s > best) { best = s; d = k; }
-        }
-    }
-    splitdim[f] = d;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n0 + i >= n1) return;
+    const uint32_t nd = n0 + i, size = nend[nd] - nstart[nd];
+    const bool split = size > bucket;
+    flags[i] = split ? 1u : 0u;
+    if (!split) return;
+    if (size > KD_SMALL) big_list[atomicAdd(&counters[0], 1u)] = nd;
+    else if (root_level) sub_list[atomicAdd(&counters[1], 1u)] = nd;
 }
-
-__global__ void k_pt_level_keys(const uint32_t *__restrict__ perm, const uint32_t *__restrict__ fidx, const uint32_t *__restrict__ splitflag,
-                                const uint32_t *__restrict__ splitdim, const uint32_t *__restrict__ rank /* 3 x nL */, uint32_t nL,
-                                uint32_t nAct, int rb, uint64_t *__restrict__ keys)
+__global__ void k_kd_level_children(uint32_t n0, uint32_t n1, const uint32_t *__restrict__ flags, const uint32_t *__restrict__ excl, uint32_t bucket,
+                                    uint32_t *__restrict__ nstart, uint32_t *__restrict__ nend, uint32_t *__restrict__ nleft,
+                                    uint32_t *__restrict__ sub_list, uint32_t *__restrict__ counters)
 {
-    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= nAct) return;
-    const uint32_t f = fidx[p];
-    uint32_t lo = 0;
-    if (splitflag[f]) lo = rank[(size_t)splitdim[f] * nL + perm[p]];
-    keys[p] = ((uint64_t)f << rb) | lo;
-}
-
-// children of the splitting nodes + next frontier (ordered by start)
-__global__ void k_pt_children(const uint32_t *__restrict__ frontier, uint32_t nF, const uint32_t *__restrict__ splitflag,
-                              const uint32_t *__restrict__ sexcl, uint32_t node_base, uint32_t *__restrict__ nstart,
-                              uint32_t *__restrict__ nend, uint32_t *__restrict__ nleft, uint32_t *__restrict__ next_frontier)
-{
-    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= nF) return;
-    const uint32_t nd = frontier[f];
-    const uint32_t k = sexcl[f];
-    if (!splitflag[f]) { next_frontier[f + k] = nd; return; }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n0 + i >= n1 || !flags[i]) return;
+    const uint32_t nd = n0 + i;
     const uint32_t s = nstart[nd], e = nend[nd];
     const uint32_t mid = s + (e - s - 1) / 2 + 1; // left = [s, k+1) with k = s + (size-1)/2
-    const uint32_t l = node_base + 2 * k, r = l + 1;
-    nleft[nd] = l;                                // right child = left + 1
+    const uint32_t l = n1 + 2 * excl[i], r = l + 1; // right child = left + 1
+    nleft[nd] = l;
     nstart[l] = s; nend[l] = mid; nleft[l] = NOCHILD;
     nstart[r] = mid; nend[r] = e; nleft[r] = NOCHILD;
-    next_frontier[f + k] = l;
-    next_frontier[f + k + 1] = r;
+    if (e - s > KD_SMALL) { // children that fit shared memory start a subtree
+        if (mid - s <= KD_SMALL && mid - s > bucket) sub_list[atomicAdd(&counters[1], 1u)] = l;
+        if (e - mid <= KD_SMALL && e - mid > bucket) sub_list[atomicAdd(&counters[1], 1u)] = r;
+    }
 }
 
-// ---- VRGPU_TREE_TIES=1: the reference's quickselect arrangement instead of the sort (qsel.cuh) ---------------------
-__global__ void k_qs_init(qsel::Level L)
+__device__ __forceinline__ void kd_swap_rec(KdRec *rec, uint32_t a, uint32_t b)
 {
-    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < L.nF) qsel::init_thread(L, f);
+    uint4 *pa = reinterpret_cast<uint4 *>(rec + a), *pb = reinterpret_cast<uint4 *>(rec + b);
+    const uint4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];
+    pa[0] = b0; pa[1] = b1; pb[0] = a0; pb[1] = a1;
 }
-__global__ void k_qs_begin(qsel::Level L)
+__device__ __forceinline__ double kd_coord(const KdRec *rec, uint32_t p, int d) { return reinterpret_cast<const double *>(rec + p)[d]; }
+
+// One CTA arranges one node of more than KD_SMALL particles in global memory.  A, B: scratch of nL entries each (a node uses
+// the entries of its own position range).  No __restrict__ / __ldg on rec: the CTA re-reads what it wrote.
+constexpr int KB_NT = 1024, KB_ITEMS = 4, KB_TILE = KB_NT * KB_ITEMS;
+__global__ void __launch_bounds__(KB_NT) k_kd_big(KdRec *rec, const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend,
+                                                  const uint32_t *__restrict__ list, uint32_t *A, uint32_t *B)
 {
-    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < L.nF) qsel::begin_thread(L, f);
-}
-__global__ void k_qs_flag(qsel::Level L)
-{
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < L.W + 1u) qsel::flag_thread(L, w);
-}
-__global__ void k_qs_scatter(qsel::Level L)
-{
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < L.W) qsel::scatter_thread(L, w);
-}
-__global__ void k_qs_match(qsel::Level L)
-{
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < L.W) qsel::match_thread(L, w);
-}
-__global__ void k_qs_end(qsel::Level L)
-{
-    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < L.nF) qsel::end_thread(L, f);
-}
-// nodes of at most QS_SMALL particles: a copy of the node in shared memory, MedianPos itself on one thread
-constexpr int QS_SMALL_THREADS = 64;
-constexpr size_t QS_SMALL_SMEM = (size_t)qsel::QS_SMALL * (sizeof(double) + sizeof(uint32_t));
-__global__ void __launch_bounds__(QS_SMALL_THREADS) k_qs_small(qsel::Level L)
-{
-    extern __shared__ __align__(8) unsigned char qs_smem[];
-    double *val = reinterpret_cast<double *>(qs_smem);
-    uint32_t *idx = reinterpret_cast<uint32_t *>(val + qsel::QS_SMALL);
-    for (uint32_t f = blockIdx.x; f < L.nF; f += gridDim.x) {
-        uint32_t s, e;
-        if (!qsel::small_node(L, f, s, e)) continue; // the same answer for the whole CTA
-        const uint32_t n = e - s, d = L.splitdim[f];
-        for (uint32_t i = threadIdx.x; i < n; i += QS_SMALL_THREADS) {
-            const uint32_t m = L.perm[s + i];
-            idx[i] = m;
-            val[i] = qsel::coord(L, d, m);
+    __shared__ double s_red[6][KB_NT / 32];
+    __shared__ uint32_t s_w[KB_NT / 32];
+    __shared__ uint32_t s_tot, s_first, s_lo, s_hi;
+    __shared__ double s_x;
+    __shared__ int s_dim;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t nd = list[blockIdx.x];
+    const uint32_t s = nstart[nd], e = nend[nd];
+    // ---- split dimension: largest spread, the first dimension wins a tie (KDTree.cxx:463-503) ----
+    {
+        double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+        for (uint32_t p = s + tid; p < e; p += KB_NT) {
+            const double2 a = *reinterpret_cast<const double2 *>(rec + p);
+            const double c = rec[p].z;
+            mn[0] = fmin(mn[0], a.x); mx[0] = fmax(mx[0], a.x);
+            mn[1] = fmin(mn[1], a.y); mx[1] = fmax(mx[1], a.y);
+            mn[2] = fmin(mn[2], c); mx[2] = fmax(mx[2], c);
+        }
+        for (int k = 0; k < 3; k++) {
+            for (int o = 16; o; o >>= 1) {
+                mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+                mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+            }
+            if (lane == 0) { s_red[k][warp] = mn[k]; s_red[3 + k][warp] = mx[k]; }
         }
         __syncthreads();
-        if (threadIdx.x == 0) qsel::select_serial(val, idx, qsel::median_index(s, e) - s, n);
+        if (tid == 0) {
+            double lo3[3], hi3[3];
+            for (int k = 0; k < 3; k++) {
+                lo3[k] = s_red[k][0]; hi3[k] = s_red[3 + k][0];
+                for (int w = 1; w < KB_NT / 32; w++) { lo3[k] = fmin(lo3[k], s_red[k][w]); hi3[k] = fmax(hi3[k], s_red[3 + k][w]); }
+            }
+            int d = 0;
+            double best = __dsub_rn(hi3[0], lo3[0]);
+            for (int k = 1; k < 3; k++) {
+                const double sp = __dsub_rn(hi3[k], lo3[k]);
+                if (sp > best) { best = sp; d = k; }
+            }
+            s_dim = d;
+            s_lo = s; s_hi = e;
+        }
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < n; i += QS_SMALL_THREADS) L.perm[s + i] = idx[i];
+    }
+    const int d = s_dim;
+    const uint32_t k = s + (e - s - 1) / 2;
+    uint32_t lo = s, hi = e;
+    uint32_t *An = A + s, *Bn = B + s;
+    while (lo + 1 < hi) {
+        if (tid == 0) {
+            s_x = kd_coord(rec, k, d);
+            if (k != hi - 1) kd_swap_rec(rec, k, hi - 1);
+        }
         __syncthreads();
+        const double x = s_x;
+        const uint32_t top = hi - 1; // the scans cover [lo, top)
+        // ---- the two lists (both ascending; B is read from its end) ----
+        uint32_t nA = 0, nB = 0;
+        double v[KB_ITEMS];
+#pragma unroll
+        for (int j = 0; j < KB_ITEMS; j++) {
+            const uint32_t p = lo + tid * KB_ITEMS + j;
+            v[j] = p < top ? kd_coord(rec, p, d) : 0.0;
+        }
+        for (uint32_t base = lo; base < top; base += KB_TILE) {
+            double vn[KB_ITEMS];
+            const uint32_t nbase = base + KB_TILE;
+#pragma unroll
+            for (int j = 0; j < KB_ITEMS; j++) { // the next tile's loads leave before this tile's scan
+                const uint32_t p = nbase + tid * KB_ITEMS + j;
+                vn[j] = (nbase < top && p < top) ? kd_coord(rec, p, d) : 0.0;
+            }
+            const uint32_t p0 = base + tid * KB_ITEMS;
+            unsigned fa = 0, fb = 0;
+#pragma unroll
+            for (int j = 0; j < KB_ITEMS; j++)
+                if (p0 + j < top) { fa |= (v[j] >= x ? 1u : 0u) << j; fb |= (v[j] <= x ? 1u : 0u) << j; }
+            // exclusive scan over the CTA of (count A | count B << 16): at most 4096 each per tile
+            const uint32_t mine = (uint32_t)__popc(fa) | ((uint32_t)__popc(fb) << 16);
+            uint32_t incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= (unsigned)o) incl += y;
+            }
+            if (lane == 31) s_w[warp] = incl;
+            __syncthreads();
+            if (warp == 0) {
+                const uint32_t wv = s_w[lane];
+                uint32_t wi = wv;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, wi, o);
+                    if (lane >= (unsigned)o) wi += y;
+                }
+                s_w[lane] = wi - wv;
+                if (lane == 31) s_tot = wi;
+            }
+            __syncthreads();
+            const uint32_t excl = s_w[warp] + incl - mine, tot = s_tot;
+            uint32_t ea = nA + (excl & 0xffffu), eb = nB + (excl >> 16);
+#pragma unroll
+            for (int j = 0; j < KB_ITEMS; j++) {
+                if ((fa >> j) & 1u) An[ea++] = p0 + j;
+                if ((fb >> j) & 1u) Bn[eb++] = p0 + j;
+            }
+            nA += tot & 0xffffu; nB += tot >> 16;
+#pragma unroll
+            for (int j = 0; j < KB_ITEMS; j++) v[j] = vn[j];
+            __syncthreads(); // s_w / s_tot are rewritten by the next tile
+        }
+        // ---- M = first m with !(A[m] < B[nB-1-m]) (the predicate holds on a prefix): KB_NT-ary search ----
+        const uint32_t mm = nA < nB ? nA : nB;
+        uint32_t a = 0, b = mm;
+        while (a < b) {
+            const uint32_t step = (b - a + KB_NT - 1) / KB_NT;
+            const uint32_t m = a + tid * step;
+            const bool fail = m < b && !(An[m] < Bn[nB - 1 - m]);
+            const unsigned bal = __ballot_sync(0xffffffffu, fail);
+            if (lane == 0) s_w[warp] = bal ? warp * 32 + (uint32_t)__ffs(bal) - 1u : (uint32_t)KB_NT;
+            __syncthreads();
+            if (warp == 0) {
+                const unsigned has = __ballot_sync(0xffffffffu, s_w[lane] != (uint32_t)KB_NT);
+                if (lane == 0) s_first = has ? s_w[__ffs(has) - 1] : (uint32_t)KB_NT;
+            }
+            __syncthreads();
+            const uint32_t first = s_first;
+            if (first == (uint32_t)KB_NT) a = a + ((b - a - 1) / step) * step + 1; // every probe holds: M lies behind the last one
+            else { b = a + first * step; if (first) a = a + (first - 1) * step + 1; }
+            __syncthreads(); // s_w / s_first are rewritten by the next round
+        }
+        const uint32_t M = a;
+        for (uint32_t m = tid; m < M; m += KB_NT) kd_swap_rec(rec, An[m], Bn[nB - 1 - m]);
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t istar;
+            if (M < nA && (M == 0 || An[M] < Bn[nB - M])) istar = An[M];
+            else if (M > 0) istar = Bn[nB - M];
+            else istar = top;
+            if (istar != top) kd_swap_rec(rec, istar, top);
+            uint32_t nlo = lo, nhi = hi;
+            if (istar >= k) nhi = istar;
+            if (istar <= k) nlo = istar + 1;
+            s_lo = nlo; s_hi = nhi;
+        }
+        __syncthreads();
+        lo = s_lo; hi = s_hi;
+    }
+}
+
+// One CTA finishes one subtree of at most KD_SMALL particles in shared memory: columns + member (SoA, conflict-free scans),
+// one warp per node, sub-level by sub-level.
+constexpr int KS_NT = 256, KS_NW = KS_NT / 32, KS_LIST = KD_SMALL / 2;
+struct KsShared {
+    double x[KD_SMALL], y[KD_SMALL], z[KD_SMALL];
+    uint32_t member[KD_SMALL];
+    uint16_t A[KD_SMALL], B[KD_SMALL];
+    uint16_t ls[2][KS_LIST], le[2][KS_LIST];
+    uint32_t ncur, nnext;
+};
+__device__ __forceinline__ void ks_swap(KsShared &S, uint32_t a, uint32_t b)
+{
+    const double ax = S.x[a], ay = S.y[a], az = S.z[a];
+    const uint32_t am = S.member[a];
+    S.x[a] = S.x[b]; S.y[a] = S.y[b]; S.z[a] = S.z[b]; S.member[a] = S.member[b];
+    S.x[b] = ax; S.y[b] = ay; S.z[b] = az; S.member[b] = am;
+}
+// MedianPos on the node [s, e) by one warp; all lanes hold the same lo / hi / counts
+__device__ __forceinline__ void ks_warp_select(KsShared &S, const uint32_t s, const uint32_t e, const unsigned lane)
+{
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (uint32_t p = s + lane; p < e; p += 32) {
+        mn[0] = fmin(mn[0], S.x[p]); mx[0] = fmax(mx[0], S.x[p]);
+        mn[1] = fmin(mn[1], S.y[p]); mx[1] = fmax(mx[1], S.y[p]);
+        mn[2] = fmin(mn[2], S.z[p]); mx[2] = fmax(mx[2], S.z[p]);
+    }
+    int d = 0;
+    double best = 0;
+    for (int k = 0; k < 3; k++) {
+        for (int o = 16; o; o >>= 1) {
+            mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+        const double sp = __dsub_rn(mx[k], mn[k]);
+        if (k == 0 || sp > best) { best = sp; d = k; }
+    }
+    const double *val = d == 0 ? S.x : (d == 1 ? S.y : S.z);
+    const uint32_t k = s + (e - s - 1) / 2;
+    const unsigned lt = (1u << lane) - 1u;
+    uint32_t lo = s, hi = e;
+    uint16_t *An = S.A + s, *Bn = S.B + s;
+    while (lo + 1 < hi) {
+        const double x = val[k];
+        const uint32_t top = hi - 1;
+        __syncwarp();
+        if (lane == 0 && k != top) ks_swap(S, k, top);
+        __syncwarp();
+        uint32_t nA = 0, nB = 0;
+        for (uint32_t base = lo; base < top; base += 32) {
+            const uint32_t p = base + lane;
+            const bool in = p < top;
+            const double v = in ? val[p] : 0.0;
+            const bool ge = in && v >= x, le = in && v <= x;
+            const unsigned ba = __ballot_sync(0xffffffffu, ge), bb = __ballot_sync(0xffffffffu, le);
+            if (ge) An[nA + __popc(ba & lt)] = (uint16_t)p;
+            if (le) Bn[nB + __popc(bb & lt)] = (uint16_t)p;
+            nA += __popc(ba); nB += __popc(bb);
+        }
+        __syncwarp();
+        const uint32_t mm = nA < nB ? nA : nB;
+        uint32_t M = 0;
+        for (uint32_t base = 0; base < mm; base += 32) {
+            const uint32_t m = base + lane;
+            uint32_t pa = 0, pb = 0;
+            bool ok = false;
+            if (m < mm) { pa = An[m]; pb = Bn[nB - 1 - m]; ok = pa < pb; }
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (ok) ks_swap(S, pa, pb); // the swapped positions are pairwise distinct
+            const uint32_t c = (uint32_t)__popc(bal);
+            M += c;
+            if (c < 32) break;
+        }
+        __syncwarp();
+        uint32_t istar;
+        if (M < nA && (M == 0 || An[M] < Bn[nB - M])) istar = An[M];
+        else if (M > 0) istar = Bn[nB - M];
+        else istar = top;
+        __syncwarp();
+        if (lane == 0 && istar != top) ks_swap(S, istar, top);
+        __syncwarp();
+        if (istar >= k) hi = istar;
+        if (istar <= k) lo = istar + 1;
+    }
+}
+__global__ void __launch_bounds__(KS_NT) k_kd_small(KdRec *rec, const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend,
+                                                    const uint32_t *__restrict__ list, const uint32_t *__restrict__ count, uint32_t bucket)
+{
+    extern __shared__ __align__(16) unsigned char ks_raw[];
+    KsShared &S = *reinterpret_cast<KsShared *>(ks_raw);
+    if (blockIdx.x >= *count) return;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t nd = list[blockIdx.x];
+    const uint32_t g0 = nstart[nd], n = nend[nd] - g0;
+    for (uint32_t p = tid; p < n; p += KS_NT) {
+        const uint4 *q = reinterpret_cast<const uint4 *>(rec + g0 + p);
+        const uint4 a = q[0], b = q[1];
+        S.x[p] = __hiloint2double((int)a.y, (int)a.x);
+        S.y[p] = __hiloint2double((int)a.w, (int)a.z);
+        S.z[p] = __hiloint2double((int)b.y, (int)b.x);
+        S.member[p] = b.z;
+    }
+    if (tid == 0) { S.ls[0][0] = 0; S.le[0][0] = (uint16_t)n; S.ncur = n > bucket ? 1u : 0u; }
+    int cur = 0;
+    for (;;) {
+        __syncthreads();
+        const uint32_t ncur = S.ncur;
+        if (ncur == 0) break;
+        __syncthreads();
+        if (tid == 0) S.nnext = 0;
+        __syncthreads();
+        for (uint32_t i = warp; i < ncur; i += KS_NW) {
+            const uint32_t s = S.ls[cur][i], e = S.le[cur][i];
+            ks_warp_select(S, s, e, lane);
+            if (lane == 0) {
+                const uint32_t mid = s + (e - s - 1) / 2 + 1;
+                if (mid - s > bucket) { const uint32_t t = atomicAdd(&S.nnext, 1u); S.ls[cur ^ 1][t] = (uint16_t)s; S.le[cur ^ 1][t] = (uint16_t)mid; }
+                if (e - mid > bucket) { const uint32_t t = atomicAdd(&S.nnext, 1u); S.ls[cur ^ 1][t] = (uint16_t)mid; S.le[cur ^ 1][t] = (uint16_t)e; }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) S.ncur = S.nnext;
+        cur ^= 1;
+    }
+    for (uint32_t p = tid; p < n; p += KS_NT) {
+        KdRec r;
+        r.x = S.x[p]; r.y = S.y[p]; r.z = S.z[p]; r.member = S.member[p]; r.pad = 0;
+        rec[g0 + p] = r;
     }
 }
 
@@ -436,30 +639,22 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(ninter, cnt);
 }
 
-__global__ void k_pt_gather_tree(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
-                                 const double *__restrict__ m, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of, uint32_t nL,
+// tree-ordered columns: coordinates straight from the build's records, the mass through the member index
+__global__ void k_pt_gather_tree(const KdRec *__restrict__ rec, const double *__restrict__ m, const uint32_t *__restrict__ slot_of, uint32_t nL,
                                  double *__restrict__ tx, double *__restrict__ ty, double *__restrict__ tz, double *__restrict__ tm)
 {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= nL) return;
-    const uint32_t s = slot_of[perm[p]];
-    tx[p] = x[s]; ty[p] = y[s]; tz[p] = z[s]; tm[p] = m[s];
+    const KdRec r = rec[p];
+    tx[p] = r.x; ty[p] = r.y; tz[p] = r.z; tm[p] = m[slot_of[r.member]];
 }
 
-} // namespace
-
-namespace {
-__global__ void k_pt_mm_init(unsigned long long *__restrict__ mm, uint32_t nF)
-{
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < 6 * nF) mm[i] = (i % 6) < 3 ? ~0ull : 0ull;
-}
 } // namespace
 
 // The build shared by the potentials (below) and the local velocity density (veldens.cu): members of the groups above
 // pp_threshold in tree order (t.perm over compact member indices, t.slot_of to the group-major columns) and the nodes over
 // them, numbered level by level (right child = left + 1).  False when no group qualifies.
-bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_threshold, bool exact_ties, PtTree &t)
+bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_threshold, PtTree &t)
 {
     t.nL = t.nLG = t.nnodes = 0;
     t.level_off.clear();
@@ -483,105 +678,82 @@ bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_thres
     if (nL == 0) return false;
     slot_of.alloc(ctx, nL);
     VR_LAUNCH(ctx, k_pt_compact, grid_for(ntot, T), T, 0, flags.p, sexcl.p, ntot, slot_of.p);
+    flags.reset(); 
 
-    // ---- ranks along the three axes (ties: lower member first); exact_ties arranges every node with the reference's own
-    // selection instead (qsel.cuh) and needs none ----
-    perm.alloc(ctx, nL);
-    DBuf<uint32_t> rank(ctx, exact_ties ? 1 : 3 * (size_t)nL), vtmp(ctx, exact_ties ? 1 : nL);
-    DBuf<uint64_t> keys(ctx, exact_ties ? 1 : nL), ktmp(ctx, exact_ties ? 1 : nL);
-    if (!exact_ties) {
-        KScope k(ctx, "ptree.ranks");
-        const double *cols[3] = {gs.x.p, gs.y.p, gs.z.p};
-        for (int d = 0; d < 3; d++) {
-            VR_LAUNCH(ctx, k_pt_coord_keys, grid_for(nL, T), T, 0, cols[d], slot_of.p, nL, keys.p, perm.p);
-            radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nL, 64);
-            VR_LAUNCH(ctx, k_pt_rank, grid_for(nL, T), T, 0, perm.p, nL, rank.p + (size_t)d * nL);
-        }
-    }
-
-    // ---- nodes ----
+    // ---- the nodes: a function of the group sizes alone, laid down level by level ----
     const uint32_t minleaf = std::max(1u, ((uint32_t)bucket + 1u) / 2u);
     const size_t cap = 2 * ((size_t)nL / minleaf + 1) + nLG + 16;
     nstart.alloc(ctx, cap); nend.alloc(ctx, cap); nleft.alloc(ctx, cap);
     rootidx.alloc(ctx, nL);
-    DBuf<uint32_t> frontier(ctx, cap), frontier2(ctx, cap), splitflag(ctx, cap), splitdim(ctx, cap), fexcl(ctx, cap);
-    DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL), fidx(ctx, nL);
-    DBuf<unsigned long long> mm(ctx, 6 * cap);
-    // selection state of the exact-ties variant
-    const size_t qcap = exact_ties ? cap : 1, qn = exact_ties ? (size_t)nL + 1 : 1;
-    DBuf<uint32_t> qlo(ctx, qcap), qhi(ctx, qcap), qnp(ctx, qcap), qlen(ctx, qcap), qwoff(ctx, qcap), qtotal(ctx, 1);
-    DBuf<double> qpiv(ctx, qcap);
-    DBuf<unsigned long long> qflags(ctx, qn), qscan(ctx, qn);
-    DBuf<uint32_t> qwf(ctx, qn), qA(ctx, qn), qB(ctx, qn);
-    VR_LAUNCH(ctx, k_pt_roots, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, gflag.p, gexcl.p, sexcl.p, NG, ntot, nstart.p, nend.p, nleft.p, frontier.p);
-    VR_LAUNCH(ctx, k_pt_iota, grid_for(nL, T), T, 0, perm.p, nL);
-    uint32_t nF = nLG, nnodes = nLG;
-    level_off.assign({0u, nLG});
-    // A group's largest node at level l holds ceil(n / 2^l) particles (median splits), so the group is finished once that
-    // is <= bucket: the per-particle passes of a level only cover positions below the end of the last unfinished group
-    // (groups come in size order from the search stages, so this prefix shrinks level by level).
-    std::vector<uint32_t> gstart(nLG), gend(nLG);
-    VR_CUDA(cudaMemcpyAsync(gstart.data(), nstart.p, sizeof(uint32_t) * nLG, cudaMemcpyDeviceToHost, ctx->stream));
-    VR_CUDA(cudaMemcpyAsync(gend.data(), nend.p, sizeof(uint32_t) * nLG, cudaMemcpyDeviceToHost, ctx->stream));
-    VR_CUDA(cudaStreamSynchronize(ctx->stream));
-    auto active_prefix = [&](int level) {
-        uint32_t top = 0;
-        for (uint32_t r = 0; r < nLG; r++) {
-            const uint64_t n = gend[r] - gstart[r];
-            const uint64_t big = level < 40 ? ((n + (1ull << level) - 1) >> level) : 1;
-            if (big > (uint64_t)bucket) top = std::max(top, gend[r]);
+    perm.alloc(ctx, nL);
+    const size_t cap_list = 4 * ((size_t)nL / KD_SMALL + 1) + nLG + 64;
+    DBuf<uint32_t> big_list(ctx, cap_list), sub_list(ctx, cap_list), counters(ctx, 2), lflags, lexcl;
+    std::vector<uint32_t> big_off{0u}; // nodes above KD_SMALL of level l: big_list[big_off[l], big_off[l+1])
+    uint32_t nsub = 0, nnodes = nLG;
+    {
+        KScope kb(ctx, "ptree.nodes");
+        VR_LAUNCH(ctx, k_pt_roots, grid_for((size_t)NG + 1, T), T, 0, gs.off.p, gflag.p, gexcl.p, sexcl.p, NG, ntot, nstart.p, nend.p, nleft.p, perm.p /* unused frontier */);
+        {   // tree position -> root node
+            DBuf<uint32_t> heads(ctx, nL), hexcl(ctx, nL);
+            VR_CUDA(cudaMemsetAsync(heads.p, 0, sizeof(uint32_t) * nL, ctx->stream));
+            VR_LAUNCH(ctx, k_pt_iota, grid_for(nLG, T), T, 0, hexcl.p, nLG);
+            VR_LAUNCH(ctx, k_pt_heads, grid_for(nLG, T), T, 0, hexcl.p, nLG, nstart.p, nL, heads.p);
+            exclusive_scan_u32(ctx, heads.p, hexcl.p, nL, nullptr);
+            VR_LAUNCH(ctx, k_pt_fidx, grid_for(nL, T), T, 0, heads.p, hexcl.p, nL, rootidx.p);
         }
-        return top;
-    };
-    const int rb = bits_for_u64v(nL > 1 ? nL - 1 : 1);
-    PtCols C{gs.x.p, gs.y.p, gs.z.p};
-    uint32_t *fr = frontier.p, *fr2 = frontier2.p;
+        VR_CUDA(cudaMemsetAsync(counters.p, 0, 2 * sizeof(uint32_t), ctx->stream));
+        level_off.assign({0u, nLG});
+        for (int level = 0; level < 64; level++) {
+            const uint32_t n0 = level_off[level], n1 = level_off[level + 1];
+            if (n1 == n0) break;
+            const uint32_t cnt = n1 - n0;
+            lflags.alloc(ctx, cnt); lexcl.alloc(ctx, cnt);
+            VR_LAUNCH(ctx, k_kd_level_flags, grid_for(cnt, T), T, 0, nstart.p, nend.p, n0, n1, (uint32_t)bucket, level == 0 ? 1 : 0, lflags.p,
+                      big_list.p + big_off.back(), sub_list.p, counters.p);
+            exclusive_scan_u32(ctx, lflags.p, lexcl.p, cnt, total.p);
+            uint32_t h[3];
+            VR_CUDA(cudaMemcpyAsync(h, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            VR_CUDA(cudaMemcpyAsync(h + 1, counters.p, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            const uint32_t nsplit = h[0];
+            big_off.push_back(big_off.back() + h[1]);
+            VR_REQUIRE(big_off.back() <= cap_list, VRGPU_ECUDA, "kd-tree: node list capacity exceeded");
+            VR_CUDA(cudaMemsetAsync(counters.p, 0, sizeof(uint32_t), ctx->stream));
+            if (nsplit == 0) { nsub = h[2]; break; }
+            VR_REQUIRE((size_t)nnodes + 2 * (size_t)nsplit <= cap, VRGPU_ECUDA, "kd-tree node capacity exceeded");
+            VR_LAUNCH(ctx, k_kd_level_children, grid_for(cnt, T), T, 0, n0, n1, lflags.p, lexcl.p, (uint32_t)bucket, nstart.p, nend.p, nleft.p,
+                      sub_list.p, counters.p);
+            nnodes += 2 * nsplit;
+            level_off.push_back(nnodes);
+            // subtree roots so far are read back with the next level's counters; the last level has no children above the bucket
+        }
+        if (nsub == 0) { // the loop ended through its level limit or an empty level: read the subtree count
+            uint32_t h[2];
+            VR_CUDA(cudaMemcpyAsync(h, counters.p, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            nsub = h[1];
+        }
+        VR_REQUIRE(nsub <= cap_list, VRGPU_ECUDA, "kd-tree: subtree list capacity exceeded");
+    }
+
+    // ---- the arrangement: MedianPos on every node ----
     {
         KScope kb(ctx, "ptree.build");
-        for (int level = 0; level < 64; level++) {
-            const uint32_t nAct = level == 0 ? nL : active_prefix(level);
-            if (nAct == 0) break;
-            VR_CUDA(cudaMemsetAsync(heads.p, 0, sizeof(uint32_t) * nAct, ctx->stream));
-            VR_LAUNCH(ctx, k_pt_heads, grid_for(nF, T), T, 0, fr, nF, nstart.p, nAct, heads.p);
-            exclusive_scan_u32(ctx, heads.p, hexcl.p, nAct, nullptr);
-            VR_LAUNCH(ctx, k_pt_fidx, grid_for(nAct, T), T, 0, heads.p, hexcl.p, nAct, fidx.p);
-            if (level == 0) VR_CUDA(cudaMemcpyAsync(rootidx.p, fidx.p, sizeof(uint32_t) * nL, cudaMemcpyDeviceToDevice, ctx->stream));
-            VR_LAUNCH(ctx, k_pt_mm_init, grid_for((size_t)6 * nF, T), T, 0, mm.p, nF);
-            VR_LAUNCH(ctx, k_pt_minmax, grid_for(nAct, T), T, 0, C, slot_of.p, perm.p, fidx.p, fr, nstart.p, nend.p, nAct, (uint32_t)bucket, mm.p);
-            VR_LAUNCH(ctx, k_pt_choose, grid_for(nF, T), T, 0, fr, nF, nstart.p, nend.p, (uint32_t)bucket, mm.p, splitflag.p, splitdim.p);
-            exclusive_scan_u32(ctx, splitflag.p, fexcl.p, nF, total.p);
-            uint32_t nsplit = 0;
-            VR_CUDA(cudaMemcpyAsync(&nsplit, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-            VR_CUDA(cudaStreamSynchronize(ctx->stream));
-            if (nsplit == 0) break;
-            VR_REQUIRE((size_t)nnodes + 2 * (size_t)nsplit <= cap, VRGPU_ECUDA, "kd-tree node capacity exceeded");
-            if (exact_ties) {
-                qsel::Level L{gs.x.p, gs.y.p, gs.z.p, slot_of.p, perm.p, fr, nstart.p, nend.p, splitflag.p, splitdim.p, qlo.p, qhi.p,
-                              qnp.p, qlen.p, qwoff.p, qpiv.p, qwf.p, qflags.p, qscan.p, qA.p, qB.p, nF, 0u};
-                VR_LAUNCH(ctx, k_qs_init, grid_for(nF, T), T, 0, L);
-                VR_LAUNCH(ctx, k_qs_small, (unsigned)std::min<size_t>(nF, (size_t)148 * 64), QS_SMALL_THREADS, QS_SMALL_SMEM, L);
-                for (;;) { // one iteration of MedianPos for every node above QS_SMALL that is not finished
-                    exclusive_scan_u32(ctx, qlen.p, qwoff.p, nF, qtotal.p);
-                    VR_CUDA(cudaMemcpyAsync(&L.W, qtotal.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-                    VR_CUDA(cudaStreamSynchronize(ctx->stream));
-                    if (L.W == 0) break;
-                    VR_LAUNCH(ctx, k_qs_begin, grid_for(nF, T), T, 0, L);
-                    VR_LAUNCH(ctx, k_qs_flag, grid_for((size_t)L.W + 1, T), T, 0, L);
-                    exclusive_scan_u64(ctx, qflags.p, qscan.p, (size_t)L.W + 1, nullptr);
-                    VR_LAUNCH(ctx, k_qs_scatter, grid_for(L.W, T), T, 0, L);
-                    VR_LAUNCH(ctx, k_qs_match, grid_for(L.W, T), T, 0, L);
-                    VR_LAUNCH(ctx, k_qs_end, grid_for(nF, T), T, 0, L);
-                }
-            } else {
-                VR_LAUNCH(ctx, k_pt_level_keys, grid_for(nAct, T), T, 0, perm.p, fidx.p, splitflag.p, splitdim.p, rank.p, nL, nAct, rb, keys.p);
-                radix_sort_pairs(ctx, keys.p, perm.p, ktmp.p, vtmp.p, nAct, rb + bits_for_u64v(nF > 1 ? nF - 1 : 1));
+        t.rec.alloc(ctx, (size_t)nL * 4); // 32-byte records
+        KdRec *rec = reinterpret_cast<KdRec *>(t.rec.p);
+        VR_LAUNCH(ctx, k_kd_init_rec, grid_for(nL, T), T, 0, gs.x.p, gs.y.p, gs.z.p, slot_of.p, nL, rec);
+        if (big_off.back() > 0) {
+            DBuf<uint32_t> A(ctx, nL), B(ctx, nL);
+            for (size_t l = 0; l + 1 < big_off.size(); l++) {
+                const uint32_t nb = big_off[l + 1] - big_off[l];
+                if (nb) VR_LAUNCH(ctx, k_kd_big, nb, KB_NT, 0, rec, nstart.p, nend.p, big_list.p + big_off[l], A.p, B.p);
             }
-            VR_LAUNCH(ctx, k_pt_children, grid_for(nF, T), T, 0, fr, nF, splitflag.p, fexcl.p, nnodes, nstart.p, nend.p, nleft.p, fr2);
-            nnodes += 2 * nsplit;
-            nF += nsplit;
-            level_off.push_back(nnodes);
-            std::swap(fr, fr2);
         }
+        if (nsub) {
+            VR_CUDA(cudaFuncSetAttribute(k_kd_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(KsShared)));
+            VR_LAUNCH(ctx, k_kd_small, nsub, KS_NT, sizeof(KsShared), rec, nstart.p, nend.p, sub_list.p, counters.p + 1, (uint32_t)bucket);
+        }
+        VR_LAUNCH(ctx, k_kd_perm, grid_for(nL, T), T, 0, rec, nL, perm.p);
     }
     t.nL = nL;
     t.nLG = nLG;
@@ -593,10 +765,8 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
 {
     if (gs.ntot == 0 || gs.ngroups == 0 || pp_threshold < 0) return;
     VR_REQUIRE(theta > 0, VRGPU_EINVAL, "TreeThetaOpen must be positive");
-    // VRGPU_TREE_TIES=1 (read per call): arrange every node with the reference's own selection, see qsel.cuh
-    const bool exact_ties = [] { const char *e = getenv("VRGPU_TREE_TIES"); return e && atoi(e) == 1; }();
     PtTree t;
-    if (!pt_build(ctx, gs, bucket, pp_threshold, exact_ties, t)) return;
+    if (!pt_build(ctx, gs, bucket, pp_threshold, t)) return;
     const int T = 256;
     const uint32_t nL = t.nL, nLG = t.nLG, nnodes = t.nnodes;
     DBuf<uint32_t> &slot_of = t.slot_of, &perm = t.perm, &nstart = t.nstart, &nend = t.nend, &nleft = t.nleft, &rootidx = t.rootidx;
@@ -609,7 +779,8 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     PtNodes N{nstart.p, nend.p, nleft.p, sx.p, sy.p, sz.p, sm.p, bmax.p, r2max.p};
     {
         KScope k(ctx, "ptree.moments");
-        VR_LAUNCH(ctx, k_pt_gather_tree, grid_for(nL, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, perm.p, slot_of.p, nL, tx.p, ty.p, tz.p, tm.p);
+        VR_LAUNCH(ctx, k_pt_gather_tree, grid_for(nL, T), T, 0, reinterpret_cast<const KdRec *>(t.rec.p), gs.m.p, slot_of.p, nL, tx.p, ty.p, tz.p, tm.p);
+        t.rec.reset();
         VR_LAUNCH(ctx, k_pt_leaf_sums, grid_for(nnodes, T), T, 0, N, nnodes, tx.p, ty.p, tz.p, tm.p);
         for (size_t l = level_off.size() - 1; l-- > 0;) {
             const uint32_t n0 = level_off[l], n1 = level_off[l + 1];
@@ -640,6 +811,25 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->stats.n_tree_interactions += (long long)hi;
     ctx->stats.n_tree_nodes += (long long)nnodes;
+}
+
+namespace {
+__global__ void k_pt_order_out(const uint32_t *__restrict__ perm, const uint32_t *__restrict__ slot_of, const uint32_t *__restrict__ gid,
+                               const uint32_t *__restrict__ off, uint32_t nL, long long *__restrict__ out)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nL) return;
+    const uint32_t slot = slot_of[perm[p]];
+    out[slot_of[p]] = (long long)(slot - off[gid[slot]]); // trees cover their groups' slots in order: position p <-> slot_of[p]
+}
+} // namespace
+
+void tree_order_device(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long *out_dev)
+{
+    PtTree t;
+    if (!pt_build(ctx, gs, bucket, 0, t)) return;
+    VR_REQUIRE(t.nL == gs.ntot, VRGPU_ECUDA, "tree order: empty groups are not allowed");
+    VR_LAUNCH(ctx, k_pt_order_out, grid_for(t.nL, 256), 256, 0, t.perm.p, t.slot_of.p, gs.gid.p, gs.off.p, t.nL, out_dev);
 }
 
 } // namespace vrgpu

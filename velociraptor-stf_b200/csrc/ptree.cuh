@@ -14,11 +14,12 @@ struct PtTree {
     DBuf<uint32_t> perm;                        // tree position -> compact member index
     DBuf<uint32_t> nstart, nend, nleft;         // per node: tree positions [start, end), left child
     DBuf<uint32_t> rootidx;                     // tree position -> root node
+    DBuf<double> rec;                           // the build's 32-byte records in tree order: x, y, z, (member, 0) -- 4 doubles per position
     std::vector<uint32_t> level_off;            // nodes of level l: [level_off[l], level_off[l + 1])
 };
 
-// NBody::KDTree::BuildNodes (NBodylib/src/KDTree/KDTree.cxx:438-507) for every group of gs with more than pp_threshold members;
-// exact_ties selects the reference's MedianPos arrangement (qsel.cuh) instead of the sort (ties -> lower member index).
-bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_threshold, bool exact_ties, PtTree &t);
+// NBody::KDTree::BuildNodes (NBodylib/src/KDTree/KDTree.cxx:438-507) with MedianPos's own arrangement (:304-337) for every
+// group of gs with more than pp_threshold members.
+bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_threshold, PtTree &t);
 
 } // namespace vrgpu

@@ -33,6 +33,8 @@ void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngro
                         double *phi_out_host);
 
 // GetBindingEnergy (src/substructureproperties.cxx:3884-4255) for group-ordered particles (energy.cu)
+void tree_order_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                         const long long *index_host, int bucket, long long *perm_out_host);
 void binding_energy_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
                          const double *gcmvel_host, double G, double eps, double theta, int bucket, long long large_threshold,
                          double *phi_out, double *E_out, double *T_out, double *Pot_out, double *Efrac_out, long long *iminpot_out,

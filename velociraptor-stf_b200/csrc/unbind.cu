@@ -688,13 +688,12 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
     ctx->stats.unbind_ms += t.stop();
 }
 
-// vrgpu_potential: groups handed over in CSR form by the host
-void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
-                        const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,
-                        double *phi_out_host)
+// groups handed over in CSR form by the host (vrgpu_potential, vrgpu_tree_order) -> group-major layout
+static bool groupset_from_csr(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                              const long long *index_host, GroupSet &gs)
 {
     const long long ntot = offsets_host[ngroups];
-    if (ntot == 0) return;
+    if (ntot == 0) return false;
     VR_REQUIRE(ntot < 0xfffffff0LL && ngroups < 0x7fffffffLL, VRGPU_EINVAL, "CSR too large");
     VR_REQUIRE(offsets_host[0] == 0, VRGPU_EINVAL, "offsets[0] must be 0");
     std::vector<uint32_t> off((size_t)ngroups + 2), idx((size_t)ntot);
@@ -707,7 +706,6 @@ void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngro
         VR_REQUIRE(index_host[k] >= 0 && (size_t)index_host[k] < P.n, VRGPU_EINVAL, "index out of range");
         idx[(size_t)k] = (uint32_t)index_host[k];
     }
-    GroupSet gs;
     gs.ntot = (size_t)ntot;
     gs.ngroups = ngroups;
     gs.off.alloc(ctx, off.size());
@@ -717,12 +715,37 @@ void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngro
     VR_CUDA(cudaMemcpyAsync(gs.idx.p, idx.data(), idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     VR_LAUNCH(ctx, k_csr_gid, std::max(1u, std::min<unsigned>(grid_for((size_t)ngroups * 32, 256), (unsigned)ctx->sm_count * 16u)), 256, 0,
               gs.off.p, (uint32_t)ngroups, gs.gid.p);
+    return true;
+}
+
+// vrgpu_potential
+void potential_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                        const long long *index_host, double G, double eps, double theta, int bucket, long long pp_threshold,
+                        double *phi_out_host)
+{
+    GroupSet gs;
+    if (!groupset_from_csr(ctx, P, ngroups, offsets_host, index_host, gs)) return;
+    const long long ntot = (long long)gs.ntot;
     gather_groupset(ctx, P, gs, false, true);
     DBuf<double> phi(ctx, (size_t)ntot);
     compute_potentials(ctx, gs, G, eps, theta, bucket, pp_threshold, phi.p);
     VR_CUDA(cudaMemcpyAsync(phi_out_host, phi.p, (size_t)ntot * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->stats.d2h_bytes += ntot * 8;
+}
+
+// vrgpu_tree_order: the arrangement BuildNodes leaves (every group a tree of its own)
+void tree_order_csr_host(vrgpu_ctx *ctx, const DeviceParticles &P, long long ngroups, const long long *offsets_host,
+                         const long long *index_host, int bucket, long long *perm_out_host)
+{
+    GroupSet gs;
+    if (!groupset_from_csr(ctx, P, ngroups, offsets_host, index_host, gs)) return;
+    gather_groupset(ctx, P, gs, false, false);
+    DBuf<long long> out(ctx, gs.ntot);
+    tree_order_device(ctx, gs, bucket, out.p);
+    VR_CUDA(cudaMemcpyAsync(perm_out_host, out.p, gs.ntot * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->stats.d2h_bytes += (long long)gs.ntot * 8;
 }
 
 } // namespace vrgpu

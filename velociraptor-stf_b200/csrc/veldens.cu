@@ -4,7 +4,7 @@
 // (search.cxx:2646, tree == NULL): the reference builds a physical kd-tree (bucket Options::Bsize, Epanechnikov kernel
 // table of 1000 entries, period Options::p), runs one neighbour search per leaf (default) or per particle, and writes
 // Particle::density.  Device stages:
-//   tree      pt_build with the exact-ties selection (ptree.cu, qsel.cuh): the leaves are the reference's
+//   tree      pt_build (ptree.cu: the reference's MedianPos arrangement): the leaves are the reference's
 //   gather    tree-ordered position / velocity / type columns; bounding box of every node (leaves, then level by level up)
 //   leaves    list of leaf nodes, centre and typed count of each (veldens::leaf_thread)
 //   search    veldens::knn_thread per query, queries in batches bounded by the scratch of their queues
@@ -160,10 +160,8 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
     PtTree t;
     {
         KScope k(ctx, "veldens.tree");
-        // VRGPU_VD_SORT_TREE=1 (debugging aid): the sort-based build instead of the reference's selection -- the same leaves
-        // wherever split coordinates are distinct, members of a leaf in another order (leaf centres differ in the last bits)
-        const bool sort_tree = [] { const char *e = getenv("VRGPU_VD_SORT_TREE"); return e && atoi(e) == 1; }();
-        const bool ok = pt_build(ctx, gs, bsize, 0, !sort_tree, t);
+        const bool ok = pt_build(ctx, gs, bsize, 0, t);
+        t.rec.reset();
         VR_REQUIRE(ok && t.nL == n && t.nLG == 1, VRGPU_ECUDA, "velocity density: tree build failed");
     }
     const uint32_t nnodes = t.nnodes;

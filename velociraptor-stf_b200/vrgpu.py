@@ -119,6 +119,7 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_fof6d.argtypes = [C.c_void_p, View, P_ll, C.c_longlong, C.c_double, C.c_double, C.c_int, C.c_longlong, P_ll, P_ll]
     L.vrgpu_potential.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_ll, C.c_double, C.c_double, C.c_double, C.c_int,
                                   C.c_longlong, P_d]
+    L.vrgpu_tree_order.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_ll, C.c_int, P_ll]
     L.vrgpu_binding_energy.argtypes = [C.c_void_p, View, C.c_longlong, P_ll, P_d, C.c_double, C.c_double, C.c_double, C.c_int,
                                        C.c_longlong, P_d, P_d, P_d, P_d, P_d, P_ll, P_ll]
     L.vrgpu_sort_groups_by_key.argtypes = [C.c_void_p, C.c_longlong, P_ll, P_d, P_ll]
@@ -152,7 +153,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
                     "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes", "vrgpu_fof_criterion6d", "vrgpu_velocity_density",
-                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist"]
+                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist", "vrgpu_tree_order"]
 
 
 def pinned_i64(n: int) -> np.ndarray:
@@ -273,6 +274,17 @@ class Context:
         self._check(self.lib.vrgpu_potential(self.h, view_of(parts), ng, offsets.ctypes.data_as(P), index.ctypes.data_as(P),
                                              G, eps, theta, bucket, pp_threshold, phi.ctypes.data_as(C.POINTER(C.c_double))))
         return phi
+
+    def tree_order(self, parts, offsets, index, bucket=8):
+        """The arrangement KDTree::BuildNodes / MedianPos (KDTree.cxx:438-507, 304-337) leave in every group: perm[offsets[g] + j] =
+        offset inside group g of the member at tree position j."""
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        index = np.ascontiguousarray(index, dtype=np.int64)
+        perm = np.zeros(index.shape[0], dtype=np.int64)
+        P = C.POINTER(C.c_longlong)
+        self._check(self.lib.vrgpu_tree_order(self.h, view_of(parts), offsets.shape[0] - 1, offsets.ctypes.data_as(P), index.ctypes.data_as(P),
+                                              bucket, perm.ctypes.data_as(P)))
+        return perm
 
     def binding_energy(self, parts, offsets, gcmvel, G, eps=0.0, theta=0.5, bucket=8, large_threshold=1000):
         """GetBindingEnergy (substructureproperties.cxx:3884-4255) for group-ordered particles; group g = parts[offsets[g]:offsets[g+1]]."""
