@@ -94,3 +94,51 @@ def test_fof3d_size_order_and_ties(gpu_ctx):
     assert set(pf[5:12]) == {1}
     assert set(pf[12:17]) == {2} and set(pf[0:5]) == {3}  # clump at 50 has the smaller pids
     assert set(pf[17:20]) == {4}
+
+
+def test_fof3d_random_small_boxes(gpu_ctx, oracle):
+    """120 random small inputs in boxes 5 to 24 linking lengths wide, periodic and open: most neighbour blocks wrap, the same
+    block is reached through several periodic images, and the smallest boxes (no whole number of 4-cell blocks with
+    2 c >= b) take the hash-table path of fof3d.cu instead of the block bitmap."""
+    import vrgpu
+    rng = np.random.default_rng(2027)
+    for trial in range(120):
+        b = float(rng.choice([0.5, 1.0, 1.7]))
+        L = float(b * rng.uniform(4.7, 24.0))
+        if int(np.ceil(L / (b / np.sqrt(3.0) * (1.0 - 1e-8)))) < 8:
+            continue
+        n = int(rng.integers(1, 600))
+        centres = rng.random((int(rng.integers(1, 6)), 3)) * L
+        pos = centres[rng.integers(0, len(centres), size=n)] + rng.normal(size=(n, 3)) * b * rng.uniform(0.2, 1.5)
+        pos = np.mod(pos, L)
+        if rng.random() < 0.2 and n > 3:
+            pos[rng.integers(0, n, size=3), rng.integers(0, 3, size=3)] = rng.choice([0.0, L], size=3)
+        pos = np.clip(pos.astype(np.float32).astype(np.float64), 0.0, L)
+        periodic = rng.random() < 0.7
+        minsize = int(rng.integers(1, 6))
+        pid = np.arange(n)
+        parts = vrgpu.particles_from_arrays(pos, pid=pid)
+        pf, ng = gpu_ctx.fof3d(parts, b, L if periodic else None, minsize)
+        want, no = oracle.fof3d(pos, b, L if periodic else None, minsize, pid)
+        assert ng == no, (trial, n, b, L, periodic)
+        assert np.array_equal(pf, want), (trial, n, b, L, periodic)
+
+
+def test_fof3d_dense_cells_use_the_dense_queue(gpu_ctx, oracle):
+    """Two well-filled cells two cells apart along x whose FIRST 4 x 4 particle pairs do not link while one later pair does:
+    the short trial must leave the pair undecided and the warp-per-pair kernel must find the link."""
+    import vrgpu
+    rng = np.random.default_rng(3)
+    L, b = 100.0, 1.0
+    nc = int(np.ceil(np.ceil(L / (b / np.sqrt(3.0) * (1.0 - 1e-8))) / 4.0) * 4)
+    c = L / nc
+    yz = 17.5 * c + 0.01 * rng.random((82, 2))
+    xa = np.concatenate([17.05 * c + 0.01 * rng.random(40), [17.9 * c]])
+    xb = np.concatenate([19.8 * c + 0.01 * rng.random(40), [19.1 * c]])
+    pos = np.column_stack([np.concatenate([xa, xb]), yz])
+    pid = np.arange(len(pos))
+    parts = vrgpu.particles_from_arrays(pos, pid=pid)
+    pf, ng = gpu_ctx.fof3d(parts, b, L, 2)
+    assert gpu_ctx.stats()["n_link_queue"] == 1
+    want, no = oracle.fof3d(pos, b, L, 2, pid)
+    assert ng == no == 1 and np.array_equal(pf, want) and np.all(pf == 1)

@@ -109,8 +109,12 @@ def test_tree_with_tied_coordinates(gpu_ctx, oracle, n, scale):
     eps = 1e-3  # coincident float32 positions exist: keep every term finite
     phi = gpu_ctx.potential(parts, np.array([0, n]), np.arange(n), G, eps=eps, pp_threshold=150)
     ref, ninter = oracle.potential_tree(pos, mass, G, eps, 0.5, 8)
-    assert gpu_ctx.stats()["n_tree_interactions"] == ninter
-    assert np.max(np.abs(phi / ref - 1.0)) < 1e-10
+    got_inter = gpu_ctx.stats()["n_tree_interactions"]
+    rel = np.abs(phi / ref - 1.0)
+    print(f"tied coordinates n={n}: interactions {got_inter} vs {ninter}, max |dphi/phi| {rel.max():.3e}, "
+          f"particles above 1e-10: {int(np.count_nonzero(rel > 1e-10))}")
+    assert rel.max() < 1e-10
+    assert got_inter == ninter
 
 
 def test_tree_ties_many_groups(gpu_ctx, oracle):

@@ -7,9 +7,12 @@
 //   1. particles are binned into FINE cells of edge c < b/sqrt(3): two particles in one cell are always linked,
 //      so the union-find runs over non-empty CELLS, not particles;
 //   2. particles are radix-sorted by cell key (sort.cu), positions gathered into cell order (SoA, coalesced);
-//   3. a hash table maps cell key -> cell id; one warp per cell probes its 62 half-space neighbours (|d|<=2),
-//      skips neighbours already in the same set, otherwise tests particle pairs with the reference's exact
-//      fp64 predicate until one link is found and unites the two cells (lock-free atomicCAS union, path halving);
+//   3. cells are grouped into 4 x 4 x 4 blocks (the sort key is block-major): a bitmap over the blocks with a per-word rank and a
+//      64-bit occupancy mask per non-empty block turn "which of my 62 half-space neighbour cells exist" into two independent
+//      look-ups and a table AND per neighbouring block (link3.cuh).  One thread per cell enumerates its candidates; the
+//      candidates of a warp go through a per-warp queue in shared memory, so the root checks and pair trials always run on
+//      full warps; cell pairs the short trial leaves undecided go to a warp-per-pair kernel (exhaustive test, fp64 predicate
+//      of the reference); lock-free atomicCAS union with path halving over CELLS;
 //   4. roots are flattened, group sizes / min pid accumulated per root, groups >= minsize ordered by
 //      (size desc, min pid asc) and pfof written in the caller's particle order.
 // Pair predicate: d2 = dx*dx + dy*dy + dz*dz summed left to right in fp64 WITHOUT fma, link iff d2 < b*b
@@ -19,6 +22,7 @@
 #include "fof.cuh"
 #include "groups.cuh"
 #include "ufhash.cuh"
+#include "link3.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -40,6 +44,7 @@ struct LinkParams {
     double period;
     double b2;
     int perx, pery, perz; // per-axis periodicity (a slab of a multi-GPU run is open along x)
+    link3::Geom g;        // blocks of 4 x 4 x 4 cells; cell_key = (block, local), link3.cuh
 };
 
 __constant__ signed char c_offsets[62][3];
@@ -47,8 +52,8 @@ __constant__ signed char c_offsets[62][3];
 // ---------------------------------------------------------------------------------------------------
 // binning
 // ---------------------------------------------------------------------------------------------------
-__global__ void k_cell_keys(const double *__restrict__ pos, size_t n, Grid g, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals,
-                            unsigned int *__restrict__ nbad)
+__global__ void k_cell_keys(const double *__restrict__ pos, size_t n, Grid g, link3::Geom geom, uint64_t *__restrict__ keys,
+                            uint32_t *__restrict__ vals, unsigned int *__restrict__ nbad)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -64,7 +69,7 @@ __global__ void k_cell_keys(const double *__restrict__ pos, size_t n, Grid g, ui
     ix = ix < 0 ? 0 : (ix >= g.nc[0] ? g.nc[0] - 1 : ix);
     iy = iy < 0 ? 0 : (iy >= g.nc[1] ? g.nc[1] - 1 : iy);
     iz = iz < 0 ? 0 : (iz >= g.nc[2] ? g.nc[2] - 1 : iz);
-    keys[i] = ((uint64_t)iz * (uint64_t)g.nc[1] + (uint64_t)iy) * (uint64_t)g.nc[0] + (uint64_t)ix;
+    keys[i] = link3::cell_key(geom, (int)ix, (int)iy, (int)iz);
     vals[i] = (uint32_t)i;
 }
 
@@ -111,27 +116,62 @@ __global__ void k_gather_pos(const double *__restrict__ pos, const uint32_t *__r
     sz[k] = pos[3 * i + 2];
 }
 
-__global__ void k_flag_heads(const uint64_t *__restrict__ keys, size_t n, uint32_t *__restrict__ flags)
+// head flags of cells (low word) and of blocks (high word); one 64-bit scan numbers both
+__global__ void k_flag_heads(const uint64_t *__restrict__ keys, size_t n, unsigned long long *__restrict__ flags)
 {
     size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    flags[k] = (k == 0 || keys[k] != keys[k - 1]) ? 1u : 0u;
+    const uint64_t key = keys[k];
+    const uint64_t prev = k ? keys[k - 1] : ~key;
+    flags[k] = (key != prev ? 1ull : 0ull) | ((key >> 6) != (prev >> 6) ? (1ull << 32) : 0ull);
 }
 
-__global__ void k_fill_cells(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ flags, const uint32_t *__restrict__ excl,
-                             size_t n, uint32_t *__restrict__ cell_of, uint32_t *__restrict__ cell_start, uint64_t *__restrict__ cell_key,
-                             uint32_t ncells)
+struct BlockArrays {
+    uint32_t *cell_blk;            // cell -> rank of its block among the non-empty blocks
+    uint8_t *cell_loc;             // cell -> 6-bit index inside its block
+    uint32_t *blk_cell0;           // block rank -> first cell
+    unsigned long long *blk_xyz;   // block rank -> packed block coordinates
+    unsigned long long *blk_occ;   // block rank -> occupancy of its 64 cells (zeroed before)
+    unsigned long long *bitmap;    // all blocks of the grid, one bit each (zeroed before; nullptr: hash path)
+};
+
+__global__ void k_fill_cells(const uint64_t *__restrict__ keys, const unsigned long long *__restrict__ excl, size_t n, link3::Geom geom,
+                             uint32_t *__restrict__ cell_of, uint32_t *__restrict__ cell_start, uint64_t *__restrict__ cell_key, uint32_t ncells,
+                             BlockArrays B)
 {
     size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    uint32_t f = flags[k];
-    uint32_t c = excl[k] - (f ? 0u : 1u);
+    const uint64_t key = keys[k];
+    const uint64_t prev = k ? keys[k - 1] : ~key;
+    const bool chead = key != prev, bhead = (key >> 6) != (prev >> 6);
+    const unsigned long long e = excl[k];
+    const uint32_t c = (uint32_t)(e & 0xffffffffull) - (chead ? 0u : 1u);
     cell_of[k] = c;
-    if (f) {
+    if (chead) {
         cell_start[c] = (uint32_t)k;
-        cell_key[c] = keys[k];
+        cell_key[c] = key;
+        if (B.bitmap) {
+            const uint32_t r = (uint32_t)(e >> 32) - (bhead ? 0u : 1u);
+            B.cell_blk[c] = r;
+            B.cell_loc[c] = (uint8_t)(key & 63u);
+            atomicOr(&B.blk_occ[r], 1ull << (key & 63u));
+            if (bhead) {
+                int ix, iy, iz;
+                link3::key_cell(geom, key, ix, iy, iz);
+                B.blk_cell0[r] = c;
+                B.blk_xyz[r] = link3::pack_xyz(ix >> 2, iy >> 2, iz >> 2);
+                const uint64_t lin = key >> 6;
+                atomicOr(&B.bitmap[lin >> 6], 1ull << (lin & 63u));
+            }
+        }
     }
     if (k == n - 1) cell_start[ncells] = (uint32_t)n;
+}
+
+__global__ void k_bitmap_counts(const unsigned long long *__restrict__ bitmap, size_t nwords, uint32_t *__restrict__ cnt)
+{
+    size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < nwords) cnt[w] = (uint32_t)__popcll(bitmap[w]);
 }
 
 __device__ __forceinline__ bool pair_links(double ax, double ay, double az, double bx, double by, double bz, double b2)
@@ -220,20 +260,17 @@ __device__ __forceinline__ void try_link_cells(const LinkParams &P, const uint32
     __syncwarp();
 }
 
-// One warp per cell.  off_begin/off_end select the slice of the 62 half-space offsets handled by this launch:
+// Hash-table path (grids too large for the block bitmap, periodic boxes too small for whole blocks): one warp per cell probes
+// its half-space neighbours in a cell-key hash table.  off_begin/off_end select the slice of the 62 half-space offsets handled by this launch:
 // the 13 face/edge/corner neighbours first, the 49 second-shell ones afterwards (by then most are already united).
 __global__ void __launch_bounds__(256) k_link_cells(LinkParams P, int off_begin, int off_end)
 {
     const unsigned lane = threadIdx.x & 31;
     const uint32_t warps_total = (gridDim.x * blockDim.x) >> 5;
     const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint64_t nxy = (uint64_t)P.ncx * (uint64_t)P.ncy;
     for (uint32_t cell = warp_global; cell < P.ncells; cell += warps_total) {
-        const uint64_t key = P.cell_key[cell];
-        const int iz = (int)(key / nxy);
-        const uint64_t rem = key - (uint64_t)iz * nxy;
-        const int iy = (int)(rem / (uint64_t)P.ncx);
-        const int ix = (int)(rem - (uint64_t)iy * (uint64_t)P.ncx);
+        int ix, iy, iz;
+        link3::key_cell(P.g, P.cell_key[cell], ix, iy, iz);
         const uint32_t a0 = P.cell_start[cell], a1 = P.cell_start[cell + 1];
         const uint32_t na = a1 - a0;
         for (int obase = off_begin; obase < off_end; obase += 32) {
@@ -253,7 +290,7 @@ __global__ void __launch_bounds__(256) k_link_cells(LinkParams P, int off_begin,
                 if (nz < 0) { if (P.perz) { nz += P.ncz; sz = 1; } else ok = false; }
                 else if (nz >= P.ncz) { if (P.perz) { nz -= P.ncz; sz = -1; } else ok = false; }
                 if (ok) {
-                    uint64_t nkey = ((uint64_t)nz * (uint64_t)P.ncy + (uint64_t)ny) * (uint64_t)P.ncx + (uint64_t)nx;
+                    const uint64_t nkey = link3::cell_key(P.g, nx, ny, nz);
                     nb = hash_lookup(P.hkeys, P.hvals, P.hmask, nkey);
                     scode = (sx + 1) | ((sy + 1) << 2) | ((sz + 1) << 4);
                 }
@@ -273,110 +310,8 @@ __global__ void __launch_bounds__(256) k_link_cells(LinkParams P, int off_begin,
 }
 
 // ---------------------------------------------------------------------------------------------------
-// row-table linker.  Cells are sorted by key = (iz*ncy + iy)*ncx + ix, so the cells of one (iy,iz) ROW are contiguous
-// and ordered by ix.  A dense table row -> [first,last) cell (4 B x 2 per row; 39 MB at 256^3, L2 resident) turns the 62
-// neighbour-cell hash probes of a cell into 12 row look-ups + short scans (the 5 x-neighbours of a row are adjacent).
-// ---------------------------------------------------------------------------------------------------
-constexpr uint32_t ROW_NONE = 0xffffffffu;
-
-__global__ void k_row_table(const uint64_t *__restrict__ cell_key, uint32_t ncells, uint64_t ncx, uint32_t *__restrict__ row_first,
-                            uint32_t *__restrict__ row_last)
-{
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncells) return;
-    const uint64_t r = cell_key[c] / ncx;
-    if (c == 0 || cell_key[c - 1] / ncx != r) row_first[r] = c;
-    if (c == ncells - 1 || cell_key[c + 1] / ncx != r) row_last[r] = c + 1;
-}
-
-// reach = 1: only the 13 adjacent half-space cells (cheap first pass that unites most of a halo), reach = 2: all 62.
-__global__ void __launch_bounds__(256) k_link_rows(LinkParams P, const uint32_t *__restrict__ row_first, const uint32_t *__restrict__ row_last,
-                                                   int reach)
-{
-    const unsigned lane = threadIdx.x & 31;
-    const uint32_t warps_total = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint64_t ncx = (uint64_t)P.ncx;
-    for (uint32_t cell = warp_global; cell < P.ncells; cell += warps_total) {
-        const uint64_t key = P.cell_key[cell];
-        const uint64_t row = key / ncx;
-        const int ix = (int)(key - row * ncx);
-        const int iz = (int)(row / (uint64_t)P.ncy);
-        const int iy = (int)(row - (uint64_t)iz * (uint64_t)P.ncy);
-        const uint32_t a0 = P.cell_start[cell], a1 = P.cell_start[cell + 1];
-        // lane -> (role, segment): role 0..11 = neighbour rows of the half space, role 12 = own row (dx > 0);
-        // segment 0 = the part of the x-interval inside [0,ncx), segment 1 = the part that wraps (periodic x only)
-        const int role = (int)(lane & 15), seg = (int)(lane >> 4);
-        int dy = 0, dz = 0;
-        bool ok = role <= 12;
-        if (role < 5) { dz = 1; dy = role - 2; }
-        else if (role < 10) { dz = 2; dy = role - 7; }
-        else if (role < 12) { dz = 0; dy = role - 9; }
-        if (ok && (abs(dy) > reach || dz > reach)) ok = false;
-        int xlo = role == 12 ? ix + 1 : ix - reach, xhi = ix + reach; // unwrapped x-interval
-        int xoff = 0, sx = 0, sy = 0, sz = 0;
-        if (ok) {
-            if (seg == 0) { xlo = max(xlo, 0); xhi = min(xhi, P.ncx - 1); }
-            else if (!P.perx) ok = false;
-            else if (xlo < 0) { xhi = min(xhi, -1) + P.ncx; xlo += P.ncx; xoff = -P.ncx; sx = 1; }
-            else if (xhi >= P.ncx) { xlo = max(xlo, P.ncx) - P.ncx; xhi -= P.ncx; xoff = P.ncx; sx = -1; }
-            else ok = false;
-            if (xlo > xhi) ok = false;
-        }
-        int ny = iy + dy, nz = iz + dz;
-        if (ok) {
-            if (ny < 0) { if (P.pery) { ny += P.ncy; sy = 1; } else ok = false; }
-            else if (ny >= P.ncy) { if (P.pery) { ny -= P.ncy; sy = -1; } else ok = false; }
-            if (nz >= P.ncz) { if (P.perz) { nz -= P.ncz; sz = -1; } else ok = false; }
-        }
-        uint32_t c0 = 0, c1 = 0;
-        uint64_t rowbase = 0;
-        if (ok) {
-            const uint64_t r = (uint64_t)nz * (uint64_t)P.ncy + (uint64_t)ny;
-            rowbase = r * ncx;
-            uint32_t f = row_first[r];
-            if (f != ROW_NONE) {
-                uint32_t l = row_last[r];
-                const uint64_t klo = rowbase + (uint64_t)xlo, khi = rowbase + (uint64_t)xhi;
-                if (role == 12 && seg == 0) f = cell + 1; // own row, forward: the next cells in the array
-                else {
-                    // lower bound of klo in cell_key[f, l)
-                    uint32_t lo = f, hi = l;
-                    while (lo < hi) {
-                        uint32_t mid = (lo + hi) >> 1;
-                        if (__ldg(&P.cell_key[mid]) < klo) lo = mid + 1; else hi = mid;
-                    }
-                    f = lo;
-                }
-                uint32_t e = f;
-                while (e < l && __ldg(&P.cell_key[e]) <= khi) e++;
-                c0 = f; c1 = e;
-            }
-        }
-        const int scode = (sx + 1) | ((sy + 1) << 2) | ((sz + 1) << 4);
-        unsigned has = __ballot_sync(0xffffffffu, c0 < c1);
-        while (has) {
-            const int src = __ffs(has) - 1;
-            const uint32_t B = __shfl_sync(0xffffffffu, c0, src);
-            const int sc = __shfl_sync(0xffffffffu, scode, src);
-            const int ddy = __shfl_sync(0xffffffffu, dy, src), ddz = __shfl_sync(0xffffffffu, dz, src);
-            const int xo = __shfl_sync(0xffffffffu, xoff, src);
-            const unsigned long long rb = __shfl_sync(0xffffffffu, (unsigned long long)rowbase, src);
-            const int ddx = (int)(P.cell_key[B] - rb) + xo - ix;
-            if ((int)lane == src) c0++;
-            try_link_cells(P, cell, a0, a1, ix, iy, iz, B, ddx, ddy, ddz, sc, lane);
-            has = __ballot_sync(0xffffffffu, c0 < c1);
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------
-// thread-per-cell linker.  Most non-empty cells of a cosmological box hold ONE particle and have no neighbour at all, so a
-// warp per cell spends hundreds of instructions on bookkeeping for nothing (ncu, profiles/r01b: 5.8e9 warp instructions,
-// 1 % of them fp64).  Here every THREAD owns a cell: it walks its 12 neighbour rows + its own row through the row table,
-// and for every neighbour cell in a different set it tests up to 16 pairs inline (enough for sparse cells and for most
-// dense neighbours, which link at the first try); only cell pairs that are still undecided go to a queue that a
-// warp-per-pair kernel finishes with the exhaustive test.
+// block linker (link3.cuh).  Measured and replaced (profiles/r01h_stall_analysis.md, r02a_probe.md): a thread per cell that
+// walks a dense (iy, iz) row table with binary searches -- 13 to 25 dependent look-up chains per cell, 9 of 32 lanes active.
 // ---------------------------------------------------------------------------------------------------
 struct LinkQueue {
     uint32_t *a, *b, *meta;     // meta: sc (6 bits) | (ddx+2)<<6 | (ddy+2)<<9 | (ddz+2)<<12
@@ -384,121 +319,121 @@ struct LinkQueue {
     uint32_t capacity;
 };
 
-__global__ void k_cell_coords(const uint64_t *__restrict__ cell_key, uint32_t ncells, uint64_t ncx, uint32_t *__restrict__ cell_row,
-                              int *__restrict__ cell_ix, uint32_t *__restrict__ row_first, uint32_t *__restrict__ row_last)
-{
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncells) return;
-    const uint64_t key = cell_key[c];
-    const uint64_t r = key / ncx;
-    cell_row[c] = (uint32_t)r;
-    cell_ix[c] = (int)(key - r * ncx);
-    if (c == 0 || cell_key[c - 1] / ncx != r) row_first[r] = c;
-    if (c == ncells - 1 || cell_key[c + 1] / ncx != r) row_last[r] = c + 1;
-}
+struct BlockParams {
+    link3::Tables T;
+    const uint32_t *cell_blk;
+    const uint8_t *cell_loc;
+    const unsigned long long *blk_xyz;
+    const unsigned long long *table; // link3::build_table, TABLE_WORDS entries
+};
 
-__global__ void __launch_bounds__(128, 12) k_link_thread(LinkParams P, const uint32_t *__restrict__ cell_row, const int *__restrict__ cell_ix,
-                                                     const uint32_t *__restrict__ row_first, const uint32_t *__restrict__ row_last, int reach,
-                                                     LinkQueue Q)
+// one candidate: are the cells A and B (image code and cell offset in meta) in one set already?  If not, a short trial of
+// particle pairs (all of them when there are at most 16, else the first 4 x 4); a link unites the sets, an undecided dense pair
+// goes to the queue of the warp-per-pair kernel (or is finished here when the queue is full)
+__device__ __forceinline__ void link_candidate(const LinkParams &P, const uint32_t A, const uint32_t B, const uint32_t meta, LinkQueue Q)
 {
-    const uint32_t cell = blockIdx.x * blockDim.x + threadIdx.x;
-    if (cell >= P.ncells) return;
-    const uint32_t row = cell_row[cell];
-    const int ix = cell_ix[cell];
-    const int iz = (int)(row / (uint32_t)P.ncy);
-    const int iy = (int)(row - (uint32_t)iz * (uint32_t)P.ncy);
-    const uint32_t a0 = P.cell_start[cell], a1 = P.cell_start[cell + 1];
-    const uint32_t na = a1 - a0;
-    uint32_t ra = uf_find(P.parent, cell);
-    // own row first (dx > 0), then dz = 0 / dy > 0, then dz = 1, 2
-    for (int role = 0; role < 13; role++) {
-        int dy, dz;
-        if (role == 0) { dy = 0; dz = 0; }
-        else if (role < 3) { dz = 0; dy = role; }
-        else if (role < 8) { dz = 1; dy = role - 5; }
-        else { dz = 2; dy = role - 10; }
-        if (abs(dy) > reach || dz > reach) continue;
-        int ny = iy + dy, nz = iz + dz, sy = 0, sz = 0;
-        if (ny < 0) { if (!P.pery) continue; ny += P.ncy; sy = 1; }
-        else if (ny >= P.ncy) { if (!P.pery) continue; ny -= P.ncy; sy = -1; }
-        if (nz >= P.ncz) { if (!P.perz) continue; nz -= P.ncz; sz = -1; }
-        const uint32_t r = (uint32_t)nz * (uint32_t)P.ncy + (uint32_t)ny;
-        const uint32_t rf = row_first[r];
-        if (rf == ROW_NONE) continue;
-        const uint32_t rl = row_last[r];
-        const int x0 = role == 0 ? ix + 1 : ix - reach, x1 = ix + reach; // unwrapped interval
-        for (int seg = 0; seg < 2; seg++) {
-            int xlo = x0, xhi = x1, xoff = 0, sx = 0;
-            if (seg == 0) { xlo = max(xlo, 0); xhi = min(xhi, P.ncx - 1); }
-            else {
-                if (!P.perx) break;
-                if (x0 < 0) { xhi = min(x1, -1) + P.ncx; xlo = x0 + P.ncx; xoff = -P.ncx; sx = 1; }
-                else if (x1 >= P.ncx) { xlo = max(x0, P.ncx) - P.ncx; xhi = x1 - P.ncx; xoff = P.ncx; sx = -1; }
-                else break;
-            }
-            if (xlo > xhi) continue;
-            uint32_t c;
-            if (role == 0 && seg == 0) c = cell + 1;
-            else {
-                uint32_t lo = rf, hi = rl;
-                while (lo < hi) {
-                    const uint32_t mid = (lo + hi) >> 1;
-                    if (__ldg(&cell_ix[mid]) < xlo) lo = mid + 1; else hi = mid;
-                }
-                c = lo;
-            }
-            const int sc = (sx + 1) | ((sy + 1) << 2) | ((sz + 1) << 4);
-            const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
-            const double shx = (double)sx * P.period, shy = (double)sy * P.period, shz = (double)sz * P.period;
-            for (; c < rl; c++) {
-                const int bx = __ldg(&cell_ix[c]);
-                if (bx > xhi) break;
-                const uint32_t B = c;
-                const uint32_t rb = uf_find(P.parent, B);
-                if (rb == ra) continue;
-                const uint32_t b0 = P.cell_start[B], b1 = P.cell_start[B + 1];
-                const uint32_t nb = b1 - b0;
-                // inline trial: all pairs when there are few, else the first 4 x 4
-                const uint32_t ta = na * nb <= 16u ? na : min(na, 4u), tb = na * nb <= 16u ? nb : min(nb, 4u);
-                bool linked = false;
-                for (uint32_t i = 0; i < ta && !linked; i++) {
-                    const double ax = P.sx[a0 + i], ay = P.sy[a0 + i], az = P.sz[a0 + i];
-                    for (uint32_t j = 0; j < tb && !linked; j++) {
-                        const double qx = P.sx[b0 + j], qy = P.sy[b0 + j], qz = P.sz[b0 + j];
-                        if (!wrapped) linked = pair_links(ax, ay, az, qx, qy, qz, P.b2);
-                        else
-                            linked = pair_links(__dadd_rn(ax, shx), __dadd_rn(ay, shy), __dadd_rn(az, shz), qx, qy, qz, P.b2) ||
-                                     pair_links(__dsub_rn(qx, shx), __dsub_rn(qy, shy), __dsub_rn(qz, shz), ax, ay, az, P.b2);
-                    }
-                }
-                if (linked) {
-                    uf_union(P.parent, cell, B);
-                    ra = uf_find(P.parent, cell);
-                } else if (na * nb > 16u) {
-                    const unsigned int slot = atomicAdd(Q.count, 1u);
-                    if (slot < Q.capacity) {
-                        Q.a[slot] = cell;
-                        Q.b[slot] = B;
-                        Q.meta[slot] = (uint32_t)sc | ((uint32_t)(bx + xoff - ix + 2) << 6) | ((uint32_t)(dy + 2) << 9) | ((uint32_t)(dz + 2) << 12);
-                    }
-                }
+    const uint32_t ra = uf_find(P.parent, A), rb = uf_find(P.parent, B);
+    if (ra == rb) return;
+    const uint32_t a0 = P.cell_start[A], na = P.cell_start[A + 1] - a0;
+    const uint32_t b0 = P.cell_start[B], nb = P.cell_start[B + 1] - b0;
+    const int sc = (int)(meta & 63u);
+    const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
+    const double shx = (double)((sc & 3) - 1) * P.period, shy = (double)(((sc >> 2) & 3) - 1) * P.period,
+                 shz = (double)(((sc >> 4) & 3) - 1) * P.period;
+    const bool few = na * nb <= 16u;
+    uint32_t ta = few ? na : min(na, 4u), tb = few ? nb : min(nb, 4u);
+    bool linked = false;
+    for (int attempt = 0; attempt < 2 && !linked; attempt++) {
+        for (uint32_t i = 0; i < ta && !linked; i++) {
+            const double ax = P.sx[a0 + i], ay = P.sy[a0 + i], az = P.sz[a0 + i];
+            for (uint32_t j = 0; j < tb && !linked; j++) {
+                const double qx = P.sx[b0 + j], qy = P.sy[b0 + j], qz = P.sz[b0 + j];
+                if (!wrapped) linked = pair_links(ax, ay, az, qx, qy, qz, P.b2);
+                else
+                    linked = pair_links(__dadd_rn(ax, shx), __dadd_rn(ay, shy), __dadd_rn(az, shz), qx, qy, qz, P.b2) ||
+                             pair_links(__dsub_rn(qx, shx), __dsub_rn(qy, shy), __dsub_rn(qz, shz), ax, ay, az, P.b2);
             }
         }
+        if (linked || few) break;
+        const unsigned int slot = atomicAdd(Q.count, 1u);
+        if (slot < Q.capacity) { Q.a[slot] = A; Q.b[slot] = B; Q.meta[slot] = meta; break; }
+        ta = na; tb = nb; // queue full (pathological density): this thread tests every pair itself
     }
+    if (linked) uf_union(P.parent, A, B);
+}
+
+constexpr int LB_THREADS = 256, LB_WARPS = LB_THREADS / 32;
+__global__ void __launch_bounds__(LB_THREADS) k_link_blocks(LinkParams P, BlockParams Bp, LinkQueue Q)
+{
+    __shared__ unsigned long long s_tab[link3::TABLE_WORDS];
+    __shared__ unsigned long long s_occ[8][LB_THREADS];
+    __shared__ uint32_t s_rank[8][LB_THREADS];
+    __shared__ uint32_t s_qa[LB_WARPS][64], s_qb[LB_WARPS][64], s_qm[LB_WARPS][64];
+    const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int i = tid; i < link3::TABLE_WORDS; i += LB_THREADS) s_tab[i] = Bp.table[i];
+    const uint32_t cell = blockIdx.x * LB_THREADS + tid;
+    const bool valid = cell < P.ncells;
+    unsigned loc = 0;
+    unsigned long long codes = 0;
+    if (valid) {
+        const uint32_t r = Bp.cell_blk[cell];
+        loc = Bp.cell_loc[cell];
+        int bx, by, bz;
+        link3::unpack_xyz(__ldg(Bp.blk_xyz + r), bx, by, bz);
+        uint32_t rank[8];
+        unsigned long long occ[8];
+        link3::lookup_blocks(P.g, Bp.T, r, bx, by, bz, loc, rank, occ, codes);
+#pragma unroll
+        for (int j = 0; j < 8; j++) { s_occ[j][tid] = occ[j]; s_rank[j][tid] = rank[j]; }
+    }
+    __syncthreads();
+    // every lane walks its candidates (13 adjacent cells first, the second shell afterwards); the candidates of the warp are
+    // collected in shared memory and worked off 32 at a time, so the expensive part always runs on a full warp
+    const unsigned lt = (1u << lane) - 1u;
+    int pj = valid ? 0 : 16; // next (pass, block) to look at: pass * 8 + j
+    unsigned long long cand = 0;
+    uint32_t qn = 0;
+    for (;;) {
+        while (cand == 0 && pj < 16) {
+            const int j = pj & 7;
+            cand = s_occ[j][tid] & s_tab[((pj >> 3) * 64 + (int)loc) * 8 + j];
+            pj++;
+        }
+        const bool has = cand != 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, has);
+        if (!bal) break;
+        if (has) {
+            const unsigned j = (unsigned)(pj - 1) & 7u;
+            const unsigned bit = (unsigned)__ffsll((long long)cand) - 1u;
+            cand &= cand - 1ull;
+            int ddx, ddy, ddz;
+            link3::cell_offset(loc, j, bit, ddx, ddy, ddz);
+            const uint32_t slot = qn + (uint32_t)__popc(bal & lt);
+            s_qa[w][slot] = cell;
+            s_qb[w][slot] = link3::cell_of_bit(Bp.T, s_rank[j][tid], s_occ[j][tid], bit);
+            s_qm[w][slot] = (uint32_t)((codes >> (6 * j)) & 63ull) | ((uint32_t)(ddx + 2) << 6) | ((uint32_t)(ddy + 2) << 9) | ((uint32_t)(ddz + 2) << 12);
+        }
+        qn += (uint32_t)__popc(bal);
+        __syncwarp();
+        if (qn >= 32) {
+            qn -= 32;
+            link_candidate(P, s_qa[w][qn + lane], s_qb[w][qn + lane], s_qm[w][qn + lane], Q);
+            __syncwarp();
+        }
+    }
+    if (lane < qn) link_candidate(P, s_qa[w][lane], s_qb[w][lane], s_qm[w][lane], Q);
 }
 
 // one warp per undecided cell pair: the exhaustive test
-__global__ void __launch_bounds__(256) k_link_queue(LinkParams P, const uint32_t *__restrict__ cell_row, const int *__restrict__ cell_ix,
-                                                    LinkQueue Q, uint32_t nq)
+__global__ void __launch_bounds__(256) k_link_queue(LinkParams P, LinkQueue Q)
 {
     const unsigned lane = threadIdx.x & 31;
     const uint32_t warps_total = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t nq = min(*Q.count, Q.capacity); // written by the kernel before this one: no host round trip
     for (uint32_t e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < nq; e += warps_total) {
         const uint32_t cell = Q.a[e], B = Q.b[e], m = Q.meta[e];
-        const uint32_t row = cell_row[cell];
-        const int ix = cell_ix[cell];
-        const int iz = (int)(row / (uint32_t)P.ncy);
-        const int iy = (int)(row - (uint32_t)iz * (uint32_t)P.ncy);
+        int ix, iy, iz;
+        link3::key_cell(P.g, P.cell_key[cell], ix, iy, iz);
         try_link_cells(P, cell, P.cell_start[cell], P.cell_start[cell + 1], ix, iy, iz, B, (int)((m >> 6) & 7) - 2, (int)((m >> 9) & 7) - 2,
                        (int)((m >> 12) & 7) - 2, (int)(m & 63), lane);
     }
@@ -717,13 +652,21 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
             std::memcpy(&lohi[k], &u, 8);
         }
     }
+    // Periodic axes: whole 4-cell blocks, so that the grid wraps block on block -- as long as cells three apart still cannot link
+    // (2 c >= b).  Boxes below ~15 linking lengths may have no such cell count: they keep the plain count and take the hash path.
+    bool use_blocks = true;
+    double mper = 0;
+    if (g.period > 0) {
+        mper = std::ceil(g.period / cmax);
+        VR_REQUIRE(mper < 2.0e6, VRGPU_EUNSUPPORTED, "linking length too small for the cell key (period/b > ~1e6)");
+        VR_REQUIRE(mper >= 8, VRGPU_EUNSUPPORTED, "periodic box smaller than ~5 linking lengths is not supported");
+        const double m4 = std::ceil(mper / 4.0) * 4.0;
+        if (2.0 * (g.period / m4) >= b * (1.0 + 1e-6)) mper = m4; else use_blocks = false;
+    }
     for (int k = 0; k < 3; k++) {
         if (g.periodic[k]) {
             g.lo[k] = 0.0;
-            double m = std::ceil(g.period / cmax);
-            VR_REQUIRE(m < 2.0e6, VRGPU_EUNSUPPORTED, "linking length too small for the cell key (period/b > ~1e6)");
-            g.nc[k] = (int)m;
-            VR_REQUIRE(g.nc[k] >= 8, VRGPU_EUNSUPPORTED, "periodic box smaller than ~5 linking lengths is not supported");
+            g.nc[k] = (int)mper;
             g.c[k] = g.period / g.nc[k];
             g.inv_c[k] = (double)g.nc[k] / g.period;
         } else {
@@ -737,8 +680,15 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
             g.inv_c[k] = 1.0 / cmax;
         }
     }
-    const uint64_t ncell_total = (uint64_t)g.nc[0] * g.nc[1] * g.nc[2];
-    const int nbits = bits_for(ncell_total - 1);
+    link3::Geom geom{};
+    geom.ncx = g.nc[0]; geom.ncy = g.nc[1]; geom.ncz = g.nc[2];
+    geom.nbx = (g.nc[0] + 3) / 4; geom.nby = (g.nc[1] + 3) / 4; geom.nbz = (g.nc[2] + 3) / 4;
+    geom.perx = g.periodic[0]; geom.pery = g.periodic[1]; geom.perz = g.periodic[2];
+    const uint64_t nblk_total = (uint64_t)geom.nbx * (uint64_t)geom.nby * (uint64_t)geom.nbz;
+    const int nbits = bits_for(nblk_total - 1) + 6;
+    // the block bitmap and its rank take 3 bits per block of the grid: up to 2^33 blocks (3 GiB)
+    if (nblk_total > (1ull << 33)) use_blocks = false;
+    const size_t nwords = (size_t)(nblk_total / 64 + 1);
     S.grid = g;
 
     // ---- keys + sort ----
@@ -747,44 +697,60 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
     S.order.alloc(ctx, n);
     DBuf<unsigned int> nbad(ctx, 1);
     VR_CUDA(cudaMemsetAsync(nbad.p, 0, sizeof(unsigned int), ctx->stream));
+    DBuf<uint32_t> cell_blk, blk_cell0, prefix;
+    DBuf<uint8_t> cell_loc;
+    DBuf<unsigned long long> blk_xyz, blk_occ, bitmap;
     {
         StageTimer t(ctx);
-        { KScope k(ctx, "fof3d.cell_keys"); VR_LAUNCH(ctx, k_cell_keys, grid_for(n, T), T, 0, P.pos.p, n, g, keys.p, S.order.p, nbad.p); }
+        { KScope k(ctx, "fof3d.cell_keys"); VR_LAUNCH(ctx, k_cell_keys, grid_for(n, T), T, 0, P.pos.p, n, g, geom, keys.p, S.order.p, nbad.p); }
         { KScope k(ctx, "fof3d.radix_sort"); radix_sort_pairs(ctx, keys.p, S.order.p, keys_tmp.p, order_tmp.p, n, nbits); }
+        keys_tmp.reset(); order_tmp.reset();
         S.sx.alloc(ctx, n); S.sy.alloc(ctx, n); S.sz.alloc(ctx, n);
         { KScope k(ctx, "fof3d.gather_pos"); VR_LAUNCH(ctx, k_gather_pos, grid_for(n, T), T, 0, P.pos.p, S.order.p, n, S.sx.p, S.sy.p, S.sz.p); }
-        // cells
-        DBuf<uint32_t> flags(ctx, n), excl(ctx, n), total(ctx, 1);
-        { KScope k(ctx, "fof3d.cell_table"); VR_LAUNCH(ctx, k_flag_heads, grid_for(n, T), T, 0, keys.p, n, flags.p);
-        exclusive_scan_u32(ctx, flags.p, excl.p, n, total.p); }
-        uint32_t hn = 0;
+        // cells and blocks: one 64-bit scan numbers both
+        DBuf<unsigned long long> heads(ctx, n), total(ctx, 1);
+        { KScope k(ctx, "fof3d.cell_table"); VR_LAUNCH(ctx, k_flag_heads, grid_for(n, T), T, 0, keys.p, n, heads.p);
+        exclusive_scan_u64(ctx, heads.p, heads.p, n, total.p); }
+        unsigned long long htot = 0;
         unsigned int hbad = 0;
-        VR_CUDA(cudaMemcpyAsync(&hn, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(&htot, total.p, sizeof(htot), cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(&hbad, nbad.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
         VR_REQUIRE(hbad == 0, VRGPU_EINVAL, "positions are NaN or outside [0, period]");
+        const uint32_t hn = (uint32_t)(htot & 0xffffffffull), hb = (uint32_t)(htot >> 32);
         S.ncells = hn;
         S.cell_of.alloc(ctx, n);
         S.cell_start.alloc(ctx, (size_t)hn + 1);
         S.cell_key.alloc(ctx, hn);
-        { KScope k(ctx, "fof3d.cell_table"); VR_LAUNCH(ctx, k_fill_cells, grid_for(n, T), T, 0, keys.p, flags.p, excl.p, n, S.cell_of.p, S.cell_start.p, S.cell_key.p, hn); }
+        BlockArrays BA{};
+        KScope k(ctx, "fof3d.cell_table");
+        if (use_blocks) {
+            cell_blk.alloc(ctx, hn); cell_loc.alloc(ctx, hn); blk_cell0.alloc(ctx, hb); blk_xyz.alloc(ctx, hb); blk_occ.alloc(ctx, hb);
+            bitmap.alloc(ctx, nwords); prefix.alloc(ctx, nwords);
+            VR_CUDA(cudaMemsetAsync(blk_occ.p, 0, sizeof(unsigned long long) * hb, ctx->stream));
+            VR_CUDA(cudaMemsetAsync(bitmap.p, 0, sizeof(unsigned long long) * nwords, ctx->stream));
+            BA = BlockArrays{cell_blk.p, cell_loc.p, blk_cell0.p, blk_xyz.p, blk_occ.p, bitmap.p};
+        }
+        VR_LAUNCH(ctx, k_fill_cells, grid_for(n, T), T, 0, keys.p, heads.p, n, geom, S.cell_of.p, S.cell_start.p, S.cell_key.p, hn, BA);
+        if (use_blocks) {
+            VR_LAUNCH(ctx, k_bitmap_counts, grid_for(nwords, T), T, 0, bitmap.p, nwords, prefix.p);
+            exclusive_scan_u32(ctx, prefix.p, prefix.p, nwords, nullptr);
+        }
         ctx->stats.sort_ms += t.stop();
     }
-    keys.reset(); keys_tmp.reset(); order_tmp.reset();
+    keys.reset();
     const uint32_t ncells = S.ncells;
     ctx->stats.n_cells = ncells;
 
-    // ---- hash + link ----
+    // ---- link ----
     DBuf<uint32_t> parent(ctx, ncells);
     {
         StageTimer t(ctx);
-        const uint64_t nrows = (uint64_t)g.nc[1] * (uint64_t)g.nc[2];
-        const bool use_rows = nrows <= (1ull << 29);
         size_t h = 1;
-        if (!use_rows) while (h < 2 * (size_t)ncells) h <<= 1;
+        if (!use_blocks) while (h < 2 * (size_t)ncells) h <<= 1;
         DBuf<uint64_t> hkeys(ctx, h);
         DBuf<uint32_t> hvals(ctx, h);
-        if (use_rows) {
+        if (use_blocks) {
             VR_LAUNCH(ctx, k_uf_init, grid_for(ncells, T), T, 0, parent.p, ncells);
         } else {
             KScope k(ctx, "fof3d.hash_build");
@@ -800,47 +766,43 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
         L.lox = g.lo[0]; L.loy = g.lo[1]; L.loz = g.lo[2];
         L.period = g.period; L.perx = g.periodic[0]; L.pery = g.periodic[1]; L.perz = g.periodic[2];
         L.b2 = b * b; // KDFOF.cxx:14
-        // one warp per cell, grid a multiple of the SM count
-        unsigned warps_needed = ncells;
-        unsigned blocks = std::min<unsigned>((warps_needed + 7) / 8, (unsigned)ctx->sm_count * 32u);
-        blocks = std::max(blocks, 1u);
-        if (use_rows) {
-            // dense row table (L2 resident at 256^3) + thread-per-cell linking, undecided dense pairs finished by warps
-            DBuf<uint32_t> row_first(ctx, nrows), row_last(ctx, nrows), cell_row(ctx, ncells);
-            DBuf<int> cell_ix(ctx, ncells);
+        L.g = geom;
+        if (use_blocks) {
+            // candidate table: built once per context on the host (pure integer function, link3.cuh)
+            static std::vector<unsigned long long> host_tab = [] {
+                std::vector<uint64_t> t(link3::TABLE_WORDS);
+                link3::build_table(t.data());
+                return std::vector<unsigned long long>(t.begin(), t.end());
+            }();
+            DBuf<unsigned long long> tab(ctx, link3::TABLE_WORDS);
+            VR_CUDA(cudaMemcpyAsync(tab.p, host_tab.data(), sizeof(unsigned long long) * link3::TABLE_WORDS, cudaMemcpyHostToDevice, ctx->stream));
             const uint32_t qcap = (uint32_t)std::min<size_t>((size_t)8 * ncells + 1024, (size_t)0x7fffffff);
             DBuf<uint32_t> qa(ctx, qcap), qb(ctx, qcap), qm(ctx, qcap);
             DBuf<unsigned int> qcount(ctx, 1);
             LinkQueue Q{qa.p, qb.p, qm.p, qcount.p, qcap};
+            BlockParams Bp{link3::Tables{bitmap.p, prefix.p, blk_occ.p, blk_cell0.p}, cell_blk.p, cell_loc.p, blk_xyz.p, tab.p};
             KScope k(ctx, "fof3d.link_cells");
-            VR_CUDA(cudaMemsetAsync(row_first.p, 0xff, sizeof(uint32_t) * nrows, ctx->stream));
-            VR_LAUNCH(ctx, k_cell_coords, grid_for(ncells, T), T, 0, S.cell_key.p, ncells, (uint64_t)g.nc[0], cell_row.p, cell_ix.p, row_first.p,
-                      row_last.p);
-            for (int reach = 1; reach <= 2; reach++) {
-                VR_CUDA(cudaMemsetAsync(qcount.p, 0, sizeof(unsigned int), ctx->stream));
-                VR_LAUNCH(ctx, k_link_thread, grid_for(ncells, 128), 128, 0, L, cell_row.p, cell_ix.p, row_first.p, row_last.p, reach, Q);
-                unsigned int nq = 0;
-                VR_CUDA(cudaMemcpyAsync(&nq, qcount.p, sizeof(nq), cudaMemcpyDeviceToHost, ctx->stream));
-                VR_CUDA(cudaStreamSynchronize(ctx->stream));
-                if (nq > qcap) {
-                    // queue overflow (pathological density): the warp-per-cell kernel redoes this reach exhaustively
-                    VR_LAUNCH(ctx, k_link_rows, blocks, 256, 0, L, row_first.p, row_last.p, reach);
-                } else if (nq) {
-                    const unsigned qblocks = std::max(1u, std::min<unsigned>((nq + 7) / 8, (unsigned)ctx->sm_count * 32u));
-                    VR_LAUNCH(ctx, k_link_queue, qblocks, 256, 0, L, cell_row.p, cell_ix.p, Q, nq);
-                }
-                ctx->stats.n_link_queue += nq;
-            }
+            VR_CUDA(cudaMemsetAsync(qcount.p, 0, sizeof(unsigned int), ctx->stream));
+            VR_LAUNCH(ctx, k_link_blocks, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, Q);
+            // dense cell pairs the short trial left undecided: one warp per pair, the count is read on the device
+            VR_LAUNCH(ctx, k_link_queue, (unsigned)ctx->sm_count * 16u, 256, 0, L, Q);
+            unsigned int nq = 0;
+            VR_CUDA(cudaMemcpyAsync(&nq, qcount.p, sizeof(nq), cudaMemcpyDeviceToHost, ctx->stream));
+            S.root.alloc(ctx, ncells);
+            { KScope kf(ctx, "fof3d.flatten"); VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); }
+            ctx->stats.link_ms += t.stop(); // synchronises: nq has arrived
+            ctx->stats.n_link_queue += std::min(nq, qcap);
         } else {
-            KScope k(ctx, "fof3d.link_cells");
-            VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 0, 13);
-            VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 13, 62);
+            // one warp per cell, grid a multiple of the SM count
+            const unsigned blocks = std::max(1u, std::min<unsigned>((ncells + 7) / 8, (unsigned)ctx->sm_count * 32u));
+            { KScope k(ctx, "fof3d.link_cells");
+              VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 0, 13);
+              VR_LAUNCH(ctx, k_link_cells, blocks, 256, 0, L, 13, 62); }
+            S.root.alloc(ctx, ncells);
+            { KScope k(ctx, "fof3d.flatten"); VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); }
+            ctx->stats.link_ms += t.stop();
         }
-        S.root.alloc(ctx, ncells);
-        { KScope k(ctx, "fof3d.flatten"); VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); }
-        ctx->stats.link_ms += t.stop();
     }
-
 }
 
 // group sizes / min pid per root cell, drop < minsize, ids by (size desc, min pid asc), pfof in caller order
