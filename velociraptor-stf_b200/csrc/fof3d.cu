@@ -327,16 +327,16 @@ struct BlockParams {
     const unsigned long long *table; // link3::build_table, TABLE_WORDS entries
 };
 
-// one candidate: are the cells A and B (image code and cell offset in meta) in one set already?  If not, a short trial of
-// particle pairs (all of them when there are at most 16, else the first 4 x 4); a link unites the sets, an undecided dense pair
-// goes to the queue of the warp-per-pair kernel (or is finished here when the queue is full)
-__device__ __forceinline__ void link_candidate(const LinkParams &P, const uint32_t A, const uint32_t B, const uint32_t meta, LinkQueue Q)
+// one candidate: are the cells A and B in one set already?  If not, a short trial of particle pairs (all of them when there are
+// at most 16, else the first 4 x 4); a link unites the sets, an undecided dense pair goes to the queue of the warp-per-pair
+// kernel (or is finished here when the queue is full).  cmeta: image code (6 bits) | block j << 6 | bit << 9 | local index << 15.
+__device__ __forceinline__ void link_candidate(const LinkParams &P, const uint32_t A, const uint32_t B, const uint32_t cmeta, const LinkQueue &Q)
 {
     const uint32_t ra = uf_find(P.parent, A), rb = uf_find(P.parent, B);
     if (ra == rb) return;
     const uint32_t a0 = P.cell_start[A], na = P.cell_start[A + 1] - a0;
     const uint32_t b0 = P.cell_start[B], nb = P.cell_start[B + 1] - b0;
-    const int sc = (int)(meta & 63u);
+    const int sc = (int)(cmeta & 63u);
     const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
     const double shx = (double)((sc & 3) - 1) * P.period, shy = (double)(((sc >> 2) & 3) - 1) * P.period,
                  shz = (double)(((sc >> 4) & 3) - 1) * P.period;
@@ -356,72 +356,88 @@ __device__ __forceinline__ void link_candidate(const LinkParams &P, const uint32
         }
         if (linked || few) break;
         const unsigned int slot = atomicAdd(Q.count, 1u);
-        if (slot < Q.capacity) { Q.a[slot] = A; Q.b[slot] = B; Q.meta[slot] = meta; break; }
+        if (slot < Q.capacity) {
+            int ddx, ddy, ddz;
+            link3::cell_offset((cmeta >> 15) & 63u, (cmeta >> 6) & 7u, (cmeta >> 9) & 63u, ddx, ddy, ddz);
+            Q.a[slot] = A;
+            Q.b[slot] = B;
+            Q.meta[slot] = (uint32_t)sc | ((uint32_t)(ddx + 2) << 6) | ((uint32_t)(ddy + 2) << 9) | ((uint32_t)(ddz + 2) << 12);
+            break;
+        }
         ta = na; tb = nb; // queue full (pathological density): this thread tests every pair itself
     }
     if (linked) uf_union(P.parent, A, B);
 }
 
+// PASS 0: the 13 adjacent half-space cells of every cell (this unites most of a halo).  PASS 1: the 49 cells of the second shell,
+// after every cell's root has been written to `snap`: a candidate whose snapshot root equals the cell's is dropped at once
+// (two independent loads instead of two pointer chases) -- inside a halo that is nearly all of them.
 constexpr int LB_THREADS = 256, LB_WARPS = LB_THREADS / 32;
-__global__ void __launch_bounds__(LB_THREADS) k_link_blocks(LinkParams P, BlockParams Bp, LinkQueue Q)
+template <int PASS>
+__global__ void __launch_bounds__(LB_THREADS) k_link_blocks(LinkParams P, BlockParams Bp, const uint32_t *__restrict__ snap, LinkQueue Q)
 {
-    __shared__ unsigned long long s_tab[link3::TABLE_WORDS];
-    __shared__ unsigned long long s_occ[8][LB_THREADS];
-    __shared__ uint32_t s_rank[8][LB_THREADS];
+    __shared__ unsigned long long s_tab[64 * 8];
     __shared__ uint32_t s_qa[LB_WARPS][64], s_qb[LB_WARPS][64], s_qm[LB_WARPS][64];
     const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    for (int i = tid; i < link3::TABLE_WORDS; i += LB_THREADS) s_tab[i] = Bp.table[i];
+    for (int i = tid; i < 64 * 8; i += LB_THREADS) s_tab[i] = Bp.table[PASS * 64 * 8 + i];
     const uint32_t cell = blockIdx.x * LB_THREADS + tid;
     const bool valid = cell < P.ncells;
     unsigned loc = 0;
     unsigned long long codes = 0;
+    uint32_t rank[8], myroot = 0;
+    unsigned long long occ[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) { rank[j] = 0; occ[j] = 0; }
     if (valid) {
         const uint32_t r = Bp.cell_blk[cell];
         loc = Bp.cell_loc[cell];
         int bx, by, bz;
         link3::unpack_xyz(__ldg(Bp.blk_xyz + r), bx, by, bz);
-        uint32_t rank[8];
-        unsigned long long occ[8];
         link3::lookup_blocks(P.g, Bp.T, r, bx, by, bz, loc, rank, occ, codes);
-#pragma unroll
-        for (int j = 0; j < 8; j++) { s_occ[j][tid] = occ[j]; s_rank[j][tid] = rank[j]; }
+        if (PASS == 1) myroot = __ldg(snap + cell);
     }
     __syncthreads();
-    // every lane walks its candidates (13 adjacent cells first, the second shell afterwards); the candidates of the warp are
-    // collected in shared memory and worked off 32 at a time, so the expensive part always runs on a full warp
+    // The 8 blocks in lockstep; the candidates of the warp are collected in shared memory and worked off 32 at a time, so the
+    // expensive part (root look-ups, pair trials) always runs on a full warp.
     const unsigned lt = (1u << lane) - 1u;
-    int pj = valid ? 0 : 16; // next (pass, block) to look at: pass * 8 + j
-    unsigned long long cand = 0;
     uint32_t qn = 0;
-    for (;;) {
-        while (cand == 0 && pj < 16) {
-            const int j = pj & 7;
-            cand = s_occ[j][tid] & s_tab[((pj >> 3) * 64 + (int)loc) * 8 + j];
-            pj++;
-        }
-        const bool has = cand != 0;
-        const unsigned bal = __ballot_sync(0xffffffffu, has);
-        if (!bal) break;
-        if (has) {
-            const unsigned j = (unsigned)(pj - 1) & 7u;
-            const unsigned bit = (unsigned)__ffsll((long long)cand) - 1u;
-            cand &= cand - 1ull;
-            int ddx, ddy, ddz;
-            link3::cell_offset(loc, j, bit, ddx, ddy, ddz);
-            const uint32_t slot = qn + (uint32_t)__popc(bal & lt);
-            s_qa[w][slot] = cell;
-            s_qb[w][slot] = link3::cell_of_bit(Bp.T, s_rank[j][tid], s_occ[j][tid], bit);
-            s_qm[w][slot] = (uint32_t)((codes >> (6 * j)) & 63ull) | ((uint32_t)(ddx + 2) << 6) | ((uint32_t)(ddy + 2) << 9) | ((uint32_t)(ddz + 2) << 12);
-        }
-        qn += (uint32_t)__popc(bal);
-        __syncwarp();
-        if (qn >= 32) {
-            qn -= 32;
-            link_candidate(P, s_qa[w][qn + lane], s_qb[w][qn + lane], s_qm[w][qn + lane], Q);
-            __syncwarp();
+#pragma unroll 1
+    for (int j = 0; j <= 8; j++) { // j == 8: nothing new, the rest of the queue is worked off
+        // occ[j], rank[j] by a chain of selects: the arrays stay in registers and the loop body exists once
+        unsigned long long oj = occ[0];
+        uint32_t rj = rank[0];
+#pragma unroll
+        for (int k = 1; k < 8; k++) if (j == k) { oj = occ[k]; rj = rank[k]; }
+        unsigned long long cand = j < 8 ? (oj & s_tab[loc * 8 + (j & 7)]) : 0ull;
+        for (;;) {
+            const bool more = __any_sync(0xffffffffu, cand != 0);
+            if (more) {
+                bool keep = false;
+                uint32_t B = 0, cm = 0;
+                if (cand != 0) {
+                    const unsigned bit = (unsigned)__ffsll((long long)cand) - 1u;
+                    cand &= cand - 1ull;
+                    B = link3::cell_of_bit(Bp.T, rj, oj, bit);
+                    keep = PASS == 0 || __ldg(snap + B) != myroot;
+                    cm = (uint32_t)((codes >> (6 * j)) & 63ull) | ((uint32_t)j << 6) | (bit << 9) | (loc << 15);
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, keep);
+                if (keep) {
+                    const uint32_t slot = qn + (uint32_t)__popc(bal & lt);
+                    s_qa[w][slot] = cell; s_qb[w][slot] = B; s_qm[w][slot] = cm;
+                }
+                qn += (uint32_t)__popc(bal);
+                __syncwarp();
+            }
+            if (qn >= 32 || (j == 8 && qn > 0)) {
+                const uint32_t take = qn >= 32 ? 32u : qn;
+                qn -= take;
+                if (lane < take) link_candidate(P, s_qa[w][qn + lane], s_qb[w][qn + lane], s_qm[w][qn + lane], Q);
+                __syncwarp();
+            }
+            if (!more) break;
         }
     }
-    if (lane < qn) link_candidate(P, s_qa[w][lane], s_qb[w][lane], s_qm[w][lane], Q);
 }
 
 // one warp per undecided cell pair: the exhaustive test
@@ -783,12 +799,14 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
             BlockParams Bp{link3::Tables{bitmap.p, prefix.p, blk_occ.p, blk_cell0.p}, cell_blk.p, cell_loc.p, blk_xyz.p, tab.p};
             KScope k(ctx, "fof3d.link_cells");
             VR_CUDA(cudaMemsetAsync(qcount.p, 0, sizeof(unsigned int), ctx->stream));
-            VR_LAUNCH(ctx, k_link_blocks, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, Q);
+            S.root.alloc(ctx, ncells);
+            VR_LAUNCH(ctx, k_link_blocks<0>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)nullptr, Q);
+            VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); // snapshot of the roots after pass 0
+            VR_LAUNCH(ctx, k_link_blocks<1>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)S.root.p, Q);
             // dense cell pairs the short trial left undecided: one warp per pair, the count is read on the device
             VR_LAUNCH(ctx, k_link_queue, (unsigned)ctx->sm_count * 16u, 256, 0, L, Q);
             unsigned int nq = 0;
             VR_CUDA(cudaMemcpyAsync(&nq, qcount.p, sizeof(nq), cudaMemcpyDeviceToHost, ctx->stream));
-            S.root.alloc(ctx, ncells);
             { KScope kf(ctx, "fof3d.flatten"); VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); }
             ctx->stats.link_ms += t.stop(); // synchronises: nq has arrived
             ctx->stats.n_link_queue += std::min(nq, qcap);

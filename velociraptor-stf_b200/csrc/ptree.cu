@@ -20,6 +20,7 @@
 #include "groups.cuh"
 #include "ptree.cuh"
 #include "rsqrt.cuh"
+#include "seqblock.cuh"
 #include "ufhash.cuh"
 
 #include <algorithm>
@@ -492,15 +493,73 @@ __global__ void k_pt_leaf_sums(PtNodes N, uint32_t nnodes, const double *__restr
     }
     N.sx[nd] = sx; N.sy[nd] = sy; N.sz[nd] = sz; N.sm[nd] = sm;
 }
-// internal nodes of one level: sum of the two children
-__global__ void k_pt_inner_sums(PtNodes N, uint32_t n0, uint32_t n1)
+// Internal nodes: the reference sums EVERY node from its first particle to its last (unbind.cxx:1672-1675), not parent =
+// left + right, and which cells a walk opens can depend on the last bit of the centre of mass (float32-quantised inputs
+// produce exact ties in the opening test: 68 of 200 000 particles of tests/test_gpu_tree.py::test_tree_with_tied_coordinates
+// flip with pairwise sums).  So every node gets the sequential sum:
+//   nodes above KD_SMALL particles: one CTA per (node, component) with the exact integer scan of seqsum.h,
+//   subtrees of at most KD_SMALL particles: one CTA per subtree, its particles in shared memory, one thread per (node, component).
+__global__ void __launch_bounds__(SQ_NT) k_pt_big_sums(PtNodes N, const uint32_t *__restrict__ list, const double *__restrict__ tx,
+                                                       const double *__restrict__ ty, const double *__restrict__ tz, const double *__restrict__ tm)
 {
-    uint32_t nd = n0 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (nd >= n1) return;
-    const uint32_t l = N.left[nd];
-    if (l == NOCHILD) return;
-    N.sx[nd] = __dadd_rn(N.sx[l], N.sx[l + 1]); N.sy[nd] = __dadd_rn(N.sy[l], N.sy[l + 1]);
-    N.sz[nd] = __dadd_rn(N.sz[l], N.sz[l + 1]); N.sm[nd] = __dadd_rn(N.sm[l], N.sm[l + 1]);
+    __shared__ SeqShared sh;
+    const uint32_t nd = list[blockIdx.x >> 2], comp = blockIdx.x & 3u;
+    const uint32_t s = N.start[nd];
+    const unsigned long long n = N.end[nd] - s;
+    double r;
+    if (comp == 3) r = block_seqsum(TermMass{tm + s}, n, 0.0, sh);
+    else r = block_seqsum(TermMomentum{(comp == 0 ? tx : (comp == 1 ? ty : tz)) + s, tm + s}, n, 0.0, sh);
+    if (threadIdx.x == 0) (comp == 0 ? N.sx : (comp == 1 ? N.sy : (comp == 2 ? N.sz : N.sm)))[nd] = r;
+}
+
+constexpr int PS_NT = 256, PS_QUEUE = KD_SMALL; // a subtree of n particles has fewer than n internal nodes
+struct PsShared {
+    double x[KD_SMALL], y[KD_SMALL], z[KD_SMALL], m[KD_SMALL];
+    uint32_t qnd[PS_QUEUE];
+    uint16_t qs[PS_QUEUE], qe[PS_QUEUE];
+    uint32_t qn;
+};
+__global__ void __launch_bounds__(PS_NT) k_pt_sub_sums(PtNodes N, const uint32_t *__restrict__ list, const uint32_t *__restrict__ count,
+                                                       const double *__restrict__ tx, const double *__restrict__ ty, const double *__restrict__ tz,
+                                                       const double *__restrict__ tm)
+{
+    extern __shared__ __align__(16) unsigned char ps_raw[];
+    PsShared &S = *reinterpret_cast<PsShared *>(ps_raw);
+    if (blockIdx.x >= *count) return;
+    const unsigned tid = threadIdx.x;
+    const uint32_t root = list[blockIdx.x];
+    const uint32_t g0 = N.start[root], n = N.end[root] - g0;
+    for (uint32_t p = tid; p < n; p += PS_NT) { S.x[p] = tx[g0 + p]; S.y[p] = ty[g0 + p]; S.z[p] = tz[g0 + p]; S.m[p] = tm[g0 + p]; }
+    if (tid == 0) { S.qnd[0] = root; S.qs[0] = 0; S.qe[0] = (uint16_t)n; S.qn = 1; } // the root splits (it is on the list)
+    __syncthreads();
+    // internal nodes of the subtree, level by level (children of the nodes queued by the previous round)
+    uint32_t qb = 0, qe = 1;
+    while (qb < qe) {
+        for (uint32_t i = qb + tid; i < qe; i += PS_NT) {
+            const uint32_t l = N.left[S.qnd[i]];
+            for (uint32_t c = l; c <= l + 1; c++)
+                if (N.left[c] != NOCHILD) {
+                    const uint32_t t = atomicAdd(&S.qn, 1u);
+                    S.qnd[t] = c; S.qs[t] = (uint16_t)(N.start[c] - g0); S.qe[t] = (uint16_t)(N.end[c] - g0);
+                }
+        }
+        __syncthreads();
+        qb = qe;
+        qe = S.qn;
+        __syncthreads();
+    }
+    // one thread per (node, component); the queue is in breadth-first order, so the long sums are spread over the threads
+    for (uint32_t task = tid; task < 4 * qe; task += PS_NT) {
+        const uint32_t q = task >> 2, comp = task & 3u;
+        const uint32_t a = S.qs[q], b = S.qe[q];
+        double acc = 0.0;
+        if (comp == 3) for (uint32_t p = a; p < b; p++) acc = __dadd_rn(acc, S.m[p]);
+        else {
+            const double *v = comp == 0 ? S.x : (comp == 1 ? S.y : S.z);
+            for (uint32_t p = a; p < b; p++) acc = __dadd_rn(acc, __dmul_rn(v[p], S.m[p]));
+        }
+        (comp == 0 ? N.sx : (comp == 1 ? N.sy : (comp == 2 ? N.sz : N.sm)))[S.qnd[q]] = acc;
+    }
 }
 __global__ void k_pt_cm(PtNodes N, uint32_t nnodes)
 {
@@ -687,7 +746,9 @@ bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_thres
     rootidx.alloc(ctx, nL);
     perm.alloc(ctx, nL);
     const size_t cap_list = 4 * ((size_t)nL / KD_SMALL + 1) + nLG + 64;
-    DBuf<uint32_t> big_list(ctx, cap_list), sub_list(ctx, cap_list), counters(ctx, 2), lflags, lexcl;
+    DBuf<uint32_t> &big_list = t.big_list, &sub_list = t.sub_list, &counters = t.sub_count;
+    big_list.alloc(ctx, cap_list); sub_list.alloc(ctx, cap_list); counters.alloc(ctx, 2);
+    DBuf<uint32_t> lflags, lexcl;
     std::vector<uint32_t> big_off{0u}; // nodes above KD_SMALL of level l: big_list[big_off[l], big_off[l+1])
     uint32_t nsub = 0, nnodes = nLG;
     {
@@ -758,6 +819,8 @@ bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_thres
     t.nL = nL;
     t.nLG = nLG;
     t.nnodes = nnodes;
+    t.nbig = big_off.back();
+    t.nsub = nsub;
     return true;
 }
 
@@ -782,9 +845,10 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
         VR_LAUNCH(ctx, k_pt_gather_tree, grid_for(nL, T), T, 0, reinterpret_cast<const KdRec *>(t.rec.p), gs.m.p, slot_of.p, nL, tx.p, ty.p, tz.p, tm.p);
         t.rec.reset();
         VR_LAUNCH(ctx, k_pt_leaf_sums, grid_for(nnodes, T), T, 0, N, nnodes, tx.p, ty.p, tz.p, tm.p);
-        for (size_t l = level_off.size() - 1; l-- > 0;) {
-            const uint32_t n0 = level_off[l], n1 = level_off[l + 1];
-            if (n1 > n0) VR_LAUNCH(ctx, k_pt_inner_sums, grid_for(n1 - n0, T), T, 0, N, n0, n1);
+        if (t.nbig) VR_LAUNCH(ctx, k_pt_big_sums, 4u * t.nbig, SQ_NT, 0, N, t.big_list.p, tx.p, ty.p, tz.p, tm.p);
+        if (t.nsub) {
+            VR_CUDA(cudaFuncSetAttribute(k_pt_sub_sums, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PsShared)));
+            VR_LAUNCH(ctx, k_pt_sub_sums, t.nsub, PS_NT, sizeof(PsShared), N, t.sub_list.p, t.sub_count.p + 1, tx.p, ty.p, tz.p, tm.p);
         }
         VR_LAUNCH(ctx, k_pt_cm, grid_for(nnodes, T), T, 0, N, nnodes);
         VR_LAUNCH(ctx, k_pt_bmax, grid_for(nL, T), T, 0, N, rootidx.p, nL, tx.p, ty.p, tz.p);

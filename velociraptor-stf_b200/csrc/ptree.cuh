@@ -15,6 +15,8 @@ struct PtTree {
     DBuf<uint32_t> nstart, nend, nleft;         // per node: tree positions [start, end), left child
     DBuf<uint32_t> rootidx;                     // tree position -> root node
     DBuf<double> rec;                           // the build's 32-byte records in tree order: x, y, z, (member, 0) -- 4 doubles per position
+    DBuf<uint32_t> big_list, sub_list, sub_count; // nodes above 2048 particles (all levels); roots of the subtrees of at most 2048; sub_count[1] = nsub
+    uint32_t nbig = 0, nsub = 0;
     std::vector<uint32_t> level_off;            // nodes of level l: [level_off[l], level_off[l + 1])
 };
 
