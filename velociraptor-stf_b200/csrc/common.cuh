@@ -112,6 +112,8 @@ struct vrgpu_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr; // host->device staging copies, overlapped with the unpack kernel
     void *stage_host[2] = {nullptr, nullptr}; // page-locked staging for results that go to pageable caller memory
+    static constexpr size_t UP_HOST_BYTES = (size_t)32 << 20;
+    void *up_host[3] = {nullptr, nullptr, nullptr}; // page-locked staging for particle records that come from pageable caller memory
     std::string err;
     vrgpu::Pool pool;
     vrgpu_stats stats{};

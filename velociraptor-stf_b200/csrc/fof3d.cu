@@ -369,15 +369,30 @@ __device__ __forceinline__ void link_candidate(const LinkParams &P, const uint32
     if (linked) uf_union(P.parent, A, B);
 }
 
+// after pass 0: the common root of a block's cells (0xffffffff when they differ).  Pass 1 skips a neighbouring block whose cells all
+// sit in the cell's own set with ONE look-up instead of one per candidate cell -- inside a halo that is nearly every block.
+__global__ void k_block_roots(const uint32_t *__restrict__ snap, const uint32_t *__restrict__ blk_cell0, uint32_t nblocks, uint32_t ncells,
+                              uint32_t *__restrict__ blk_root)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nblocks) return;
+    const uint32_t c0 = blk_cell0[r], c1 = r + 1 < nblocks ? blk_cell0[r + 1] : ncells;
+    const uint32_t root = snap[c0];
+    bool same = true;
+    for (uint32_t c = c0 + 1; c < c1; c++) same = same && snap[c] == root;
+    blk_root[r] = same ? root : 0xffffffffu;
+}
+
 // PASS 0: the 13 adjacent half-space cells of every cell (this unites most of a halo).  PASS 1: the 49 cells of the second shell,
 // after every cell's root has been written to `snap`: a candidate whose snapshot root equals the cell's is dropped at once
 // (two independent loads instead of two pointer chases) -- inside a halo that is nearly all of them.
-constexpr int LB_THREADS = 256, LB_WARPS = LB_THREADS / 32;
+constexpr int LB_THREADS = 256, LB_WARPS = LB_THREADS / 32, LB_POP = 4, LB_QCAP = 32 * (LB_POP + 1);
 template <int PASS>
-__global__ void __launch_bounds__(LB_THREADS) k_link_blocks(LinkParams P, BlockParams Bp, const uint32_t *__restrict__ snap, LinkQueue Q)
+__global__ void __launch_bounds__(LB_THREADS, 4) k_link_blocks(LinkParams P, BlockParams Bp, const uint32_t *__restrict__ snap,
+                                                            const uint32_t *__restrict__ blk_root, LinkQueue Q)
 {
     __shared__ unsigned long long s_tab[64 * 8];
-    __shared__ uint32_t s_qa[LB_WARPS][64], s_qb[LB_WARPS][64], s_qm[LB_WARPS][64];
+    __shared__ uint32_t s_qa[LB_WARPS][LB_QCAP], s_qb[LB_WARPS][LB_QCAP], s_qm[LB_WARPS][LB_QCAP];
     const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     for (int i = tid; i < 64 * 8; i += LB_THREADS) s_tab[i] = Bp.table[PASS * 64 * 8 + i];
     const uint32_t cell = blockIdx.x * LB_THREADS + tid;
@@ -397,8 +412,9 @@ __global__ void __launch_bounds__(LB_THREADS) k_link_blocks(LinkParams P, BlockP
         if (PASS == 1) myroot = __ldg(snap + cell);
     }
     __syncthreads();
-    // The 8 blocks in lockstep; the candidates of the warp are collected in shared memory and worked off 32 at a time, so the
-    // expensive part (root look-ups, pair trials) always runs on a full warp.
+    // The 8 blocks in lockstep; every lane pops up to LB_POP candidates per round (their snapshot look-ups leave together),
+    // the candidates of the warp are collected in shared memory and worked off 32 at a time, so the expensive part (root
+    // look-ups, pair trials) always runs on a full warp.
     const unsigned lt = (1u << lane) - 1u;
     uint32_t qn = 0;
 #pragma unroll 1
@@ -409,27 +425,40 @@ __global__ void __launch_bounds__(LB_THREADS) k_link_blocks(LinkParams P, BlockP
 #pragma unroll
         for (int k = 1; k < 8; k++) if (j == k) { oj = occ[k]; rj = rank[k]; }
         unsigned long long cand = j < 8 ? (oj & s_tab[loc * 8 + (j & 7)]) : 0ull;
+        if (PASS == 1 && cand != 0 && __ldg(blk_root + rj) == myroot) cand = 0; // the whole block is in this cell's set already
+        const uint32_t c0 = cand != 0 ? __ldg(Bp.T.blk_cell0 + rj) : 0u;
+        const uint32_t cmj = (uint32_t)((codes >> (6 * (j & 7))) & 63ull) | ((uint32_t)j << 6) | (loc << 15);
         for (;;) {
             const bool more = __any_sync(0xffffffffu, cand != 0);
             if (more) {
-                bool keep = false;
-                uint32_t B = 0, cm = 0;
-                if (cand != 0) {
-                    const unsigned bit = (unsigned)__ffsll((long long)cand) - 1u;
-                    cand &= cand - 1ull;
-                    B = link3::cell_of_bit(Bp.T, rj, oj, bit);
-                    keep = PASS == 0 || __ldg(snap + B) != myroot;
-                    cm = (uint32_t)((codes >> (6 * j)) & 63ull) | ((uint32_t)j << 6) | (bit << 9) | (loc << 15);
+                uint32_t B[LB_POP], bit[LB_POP];
+                bool keep[LB_POP];
+#pragma unroll
+                for (int k = 0; k < LB_POP; k++) {
+                    keep[k] = cand != 0;
+                    bit[k] = keep[k] ? (uint32_t)__ffsll((long long)cand) - 1u : 0u;
+                    cand &= cand - 1ull; // 0 stays 0
+                    B[k] = c0 + (uint32_t)__popcll(oj & ((1ull << bit[k]) - 1ull));
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, keep);
-                if (keep) {
-                    const uint32_t slot = qn + (uint32_t)__popc(bal & lt);
-                    s_qa[w][slot] = cell; s_qb[w][slot] = B; s_qm[w][slot] = cm;
+                if (PASS == 1) {
+                    uint32_t sb[LB_POP];
+#pragma unroll
+                    for (int k = 0; k < LB_POP; k++) sb[k] = keep[k] ? __ldg(snap + B[k]) : myroot;
+#pragma unroll
+                    for (int k = 0; k < LB_POP; k++) keep[k] = sb[k] != myroot;
                 }
-                qn += (uint32_t)__popc(bal);
+#pragma unroll
+                for (int k = 0; k < LB_POP; k++) {
+                    const unsigned bal = __ballot_sync(0xffffffffu, keep[k]);
+                    if (keep[k]) {
+                        const uint32_t slot = qn + (uint32_t)__popc(bal & lt);
+                        s_qa[w][slot] = cell; s_qb[w][slot] = B[k]; s_qm[w][slot] = cmj | (bit[k] << 9);
+                    }
+                    qn += (uint32_t)__popc(bal);
+                }
                 __syncwarp();
             }
-            if (qn >= 32 || (j == 8 && qn > 0)) {
+            while (qn >= 32 || (!more && j == 8 && qn > 0)) {
                 const uint32_t take = qn >= 32 ? 32u : qn;
                 qn -= take;
                 if (lane < take) link_candidate(P, s_qa[w][qn + lane], s_qb[w][qn + lane], s_qm[w][qn + lane], Q);
@@ -716,6 +745,7 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
     DBuf<uint32_t> cell_blk, blk_cell0, prefix;
     DBuf<uint8_t> cell_loc;
     DBuf<unsigned long long> blk_xyz, blk_occ, bitmap;
+    uint32_t nblocks = 0;
     {
         StageTimer t(ctx);
         { KScope k(ctx, "fof3d.cell_keys"); VR_LAUNCH(ctx, k_cell_keys, grid_for(n, T), T, 0, P.pos.p, n, g, geom, keys.p, S.order.p, nbad.p); }
@@ -735,6 +765,7 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
         VR_REQUIRE(hbad == 0, VRGPU_EINVAL, "positions are NaN or outside [0, period]");
         const uint32_t hn = (uint32_t)(htot & 0xffffffffull), hb = (uint32_t)(htot >> 32);
         S.ncells = hn;
+        nblocks = hb;
         S.cell_of.alloc(ctx, n);
         S.cell_start.alloc(ctx, (size_t)hn + 1);
         S.cell_key.alloc(ctx, hn);
@@ -800,9 +831,11 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
             KScope k(ctx, "fof3d.link_cells");
             VR_CUDA(cudaMemsetAsync(qcount.p, 0, sizeof(unsigned int), ctx->stream));
             S.root.alloc(ctx, ncells);
-            VR_LAUNCH(ctx, k_link_blocks<0>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)nullptr, Q);
+            DBuf<uint32_t> blk_root(ctx, nblocks);
+            VR_LAUNCH(ctx, k_link_blocks<0>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)nullptr, (const uint32_t *)nullptr, Q);
             VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); // snapshot of the roots after pass 0
-            VR_LAUNCH(ctx, k_link_blocks<1>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)S.root.p, Q);
+            VR_LAUNCH(ctx, k_block_roots, grid_for(nblocks, T), T, 0, S.root.p, blk_cell0.p, nblocks, ncells, blk_root.p);
+            VR_LAUNCH(ctx, k_link_blocks<1>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)S.root.p, (const uint32_t *)blk_root.p, Q);
             // dense cell pairs the short trial left undecided: one warp per pair, the count is read on the device
             VR_LAUNCH(ctx, k_link_queue, (unsigned)ctx->sm_count * 16u, 256, 0, L, Q);
             unsigned int nq = 0;
