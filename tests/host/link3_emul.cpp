@@ -163,7 +163,9 @@ extern "C" long long link3_fof(const double *pos, long long n, double b, double 
             const unsigned loc = cell_loc[c];
             uint32_t rank[8];
             unsigned long long occ[8], codes;
-            lookup_blocks(g, T, cell_blk[c], bx, by, bz, loc, rank, occ, codes);
+            lookup_blocks(g, T, bx, by, bz, loc, rank, occ, codes);
+            if (rank[0] != cell_blk[c]) return -6;
+            { int x2, y2, z2; unsigned l2; unpack_cell(pack_cell(bx, by, bz, loc), x2, y2, z2, l2); if (x2 != bx || y2 != by || z2 != bz || l2 != loc) return -7; }
             for (unsigned j = 0; j < 8; j++) {
                 unsigned long long cand = occ[j] & tab[(pass * 64 + loc) * 8 + j];
                 while (cand) {

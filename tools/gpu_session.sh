@@ -9,6 +9,7 @@ for s in "$@"; do
     rest) timeout 900 python -m pytest tests/test_gpu_unbind.py tests/test_gpu_zoom.py tests/test_gpu_dropin.py tests/test_gpu_veldens.py tests/test_gpu_energy.py -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/rest_pytest.log 2>&1; tail -30 gpurun_out/rest_pytest.log ;;
     all) timeout 1500 python -m pytest tests -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/all_pytest.log 2>&1; tail -30 gpurun_out/all_pytest.log ;;
     fof) timeout 900 python -m pytest tests/test_gpu_fof3d.py tests/test_gpu_fof6d.py tests/test_gpu_dropin.py -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/fof_pytest.log 2>&1; tail -30 gpurun_out/fof_pytest.log ;;
+    base) timeout 1500 python -m pytest tests/test_gpu_baseline_sizes.py -q -m gpu --tb=short -s -p no:cacheprovider > gpurun_out/base_pytest.log 2>&1; tail -12 gpurun_out/base_pytest.log ;;
     b256) timeout 600 python bench.py --nside 256 --steps 3 --warmup 2 --no-cpu-baseline --no-e2e-secondary > gpurun_out/b256_c3.json 2> gpurun_out/b256_c3.err; python tools/bench_summary.py gpurun_out/b256_c3.json 2>/dev/null | head -30; tail -3 gpurun_out/b256_c3.err ;;
     b256c2) timeout 600 python bench.py --config 2 --steps 3 --warmup 2 --no-cpu-baseline --no-e2e-secondary > gpurun_out/b256_c2.json 2> gpurun_out/b256_c2.err; python tools/bench_summary.py gpurun_out/b256_c2.json 2>/dev/null | head -30; tail -3 gpurun_out/b256_c2.err ;;
     b512) timeout 1500 python bench.py --steps 3 --warmup 2 --no-cpu-baseline --no-e2e-secondary > gpurun_out/b512_c3.json 2> gpurun_out/b512_c3.err; python tools/bench_summary.py gpurun_out/b512_c3.json 2>/dev/null | head -40; tail -3 gpurun_out/b512_c3.err ;;

@@ -127,10 +127,8 @@ __global__ void k_flag_heads(const uint64_t *__restrict__ keys, size_t n, unsign
 }
 
 struct BlockArrays {
-    uint32_t *cell_blk;            // cell -> rank of its block among the non-empty blocks
-    uint8_t *cell_loc;             // cell -> 6-bit index inside its block
+    unsigned long long *cell_rec;  // cell -> block coordinates + local index (link3::pack_cell)
     uint32_t *blk_cell0;           // block rank -> first cell
-    unsigned long long *blk_xyz;   // block rank -> packed block coordinates
     unsigned long long *blk_occ;   // block rank -> occupancy of its 64 cells (zeroed before)
     unsigned long long *bitmap;    // all blocks of the grid, one bit each (zeroed before; nullptr: hash path)
 };
@@ -152,14 +150,12 @@ __global__ void k_fill_cells(const uint64_t *__restrict__ keys, const unsigned l
         cell_key[c] = key;
         if (B.bitmap) {
             const uint32_t r = (uint32_t)(e >> 32) - (bhead ? 0u : 1u);
-            B.cell_blk[c] = r;
-            B.cell_loc[c] = (uint8_t)(key & 63u);
+            int ix, iy, iz;
+            link3::key_cell(geom, key, ix, iy, iz);
+            B.cell_rec[c] = link3::pack_cell(ix >> 2, iy >> 2, iz >> 2, (unsigned)(key & 63u));
             atomicOr(&B.blk_occ[r], 1ull << (key & 63u));
             if (bhead) {
-                int ix, iy, iz;
-                link3::key_cell(geom, key, ix, iy, iz);
                 B.blk_cell0[r] = c;
-                B.blk_xyz[r] = link3::pack_xyz(ix >> 2, iy >> 2, iz >> 2);
                 const uint64_t lin = key >> 6;
                 atomicOr(&B.bitmap[lin >> 6], 1ull << (lin & 63u));
             }
@@ -321,9 +317,7 @@ struct LinkQueue {
 
 struct BlockParams {
     link3::Tables T;
-    const uint32_t *cell_blk;
-    const uint8_t *cell_loc;
-    const unsigned long long *blk_xyz;
+    const unsigned long long *cell_rec;
     const unsigned long long *table; // link3::build_table, TABLE_WORDS entries
 };
 
@@ -332,10 +326,18 @@ struct BlockParams {
 // kernel (or is finished here when the queue is full).  cmeta: image code (6 bits) | block j << 6 | bit << 9 | local index << 15.
 __device__ __forceinline__ void link_candidate(const LinkParams &P, const uint32_t A, const uint32_t B, const uint32_t cmeta, const LinkQueue &Q)
 {
-    const uint32_t ra = uf_find(P.parent, A), rb = uf_find(P.parent, B);
+    // both root chases side by side, the cell ranges fetched while they run
+    volatile uint32_t *vp = P.parent;
+    uint32_t ra = A, rb = B, pa = vp[A], pb = vp[B];
+    const uint32_t a0 = __ldg(P.cell_start + A), a1 = __ldg(P.cell_start + A + 1);
+    const uint32_t b0 = __ldg(P.cell_start + B), b1 = __ldg(P.cell_start + B + 1);
+    while (pa != ra || pb != rb) {
+        const uint32_t ga = pa != ra ? vp[pa] : pa, gb = pb != rb ? vp[pb] : pb;
+        if (pa != ra) { if (ga != pa) P.parent[ra] = ga; ra = pa; pa = ga; } // path halving; a stale value is still an ancestor
+        if (pb != rb) { if (gb != pb) P.parent[rb] = gb; rb = pb; pb = gb; }
+    }
     if (ra == rb) return;
-    const uint32_t a0 = P.cell_start[A], na = P.cell_start[A + 1] - a0;
-    const uint32_t b0 = P.cell_start[B], nb = P.cell_start[B + 1] - b0;
+    const uint32_t na = a1 - a0, nb = b1 - b0;
     const int sc = (int)(cmeta & 63u);
     const bool wrapped = sc != (1 | (1 << 2) | (1 << 4));
     const double shx = (double)((sc & 3) - 1) * P.period, shy = (double)(((sc >> 2) & 3) - 1) * P.period,
@@ -389,14 +391,19 @@ __global__ void k_block_roots(const uint32_t *__restrict__ snap, const uint32_t 
 constexpr int LB_THREADS = 256, LB_WARPS = LB_THREADS / 32, LB_POP = 4, LB_QCAP = 32 * (LB_POP + 1);
 template <int PASS>
 __global__ void __launch_bounds__(LB_THREADS, 4) k_link_blocks(LinkParams P, BlockParams Bp, const uint32_t *__restrict__ snap,
-                                                            const uint32_t *__restrict__ blk_root, LinkQueue Q)
+                                                               const uint32_t *__restrict__ blk_root, uint8_t *__restrict__ need2, LinkQueue Q)
 {
-    __shared__ unsigned long long s_tab[64 * 8];
+    __shared__ unsigned long long s_tab[(PASS == 0 ? 2 : 1) * 64 * 8]; // pass 0 also looks at the second shell: who needs pass 1?
     __shared__ uint32_t s_qa[LB_WARPS][LB_QCAP], s_qb[LB_WARPS][LB_QCAP], s_qm[LB_WARPS][LB_QCAP];
     const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    for (int i = tid; i < 64 * 8; i += LB_THREADS) s_tab[i] = Bp.table[PASS * 64 * 8 + i];
+    for (int i = tid; i < (PASS == 0 ? 2 : 1) * 64 * 8; i += LB_THREADS) s_tab[i] = Bp.table[PASS * 64 * 8 + i];
+    __syncthreads();
     const uint32_t cell = blockIdx.x * LB_THREADS + tid;
-    const bool valid = cell < P.ncells;
+    bool valid = cell < P.ncells;
+    if (PASS == 1) {
+        valid = valid && need2[cell] != 0;
+        if (!__any_sync(0xffffffffu, valid)) return; // no cell of this warp has a neighbour in the second shell
+    }
     unsigned loc = 0;
     unsigned long long codes = 0;
     uint32_t rank[8], myroot = 0;
@@ -404,28 +411,38 @@ __global__ void __launch_bounds__(LB_THREADS, 4) k_link_blocks(LinkParams P, Blo
 #pragma unroll
     for (int j = 0; j < 8; j++) { rank[j] = 0; occ[j] = 0; }
     if (valid) {
-        const uint32_t r = Bp.cell_blk[cell];
-        loc = Bp.cell_loc[cell];
         int bx, by, bz;
-        link3::unpack_xyz(__ldg(Bp.blk_xyz + r), bx, by, bz);
-        link3::lookup_blocks(P.g, Bp.T, r, bx, by, bz, loc, rank, occ, codes);
+        link3::unpack_cell(__ldg(Bp.cell_rec + cell), bx, by, bz, loc);
+        link3::lookup_blocks(P.g, Bp.T, bx, by, bz, loc, rank, occ, codes);
         if (PASS == 1) myroot = __ldg(snap + cell);
     }
-    __syncthreads();
-    // The 8 blocks in lockstep; every lane pops up to LB_POP candidates per round (their snapshot look-ups leave together),
-    // the candidates of the warp are collected in shared memory and worked off 32 at a time, so the expensive part (root
-    // look-ups, pair trials) always runs on a full warp.
+    // which of the 8 blocks hold candidates for some lane of the warp?
+    unsigned jmask = 0;
+    bool later = false;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        unsigned long long c = occ[j] & s_tab[loc * 8 + j];
+        if (PASS == 1 && c != 0 && __ldg(blk_root + rank[j]) == myroot) { c = 0; occ[j] = 0; } // the whole block is in this cell's set already
+        if (PASS == 0) later = later || (occ[j] & s_tab[64 * 8 + loc * 8 + j]) != 0;
+        if (__any_sync(0xffffffffu, c != 0)) jmask |= 1u << j;
+    }
+    if (PASS == 0 && valid) need2[cell] = later ? 1 : 0;
+    if (jmask == 0) return;
+    jmask |= 1u << 8; // last round: nothing new, the rest of the queue is worked off
+    // The blocks in lockstep; every lane pops up to LB_POP candidates per round (their snapshot look-ups leave together), the
+    // candidates of the warp are collected in shared memory and worked off 32 at a time, so the expensive part (root look-ups,
+    // pair trials) always runs on a full warp.
     const unsigned lt = (1u << lane) - 1u;
     uint32_t qn = 0;
-#pragma unroll 1
-    for (int j = 0; j <= 8; j++) { // j == 8: nothing new, the rest of the queue is worked off
+    while (jmask) {
+        const int j = __ffs(jmask) - 1;
+        jmask &= jmask - 1;
         // occ[j], rank[j] by a chain of selects: the arrays stay in registers and the loop body exists once
         unsigned long long oj = occ[0];
         uint32_t rj = rank[0];
 #pragma unroll
         for (int k = 1; k < 8; k++) if (j == k) { oj = occ[k]; rj = rank[k]; }
         unsigned long long cand = j < 8 ? (oj & s_tab[loc * 8 + (j & 7)]) : 0ull;
-        if (PASS == 1 && cand != 0 && __ldg(blk_root + rj) == myroot) cand = 0; // the whole block is in this cell's set already
         const uint32_t c0 = cand != 0 ? __ldg(Bp.T.blk_cell0 + rj) : 0u;
         const uint32_t cmj = (uint32_t)((codes >> (6 * (j & 7))) & 63ull) | ((uint32_t)j << 6) | (loc << 15);
         for (;;) {
@@ -742,9 +759,8 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
     S.order.alloc(ctx, n);
     DBuf<unsigned int> nbad(ctx, 1);
     VR_CUDA(cudaMemsetAsync(nbad.p, 0, sizeof(unsigned int), ctx->stream));
-    DBuf<uint32_t> cell_blk, blk_cell0, prefix;
-    DBuf<uint8_t> cell_loc;
-    DBuf<unsigned long long> blk_xyz, blk_occ, bitmap;
+    DBuf<uint32_t> blk_cell0, prefix;
+    DBuf<unsigned long long> cell_rec, blk_occ, bitmap;
     uint32_t nblocks = 0;
     {
         StageTimer t(ctx);
@@ -772,11 +788,11 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
         BlockArrays BA{};
         KScope k(ctx, "fof3d.cell_table");
         if (use_blocks) {
-            cell_blk.alloc(ctx, hn); cell_loc.alloc(ctx, hn); blk_cell0.alloc(ctx, hb); blk_xyz.alloc(ctx, hb); blk_occ.alloc(ctx, hb);
+            cell_rec.alloc(ctx, hn); blk_cell0.alloc(ctx, hb); blk_occ.alloc(ctx, hb);
             bitmap.alloc(ctx, nwords); prefix.alloc(ctx, nwords);
             VR_CUDA(cudaMemsetAsync(blk_occ.p, 0, sizeof(unsigned long long) * hb, ctx->stream));
             VR_CUDA(cudaMemsetAsync(bitmap.p, 0, sizeof(unsigned long long) * nwords, ctx->stream));
-            BA = BlockArrays{cell_blk.p, cell_loc.p, blk_cell0.p, blk_xyz.p, blk_occ.p, bitmap.p};
+            BA = BlockArrays{cell_rec.p, blk_cell0.p, blk_occ.p, bitmap.p};
         }
         VR_LAUNCH(ctx, k_fill_cells, grid_for(n, T), T, 0, keys.p, heads.p, n, geom, S.cell_of.p, S.cell_start.p, S.cell_key.p, hn, BA);
         if (use_blocks) {
@@ -827,15 +843,16 @@ void fof3d_link(vrgpu_ctx *ctx, const DeviceParticles &P, double b, double perio
             DBuf<uint32_t> qa(ctx, qcap), qb(ctx, qcap), qm(ctx, qcap);
             DBuf<unsigned int> qcount(ctx, 1);
             LinkQueue Q{qa.p, qb.p, qm.p, qcount.p, qcap};
-            BlockParams Bp{link3::Tables{bitmap.p, prefix.p, blk_occ.p, blk_cell0.p}, cell_blk.p, cell_loc.p, blk_xyz.p, tab.p};
+            BlockParams Bp{link3::Tables{bitmap.p, prefix.p, blk_occ.p, blk_cell0.p}, cell_rec.p, tab.p};
             KScope k(ctx, "fof3d.link_cells");
             VR_CUDA(cudaMemsetAsync(qcount.p, 0, sizeof(unsigned int), ctx->stream));
             S.root.alloc(ctx, ncells);
             DBuf<uint32_t> blk_root(ctx, nblocks);
-            VR_LAUNCH(ctx, k_link_blocks<0>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)nullptr, (const uint32_t *)nullptr, Q);
+            DBuf<uint8_t> need2(ctx, ncells);
+            VR_LAUNCH(ctx, k_link_blocks<0>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)nullptr, (const uint32_t *)nullptr, need2.p, Q);
             VR_LAUNCH(ctx, k_flatten, grid_for(ncells, T), T, 0, parent.p, ncells, S.root.p); // snapshot of the roots after pass 0
             VR_LAUNCH(ctx, k_block_roots, grid_for(nblocks, T), T, 0, S.root.p, blk_cell0.p, nblocks, ncells, blk_root.p);
-            VR_LAUNCH(ctx, k_link_blocks<1>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)S.root.p, (const uint32_t *)blk_root.p, Q);
+            VR_LAUNCH(ctx, k_link_blocks<1>, grid_for(ncells, LB_THREADS), LB_THREADS, 0, L, Bp, (const uint32_t *)S.root.p, (const uint32_t *)blk_root.p, need2.p, Q);
             // dense cell pairs the short trial left undecided: one warp per pair, the count is read on the device
             VR_LAUNCH(ctx, k_link_queue, (unsigned)ctx->sm_count * 16u, 256, 0, L, Q);
             unsigned int nq = 0;

@@ -145,22 +145,35 @@ struct Tables {
     const uint32_t *blk_cell0;        // per non-empty block: index of its first cell
 };
 
-// For the cell with local index loc in the non-empty block own_rank at (bx, by, bz): rank and occupancy of the 8 blocks its
-// neighbourhood touches (occ[j] == 0: empty, outside an open grid, or wholly behind the cell) and the image code of each
-// (6 bits per j in `codes`: (sx+1) | (sy+1) << 2 | (sz+1) << 4).
-L3_HD void lookup_blocks(const Geom &g, const Tables &T, uint32_t own_rank, int bx, int by, int bz, unsigned loc, uint32_t rank[8],
-                         unsigned long long occ[8], unsigned long long &codes)
+// one 64-bit record per cell: block coordinates (19 bits each) and the local index
+L3_HD uint64_t pack_cell(int bx, int by, int bz, unsigned loc)
+{
+    return (uint64_t)bx | ((uint64_t)by << 19) | ((uint64_t)bz << 38) | ((uint64_t)loc << 57);
+}
+L3_HD void unpack_cell(uint64_t v, int &bx, int &by, int &bz, unsigned &loc)
+{
+    bx = (int)(v & 0x7ffffu); by = (int)((v >> 19) & 0x7ffffu); bz = (int)((v >> 38) & 0x7ffffu); loc = (unsigned)(v >> 57) & 63u;
+}
+
+// For the cell with local index loc in the block at (bx, by, bz): rank and occupancy of the 8 blocks its neighbourhood touches
+// (occ[j] == 0: empty, outside an open grid, or wholly behind the cell) and the image code of each (6 bits per j in `codes`:
+// (sx+1) | (sy+1) << 2 | (sz+1) << 4).  Two levels of independent loads: 8 bitmap words, then rank + occupancy of the blocks
+// that exist (j = 0 is the cell's own block).
+L3_HD void lookup_blocks(const Geom &g, const Tables &T, int bx, int by, int bz, unsigned loc, uint32_t rank[8], unsigned long long occ[8],
+                         unsigned long long &codes)
 {
     const int lx = (int)(loc & 3u), ly = (int)((loc >> 2) & 3u), lz = (int)(loc >> 4);
-    int nx[2], ny[2], nz[2], sx[2], sy[2], sz[2], d;
-    bool okx[2], oky[2], okz[2];
-    for (int w = 0; w < 2; w++) {
-        okx[w] = axis_block(bx, lx, w, g.nbx, g.perx, nx[w], sx[w], d);
-        oky[w] = axis_block(by, ly, w, g.nby, g.pery, ny[w], sy[w], d);
-        okz[w] = axis_block(bz, lz, w, g.nbz, g.perz, nz[w], sz[w], d);
-    }
+    int n1, s1[3], d;
+    bool ok1[3];
+    // linear index = ax[jx] + ay[jy] + az[jz]
+    uint64_t ax[2], ay[2], az[2];
+    const uint64_t nxy = (uint64_t)g.nbx * (uint64_t)g.nby;
+    ax[0] = (uint64_t)bx; ay[0] = (uint64_t)by * (uint64_t)g.nbx; az[0] = (uint64_t)bz * nxy;
+    ok1[0] = axis_block(bx, lx, 1, g.nbx, g.perx, n1, s1[0], d); ax[1] = (uint64_t)n1;
+    ok1[1] = axis_block(by, ly, 1, g.nby, g.pery, n1, s1[1], d); ay[1] = (uint64_t)n1 * (uint64_t)g.nbx;
+    ok1[2] = axis_block(bz, lz, 1, g.nbz, g.perz, n1, s1[2], d); az[1] = (uint64_t)n1 * nxy;
     // the other block along z lies behind the cell when it is the lower one: nothing of it is in the forward half space
-    if (lz < 2) okz[1] = false;
+    if (lz < 2) ok1[2] = false;
     unsigned long long word[8];
     uint64_t blin[8];
     codes = 0;
@@ -169,25 +182,19 @@ L3_HD void lookup_blocks(const Geom &g, const Tables &T, uint32_t own_rank, int 
 #endif
     for (int j = 0; j < 8; j++) {
         const int jx = j & 1, jy = (j >> 1) & 1, jz = j >> 2;
-        const bool ok = okx[jx] && oky[jy] && okz[jz];
-        blin[j] = ok ? block_linear(g, nx[jx], ny[jy], nz[jz]) : 0;
-        word[j] = (ok && j != 0) ? L3_LD64(T.bitmap + (blin[j] >> 6)) : 0ull;
-        if (!ok) blin[j] = ~(uint64_t)0;
-        codes |= (unsigned long long)((sx[jx] + 1) | ((sy[jy] + 1) << 2) | ((sz[jz] + 1) << 4)) << (6 * j);
+        const bool ok = (!jx || ok1[0]) && (!jy || ok1[1]) && (!jz || ok1[2]);
+        blin[j] = ax[jx] + ay[jy] + az[jz];
+        word[j] = ok ? L3_LD64(T.bitmap + (blin[j] >> 6)) : 0ull;
+        codes |= (unsigned long long)(((jx ? s1[0] : 0) + 1) | (((jy ? s1[1] : 0) + 1) << 2) | (((jz ? s1[2] : 0) + 1) << 4)) << (6 * j);
     }
-    rank[0] = own_rank;
-    occ[0] = L3_LD64(T.blk_occ + own_rank);
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-    for (int j = 1; j < 8; j++) {
-        rank[j] = 0;
-        occ[j] = 0;
-        if (blin[j] == ~(uint64_t)0) continue;
+    for (int j = 0; j < 8; j++) {
         const unsigned bit = (unsigned)(blin[j] & 63u);
-        if (!((word[j] >> bit) & 1ull)) continue;
-        rank[j] = L3_LD32(T.prefix + (blin[j] >> 6)) + (uint32_t)L3_POPC64(word[j] & ((1ull << bit) - 1ull));
-        occ[j] = L3_LD64(T.blk_occ + rank[j]);
+        const bool there = ((word[j] >> bit) & 1ull) != 0; // word == 0 for the blocks that were not looked at
+        rank[j] = there ? L3_LD32(T.prefix + (blin[j] >> 6)) + (uint32_t)L3_POPC64(word[j] & ((1ull << bit) - 1ull)) : 0u;
+        occ[j] = there ? L3_LD64(T.blk_occ + rank[j]) : 0ull;
     }
 }
 
