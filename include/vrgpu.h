@@ -54,7 +54,8 @@ typedef struct {
     double minEfrac;           /* UnbindInfo::minEfrac                                              */
     int unbindtype;            /* UnbindInfo::unbindtype 0 = USYSANDPART, 1 = UPART                 */
     int bgpot;                 /* UnbindInfo::bgpot; 1 keep the background potential, 0 take removed particles' pair terms off */
-    double fracpotref;         /* UnbindInfo::fracpotref; only 1.0 (whole-group CM frame)           */
+    double fracpotref;         /* UnbindInfo::fracpotref: 1.0 = CM velocity of the whole group, else the frame of the innermost
+                                  max(npotref, fracpotref * n) members (unbind.cxx:460-544), see cmvelreftype */
     double maxunbindfrac;      /* UnbindInfo::maxunbindfrac (0.5)                                   */
     double maxunboundfracforiterativeunbind; /* (0.95)                                              */
     double maxallowedunboundfrac;            /* (0.025)                                             */
@@ -64,6 +65,9 @@ typedef struct {
     long long pp_threshold;    /* UNBINDNUM (150): n <= this -> direct sum; < 0 -> direct sum always */
     long long large_threshold; /* ompunbindnum (1000): selects the reference's two loop variants    */
     double marginal_tol;       /* |E| <= tol*|phi| counts as marginal (BASELINE.json: 1e-6)         */
+    int cmvelreftype;          /* UnbindInfo::cmvelreftype, read when fracpotref != 1: 0 CMVELREF (radii about the centre of mass),
+                                  1 POTREF (about the member with the lowest potential) -- allvars.h:216-218 */
+    long long npotref;         /* UnbindInfo::Npotref (20)                                          */
 } vrgpu_unbind_opts;
 
 /* Options subset SearchFullSet reads on the DM-only path (src/search.cxx:24-854). */

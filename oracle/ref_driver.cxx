@@ -302,6 +302,36 @@ long long vrref_unbind(long long n, const double *pos, const double *vel, const 
     return ng;
 }
 
+/* CheckUnboundGroups with the full argument list of the SearchSubSub call sites (search.cxx:2674, :2867): numingroup and pglist
+ * built by the reference's own BuildNumInGroup / BuildPGList, ireorder as given, groupflag (may be NULL, ngroup + 1 entries, IN/OUT).
+ * numingroup_out: ngroup + 1 entries as the callee leaves them. */
+long long vrref_unbind_full(long long n, const double *pos, const double *vel, const double *mass, const vrref_opts *o, long long *pfof,
+                            long long ngroup, int ireorder, long long *groupflag, long long *numingroup_out, int *changed)
+{
+    Options opt;
+    fill_options(opt, o);
+    vector<Particle> P;
+    fill_particles(P, n, pos, vel, mass, NULL);
+    Int_t *pf = new Int_t[n];
+    for (long long i = 0; i < n; i++) pf[i] = pfof[i];
+    Int_t ng = ngroup;
+    Int_t *num = BuildNumInGroup(n, ng, pf);
+    Int_t **pgl = BuildPGList(n, ng, num, pf);
+    Int_t *gf = NULL;
+    if (groupflag) { gf = new Int_t[ngroup + 1]; for (long long g = 0; g <= ngroup; g++) gf[g] = groupflag[g]; }
+    streambuf *old = NULL;
+    stringstream sink;
+    if (!o->verbose) old = cout.rdbuf(sink.rdbuf());
+    int flag = CheckUnboundGroups(opt, n, P.data(), ng, pf, num, pgl, ireorder, gf);
+    if (old) cout.rdbuf(old);
+    if (changed) *changed = flag;
+    for (long long i = 0; i < n; i++) pfof[i] = pf[i];
+    for (long long g = 0; g <= ngroup; g++) { if (numingroup_out) numingroup_out[g] = num[g]; if (gf) groupflag[g] = gf[g]; }
+    for (long long g = 1; g <= ngroup; g++) delete[] pgl[g];
+    delete[] pgl; delete[] num; delete[] pf; delete[] gf;
+    return ng;
+}
+
 /* GetBindingEnergy on GROUP-ORDERED flat arrays: group g = 1..ngroup owns numingroup[g] consecutive particles (the layout
  * SortAccordingtoBindingEnergy builds, substructureproperties.cxx:4279-4290).  gcmvel[3*g..] is stored into pdata[g].gcmvel
  * (what GetCM would have left there).  Outputs per particle: potential and binding energy (Particle::rho); per group: T,

@@ -942,8 +942,8 @@ static void unbind_group(uctx *c, i64 *ning_io, upart *gp, double *cmvel, double
     double eps2 = o->eps * o->eps;
     while (unbindcheck) {
         (*iunbindflag)++;
-        /* UpdateCMForUnboundParticles (unbind.cxx:111-127), fracpotref == 1 */
-        {
+        /* UpdateCMForUnboundParticles (unbind.cxx:111-127): only the whole-group frame follows the removals */
+        if (o->fracpotref == 1.0) {
             double temp = 1.0 / (*gmass), temp2 = 0.;
             for (i64 j = 0; j < nEplus; j++) {
                 i64 i = gp[nEplusid[j]].idx;
@@ -995,6 +995,14 @@ static void unbind_group(uctx *c, i64 *ning_io, upart *gp, double *cmvel, double
     *ning_io = ning;
 }
 
+typedef struct { double r; i64 j; } radrec;
+static int cmp_radrec(const void *a, const void *b)
+{
+    const radrec *x = (const radrec *)a, *y = (const radrec *)b;
+    if (x->r != y->r) return x->r < y->r ? -1 : 1;
+    return x->j < y->j ? -1 : (x->j > y->j ? 1 : 0);
+}
+
 long long vro_unbind(long long n, const double *pos, const double *vel, const double *mass, long long *pfof,
                      long long ngroups, const vro_unbind_opts *o, const long long *pid, double marginal_tol,
                      long long *n_marginal_out, double *phi_out, int *changed_out)
@@ -1002,7 +1010,6 @@ long long vro_unbind(long long n, const double *pos, const double *vel, const do
     if (changed_out) *changed_out = 0;
     if (n_marginal_out) *n_marginal_out = 0;
     if (ngroups <= 0) return 0;
-    if (o->fracpotref != 1.0) { fprintf(stderr, "vro_unbind: only Frac_pot_ref=1 is restated\n"); return -1; }
     /* BuildNumInGroup / BuildPGList (buildandsortarrays.cxx:11-43): members in index order */
     i64 *num = (i64 *)calloc((size_t)ngroups + 2, sizeof(i64));
     i64 *off = (i64 *)calloc((size_t)ngroups + 2, sizeof(i64));
@@ -1036,13 +1043,50 @@ long long vro_unbind(long long n, const double *pos, const double *vel, const do
         if (o->pp_threshold < 0 || ng <= o->pp_threshold) vro_potential_pp(ng, gx, gm, o->G, o->eps, gphi);
         else vro_potential_tree(ng, gx, gm, o->G, o->eps, o->theta, o->bucket, gphi, NULL);
         for (i64 j = 0; j < ng; j++) { p[j].phi = gphi[j]; p[j].E = 0; if (phi_out) phi_out[p[j].idx] = gphi[j]; }
-        /* unbind.cxx:447-455 */
-        for (i64 j = 0; j < ng; j++) {
-            gmass[g] += mass[p[j].idx];
-            for (int k = 0; k < 3; k++) cmvel[3 * g + k] += vel[3 * p[j].idx + k] * mass[p[j].idx];
+        if (o->fracpotref == 1.0) {
+            /* unbind.cxx:447-455 */
+            for (i64 j = 0; j < ng; j++) {
+                gmass[g] += mass[p[j].idx];
+                for (int k = 0; k < 3; k++) cmvel[3 * g + k] += vel[3 * p[j].idx + k] * mass[p[j].idx];
+            }
+            double inv = 1.0 / gmass[g];
+            for (int k = 0; k < 3; k++) cmvel[3 * g + k] *= inv;
+        } else {
+            /* unbind.cxx:460-544: velocity frame of the innermost npot members, by radius about the centre of mass (CMVELREF) or
+             * about the member with the lowest potential (POTREF, first strict minimum).  gsl_heapsort leaves equal radii in an
+             * order of its own; here they keep member order. */
+            double c0[3] = {0., 0., 0.};
+            if (o->cmvelreftype == 0) {
+                for (i64 j = 0; j < ng; j++) {
+                    gmass[g] += mass[p[j].idx];
+                    for (int k = 0; k < 3; k++) c0[k] += pos[3 * p[j].idx + k] * mass[p[j].idx];
+                }
+                const double inv = 1.0 / gmass[g];
+                for (int k = 0; k < 3; k++) c0[k] *= inv;
+            } else {
+                i64 imin = 0;
+                for (i64 j = 1; j < ng; j++) if (p[j].phi < p[imin].phi) imin = j;
+                for (int k = 0; k < 3; k++) c0[k] = pos[3 * p[imin].idx + k];
+            }
+            radrec *rr = (radrec *)malloc(sizeof(radrec) * (size_t)(ng + 1));
+            for (i64 j = 0; j < ng; j++) {
+                const double x = pos[3 * p[j].idx] - c0[0], y = pos[3 * p[j].idx + 1] - c0[1], z = pos[3 * p[j].idx + 2] - c0[2];
+                rr[j].r = sqrt(x * x + y * y + z * z); /* Particle::Radius() */
+                rr[j].j = j;
+            }
+            qsort(rr, (size_t)ng, sizeof(radrec), cmp_radrec);
+            i64 npot = (i64)(o->fracpotref * (double)ng);
+            if (npot < o->npotref) npot = o->npotref;
+            if (npot > ng) npot = ng;
+            double menc = 0.;
+            for (i64 q = 0; q < npot; q++) {
+                const i64 i = p[rr[q].j].idx;
+                for (int k = 0; k < 3; k++) cmvel[3 * g + k] += vel[3 * i + k] * mass[i];
+                menc += mass[i];
+            }
+            for (int k = 0; k < 3; k++) cmvel[3 * g + k] /= menc;
+            free(rr);
         }
-        double inv = 1.0 / gmass[g];
-        for (int k = 0; k < 3; k++) cmvel[3 * g + k] *= inv;
     }
     free(gphi); free(gm); free(gx);
 

@@ -20,7 +20,8 @@ typedef struct {
     double minEfrac;          /* uinfo.minEfrac */
     int unbindtype;           /* 0 USYSANDPART, 1 UPART  (allvars.h:211-213) */
     int bgpot;                /* uinfo.bgpot (1: keep background potential) */
-    double fracpotref;        /* must be 1.0 (CM frame of the whole group, unbind.cxx:440-459) */
+    double fracpotref;        /* uinfo.fracpotref: 1.0 = CM velocity of the whole group (unbind.cxx:440-459), else the frame of the
+                                 innermost max(npotref, fracpotref * n) members (unbind.cxx:460-544) */
     double maxunbindfrac;     /* 0.5 */
     double maxunboundfracforiterativeunbind; /* 0.95 */
     double maxallowedunboundfrac;            /* 0.025 */
@@ -33,6 +34,9 @@ typedef struct {
                                  1: literal serial reference: oldnumingroup carried across groups,
                                     starting from oldn_init (the reference reads it UNINITIALISED: stack garbage) */
     long long oldn_init;      /* mode 1 only: the garbage value assumed for the uninitialised oldnumingroup */
+    int cmvelreftype;         /* uinfo.cmvelreftype when fracpotref != 1: 0 CMVELREF (radii about the centre of mass), 1 POTREF
+                                 (about the member with the lowest potential) -- allvars.h:216-218 */
+    long long npotref;        /* uinfo.Npotref (20) */
 } vro_unbind_opts;
 
 /* KDTree::FOF with TPHYS (KDFOF.cxx:12-129, KDLeafNode.cxx:518-573, KDSplitNode.cxx:1496-1540):

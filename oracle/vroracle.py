@@ -201,6 +201,20 @@ class Ref:
         return {"pfof": pf, "ngroups": int(ng), "changed": int(ch.value), "seconds": sec.value}
 
 
+    def unbind_full(self, pos, vel, mass, pfof, ngroup, opts: RefOpts, ireorder=1, groupflag=None):
+        """CheckUnboundGroups as SearchSubSub calls it (numingroup / pglist given, ireorder, optional groupflag)."""
+        pos = _f64(pos); vel = _f64(vel); mass = _f64(mass)
+        pf = _i64(pfof).copy()
+        n = pos.shape[0]
+        gf = None if groupflag is None else _i64(groupflag).copy()
+        num = np.zeros(ngroup + 1, dtype=np.int64)
+        ch = C.c_int(0)
+        f = self.lib.vrref_unbind_full
+        f.restype = c_ll
+        ng = f(c_ll(n), _pd(pos), _pd(vel), _pd(mass), C.byref(opts), _pl(pf), c_ll(ngroup), C.c_int(ireorder),
+               None if gf is None else _pl(gf), _pl(num), C.byref(ch))
+        return {"pfof": pf, "ngroups": int(ng), "changed": int(ch.value), "numingroup": num, "groupflag": gf}
+
     def binding_energy(self, pos, vel, mass, numingroup, gcmvel, opts: RefOpts):
         """GetBindingEnergy on group-ordered particles; numingroup[g], gcmvel[g] for g = 1..G (index 0 unused)."""
         pos = _f64(pos); vel = _f64(vel); mass = _f64(mass)
@@ -248,6 +262,7 @@ class UnbindOpts(C.Structure):
         ("theta", c_dbl), ("bucket", C.c_int),
         ("min_size", c_ll), ("pp_threshold", c_ll), ("large_threshold", c_ll),
         ("sortflag_mode", C.c_int), ("oldn_init", c_ll),
+        ("cmvelreftype", C.c_int), ("npotref", c_ll),
     ]
 
 
@@ -262,6 +277,8 @@ def unbind_opts_from(o: RefOpts, pp_threshold: int = 150, sortflag_mode: int = 0
     u.min_size = o.min_size; u.pp_threshold = pp_threshold; u.large_threshold = 1000
     u.sortflag_mode = sortflag_mode
     u.oldn_init = oldn_init
+    u.cmvelreftype = o.cmvelreftype
+    u.npotref = o.Npotref
     return u
 
 

@@ -91,3 +91,52 @@ def test_core_search_linking_through_reference_types(ref, refgpu):
         cw, _ = vrsynth.canonical_groups(want, pid)
         assert ng == nw and np.array_equal(got, cw)
         p6 *= 0.75 ** 2; p7 *= 0.75 ** 2
+
+
+@pytest.mark.parametrize("form", ["keep_ids", "core_flags"])
+def test_check_unbound_groups_as_search_sub_sub_calls_it(ref, refgpu, oracle, form):
+    """The two other forms of CheckUnboundGroups on the hot path: ireorder = 0 (search.cxx:2867: ids
+    kept, dissolved groups left with numingroup = 0) and ireorder = 1 with a group flag (search.cxx:2674: flagged groups first
+    by size, the others by ascending size, flags permuted with the ids).  Direct sums only (every group below UNBINDNUM would be
+    too small a sample, so the stock thresholds apply; groups above 150 take the tree on both sides)."""
+    import vroracle
+    nside = 40
+    d = vrsynth.make_box(nside ** 3, 31)
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    o = vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, fofbgtype=5, bound_halos=1, omp_fof=0)
+    if form == "keep_ids":
+        want = ref.unbind_full(pos, d["vel"], d["mass"], pf, ng, o, ireorder=0)
+        got = refgpu.unbind_full(pos, d["vel"], d["mass"], pf, ng, o, ireorder=0)
+    else:
+        flag = np.ones(ng + 1, dtype=np.int64)
+        flag[ng - ng // 3:] = 2                                   # the last third are "cores" (search.cxx:2671)
+        want = ref.unbind_full(pos, d["vel"], d["mass"], pf, ng, o, ireorder=1, groupflag=flag)
+        got = refgpu.unbind_full(pos, d["vel"], d["mass"], pf, ng, o, ireorder=1, groupflag=flag)
+    assert got["changed"] == want["changed"] == 1
+    assert got["ngroups"] == want["ngroups"]
+    # Q10 (uninitialised oldnumingroup in the reference) may move a handful of bound flags; everything else must agree
+    nb = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
+    assert nb <= 40
+    both = (got["pfof"] > 0) & (want["pfof"] > 0)
+    if form == "keep_ids":
+        assert np.array_equal(got["pfof"][both], pf[both]) and np.array_equal(want["pfof"][both], pf[both])
+        assert np.array_equal(got["numingroup"] == 0, want["numingroup"] == 0)
+        assert np.abs(got["numingroup"] - want["numingroup"]).sum() <= nb
+    else:
+        # flags travel with their groups: every particle carries the same flag on both sides
+        assert np.array_equal(got["groupflag"][got["pfof"][both]], want["groupflag"][want["pfof"][both]])
+        # flagged groups come first; inside each class the sizes are monotonic (descending, then ascending)
+        for r in (got, want):
+            gf, G = r["groupflag"], r["ngroups"]
+            num = np.bincount(r["pfof"], minlength=G + 1)   # (the reference leaves numingroup in the OLD numbering; its caller rebuilds it)
+            cls = gf[1:G + 1]
+            assert np.all(np.diff((cls != 1).astype(int)) >= 0)
+            n1 = num[1:G + 1][cls == 1]
+            n2 = num[1:G + 1][cls != 1]
+            assert np.all(np.diff(n1) <= 0) and np.all(np.diff(n2) >= 0)
+        if nb == 0:
+            # same partition of the particles into groups (ids may differ among groups of equal value: quirk Q5)
+            pairs = set(zip(got["pfof"][both].tolist(), want["pfof"][both].tolist()))
+            assert len(pairs) == got["ngroups"]

@@ -117,3 +117,25 @@ def test_search_full_set_3dfof_unbind(gpu_ctx, oracle):
     assert np.array_equal(got, want["pfof"])
     # positions of grouped particles were unwrapped in the caller's array exactly like AdjustStructureForPeriod
     assert np.array_equal(parts["pos"], pos)
+
+
+@pytest.mark.parametrize("reftype,frac", [(0, 0.1), (1, 0.1), (1, 0.5)])
+def test_unbind_kinetic_reference_frames(gpu_ctx, oracle, reftype, frac):
+    """Frac_pot_ref < 1 (unbind.cxx:460-544; examples/sample.cfg:116-118): the velocity frame of the innermost members by radius
+    about the centre of mass (type 0) or about the potential minimum (type 1), fixed during the unbinding.  The oracle's frames
+    are pinned to the compiled reference in tests/test_oracle_vs_ref.py::test_unbind_kinetic_reference_frames."""
+    import vrgpu
+    import vroracle
+    nside = 40
+    d = vrsynth.make_box(nside ** 3, 31)
+    pf, ng, pos, _ = _fof_groups(oracle, d, nside)
+    ro = vroracle.default_opts(cmvelreftype=reftype, fracpotref=frac)
+    want = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(ro, 150, sortflag_mode=0), d["pid"], 1e-6)
+    base = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(vroracle.default_opts(), 150, sortflag_mode=0), d["pid"], 1e-6)
+    assert np.count_nonzero((want["pfof"] > 0) != (base["pfof"] > 0)) > 50
+    parts = vrgpu.particles_from_arrays(pos, d["vel"], d["mass"], d["pid"])
+    got = gpu_ctx.unbind(parts, pf, ng, vrgpu.default_unbind_opts(pp_threshold=150, fracpotref=frac, cmvelreftype=reftype, npotref=20))
+    ndiff = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
+    assert ndiff <= want["n_marginal"] + got["n_marginal"], (ndiff, want["n_marginal"], got["n_marginal"])
+    if ndiff == 0:
+        assert got["ngroups"] == want["ngroups"] and np.array_equal(got["pfof"], want["pfof"])

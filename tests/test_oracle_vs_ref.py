@@ -350,3 +350,28 @@ def test_velocity_density(ref, oracle, approx):
         if approx:   # a tree built by the caller and handed in (search.cxx:232) gives what the routine's own tree gives
             assert np.array_equal(ref.velocity_density(pos, vel[:len(pos)], approx=2, **kw), want)
         assert np.count_nonzero(want) == (int(kw["ptype"].sum()) if "ptype" in kw else len(pos))
+
+
+@pytest.mark.parametrize("reftype,frac", [(0, 0.1), (1, 0.1), (1, 0.5), (0, 0.02)])
+def test_unbind_kinetic_reference_frames(ref, oracle, reftype, frac):
+    """Frac_pot_ref < 1 (unbind.cxx:460-544; examples/sample.cfg:116-118 uses type 0 with 0.1): the velocity frame of the innermost
+    max(Npotref, frac n) members by radius about the centre of mass (CMVELREF = 0) or about the minimum of the potential
+    (POTREF = 1), fixed for the whole unbinding (UpdateCMForUnboundParticles only follows removals for frac == 1)."""
+    import vroracle
+    nside = 40
+    d = vrsynth.make_box(nside ** 3, 31)
+    b = 0.2 * vrsynth.BOX / nside
+    pf, ng = oracle.fof3d(d["pos"], b, vrsynth.BOX, 20, d["pid"])
+    pos = oracle.adjust_for_period(d["pos"], vrsynth.BOX, pf, ng)
+    o = vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside, fofbgtype=5, bound_halos=1, omp_fof=0,
+                              cmvelreftype=reftype, fracpotref=frac)
+    want = ref.unbind(pos, d["vel"], d["mass"], pf, ng, o)
+    cw, _ = vrsynth.canonical_groups(want["pfof"], d["pid"])
+    base = ref.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.default_opts(period=vrsynth.BOX, ellxscale=vrsynth.BOX / nside,
+                                                                              fofbgtype=5, bound_halos=1, omp_fof=0))
+    assert np.count_nonzero((want["pfof"] > 0) != (base["pfof"] > 0)) > 50      # the frame matters on this box
+    got = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=1, oldn_init=0), d["pid"], 1e-6)
+    nd = int(np.count_nonzero((got["pfof"] > 0) != (cw > 0)))
+    assert nd <= got["n_marginal"], (nd, got["n_marginal"])
+    if nd == 0:
+        assert got["ngroups"] == want["ngroups"] and np.array_equal(got["pfof"], cw)

@@ -30,6 +30,7 @@ struct UbParams {
     double Eratio, minEfrac, maxunbindfrac, maxunboundfrac, maxallowed, marginal_tol;
     int unbindtype;
     long long min_size, large_threshold;
+    int fixed_frame; // Frac_pot_ref != 1: the velocity frame does not follow the removals (unbind.cxx:118)
 };
 
 struct UbArrays {
@@ -294,12 +295,14 @@ __global__ void __launch_bounds__(256) k_large_finish(UbArrays A, UbParams P, ui
             nn = 0;
         }
         if (lane == 0) {
-            double mass = A.gmass[g];
-            double temp = 1.0 / mass;
-            double cx = A.cmvel[3 * g] - sx * temp, cy = A.cmvel[3 * g + 1] - sy * temp, cz = A.cmvel[3 * g + 2] - sz * temp;
-            temp = mass / (mass - sm);
-            A.cmvel[3 * g] = cx * temp; A.cmvel[3 * g + 1] = cy * temp; A.cmvel[3 * g + 2] = cz * temp;
-            A.gmass[g] = mass - sm;
+            if (!P.fixed_frame) {
+                double mass = A.gmass[g];
+                double temp = 1.0 / mass;
+                double cx = A.cmvel[3 * g] - sx * temp, cy = A.cmvel[3 * g + 1] - sy * temp, cz = A.cmvel[3 * g + 2] - sz * temp;
+                temp = mass / (mass - sm);
+                A.cmvel[3 * g] = cx * temp; A.cmvel[3 * g + 1] = cy * temp; A.cmvel[3 * g + 2] = cz * temp;
+                A.gmass[g] = mass - sm;
+            }
             A.ning[g] = nn;
         }
     }
@@ -457,11 +460,13 @@ template <bool BG0> __global__ void __launch_bounds__(UB_T) k_unbind_small(UbArr
             }
             double sm = ub_block_sum<double>(sm_l, dscr), sx = ub_block_sum<double>(sx_l, dscr);
             double sy = ub_block_sum<double>(sy_l, dscr), sz = ub_block_sum<double>(sz_l, dscr);
-            double temp = 1.0 / mass;
-            cx -= sx * temp; cy -= sy * temp; cz -= sz * temp;
-            temp = mass / (mass - sm);
-            cx *= temp; cy *= temp; cz *= temp;
-            mass -= sm;
+            if (!P.fixed_frame) {
+                double temp = 1.0 / mass;
+                cx -= sx * temp; cy -= sy * temp; cz -= sz * temp;
+                temp = mass / (mass - sm);
+                cx *= temp; cy *= temp; cz *= temp;
+                mass -= sm;
+            }
         }
         if (BG0) {
             const uint32_t nrm = (uint32_t)nEplus;
@@ -570,13 +575,101 @@ static void compute_potentials(vrgpu_ctx *ctx, const GroupSet &gs, double G, dou
     ctx->stats.potential_ms += t.stop();
 }
 
+// ---- kinetic reference frame for Frac_pot_ref != 1 (unbind.cxx:460-544) ---------------------------------------------------
+// centre of every group: its centre of mass (CMVELREF) or the position of the member with the lowest potential (POTREF, the
+// first strict minimum); one CTA per group, fixed reduction shape
+constexpr int FR_T = 128;
+__global__ void __launch_bounds__(FR_T) k_frame_centre(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                                                       const double *__restrict__ m, const double *__restrict__ phi, const uint32_t *__restrict__ off,
+                                                       int potref, double *__restrict__ centre, double *__restrict__ gmass)
+{
+    __shared__ double red[4][FR_T];
+    __shared__ uint32_t ri[FR_T];
+    const uint32_t g = blockIdx.x + 1, s0 = off[g], s1 = off[g + 1];
+    const unsigned tid = threadIdx.x;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    uint32_t best = 0xffffffffu;
+    double bphi = 0;
+    for (uint32_t s = s0 + tid; s < s1; s += FR_T) {
+        const double mm = m[s];
+        a0 += x[s] * mm; a1 += y[s] * mm; a2 += z[s] * mm; a3 += mm;
+        const double p = phi[s];
+        if (best == 0xffffffffu || p < bphi) { best = s; bphi = p; } // slots ascend: the first strict minimum of this thread
+    }
+    red[0][tid] = potref ? bphi : a0; red[1][tid] = a1; red[2][tid] = a2; red[3][tid] = a3; ri[tid] = best;
+    __syncthreads();
+    for (int o = FR_T / 2; o; o >>= 1) {
+        if ((int)tid < o) {
+            if (potref) {
+                const uint32_t b = ri[tid + o];
+                if (b != 0xffffffffu && (ri[tid] == 0xffffffffu || red[0][tid + o] < red[0][tid] || (red[0][tid + o] == red[0][tid] && b < ri[tid]))) {
+                    ri[tid] = b; red[0][tid] = red[0][tid + o];
+                }
+            } else red[0][tid] += red[0][tid + o];
+            red[1][tid] += red[1][tid + o]; red[2][tid] += red[2][tid + o]; red[3][tid] += red[3][tid + o];
+        }
+        __syncthreads();
+    }
+    if (tid == 0 && s1 > s0) {
+        gmass[g] = red[3][0];
+        if (potref) { const uint32_t s = ri[0]; centre[3 * g] = x[s]; centre[3 * g + 1] = y[s]; centre[3 * g + 2] = z[s]; }
+        else { const double inv = 1.0 / red[3][0]; centre[3 * g] = red[0][0] * inv; centre[3 * g + 1] = red[1][0] * inv; centre[3 * g + 2] = red[2][0] * inv; }
+    }
+}
+// Particle::Radius() about the group's centre, as a sort key (radii are non-negative: the bit pattern orders them)
+__global__ void k_frame_radius(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                               const uint32_t *__restrict__ gid, const double *__restrict__ centre, uint32_t ntot, uint64_t *__restrict__ keys,
+                               uint32_t *__restrict__ vals)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ntot) return;
+    const uint32_t g = gid[s];
+    const double dx = __dsub_rn(x[s], centre[3 * g]), dy = __dsub_rn(y[s], centre[3 * g + 1]), dz = __dsub_rn(z[s], centre[3 * g + 2]);
+    const double r = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+    keys[s] = (uint64_t)__double_as_longlong(r);
+    vals[s] = s;
+}
+__global__ void k_frame_gidkeys(const uint32_t *__restrict__ gid, const uint32_t *__restrict__ vals, uint32_t ntot, uint64_t *__restrict__ keys)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < ntot) keys[k] = gid[vals[k]];
+}
+// mean velocity of the npot innermost members (positions [off[g], off[g] + npot) of the radius order)
+__global__ void __launch_bounds__(FR_T) k_frame_cmvel(UbArrays A, const uint32_t *__restrict__ order, double frac, long long npotref)
+{
+    __shared__ double red[4][FR_T];
+    const uint32_t g = blockIdx.x + 1, s0 = A.off[g], n = A.off[g + 1] - s0;
+    const unsigned tid = threadIdx.x;
+    long long npot = (long long)(frac * (double)n);
+    if (npot < npotref) npot = npotref;
+    if (npot > (long long)n) npot = n;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (uint32_t q = tid; q < (uint32_t)npot; q += FR_T) {
+        const uint32_t s = order[s0 + q];
+        const double mm = A.m[s];
+        a0 += A.vx[s] * mm; a1 += A.vy[s] * mm; a2 += A.vz[s] * mm; a3 += mm;
+    }
+    red[0][tid] = a0; red[1][tid] = a1; red[2][tid] = a2; red[3][tid] = a3;
+    __syncthreads();
+    for (int o = FR_T / 2; o; o >>= 1) {
+        if ((int)tid < o) { red[0][tid] += red[0][tid + o]; red[1][tid] += red[1][tid + o]; red[2][tid] += red[2][tid + o]; red[3][tid] += red[3][tid + o]; }
+        __syncthreads();
+    }
+    if (tid == 0 && n > 0) {
+        A.cmvel[3 * g] = red[0][0] / red[3][0]; A.cmvel[3 * g + 1] = red[1][0] / red[3][0]; A.cmvel[3 * g + 2] = red[2][0] / red[3][0];
+        A.ning[g] = n;
+        A.status[g] = 0;
+    }
+}
+
 void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev, long long &ngroups, const vrgpu_unbind_opts &o,
                    int &changed, long long &n_marginal)
 {
     changed = 0;
     n_marginal = 0;
     if (ngroups <= 0 || P.n == 0) return;
-    VR_REQUIRE(o.fracpotref == 1.0, VRGPU_EUNSUPPORTED, "only Frac_pot_ref=1 (whole-group CM frame) is implemented");
+    VR_REQUIRE(o.fracpotref > 0 && o.fracpotref <= 1.0, VRGPU_EINVAL, "Frac_pot_ref must be in (0, 1]");
+    VR_REQUIRE(o.fracpotref == 1.0 || o.cmvelreftype == 0 || o.cmvelreftype == 1, VRGPU_EINVAL, "Kinetic_reference_frame_type must be 0 or 1");
     VR_REQUIRE(o.bgpot == 0 || o.bgpot == 1, VRGPU_EINVAL, "Keep_background_potential must be 0 or 1");
     // Keep_background_potential = 0 in the large-group loop (unbind.cxx:577-606): pair terms are taken off only when
     // nEplus < 2 ln n, and a pass happens only when nEplus >= maxallowedunboundfrac * n (FillUnboundArrays), so with
@@ -624,11 +717,27 @@ void unbind_device(vrgpu_ctx *ctx, const DeviceParticles &P, long long *pfof_dev
     Pm.Eratio = o.Eratio; Pm.minEfrac = o.minEfrac; Pm.maxunbindfrac = o.maxunbindfrac;
     Pm.maxunboundfrac = o.maxunboundfracforiterativeunbind; Pm.maxallowed = o.maxallowedunboundfrac;
     Pm.marginal_tol = o.marginal_tol; Pm.unbindtype = o.unbindtype; Pm.min_size = o.min_size; Pm.large_threshold = o.large_threshold;
+    Pm.fixed_frame = o.fracpotref != 1.0 ? 1 : 0;
     const unsigned warp_grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 16u));
 
     { KScope k(ctx, "unbind.cm_frame"); VR_LAUNCH(ctx, k_init_slots, grid_for(ntot, T), T, 0, A, ntot);
-    VR_LAUNCH(ctx, k_group_cm_big, G, 1024, 0, A);
-    VR_LAUNCH(ctx, k_group_cm, warp_grid, T, 0, A, G); }
+    if (!Pm.fixed_frame) {
+        VR_LAUNCH(ctx, k_group_cm_big, G, 1024, 0, A);
+        VR_LAUNCH(ctx, k_group_cm, warp_grid, T, 0, A, G);
+    } else {
+        // radius order inside every group: stable sort by radius, then by group id
+        DBuf<double> centre(ctx, 3 * G1);
+        DBuf<uint64_t> keys(ctx, ntot), keys_tmp(ctx, ntot);
+        DBuf<uint32_t> vals(ctx, ntot), vals_tmp(ctx, ntot);
+        VR_LAUNCH(ctx, k_frame_centre, G, FR_T, 0, gs.x.p, gs.y.p, gs.z.p, gs.m.p, phi.p, gs.off.p, o.cmvelreftype == 1 ? 1 : 0, centre.p, gmass.p);
+        VR_LAUNCH(ctx, k_frame_radius, grid_for(ntot, T), T, 0, gs.x.p, gs.y.p, gs.z.p, gs.gid.p, centre.p, ntot, keys.p, vals.p);
+        radix_sort_pairs(ctx, keys.p, vals.p, keys_tmp.p, vals_tmp.p, ntot, 64);
+        VR_LAUNCH(ctx, k_frame_gidkeys, grid_for(ntot, T), T, 0, gs.gid.p, vals.p, ntot, keys.p);
+        int gbits = 1;
+        while ((1ull << gbits) <= (unsigned long long)G) gbits++;
+        radix_sort_pairs(ctx, keys.p, vals.p, keys_tmp.p, vals_tmp.p, ntot, gbits);
+        VR_LAUNCH(ctx, k_frame_cmvel, G, FR_T, 0, A, vals.p, o.fracpotref, (long long)o.npotref);
+    } }
 
     // ---- phase A ----
     {

@@ -127,6 +127,8 @@ vrgpu_unbind_opts unbind_opts_of(const Options &opt)
     u.pp_threshold = UNBINDNUM;   /* allvars.h:210 */
     u.large_threshold = 1000;     /* ompunbindnum, ompvar.h:26 */
     u.marginal_tol = 1e-6;
+    u.cmvelreftype = opt.uinfo.cmvelreftype;
+    u.npotref = opt.uinfo.Npotref;
     return u;
 }
 
@@ -183,39 +185,71 @@ Int_t *VRGPU_NAME(SearchFullSet)(Options &opt, const Int_t nbodies, vector<Parti
     return pfof;
 }
 
-/* CheckUnboundGroups (src/unbind.cxx:196-304): pfof updated in place (0 = unbound), ids compacted / re-ordered when
- * ireorder, ngroup updated, optional numingroup / pglist refreshed with the surviving members, returns 1 if anything
- * changed.  The originals in Part are untouched, as in the reference (it works on copies). */
+/* CheckUnboundGroups (src/unbind.cxx:196-304): pfof updated in place (0 = unbound), ngroup = the number of groups that survive,
+ * optional numingroup / pglist refreshed with the surviving members, returns 1 if anything changed.  The originals in Part are
+ * untouched, as in the reference (it works on copies).  The three forms the reference calls:
+ *   ireorder = 1, groupflag = NULL (search.cxx:703): ids compacted and re-ordered by size (the library's canonical order);
+ *   ireorder = 0 (search.cxx:2867, :3452): every surviving group KEEPS its id, dissolved groups have numingroup = 0
+ *     (unbind.cxx:718-720; groupflag, if given, is not touched on this branch);
+ *   ireorder = 1 with groupflag (search.cxx:2674, the core flags of SearchSubSub): ids re-ordered by the reference's group value
+ *     -- flagged groups (flag == 1) first by size descending, the others by 1/size, i.e. size ascending -- and groupflag
+ *     permuted with them, dissolved groups get flag 0 (unbind.cxx:271-287; ReorderGroupIDsAndArraybyValue,
+ *     buildandsortarrays.cxx:238-253).  Equal values: the smaller minimum particle index first (the reference's heap order
+ *     among equal values is not a function of the input, quirk Q5). */
 int VRGPU_NAME(CheckUnboundGroups)(Options opt, const Int_t nbodies, Particle *Part, Int_t &ngroup, Int_t *&pfof, Int_t *numingroup,
                                    Int_t **pglist, int ireorder, Int_t *groupflag)
 {
-    if (ireorder != 1) {
-        cerr << "vrgpu: CheckUnboundGroups with ireorder=0 is not implemented on the GPU path" << endl;
-        exit(9);
-    }
     vrgpu_unbind_opts u = unbind_opts_of(opt);
     const Int_t ngroup_in = ngroup;
+    const bool keep_ids = ireorder != 1 || groupflag != NULL;
+    Int_t *oldpf = NULL;
+    if (keep_ids) {
+        oldpf = new Int_t[nbodies > 0 ? nbodies : 1];
+        for (Int_t i = 0; i < nbodies; i++) oldpf[i] = pfof[i];
+    }
     long long ng = ngroup;
     int changed = 0;
     long long nmarginal = 0;
     int rc = vrgpu_unbind(context(), view_of(Part, nbodies), reinterpret_cast<long long *>(pfof), &ng, &u, &changed, &nmarginal);
     if (rc != VRGPU_OK) die("vrgpu_unbind", rc);
     ngroup = ng;
+    if (keep_ids) {
+        /* unbinding neither merges nor splits groups: a surviving particle's old id names its group */
+        for (Int_t i = 0; i < nbodies; i++) pfof[i] = pfof[i] > 0 ? oldpf[i] : 0;
+        delete[] oldpf;
+        if (ireorder == 1 && changed && ngroup > 0) {
+            /* sizes, first members and values by OLD id; new id = rank by (value descending, first member ascending) */
+            Int_t *num = new Int_t[ngroup_in + 1], *first = new Int_t[ngroup_in + 1], *order = new Int_t[ngroup_in + 1], *newid = new Int_t[ngroup_in + 1];
+            Int_t *gtemp = new Int_t[ngroup_in + 1];
+            double *value = new double[ngroup_in + 1];
+            for (Int_t g = 0; g <= ngroup_in; g++) { num[g] = 0; first[g] = nbodies; newid[g] = 0; }
+            for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) { if (num[pfof[i]]++ == 0) first[pfof[i]] = i; }
+            Int_t nlive = 0;
+            for (Int_t g = 1; g <= ngroup_in; g++) {
+                gtemp[g] = groupflag[g];
+                if (num[g] == 0) { value[g] = 0; groupflag[g] = 0; }
+                else { value[g] = groupflag[g] == 1 ? (double)num[g] : 1.0 / (double)num[g]; order[nlive++] = g; }
+            }
+            std::sort(order, order + nlive, [&](Int_t a, Int_t b) { return value[a] != value[b] ? value[a] > value[b] : first[a] < first[b]; });
+            for (Int_t k = 0; k < nlive; k++) { newid[order[k]] = k + 1; groupflag[k + 1] = gtemp[order[k]]; }
+            for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) pfof[i] = newid[pfof[i]];
+            delete[] num; delete[] first; delete[] order; delete[] newid; delete[] gtemp; delete[] value;
+        }
+    }
     if (numingroup != NULL) {
         for (Int_t g = 0; g <= ngroup_in; g++) numingroup[g] = 0;
         for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) numingroup[pfof[i]]++;
     }
     if (pglist != NULL && numingroup != NULL) {
         /* lists are re-filled with the surviving indices (unbind.cxx:142-144); the caller's arrays are large enough
-         * because groups only shrink */
-        Int_t *fill = new Int_t[ngroup + 1];
-        for (Int_t g = 0; g <= ngroup; g++) fill[g] = 0;
-        for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) pglist[pfof[i]][fill[pfof[i]]++] = i;
-        delete[] fill;
-    }
-    if (groupflag != NULL) {
-        cerr << "vrgpu: groupflag is not carried through the GPU unbinding (ids are re-ordered)" << endl;
-        exit(9);
+         * because groups only shrink -- after a re-ordering the caller rebuilds them (search.cxx:2675-2682, unbind.cxx:296) */
+        const bool same_ids = ireorder != 1 || !changed;
+        if (same_ids) {
+            Int_t *fill = new Int_t[ngroup_in + 1];
+            for (Int_t g = 0; g <= ngroup_in; g++) fill[g] = 0;
+            for (Int_t i = 0; i < nbodies; i++) if (pfof[i] > 0) pglist[pfof[i]][fill[pfof[i]]++] = i;
+            delete[] fill;
+        }
     }
     return changed;
 }

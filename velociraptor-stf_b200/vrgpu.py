@@ -46,7 +46,7 @@ class UnbindOpts(C.Structure):
                 ("maxunbindfrac", C.c_double), ("maxunboundfracforiterativeunbind", C.c_double),
                 ("maxallowedunboundfrac", C.c_double), ("theta", C.c_double), ("bucket", C.c_int),
                 ("min_size", C.c_longlong), ("pp_threshold", C.c_longlong), ("large_threshold", C.c_longlong),
-                ("marginal_tol", C.c_double)]
+                ("marginal_tol", C.c_double), ("cmvelreftype", C.c_int), ("npotref", C.c_longlong)]
 
 
 class SearchOpts(C.Structure):
@@ -86,6 +86,8 @@ def default_unbind_opts(**kw) -> UnbindOpts:
     u.pp_threshold = 150
     u.large_threshold = 1000
     u.marginal_tol = 1e-6
+    u.cmvelreftype = 0
+    u.npotref = 20
     for k, v in kw.items():
         if not hasattr(u, k):
             raise AttributeError(k)
