@@ -14,6 +14,12 @@ for s in "$@"; do
     b256c2) timeout 600 python bench.py --config 2 --steps 3 --warmup 2 --no-cpu-baseline --no-e2e-secondary > gpurun_out/b256_c2.json 2> gpurun_out/b256_c2.err; python tools/bench_summary.py gpurun_out/b256_c2.json 2>/dev/null | head -30; tail -3 gpurun_out/b256_c2.err ;;
     b512) timeout 1500 python bench.py --steps 3 --warmup 2 --no-cpu-baseline --no-e2e-secondary > gpurun_out/b512_c3.json 2> gpurun_out/b512_c3.err; python tools/bench_summary.py gpurun_out/b512_c3.json 2>/dev/null | head -40; tail -3 gpurun_out/b512_c3.err ;;
     zoom20) timeout 900 python bench.py --single-halo 20000000 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e-secondary > gpurun_out/zoom20.json 2> gpurun_out/zoom20.err; python tools/bench_summary.py gpurun_out/zoom20.json 2>/dev/null | head -24; tail -3 gpurun_out/zoom20.err ;;
+    l512) bash tools/ncu_launches.sh r02g_launches_512c3 ;;
+    l256) bash tools/ncu_launches.sh r02g_launches_256c3 --nside 256 ;;
+    t256) bash tools/ncu_traffic.sh r02g_traffic_256c3 --nside 256 ;;
+    t512) bash tools/ncu_traffic.sh r02g_traffic_512c3 ;;
+    t256c2) bash tools/ncu_traffic.sh r02g_traffic_256c2 --config 2 ;;
+    zz) timeout 600 python -m pytest tests/test_zz_no_alloc.py -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/zz_pytest.log 2>&1; tail -15 gpurun_out/zz_pytest.log ;;
     *) echo "unknown section $s" ;;
   esac
 done
