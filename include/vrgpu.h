@@ -9,7 +9,7 @@
  *   - plain C, no exceptions cross the boundary; return 0 = OK, non-zero = VRGPU_E* code,
  *     vrgpu_last_error(ctx) gives the text.
  *   - every pointer is a HOST pointer owned by the caller (pinned or pageable); the library never frees
- *     or retains caller memory.  Outputs are fully written on success and untouched on failure.
+ *     or retains caller memory (one exception, stated there: vrgpu_potential_direct_noalloc takes device pointers).  Outputs are fully written on success and untouched on failure.
  *   - Int_t == long long (the reference's default LONGINT build, NBodylib/src/Math/Precision.h:49),
  *     Double_t == double.  NBody::Particle must be the 96-byte default layout
  *     (NBodylib/src/NBody/Particle.h:75-109); other layouts are described through vrgpu_view.
@@ -229,6 +229,26 @@ int vrgpu_dist_search_full_set(vrgpu_ctx *ctx, vrgpu_view local, double slab_lo,
 /* the same on the particles handed over with vrgpu_particles_upload (result: vrgpu_resident_pfof) */
 int vrgpu_dist_search_full_set_resident(vrgpu_ctx *ctx, double slab_lo, double slab_hi, const vrgpu_search_opts *opts,
                                         long long *ngroups_out);
+
+/* ---- allocation-free variant ------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Direct-sum potentials of ONE group, phi_j = -G m_j sum_{k != j} m_k / sqrt(r_jk^2 + eps^2) -- the arithmetic and the kernel
+ * of vrgpu_potential with pp_threshold < 0 (velociraptor-stf_b200/csrc/potential.cu) -- with every buffer supplied by the
+ * caller and the kernel's scratch (group-major SoA columns) in a file-scope device array of the library:
+ *   - UNLIKE every other entry point the pointers are DEVICE pointers on `device` (-1 = the current device): pos_dev[3n]
+ *     (x, y, z per particle), mass_dev[n] (NULL = unit masses), phi_dev[n] (output).  `stream` is a cudaStream_t (NULL = the
+ *     default stream); the kernels are queued on it and the call returns without synchronising.
+ *   - n <= VRGPU_NOALLOC_MAX_PARTICLES; a larger n is rejected with VRGPU_EINVAL and a message (use vrgpu_potential).
+ *   - the call makes no cudaMalloc / cudaFree / pool allocation and needs no context.  The scratch (2.25 MiB) is held by every
+ *     GPU that loads the library until exit.  All calls share it: two calls whose kernels overlap on the GPU (different
+ *     streams or threads) race -- serialise them.  Every word a call reads it writes first, so no state carries over.
+ *   - the first call per device resolves the array's device address (cudaGetSymbolAddress); make it outside graph capture.
+ *   - errbuf (may be NULL) receives the error text, at most errbuf_len bytes with the terminator. */
+#define VRGPU_NOALLOC_MAX_PARTICLES 65536
+int vrgpu_potential_direct_noalloc(int device, void *stream, const double *pos_dev, const double *mass_dev, long long n, double G,
+                                   double eps, double *phi_dev, char *errbuf, long long errbuf_len);
 
 /* ---- measurement hooks ------------------------------------------------------------------------------- */
 /* the CUDA stream (cudaStream_t) every kernel of this context is launched on, for event timing by the caller */

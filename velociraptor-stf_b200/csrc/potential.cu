@@ -414,3 +414,104 @@ void probe_fp64_pipes(vrgpu_ctx *ctx, double out4[4])
     out4[3] = dmma_flops / (ms_mode[2] * 1e-3) / 1e12;
 }
 } // namespace vrgpu
+
+// ---------------------------------------------------------------------------------------------------
+// vrgpu_potential_direct_noalloc (include/vrgpu.h): the direct-sum potential of ONE group for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// It runs k_potential_direct -- the kernel vrgpu_potential / vrgpu_unbind use -- on a
+// group-major SoA that a gather kernel writes into a FILE-SCOPE device array instead of the DBuf scratch of groups.cu, so
+// the call allocates nothing (no cudaMalloc / cudaFree / stream-ordered pool, no context, no events).
+//
+// The array is 2.25 MiB and is held by every GPU that loads the library until exit.  All calls share it and it keeps the
+// last call's contents: every word a call reads it first writes (columns [0, n), gid[0, n), off[0..2]), so nothing has to
+// start at zero -- but two calls whose kernels overlap on the GPU (different streams, or different threads) RACE.
+// ---------------------------------------------------------------------------------------------------
+#include <cstdio>
+#include <mutex>
+
+namespace vrgpu {
+constexpr long long NA_MAX = VRGPU_NOALLOC_MAX_PARTICLES;
+static_assert(NA_MAX % 512 == 0, "column starts must keep the 256-byte alignment");
+// layout in doubles: x | y | z | m (NA_MAX each) | gid (NA_MAX uint32 = NA_MAX/2 doubles) | off (4 uint32, padded to 32 doubles)
+constexpr size_t NA_DOUBLES = (size_t)4 * NA_MAX + NA_MAX / 2 + 32;
+static __device__ __align__(256) double g_noalloc_scratch[NA_DOUBLES];
+
+// AoS positions (3 doubles per particle) and masses -> the SoA, group ids and offsets k_potential_direct reads: one group
+// (id 1) in slots [0, n); off[0] = off[1] = 0, off[2] = n as in GroupSet (groups.cuh)
+__global__ void k_noalloc_gather(const double *__restrict__ pos, const double *__restrict__ mass, uint32_t n, double *__restrict__ x,
+                                 double *__restrict__ y, double *__restrict__ z, double *__restrict__ m, uint32_t *__restrict__ gid,
+                                 uint32_t *__restrict__ off)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { off[0] = 0u; off[1] = 0u; off[2] = n; off[3] = n; }
+    if (i >= n) return;
+    x[i] = pos[3 * (size_t)i];
+    y[i] = pos[3 * (size_t)i + 1];
+    z[i] = pos[3 * (size_t)i + 2];
+    m[i] = mass ? mass[i] : 1.0;
+    gid[i] = 1u;
+}
+
+namespace {
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+double *g_noalloc_addr[NA_MAX_DEVICES]; // device address of g_noalloc_scratch on device d (the symbol itself is a host-side stand-in)
+
+int noalloc_fail(char *errbuf, long long errbuf_len, int code, const char *what, const char *detail)
+{
+    if (errbuf && errbuf_len > 0) std::snprintf(errbuf, (size_t)errbuf_len, "vrgpu_potential_direct_noalloc: %s%s%s", what, detail ? ": " : "", detail ? detail : "");
+    return code;
+}
+} // namespace
+} // namespace vrgpu
+
+extern "C" int vrgpu_potential_direct_noalloc(int device, void *stream, const double *pos_dev, const double *mass_dev, long long n, double G,
+                                              double eps, double *phi_dev, char *errbuf, long long errbuf_len)
+{
+    using namespace vrgpu;
+    if (errbuf && errbuf_len > 0) errbuf[0] = 0;
+    if (n < 0) return noalloc_fail(errbuf, errbuf_len, VRGPU_EINVAL, "negative particle count", nullptr);
+    if (n > NA_MAX) {
+        char msg[160];
+        std::snprintf(msg, sizeof msg, "%lld particles exceed the fixed scratch of VRGPU_NOALLOC_MAX_PARTICLES = %lld (use vrgpu_potential)", n, NA_MAX);
+        return noalloc_fail(errbuf, errbuf_len, VRGPU_EINVAL, "group too large", msg);
+    }
+    if (n == 0) return VRGPU_OK;
+    if (!pos_dev || !phi_dev) return noalloc_fail(errbuf, errbuf_len, VRGPU_EINVAL, "null device pointer (pos_dev / phi_dev)", nullptr);
+    int cur = -1;
+    cudaError_t e = cudaGetDevice(&cur);
+    if (e != cudaSuccess) return noalloc_fail(errbuf, errbuf_len, VRGPU_ENODEV, "cudaGetDevice", cudaGetErrorString(e));
+    if (device < 0) device = cur;
+    if (device >= NA_MAX_DEVICES) return noalloc_fail(errbuf, errbuf_len, VRGPU_EINVAL, "device ordinal out of range", nullptr);
+    if (device != cur) {
+        e = cudaSetDevice(device);
+        if (e != cudaSuccess) return noalloc_fail(errbuf, errbuf_len, VRGPU_ENODEV, "cudaSetDevice", cudaGetErrorString(e));
+    }
+    int rc = VRGPU_OK;
+    double *base = nullptr;
+    {
+        // set-up, once per device, with that device current: the device address of the file-scope array
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_addr[device]) {
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) rc = noalloc_fail(errbuf, errbuf_len, VRGPU_ECUDA, "cudaGetSymbolAddress", cudaGetErrorString(e));
+            else g_noalloc_addr[device] = static_cast<double *>(p);
+        }
+        base = g_noalloc_addr[device];
+    }
+    if (rc == VRGPU_OK) {
+        double *x = base, *y = base + NA_MAX, *z = base + 2 * NA_MAX, *m = base + 3 * NA_MAX;
+        uint32_t *gid = reinterpret_cast<uint32_t *>(base + 4 * NA_MAX);
+        uint32_t *off = reinterpret_cast<uint32_t *>(base + 4 * NA_MAX + NA_MAX / 2);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const uint32_t nn = (uint32_t)n;
+        k_noalloc_gather<<<(nn + 255u) / 256u, 256, 0, st>>>(pos_dev, mass_dev, nn, x, y, z, m, gid, off);
+        // pp_threshold < 0 and sym_min = 2^32 - 1: every slot is served by this kernel (no symmetric pass, no atomics)
+        k_potential_direct<<<(nn + PS - 1) / PS, PT, 0, st>>>(x, y, z, m, gid, off, nn, G, eps * eps, -1ll, 0xffffffffu, phi_dev);
+        e = cudaPeekAtLastError();
+        if (e != cudaSuccess) rc = noalloc_fail(errbuf, errbuf_len, VRGPU_ECUDA, "kernel launch", cudaGetErrorString(e));
+    }
+    if (device != cur) cudaSetDevice(cur);
+    return rc;
+}

@@ -26,6 +26,8 @@ PARTICLE_DTYPE = np.dtype({
 
 NOFIELD = C.c_size_t(-1).value
 
+EINVAL = 3
+NOALLOC_MAX_PARTICLES = 65536   # VRGPU_NOALLOC_MAX_PARTICLES (include/vrgpu.h)
 ERRORS = {1: "VRGPU_ENODEV", 2: "VRGPU_ECUDA", 3: "VRGPU_EINVAL", 4: "VRGPU_EUNSUPPORTED", 5: "VRGPU_ENOMEM"}
 
 
@@ -145,6 +147,10 @@ def load_library(path: str = LIB_PATH):
     L.vrgpu_measure_fp64_tflops.argtypes = [C.c_void_p, P_d]
     L.vrgpu_probe_fp64_pipes.argtypes = [C.c_void_p, P_d]
     L.vrgpu_kernel_times_reset.argtypes = [C.c_void_p]
+    # device pointers as integers (c_void_p): pos_dev, mass_dev, phi_dev
+    L.vrgpu_potential_direct_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_double, C.c_double,
+                                                 C.c_void_p, C.c_char_p, C.c_longlong]
+    L.vrgpu_potential_direct_noalloc.restype = C.c_int
     L.vrgpu_kernel_times_reset.restype = None
     _lib = L
     return L
@@ -155,7 +161,7 @@ EXPORTED_SYMBOLS = ["vrgpu_init", "vrgpu_destroy", "vrgpu_last_error", "vrgpu_ve
                     "vrgpu_particles_upload", "vrgpu_particles_release", "vrgpu_search_full_set_resident",
                     "vrgpu_resident_pfof", "vrgpu_dist_unique_id", "vrgpu_dist_init", "vrgpu_dist_search_full_set",
                     "vrgpu_dist_search_full_set_resident", "vrgpu_stream", "vrgpu_kernel_times", "vrgpu_kernel_times_reset", "vrgpu_measure_fp64_tflops", "vrgpu_probe_fp64_pipes", "vrgpu_fof_criterion6d", "vrgpu_velocity_density",
-                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist", "vrgpu_tree_order"]
+                    "vrgpu_binding_energy", "vrgpu_sort_groups_by_key", "vrgpu_build_pglist", "vrgpu_tree_order", "vrgpu_potential_direct_noalloc"]
 
 
 def pinned_i64(n: int) -> np.ndarray:
