@@ -1,8 +1,11 @@
 """Multi-GPU parity check, launched as `torchrun --nproc-per-node N tests/dist/mg_check.py [nside]` on a box with N GPUs.
 
-Every rank builds the same synthetic box, keeps its x-slab, runs vrgpu_dist_search_full_set; rank 0 also runs the
-single-GPU path on the whole box and compares the per-particle GLOBAL group ids (must be identical for 3DFOF; for the
-6DFOF / unbinding configurations differences are allowed only for marginal particles, whose count is reported)."""
+Every rank builds the same synthetic box, keeps its x-slab, runs vrgpu_dist_search_full_set; rank 0 gathers the per-particle
+GLOBAL group ids and the coordinates the call wrote back into the ranks' particle records and compares them
+  - with the ORACLE (oracle/vr_oracle.c, pinned to the compiled reference): 3DFOF membership and AdjustStructureForPeriod
+    positions bit for bit; the bound sets of the unbinding configurations identical up to the reported marginal particles;
+  - with the single-GPU path on the whole box: labels and written-back positions / velocities identical for every
+    configuration (6DFOF included: the Q3 rounding of the scaling round trip travels home with the labels)."""
 import os
 import sys
 
@@ -12,6 +15,7 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "velociraptor-stf_b200"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import vrgpu  # noqa: E402
 import vrsynth  # noqa: E402
 
@@ -30,7 +34,6 @@ def main():
     lo, hi = L * rank / world, L * (rank + 1) / world
     x = d["pos"][:, 0]
     sel = np.flatnonzero((x >= lo) & (x < hi))
-    parts = vrgpu.particles_from_arrays(d["pos"][sel], d["vel"][sel], d["mass"][sel], d["pid"][sel])
     ell = L / nside
     param1 = (ell * ell) * (0.2 * 0.2) * (1.0 * 1.0)
     configs = [("3dfof", dict(fofbgtype=5, bound_halos=0)),
@@ -38,15 +41,26 @@ def main():
                ("3dfof+unbind(tree)", dict(fofbgtype=5, bound_halos=1, unbind=vrgpu.default_unbind_opts(pp_threshold=150))),
                ("6dfof+unbind(direct)", dict(fofbgtype=3, bound_halos=1, unbind=vrgpu.default_unbind_opts(pp_threshold=-1)))]
     ok = True
+    oracle = None
+    if rank == 0:
+        import vroracle
+        oracle = vroracle.Oracle()
+        b = 0.2 * ell
+        pf3, ng3 = oracle.fof3d(d["pos"], b, L, 20, d["pid"])
+        pos3 = oracle.adjust_for_period(d["pos"], L, pf3, ng3)
     for name, kw in configs:
         so = vrgpu.search_opts(L, param1, halo_min_size=20, **kw)
+        parts = vrgpu.particles_from_arrays(d["pos"][sel], d["vel"][sel], d["mass"][sel], d["pid"][sel])   # the call rewrites them
         pf, ng = ctx.dist_search_full_set(parts, lo, hi, so)
         gathered = [None] * world
-        dist.all_gather_object(gathered, (sel, pf, ng))
+        dist.all_gather_object(gathered, (sel, pf, ng, np.array(parts["pos"]), np.array(parts["vel"])))
         if rank == 0:
             full = np.zeros(nside ** 3, dtype=np.int64)
-            for s, p, g in gathered:
+            fpos, fvel = np.zeros((nside ** 3, 3)), np.zeros((nside ** 3, 3))
+            for s, p, g, xp, xv in gathered:
                 full[s] = p
+                fpos[s] = xp
+                fvel[s] = xv
                 assert g == ng
             ref_ctx = vrgpu.Context(local)
             allp = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"])
@@ -55,11 +69,29 @@ def main():
             ref_ctx.close()
             ndiff = int(np.count_nonzero(full != want))
             nbound = int(np.count_nonzero((full > 0) != (want > 0)))
+            coords = bool(np.array_equal(fpos, allp["pos"]) and np.array_equal(fvel, allp["vel"]))
             exact = name == "3dfof"
-            good = (ndiff == 0 and ng == ngw) if exact else (nbound <= 2 * nmarg + 2)
+            good = coords and ((ndiff == 0 and ng == ngw) if exact else (nbound <= 2 * nmarg + 2))
+            # against the oracle
+            if name == "3dfof":
+                o_ok = ng == ng3 and np.array_equal(full, pf3) and np.array_equal(fpos, pos3)
+                o_txt = f"oracle: groups {ng3}, membership + positions {'identical' if o_ok else 'DIFFER'}"
+            elif name.startswith("3dfof+unbind"):
+                import vroracle
+                pp = kw["unbind"].pp_threshold
+                uo = vroracle.unbind_opts_from(vroracle.default_opts(period=L, ellxscale=ell, fofbgtype=5, bound_halos=1), pp if pp >= 0 else 10 ** 9,
+                                               sortflag_mode=0)
+                orc = oracle.unbind(pos3, d["vel"], d["mass"], pf3, ng3, uo, d["pid"], 1e-6)
+                od = int(np.count_nonzero((full > 0) != (orc["pfof"] > 0)))
+                o_ok = od <= orc["n_marginal"] + nmarg and (od > 0 or (ng == orc["ngroups"] and np.array_equal(full, orc["pfof"])))
+                o_txt = f"oracle: groups {orc['ngroups']}, bound-set diffs {od}, oracle marginal {orc['n_marginal']}"
+            else:
+                o_ok, o_txt = True, "oracle: (6DFOF chain compared through the single-GPU path, itself pinned in tests/test_gpu_fof6d.py)"
+            good = good and o_ok
             ok = ok and good
             print(f"[mg_check] world={world} nside={nside} {name}: groups dist={ng} single={ngw} label diffs={ndiff} "
-                  f"bound-set diffs={nbound} marginal={nmarg} -> {'OK' if good else 'FAIL'}", flush=True)
+                  f"bound-set diffs={nbound} marginal={nmarg} coordinates written back {'identical' if coords else 'DIFFER'}; {o_txt} "
+                  f"-> {'OK' if good else 'FAIL'}", flush=True)
     res = [ok]
     dist.broadcast_object_list(res, src=0)
     ctx.close()

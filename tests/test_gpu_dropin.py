@@ -115,28 +115,35 @@ def test_check_unbound_groups_as_search_sub_sub_calls_it(ref, refgpu, oracle, fo
         want = ref.unbind_full(pos, d["vel"], d["mass"], pf, ng, o, ireorder=1, groupflag=flag)
         got = refgpu.unbind_full(pos, d["vel"], d["mass"], pf, ng, o, ireorder=1, groupflag=flag)
     assert got["changed"] == want["changed"] == 1
-    assert got["ngroups"] == want["ngroups"]
-    # Q10 (uninitialised oldnumingroup in the reference) may move a handful of bound flags; everything else must agree
-    nb = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
-    assert nb <= 40
-    both = (got["pfof"] > 0) & (want["pfof"] > 0)
-    if form == "keep_ids":
-        assert np.array_equal(got["pfof"][both], pf[both]) and np.array_equal(want["pfof"][both], pf[both])
-        assert np.array_equal(got["numingroup"] == 0, want["numingroup"] == 0)
-        assert np.abs(got["numingroup"] - want["numingroup"]).sum() <= nb
-    else:
-        # flags travel with their groups: every particle carries the same flag on both sides
-        assert np.array_equal(got["groupflag"][got["pfof"][both]], want["groupflag"][want["pfof"][both]])
-        # flagged groups come first; inside each class the sizes are monotonic (descending, then ascending)
-        for r in (got, want):
+    # Each side against ITS oracle, exactly (as in test_unbinding_through_reference_types): the library against the intended
+    # semantics of Q10, the reference against the oracle that carries oldnumingroup from group to group as the serial build does.
+    # On this box the two differ by 40 bound flags and one surviving group (300 / 301).
+    intended = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=0), d["pid"], 1e-6)
+    carried = oracle.unbind(pos, d["vel"], d["mass"], pf, ng, vroracle.unbind_opts_from(o, 150, sortflag_mode=1, oldn_init=0), d["pid"], 1e-6)
+    assert intended["n_marginal"] == 0
+    for side, r, orc in (("library", got, intended), ("reference", want, carried)):
+        bound = orc["pfof"] > 0
+        assert r["ngroups"] == orc["ngroups"], side
+        assert np.array_equal(r["pfof"] > 0, bound), side
+        if form == "keep_ids":
+            # ids kept, dissolved groups emptied, numingroup = the bound members left in every group
+            assert np.array_equal(r["pfof"], np.where(bound, pf, 0)), side
+            assert np.array_equal(r["numingroup"][1:], np.bincount(r["pfof"], minlength=ng + 1)[1:]), side
+            assert np.count_nonzero(r["numingroup"][1:] > 0) == r["ngroups"], side
+        else:
             gf, G = r["groupflag"], r["ngroups"]
+            # the same partition of the bound particles as the oracle's (ids differ: another ordering rule)
+            pairs = set(zip(r["pfof"][bound].tolist(), orc["pfof"][bound].tolist()))
+            assert len(pairs) == G == len({a for a, _ in pairs}) == len({b for _, b in pairs}), side
+            # flags travel with their groups
+            assert np.array_equal(gf[r["pfof"][bound]], flag[pf[bound]]), side
+            # flagged groups come first; inside each class the sizes are monotonic (descending, then ascending)
             num = np.bincount(r["pfof"], minlength=G + 1)   # (the reference leaves numingroup in the OLD numbering; its caller rebuilds it)
             cls = gf[1:G + 1]
-            assert np.all(np.diff((cls != 1).astype(int)) >= 0)
+            assert np.all(np.diff((cls != 1).astype(int)) >= 0), side
             n1 = num[1:G + 1][cls == 1]
             n2 = num[1:G + 1][cls != 1]
-            assert np.all(np.diff(n1) <= 0) and np.all(np.diff(n2) >= 0)
-        if nb == 0:
-            # same partition of the particles into groups (ids may differ among groups of equal value: quirk Q5)
-            pairs = set(zip(got["pfof"][both].tolist(), want["pfof"][both].tolist()))
-            assert len(pairs) == got["ngroups"]
+            assert np.all(np.diff(n1) <= 0) and np.all(np.diff(n2) >= 0), side
+    nq10 = int(np.count_nonzero((got["pfof"] > 0) != (want["pfof"] > 0)))
+    print(f"{form}: library {got['ngroups']} groups, reference {want['ngroups']}; Q10 particles {nq10}")
+    assert nq10 == 40

@@ -659,8 +659,16 @@ int vrgpu_dist_search_full_set(vrgpu_ctx *ctx, vrgpu_view view, double slab_lo, 
         }
         DBuf<long long> pf;
         long long ng = 0;
-        if (mg_nranks(ctx) == 1) run_search(ctx, P, o, nullptr, pf, ng);
-        else mg_search(ctx, P, slab_lo, slab_hi, o, pf, ng);
+        // the view receives the reference's in-place coordinate updates, as in vrgpu_search_full_set
+        if (mg_nranks(ctx) == 1) run_search(ctx, P, o, &view, pf, ng);
+        else {
+            MgWriteback wb;
+            mg_search(ctx, P, slab_lo, slab_hi, o, pf, ng, &wb);
+            StageTimer t(ctx);
+            if (wb.phase) writeback_phase(ctx, view, P, wb.pf3.p);
+            else if (wb.nmoved) scatter_positions_to_host(ctx, view, view.off_pos, wb.midx.p, wb.mxyz.p, wb.nmoved);
+            ctx->stats.d2h_ms += t.stop();
+        }
         {
             StageTimer t(ctx);
             download_i64(ctx, pf.p, pfof_out, P.n);

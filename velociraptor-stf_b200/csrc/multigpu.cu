@@ -714,13 +714,110 @@ __global__ void k_mg_scatter_back(const long long *__restrict__ lab, const uint3
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k < cnt) pfof[idx[k]] = lab[k];
 }
+// the same with the coordinates the consolidating rank rewrote: 7 words per particle (label, pos, vel)
+__global__ void k_mg_pack_back(const long long *__restrict__ lab, const double *__restrict__ pos, const double *__restrict__ vel, size_t at, size_t cnt,
+                               uint64_t *__restrict__ out)
+{
+    size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= cnt) return;
+    const size_t i = at + k;
+    out[7 * k] = (uint64_t)lab[i];
+    double *o = reinterpret_cast<double *>(out + 7 * k + 1);
+    o[0] = pos[3 * i]; o[1] = pos[3 * i + 1]; o[2] = pos[3 * i + 2];
+    o[3] = vel[3 * i]; o[4] = vel[3 * i + 1]; o[5] = vel[3 * i + 2];
+}
+__global__ void k_mg_scatter_back_phase(const uint64_t *__restrict__ in, const uint32_t *__restrict__ idx, uint32_t cnt, long long *__restrict__ pfof,
+                                        double *__restrict__ pos, double *__restrict__ vel)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= cnt) return;
+    const size_t i = idx[k];
+    pfof[i] = (long long)in[7 * (size_t)k];
+    const double *r = reinterpret_cast<const double *>(in + 7 * (size_t)k + 1);
+    pos[3 * i] = r[0]; pos[3 * i + 1] = r[1]; pos[3 * i + 2] = r[2];
+    vel[3 * i] = r[3]; vel[3 * i + 1] = r[4]; vel[3 * i + 2] = r[5];
+}
+
+// ---- AdjustStructureForPeriod over all ranks, without moving a particle ------------------------------------------------
+// The reference particle of a group is its member with the smallest pid (the first member of the reference's list whenever
+// pids follow the input order; a rank does not know the caller's global order).  Its position reaches every rank through two
+// all-reduces over per-group tables: MIN of the pid, then SUM of a table in which only the owner of that pid wrote its
+// position (x + 0 is exact).  Every member is then shifted by whole periods exactly as search.cxx:871-887 does.
+__global__ void k_mg_group_minpid(const long long *__restrict__ pfof, const long long *__restrict__ pid, size_t n, unsigned long long *__restrict__ minpid)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long g = pfof[i];
+    if (g > 0) atomicMin(&minpid[g], (unsigned long long)(pid ? pid[i] : (long long)i));
+}
+__global__ void k_mg_ref_pos(const long long *__restrict__ pfof, const long long *__restrict__ pid, const double *__restrict__ pos, size_t n,
+                             const unsigned long long *__restrict__ minpid, double *__restrict__ refpos)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long g = pfof[i];
+    if (g > 0 && (unsigned long long)(pid ? pid[i] : (long long)i) == minpid[g]) {
+        refpos[3 * (size_t)g] = pos[3 * i]; refpos[3 * (size_t)g + 1] = pos[3 * i + 1]; refpos[3 * (size_t)g + 2] = pos[3 * i + 2];
+    }
+}
+__global__ void k_mg_adjust_ref(double *__restrict__ pos, const long long *__restrict__ pfof, size_t n, const double *__restrict__ refpos, double period,
+                                uint32_t *__restrict__ moved_idx, double *__restrict__ moved_xyz, unsigned int *__restrict__ nmoved)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long g = pfof[i];
+    if (g <= 0) return;
+    double np[3];
+    bool moved = false;
+    for (int j = 0; j < 3; j++) {
+        double x = pos[3 * i + j];
+        const double diff = __dsub_rn(refpos[3 * (size_t)g + j], x);
+        if (diff < -0.5 * period) { x = __dsub_rn(x, period); moved = true; }
+        else if (diff > 0.5 * period) { x = __dadd_rn(x, period); moved = true; }
+        np[j] = x;
+    }
+    if (moved) {
+        const unsigned int slot = atomicAdd(nmoved, 1u);
+        moved_idx[slot] = (uint32_t)i;
+        for (int j = 0; j < 3; j++) { moved_xyz[3 * (size_t)slot + j] = np[j]; pos[3 * i + j] = np[j]; }
+    }
+}
+
+// every rank calls this with the same (global) ngroups; returns the number of particles of P it moved
+size_t mg_adjust_global(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof, long long ngroups, double period, DBuf<uint32_t> &moved_idx,
+                        DBuf<double> &moved_xyz)
+{
+    MultiGpu &M = *ctx->mg;
+    const int T = 256;
+    KScope k(ctx, "mg.adjust_for_period");
+    const size_t ng1 = (size_t)ngroups + 1;
+    DBuf<unsigned long long> minpid(ctx, ng1);
+    DBuf<double> refpos(ctx, 3 * ng1);
+    VR_CUDA(cudaMemsetAsync(minpid.p, 0xff, sizeof(unsigned long long) * ng1, ctx->stream));
+    VR_CUDA(cudaMemsetAsync(refpos.p, 0, sizeof(double) * 3 * ng1, ctx->stream));
+    const long long *pid = P.has_pid ? P.pid.p : nullptr;
+    if (P.n) VR_LAUNCH(ctx, k_mg_group_minpid, grid_for(P.n, T), T, 0, pfof, pid, P.n, minpid.p);
+    VR_NCCL(nccl_api().AllReduce(minpid.p, minpid.p, ng1, ncclUint64, ncclMin, M.comm, ctx->stream));
+    if (P.n) VR_LAUNCH(ctx, k_mg_ref_pos, grid_for(P.n, T), T, 0, pfof, pid, P.pos.p, P.n, minpid.p, refpos.p);
+    VR_NCCL(nccl_api().AllReduce(refpos.p, refpos.p, 3 * ng1, ncclDouble, ncclSum, M.comm, ctx->stream));
+    moved_idx.alloc(ctx, P.n + 1);
+    moved_xyz.alloc(ctx, 3 * P.n + 1);
+    DBuf<unsigned int> nmoved(ctx, 1);
+    VR_CUDA(cudaMemsetAsync(nmoved.p, 0, sizeof(unsigned int), ctx->stream));
+    if (P.n) VR_LAUNCH(ctx, k_mg_adjust_ref, grid_for(P.n, T), T, 0, P.pos.p, pfof, P.n, refpos.p, period, moved_idx.p, moved_xyz.p, nmoved.p);
+    unsigned int h = 0;
+    VR_CUDA(cudaMemcpyAsync(&h, nmoved.p, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    return h;
+}
 
 } // namespace
 
 // SearchFullSet over all ranks.  P: this rank's slab (device resident, original order).  pfof_out: device array of P.n
-// global group ids.  Coordinates are NOT written back to the caller in multi-GPU runs (documented in DESIGN.md).
+// global group ids.  With wb the coordinates the path rewrites are rewritten in P as well (and wb says which, for the host
+// write-back); without it P is only read.
 void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_hi, const vrgpu_search_opts *o, DBuf<long long> &pfof_out,
-               long long &ngroups)
+               long long &ngroups, MgWriteback *wb)
 {
     VR_REQUIRE(ctx->mg != nullptr, VRGPU_EINVAL, "vrgpu_dist_init has not been called");
     MultiGpu &M = *ctx->mg;
@@ -732,6 +829,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
     StageA A;
     mg_fof3d(ctx, P, slab_lo, slab_hi, std::sqrt(o->param1), o->period, o->halo_min_size, A);
     ctx->stats.n_groups3d = A.ngroups;
+    if (wb && o->period > 0 && A.ngroups > 0) wb->nmoved = mg_adjust_global(ctx, P, A.pfof.p, A.ngroups, o->period, wb->midx, wb->mxyz);
     if (!(six || unbind) || A.ngroups == 0) {
         pfof_out = std::move(A.pfof);
         ngroups = A.ngroups;
@@ -823,7 +921,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
 
     // ---- the single-GPU stages on the consolidated groups ----
     long long ngl = nloc;
-    if (ngl > 0) {
+    if (ngl > 0 && !wb) { // (with wb every group has been adjusted in P already, by the same rule)
         DBuf<uint32_t> midx;
         DBuf<double> mxyz;
         adjust_for_period_device(ctx, W, pfw.p, ngl, o->period, midx, mxyz, true);
@@ -856,21 +954,39 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
     }
     ngroups = O.total;
 
-    // ---- labels of imported particles go home ----
+    // ---- labels of imported particles go home; after a 6DFOF, with wb, their rewritten coordinates as well ----
     pfof_out.alloc(ctx, n_own + 1);
     if (n_own) VR_CUDA(cudaMemcpyAsync(pfof_out.p, pfw.p, n_own * sizeof(long long), cudaMemcpyDeviceToDevice, ctx->stream));
-    std::vector<DBuf<long long>> back(N);
-    for (int d = 0; d < N; d++) if (d != me) back[d].alloc(ctx, ecnt[d] + 1);
+    const bool phase = wb && six;
+    if (phase && n_own) {
+        // own particles that stayed here (the exported ones are unlabelled in W, so nothing touched their copies)
+        VR_CUDA(cudaMemcpyAsync(P.pos.p, W.pos.p, 3 * n_own * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(P.vel.p, W.vel.p, 3 * n_own * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    const size_t bw = phase ? 7 : 1; // words per returned particle
+    std::vector<DBuf<uint64_t>> back(N), bsend(N);
+    for (int d = 0; d < N; d++) if (d != me) back[d].alloc(ctx, bw * ecnt[d] + 1);
+    if (phase)
+        for (int s = 0; s < N; s++) {
+            const size_t rc = s == me ? 0 : (size_t)allcnt[(size_t)s * N + me];
+            if (!rc) continue;
+            bsend[s].alloc(ctx, 7 * rc);
+            VR_LAUNCH(ctx, k_mg_pack_back, grid_for(rc, T), T, 0, pfw.p, W.pos.p, W.vel.p, n_own + ioff[s], rc, bsend[s].p);
+        }
     VR_NCCL(nccl_api().GroupStart());
     for (int s = 0; s < N; s++) {
         if (s == me) continue;
         const size_t rc = (size_t)allcnt[(size_t)s * N + me];
-        if (rc) VR_NCCL(nccl_api().Send(pfw.p + n_own + ioff[s], rc * 8, ncclUint8, s, M.comm, ctx->stream));
-        if (ecnt[s]) VR_NCCL(nccl_api().Recv(back[s].p, (size_t)ecnt[s] * 8, ncclUint8, s, M.comm, ctx->stream));
+        if (rc) VR_NCCL(nccl_api().Send(phase ? (const void *)bsend[s].p : (const void *)(pfw.p + n_own + ioff[s]), rc * 8 * bw, ncclUint8, s, M.comm, ctx->stream));
+        if (ecnt[s]) VR_NCCL(nccl_api().Recv(back[s].p, (size_t)ecnt[s] * 8 * bw, ncclUint8, s, M.comm, ctx->stream));
     }
     VR_NCCL(nccl_api().GroupEnd());
-    for (int d = 0; d < N; d++)
-        if (d != me && ecnt[d]) VR_LAUNCH(ctx, k_mg_scatter_back, grid_for((size_t)ecnt[d], T), T, 0, back[d].p, eidx[d].p, (uint32_t)ecnt[d], pfof_out.p);
+    for (int d = 0; d < N; d++) {
+        if (d == me || !ecnt[d]) continue;
+        if (phase) VR_LAUNCH(ctx, k_mg_scatter_back_phase, grid_for((size_t)ecnt[d], T), T, 0, back[d].p, eidx[d].p, (uint32_t)ecnt[d], pfof_out.p, P.pos.p, P.vel.p);
+        else VR_LAUNCH(ctx, k_mg_scatter_back, grid_for((size_t)ecnt[d], T), T, 0, reinterpret_cast<const long long *>(back[d].p), eidx[d].p, (uint32_t)ecnt[d], pfof_out.p);
+    }
+    if (wb) { wb->phase = phase; if (phase) wb->pf3 = std::move(A.pfof); }
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
 }
 

@@ -642,13 +642,19 @@ __global__ void k_pt_pack(PtNodes N, const uint32_t *__restrict__ next, uint32_t
 // leaves that subtree (cur == the node's next link).  Every lane therefore sees exactly the nodes, in exactly the order,
 // of the reference's per-particle recursion, and node records are fetched once per warp instead of once per lane.
 constexpr uint32_t PT_ACTIVE = 0xfffffffeu;
-// Measured and dropped (profiles/r02a_probe.md): prefetch.global.L1 of both possible successors of a node -- 10 % slower.
+// Measured and dropped (profiles/r02_walk.md): prefetch.global.L1 of both possible successors of a node -- 10 % slower; one
+// warp per leaf with 8 targets x 4 sources and a shared-memory source stack -- the same number of warp steps (240 M against
+// 251 M at 256^3), each dearer: 28.0 ms against 13.3 ms.
+// STATS (VRGPU_WALK_STATS=1, a measuring aid): ninter[1..5] = warp-level node visits, visits in which some lane accepted the
+// monopole, accepting lanes summed over those, warp-level leaf-particle iterations, opening lanes summed over those.
+template <bool STATS>
 __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ nodes, const uint32_t *__restrict__ rootidx, uint32_t nL,
                                                  const double *__restrict__ tx, const double *__restrict__ ty, const double *__restrict__ tz,
                                                  const double *__restrict__ tm, double G, double eps2, const uint32_t *__restrict__ perm,
                                                  const uint32_t *__restrict__ slot_of, double *__restrict__ phi,
                                                  unsigned long long *__restrict__ ninter)
 {
+    unsigned long long st_visits = 0, st_accv = 0, st_accl = 0, st_leaf = 0, st_leafl = 0;
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = p < nL;
     const uint32_t myroot = valid ? rootidx[p] : NOCHILD;
@@ -679,8 +685,13 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
                 cnt++;
                 wait = next;
             }
+            if (STATS) {
+                const unsigned am = __ballot_sync(0xffffffffu, act && !open);
+                st_visits++; st_accv += am != 0; st_accl += __popc(am);
+            }
             if (!__any_sync(0xffffffffu, open)) { cur = next; continue; }
             if (left != NOCHILD) { cur = left; continue; }
+            if (STATS) { st_leaf += end - start; st_leafl += (unsigned long long)(end - start) * __popc(__ballot_sync(0xffffffffu, open)); }
             for (uint32_t l = start; l < end; l++) {
                 const double lx = __ldg(tx + l), ly = __ldg(ty + l), lz = __ldg(tz + l), lm = __ldg(tm + l);
                 if (open && l != p) {
@@ -696,6 +707,10 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
     if (valid) phi[slot_of[perm[p]]] = acc * G;
     for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(ninter, cnt);
+    if (STATS && (threadIdx.x & 31) == 0) {
+        atomicAdd(ninter + 1, st_visits); atomicAdd(ninter + 2, st_accv); atomicAdd(ninter + 3, st_accl);
+        atomicAdd(ninter + 4, st_leaf); atomicAdd(ninter + 5, st_leafl);
+    }
 }
 
 // tree-ordered columns: coordinates straight from the build's records, the mass through the member index
@@ -855,9 +870,10 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
         VR_LAUNCH(ctx, k_pt_r2max, grid_for(nnodes, T), T, 0, N, nnodes, theta);
     }
     // ---- walk ----
-    DBuf<unsigned long long> ninter(ctx, 1);
+    DBuf<unsigned long long> ninter(ctx, 8);
     DBuf<PtNode64> packed(ctx, nnodes);
-    VR_CUDA(cudaMemsetAsync(ninter.p, 0, sizeof(unsigned long long), ctx->stream));
+    VR_CUDA(cudaMemsetAsync(ninter.p, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    static const bool walk_stats = [] { const char *e = getenv("VRGPU_WALK_STATS"); return e && atoi(e) == 1; }();
     {
         KScope k(ctx, "ptree.walk");
         DBuf<uint32_t> next(ctx, nnodes);
@@ -867,12 +883,20 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             if (n1 > n0) VR_LAUNCH(ctx, k_pt_next, grid_for(n1 - n0, T), T, 0, nleft.p, next.p, n0, n1);
         }
         VR_LAUNCH(ctx, k_pt_pack, grid_for(nnodes, T), T, 0, N, next.p, nnodes, packed.p);
-        VR_LAUNCH(ctx, k_pt_walk, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
-                  phi, ninter.p);
+        if (walk_stats)
+            VR_LAUNCH(ctx, k_pt_walk<true>, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
+                      phi, ninter.p);
+        else
+            VR_LAUNCH(ctx, k_pt_walk<false>, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
+                      phi, ninter.p);
     }
-    unsigned long long hi = 0;
-    VR_CUDA(cudaMemcpyAsync(&hi, ninter.p, sizeof(hi), cudaMemcpyDeviceToHost, ctx->stream));
+    unsigned long long hs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    VR_CUDA(cudaMemcpyAsync(hs, ninter.p, sizeof(hs), cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    const unsigned long long hi = hs[0];
+    if (walk_stats)
+        fprintf(stderr, "[walk stats] targets %u nodes %u interactions %llu | warp visits %llu, with an accepting lane %llu (lanes %llu) | warp leaf iterations %llu (lanes %llu)\n",
+                nL, nnodes, hs[0], hs[1], hs[2], hs[3], hs[4], hs[5]);
     ctx->stats.n_tree_interactions += (long long)hi;
     ctx->stats.n_tree_nodes += (long long)nnodes;
 }

@@ -53,7 +53,18 @@ void mg_unique_id(char *out128);
 void mg_init(vrgpu_ctx *ctx, int nranks, int rank, const char *id128);
 int mg_nranks(const vrgpu_ctx *ctx);
 int mg_rank(const vrgpu_ctx *ctx);
+// What a multi-GPU search leaves for the host write-back of the coordinates the path rewrote (AdjustStructureForPeriod,
+// search.cxx:393-396 / :856-895; the scaling round trip of the 6DFOF, :565-575): with `phase` the positions and velocities of
+// every member of a 3D group (labels in pf3) changed in P, otherwise only the nmoved positions listed in midx / mxyz.
+struct MgWriteback {
+    DBuf<long long> pf3;
+    DBuf<uint32_t> midx;
+    DBuf<double> mxyz;
+    size_t nmoved = 0;
+    bool phase = false;
+};
+// wb == nullptr: P is left untouched (the resident variant restarts every run from it)
 void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_hi, const vrgpu_search_opts *o, DBuf<long long> &pfof_out,
-               long long &ngroups);
+               long long &ngroups, MgWriteback *wb = nullptr);
 
 } // namespace vrgpu

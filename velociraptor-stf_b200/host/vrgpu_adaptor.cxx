@@ -39,6 +39,10 @@
 using namespace std;
 using namespace NBody;
 
+/* bodies further down that SearchFullSet uses */
+Int_t *VRGPU_NAME(BuildNumInGroup)(const Int_t nbodies, const Int_t numgroups, Int_t *pfof);
+void VRGPU_NAME(GetVelocityDensity)(Options &opt, const Int_t nbodies, Particle *Part, KDTree *tree);
+
 static_assert(sizeof(Int_t) == sizeof(long long), "the GPU path needs the default LONGINT build (Int_t == long long)");
 static_assert(sizeof(Double_t) == sizeof(double), "the GPU path needs the default double precision build");
 
@@ -163,7 +167,38 @@ Int_t *VRGPU_NAME(SearchFullSet)(Options &opt, const Int_t nbodies, vector<Parti
     so.unbind = unbind_opts_of(opt);
     Int_t *pfof = new Int_t[nbodies > 0 ? nbodies : 1];
     long long ng = 0;
-    int rc = vrgpu_search_full_set(context(), view_of(Part.data(), nbodies), &so, reinterpret_cast<long long *>(pfof), &ng);
+    int rc;
+#ifdef STRUCDEN
+    /* search.cxx:205-235: a STRUCDEN build that goes on to the substructure search computes the local velocity density of the
+     * members of 3D groups of at least MINSUBSIZE particles here -- on the coordinates as read (before AdjustStructureForPeriod),
+     * with the tree of the 3DFOF, which is the tree GetVelocityDensity builds for tree == NULL (same bucket, same particles).
+     * So: the 3D labels first (no coordinate is touched), the density with the types set as the reference sets them, then the
+     * whole path. */
+    if (opt.iSubSearch == 1 && opt.foftype != FOF6DCORE && nbodies > 0) {
+        double per[3] = {(double)opt.p, (double)opt.p, (double)opt.p};
+        long long ng3 = 0;
+        rc = vrgpu_fof3d(context(), view_of(Part.data(), nbodies), sqrt(so.param1), opt.p > 0 ? per : NULL, so.halo_min_size,
+                         reinterpret_cast<long long *>(pfof), &ng3);
+        if (rc != VRGPU_OK) die("vrgpu_fof3d", rc);
+        if (ng3 > 0) {
+            Int_t *num3 = VRGPU_NAME(BuildNumInGroup)(nbodies, ng3, pfof);
+            vector<int> storetype((size_t)nbodies);
+            Int_t numinstrucs = 0;
+            for (Int_t i = 0; i < nbodies; i++) {
+                storetype[i] = Part[i].GetType();
+                int t;
+                if (!(opt.iBaryonSearch >= 1 && opt.partsearchtype == PSTALL)) t = num3[pfof[i]] >= MINSUBSIZE;
+                else t = storetype[i] == DARKTYPE ? (int)(num3[pfof[i]] >= MINSUBSIZE) : -1;
+                Part[i].SetType(t);
+                numinstrucs += t > 0;
+            }
+            if (numinstrucs > 0) VRGPU_NAME(GetVelocityDensity)(opt, nbodies, Part.data(), NULL);
+            for (Int_t i = 0; i < nbodies; i++) Part[i].SetType(storetype[i]);
+            delete[] num3;
+        }
+    }
+#endif
+    rc = vrgpu_search_full_set(context(), view_of(Part.data(), nbodies), &so, reinterpret_cast<long long *>(pfof), &ng);
     if (rc != VRGPU_OK) die("vrgpu_search_full_set", rc);
     numgroups = ng;
     /* the reference rewrites the scratch id field to the array index (KDTree construction, search.cxx:692-693) */
@@ -408,6 +443,20 @@ Int_t **VRGPU_NAME(BuildPGList)(const Int_t nbodies, const Int_t numgroups, Int_
     delete[] index;
     return pglist;
 }
+
+#ifndef VRGPU_REPLACE_REFERENCE_SYMBOLS
+/* A build that routes the call sites by renaming (-DBuildPGList=BuildPGListGPU, oracle/Makefile's stf_gpu) renames every
+ * overload.  The two index-indirect ones (src/buildandsortarrays.cxx:63-81, 83-100: lists of Part[i].GetID() / ids[i], used by
+ * SearchSubset on its sub-volumes) are not on the path: they forward to the reference's own bodies. */
+Int_t **BuildPGListGPU(const Int_t nbodies, const Int_t numgroups, Int_t *numingroup, Int_t *pfof, Particle *Part)
+{
+    return BuildPGList(nbodies, numgroups, numingroup, pfof, Part);
+}
+Int_t **BuildPGListGPU(const Int_t nbodies, const Int_t numgroups, Int_t *numingroup, Int_t *pfof, Int_t *ids)
+{
+    return BuildPGList(nbodies, numgroups, numingroup, pfof, ids);
+}
+#endif
 
 /* Row f2, linking step.  The 6D core search of SearchSubset (src/search.cxx:1531-1700) calls
  *     pfofbg = tree->FOFCriterion(fofcmp = FOF6d, param, numgroupsbg, minsize, iorder = 1, icheck = 1, FOFcheckbg);
