@@ -69,7 +69,13 @@ def main():
             ref_ctx.close()
             ndiff = int(np.count_nonzero(full != want))
             nbound = int(np.count_nonzero((full > 0) != (want > 0)))
-            coords = bool(np.array_equal(fpos, allp["pos"]) and np.array_equal(fvel, allp["vel"]))
+            # positions: bit for bit.  Velocities after a 6DFOF: the scaling round trip (Q3) multiplies by a group's dispersion, a sum
+            # over its members in array order -- and a group consolidated from two slabs is summed in another order than on one GPU,
+            # so the last bits of those members' velocities may differ; everything else must be identical
+            vsame = np.array_equal(fvel, allp["vel"])
+            vrel = 0.0 if vsame else float(np.max(np.abs(fvel - allp["vel"]) / np.maximum(np.abs(allp["vel"]), 1e-300)))
+            nv = 0 if vsame else int(np.count_nonzero(np.any(fvel != allp["vel"], axis=1)))
+            coords = bool(np.array_equal(fpos, allp["pos"]) and (vsame or (kw["fofbgtype"] <= 4 and vrel < 1e-14)))
             exact = name == "3dfof"
             good = coords and ((ndiff == 0 and ng == ngw) if exact else (nbound <= 2 * nmarg + 2))
             # against the oracle
@@ -90,7 +96,7 @@ def main():
             good = good and o_ok
             ok = ok and good
             print(f"[mg_check] world={world} nside={nside} {name}: groups dist={ng} single={ngw} label diffs={ndiff} "
-                  f"bound-set diffs={nbound} marginal={nmarg} coordinates written back {'identical' if coords else 'DIFFER'}; {o_txt} "
+                  f"bound-set diffs={nbound} marginal={nmarg} coordinates written back {'identical' if coords and vsame else ('positions identical, %d velocities within %.1e' % (nv, vrel) if coords else 'DIFFER (vel %.2e, %d particles)' % (vrel, nv))}; {o_txt} "
                   f"-> {'OK' if good else 'FAIL'}", flush=True)
     res = [ok]
     dist.broadcast_object_list(res, src=0)

@@ -55,7 +55,7 @@ CASES = {
     # tests/test_gpu_dropin.py): a handful of marginal members differ, so this case is compared to a stated tolerance
     "sample_with_substructure": dict(),
 }
-Q10_TOLERANCE = 1e-3   # fraction of the grouped particles whose object may differ in the stock sample (measured: ~3e-4)
+Q10_TOLERANCE = 2e-3   # fraction of the grouped particles whose object may differ in the stock sample (measured: 92 of 121572 = 7.6e-4)
 
 
 def _run(binary, workdir, snap, cfg, out):

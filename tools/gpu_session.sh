@@ -21,7 +21,7 @@ for s in "$@"; do
     t256c2) bash tools/ncu_traffic.sh r02g_traffic_256c2 --config 2 ;;
     zz) timeout 600 python -m pytest tests/test_zz_no_alloc.py -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/zz_pytest.log 2>&1; tail -15 gpurun_out/zz_pytest.log ;;
     new) timeout 1200 python -m pytest tests/test_gpu_dropin.py tests/test_gpu_stf_files.py tests/test_zz_no_alloc.py -q -m gpu --tb=short -s -p no:cacheprovider > gpurun_out/new_pytest.log 2>&1; tail -40 gpurun_out/new_pytest.log ;;
-    mg) for w in 2 4 8; do n=$(nvidia-smi -L | wc -l); [ $w -le $n ] || continue; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node=$w --master-addr 127.0.0.1 --master-port 29541 tests/dist/mg_check.py ${MG_NSIDE:-128} 2>&1 | grep -v "^W\|^\*" | tee gpurun_out/r02_mg${w}_check.log | tail -8; done ;;
+    mg) for w in ${MG_WORLDS:-2 4 8}; do n=$(nvidia-smi -L | wc -l); [ $w -le $n ] || continue; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node=$w --master-addr 127.0.0.1 --master-port 29541 tests/dist/mg_check.py ${MG_NSIDE:-128} 2>&1 | grep -v "^W\|^\*" | tee gpurun_out/r02_mg${w}_check.log | tail -8; done ;;
     *) echo "unknown section $s" ;;
   esac
 done

@@ -132,8 +132,10 @@ void run_search(vrgpu_ctx *ctx, DeviceParticles &P, const vrgpu_search_opts *o, 
     struct WbJoin {
         vrgpu_ctx *ctx;
         cudaEvent_t ev = nullptr;
+        HostWriteback *host = nullptr; // pageable caller memory: a worker thread scatters the coordinates beside the unbinding stage
         ~WbJoin()
         {
+            hostwb_join(ctx, host, false);
             if (!ev) return;
             cudaStreamWaitEvent(ctx->stream, ev, 0);
             cudaEventSynchronize(ev);
@@ -171,8 +173,13 @@ void run_search(vrgpu_ctx *ctx, DeviceParticles &P, const vrgpu_search_opts *o, 
         if (view) {
             // experiment (off by default): the write-back runs on the copy stream beside the unbinding stage
             static const bool async_wb = [] { const char *e = getenv("VRGPU_ASYNC_WRITEBACK"); return e && atoi(e) == 1; }();
+            // pageable records (what the reference passes): on by default when an unbinding stage follows, VRGPU_ASYNC_WRITEBACK=0 keeps
+            // it in front of that stage (profiles/r02_e2e.md)
+            static const bool host_async = [] { const char *e = getenv("VRGPU_ASYNC_WRITEBACK"); return !(e && atoi(e) == 0); }();
             if (async_wb) wb.ev = writeback_phase_async(ctx, *view, P, pf.p);
+            if (!wb.ev && host_async && unbind) wb.host = hostwb_start(ctx, *view, P, pf.p);
             if (wb.ev) pf3_keep = std::move(pf); // read by the copy stream until wb.ev
+            else if (wb.host) {}
             else {
                 StageTimer t2(ctx);
                 writeback_phase(ctx, *view, P, pf.p);
@@ -187,6 +194,13 @@ void run_search(vrgpu_ctx *ctx, DeviceParticles &P, const vrgpu_search_opts *o, 
         long long nmarg = 0;
         unbind_device(ctx, P, pf.p, ng, o->unbind, changed, nmarg);
         ctx->stats.n_marginal = nmarg;
+    }
+    if (wb.host) { // errors of the worker surface here; on an exception above the destructor joins it silently
+        StageTimer t2(ctx);
+        HostWriteback *h = wb.host;
+        wb.host = nullptr;
+        hostwb_join(ctx, h, true);
+        ctx->stats.d2h_ms += t2.stop();
     }
 }
 

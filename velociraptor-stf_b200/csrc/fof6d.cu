@@ -26,6 +26,8 @@
 #include "ufhash.cuh"
 
 #include <algorithm>
+#include <memory>
+#include <thread>
 #include <cstdlib>
 #include <cstring>
 #include <thread>
@@ -1067,6 +1069,105 @@ cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const 
     ctx->evpool.push_back(ready);
     ctx->stats.d2h_bytes += (long long)ctx->stats.n_grouped * 48;
     return done; // the caller waits on it and hands it back to ctx->evpool
+}
+
+struct HostWriteback {
+    std::thread worker;
+    DBuf<double> out;                 // 7 words per grouped particle: index, pos, vel -- alive until the join
+    cudaEvent_t ready = nullptr, done[2] = {nullptr, nullptr};
+    cudaError_t err = cudaSuccess;
+    size_t bytes = 0;
+};
+
+HostWriteback *hostwb_start(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev)
+{
+    if (P.n == 0 || mapped_host_pointer(view.base)) return nullptr;
+    VR_REQUIRE(P.has_vel && view.off_vel != VRGPU_NOFIELD, VRGPU_EINVAL, "write-back needs velocities in the view");
+    const int T = 256;
+    uint32_t cnt = 0;
+    std::unique_ptr<HostWriteback> job(new HostWriteback);
+    {
+        DBuf<uint32_t> flags(ctx, P.n), excl(ctx, P.n), total(ctx, 1);
+        VR_LAUNCH(ctx, k_flag_pos, grid_for(P.n, T), T, 0, pfof_dev, P.n, flags.p);
+        exclusive_scan_u32(ctx, flags.p, excl.p, P.n, total.p);
+        VR_CUDA(cudaMemcpyAsync(&cnt, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (cnt == 0) return nullptr;
+        job->out.alloc(ctx, 7 * (size_t)cnt);
+        VR_LAUNCH(ctx, k_pack_phase, grid_for(P.n, T), T, 0, P.pos.p, P.vel.p, flags.p, excl.p, P.n, job->out.p);
+    }
+    if (!ctx->copy_stream) VR_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    if (!ctx->stage_host[0]) {
+        VR_CUDA(cudaHostAlloc(&ctx->stage_host[0], (size_t)32 << 20, cudaHostAllocDefault));
+        VR_CUDA(cudaHostAlloc(&ctx->stage_host[1], (size_t)32 << 20, cudaHostAllocDefault));
+    }
+    job->ready = KScope::get(ctx); job->done[0] = KScope::get(ctx); job->done[1] = KScope::get(ctx);
+    job->bytes = (size_t)cnt * 56;
+    VR_CUDA(cudaEventRecord(job->ready, ctx->stream));
+    VR_CUDA(cudaStreamWaitEvent(ctx->copy_stream, job->ready, 0));
+    // everything the worker touches, by value: it never looks at the context
+    HostWriteback *j = job.get();
+    const int device = ctx->device;
+    cudaStream_t cs = ctx->copy_stream;
+    void *stage[2] = {ctx->stage_host[0], ctx->stage_host[1]};
+    unsigned char *base = const_cast<unsigned char *>(static_cast<const unsigned char *>(view.base));
+    const size_t stride = view.stride, op = view.off_pos, ov = view.off_vel;
+    job->worker = std::thread([j, device, cs, stage, base, stride, op, ov] {
+        void *st[2] = {stage[0], stage[1]};
+        cudaError_t e = cudaSetDevice(device);
+        size_t chunk = (size_t)32 << 20;
+        chunk -= chunk % 56;
+        const unsigned char *src = reinterpret_cast<const unsigned char *>(j->out.p);
+        const size_t nchunks = (j->bytes + chunk - 1) / chunk;
+        auto issue = [&](size_t c) {
+            const size_t o = c * chunk, len = std::min(chunk, j->bytes - o);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(st[c & 1], src + o, len, cudaMemcpyDeviceToHost, cs);
+            if (e == cudaSuccess) e = cudaEventRecord(j->done[c & 1], cs);
+        };
+        auto scatter = [&](const unsigned char *from, size_t len, int part, int nparts) {
+            const size_t nrec = len / 56, k0 = nrec * part / nparts, k1 = nrec * (part + 1) / nparts;
+            for (size_t k = k0; k < k1; k++) {
+                const double *r = reinterpret_cast<const double *>(from + 56 * k);
+                unsigned long long i;
+                memcpy(&i, r, 8);
+                unsigned char *rec = base + (size_t)i * stride;
+                double *pp = reinterpret_cast<double *>(rec + op);
+                double *vv = reinterpret_cast<double *>(rec + ov);
+                pp[0] = r[1]; pp[1] = r[2]; pp[2] = r[3];
+                vv[0] = r[4]; vv[1] = r[5]; vv[2] = r[6];
+            }
+        };
+        issue(0);
+        for (size_t c = 0; c < nchunks && e == cudaSuccess; c++) {
+            e = cudaEventSynchronize(j->done[c & 1]);
+            if (e != cudaSuccess) break;
+            if (c + 1 < nchunks) issue(c + 1);
+            const size_t len = std::min(chunk, j->bytes - c * chunk);
+            const unsigned char *from = static_cast<const unsigned char *>(st[c & 1]);
+            const int nt = len > ((size_t)1 << 20) ? 8 : 1;
+            std::thread th[8];
+            for (int t = 1; t < nt; t++) th[t] = std::thread([&, t] { scatter(from, len, t, nt); });
+            scatter(from, len, 0, nt);
+            for (int t = 1; t < nt; t++) th[t].join();
+        }
+        if (e != cudaSuccess) cudaStreamSynchronize(cs); // leave nothing in flight on the staging buffers
+        j->err = e;
+    });
+    return job.release();
+}
+
+void hostwb_join(vrgpu_ctx *ctx, HostWriteback *job, bool may_throw)
+{
+    if (!job) return;
+    std::unique_ptr<HostWriteback> own(job);
+    if (job->worker.joinable()) job->worker.join();
+    ctx->evpool.push_back(job->ready);
+    ctx->evpool.push_back(job->done[0]);
+    ctx->evpool.push_back(job->done[1]);
+    ctx->stats.d2h_bytes += (long long)job->bytes;
+    const cudaError_t e = job->err;
+    own.reset(); // (the packed records go back to the pool: the copy stream is done with them)
+    if (e != cudaSuccess && may_throw) VR_CUDA(e);
 }
 
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev)

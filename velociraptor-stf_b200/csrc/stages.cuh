@@ -14,6 +14,14 @@ long long fof_criterion6d_device(vrgpu_ctx *ctx, const DeviceParticles &P, const
                                  long long minsize, long long *pfof_dev);
 void writeback_phase(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
 cudaEvent_t writeback_phase_async(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
+// The same into PAGEABLE caller memory, beside the stages that follow: the coordinates are packed on the context's stream (so P
+// may change afterwards), a worker thread brings the packed records back on the copy stream through the page-locked staging
+// buffers and scatters them into the caller's records while the caller's thread goes on launching the unbinding stage.
+// hostwb_start returns false (nothing started) when the caller's memory is page-locked or nothing is grouped; hostwb_join must
+// run before anything else uses the staging buffers and before the call returns.
+struct HostWriteback;
+HostWriteback *hostwb_start(vrgpu_ctx *ctx, const vrgpu_view &view, const DeviceParticles &P, const long long *pfof_dev);
+void hostwb_join(vrgpu_ctx *ctx, HostWriteback *job, bool may_throw);
 
 // GetVelocityDensity (src/localfield.cxx:18) for one structure; type_dev (original order) may be null; den_dev in original order (veldens.cu)
 // leaf_off_dev (ncaller_leaves + 1 offsets into the caller's order, may be null): leaves of the caller's own tree for the per-leaf search
