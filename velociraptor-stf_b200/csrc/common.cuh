@@ -184,20 +184,21 @@ struct KScope {
     static cudaEvent_t get(vrgpu_ctx *c)
     {
         if (!c->evpool.empty()) { cudaEvent_t e = c->evpool.back(); c->evpool.pop_back(); return e; }
-        cudaEvent_t e;
-        cudaEventCreate(&e);
+        cudaEvent_t e = nullptr; // (stays null when the context is in a sticky error state: every user checks)
+        if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); return nullptr; }
         return e;
     }
     KScope(vrgpu_ctx *c, const char *n) : ctx(c), name(n)
     {
         if (!c->ktiming) return;
         a = get(c);
-        cudaEventRecord(a, c->stream);
+        if (a) cudaEventRecord(a, c->stream);
     }
     ~KScope()
     {
         if (!a) return;
         cudaEvent_t b = get(ctx);
+        if (!b) { ctx->evpool.push_back(a); return; }
         cudaEventRecord(b, ctx->stream);
         ctx->kpending.push_back({name, a, b});
     }

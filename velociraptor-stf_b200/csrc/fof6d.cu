@@ -481,6 +481,15 @@ __global__ void k_chunk_counts(const uint32_t *__restrict__ cell_start, uint32_t
     if (c < ncells) nchunk[c] = (cell_start[c + 1] - cell_start[c] + 31) >> 5;
 }
 
+// chunk -> its cell (most cells are one chunk; a dense cell writes its few chunk entries in a loop)
+__global__ void k_chunk_cells(const uint32_t *__restrict__ chunk_start, const uint32_t *__restrict__ nchunk, uint32_t ncells, uint32_t *__restrict__ chunk_cell)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const uint32_t k0 = chunk_start[c], k1 = k0 + nchunk[c];
+    for (uint32_t k = k0; k < k1; k++) chunk_cell[k] = c;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // linking
 // ---------------------------------------------------------------------------------------------------
@@ -496,7 +505,9 @@ struct Link6 {
     uint32_t *parent;
     const uint32_t *uni;        // per cell: common root of all its particles, or NONE32
     const uint32_t *chunk_start; // exclusive scan of per-cell 32-particle chunk counts
+    const uint32_t *chunk_cell;  // chunk -> cell
     uint32_t nchunks;
+    uint32_t sparse_a;           // cells of at most this many particles may take the sparse path (0: never)
     double p6, p7, ip6, ip7;    // criterion predicate only (FOF6d: params[6], params[7] and their reciprocals)
 };
 
@@ -574,6 +585,7 @@ __global__ void __launch_bounds__(256) k_cell_uniform(const uint32_t *__restrict
 }
 
 constexpr int L6_WARPS = 8;
+constexpr uint32_t L6_SPARSE_A = 8, L6_SPARSE_B = 32; // a cell of at most 8 particles whose 14 neighbour cells hold at most 32 each
 
 // exhaustive pass: one warp per 32-particle chunk of a cell; 13 forward neighbour cells + the cell itself.
 template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_link6(Link6 L)
@@ -584,13 +596,7 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
     const uint32_t nw = gridDim.x * L6_WARPS;
     const size_t n = L.ntot;
     for (uint32_t item = blockIdx.x * L6_WARPS + w; item < L.nchunks; item += nw) {
-        // cell of this chunk: largest c with chunk_start[c] <= item
-        uint32_t lo = 0, hi = L.ncells - 1;
-        while (lo < hi) {
-            uint32_t mid = (lo + hi + 1) >> 1;
-            if (L.chunk_start[mid] <= item) lo = mid; else hi = mid - 1;
-        }
-        const uint32_t A = lo;
+        const uint32_t A = L.chunk_cell[item];
         const uint32_t a0 = L.cell_start[A], a1 = L.cell_start[A + 1];
         const uint32_t i = a0 + ((item - L.chunk_start[A]) << 5) + lane;
         const bool valid = i < a1;
@@ -622,6 +628,39 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
             }
         }
         unsigned found = __ballot_sync(0xffffffffu, nb >= 0);
+        // Sparse neighbourhoods (the outskirts of every group: a handful of particles per cell) leave most lanes of a chunk idle
+        // and pay one tile round trip per neighbour cell.  There the (particle, neighbour cell) pairs are spread over the lanes
+        // instead, and every lane walks its neighbour cell straight from global memory.
+        if (a1 - a0 <= L.sparse_a) {
+            uint32_t nb0 = 0, nbsz = 0, nbuni = NONE32;
+            if (nb >= 0) { nb0 = L.cell_start[nb]; nbsz = L.cell_start[nb + 1] - nb0; nbuni = L.uni[nb]; }
+            if (!__any_sync(0xffffffffu, nbsz > L6_SPARSE_B)) {
+                const uint32_t ka = a1 - a0;
+                const unsigned nitems = ka * (unsigned)__popc(found);
+                for (unsigned base = 0; base < nitems; base += 32) {
+                    const unsigned it = base + lane;
+                    const bool on = it < nitems;
+                    const unsigned il = on ? it % ka : 0u, oi = on ? it / ka : 0u;
+                    const int src = (int)__fns(found, 0, (int)oi + 1);
+                    const uint32_t B = (uint32_t)__shfl_sync(0xffffffffu, nb, src), b0 = __shfl_sync(0xffffffffu, nb0, src),
+                                   bs = __shfl_sync(0xffffffffu, nbsz, src), uniB = __shfl_sync(0xffffffffu, nbuni, src);
+                    if (!on || (uniA != NONE32 && uniA == uniB)) continue;
+                    const uint32_t pi = a0 + il;
+                    const bool self = B == A;
+                    const double px = L.q[pi], py = L.q[n + pi], pz = L.q[2 * n + pi], pvx = L.q[3 * n + pi], pvy = L.q[4 * n + pi], pvz = L.q[5 * n + pi];
+                    uint32_t rp = uf_find(L.parent, pi);
+                    for (uint32_t j = self ? pi + 1 : b0; j < b0 + bs; j++) {
+                        if (((volatile uint32_t *)L.parent)[j] == rp) continue; // possibly stale ancestor: only costs a redundant test
+                        if (links6p<CRIT>(L, px, py, pz, pvx, pvy, pvz, L.q[j], L.q[n + j], L.q[2 * n + j], L.q[3 * n + j], L.q[4 * n + j], L.q[5 * n + j])) {
+                            uf_union(L.parent, pi, j);
+                            if (uniB != NONE32 && !self) break; // B was one component already: nothing left to find in it
+                            rp = uf_find(L.parent, pi);
+                        }
+                    }
+                }
+                continue;
+            }
+        }
         while (found) {
             const int src = __ffs(found) - 1;
             found &= found - 1;
@@ -737,7 +776,7 @@ static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &
     DBuf<uint64_t> keys(ctx, ntot), keys_tmp(ctx, ntot);
     DBuf<uint32_t> ord(ctx, ntot), ord_tmp(ctx, ntot);
     DBuf<double> q(ctx, 6 * (size_t)ntot);
-    DBuf<uint32_t> cell_of(ctx, ntot), cell_start, nchunk, chunk_start;
+    DBuf<uint32_t> cell_of(ctx, ntot), cell_start, nchunk, chunk_start, chunk_cell;
     DBuf<uint64_t> cell_key;
     uint32_t ncells = 0, nwork = 0;
     {
@@ -775,6 +814,8 @@ static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &
         exclusive_scan_u32(ctx, nchunk.p, chunk_start.p, ncells, total.p);
         VR_CUDA(cudaMemcpyAsync(&nwork, total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        chunk_cell.alloc(ctx, (size_t)nwork + 1);
+        VR_LAUNCH(ctx, k_chunk_cells, grid_for(ncells, T), T, 0, chunk_start.p, nchunk.p, ncells, chunk_cell.p);
     }
     keys.reset(); keys_tmp.reset(); ord_tmp.reset();
     bx.reset(); by.reset(); bz.reset();
@@ -791,7 +832,9 @@ static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &
         Link6 L{};
         L.q = q.p; L.ntot = ntot; L.cell_of = cell_of.p; L.cell_start = cell_start.p; L.cell_key = cell_key.p; L.ncells = ncells;
         L.hkeys = hkeys.p; L.hvals = hvals.p; L.hmask = (uint32_t)(h - 1); L.parent = parent.p; L.uni = uni.p;
-        L.chunk_start = chunk_start.p; L.nchunks = nwork;
+        L.chunk_start = chunk_start.p; L.chunk_cell = chunk_cell.p; L.nchunks = nwork;
+        static const int sparse_a = [] { const char *e = getenv("VRGPU_LINK6_SPARSE"); return e ? atoi(e) : (int)L6_SPARSE_A; }();
+        L.sparse_a = (uint32_t)sparse_a;
         if (crit) { L.p6 = crit[0]; L.p7 = crit[1]; L.ip6 = 1.0 / crit[0]; L.ip7 = 1.0 / crit[1]; }
         {
             KScope k(ctx, "fof6d.hash_build");

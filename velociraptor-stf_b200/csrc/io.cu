@@ -12,6 +12,10 @@
 #include <vector>
 #include <string>
 
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
+
 namespace vrgpu {
 
 struct UnpackArgs {
@@ -71,6 +75,20 @@ void pack_window(unsigned char *dst, const unsigned char *src, size_t cnt, size_
     auto work = [=](size_t r0, size_t r1) {
         if (width == stride) { std::memcpy(dst + r0 * width, src + r0 * stride, (r1 - r0) * width); return; }
         const size_t nw = width / 8;
+#if defined(__SSE2__)
+        // 64-byte windows into the 64-byte aligned staging buffer (NBody::Particle: mass, pos, vel, pid): streaming stores, so that
+        // the staging lines are not read before they are overwritten -- the packing is bound by the host's memory bandwidth
+        if (width == 64 && (reinterpret_cast<uintptr_t>(dst) & 63u) == 0) {
+            for (size_t i = r0; i < r1; i++) {
+                const __m128i *s16 = reinterpret_cast<const __m128i *>(src + i * stride + wlo);
+                __m128i *d16 = reinterpret_cast<__m128i *>(dst + i * 64);
+                const __m128i a = _mm_loadu_si128(s16), b = _mm_loadu_si128(s16 + 1), c = _mm_loadu_si128(s16 + 2), d = _mm_loadu_si128(s16 + 3);
+                _mm_stream_si128(d16, a); _mm_stream_si128(d16 + 1, b); _mm_stream_si128(d16 + 2, c); _mm_stream_si128(d16 + 3, d);
+            }
+            _mm_sfence();
+            return;
+        }
+#endif
         for (size_t i = r0; i < r1; i++) {
             const uint64_t *s8 = reinterpret_cast<const uint64_t *>(src + i * stride + wlo);
             uint64_t *d8 = reinterpret_cast<uint64_t *>(dst + i * width);
