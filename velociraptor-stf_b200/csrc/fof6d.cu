@@ -507,7 +507,8 @@ struct Link6 {
     const uint32_t *chunk_start; // exclusive scan of per-cell 32-particle chunk counts
     const uint32_t *chunk_cell;  // chunk -> cell
     uint32_t nchunks;
-    uint32_t sparse_a;           // cells of at most this many particles may take the sparse path (0: never)
+    unsigned long long *st;      // VRGPU_LINK6_STATS=1: counters (a measuring aid)
+    uint32_t sparse_a, sparse_b; // a cell of at most sparse_a particles whose neighbour cells hold at most sparse_b each takes the sparse path
     double p6, p7, ip6, ip7;    // criterion predicate only (FOF6d: params[6], params[7] and their reciprocals)
 };
 
@@ -634,7 +635,7 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
         if (a1 - a0 <= L.sparse_a) {
             uint32_t nb0 = 0, nbsz = 0, nbuni = NONE32;
             if (nb >= 0) { nb0 = L.cell_start[nb]; nbsz = L.cell_start[nb + 1] - nb0; nbuni = L.uni[nb]; }
-            if (!__any_sync(0xffffffffu, nbsz > L6_SPARSE_B)) {
+            if (!__any_sync(0xffffffffu, nbsz > L.sparse_b)) {
                 const uint32_t ka = a1 - a0;
                 const unsigned nitems = ka * (unsigned)__popc(found);
                 for (unsigned base = 0; base < nitems; base += 32) {
@@ -645,6 +646,7 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
                     const uint32_t B = (uint32_t)__shfl_sync(0xffffffffu, nb, src), b0 = __shfl_sync(0xffffffffu, nb0, src),
                                    bs = __shfl_sync(0xffffffffu, nbsz, src), uniB = __shfl_sync(0xffffffffu, nbuni, src);
                     if (!on || (uniA != NONE32 && uniA == uniB)) continue;
+                    if (L.st) { atomicAdd(L.st + 4, 1ull); atomicAdd(L.st + 5, (unsigned long long)bs); }
                     const uint32_t pi = a0 + il;
                     const bool self = B == A;
                     const double px = L.q[pi], py = L.q[n + pi], pz = L.q[2 * n + pi], pvx = L.q[3 * n + pi], pvy = L.q[4 * n + pi], pvz = L.q[5 * n + pi];
@@ -661,6 +663,7 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
                 continue;
             }
         }
+        if (L.st && lane == 0) { atomicAdd(L.st + 6, 1ull); atomicAdd(L.st + 7, (unsigned long long)(a1 - a0 < 32u ? a1 - a0 : 32u)); }
         while (found) {
             const int src = __ffs(found) - 1;
             found &= found - 1;
@@ -669,24 +672,39 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
             if (uniA != NONE32 && uniA == uniB) continue; // both cells already inside one component
             const uint32_t b0 = L.cell_start[B], b1 = L.cell_start[B + 1];
             const bool self = B == A;
+            if (valid) ri = uf_find(L.parent, i); // links made by other warps since
             for (uint32_t tb = b0; tb < b1; tb += 32) {
                 // lanes already in B's (uniform) component have nothing left to find in B
                 if (uniB != NONE32 && __all_sync(0xffffffffu, !valid || ri == uniB)) break;
                 if (self && tb + 31 <= a0 + ((item - L.chunk_start[A]) << 5)) continue; // tile entirely before this chunk (j > i only)
                 const uint32_t j = tb + lane;
+                // The dense cells at the centre of a group are one component long before this pass ends, yet a few stragglers keep
+                // them from being `uniform`.  So first the tile's current roots alone: a tile whose 32 particles share one root that
+                // every particle of the chunk has too needs neither its coordinates nor the 32-step loop.
+                const uint32_t rj = j < b1 ? uf_find(L.parent, j) : NONE32;
+                const uint32_t r0 = __shfl_sync(0xffffffffu, rj, 0);
+                if (__all_sync(0xffffffffu, (j >= b1 || rj == r0) && (!valid || ri == r0))) {
+                    if (L.st && lane == 0) atomicAdd(L.st + 1, 1ull);
+                    continue;
+                }
                 __syncwarp();
                 if (j < b1) {
                     tq[w][0][lane] = L.q[j]; tq[w][1][lane] = L.q[n + j]; tq[w][2][lane] = L.q[2 * n + j];
                     tq[w][3][lane] = L.q[3 * n + j]; tq[w][4][lane] = L.q[4 * n + j]; tq[w][5][lane] = L.q[5 * n + j];
-                    tr[w][lane] = ((volatile uint32_t *)L.parent)[j]; // possibly stale ancestor: only costs a redundant test
+                    // the CURRENT root (with path halving), not parent[j]: once components have met, a stale ancestor would send every
+                    // pair of the two cells through the full test and a union that finds nothing to do
+                    tr[w][lane] = rj;
                 }
                 __syncwarp();
                 const int cnt = (int)min(32u, b1 - tb);
+                if (L.st && lane == 0) atomicAdd(L.st + 0, 1ull);
+                if (L.st) atomicAdd(L.st + 2, valid ? (unsigned long long)cnt : 0ull);
                 if (valid) {
                     for (int jj = 0; jj < cnt; jj++) {
                         const uint32_t jx = tb + jj;
                         if (self && jx <= i) continue;
                         if (tr[w][jj] == ri) continue;
+                        if (L.st) atomicAdd(L.st + 3, 1ull);
                         if (links6p<CRIT>(L, ax, ay, az, avx, avy, avz, tq[w][0][jj], tq[w][1][jj], tq[w][2][jj], tq[w][3][jj], tq[w][4][jj], tq[w][5][jj])) {
                             uf_union(L.parent, i, jx);
                             ri = uf_find(L.parent, i);
@@ -835,6 +853,11 @@ static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &
         L.chunk_start = chunk_start.p; L.chunk_cell = chunk_cell.p; L.nchunks = nwork;
         static const int sparse_a = [] { const char *e = getenv("VRGPU_LINK6_SPARSE"); return e ? atoi(e) : (int)L6_SPARSE_A; }();
         L.sparse_a = (uint32_t)sparse_a;
+        static const bool link6_stats = [] { const char *e = getenv("VRGPU_LINK6_STATS"); return e && atoi(e) == 1; }();
+        DBuf<unsigned long long> lst;
+        if (link6_stats) { lst.alloc(ctx, 8); VR_CUDA(cudaMemsetAsync(lst.p, 0, 64, ctx->stream)); L.st = lst.p; }
+        static const int sparse_b = [] { const char *e = getenv("VRGPU_LINK6_SPARSE_B"); return e ? atoi(e) : (int)L6_SPARSE_B; }();
+        L.sparse_b = (uint32_t)sparse_b;
         if (crit) { L.p6 = crit[0]; L.p7 = crit[1]; L.ip6 = 1.0 / crit[0]; L.ip7 = 1.0 / crit[1]; }
         {
             KScope k(ctx, "fof6d.hash_build");
@@ -855,6 +878,13 @@ static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &
             const unsigned grid = std::max(1u, std::min<unsigned>((nwork + L6_WARPS - 1) / L6_WARPS, (unsigned)ctx->sm_count * 32u));
             if (crit) VR_LAUNCH(ctx, k_link6<true>, grid, L6_WARPS * 32, 0, L);
             else VR_LAUNCH(ctx, k_link6<false>, grid, L6_WARPS * 32, 0, L);
+            if (link6_stats) {
+                unsigned long long h[8];
+                VR_CUDA(cudaMemcpyAsync(h, lst.p, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+                VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                fprintf(stderr, "[link6 stats] particles %u cells %u chunks %u | dense chunks %llu (particles %llu), tiles %llu (+ %llu skipped on their roots), valid-lane iterations %llu, "
+                        "full tests %llu | sparse items %llu, their neighbour particles %llu\n", ntot, ncells, nwork, h[6], h[7], h[0], h[1], h[2], h[3], h[4], h[5]);
+            }
             VR_LAUNCH(ctx, k_uf_flatten, grid_for(ntot, T), T, 0, parent.p, ntot, root.p);
         }
     }
