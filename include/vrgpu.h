@@ -219,8 +219,10 @@ int vrgpu_resident_pfof(vrgpu_ctx *ctx, long long *pfof_out);
  * Rank r of `nranks` holds the particles with slab_lo <= x < slab_hi; the slabs are ordered by rank and tile
  * [0, period).  Rank 0 creates the 128-byte id, the host code broadcasts it (MPI_Bcast in the reference's world,
  * torch.distributed in bench.py), every rank calls vrgpu_dist_init.  The search returns GLOBAL group ids (identical on
- * every rank and identical to the single-GPU ids); *ngroups_out is the global group count.  Unlike the single-GPU
- * call, coordinates are not written back to the caller (pfof only). */
+ * every rank and identical to the single-GPU ids); *ngroups_out is the global group count.  Like the single-GPU call it
+ * rewrites the caller's (writable) records: grouped particles unwrapped across the period about their group's smallest-pid
+ * member (search.cxx:856-895; a rank does not know the caller's global order, and the two agree when pids follow the input
+ * order), and after a 6DFOF the scale / unscale rounding of positions and velocities (search.cxx:565-575). */
 #define VRGPU_UNIQUE_ID_BYTES 128
 int vrgpu_dist_unique_id(char *id_out /*[128]*/);
 int vrgpu_dist_init(vrgpu_ctx *ctx, int nranks, int rank, const char *id /*[128]*/);

@@ -2,8 +2,8 @@
 //
 // Test infrastructure.  The per-thread functions of veldens.cuh (leaf centres, neighbour search, velocity step + kernel
 // sum) are compiled here by g++ (-ffp-contract=off) and run once per "thread"; the steps around them are plain host
-// restatements of the device steps in veldens.cu: the tree (recursive here, with the reference's selection from qsel.cuh:
-// the node membership and order of the exact-ties build, which tests/test_qsel_host.py pins), tree-ordered columns,
+// restatements of the device steps in veldens.cu: the tree (recursive here, with the reference's selection restated below:
+// the node membership and order of the exact-ties build, which tests/test_gpu_tree.py pins on the device), tree-ordered columns,
 // bounding boxes, the leaf list and the kernel table.  Queries run in batches like the device code.
 // Output: densities in input order, which tests/test_veldens_host.py compares with the oracle's GetVelocityDensity.
 #include <algorithm>
@@ -11,7 +11,38 @@
 #include <cstdint>
 #include <vector>
 
-#include "qsel.cuh"
+#include <cstdint>
+
+// The reference's median selection (NBody::KDTree::MedianPos, KDTree.cxx:304-337) as the literal loop over (value, index) pairs: the
+// arrangement the library's kd-tree build reproduces on the device (csrc/ptree.cu: k_kd_big / k_kd_small), which
+// tests/test_gpu_tree.py compares with the compiled reference through vrgpu_tree_order and tests/test_hoare_model.py pins on the CPU.
+namespace emul_sel {
+static inline uint32_t median_index(uint32_t start, uint32_t end) { return start + (end - start - 1u) / 2u; }
+static inline void select_serial(double *val, uint32_t *idx, uint32_t k, uint32_t n)
+{
+    if (n == 0u) return;
+    int left = 0, right = (int)n - 1;
+    const int kk = (int)k;
+    while (left < right) {
+        const double x = val[kk];
+        double wv = val[right]; val[right] = val[kk]; val[kk] = wv;
+        uint32_t wi = idx[right]; idx[right] = idx[kk]; idx[kk] = wi;
+        int i = left - 1, j = right;
+        for (;;) {
+            while (i < j) if (val[++i] >= x) break;
+            while (i < j) if (val[--j] <= x) break;
+            wv = val[i]; val[i] = val[j]; val[j] = wv;
+            wi = idx[i]; idx[i] = idx[j]; idx[j] = wi;
+            if (j <= i) break;
+        }
+        val[j] = val[i]; idx[j] = idx[i];
+        val[i] = val[right]; idx[i] = idx[right];
+        val[right] = wv; idx[right] = wi;
+        if (i >= kk) right = i - 1;
+        if (i <= kk) left = i + 1;
+    }
+}
+} // namespace emul_sel
 #include "veldens.cuh"
 
 using namespace vrgpu::veldens;
@@ -39,8 +70,8 @@ void build(Tree &t, uint32_t nd)
     std::vector<double> val(e - s);
     std::vector<uint32_t> idx(e - s);
     for (uint32_t i = 0; i < e - s; i++) { idx[i] = t.perm[s + i]; val[i] = t.pos[3 * (size_t)idx[i] + d]; }
-    const uint32_t k = vrgpu::qsel::median_index(s, e);
-    vrgpu::qsel::select_serial(val.data(), idx.data(), k - s, e - s);
+    const uint32_t k = emul_sel::median_index(s, e);
+    emul_sel::select_serial(val.data(), idx.data(), k - s, e - s);
     for (uint32_t i = 0; i < e - s; i++) t.perm[s + i] = idx[i];
     const uint32_t l = (uint32_t)t.nstart.size();
     t.nleft[nd] = l;
