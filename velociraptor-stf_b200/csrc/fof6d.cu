@@ -508,6 +508,7 @@ struct Link6 {
     const uint32_t *chunk_cell;  // chunk -> cell
     uint32_t nchunks;
     unsigned long long *st;      // VRGPU_LINK6_STATS=1: counters (a measuring aid)
+    unsigned int *next_item;     // work counter: chunks are handed out in order, so that the warps in flight work on neighbouring cells
     uint32_t sparse_a, sparse_b; // a cell of at most sparse_a particles whose neighbour cells hold at most sparse_b each takes the sparse path
     double p6, p7, ip6, ip7;    // criterion predicate only (FOF6d: params[6], params[7] and their reciprocals)
 };
@@ -594,9 +595,15 @@ template <bool CRIT = false> __global__ void __launch_bounds__(L6_WARPS * 32) k_
     __shared__ double tq[L6_WARPS][6][32];
     __shared__ uint32_t tr[L6_WARPS][32];
     const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t nw = gridDim.x * L6_WARPS;
     const size_t n = L.ntot;
-    for (uint32_t item = blockIdx.x * L6_WARPS + w; item < L.nchunks; item += nw) {
+    // Chunks are taken from a counter, not by a fixed stride: the chunks in flight at any moment are then a contiguous window of
+    // cells (neighbours along x, the same rows of the same group), whose neighbour tiles overlap and stay in L2.  With a grid
+    // stride over eight waves of blocks every wave swept the whole array: 33 GB of DRAM traffic at 512^3 for 2.6 GB of columns.
+    for (;;) {
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(L.next_item, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= L.nchunks) break;
         const uint32_t A = L.chunk_cell[item];
         const uint32_t a0 = L.cell_start[A], a1 = L.cell_start[A + 1];
         const uint32_t i = a0 + ((item - L.chunk_start[A]) << 5) + lane;
@@ -853,6 +860,9 @@ static long long link6_back(vrgpu_ctx *ctx, const DeviceParticles &P, GroupSet &
         L.chunk_start = chunk_start.p; L.chunk_cell = chunk_cell.p; L.nchunks = nwork;
         static const int sparse_a = [] { const char *e = getenv("VRGPU_LINK6_SPARSE"); return e ? atoi(e) : (int)L6_SPARSE_A; }();
         L.sparse_a = (uint32_t)sparse_a;
+        DBuf<unsigned int> next_item(ctx, 1);
+        VR_CUDA(cudaMemsetAsync(next_item.p, 0, sizeof(unsigned int), ctx->stream));
+        L.next_item = next_item.p;
         static const bool link6_stats = [] { const char *e = getenv("VRGPU_LINK6_STATS"); return e && atoi(e) == 1; }();
         DBuf<unsigned long long> lst;
         if (link6_stats) { lst.alloc(ctx, 8); VR_CUDA(cudaMemsetAsync(lst.p, 0, 64, ctx->stream)); L.st = lst.p; }

@@ -217,6 +217,9 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
     DBuf<double> heap_d2(ctx, (size_t)batch * (nsearch + 1));
     DBuf<uint32_t> heap_id(ctx, (size_t)batch * (nsearch + 1)), nn(ctx, (size_t)batch * nsearch);
     V.heap_d2 = heap_d2.p; V.heap_id = heap_id.p; V.nn = nn.p;
+    DBuf<unsigned int> ovf(ctx, 1);
+    VR_CUDA(cudaMemsetAsync(ovf.p, 0, sizeof(unsigned int), ctx->stream));
+    V.overflow = ovf.p;
     for (uint32_t q0 = 0; q0 < nq; q0 += batch) {
         V.q0 = q0;
         V.q1 = (uint32_t)std::min<size_t>(nq, (size_t)q0 + batch);
@@ -224,6 +227,10 @@ void velocity_density_device(vrgpu_ctx *ctx, const DeviceParticles &P, const int
         { KScope k(ctx, "veldens.density"); VR_LAUNCH(ctx, k_vd_density, grid_for(approx ? n : V.q1 - V.q0, 128), 128, 0, V); }
     }
     VR_LAUNCH(ctx, k_vd_scatter, grid_for(n, T), T, 0, den.p, t.perm.p, t.slot_of.p, gs.idx.p, n, den_dev);
+    unsigned int hovf = 0;
+    VR_CUDA(cudaMemcpyAsync(&hovf, ovf.p, sizeof(hovf), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    VR_REQUIRE(hovf == 0, VRGPU_EUNSUPPORTED, "velocity density: the neighbour search ran out of stack (tree deeper than 47 levels)");
 }
 
 } // namespace vrgpu

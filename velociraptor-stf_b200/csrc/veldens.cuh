@@ -92,6 +92,7 @@ struct Params {
     const double *kernel;
     int kernres;
     double *den;                    // per tree position
+    unsigned int *overflow;         // set when a search would have needed more than STACK entries (null: not reported)
 };
 
 // ---- leaves ------------------------------------------------------------------------------------------------------------
@@ -214,8 +215,12 @@ VD_HD void search_from(const Params &P, const Heap &H, const double *q, uint32_t
         }
         const double dl = box_d2(P, l, q), dr = box_d2(P, l + 1u, q);
         // the nearer child is searched first: push the farther one first
-        if (dl <= dr) { if (sp < STACK - 1) { stack[sp++] = l + 1u; stack[sp++] = l; } }
-        else { if (sp < STACK - 1) { stack[sp++] = l; stack[sp++] = l + 1u; } }
+        if (sp >= STACK - 1) { // cannot happen for a median-split tree (32 levels): reported, never silently dropped
+            if (P.overflow) *P.overflow = 1u;
+            continue;
+        }
+        if (dl <= dr) { stack[sp++] = l + 1u; stack[sp++] = l; }
+        else { stack[sp++] = l; stack[sp++] = l + 1u; }
     }
 }
 

@@ -485,10 +485,17 @@ Int_t *VRGPU_NAME(FOFCriterion6DCore)(Particle *Partsubset, Int_t nsubset, Doubl
  * in STRUCDEN builds) from Options::Nsearch position neighbours and Options::Nvel velocity neighbours, per leaf of the kd-tree
  * with bucket Options::Bsize (iLocalVelDenApproxCalcFlag, the default) or per particle.  The library builds the tree the
  * routine would build for tree == NULL (the call of SearchSubSub, search.cxx:2646).  From a tree handed in by the caller
- * (search.cxx:232, :384: the FOF tree over the same particles, which are then in that tree's order) the body reads the leaf
+ * (search.cxx:232: the FOF tree over the same particles, which are then in that tree's order) the body reads the leaf
  * boundaries the way the reference itself does (FindLeafNode, localfield.cxx:772-781) and passes them on, so the per-leaf
- * search runs on the caller's leaves.  Not covered: the MPI import / export of neighbours (single task only) and the
- * baryon search variant that restricts neighbours by type (iBaryonSearch == 1 with PSTALL). */
+ * search runs on the caller's leaves.  The smoothing kernel and the periodicity are the ones the routine's own tree has
+ * (Epanechnikov table of 1000 entries, period = Options::p), which is also what the tree of search.cxx:232 has; a caller's
+ * tree with other settings -- the MPI branch's tree of search.cxx:383 is built with a table of 100 entries, the OpenMP one of
+ * :88 without a period -- is outside what this body reproduces (KDTree offers no way to ask: GetPeriod() dereferences a null
+ * pointer on an open tree, the kernel resolution is private).  Not covered either: the MPI import / export of neighbours (single task only), HALOONLYDEN builds (another reference routine) and
+ * the baryon search variant that restricts neighbours by type (iBaryonSearch == 1 with PSTALL). */
+#ifdef HALOONLYDEN
+#error "vrgpu_adaptor.cxx: HALOONLYDEN builds use GetVelocityDensityHaloOnlyDen, which the GPU path does not replace"
+#endif
 void VRGPU_NAME(GetVelocityDensity)(Options &opt, const Int_t nbodies, Particle *Part, KDTree *tree)
 {
     if (nbodies <= 0) return;
