@@ -79,6 +79,24 @@ def test_tree_order_is_the_references(gpu_ctx, oracle, n, scale, bucket):
     assert bad.size == 0, f"{bad.size} of {n} tree positions differ, first at {bad[:5]}"
 
 
+def test_tree_order_with_nodes_that_take_the_whole_gpu(gpu_ctx, oracle, monkeypatch):
+    """Nodes of at least 2^22 particles are arranged by the cooperative kernel (k_kd_huge: every SM on one node, csrc/ptree.cu; the
+    threshold is lowered to 2^19 here): two such groups and a small one in one call -- root and first children of the big one,
+    the root of the second -- against the oracle's BuildNodes position for position."""
+    import vrgpu
+    monkeypatch.setenv("VRGPU_KD_HUGE", str(1 << 19))
+    rng = np.random.default_rng(10)
+    sizes = [1_300_000, 5000, 600_000]
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    pos = np.concatenate([_quantised(s, rng, 0.05) + 5.0 * k for k, s in enumerate(sizes)])
+    parts = vrgpu.particles_from_arrays(pos)
+    got = gpu_ctx.tree_order(parts, off, np.arange(len(pos)), bucket=8)
+    for g, s in enumerate(sizes):
+        want, _ = oracle.tree_order(pos[off[g]:off[g + 1]], 8)
+        bad = np.flatnonzero(got[off[g]:off[g + 1]] != want)
+        assert bad.size == 0, f"group {g} ({s} members): {bad.size} tree positions differ, first at {bad[:5]}"
+
+
 def test_tree_order_many_groups_any_order(gpu_ctx, oracle):
     """Several trees in the same launches, group sizes in no particular order, members handed over through an index list."""
     import vrgpu

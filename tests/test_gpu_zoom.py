@@ -51,6 +51,41 @@ def test_single_halo_search_full_set(gpu_ctx, oracle, fofbgtype, pp):
 
 
 
+def test_single_halo_of_a_million_members_against_the_compiled_reference(gpu_ctx, ref, oracle):
+    """BASELINE configs[4] at a size the CPU side still finishes in a minute: 1.2e6 particles in ONE 3D group (964 186 of them stay in
+    the main 6D group), the stock settings.  3DFOF + 6DFOF: canonical membership and the rewritten positions / velocities bit for bit
+    against the reference's own SearchFullSet -- the dispersion of the million-member group goes through the many-window evaluation
+    (csrc/seqsum.h) and every bit of it enters the scaled coordinates.  Unbinding (kd-tree potentials of a 10^6-member tree, one-pass
+    removal): against the oracle chained from the reference's 6DFOF output, bound sets identical up to the reported marginal
+    particles (the reference itself adds quirk Q10 on the small subclumps, pinned in tests/test_gpu_dropin.py)."""
+    import vrgpu
+    import vroracle
+    n = 1_200_000
+    d, ell = _inputs(n)
+    param1 = (ell * ell) * (0.2 * 0.2) * (1.0 * 1.0)
+    o = vroracle.default_opts(period=vrsynth.BOX, ellxscale=ell, fofbgtype=3, bound_halos=0, omp_fof=0)
+    want6 = ref.search_full_set(d["pos"], d["vel"], d["mass"], d["pid"], o)
+    cw6, sizes6 = vrsynth.canonical_groups(want6["pfof"], d["pid"])
+    assert sizes6[0] > 0.75 * n
+    parts = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"])
+    so = vrgpu.search_opts(vrsynth.BOX, param1, halo_min_size=20, fofbgtype=3, bound_halos=0)
+    got6, ng6 = gpu_ctx.search_full_set(parts, so)
+    assert ng6 == len(sizes6) == want6["ngroups"] and np.array_equal(got6, cw6)
+    assert np.array_equal(parts["pos"], want6["pos"]) and np.array_equal(parts["vel"], want6["vel"])
+    uo = vroracle.unbind_opts_from(vroracle.default_opts(period=vrsynth.BOX, ellxscale=ell, fofbgtype=3, bound_halos=1), 150, sortflag_mode=0)
+    want = oracle.unbind(want6["pos"], want6["vel"], d["mass"], cw6, len(sizes6), uo, d["pid"], 1e-6)
+    parts = vrgpu.particles_from_arrays(d["pos"], d["vel"], d["mass"], d["pid"])
+    so = vrgpu.search_opts(vrsynth.BOX, param1, halo_min_size=20, fofbgtype=3, bound_halos=1, unbind=vrgpu.default_unbind_opts(pp_threshold=150))
+    got, ng = gpu_ctx.search_full_set(parts, so)
+    st = gpu_ctx.stats()
+    ndiff = int(np.count_nonzero((got > 0) != (want["pfof"] > 0)))
+    print(f"single halo of {n}: {ng6} 6D groups (largest {sizes6[0]}), {ng} bound groups (oracle {want['ngroups']}), bound flags differing {ndiff}, "
+          f"marginal gpu {st['n_marginal']} / oracle {want['n_marginal']}, tree interactions {st['n_tree_interactions']}")
+    assert ndiff <= want["n_marginal"] + st["n_marginal"]
+    if ndiff == 0:
+        assert ng == want["ngroups"] and np.array_equal(got, want["pfof"])
+
+
 @pytest.mark.parametrize("pattern", ["zero_mean", "zero_axis", "ties", "equal_mass_drift", "mixed_mass"])
 @pytest.mark.parametrize("multi_min", [0, 8192])
 def test_big_group_dispersion_is_bit_exact(gpu_ctx, oracle, pattern, multi_min, monkeypatch):

@@ -23,6 +23,8 @@
 #include "seqblock.cuh"
 #include "ufhash.cuh"
 
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -182,59 +184,15 @@ __device__ __forceinline__ void kd_swap_rec(KdRec *rec, uint32_t a, uint32_t b)
 }
 __device__ __forceinline__ double kd_coord(const KdRec *rec, uint32_t p, int d) { return reinterpret_cast<const double *>(rec + p)[d]; }
 
-// One CTA arranges one node of more than KD_SMALL particles in global memory.  A, B: scratch of nL entries each (a node uses
-// the entries of its own position range).  No __restrict__ / __ldg on rec: the CTA re-reads what it wrote.
 constexpr int KB_NT = 1024, KB_ITEMS = 4, KB_TILE = KB_NT * KB_ITEMS;
-__global__ void __launch_bounds__(KB_NT) k_kd_big(KdRec *rec, const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend,
-                                                  const uint32_t *__restrict__ list, uint32_t *A, uint32_t *B)
+// One CTA runs the reference's selection (MedianPos, KDTree.cxx:304-337) on the positions [lo, hi) of a node in global memory until
+// position k holds the median: the body of k_kd_big, also the tail of k_kd_huge once the range is too short for the whole GPU.
+__device__ void kd_cta_select(KdRec *rec, const uint32_t k, const int d, uint32_t lo, uint32_t hi, uint32_t *An, uint32_t *Bn)
 {
-    __shared__ double s_red[6][KB_NT / 32];
     __shared__ uint32_t s_w[KB_NT / 32];
     __shared__ uint32_t s_tot, s_first, s_lo, s_hi;
     __shared__ double s_x;
-    __shared__ int s_dim;
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t nd = list[blockIdx.x];
-    const uint32_t s = nstart[nd], e = nend[nd];
-    // ---- split dimension: largest spread, the first dimension wins a tie (KDTree.cxx:463-503) ----
-    {
-        double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
-        for (uint32_t p = s + tid; p < e; p += KB_NT) {
-            const double2 a = *reinterpret_cast<const double2 *>(rec + p);
-            const double c = rec[p].z;
-            mn[0] = fmin(mn[0], a.x); mx[0] = fmax(mx[0], a.x);
-            mn[1] = fmin(mn[1], a.y); mx[1] = fmax(mx[1], a.y);
-            mn[2] = fmin(mn[2], c); mx[2] = fmax(mx[2], c);
-        }
-        for (int k = 0; k < 3; k++) {
-            for (int o = 16; o; o >>= 1) {
-                mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
-                mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
-            }
-            if (lane == 0) { s_red[k][warp] = mn[k]; s_red[3 + k][warp] = mx[k]; }
-        }
-        __syncthreads();
-        if (tid == 0) {
-            double lo3[3], hi3[3];
-            for (int k = 0; k < 3; k++) {
-                lo3[k] = s_red[k][0]; hi3[k] = s_red[3 + k][0];
-                for (int w = 1; w < KB_NT / 32; w++) { lo3[k] = fmin(lo3[k], s_red[k][w]); hi3[k] = fmax(hi3[k], s_red[3 + k][w]); }
-            }
-            int d = 0;
-            double best = __dsub_rn(hi3[0], lo3[0]);
-            for (int k = 1; k < 3; k++) {
-                const double sp = __dsub_rn(hi3[k], lo3[k]);
-                if (sp > best) { best = sp; d = k; }
-            }
-            s_dim = d;
-            s_lo = s; s_hi = e;
-        }
-        __syncthreads();
-    }
-    const int d = s_dim;
-    const uint32_t k = s + (e - s - 1) / 2;
-    uint32_t lo = s, hi = e;
-    uint32_t *An = A + s, *Bn = B + s;
     while (lo + 1 < hi) {
         if (tid == 0) {
             s_x = kd_coord(rec, k, d);
@@ -334,6 +292,261 @@ __global__ void __launch_bounds__(KB_NT) k_kd_big(KdRec *rec, const uint32_t *__
         }
         __syncthreads();
         lo = s_lo; hi = s_hi;
+    }
+}
+
+// One CTA arranges one node of more than KD_SMALL particles in global memory.  A, B: scratch of nL entries each (a node uses
+// the entries of its own position range).  No __restrict__ / __ldg on rec: the CTA re-reads what it wrote.
+__global__ void __launch_bounds__(KB_NT) k_kd_big(KdRec *rec, const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend,
+                                                  const uint32_t *__restrict__ list, uint32_t *A, uint32_t *B, uint32_t skip_from)
+{
+    __shared__ double s_red[6][KB_NT / 32];
+    __shared__ int s_dim;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t nd = list[blockIdx.x];
+    const uint32_t s = nstart[nd], e = nend[nd];
+    if (e - s >= skip_from) return; // arranged by k_kd_huge
+    // ---- split dimension: largest spread, the first dimension wins a tie (KDTree.cxx:463-503) ----
+    {
+        double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+        for (uint32_t p = s + tid; p < e; p += KB_NT) {
+            const double2 a = *reinterpret_cast<const double2 *>(rec + p);
+            const double c = rec[p].z;
+            mn[0] = fmin(mn[0], a.x); mx[0] = fmax(mx[0], a.x);
+            mn[1] = fmin(mn[1], a.y); mx[1] = fmax(mx[1], a.y);
+            mn[2] = fmin(mn[2], c); mx[2] = fmax(mx[2], c);
+        }
+        for (int k = 0; k < 3; k++) {
+            for (int o = 16; o; o >>= 1) {
+                mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+                mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+            }
+            if (lane == 0) { s_red[k][warp] = mn[k]; s_red[3 + k][warp] = mx[k]; }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double lo3[3], hi3[3];
+            for (int k = 0; k < 3; k++) {
+                lo3[k] = s_red[k][0]; hi3[k] = s_red[3 + k][0];
+                for (int w = 1; w < KB_NT / 32; w++) { lo3[k] = fmin(lo3[k], s_red[k][w]); hi3[k] = fmax(hi3[k], s_red[3 + k][w]); }
+            }
+            int d = 0;
+            double best = __dsub_rn(hi3[0], lo3[0]);
+            for (int k = 1; k < 3; k++) {
+                const double sp = __dsub_rn(hi3[k], lo3[k]);
+                if (sp > best) { best = sp; d = k; }
+            }
+            s_dim = d;
+        }
+        __syncthreads();
+    }
+    const int d = s_dim;
+    kd_cta_select(rec, s + (e - s - 1) / 2, d, s, e, A + s, B + s);
+}
+
+// ---- nodes of at least KD_HUGE particles: the whole GPU on one node ----------------------------------------------------------
+// The same iteration as k_kd_big, with the scans of [lo, top) cut into one contiguous slice per CTA and a grid barrier between
+// its phases (cooperative launch): count the two kinds of stops per slice, prefix over the slices, write the lists A / B, find M
+// (every CTA for itself), swap the M pairs (all threads of the grid), place the pivot (one thread).  A single CTA moves ~0.2 G
+// particles per second through its selections, so the root of a 5e7-member group alone took 235 ms of the 470 ms build; with
+// 148 CTAs the top levels cost what their memory traffic costs.  Everything another CTA wrote is read with ld.cg (L1 is not
+// coherent between SMs).
+constexpr uint32_t KD_HUGE = 1u << 22;      // default: nodes of at least 4 Mi particles (VRGPU_KD_HUGE=<particles>, 0 = never)
+constexpr uint32_t KD_HUGE_TAIL = 1u << 16; // ranges of at most this length are finished by one CTA
+struct KdHugeState {
+    unsigned long long mn[3], mx[3];   // ordered images of the bounding box (pt_ord)
+    unsigned long long cnt[256];       // per CTA: stops of kind A | kind B << 32 in its slice
+    double x;
+    uint32_t lo, hi;
+};
+__device__ __forceinline__ double kd_coord_cg(const KdRec *rec, uint32_t p, int d) { return __ldcg(reinterpret_cast<const double *>(rec + p) + d); }
+__device__ __forceinline__ void kd_swap_rec_cg(KdRec *rec, uint32_t a, uint32_t b)
+{
+    uint4 *pa = reinterpret_cast<uint4 *>(rec + a), *pb = reinterpret_cast<uint4 *>(rec + b);
+    const uint4 a0 = __ldcg(pa), a1 = __ldcg(pa + 1), b0 = __ldcg(pb), b1 = __ldcg(pb + 1);
+    pa[0] = b0; pa[1] = b1; pb[0] = a0; pb[1] = a1;
+}
+__global__ void __launch_bounds__(KB_NT) k_kd_huge(KdRec *rec, const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend,
+                                                   const uint32_t *__restrict__ list, uint32_t nlist, uint32_t *A, uint32_t *B,
+                                                   KdHugeState *st, uint32_t huge_min)
+{
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ double s_red[6][KB_NT / 32];
+    __shared__ uint32_t s_w[KB_NT / 32];
+    __shared__ uint32_t s_tot, s_first;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t G = gridDim.x, c = blockIdx.x;
+    volatile KdHugeState *vst = st;
+    for (uint32_t li = 0; li < nlist; li++) {
+        const uint32_t nd = list[li];
+        const uint32_t s = nstart[nd], e = nend[nd];
+        if (e - s < huge_min) continue; // (the same decision in every CTA)
+        // ---- split dimension: largest spread, the first dimension wins a tie (KDTree.cxx:463-503) ----
+        if (c == 0 && tid < 3) { st->mn[tid] = ~0ull; st->mx[tid] = 0ull; }
+        grid.sync();
+        {
+            double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+            for (uint32_t p = s + c * KB_NT + tid; p < e; p += G * KB_NT) {
+                const double a = kd_coord_cg(rec, p, 0), b = kd_coord_cg(rec, p, 1), cc = kd_coord_cg(rec, p, 2);
+                mn[0] = fmin(mn[0], a); mx[0] = fmax(mx[0], a);
+                mn[1] = fmin(mn[1], b); mx[1] = fmax(mx[1], b);
+                mn[2] = fmin(mn[2], cc); mx[2] = fmax(mx[2], cc);
+            }
+            for (int k = 0; k < 3; k++) {
+                for (int o = 16; o; o >>= 1) {
+                    mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+                    mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+                }
+                if (lane == 0) { s_red[k][warp] = mn[k]; s_red[3 + k][warp] = mx[k]; }
+            }
+            __syncthreads();
+            if (tid < 3) {
+                double lo1 = s_red[tid][0], hi1 = s_red[3 + tid][0];
+                for (int w = 1; w < KB_NT / 32; w++) { lo1 = fmin(lo1, s_red[tid][w]); hi1 = fmax(hi1, s_red[3 + tid][w]); }
+                atomicMin(&st->mn[tid], pt_ord(lo1));
+                atomicMax(&st->mx[tid], pt_ord(hi1));
+            }
+        }
+        grid.sync();
+        int d = 0;
+        {
+            double best = __dsub_rn(pt_unord(vst->mx[0]), pt_unord(vst->mn[0]));
+            for (int k = 1; k < 3; k++) {
+                const double sp = __dsub_rn(pt_unord(vst->mx[k]), pt_unord(vst->mn[k]));
+                if (sp > best) { best = sp; d = k; }
+            }
+        }
+        const uint32_t k = s + (e - s - 1) / 2;
+        uint32_t lo = s, hi = e;
+        uint32_t *An = A + s, *Bn = B + s;
+        // the pivot of an iteration is taken (and parked at the end of the range) by the thread that placed the previous one
+        if (c == 0 && tid == 0) {
+            st->x = kd_coord_cg(rec, k, d);
+            if (k != hi - 1) kd_swap_rec_cg(rec, k, hi - 1);
+        }
+        grid.sync();
+        while (lo + 1 < hi && hi - lo > KD_HUGE_TAIL) {
+            const double x = vst->x;
+            const uint32_t top = hi - 1; // the scans cover [lo, top)
+            // this CTA's slice: whole tiles, contiguous, in the order of the CTA index
+            const uint32_t ntiles = (top - lo + KB_TILE - 1) / KB_TILE;
+            const uint32_t tper = (ntiles + G - 1) / G;
+            const uint32_t t0 = min(ntiles, c * tper), t1 = min(ntiles, t0 + tper);
+            const uint32_t my0 = lo + t0 * KB_TILE, my1 = min(top, lo + t1 * KB_TILE);
+            // ---- phase 1: stops in my slice ----
+            {
+                uint32_t ca = 0, cb = 0;
+                for (uint32_t p = my0 + tid; p < my1; p += KB_NT) {
+                    const double v = kd_coord_cg(rec, p, d);
+                    ca += v >= x ? 1u : 0u;
+                    cb += v <= x ? 1u : 0u;
+                }
+                for (int o = 16; o; o >>= 1) { ca += __shfl_xor_sync(0xffffffffu, ca, o); cb += __shfl_xor_sync(0xffffffffu, cb, o); }
+                if (lane == 0) { s_w[warp] = ca; s_red[0][warp] = (double)cb; }
+                __syncthreads();
+                if (tid == 0) {
+                    unsigned long long ta = 0, tb = 0;
+                    for (int w = 0; w < KB_NT / 32; w++) { ta += s_w[w]; tb += (unsigned long long)s_red[0][w]; }
+                    st->cnt[c] = ta | (tb << 32);
+                }
+                __syncthreads();
+            }
+            grid.sync();
+            // ---- prefix over the slices ----
+            uint32_t nA = 0, nB = 0, baseA = 0, baseB = 0;
+            for (uint32_t cc = 0; cc < G; cc++) {
+                const unsigned long long v = vst->cnt[cc];
+                if (cc == c) { baseA = nA; baseB = nB; }
+                nA += (uint32_t)(v & 0xffffffffull); nB += (uint32_t)(v >> 32);
+            }
+            // ---- phase 2: the two lists (both ascending; B is read from its end) ----
+            {
+                uint32_t wa = baseA, wb = baseB;
+                for (uint32_t base = my0; base < my1; base += KB_TILE) {
+                    const uint32_t p0 = base + tid * KB_ITEMS;
+                    unsigned fa = 0, fb = 0;
+#pragma unroll
+                    for (int j = 0; j < KB_ITEMS; j++)
+                        if (p0 + j < my1) { const double v = kd_coord_cg(rec, p0 + j, d); fa |= (v >= x ? 1u : 0u) << j; fb |= (v <= x ? 1u : 0u) << j; }
+                    const uint32_t mine = (uint32_t)__popc(fa) | ((uint32_t)__popc(fb) << 16);
+                    uint32_t incl = mine;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= (unsigned)o) incl += y;
+                    }
+                    if (lane == 31) s_w[warp] = incl;
+                    __syncthreads();
+                    if (warp == 0) {
+                        const uint32_t wv = s_w[lane];
+                        uint32_t wi = wv;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const uint32_t y = __shfl_up_sync(0xffffffffu, wi, o);
+                            if (lane >= (unsigned)o) wi += y;
+                        }
+                        s_w[lane] = wi - wv;
+                        if (lane == 31) s_tot = wi;
+                    }
+                    __syncthreads();
+                    const uint32_t excl = s_w[warp] + incl - mine, tot = s_tot;
+                    uint32_t ea = wa + (excl & 0xffffu), eb = wb + (excl >> 16);
+#pragma unroll
+                    for (int j = 0; j < KB_ITEMS; j++) {
+                        if ((fa >> j) & 1u) An[ea++] = p0 + j;
+                        if ((fb >> j) & 1u) Bn[eb++] = p0 + j;
+                    }
+                    wa += tot & 0xffffu; wb += tot >> 16;
+                    __syncthreads(); // s_w / s_tot are rewritten by the next tile
+                }
+            }
+            grid.sync();
+            // ---- M = first m with !(A[m] < B[nB-1-m]): every CTA searches for itself ----
+            const uint32_t mm = nA < nB ? nA : nB;
+            uint32_t a = 0, b = mm;
+            while (a < b) {
+                const uint32_t step = (b - a + KB_NT - 1) / KB_NT;
+                const uint32_t m = a + tid * step;
+                const bool fail = m < b && !(__ldcg(An + m) < __ldcg(Bn + (nB - 1 - m)));
+                const unsigned bal = __ballot_sync(0xffffffffu, fail);
+                if (lane == 0) s_w[warp] = bal ? warp * 32 + (uint32_t)__ffs(bal) - 1u : (uint32_t)KB_NT;
+                __syncthreads();
+                if (warp == 0) {
+                    const unsigned has = __ballot_sync(0xffffffffu, s_w[lane] != (uint32_t)KB_NT);
+                    if (lane == 0) s_first = has ? s_w[__ffs(has) - 1] : (uint32_t)KB_NT;
+                }
+                __syncthreads();
+                const uint32_t first = s_first;
+                if (first == (uint32_t)KB_NT) a = a + ((b - a - 1) / step) * step + 1;
+                else { b = a + first * step; if (first) a = a + (first - 1) * step + 1; }
+                __syncthreads();
+            }
+            const uint32_t M = a;
+            for (uint32_t m = c * KB_NT + tid; m < M; m += G * KB_NT) kd_swap_rec_cg(rec, __ldcg(An + m), __ldcg(Bn + (nB - 1 - m)));
+            grid.sync();
+            if (c == 0 && tid == 0) {
+                uint32_t istar;
+                if (M < nA && (M == 0 || __ldcg(An + M) < __ldcg(Bn + (nB - M)))) istar = __ldcg(An + M);
+                else if (M > 0) istar = __ldcg(Bn + (nB - M));
+                else istar = top;
+                if (istar != top) kd_swap_rec_cg(rec, istar, top);
+                uint32_t nlo = lo, nhi = hi;
+                if (istar >= k) nhi = istar;
+                if (istar <= k) nlo = istar + 1;
+                st->lo = nlo; st->hi = nhi;
+                if (nlo + 1 < nhi && nhi - nlo > KD_HUGE_TAIL) { // the next cooperative iteration's pivot
+                    st->x = kd_coord_cg(rec, k, d);
+                    if (k != nhi - 1) kd_swap_rec_cg(rec, k, nhi - 1);
+                }
+            }
+            grid.sync();
+            lo = vst->lo; hi = vst->hi;
+        }
+        // the rest of the selection is too short to be worth a grid barrier per phase: one CTA finishes it (plain loads are safe: this
+        // kernel has only ever read rec with ld.cg, so no stale line can sit in this SM's L1)
+        if (c == 0 && lo + 1 < hi) kd_cta_select(rec, k, d, lo, hi, An, Bn);
+        grid.sync(); // the next node's box reset must not overtake readers of this node's state; the tail's writes are visible
     }
 }
 
@@ -820,9 +1033,36 @@ bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_thres
         VR_LAUNCH(ctx, k_kd_init_rec, grid_for(nL, T), T, 0, gs.x.p, gs.y.p, gs.z.p, slot_of.p, nL, rec);
         if (big_off.back() > 0) {
             DBuf<uint32_t> A(ctx, nL), B(ctx, nL);
+            // nodes of at least KD_HUGE particles take the whole GPU, one after the other (k_kd_huge, cooperative launch); a level can
+            // only hold such a node while nL >> level reaches that size.  VRGPU_KD_HUGE=<particles> moves the threshold, 0 switches
+            // the kernel off (every node to k_kd_big).
+            uint32_t huge_min = KD_HUGE;
+            if (const char *e = getenv("VRGPU_KD_HUGE")) huge_min = (uint32_t)std::max(0ll, atoll(e));
+            if (huge_min == 0) huge_min = 0xffffffffu;
+            huge_min = std::max(huge_min, 4u * KD_HUGE_TAIL);
+            DBuf<KdHugeState> hst;
+            int hgrid = 0;
+            if (nL >= huge_min) {
+                int per_sm = 0;
+                VR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_kd_huge, KB_NT, 0));
+                hgrid = std::min(256, ctx->sm_count * std::max(per_sm, 0));
+                if (hgrid >= 2) hst.alloc(ctx, 1);
+            }
             for (size_t l = 0; l + 1 < big_off.size(); l++) {
                 const uint32_t nb = big_off[l + 1] - big_off[l];
-                if (nb) VR_LAUNCH(ctx, k_kd_big, nb, KB_NT, 0, rec, nstart.p, nend.p, big_list.p + big_off[l], A.p, B.p);
+                if (!nb) continue;
+                const bool huge = hgrid >= 2 && (nL >> std::min<size_t>(l, 31)) >= huge_min;
+                if (huge) {
+                    KdRec *a_rec = rec;
+                    const uint32_t *a_ns = nstart.p, *a_ne = nend.p, *a_list = big_list.p + big_off[l];
+                    uint32_t a_n = nb, *a_A = A.p, *a_B = B.p;
+                    KdHugeState *a_st = hst.p;
+                    uint32_t a_min = huge_min;
+                    void *args[] = {&a_rec, &a_ns, &a_ne, &a_list, &a_n, &a_A, &a_B, &a_st, &a_min};
+                    VR_CUDA(cudaLaunchCooperativeKernel((const void *)k_kd_huge, dim3((unsigned)hgrid), dim3(KB_NT), args, 0, ctx->stream));
+                    ctx->stats.kernel_launches++;
+                }
+                VR_LAUNCH(ctx, k_kd_big, nb, KB_NT, 0, rec, nstart.p, nend.p, big_list.p + big_off[l], A.p, B.p, huge ? huge_min : 0xffffffffu);
             }
         }
         if (nsub) {
