@@ -79,12 +79,18 @@ def test_tree_order_is_the_references(gpu_ctx, oracle, n, scale, bucket):
     assert bad.size == 0, f"{bad.size} of {n} tree positions differ, first at {bad[:5]}"
 
 
-def test_tree_order_with_nodes_that_take_the_whole_gpu(gpu_ctx, oracle, monkeypatch):
+@pytest.mark.parametrize("tier", ["grid", "cluster"])
+def test_tree_order_with_nodes_that_take_the_whole_gpu(gpu_ctx, oracle, monkeypatch, tier):
     """Nodes of at least 2^22 particles are arranged by the cooperative kernel (k_kd_huge: every SM on one node, csrc/ptree.cu; the
     threshold is lowered to 2^19 here): two such groups and a small one in one call -- root and first children of the big one,
     the root of the second -- against the oracle's BuildNodes position for position."""
     import vrgpu
-    monkeypatch.setenv("VRGPU_KD_HUGE", str(1 << 19))
+    if tier == "grid":
+        monkeypatch.setenv("VRGPU_KD_HUGE", str(1 << 19))
+        monkeypatch.setenv("VRGPU_KD_CLUSTER", "0")
+    else:                                   # the middle tier: a cluster of 8 CTAs per node from 2^18 particles (default 2^19)
+        monkeypatch.delenv("VRGPU_KD_HUGE", raising=False)
+        monkeypatch.setenv("VRGPU_KD_CLUSTER", str(1 << 18))
     rng = np.random.default_rng(10)
     sizes = [1_300_000, 5000, 600_000]
     off = np.concatenate([[0], np.cumsum(sizes)])

@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(KB_NT) k_kd_big(KdRec *rec, const uint32_t *__
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t nd = list[blockIdx.x];
     const uint32_t s = nstart[nd], e = nend[nd];
-    if (e - s >= skip_from) return; // arranged by k_kd_huge
+    if (e - s >= skip_from) return; // arranged by k_kd_huge (whole grid or cluster)
     // ---- split dimension: largest spread, the first dimension wins a tie (KDTree.cxx:463-503) ----
     {
         double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
@@ -353,6 +353,7 @@ __global__ void __launch_bounds__(KB_NT) k_kd_big(KdRec *rec, const uint32_t *__
 // coherent between SMs).
 constexpr uint32_t KD_HUGE = 1u << 22;      // default: nodes of at least 4 Mi particles (VRGPU_KD_HUGE=<particles>, 0 = never)
 constexpr uint32_t KD_HUGE_TAIL = 1u << 16; // ranges of at most this length are finished by one CTA
+constexpr uint32_t KD_CLUSTER_MIN = 1u << 18, KD_CLUSTER_CTAS = 8; // the middle tier: a cluster of 8 CTAs per node of at least 256 Ki particles
 struct KdHugeState {
     unsigned long long mn[3], mx[3];   // ordered images of the bounding box (pt_ord)
     unsigned long long cnt[256];       // per CTA: stops of kind A | kind B << 32 in its slice
@@ -366,22 +367,40 @@ __device__ __forceinline__ void kd_swap_rec_cg(KdRec *rec, uint32_t a, uint32_t 
     const uint4 a0 = __ldcg(pa), a1 = __ldcg(pa + 1), b0 = __ldcg(pb), b1 = __ldcg(pb + 1);
     pa[0] = b0; pa[1] = b1; pb[0] = a0; pb[1] = a1;
 }
+// CLUSTER = false: the whole grid works through the nodes of the list one after the other (cooperative launch, grid barrier).
+// CLUSTER = true: one thread-block cluster per list entry, all of them at once (hardware cluster barrier): the middle tier, nodes of
+// at least min_size and less than max_size particles.
+template <bool CLUSTER> struct KdSync;
+template <> struct KdSync<false> {
+    cooperative_groups::grid_group g = cooperative_groups::this_grid();
+    __device__ void sync() { g.sync(); }
+    __device__ uint32_t size() const { return gridDim.x; }
+    __device__ uint32_t rank() const { return blockIdx.x; }
+};
+template <> struct KdSync<true> {
+    cooperative_groups::cluster_group g = cooperative_groups::this_cluster();
+    __device__ void sync() { g.sync(); }
+    __device__ uint32_t size() const { return g.num_blocks(); }
+    __device__ uint32_t rank() const { return g.block_rank(); }
+};
+template <bool CLUSTER>
 __global__ void __launch_bounds__(KB_NT) k_kd_huge(KdRec *rec, const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ nend,
                                                    const uint32_t *__restrict__ list, uint32_t nlist, uint32_t *A, uint32_t *B,
-                                                   KdHugeState *st, uint32_t huge_min)
+                                                   KdHugeState *st_all, uint32_t min_size, uint32_t max_size)
 {
-    namespace cg = cooperative_groups;
-    cg::grid_group grid = cg::this_grid();
+    KdSync<CLUSTER> grid;
     __shared__ double s_red[6][KB_NT / 32];
     __shared__ uint32_t s_w[KB_NT / 32];
     __shared__ uint32_t s_tot, s_first;
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t G = gridDim.x, c = blockIdx.x;
+    const uint32_t G = grid.size(), c = grid.rank();
+    KdHugeState *st = CLUSTER ? st_all + blockIdx.x / G : st_all;
     volatile KdHugeState *vst = st;
-    for (uint32_t li = 0; li < nlist; li++) {
+    const uint32_t li0 = CLUSTER ? blockIdx.x / G : 0u, li1 = CLUSTER ? li0 + 1u : nlist;
+    for (uint32_t li = li0; li < li1; li++) {
         const uint32_t nd = list[li];
         const uint32_t s = nstart[nd], e = nend[nd];
-        if (e - s < huge_min) continue; // (the same decision in every CTA)
+        if (e - s < min_size || e - s >= max_size) continue; // (the same decision in every CTA of the grid / cluster)
         // ---- split dimension: largest spread, the first dimension wins a tie (KDTree.cxx:463-503) ----
         if (c == 0 && tid < 3) { st->mn[tid] = ~0ull; st->mx[tid] = 0ull; }
         grid.sync();
@@ -717,11 +736,16 @@ __global__ void __launch_bounds__(SQ_NT) k_pt_big_sums(PtNodes N, const uint32_t
 {
     __shared__ SeqShared sh;
     const uint32_t nd = list[blockIdx.x >> 2], comp = blockIdx.x & 3u;
-    const uint32_t s = N.start[nd];
-    const unsigned long long n = N.end[nd] - s;
+    // The node's sum over its particles in order is its left child's sum carried on over the right child's particles: the same
+    // sequence of roundings, half the elements.  The levels run bottom-up (one launch each), so the left child -- a big node of the
+    // level below, or the root of a shared-memory subtree -- is final.
+    const uint32_t lc = N.left[nd];
+    const uint32_t s = N.start[lc + 1];
+    const unsigned long long n = N.end[lc + 1] - s;
+    const double s0 = (comp == 0 ? N.sx : (comp == 1 ? N.sy : (comp == 2 ? N.sz : N.sm)))[lc];
     double r;
-    if (comp == 3) r = block_seqsum(TermMass{tm + s}, n, 0.0, sh);
-    else r = block_seqsum(TermMomentum{(comp == 0 ? tx : (comp == 1 ? ty : tz)) + s, tm + s}, n, 0.0, sh);
+    if (comp == 3) r = block_seqsum(TermMass{tm + s}, n, s0, sh);
+    else r = block_seqsum(TermMomentum{(comp == 0 ? tx : (comp == 1 ? ty : tz)) + s, tm + s}, n, s0, sh);
     if (threadIdx.x == 0) (comp == 0 ? N.sx : (comp == 1 ? N.sy : (comp == 2 ? N.sz : N.sm)))[nd] = r;
 }
 
@@ -1044,25 +1068,51 @@ bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_thres
             int hgrid = 0;
             if (nL >= huge_min) {
                 int per_sm = 0;
-                VR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_kd_huge, KB_NT, 0));
+                VR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_kd_huge<false>, KB_NT, 0));
                 hgrid = std::min(256, ctx->sm_count * std::max(per_sm, 0));
                 if (hgrid >= 2) hst.alloc(ctx, 1);
             }
+            // the middle tier: nodes from KD_CLUSTER_MIN particles up to the whole-GPU threshold get a cluster of 8 CTAs each, all nodes
+            // of a level at once (VRGPU_KD_CLUSTER=<particles>, 0 = off)
+            uint32_t cl_min = KD_CLUSTER_MIN;
+            if (const char *e = getenv("VRGPU_KD_CLUSTER")) cl_min = (uint32_t)std::max(0ll, atoll(e));
+            if (cl_min == 0) cl_min = 0xffffffffu;
+            cl_min = std::max(cl_min, 4u * KD_HUGE_TAIL);
+            const uint32_t cl_max = hgrid >= 2 ? huge_min : 0xffffffffu;
+            DBuf<KdHugeState> cst;
             for (size_t l = 0; l + 1 < big_off.size(); l++) {
                 const uint32_t nb = big_off[l + 1] - big_off[l];
                 if (!nb) continue;
-                const bool huge = hgrid >= 2 && (nL >> std::min<size_t>(l, 31)) >= huge_min;
+                const uint32_t level_max = nL >> std::min<size_t>(l, 31);   // no node of this level is larger
+                const bool huge = hgrid >= 2 && level_max >= huge_min;
+                const bool clus = level_max >= cl_min && cl_min < cl_max;
                 if (huge) {
                     KdRec *a_rec = rec;
                     const uint32_t *a_ns = nstart.p, *a_ne = nend.p, *a_list = big_list.p + big_off[l];
                     uint32_t a_n = nb, *a_A = A.p, *a_B = B.p;
                     KdHugeState *a_st = hst.p;
-                    uint32_t a_min = huge_min;
-                    void *args[] = {&a_rec, &a_ns, &a_ne, &a_list, &a_n, &a_A, &a_B, &a_st, &a_min};
-                    VR_CUDA(cudaLaunchCooperativeKernel((const void *)k_kd_huge, dim3((unsigned)hgrid), dim3(KB_NT), args, 0, ctx->stream));
+                    uint32_t a_min = huge_min, a_max = 0xffffffffu;
+                    void *args[] = {&a_rec, &a_ns, &a_ne, &a_list, &a_n, &a_A, &a_B, &a_st, &a_min, &a_max};
+                    VR_CUDA(cudaLaunchCooperativeKernel((const void *)k_kd_huge<false>, dim3((unsigned)hgrid), dim3(KB_NT), args, 0, ctx->stream));
                     ctx->stats.kernel_launches++;
                 }
-                VR_LAUNCH(ctx, k_kd_big, nb, KB_NT, 0, rec, nstart.p, nend.p, big_list.p + big_off[l], A.p, B.p, huge ? huge_min : 0xffffffffu);
+                if (clus) {
+                    if (cst.n < nb) cst.alloc(ctx, nb);
+                    cudaLaunchConfig_t cfg = {};
+                    cfg.gridDim = dim3(nb * KD_CLUSTER_CTAS);
+                    cfg.blockDim = dim3(KB_NT);
+                    cfg.stream = ctx->stream;
+                    cudaLaunchAttribute at[1];
+                    at[0].id = cudaLaunchAttributeClusterDimension;
+                    at[0].val.clusterDim.x = KD_CLUSTER_CTAS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                    cfg.attrs = at;
+                    cfg.numAttrs = 1;
+                    VR_CUDA(cudaLaunchKernelEx(&cfg, k_kd_huge<true>, rec, (const uint32_t *)nstart.p, (const uint32_t *)nend.p,
+                                               (const uint32_t *)(big_list.p + big_off[l]), nb, A.p, B.p, cst.p, cl_min, cl_max));
+                    ctx->stats.kernel_launches++;
+                }
+                const uint32_t skip_from = clus ? cl_min : (huge ? huge_min : 0xffffffffu);
+                VR_LAUNCH(ctx, k_kd_big, nb, KB_NT, 0, rec, nstart.p, nend.p, big_list.p + big_off[l], A.p, B.p, skip_from);
             }
         }
         if (nsub) {
@@ -1075,6 +1125,7 @@ bool pt_build(vrgpu_ctx *ctx, const GroupSet &gs, int bucket, long long pp_thres
     t.nLG = nLG;
     t.nnodes = nnodes;
     t.nbig = big_off.back();
+    t.big_off = big_off;
     t.nsub = nsub;
     return true;
 }
@@ -1100,10 +1151,13 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
         VR_LAUNCH(ctx, k_pt_gather_tree, grid_for(nL, T), T, 0, reinterpret_cast<const KdRec *>(t.rec.p), gs.m.p, slot_of.p, nL, tx.p, ty.p, tz.p, tm.p);
         t.rec.reset();
         VR_LAUNCH(ctx, k_pt_leaf_sums, grid_for(nnodes, T), T, 0, N, nnodes, tx.p, ty.p, tz.p, tm.p);
-        if (t.nbig) VR_LAUNCH(ctx, k_pt_big_sums, 4u * t.nbig, SQ_NT, 0, N, t.big_list.p, tx.p, ty.p, tz.p, tm.p);
         if (t.nsub) {
             VR_CUDA(cudaFuncSetAttribute(k_pt_sub_sums, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PsShared)));
             VR_LAUNCH(ctx, k_pt_sub_sums, t.nsub, PS_NT, sizeof(PsShared), N, t.sub_list.p, t.sub_count.p + 1, tx.p, ty.p, tz.p, tm.p);
+        }
+        for (size_t l = t.big_off.size() - 1; l-- > 0;) { // the nodes above 2048 particles, deepest level first
+            const uint32_t nb = t.big_off[l + 1] - t.big_off[l];
+            if (nb) VR_LAUNCH(ctx, k_pt_big_sums, 4u * nb, SQ_NT, 0, N, t.big_list.p + t.big_off[l], tx.p, ty.p, tz.p, tm.p);
         }
         VR_LAUNCH(ctx, k_pt_cm, grid_for(nnodes, T), T, 0, N, nnodes);
         VR_LAUNCH(ctx, k_pt_bmax, grid_for(nL, T), T, 0, N, rootidx.p, nL, tx.p, ty.p, tz.p);

@@ -18,6 +18,7 @@ struct PtTree {
     DBuf<uint32_t> big_list, sub_list, sub_count; // nodes above 2048 particles (all levels); roots of the subtrees of at most 2048; sub_count[1] = nsub
     uint32_t nbig = 0, nsub = 0;
     std::vector<uint32_t> level_off;            // nodes of level l: [level_off[l], level_off[l + 1])
+    std::vector<uint32_t> big_off;              // nodes above 2048 particles of level l: big_list[big_off[l], big_off[l + 1])
 };
 
 // NBody::KDTree::BuildNodes (NBodylib/src/KDTree/KDTree.cxx:438-507) with MedianPos's own arrangement (:304-337) for every
