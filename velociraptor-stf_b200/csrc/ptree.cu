@@ -889,7 +889,7 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
                                                  const double *__restrict__ tx, const double *__restrict__ ty, const double *__restrict__ tz,
                                                  const double *__restrict__ tm, double G, double eps2, const uint32_t *__restrict__ perm,
                                                  const uint32_t *__restrict__ slot_of, double *__restrict__ phi,
-                                                 unsigned long long *__restrict__ ninter)
+                                                 unsigned long long *__restrict__ ninter, const double2 *__restrict__ tpk /* (x, y), (z, m) per position */)
 {
     unsigned long long st_visits = 0, st_accv = 0, st_accl = 0, st_leaf = 0, st_leafl = 0;
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -897,8 +897,10 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
     const uint32_t myroot = valid ? rootidx[p] : NOCHILD;
     double x = 0, y = 0, z = 0, mj = 0;
     if (valid) { x = tx[p]; y = ty[p]; z = tz[p]; mj = tm[p]; }
+    // acc gathers sum(M / r) without the target's own mass (one DFMA per term; the reference's mj * M / r differs from mj * acc in
+    // the last bit of a term, far inside the 1e-10 the tests ask for); 32-bit count per lane (a lane meets < 2^32 sources)
     double acc = 0.0;
-    unsigned long long cnt = 0;
+    unsigned int cnt = 0;
     unsigned todo = __ballot_sync(0xffffffffu, valid);
     while (todo) {
         const uint32_t root = __shfl_sync(0xffffffffu, myroot, __ffs(todo) - 1);
@@ -918,7 +920,7 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
             const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
             const bool open = act && r2 < b.y;
             if (act && !open) {
-                acc -= mj * (c.x * rsqrt_refined(r2 + eps2));
+                acc = fma(-c.x, rsqrt_refined(r2 + eps2), acc);
                 cnt++;
                 wait = next;
             }
@@ -930,24 +932,34 @@ __global__ void __launch_bounds__(128) k_pt_walk(const PtNode64 *__restrict__ no
             if (left != NOCHILD) { cur = left; continue; }
             if (STATS) { st_leaf += end - start; st_leafl += (unsigned long long)(end - start) * __popc(__ballot_sync(0xffffffffu, open)); }
             for (uint32_t l = start; l < end; l++) {
-                const double lx = __ldg(tx + l), ly = __ldg(ty + l), lz = __ldg(tz + l), lm = __ldg(tm + l);
+                const double2 la = __ldg(tpk + 2 * (size_t)l), lb = __ldg(tpk + 2 * (size_t)l + 1);
                 if (open && l != p) {
-                    const double ax = __dsub_rn(x, lx), ay = __dsub_rn(y, ly), az = __dsub_rn(z, lz);
+                    const double ax = __dsub_rn(x, la.x), ay = __dsub_rn(y, la.y), az = __dsub_rn(z, lb.x);
                     const double q2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)), eps2);
-                    acc -= (mj * lm) * rsqrt_refined(q2);
+                    acc = fma(-lb.y, rsqrt_refined(q2), acc);
                     cnt++;
                 }
             }
             cur = next;
         }
     }
-    if (valid) phi[slot_of[perm[p]]] = acc * G;
-    for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(ninter, cnt);
+    if (valid) phi[slot_of[perm[p]]] = (acc * mj) * G;
+    unsigned long long cntw = cnt;
+    for (int o = 16; o; o >>= 1) cntw += __shfl_xor_sync(0xffffffffu, cntw, o);
+    if ((threadIdx.x & 31) == 0 && cntw) atomicAdd(ninter, cntw);
     if (STATS && (threadIdx.x & 31) == 0) {
         atomicAdd(ninter + 1, st_visits); atomicAdd(ninter + 2, st_accv); atomicAdd(ninter + 3, st_accl);
         atomicAdd(ninter + 4, st_leaf); atomicAdd(ninter + 5, st_leafl);
     }
+}
+
+__global__ void k_pt_pack_targets(const double *__restrict__ tx, const double *__restrict__ ty, const double *__restrict__ tz, const double *__restrict__ tm,
+                                  uint32_t nL, double2 *__restrict__ tpk)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nL) return;
+    tpk[2 * (size_t)p] = make_double2(tx[p], ty[p]);
+    tpk[2 * (size_t)p + 1] = make_double2(tz[p], tm[p]);
 }
 
 // tree-ordered columns: coordinates straight from the build's records, the mass through the member index
@@ -1177,12 +1189,14 @@ void potential_tree(vrgpu_ctx *ctx, const GroupSet &gs, double G, double eps, do
             if (n1 > n0) VR_LAUNCH(ctx, k_pt_next, grid_for(n1 - n0, T), T, 0, nleft.p, next.p, n0, n1);
         }
         VR_LAUNCH(ctx, k_pt_pack, grid_for(nnodes, T), T, 0, N, next.p, nnodes, packed.p);
+        DBuf<double2> tpk(ctx, 2 * (size_t)nL);
+        VR_LAUNCH(ctx, k_pt_pack_targets, grid_for(nL, T), T, 0, tx.p, ty.p, tz.p, tm.p, nL, tpk.p);
         if (walk_stats)
             VR_LAUNCH(ctx, k_pt_walk<true>, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
-                      phi, ninter.p);
+                      phi, ninter.p, tpk.p);
         else
             VR_LAUNCH(ctx, k_pt_walk<false>, grid_for(nL, 128), 128, 0, packed.p, rootidx.p, nL, tx.p, ty.p, tz.p, tm.p, G, eps * eps, perm.p, slot_of.p,
-                      phi, ninter.p);
+                      phi, ninter.p, tpk.p);
     }
     unsigned long long hs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     VR_CUDA(cudaMemcpyAsync(hs, ninter.p, sizeof(hs), cudaMemcpyDeviceToHost, ctx->stream));
