@@ -962,9 +962,11 @@ __global__ void k_adjust_period(double *__restrict__ pos, const long long *__res
 __global__ void k_group_minpid(const long long *__restrict__ pfof, const long long *__restrict__ pid, size_t n, unsigned long long *__restrict__ minpid)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    long long g = pfof[i];
-    if (g > 0) atomicMin(&minpid[g], (unsigned long long)pid[i]);
+    const long long g = i < n ? pfof[i] : 0ll;
+    const bool on = g > 0;
+    const unsigned peers = __match_any_sync(0xffffffffu, on ? (unsigned long long)g : 0ull); // one atomic per (warp, group)
+    const unsigned long long mn = warp_min_u64(peers, on ? (unsigned long long)pid[i] : ~0ull);
+    if (on && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) atomicMin(&minpid[g], mn);
 }
 __global__ void k_group_first_by_pid(const long long *__restrict__ pfof, const long long *__restrict__ pid, size_t n,
                                      const unsigned long long *__restrict__ minpid, uint32_t *__restrict__ first)

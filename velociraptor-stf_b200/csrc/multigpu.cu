@@ -237,11 +237,18 @@ __global__ void k_mg_union(const uint32_t *__restrict__ cidx, uint32_t nedges, u
 __global__ void k_mg_comp_stats(const uint32_t *__restrict__ comp, const long long *__restrict__ pid, size_t n_own, uint32_t *__restrict__ csize,
                                 unsigned long long *__restrict__ cminpid)
 {
+    // neighbours in the caller's array are usually neighbours in space (a snapshot is written domain by domain): one atomic per
+    // (warp, component) instead of one per particle -- a 10^6-member component was 10^6 atomics on one address
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_own) return;
-    const uint32_t c = comp[i];
-    atomicAdd(&csize[c], 1u);
-    atomicMin(&cminpid[c], pid ? (unsigned long long)pid[i] : (unsigned long long)i);
+    const bool valid = i < n_own;
+    const uint32_t c = valid ? comp[i] : 0xffffffffu;
+    const unsigned long long v = valid ? (pid ? (unsigned long long)pid[i] : (unsigned long long)i) : ~0ull;
+    const unsigned peers = __match_any_sync(0xffffffffu, c);
+    const unsigned long long mn = warp_min_u64(peers, v);
+    if (valid && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+        atomicAdd(&csize[c], (uint32_t)__popc(peers));
+        atomicMin(&cminpid[c], mn);
+    }
 }
 // per boundary entry owned by this rank: its local size / min pid; bidx[cell] = compact id
 __global__ void k_mg_boundary_contrib(const uint64_t *__restrict__ U, uint32_t nU, uint64_t rank, const uint32_t *__restrict__ csize,
@@ -690,11 +697,14 @@ __global__ void k_mg_remap_ids(long long *__restrict__ pfw, size_t n, const uint
 __global__ void k_mg_final_stats(const long long *__restrict__ pfw, const long long *__restrict__ pid, size_t n, uint64_t *__restrict__ rec)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const long long g = pfw[i];
-    if (g <= 0) return;
-    atomicAdd((unsigned long long *)&rec[3 * (size_t)(g - 1)], 1ull);
-    atomicMin((unsigned long long *)&rec[3 * (size_t)(g - 1) + 1], (unsigned long long)pid[i]);
+    const long long g = i < n ? pfw[i] : 0ll;
+    const bool on = g > 0;
+    const unsigned peers = __match_any_sync(0xffffffffu, on ? (unsigned long long)g : 0ull); // one atomic per (warp, group)
+    const unsigned long long mn = warp_min_u64(peers, on ? (unsigned long long)pid[i] : ~0ull);
+    if (on && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+        atomicAdd((unsigned long long *)&rec[3 * (size_t)(g - 1)], (unsigned long long)__popc(peers));
+        atomicMin((unsigned long long *)&rec[3 * (size_t)(g - 1) + 1], mn);
+    }
 }
 __global__ void k_mg_init_final_rec(uint64_t *__restrict__ rec, uint32_t ng)
 {
@@ -746,9 +756,11 @@ __global__ void k_mg_scatter_back_phase(const uint64_t *__restrict__ in, const u
 __global__ void k_mg_group_minpid(const long long *__restrict__ pfof, const long long *__restrict__ pid, size_t n, unsigned long long *__restrict__ minpid)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const long long g = pfof[i];
-    if (g > 0) atomicMin(&minpid[g], (unsigned long long)(pid ? pid[i] : (long long)i));
+    const long long g = i < n ? pfof[i] : 0ll;
+    const bool on = g > 0;
+    const unsigned peers = __match_any_sync(0xffffffffu, on ? (unsigned long long)g : 0ull); // one atomic per (warp, group)
+    const unsigned long long mn = warp_min_u64(peers, on ? (unsigned long long)(pid ? pid[i] : (long long)i) : ~0ull);
+    if (on && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) atomicMin(&minpid[g], mn);
 }
 __global__ void k_mg_ref_pos(const long long *__restrict__ pfof, const long long *__restrict__ pid, const double *__restrict__ pos, size_t n,
                              const unsigned long long *__restrict__ minpid, double *__restrict__ refpos)
