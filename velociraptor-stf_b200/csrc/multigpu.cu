@@ -28,6 +28,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <memory>
 #include <cmath>
 #include <numeric>
 
@@ -849,7 +850,10 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
     }
     VR_REQUIRE(P.has_vel, VRGPU_EINVAL, "6DFOF / unbinding need velocities");
     KScope kall(ctx, "mg.consolidate_total");
+    // phase timers (each replaces the previous one: the scope ends where the next begins)
+    std::unique_ptr<KScope> cphase(new KScope(ctx, "mg.c.place"));
     mg_place_groups(ctx, A, n_own, o);
+    cphase.reset(); cphase.reset(new KScope(ctx, "mg.c.pack"));
 
     // ---- consolidate every boundary group on the rank of its root label (MPIGroupExchange) ----
     std::vector<DBuf<uint32_t>> eidx(N);
@@ -872,6 +876,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
                           P.has_pid ? P.pid.p : (const long long *)nullptr, A.pfof.p, fl.p, ex.p, n_own, eidx[d].p, ebuf[d].p);
         }
     }
+    cphase.reset(); cphase.reset(new KScope(ctx, "mg.c.exchange"));
     std::vector<unsigned long long> allcnt = allgather_host<unsigned long long>(ctx, ecnt.data(), N); // allcnt[src*N + dst]
     size_t n_imp = 0;
     std::vector<size_t> ioff(N, 0);
@@ -886,6 +891,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
     }
     VR_NCCL(nccl_api().GroupEnd());
 
+    cphase.reset(); cphase.reset(new KScope(ctx, "mg.c.workset"));
     // ---- working set: owned particles (exported ones unlabelled) + imported ----
     const size_t n_w = n_own + n_imp;
     DeviceParticles W;
@@ -931,6 +937,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
         if (n_w) VR_LAUNCH(ctx, k_mg_remap_ids, grid_for(n_w, T), T, 0, pfw.p, n_w, present.p, excl.p);
     }
 
+    cphase.reset();
     // ---- the single-GPU stages on the consolidated groups ----
     long long ngl = nloc;
     if (ngl > 0 && !wb) { // (with wb every group has been adjusted in P already, by the same rule)
@@ -953,6 +960,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
         ctx->stats.n_marginal = nmarg;
     }
 
+    cphase.reset(new KScope(ctx, "mg.c.renumber"));
     // ---- global renumbering of the surviving groups ----
     GlobalOrder O;
     {
@@ -966,6 +974,7 @@ void mg_search(vrgpu_ctx *ctx, DeviceParticles &P, double slab_lo, double slab_h
     }
     ngroups = O.total;
 
+    cphase.reset(); cphase.reset(new KScope(ctx, "mg.c.return"));
     // ---- labels of imported particles go home; after a 6DFOF, with wb, their rewritten coordinates as well ----
     pfof_out.alloc(ctx, n_own + 1);
     if (n_own) VR_CUDA(cudaMemcpyAsync(pfof_out.p, pfw.p, n_own * sizeof(long long), cudaMemcpyDeviceToDevice, ctx->stream));
