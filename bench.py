@@ -530,6 +530,9 @@ def run_ours_multi(args, rank, world, local):
         # per-rank device time of the placed per-group stages: the imbalance the placement leaves
         heavy = ("potential.tree", "potential.direct", "fof6d.link", "fof6d.dispersion", "mg.consolidate_total", "mg.fof3d_total")
         per_rank = {k: [round(g[1].get(k, 0.0), 3) for g in gathered] for k in heavy if any(g[1].get(k, 0.0) > 0 for g in gathered)}
+        # every timer: the slowest rank and its time (what the step waits for at the next collective)
+        names = sorted({k for g in gathered for k in g[1]})
+        slowest = {k: [int(np.argmax([g[1].get(k, 0.0) for g in gathered])), round(max(g[1].get(k, 0.0) for g in gathered), 3)] for k in names}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": workload_config(args),
@@ -539,7 +542,7 @@ def run_ours_multi(args, rank, world, local):
                         "d2h_bytes_per_step": int(tot[2].item()), "ms_per_step": float(np.mean(e2e)), "ngroups": ng_e,
                         "membership_hash": "%016x" % he2e,
                         "buffers": "page-locked records, reused page-locked pfof_out" if pinned else "pageable records, fresh pageable pfof_out per call"},
-                "gpu_launches": int(tot[0].item()), "clocks": clocks, "roofline": roof, "kernel_ms_rank0": kms, "kernel_ms_per_rank": per_rank,
+                "gpu_launches": int(tot[0].item()), "clocks": clocks, "roofline": roof, "kernel_ms_rank0": kms, "kernel_ms_per_rank": per_rank, "kernel_ms_slowest_rank": slowest,
                 "cpu_baseline": None}
         emit(line)
     ctx.close()

@@ -22,8 +22,8 @@ for s in "$@"; do
     zz) timeout 600 python -m pytest tests/test_zz_no_alloc.py -q -m gpu --tb=short -p no:cacheprovider > gpurun_out/zz_pytest.log 2>&1; tail -15 gpurun_out/zz_pytest.log ;;
     new) timeout 1200 python -m pytest tests/test_gpu_dropin.py tests/test_gpu_stf_files.py tests/test_zz_no_alloc.py -q -m gpu --tb=short -s -p no:cacheprovider > gpurun_out/new_pytest.log 2>&1; tail -40 gpurun_out/new_pytest.log ;;
     mg) for w in ${MG_WORLDS:-2 4 8}; do n=$(nvidia-smi -L | wc -l); [ $w -le $n ] || continue; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node=$w --master-addr 127.0.0.1 --master-port 29541 tests/dist/mg_check.py ${MG_NSIDE:-128} 2>&1 | grep -v "^W\|^\*" | tee gpurun_out/r02_mg${w}_check.log | tail -8; done ;;
-    final) timeout 900 python bench.py > gpurun_out/r02j_bench_default.json 2> gpurun_out/r02j_bench_default.err; python tools/bench_summary.py gpurun_out/r02j_bench_default.json 2>/dev/null | head -30; tail -3 gpurun_out/r02j_bench_default.err ;;
-    refarm) timeout 900 python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/r02j_bench_reference.json 2> gpurun_out/r02j_bench_reference.err; cut -c1-400 gpurun_out/r02j_bench_reference.json; tail -3 gpurun_out/r02j_bench_reference.err ;;
+    final) timeout 900 python bench.py > gpurun_out/r02l_bench_default.json 2> gpurun_out/r02l_bench_default.err; python tools/bench_summary.py gpurun_out/r02l_bench_default.json 2>/dev/null | head -30; tail -3 gpurun_out/r02l_bench_default.err ;;
+    refarm) timeout 900 python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/r02l_bench_reference.json 2> gpurun_out/r02l_bench_reference.err; cut -c1-400 gpurun_out/r02l_bench_reference.json; tail -3 gpurun_out/r02l_bench_reference.err ;;
     ncuwalk) bash tools/ncu_kernel.sh r02j_walk k_pt_walk 1 --nside 256 ;;
     *) echo "unknown section $s" ;;
   esac
