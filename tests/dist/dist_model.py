@@ -138,6 +138,48 @@ def main():
         ok = bool(np.array_equal(full, want)) and len(allrec) == ngw
         print(f"[dist_model] world={world} nside={nside} groups={len(allrec)} oracle={ngw} boundary comps={len(U)} edges={len(alle)} -> {'OK' if ok else 'FAIL'}")
 
+    # ---- AdjustStructureForPeriod without moving a particle (mg_adjust_global): the reference particle of a group is its member
+    #      with the smallest pid; its position reaches every rank through an all-reduce MIN of the pid and an all-reduce SUM of a
+    #      table that only the owner of that pid fills (x + 0 is exact); every member is then shifted by whole periods as
+    #      search.cxx:871-887 does.  Result: the single-domain oracle's coordinates, bit for bit (pids ascend with the index here). ----
+    import torch
+    Gall = len(allrec)
+    minpid = torch.full((Gall + 1,), np.iinfo(np.int64).max, dtype=torch.int64)
+    for i in range(n_own):
+        if pf[i] > 0 and pid[i] < minpid[pf[i]]:
+            minpid[pf[i]] = int(pid[i])
+    dist.all_reduce(minpid, op=dist.ReduceOp.MIN)
+    refpos = torch.zeros((Gall + 1, 3), dtype=torch.float64)
+    mp = minpid.numpy()
+    for i in range(n_own):
+        if pf[i] > 0 and pid[i] == mp[pf[i]]:
+            refpos[pf[i]] = torch.from_numpy(pos[i].copy())
+    dist.all_reduce(refpos, op=dist.ReduceOp.SUM)
+    rp = refpos.numpy()
+    adj = pos.copy()
+    for i in range(n_own):
+        g = pf[i]
+        if g <= 0:
+            continue
+        for k in range(3):
+            diff = rp[g, k] - adj[i, k]
+            if diff < -0.5 * L:
+                adj[i, k] = adj[i, k] - L
+            elif diff > 0.5 * L:
+                adj[i, k] = adj[i, k] + L
+    abox = [None] * world
+    dist.all_gather_object(abox, (own, adj))
+    if rank == 0:
+        fullpos = np.array(d["pos"], dtype=np.float64, copy=True)
+        for o, a in abox:
+            fullpos[o] = a
+        wantpos = orc.adjust_for_period(d["pos"], L, want, ngw)
+        same_pos = bool(np.array_equal(fullpos, wantpos))
+        nmoved = int(np.count_nonzero(np.any(fullpos != d["pos"], axis=1)))
+        print(f"[dist_model] period adjustment over {world} ranks: {nmoved} particles moved, coordinates identical to the single-domain oracle: {same_pos} "
+              f"-> {'OK' if same_pos else 'FAIL'}")
+        ok = ok and same_pos
+
     # ---- placement of the per-group stages (mg_place_groups): straddling or costly groups to the least loaded rank in
     #      size order, small single-rank groups stay; then consolidation, unbinding per group, global renumbering ----
     G = len(allrec)
