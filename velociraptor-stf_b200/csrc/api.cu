@@ -255,6 +255,7 @@ void vrgpu_destroy(vrgpu_ctx *ctx)
     ctx->pool.release_all();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    for (int k = 0; k < 4; k++) if (ctx->aux_stream[k]) cudaStreamDestroy(ctx->aux_stream[k]);
     for (int k = 0; k < 2; k++) if (ctx->stage_host[k]) cudaFreeHost(ctx->stage_host[k]);
     for (int k = 0; k < 3; k++) if (ctx->up_host[k]) cudaFreeHost(ctx->up_host[k]);
     cudaStreamDestroy(ctx->stream);

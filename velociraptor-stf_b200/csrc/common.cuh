@@ -111,6 +111,7 @@ struct vrgpu_ctx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr; // host->device staging copies, overlapped with the unpack kernel
+    cudaStream_t aux_stream[4] = {nullptr, nullptr, nullptr, nullptr}; // side streams: independent per-group work beside the main stream (fof6d dispersion)
     void *stage_host[2] = {nullptr, nullptr}; // page-locked staging for results that go to pageable caller memory
     static constexpr size_t UP_HOST_BYTES = (size_t)32 << 20;
     void *up_host[3] = {nullptr, nullptr, nullptr}; // page-locked staging for particle records that come from pageable caller memory

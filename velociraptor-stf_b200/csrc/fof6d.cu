@@ -1010,6 +1010,8 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
             const unsigned grid = std::max(1u, std::min<unsigned>(grid_for((size_t)G * 32, T), (unsigned)ctx->sm_count * 8u));
             // the groups come in size order: the leading ones (at most 64) may take the many-window path
             uint32_t nskip = 0;
+            bool big_done = false;
+            static const int nside_streams = [] { const char *e = getenv("VRGPU_DISP_STREAMS"); return e ? std::max(0, std::min(4, atoi(e))) : 4; }();
             if (multi_min > 0) {
                 const uint32_t look = std::min<uint32_t>(G, 64u);
                 std::vector<uint32_t> hoff((size_t)look + 2);
@@ -1022,21 +1024,69 @@ long long fof6d_device(vrgpu_ctx *ctx, DeviceParticles &P, const long long *pfof
                 while (elig < look && (long long)(hoff[elig + 2] - hoff[elig + 1]) >= multi_min) elig++;
                 double best = 14.6e-6 * (double)(hoff[2] - hoff[1]), acc = 0.0;
                 for (uint32_t k = 1; k <= elig; k++) {
-                    acc += 5.3e-6 * (double)(hoff[k + 1] - hoff[k]) + 0.15;
+                    // (on side streams the groups overlap: about half their serial cost is hidden -- profiles/r02_dispersion.md)
+                    acc += (5.3e-6 * (double)(hoff[k + 1] - hoff[k]) + 0.15) * (nside_streams >= 2 ? 0.5 : 1.0);
                     const double rest = k < look ? 14.6e-6 * (double)(hoff[k + 2] - hoff[k + 1]) : 0.0;
                     if (acc + rest < best) { best = acc + rest; nskip = k; }
                 }
                 if (nskip) {
-                    prepare_multi((unsigned long long)(hoff[2] - hoff[1]));
-                    for (uint32_t g = 1; g <= nskip; g++) {
-                        const uint32_t s0 = hoff[g];
-                        dispersion_multi(ctx, sc, seqr, gs.vx.p + s0, gs.vy.p + s0, gs.vz.p + s0, gs.m.p + s0, (unsigned long long)(hoff[g + 1] - s0),
-                                         vfac, false, 0.0, g, 1u, vs2.p);
+                    // The groups of the many-window path are independent of each other and of the one-CTA-per-group kernel: they go
+                    // round robin to side streams (each with its own scratch), the kernel for the remaining groups runs on the
+                    // context's stream meanwhile, and the context's stream waits for the side streams at the end.  The serial parts of
+                    // a group (window prefix, the walker) then overlap with the parallel parts of the others.
+                    const int NS = (int)std::min<uint32_t>((uint32_t)nside_streams, nskip);
+                    if (NS >= 2) {
+                        SeqScratch scs[4];
+                        DBuf<double> rs[4];
+                        cudaEvent_t ready = KScope::get(ctx), done[4] = {nullptr, nullptr, nullptr, nullptr};
+                        VR_REQUIRE(ready != nullptr, VRGPU_ECUDA, "event creation failed");
+                        for (int k = 0; k < NS; k++) {
+                            if (!ctx->aux_stream[k]) VR_CUDA(cudaStreamCreateWithFlags(&ctx->aux_stream[k], cudaStreamNonBlocking));
+                            const unsigned long long nmax = hoff[k + 2] - hoff[k + 1]; // the largest group this stream gets (sizes descend)
+                            scs[k].cap = (unsigned)((3ull * nmax + SQ_W - 1) / SQ_W);
+                            scs[k].wsum.alloc(ctx, scs[k].cap); scs[k].start.alloc(ctx, scs[k].cap); scs[k].spec.alloc(ctx, scs[k].cap);
+                            scs[k].nslow.alloc(ctx, 1);
+                            rs[k].alloc(ctx, 8);
+                            VR_CUDA(cudaMemsetAsync(scs[k].nslow.p, 0, sizeof(unsigned int), ctx->stream));
+                            VR_CUDA(cudaMemsetAsync(rs[k].p, 0, 8 * sizeof(double), ctx->stream));
+                            done[k] = KScope::get(ctx);
+                            VR_REQUIRE(done[k] != nullptr, VRGPU_ECUDA, "event creation failed");
+                        }
+                        VR_CUDA(cudaEventRecord(ready, ctx->stream)); // the columns and the cleared scratch
+                        cudaStream_t main_stream = ctx->stream;
+                        struct Restore { vrgpu_ctx *c; cudaStream_t s; ~Restore() { c->stream = s; } } restore{ctx, main_stream};
+                        for (int k = 0; k < NS; k++) VR_CUDA(cudaStreamWaitEvent(ctx->aux_stream[k], ready, 0));
+                        for (uint32_t g = 1; g <= nskip; g++) {
+                            const int k = (int)((g - 1) % (uint32_t)NS);
+                            const uint32_t s0 = hoff[g];
+                            ctx->stream = ctx->aux_stream[k]; // the launches of dispersion_multi go to the side stream
+                            dispersion_multi(ctx, scs[k], rs[k], gs.vx.p + s0, gs.vy.p + s0, gs.vz.p + s0, gs.m.p + s0, (unsigned long long)(hoff[g + 1] - s0),
+                                             vfac, false, 0.0, g, 1u, vs2.p);
+                            ctx->stream = main_stream;
+                        }
+                        for (int k = 0; k < NS; k++) VR_CUDA(cudaEventRecord(done[k], ctx->aux_stream[k]));
+                        VR_LAUNCH(ctx, k_group_dispersion_big, G, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, vfac, vs2.p, nskip);
+                        VR_LAUNCH(ctx, k_group_dispersion, grid, T, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, G, vfac, vs2.p);
+                        for (int k = 0; k < NS; k++) VR_CUDA(cudaStreamWaitEvent(ctx->stream, done[k], 0));
+                        // the scratch goes back to the pool (ordered on the context's stream) only behind those waits
+                        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+                        ctx->evpool.push_back(ready);
+                        for (int k = 0; k < NS; k++) ctx->evpool.push_back(done[k]);
+                        big_done = true;
+                    } else {
+                        prepare_multi((unsigned long long)(hoff[2] - hoff[1]));
+                        for (uint32_t g = 1; g <= nskip; g++) {
+                            const uint32_t s0 = hoff[g];
+                            dispersion_multi(ctx, sc, seqr, gs.vx.p + s0, gs.vy.p + s0, gs.vz.p + s0, gs.m.p + s0, (unsigned long long)(hoff[g + 1] - s0),
+                                             vfac, false, 0.0, g, 1u, vs2.p);
+                        }
                     }
                 }
             }
-            VR_LAUNCH(ctx, k_group_dispersion_big, G, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, vfac, vs2.p, nskip);
-            VR_LAUNCH(ctx, k_group_dispersion, grid, T, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, G, vfac, vs2.p);
+            if (!big_done) {
+                VR_LAUNCH(ctx, k_group_dispersion_big, G, SQ_NT, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, vfac, vs2.p, nskip);
+                VR_LAUNCH(ctx, k_group_dispersion, grid, T, 0, gs.vx.p, gs.vy.p, gs.vz.p, gs.m.p, gs.off.p, G, vfac, vs2.p);
+            }
         }
     }
 
