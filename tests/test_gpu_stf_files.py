@@ -5,8 +5,9 @@ snapshot, comparing what north_star says must stay unchanged: .fof.grp (src/io.c
 
 Settings: examples/sample_dmcosmological_run.cfg of the reference (values restated below), with ASCII output (the compiled
 reference has no HDF5) and the group array file switched on.  Cases: the 3DFOF halo catalogue alone (BASELINE configs[0]), 6DFOF
-field halos, and the stock sample with the substructure search on (SearchSubSub -> CheckUnboundGroups with group flags and with
-ireorder = 0, GetVelocityDensity, BuildPGList from the routed call sites).
+field halos, the substructure search (SearchSubSub: GetVelocityDensity, BuildNumInGroup / BuildPGList from the routed call sites)
+without its unbinding step -- every file identical -- and the stock sample, whose unbinding (CheckUnboundGroups with group flags
+and with ireorder = 0) runs into the reference's quirk Q10 and is compared to a stated tolerance.
 
 Canonicalisation: group ids of equal-size groups may come in another order (quirk Q5: the reference's order among equal sizes is
 its heap's), so groups are matched through their smallest particle id; everything else is compared as written."""
